@@ -1,0 +1,86 @@
+"""bf16 GEMM on tcgen05 tensor cores (csrc/gemm/gemm_bf16.cu) + autograd-aware linear.
+
+`linear(x, w)` is the replacement for F.linear on the training path (reference:
+deepspeed/runtime/zero/linear.py:43-112 LinearFunctionForZeroStage3 -> cuBLAS).  Forward,
+dgrad and wgrad each map to one layout variant of the same kernel; wgrad can accumulate
+directly into an fp32 main-grad buffer with TMA reduce-add.
+"""
+import torch
+
+from . import native
+
+
+def _gemm_ref(a, b, a_mn, b_mn, out_dtype, out=None, accumulate=False):
+    A = a.t() if a_mn else a
+    Bt = b if b_mn else b.t()
+    r = (A.float() @ Bt.float())
+    if out is None:
+        return r.to(out_dtype)
+    if accumulate:
+        out.add_(r.to(out.dtype))
+    else:
+        out.copy_(r.to(out.dtype))
+    return out
+
+
+def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, accumulate=False, max_ctas=0):
+    """C = A @ B^T-style product.
+
+    a: [M,K] (a_mn=False) or stored [K,M] (a_mn=True);  b: [N,K] (b_mn=False) or stored [K,N] (b_mn=True).
+    Returns / fills C[M,N].  accumulate=True performs C += A*B (needs `out`).
+    """
+    if not a.is_cuda:
+        return _gemm_ref(a, b, a_mn, b_mn, out_dtype if out is None else out.dtype, out, accumulate)
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16, "bf16 operands required"
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn else (b.shape[0], b.shape[1])
+    assert K == Kb, f"K mismatch {K} vs {Kb}"
+    if out is None:
+        assert not accumulate
+        out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    f32 = out.dtype == torch.float32
+    mode = (2 if accumulate else 1) if f32 else (3 if accumulate else 0)
+    rc = native.lib().dsb200_gemm_bf16(native.ptr(a), native.ptr(b), native.ptr(out), M, N, K, a.stride(0),
+                                       b.stride(0), out.stride(0), int(a_mn), int(b_mn), mode, int(max_ctas),
+                                       native.stream_ptr())
+    native.check(rc)
+    return out
+
+
+class _LinearFn(torch.autograd.Function):
+
+    @staticmethod
+    def forward(ctx, x, w, main_grad):
+        ctx.save_for_backward(x, w)
+        ctx.main_grad = main_grad
+        x2 = x.reshape(-1, x.shape[-1])
+        y = gemm(x2, w)
+        return y.view(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        x2 = x.reshape(-1, x.shape[-1])
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, w, b_mn=True).view_as(x)
+        if ctx.needs_input_grad[1]:
+            mg = ctx.main_grad
+            if mg is not None:
+                # fused gradient accumulation: dW is reduced into the fp32 main grad by the epilogue
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
+                dw = None
+            else:
+                dw = gemm(dy2, x2, a_mn=True, b_mn=True)
+        return dx, dw, None
+
+
+def linear(x, w, main_grad=None):
+    """y = x @ w.T with w: [out, in].  If `main_grad` (fp32 [out,in]) is given, backward accumulates
+    the weight gradient into it and returns no .grad for w."""
+    return _LinearFn.apply(x, w, main_grad)
