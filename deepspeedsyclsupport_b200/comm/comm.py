@@ -1,0 +1,414 @@
+"""`deepspeed.comm`-compatible communication façade.
+
+Free functions with torch.distributed signatures, routed to one backend: torch.distributed over NCCL
+(NVLink-5 / NVSwitch) on GPUs, gloo on hosts.  Every op goes through `timed_op`, which feeds the comms
+logger (latency, message size, algbw/busbw, straggler analysis).  The fused compute+collective kernels in
+`parallel/` bypass this layer on purpose -- they move bytes over peer memory from inside the compute kernel;
+this façade is the plumbing and the measured baseline.
+
+Parity: deepspeed/comm/comm.py:101-134 (timed_op), :221-601 (ops), :604-670 (init_distributed),
+:673-771 (MPI/AML env discovery); deepspeed/comm/torch.py:99-368 (TorchBackend).
+"""
+import os
+import time
+from datetime import timedelta
+from enum import Enum
+
+import torch
+import torch.distributed as tdist
+
+from ..accelerator import get_accelerator
+from ..utils.comms_logging import CommsLogger, get_caller_func
+from ..utils.logging import logger
+from .reduce_op import ReduceOp
+
+DEFAULT_PG_TIMEOUT = timedelta(minutes=int(os.getenv("DEEPSPEED_TIMEOUT", default=30)))
+TORCH_DISTRIBUTED_DEFAULT_PORT = 29500
+
+comms_logger = CommsLogger()
+timer_summary = {}
+_initialized_here = False
+
+# capability probes the reference exposes
+def has_all_gather_into_tensor():
+    return hasattr(tdist, "all_gather_into_tensor")
+
+
+def has_reduce_scatter_tensor():
+    return hasattr(tdist, "reduce_scatter_tensor")
+
+
+def has_all_reduce_coalesced():
+    return hasattr(tdist, "all_reduce_coalesced")
+
+
+def has_coalescing_manager():
+    return hasattr(tdist.distributed_c10d, "_coalescing_manager")
+
+
+class ProcessGroup:  # typing alias only
+    pass
+
+
+def _op(op):
+    if isinstance(op, ReduceOp):
+        return {
+            ReduceOp.SUM: tdist.ReduceOp.SUM,
+            ReduceOp.PRODUCT: tdist.ReduceOp.PRODUCT,
+            ReduceOp.MIN: tdist.ReduceOp.MIN,
+            ReduceOp.MAX: tdist.ReduceOp.MAX,
+            ReduceOp.BAND: tdist.ReduceOp.BAND,
+            ReduceOp.BOR: tdist.ReduceOp.BOR,
+            ReduceOp.BXOR: tdist.ReduceOp.BXOR,
+            ReduceOp.AVG: tdist.ReduceOp.AVG,
+        }[op]
+    return op
+
+
+def _msg_size(args, kwargs, name):
+    """Bytes moved by the call (first tensor-like argument; lists are summed)."""
+    cand = None
+    for a in list(args) + list(kwargs.values()):
+        if torch.is_tensor(a):
+            cand = a
+            break
+        if isinstance(a, (list, tuple)) and a and torch.is_tensor(a[0]):
+            return sum(t.numel() * t.element_size() for t in a)
+    if cand is None:
+        return 0
+    return cand.numel() * cand.element_size()
+
+
+def timed_op(func):
+    """Profile a collective when the comms logger is enabled (device-synchronised wall time)."""
+
+    def log_wrapper(*args, **kwargs):
+        prof = comms_logger.enabled and (comms_logger.prof_all or kwargs.get("prof", False)
+                                         or func.__name__ in comms_logger.prof_ops
+                                         or kwargs.get("log_name", None) in comms_logger.prof_ops)
+        log_name = kwargs.pop("log_name", func.__name__)
+        kwargs.pop("prof", None)
+        debug = kwargs.pop("debug", None)
+        if not prof:
+            return func(*args, **kwargs)
+        acc = get_accelerator()
+        acc.synchronize()
+        t0 = time.perf_counter()
+        try:
+            return func(*args, **kwargs)
+        finally:
+            handle_async = kwargs.get("async_op", False)
+            if not handle_async:
+                acc.synchronize()
+            dt_ms = (time.perf_counter() - t0) * 1e3
+            name = log_name if not (comms_logger.debug and debug) else f"{log_name} | [Caller Func: {debug}]"
+            grp = kwargs.get("group", None)
+            comms_logger.append(func.__name__, name, dt_ms, _msg_size(args, kwargs, func.__name__), get_world_size(grp))
+
+    log_wrapper.__name__ = func.__name__
+    log_wrapper.__doc__ = func.__doc__
+    return log_wrapper
+
+
+def configure(deepspeed_config=None, enabled=None, prof_all=None, prof_ops=None, verbose=None, debug=None):
+    if deepspeed_config is not None:
+        comms_logger.configure(deepspeed_config.comms_config)
+    if enabled is not None:
+        comms_logger.enabled = enabled
+    if prof_all is not None:
+        comms_logger.prof_all = prof_all
+    if prof_ops is not None:
+        comms_logger.prof_ops = prof_ops
+    if verbose is not None:
+        comms_logger.verbose = verbose
+    if debug is not None:
+        comms_logger.debug = debug
+
+
+def log_summary(show_straggler=False):
+    barrier(log_name="log_summary_barrier") if is_initialized() else None
+    out = None
+    if not is_initialized() or get_rank() == 0:
+        out = comms_logger.log_all(print_log=True, show_straggler=False)
+    elif show_straggler:
+        comms_logger.log_all(print_log=False, show_straggler=True)
+    if show_straggler and (not is_initialized() or get_rank() == 0):
+        out = comms_logger.log_all(print_log=True, show_straggler=True)
+    barrier(log_name="log_summary_barrier") if is_initialized() else None
+    return out
+
+
+# ----------------------------------------------------------------------------- state
+def is_initialized():
+    return tdist.is_available() and tdist.is_initialized()
+
+
+def is_available():
+    return tdist.is_available()
+
+
+def destroy_process_group(group=None):
+    if is_initialized():
+        tdist.destroy_process_group(group)
+
+
+def new_group(ranks=None, **kwargs):
+    return tdist.new_group(ranks=ranks, **kwargs)
+
+
+def get_rank(group=None):
+    return tdist.get_rank(group) if is_initialized() else 0
+
+
+def get_world_size(group=None):
+    return tdist.get_world_size(group) if is_initialized() else 1
+
+
+def get_local_rank():
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def get_global_rank(group=None, group_rank=0):
+    if group is None or not is_initialized():
+        return group_rank
+    return tdist.get_global_rank(group, group_rank)
+
+
+def get_world_group():
+    return tdist.group.WORLD if is_initialized() else None
+
+
+_get_world_group = get_world_group
+
+
+def get_all_ranks_from_group(group=None):
+    if not is_initialized():
+        return [0]
+    return tdist.get_process_group_ranks(group if group is not None else tdist.group.WORLD)
+
+
+def get_backend(group=None):
+    return tdist.get_backend(group)
+
+
+# ----------------------------------------------------------------------------- collectives
+@timed_op
+def broadcast(tensor, src, group=None, async_op=False):
+    return tdist.broadcast(tensor, src=src, group=group, async_op=async_op)
+
+
+@timed_op
+def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
+    return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=async_op)
+
+
+@timed_op
+def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
+    """Low-latency all-reduce entry point for TP inference (reference: ccl.cpp:540-611 SHM all-reduce on CPU).
+    On B200 the fused GEMM->all-reduce kernel in parallel/fused is the fast path; this is the NCCL form."""
+    return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=async_op)
+
+
+@timed_op
+def all_reduce_coalesced(tensors, op=ReduceOp.SUM, group=None, async_op=False):
+    flat = torch._utils._flatten_dense_tensors(tensors)
+    h = tdist.all_reduce(flat, op=_op(op), group=group, async_op=False)
+    for t, f in zip(tensors, torch._utils._unflatten_dense_tensors(flat, tensors)):
+        t.copy_(f)
+    return h
+
+
+@timed_op
+def reduce(tensor, dst, op=ReduceOp.SUM, group=None, async_op=False):
+    return tdist.reduce(tensor, dst=dst, op=_op(op), group=group, async_op=async_op)
+
+
+@timed_op
+def reduce_scatter(output, input_list, op=ReduceOp.SUM, group=None, async_op=False):
+    return tdist.reduce_scatter(output, input_list, op=_op(op), group=group, async_op=async_op)
+
+
+@timed_op
+def reduce_scatter_tensor(output_tensor, tensor, op=ReduceOp.SUM, group=None, async_op=False):
+    if tdist.get_backend(group) == "gloo":
+        # gloo has no reduce_scatter: all-reduce a copy and keep this rank's slice (host plumbing path only)
+        tmp = tensor.clone()
+        tdist.all_reduce(tmp, op=_op(op) if _op(op) != tdist.ReduceOp.AVG else tdist.ReduceOp.SUM, group=group)
+        if _op(op) == tdist.ReduceOp.AVG:
+            tmp.div_(get_world_size(group))
+        r = get_rank(group)
+        n = output_tensor.numel()
+        output_tensor.copy_(tmp.view(-1)[r * n:(r + 1) * n].view_as(output_tensor))
+        return None
+    return tdist.reduce_scatter_tensor(output_tensor, tensor, op=_op(op), group=group, async_op=async_op)
+
+
+reduce_scatter_base = reduce_scatter_tensor
+reduce_scatter_fn = reduce_scatter_tensor
+
+
+@timed_op
+def all_gather(tensor_list, tensor, group=None, async_op=False):
+    return tdist.all_gather(tensor_list, tensor, group=group, async_op=async_op)
+
+
+@timed_op
+def all_gather_into_tensor(output_tensor, tensor, group=None, async_op=False):
+    return tdist.all_gather_into_tensor(output_tensor, tensor, group=group, async_op=async_op)
+
+
+all_gather_base = all_gather_into_tensor
+allgather_fn = all_gather_into_tensor
+
+
+@timed_op
+def all_gather_coalesced(output_tensors, input_tensors, group=None, async_op=False):
+    """output_tensors[i] (world*numel) <- all ranks' input_tensors[i]."""
+    handles = [tdist.all_gather_into_tensor(o, i, group=group, async_op=async_op)
+               for o, i in zip(output_tensors, input_tensors)]
+    return handles[-1] if handles else None
+
+
+@timed_op
+def all_to_all_single(output, tensor, output_split_sizes=None, input_split_sizes=None, group=None, async_op=False):
+    if tdist.get_backend(group) == "gloo":
+        ws = get_world_size(group)
+        ins = list(tensor.split(input_split_sizes, 0)) if input_split_sizes else list(tensor.chunk(ws, 0))
+        outs = list(output.split(output_split_sizes, 0)) if output_split_sizes else list(output.chunk(ws, 0))
+        outs_c = [torch.empty_like(o) for o in outs]
+        tdist.all_to_all(outs_c, [i.contiguous() for i in ins], group=group)
+        for o, c in zip(outs, outs_c):
+            o.copy_(c)
+        return None
+    return tdist.all_to_all_single(output, tensor, output_split_sizes, input_split_sizes, group=group, async_op=async_op)
+
+
+@timed_op
+def all_to_all(output_tensor_list, input_tensor_list, group=None, async_op=False):
+    return tdist.all_to_all(output_tensor_list, input_tensor_list, group=group, async_op=async_op)
+
+
+@timed_op
+def send(tensor, dst, group=None, tag=0):
+    return tdist.send(tensor, dst=dst, group=group, tag=tag)
+
+
+@timed_op
+def recv(tensor, src=None, group=None, tag=0):
+    return tdist.recv(tensor, src=src, group=group, tag=tag)
+
+
+@timed_op
+def isend(tensor, dst, group=None, tag=0):
+    return tdist.isend(tensor, dst=dst, group=group, tag=tag)
+
+
+@timed_op
+def irecv(tensor, src=None, group=None, tag=0):
+    return tdist.irecv(tensor, src=src, group=group, tag=tag)
+
+
+@timed_op
+def gather(tensor, gather_list=None, dst=0, group=None, async_op=False):
+    return tdist.gather(tensor, gather_list=gather_list, dst=dst, group=group, async_op=async_op)
+
+
+@timed_op
+def scatter(tensor, scatter_list=None, src=0, group=None, async_op=False):
+    return tdist.scatter(tensor, scatter_list=scatter_list, src=src, group=group, async_op=async_op)
+
+
+@timed_op
+def barrier(group=None, async_op=False, device_ids=None):
+    if not is_initialized():
+        return None
+    return tdist.barrier(group=group, async_op=async_op)
+
+
+@timed_op
+def monitored_barrier(group=None, timeout=None, wait_all_ranks=False):
+    if tdist.get_backend(group) == "gloo":
+        return tdist.monitored_barrier(group=group, timeout=timeout, wait_all_ranks=wait_all_ranks)
+    return tdist.barrier(group=group)
+
+
+def broadcast_object_list(object_list, src=0, group=None, device=None):
+    return tdist.broadcast_object_list(object_list, src=src, group=group, device=device)
+
+
+def all_gather_object(object_list, obj, group=None):
+    return tdist.all_gather_object(object_list, obj, group=group)
+
+
+# ----------------------------------------------------------------------------- bootstrap
+def mpi_discovery(distributed_port=TORCH_DISTRIBUTED_DEFAULT_PORT, verbose=True):
+    """Fill RANK/WORLD_SIZE/LOCAL_RANK/MASTER_* from an MPI launch (parity: comm.py:673-719)."""
+    from mpi4py import MPI
+    import subprocess
+    comm = MPI.COMM_WORLD
+    rank, world_size = comm.Get_rank(), comm.Get_size()
+    master_addr = None
+    if rank == 0:
+        master_addr = subprocess.check_output("hostname -I".split()).decode().split()[0]
+    master_addr = comm.bcast(master_addr, root=0)
+    proc_name = MPI.Get_processor_name()
+    all_procs = comm.allgather(proc_name)
+    local_rank = sum(1 for i in all_procs[:rank] if i == proc_name)
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world_size), LOCAL_RANK=str(local_rank),
+                      MASTER_ADDR=master_addr, MASTER_PORT=str(distributed_port))
+
+
+def in_aml():
+    return "AZUREML_EXPERIMENT_ID" in os.environ
+
+
+def in_aws_sm():
+    return "SM_TRAINING_ENV" in os.environ
+
+
+def in_dlts():
+    return "DLTS_JOB_ID" in os.environ
+
+
+def init_distributed(dist_backend=None, auto_mpi_discovery=True, distributed_port=TORCH_DISTRIBUTED_DEFAULT_PORT,
+                     verbose=True, timeout=DEFAULT_PG_TIMEOUT, init_method=None, dist_init_required=None, config=None,
+                     rank=-1, world_size=-1):
+    """Initialise torch.distributed (NCCL on GPUs, gloo on hosts).  One process per GPU; the device is
+    bound to LOCAL_RANK before the process group is created so NCCL picks the right NVLink peer."""
+    global _initialized_here
+    configure(deepspeed_config=config)
+    if dist_init_required is False:
+        return
+    if is_initialized():
+        return
+    required_env = ["RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "LOCAL_RANK"]
+    if auto_mpi_discovery and not all(e in os.environ for e in required_env):
+        if "OMPI_COMM_WORLD_RANK" in os.environ or "PMI_RANK" in os.environ:
+            try:
+                mpi_discovery(distributed_port=distributed_port, verbose=verbose)
+            except ImportError:
+                pass
+    if "RANK" not in os.environ and rank < 0:
+        # single-process convenience: behave like a 1-rank job
+        os.environ.setdefault("RANK", "0")
+        os.environ.setdefault("WORLD_SIZE", "1")
+        os.environ.setdefault("LOCAL_RANK", "0")
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", str(distributed_port))
+    acc = get_accelerator()
+    if dist_backend is None:
+        dist_backend = acc.communication_backend_name()
+    if acc.device_name() == "cuda":
+        acc.set_device(int(os.environ.get("LOCAL_RANK", "0")) % max(1, acc.device_count()))
+    if verbose and int(os.environ.get("RANK", "0")) == 0:
+        logger.info(f"Initializing torch.distributed with backend: {dist_backend}")
+    kwargs = {}
+    if rank >= 0:
+        kwargs.update(rank=rank, world_size=world_size)
+    if dist_backend == "nccl" and acc.device_name() == "cuda":
+        try:
+            kwargs["device_id"] = torch.device("cuda", acc.current_device())
+        except Exception:
+            pass
+    tdist.init_process_group(backend=dist_backend, timeout=timeout, init_method=init_method, **kwargs)
+    _initialized_here = True

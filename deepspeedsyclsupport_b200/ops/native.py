@@ -35,6 +35,47 @@ def _load(name, build_fn):
     return ctypes.CDLL(path)
 
 
+# C-ABI signatures (include/dsb200.h): p = pointer, i = int, l = long long, f = float.  Declaring argtypes makes ctypes
+# convert plain Python numbers correctly (a bare Python float would otherwise be passed as a double).
+_T = {"p": ctypes.c_void_p, "i": ctypes.c_int, "l": ctypes.c_longlong, "f": ctypes.c_float}
+_SIGS = {
+    "dsb200_gemm_bf16": "pppiiiiiiiiiip",
+    "dsb200_fused_adam_flat": "ppppipil fffff iii ppp",
+    "dsb200_fused_lion_flat": "pp pipil ffff ppp",
+    "dsb200_fused_adagrad_flat": "pp pipil fff ppp",
+    "dsb200_fused_lamb_flat": "ppp pipi pp l fffff ii ff pp p p",
+    "dsb200_fused_lamb_scratch_floats": "l",
+    "dsb200_multi_tensor_adam": "i ppppp i fffff iii ppp",
+    "dsb200_norm_fwd": "pppppppp ii f ii p",
+    "dsb200_norm_bwd_scratch_floats": "iii",
+    "dsb200_norm_bwd": "pppppppppp ii iiii p",
+    "dsb200_rope_inplace": "ppp l iiiiiii p",
+    "dsb200_gated_act_fwd": "ppp l iiii p",
+    "dsb200_gated_act_bwd": "ppp l iiii p",
+    "dsb200_bias_act": "ppp l iii p",
+    "dsb200_cross_entropy_fwd": "pppp l i l l i p",
+    "dsb200_cross_entropy_bwd": "pppp l i l l i p",
+    "dsb200_add": "ppp l i p",
+}
+_RESTYPE_LONG = {"dsb200_norm_bwd_scratch_floats"}
+
+
+def register_sigs(sigs, restype_long=()):
+    """Later-loaded op modules add their entry points here."""
+    _SIGS.update(sigs)
+    _RESTYPE_LONG.update(restype_long)
+    if _dev is not None:
+        _apply_sigs(_dev)
+
+
+def _apply_sigs(l):
+    for name, sig in _SIGS.items():
+        if hasattr(l, name):
+            fn = getattr(l, name)
+            fn.argtypes = [_T[c] for c in sig.replace(" ", "")]
+            fn.restype = ctypes.c_longlong if name in _RESTYPE_LONG else ctypes.c_int
+
+
 def lib():
     global _dev
     if _dev is None:
@@ -42,6 +83,7 @@ def lib():
             if _dev is None:
                 l = _load("libdsb200.so", "build_device")
                 l.dsb200_last_error.restype = ctypes.c_char_p
+                _apply_sigs(l)
                 _dev = l
     return _dev
 
@@ -71,11 +113,11 @@ def check(rc, n_launch=1):
 
 
 def stream_ptr():
-    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return torch.cuda.current_stream().cuda_stream
 
 
 def ptr(t):
-    return ctypes.c_void_p(t.data_ptr()) if t is not None else ctypes.c_void_p(0)
+    return t.data_ptr() if t is not None else None
 
 
 c_int = ctypes.c_int

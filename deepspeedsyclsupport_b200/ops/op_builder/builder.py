@@ -27,7 +27,7 @@ NVCC_FLAGS = [
     "--use_fast_math", "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=hidden",
     "--expt-relaxed-constexpr",
 ]
-HOST_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-fvisibility=hidden", "-march=native"]
+HOST_FLAGS = ["-O3", "-std=c++17", "-fPIC", "-fopenmp", "-fvisibility=hidden", "-march=x86-64-v3"]
 
 
 def nvcc_path():

@@ -1,0 +1,938 @@
+"""ZeRO optimizer core shared by every stage (0-3), MiCS and hpZ-style sub-group sharding.
+
+What the reference spreads over stage_1_and_2.py (2.5k lines), stage3.py (2.7k), parameter_offload.py and
+partitioned_param_coordinator.py is here one class over the flat unit store (param_store.py):
+
+  backward : gradients land in a contiguous per-unit buffer (autograd hook copy, or written there directly by the
+             fused linear's wgrad GEMM -- `param.ds_get_main_grad()`); when a unit is complete its buffer is
+             reduce-scattered on a side stream (stage >= 2) and accumulated into this rank's flat gradient shard.
+             Reference: stage3.py:1110-1291 (__add_grad_to_ipg_bucket / __reduce_and_partition_ipg_grads),
+             stage_1_and_2.py:860-1104 (hooks, average_tensor).
+  step     : device-side overflow flag + global norm + clip coefficient (no host sync for bf16), then fused Adam over
+             the flat fp32 shard writing the 16-bit shard in the same pass; stages 1/2 all-gather the units.
+             Reference: stage3.py:1955-2017, stage_1_and_2.py:1771-1888.
+  stage 3  : units are materialised around their module's forward/backward by hooks, with the fetch order recorded
+             on the first iteration and replayed as prefetch on a side stream (coordinator.py:256-460).
+  offload  : optimizer state (and fp32 master) in pinned host memory, AVX-512 Adam, `ratio` splits the flat shard
+             between host and device steps (Offload++ / Twin-Flow, stage3.py:926-942).
+"""
+import math
+import os
+from collections import OrderedDict
+
+import torch
+
+from ... import comm as dist
+from ...accelerator import get_accelerator
+from ...ops import flat_optim
+from ...utils.logging import log_dist, logger
+from ..fp16.loss_scaler import CreateLossScaler
+from .param_store import ParamUnit, ZeroParamStatus, build_units
+
+_ADAM_TYPES = ("Adam", "AdamW", "FusedAdam", "DeepSpeedCPUAdam")
+
+
+def _in_backward():
+    try:
+        return torch._C._current_graph_task_id() != -1
+    except Exception:
+        return False
+
+
+class _Region:
+    """A contiguous slice [lo, hi) of the rank-flat shard whose optimizer state lives on one device."""
+
+    def __init__(self, lo, hi, device, pin):
+        self.lo, self.hi, self.device = lo, hi, device
+        n = hi - lo
+        kw = dict(dtype=torch.float32, device=device)
+        self.master = torch.empty(n, **kw)
+        self.state = {}
+        self.pin = pin and device.type == "cpu" and torch.cuda.is_available()
+        if self.pin:
+            self.master = self.master.pin_memory()
+        self.host_grad = None
+        self.host_lp = None
+
+    def zeros(self):
+        t = torch.zeros(self.hi - self.lo, dtype=torch.float32, device=self.device)
+        return t.pin_memory() if self.pin else t
+
+
+class ZeroShardedOptimizer:
+
+    def __init__(self, module, init_optimizer, *, stage, zero_config, dtype, dp_group=None, shard_group=None,
+                 replica_group=None, static_loss_scale=1.0, dynamic_loss_scale=False, dynamic_loss_args=None,
+                 clip_grad=0.0, gradient_accumulation_steps=1, grad_accum_dtype=None, communication_data_type=None,
+                 mpu=None, timers=None, gradient_predivide_factor=1.0, prescale_gradients=False, grad_divisor=None,
+                 broadcast_src=0, elastic_checkpoint=False):
+        self.module = module
+        self.optimizer = init_optimizer
+        self.stage = int(stage)
+        self.zero_config = zero_config
+        self.dtype = dtype
+        self.mpu = mpu
+        self.timers = timers
+        self.clip_grad = float(clip_grad or 0.0)
+        self.gas = gradient_accumulation_steps
+        self.micro_step_id = 0
+        self.overflow = False
+        self.skipped_steps = 0
+        self.custom_loss_scaler = False
+        self.external_loss_scale = None
+        self._global_grad_norm = None
+        self.partition_gradients = self.stage >= 2
+        self.elastic_checkpoint = elastic_checkpoint
+
+        self.dp_group = dp_group
+        if self.stage == 0:
+            # optimizer states are replicated: shard world is 1 and gradients are all-reduced over the dp group
+            self.shard_group, self.replica_group = None, dp_group
+            self.shard_world, self.shard_rank = 1, 0
+            self.replica_world = dist.get_world_size(dp_group) if dist.is_initialized() else 1
+        else:
+            self.shard_group = shard_group if shard_group is not None else dp_group
+            self.replica_group = replica_group
+            self.shard_world = dist.get_world_size(self.shard_group) if dist.is_initialized() else 1
+            self.shard_rank = dist.get_rank(self.shard_group) if dist.is_initialized() else 0
+            self.replica_world = dist.get_world_size(replica_group) if (replica_group is not None and dist.is_initialized()) else 1
+        self.dp_world = dist.get_world_size(dp_group) if dist.is_initialized() else 1
+        self.partition_count = self.shard_world
+        # average over every rank that saw different data (sequence-parallel ranks share samples: engine passes divisor)
+        self.grad_divisor = float(grad_divisor) if grad_divisor else float(self.shard_world * self.replica_world)
+        self.predivide = float(gradient_predivide_factor) if prescale_gradients else 1.0
+
+        acc = get_accelerator()
+        self.device = torch.device(acc.current_device_name())
+        self.cuda = self.device.type == "cuda"
+        self.overlap_comm = bool(zero_config.overlap_comm) and self.cuda and self.shard_world * self.replica_world > 1
+        self.comm_dtype = communication_data_type or dtype
+        self.ag_stream = torch.cuda.Stream() if self.cuda else None
+        self.rs_stream = torch.cuda.Stream() if self.cuda else None
+
+        # ---- parameter groups -> units
+        self.param_groups = self.optimizer.param_groups if self.optimizer is not None else []
+        param_to_group = {}
+        for gi, g in enumerate(self.param_groups):
+            for p in g["params"]:
+                param_to_group[id(p)] = gi
+        for p in module.parameters():
+            if id(p) not in param_to_group:
+                param_to_group[id(p)] = -1  # frozen / not optimised
+        self.units, self.owner = build_units(module, param_to_group, self.shard_world, self.shard_rank, dtype, self.device)
+        self.persistence_threshold = int(zero_config.param_persistence_threshold) if self.stage == 3 else 0
+        self._setup_param_attrs()
+        self._allocate(broadcast_src)
+        self._build_runs()
+
+        if grad_accum_dtype is None:
+            grad_accum_dtype = torch.float32 if (self.gas > 1 or dtype == torch.float32) else dtype
+        self.grad_accum_dtype = grad_accum_dtype
+        self._allocate_grads()
+
+        self.loss_scaler = CreateLossScaler(dtype=dtype, static_loss_scale=static_loss_scale, dynamic_scaling=dynamic_loss_scale,
+                                            dynamic_loss_args=dynamic_loss_args)
+        self.dynamic_loss_scale = self.loss_scaler.dynamic
+        self._inv_scale = torch.ones(1, dtype=torch.float32, device=self.device)
+        self._skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+
+        self._opt_kind = type(self.optimizer).__name__ if self.optimizer is not None else None
+        self._step_count = 0
+        self._register_grad_hooks()
+        self._trace = {"fwd": [], "bwd": []}
+        self._trace_frozen = False
+        self._trace_pos = {"fwd": 0, "bwd": 0}
+        if self.stage == 3 and self.shard_world > 1:
+            self._register_module_hooks()
+        log_dist(f"ZeRO stage {self.stage}: {len(self.units)} units, shard world {self.shard_world}, replica world "
+                 f"{self.replica_world}, {self.total_shard * self.shard_world / 1e6:.1f}M padded elements, "
+                 f"shard {self.total_shard / 1e6:.1f}M, grad accum dtype {self.grad_accum_dtype}", ranks=[0])
+
+    # ------------------------------------------------------------------ setup
+    def _setup_param_attrs(self):
+        pid = 0
+        for u in self.units:
+            for i, p in enumerate(u.params):
+                if not hasattr(p, "ds_shape"):
+                    p.ds_shape = p.shape if getattr(p, "ds_init_sharded", False) is False else p.ds_shape
+                p.ds_numel = int(math.prod(p.ds_shape)) if len(p.ds_shape) else 1
+                p.ds_id = pid
+                pid += 1
+                p.ds_unit = u
+                p.ds_index = i
+                p.ds_status = ZeroParamStatus.AVAILABLE
+                p.ds_persist = False
+                p.ds_process_group = self.shard_group
+                p.ds_zero_optimizer = self
+                self._attach_param_methods(p)
+            if self.stage == 3 and u.numel <= self.persistence_threshold:
+                u.persistent = True
+                for p in u.params:
+                    p.ds_persist = True
+
+    def _attach_param_methods(self, p):
+        opt = self
+
+        def all_gather(param_list=None, async_op=False, hierarchy=0):
+            opt.fetch_units({id(q.ds_unit): q.ds_unit for q in (param_list or [p])}.values())
+
+        def partition(param_list=None, hierarchy=0, has_been_updated=False):
+            for u in {id(q.ds_unit): q.ds_unit for q in (param_list or [p])}.values():
+                if has_been_updated:
+                    opt._write_back_unit(u)
+                opt.release_unit(u)
+
+        def ds_summary(slf=p, use_debug_name=False):
+            return {"id": slf.ds_id, "status": slf.ds_status.name, "numel": slf.numel(), "ds_numel": slf.ds_numel,
+                    "shape": tuple(slf.shape), "ds_shape": tuple(slf.ds_shape), "requires_grad": slf.requires_grad,
+                    "grad_shape": tuple(slf.grad.shape) if slf.grad is not None else None, "persist": slf.ds_persist,
+                    "unit": slf.ds_unit.name, "ds_tensor.shape": tuple(slf.ds_tensor.shape)}
+
+        p.all_gather = all_gather
+        p.partition = partition
+        p.ds_summary = ds_summary
+        p.ds_get_main_grad = lambda q=p: opt.main_grad_view(q)
+        p.ds_main_grad_done = lambda q=p: opt._param_grad_ready(q)
+
+    def _unit_flat_from_params(self, u, broadcast_src):
+        """Assemble the unit's full flat buffer from whatever form its parameters currently have."""
+        flat = torch.zeros(u.padded, dtype=self.dtype, device=self.device)
+        for i, p in enumerate(u.params):
+            off, n = u.param_slice(i)
+            if getattr(p, "ds_init_sharded", False):
+                from .partition_parameters import gather_init_sharded
+                flat[off:off + n].copy_(gather_init_sharded(p).view(-1))
+            else:
+                flat[off:off + n].copy_(p.data.reshape(-1).to(self.device, self.dtype))
+        if dist.is_initialized() and broadcast_src is not None and self.dp_world > 1 and not all(
+                getattr(p, "ds_init_sharded", False) for p in u.params):
+            dist.broadcast(flat, src=dist.get_global_rank(self.dp_group, 0), group=self.dp_group)
+        return flat
+
+    def _allocate(self, broadcast_src):
+        off = 0
+        for u in self.units:
+            u.shard_off = off
+            off += u.shard_numel
+        self.total_shard = off
+        self.lp_shard = torch.zeros(self.total_shard, dtype=self.dtype, device=self.device)
+        keep_full = self.stage <= 2 or self.shard_world == 1
+        self.lp_full = None
+        if keep_full and self.shard_world > 1:
+            self.lp_full = torch.empty(sum(u.padded for u in self.units), dtype=self.dtype, device=self.device)
+        foff = 0
+        for u in self.units:
+            u.shard = self.lp_shard[u.shard_off:u.shard_off + u.shard_numel]
+            flat = self._unit_flat_from_params(u, broadcast_src)
+            lo, hi = u.shard_range()
+            u.shard.copy_(flat[lo:hi])
+            if self.shard_world == 1:
+                u.full = u.shard  # parameters alias the shard: gather/release are the identity
+                u.bind_params()
+            elif keep_full:
+                u.full = self.lp_full[foff:foff + u.padded]
+                u.full.copy_(flat)
+                foff += u.padded
+                u.bind_params()
+            else:
+                if u.persistent:
+                    u.full = flat
+                    u.bind_params()
+                else:
+                    u.full = None
+                    u.unbind_params()
+            for i, p in enumerate(u.params):
+                p.ds_init_sharded = False
+                a, n = u.param_slice(i)
+                s_lo, s_hi = max(a, lo), min(a + n, hi)
+                p.ds_tensor = u.shard[s_lo - lo:s_hi - lo] if s_lo < s_hi else u.shard[0:0]
+            del flat
+        self.keep_full = keep_full
+        # ---- optimizer-state regions (host / device split = Offload++ ratio)
+        oc = self.zero_config.offload_optimizer
+        offload = oc is not None and str(getattr(oc.device, "value", oc.device)) != "none"
+        self.offload_optimizer = offload
+        self.regions = []
+        if offload:
+            ratio = float(oc.ratio)
+            cut = int(self.total_shard * ratio) // 64 * 64 if ratio < 1.0 else self.total_shard
+            if cut > 0:
+                self.regions.append(_Region(0, cut, torch.device("cpu"), oc.pin_memory))
+            if cut < self.total_shard:
+                self.regions.append(_Region(cut, self.total_shard, self.device, False))
+        else:
+            self.regions.append(_Region(0, self.total_shard, self.device, False))
+        for r in self.regions:
+            if self.dtype == torch.float32 and r.device == self.device:
+                r.master = self.lp_shard[r.lo:r.hi]  # fp32 training: the parameters ARE the master weights
+            else:
+                r.master.copy_(self.lp_shard[r.lo:r.hi].float())
+
+    def _build_runs(self):
+        """(group_id, lo, hi) runs over the rank-flat shard space, merged across unit boundaries."""
+        runs = []
+        for u in self.units:
+            for g, a, b in u.shard_group_runs():
+                lo, hi = u.shard_off + a, u.shard_off + b
+                if runs and runs[-1][0] == g and runs[-1][2] == lo:
+                    runs[-1][2] = hi
+                else:
+                    runs.append([g, lo, hi])
+        self.runs = [tuple(r) for r in runs]
+
+    def _allocate_grads(self):
+        self.grad_shard = torch.zeros(self.total_shard, dtype=self.grad_accum_dtype, device=self.device)
+        self.grad_full_persistent = None
+        if self.shard_world == 1:
+            # full gradient == shard: hooks / fused wgrad write straight into the accumulation buffer
+            for u in self.units:
+                u.full_grad = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
+        elif self.stage <= 1:
+            self.grad_full_persistent = torch.zeros(sum(u.padded for u in self.units), dtype=self.grad_accum_dtype,
+                                                    device=self.device)
+            off = 0
+            for u in self.units:
+                u.full_grad = self.grad_full_persistent[off:off + u.padded]
+                off += u.padded
+        self._grads_dirty = False
+
+    # ------------------------------------------------------------------ gradient path
+    def _register_grad_hooks(self):
+        self._hook_handles = []
+        for u in self.units:
+            for p in u.trainable:
+                self._hook_handles.append(p.register_post_accumulate_grad_hook(self._make_grad_hook(p)))
+
+    def _make_grad_hook(self, p):
+
+        def hook(param):
+            if param.grad is None:
+                return
+            view = self.main_grad_view(param)
+            g = param.grad
+            if view.dtype == g.dtype and g.shape == view.shape:
+                view.add_(g)
+            else:
+                view.add_(g.to(view.dtype).view_as(view))
+            param.grad = None
+            self._param_grad_ready(param)
+
+        return hook
+
+    def main_grad_view(self, p):
+        """Slice of the unit's contiguous gradient buffer for `p` (allocated on first use in a backward pass)."""
+        u = p.ds_unit
+        if u.full_grad is None:
+            u.full_grad = torch.zeros(u.padded, dtype=self.comm_dtype, device=self.device)
+        off, n = u.param_slice(p.ds_index)
+        self._grads_dirty = True
+        return u.full_grad[off:off + n].view(p.ds_shape)
+
+    def _param_grad_ready(self, p):
+        u = p.ds_unit
+        u.ready += 1
+        if u.ready >= len(u.trainable):
+            self._unit_grads_done(u)
+
+    def _unit_grads_done(self, u):
+        u.ready = 0
+        if self.shard_world == 1 and self.replica_world == 1:
+            u.reduced = True
+        elif self.stage >= 2 and self.shard_world > 1:
+            self._reduce_unit(u)
+        # stage 0/1: reduction happens once at the accumulation boundary (reduce_gradients)
+        if self.stage == 3 and self.shard_world > 1 and not u.persistent and _in_backward():
+            self.release_unit(u)
+
+    def _reduce_unit(self, u):
+        """reduce-scatter (+ replica all-reduce) of one unit's gradient buffer into the flat gradient shard."""
+        if u.full_grad is None:
+            return
+        buf = u.full_grad
+        stream = self.rs_stream if self.overlap_comm else None
+        if stream is not None:
+            stream.wait_stream(torch.cuda.current_stream())
+        ctx = torch.cuda.stream(stream) if stream is not None else _nullctx()
+        with ctx:
+            if self.predivide != 1.0:
+                buf.div_(self.predivide)
+            dst = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
+            if self.shard_world > 1:
+                tmp = torch.empty(u.shard_numel, dtype=buf.dtype, device=self.device)
+                dist.reduce_scatter_tensor(tmp, buf, op=dist.ReduceOp.SUM, group=self.shard_group)
+            else:
+                tmp = buf
+            if self.replica_world > 1:
+                dist.all_reduce(tmp, op=dist.ReduceOp.SUM, group=self.replica_group)
+            scale = self.predivide / self.grad_divisor
+            if tmp.data_ptr() != dst.data_ptr():
+                dst.add_(tmp.to(dst.dtype) if tmp.dtype != dst.dtype else tmp, alpha=scale)
+            elif scale != 1.0:
+                dst.mul_(scale)
+            if stream is not None:
+                buf.record_stream(stream)
+                tmp.record_stream(stream)
+        if self.grad_full_persistent is None and self.shard_world > 1:
+            u.full_grad = None
+        u.reduced = True
+
+    def reduce_gradients(self, pipeline_parallel=False):
+        """Called by the engine after backward at an accumulation boundary (stage 0/1) or every micro-step (stage >= 2)
+        to flush units whose gradients did not all arrive (unused parameters)."""
+        boundary_only = self.stage <= 1
+        for u in self.units:
+            if self.shard_world == 1 and self.replica_world == 1:
+                continue
+            if boundary_only:
+                self._reduce_unit(u)
+                if self.grad_full_persistent is not None:
+                    pass
+            elif not u.reduced and (u.full_grad is not None and self.grad_full_persistent is None):
+                self._reduce_unit(u)
+            elif self.shard_world == 1 and self.replica_world > 1 and not u.reduced:
+                self._reduce_unit(u)
+        if self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+        if boundary_only and self.grad_full_persistent is not None:
+            self.grad_full_persistent.zero_()
+
+    def overlapping_partition_gradients_reduce_epilogue(self):
+        self.reduce_gradients()
+
+    def end_micro_step(self, boundary):
+        """Engine hook after every backward()."""
+        if self.stage >= 2 or boundary:
+            if self.stage <= 1 and not boundary:
+                pass
+            else:
+                self.reduce_gradients()
+        for u in self.units:
+            u.reduced = False
+            u.ready = 0
+        if self.stage == 3 and self.shard_world > 1:
+            for u in self.units:
+                if not u.persistent and u.status == ZeroParamStatus.AVAILABLE:
+                    self.release_unit(u)
+            self._end_of_pass()
+        self.micro_step_id += 1
+
+    # ------------------------------------------------------------------ stage-3 fetch / release
+    def fetch_units(self, units, prefetch_phase=None):
+        for u in units:
+            self._fetch(u)
+        if prefetch_phase is not None and self._trace_frozen:
+            self._prefetch_next(prefetch_phase)
+
+    def _launch_gather(self, u):
+        if u.status != ZeroParamStatus.NOT_AVAILABLE:
+            return
+        stream = self.ag_stream if self.cuda else None
+        ctx = torch.cuda.stream(stream) if stream is not None else _nullctx()
+        with ctx:
+            u.full = torch.empty(u.padded, dtype=self.dtype, device=self.device)
+            if self.zero_config.zero_quantized_weights and self.cuda:
+                from .zeropp import quantized_all_gather
+                quantized_all_gather(u.full, u.shard, self.shard_group)
+            else:
+                dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+            if stream is not None:
+                u.gather_event = torch.cuda.Event()
+                u.gather_event.record(stream)
+        u.status = ZeroParamStatus.INFLIGHT
+
+    def _fetch(self, u):
+        if u.status == ZeroParamStatus.AVAILABLE:
+            return
+        if u.status == ZeroParamStatus.NOT_AVAILABLE:
+            self._launch_gather(u)
+        if u.gather_event is not None:
+            torch.cuda.current_stream().wait_event(u.gather_event)
+            u.full.record_stream(torch.cuda.current_stream())
+            u.gather_event = None
+        u.bind_params()
+
+    def release_unit(self, u):
+        if self.keep_full or u.persistent or u.status == ZeroParamStatus.NOT_AVAILABLE:
+            return
+        if u.status == ZeroParamStatus.INFLIGHT:
+            self._fetch(u)
+        u.unbind_params()
+        u.full = None
+
+    def _write_back_unit(self, u):
+        """Copy this rank's slice of a (modified) full buffer back into the shard + fp32 master."""
+        lo, hi = u.shard_range()
+        if u.full is not None and u.full.data_ptr() != u.shard.data_ptr():
+            u.shard.copy_(u.full[lo:hi])
+        self._refresh_master(u.shard_off, u.shard_off + u.shard_numel)
+
+    def _refresh_master(self, lo, hi):
+        for r in self.regions:
+            a, b = max(lo, r.lo), min(hi, r.hi)
+            if a < b:
+                r.master[a - r.lo:b - r.lo].copy_(self.lp_shard[a:b].float())
+
+    def _record(self, phase, u):
+        if not self._trace_frozen:
+            self._trace[phase].append(u.uid)
+
+    def _prefetch_next(self, phase):
+        order = self._trace[phase]
+        pos = self._trace_pos[phase]
+        budget = int(self.zero_config.prefetch_bucket_size)
+        live = sum(x.padded for x in self.units if x.status != ZeroParamStatus.NOT_AVAILABLE and not x.persistent)
+        k = pos
+        while k < len(order) and budget > 0:
+            nu = self.units[order[k]]
+            if nu.status == ZeroParamStatus.NOT_AVAILABLE and not nu.persistent:
+                if live + nu.padded > int(self.zero_config.max_live_parameters) and live > 0:
+                    break
+                self._launch_gather(nu)
+                budget -= nu.padded
+                live += nu.padded
+            k += 1
+
+    def _end_of_pass(self):
+        if not self._trace_frozen and self._trace["fwd"]:
+            self._trace_frozen = True
+        self._trace_pos = {"fwd": 0, "bwd": 0}
+
+    def _register_module_hooks(self):
+        mod_units = OrderedDict()
+        for u in self.units:
+            for m in u.modules:
+                mod_units.setdefault(id(m), (m, []))[1].append(u)
+        # modules that *use* a tied parameter owned by another unit must fetch that unit as well
+        for m in self.module.modules():
+            if id(m) in mod_units:
+                for p in m.parameters():
+                    u = self.owner.get(id(p))
+                    if u is not None and u not in mod_units[id(m)][1]:
+                        mod_units[id(m)][1].append(u)
+        self._module_hooks = []
+        for _, (m, units) in mod_units.items():
+            self._hook_module(m, units)
+
+    def _advance(self, phase, units):
+        order = self._trace[phase]
+        pos = self._trace_pos[phase]
+        if self._trace_frozen:
+            uids = [u.uid for u in units]
+            while pos < len(order) and order[pos] not in uids:
+                pos += 1
+            self._trace_pos[phase] = min(pos + len(uids), len(order))
+
+    def _hook_module(self, m, units):
+        opt = self
+
+        def pre_fwd(mod, args):
+            phase = "bwd" if _in_backward() else "fwd"
+            for u in units:
+                opt._record(phase, u)
+            opt._advance(phase, units)
+            opt.fetch_units(units, prefetch_phase=phase)
+
+        def post_fwd(mod, args, out):
+            if _in_backward():
+                return  # recompute inside backward: parameters are still needed for dgrad/wgrad
+            for u in units:
+                opt.release_unit(u)
+
+        def pre_bwd(mod, grad_out):
+            for u in units:
+                opt._record("bwd", u)
+            opt._advance("bwd", units)
+            opt.fetch_units(units, prefetch_phase="bwd")
+
+        def post_bwd(mod, gin, gout):
+            for u in units:
+                if not u.trainable:
+                    opt.release_unit(u)
+
+        self._module_hooks.append(m.register_forward_pre_hook(pre_fwd))
+        self._module_hooks.append(m.register_forward_hook(post_fwd))
+        self._module_hooks.append(m.register_full_backward_pre_hook(pre_bwd))
+        self._module_hooks.append(m.register_full_backward_hook(post_bwd))
+
+    # ------------------------------------------------------------------ loss scaling / backward
+    @property
+    def loss_scale(self):
+        if self.custom_loss_scaler:
+            return self.external_loss_scale
+        return self.loss_scaler.cur_scale
+
+    cur_scale = loss_scale
+
+    def backward(self, loss, retain_graph=False):
+        if self.custom_loss_scaler:
+            (self.external_loss_scale * loss).backward(retain_graph=retain_graph)
+        else:
+            self.loss_scaler.backward(loss.float(), retain_graph=retain_graph)
+
+    def zero_grad(self, set_to_none=True):
+        for u in self.units:
+            for p in u.params:
+                p.grad = None
+        if self._grads_dirty or True:
+            self.grad_shard.zero_()
+            if self.grad_full_persistent is not None:
+                self.grad_full_persistent.zero_()
+            self._grads_dirty = False
+
+    # ------------------------------------------------------------------ step
+    def _model_parallel_all_reduce(self, tensor, op):
+        if self.mpu is not None and hasattr(self.mpu, "get_model_parallel_group"):
+            g = self.mpu.get_model_parallel_group()
+            if g is not None and dist.get_world_size(g) > 1:
+                dist.all_reduce(tensor, op=op, group=g)
+
+    def _check_overflow(self):
+        if self.dtype != torch.float16:
+            return False
+        bad = (~torch.isfinite(self.grad_shard.float().sum())).to(torch.float32).reshape(1)
+        if dist.is_initialized():
+            if self.shard_world > 1:
+                dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.shard_group)
+            self._model_parallel_all_reduce(bad, dist.ReduceOp.MAX)
+        return bool(bad.item() > 0)
+
+    def _compute_global_norm(self):
+        """Device-side ||g||_2 of the (still loss-scaled) gradient over all shards."""
+        g = self.grad_shard
+        sq = (g.float() if g.dtype != torch.float32 else g).square().sum().reshape(1) if g.numel() < (1 << 28) else \
+            sum((c.float().square().sum() for c in g.split(1 << 27))).reshape(1)
+        if dist.is_initialized():
+            if self.shard_world > 1:
+                dist.all_reduce(sq, op=dist.ReduceOp.SUM, group=self.shard_group)
+            self._model_parallel_all_reduce(sq, dist.ReduceOp.SUM)
+        return sq.sqrt()
+
+    def step(self, closure=None):
+        self.micro_step_id = 0
+        if self.overlap_comm:
+            torch.cuda.current_stream().wait_stream(self.rs_stream)
+        self.overflow = self._check_overflow()
+        if not self.custom_loss_scaler:
+            prev_scale = self.loss_scale
+            self.loss_scaler.update_scale(self.overflow)
+        if self.overflow:
+            self.skipped_steps += 1
+            self.zero_grad()
+            return
+        loss_scale = prev_scale if not self.custom_loss_scaler else self.external_loss_scale
+        norm = self._compute_global_norm()
+        self._global_grad_norm = norm / loss_scale
+        inv = torch.full_like(norm, 1.0 / loss_scale)
+        if self.clip_grad > 0.0:
+            clip = (self._global_grad_norm / self.clip_grad).clamp(min=1.0)
+            inv = inv / clip
+        self._inv_scale.copy_(inv)
+        self._step_count += 1
+        self._optimizer_step()
+        self._post_step()
+        self.zero_grad()
+
+    def _hyper(self, gi):
+        g = self.param_groups[gi]
+        return g
+
+    def _ensure_state(self, region, kind):
+        if region.state:
+            return
+        if kind in _ADAM_TYPES or kind in ("FusedLamb", "OnebitAdam", "ZeroOneAdam", "OnebitLamb"):
+            region.state = {"exp_avg": region.zeros(), "exp_avg_sq": region.zeros()}
+        elif kind in ("FusedLion", "DeepSpeedCPULion", "Lion"):
+            region.state = {"exp_avg": region.zeros()}
+        elif kind in ("Adagrad", "DeepSpeedCPUAdagrad"):
+            region.state = {"exp_avg_sq": region.zeros()}
+
+    def _optimizer_step(self):
+        kind = self._opt_kind
+        for region in self.regions:
+            self._ensure_state(region, kind)
+            on_host = region.device.type == "cpu" and self.cuda
+            if on_host:
+                if region.host_grad is None:
+                    region.host_grad = torch.empty(region.hi - region.lo, dtype=self.grad_shard.dtype).pin_memory()
+                    region.host_lp = torch.empty(region.hi - region.lo, dtype=self.dtype).pin_memory()
+                region.host_grad.copy_(self.grad_shard[region.lo:region.hi], non_blocking=True)
+                inv_host = float(self._inv_scale.item())  # also synchronises the D2H copy above
+                grads, lp_all, inv_dev, gs = region.host_grad, region.host_lp, None, inv_host
+            else:
+                grads = self.grad_shard[region.lo:region.hi]
+                lp_all = self.lp_shard[region.lo:region.hi]
+                inv_dev, gs = (self._inv_scale if self.cuda else None), (1.0 if self.cuda else float(self._inv_scale.item()))
+            for gi, lo, hi in self.runs:
+                a, b = max(lo, region.lo), min(hi, region.hi)
+                if a >= b or gi < 0:
+                    continue
+                s = slice(a - region.lo, b - region.lo)
+                hp = self.param_groups[gi]
+                lp = lp_all[s] if self.dtype != torch.float32 else None
+                self._apply_update(kind, region, s, grads[s], lp, hp, inv_dev, gs)
+                if lp is None and on_host:
+                    lp_all[s].copy_(region.master[s])
+            if on_host:
+                self.lp_shard[region.lo:region.hi].copy_(region.host_lp, non_blocking=True)
+
+    def _apply_update(self, kind, region, s, g, lp, hp, inv_dev, gs):
+        p = region.master[s]
+        st = region.state
+        if kind in _ADAM_TYPES:
+            if kind == "Adam":
+                adamw = False
+            elif kind == "AdamW":
+                adamw = True
+            else:
+                adamw = bool(getattr(self.optimizer, "adam_w_mode", True))
+            b1, b2 = hp.get("betas", (0.9, 0.999))
+            flat_optim.adam_step(p, st["exp_avg"][s], st["exp_avg_sq"][s], g, lr=hp["lr"], beta1=b1, beta2=b2, eps=hp.get("eps", 1e-8),
+                                 weight_decay=hp.get("weight_decay", 0.0), adamw_mode=bool(adamw),
+                                 bias_correction=hp.get("bias_correction", True), step=self._step_count, lp=lp,
+                                 inv_scale=inv_dev, grad_scale=gs)
+        elif kind in ("FusedLion", "DeepSpeedCPULion", "Lion"):
+            b1, b2 = hp.get("betas", (0.9, 0.99))
+            flat_optim.lion_step(p, st["exp_avg"][s], g, lr=hp["lr"], beta1=b1, beta2=b2, weight_decay=hp.get("weight_decay", 0.0),
+                                 lp=lp, inv_scale=inv_dev, grad_scale=gs)
+        elif kind in ("Adagrad", "DeepSpeedCPUAdagrad"):
+            flat_optim.adagrad_step(p, st["exp_avg_sq"][s], g, lr=hp["lr"], eps=hp.get("eps", 1e-10),
+                                    weight_decay=hp.get("weight_decay", 0.0), lp=lp, inv_scale=inv_dev, grad_scale=gs)
+        else:
+            self._generic_update(region, s, g, lp, hp, inv_dev, gs)
+
+    def _generic_update(self, region, s, g, lp, hp, inv_dev, gs):
+        """Any torch.optim.Optimizer: run it on fp32 views of the master shard (reference behaviour for client optimizers)."""
+        key = ("generic", region.lo, s.start, s.stop)
+        if not hasattr(self, "_generic"):
+            self._generic = {}
+        if key not in self._generic:
+            w = torch.nn.Parameter(region.master[s], requires_grad=True)
+            opt_cls = type(self.optimizer)
+            kw = {k: v for k, v in hp.items() if k != "params"}
+            try:
+                sub = opt_cls([w], **kw)
+            except TypeError:
+                sub = opt_cls([w], lr=hp["lr"])
+            self._generic[key] = (w, sub)
+        w, sub = self._generic[key]
+        for k, v in hp.items():
+            if k != "params":
+                sub.param_groups[0][k] = v
+        scale = (float(inv_dev.item()) if inv_dev is not None else 1.0) * gs
+        w.grad = g.float() * scale
+        sub.step()
+        w.grad = None
+        if lp is not None and lp.data_ptr() != w.data.data_ptr():
+            lp.copy_(w.data)
+
+    def _post_step(self):
+        if self.dtype == torch.float32 and self.shard_world >= 1:
+            # fp32 training: master is a separate fp32 copy; lp_shard was updated by the kernels (lp write)
+            pass
+        if self.shard_world > 1:
+            if self.keep_full:
+                for u in self.units:
+                    dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+            else:
+                for u in self.units:
+                    if u.persistent:
+                        dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+            if self.cuda:
+                self.ag_stream.wait_stream(torch.cuda.current_stream())
+        elif self.cuda and self.ag_stream is not None:
+            pass
+
+    # ------------------------------------------------------------------ introspection used by engine / utils
+    def get_global_grad_norm(self):
+        return self._global_grad_norm
+
+    @property
+    def global_grad_norm(self):
+        n = self._global_grad_norm
+        return float(n.item()) if torch.is_tensor(n) else n
+
+    def get_lr(self):
+        return [g["lr"] for g in self.param_groups]
+
+    def _master_slice(self, lo, hi):
+        out = torch.empty(hi - lo, dtype=torch.float32, device=self.device)
+        for r in self.regions:
+            a, b = max(lo, r.lo), min(hi, r.hi)
+            if a < b:
+                out[a - lo:b - lo].copy_(r.master[a - r.lo:b - r.lo])
+        return out
+
+    def _state_slice(self, key, lo, hi):
+        out = torch.zeros(hi - lo, dtype=torch.float32, device=self.device)
+        for r in self.regions:
+            a, b = max(lo, r.lo), min(hi, r.hi)
+            if a < b and key in r.state:
+                out[a - lo:b - lo].copy_(r.state[key][a - r.lo:b - r.lo])
+        return out
+
+    def _gather_param_from_flat(self, p, getter):
+        """Full fp32 tensor for `p` assembled from every rank's shard of a rank-flat buffer."""
+        u = p.ds_unit
+        local = getter(u.shard_off, u.shard_off + u.shard_numel)
+        if self.shard_world > 1:
+            full = torch.empty(u.padded, dtype=torch.float32, device=self.device)
+            dist.all_gather_into_tensor(full, local.contiguous(), group=self.shard_group)
+        else:
+            full = local
+        off, n = u.param_slice(p.ds_index)
+        return full[off:off + n].view(p.ds_shape).clone()
+
+    def get_full_fp32_param(self, p):
+        return self._gather_param_from_flat(p, self._master_slice)
+
+    def get_full_optimizer_state(self, p, key):
+        return self._gather_param_from_flat(p, lambda lo, hi: self._state_slice(key, lo, hi))
+
+    def get_full_grad(self, p):
+        inv = 1.0 / self.loss_scale if self.loss_scale else 1.0
+        return self._gather_param_from_flat(p, lambda lo, hi: self.grad_shard[lo:hi].float()) * inv
+
+    def _scatter_param_to_flat(self, p, value, setter):
+        u = p.ds_unit
+        off, n = u.param_slice(p.ds_index)
+        lo, hi = u.shard_range()
+        a, b = max(off, lo), min(off + n, hi)
+        if a < b:
+            setter(u.shard_off + a - lo, u.shard_off + b - lo, value.reshape(-1)[a - off:b - off].float())
+
+    def set_full_fp32_param(self, p, value):
+        def setter(lo, hi, v):
+            for r in self.regions:
+                a, b = max(lo, r.lo), min(hi, r.hi)
+                if a < b:
+                    r.master[a - r.lo:b - r.lo].copy_(v[a - lo:b - lo])
+            self.lp_shard[lo:hi].copy_(v)
+        self._scatter_param_to_flat(p, value.to(self.device), setter)
+        u = p.ds_unit
+        if self.keep_full and self.shard_world > 1:
+            dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+        elif u.persistent and self.shard_world > 1:
+            dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+
+    def set_full_optimizer_state(self, p, value, key):
+        def setter(lo, hi, v):
+            for r in self.regions:
+                self._ensure_state(r, self._opt_kind)
+                a, b = max(lo, r.lo), min(hi, r.hi)
+                if a < b:
+                    r.state[key][a - r.lo:b - r.lo].copy_(v[a - lo:b - lo])
+        self._scatter_param_to_flat(p, value.to(self.device), setter)
+
+    # ------------------------------------------------------------------ checkpoint
+    def _layout(self):
+        return {"units": [{"name": u.name, "padded": u.padded, "shard_numel": u.shard_numel, "shard_off": u.shard_off,
+                           "params": [(getattr(p, "ds_name", str(p.ds_id)), tuple(p.ds_shape), u.offsets[i])
+                                      for i, p in enumerate(u.params)]} for u in self.units],
+                "shard_world": self.shard_world, "total_shard": self.total_shard, "align": 64}
+
+    def state_dict(self):
+        """Per-rank optimizer shard in the reference's key layout (stage3.py:2382-2411, stage_1_and_2.py:2102-2142)
+        plus `ds_unit_layout`, which tells zero_to_fp32 how this rank's flat shard maps to parameters."""
+        master = self._master_slice(0, self.total_shard).cpu()
+        state = {}
+        keys = set()
+        for r in self.regions:
+            keys.update(r.state.keys())
+        for k in sorted(keys):
+            state[k] = self._state_slice(k, 0, self.total_shard).cpu()
+        sd = {
+            "zero_stage": self.stage,
+            "loss_scaler": self.loss_scaler,
+            "dynamic_loss_scale": self.dynamic_loss_scale,
+            "overflow": self.overflow,
+            "partition_count": self.partition_count,
+            "ds_unit_layout": self._layout(),
+            "step_count": self._step_count,
+            "optimizer_state_dict": {"state": {0: state},
+                                     "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]},
+        }
+        if self.stage == 3:
+            sd["fp32_flat_groups"] = [master]
+        else:
+            sd["single_partition_of_fp32_groups"] = [master]
+            sd["base_optimizer_state"] = sd["optimizer_state_dict"]["state"]
+            sd["group_paddings"] = [0]
+            sd["clip_grad"] = self.clip_grad
+        return sd
+
+    def load_state_dict(self, state_dict_list, load_optimizer_states=True, load_from_fp32_weights=True, checkpoint_folder=None,
+                        load_serial=None):
+        sd = state_dict_list[self.shard_rank] if isinstance(state_dict_list, (list, tuple)) else state_dict_list
+        assert sd["partition_count"] == self.partition_count, (
+            f"checkpoint was saved with shard world {sd['partition_count']}, current is {self.partition_count}; "
+            "use the universal checkpoint path (ds_to_universal) to reshape")
+        self.loss_scaler = sd.get("loss_scaler", self.loss_scaler)
+        self.dynamic_loss_scale = sd.get("dynamic_loss_scale", self.dynamic_loss_scale)
+        self.overflow = sd.get("overflow", False)
+        self._step_count = sd.get("step_count", 0)
+        master = (sd.get("fp32_flat_groups") or sd.get("single_partition_of_fp32_groups"))[0]
+        if load_from_fp32_weights:
+            for r in self.regions:
+                r.master.copy_(master[r.lo:r.hi])
+            self.lp_shard.copy_(master.to(self.device).to(self.dtype))
+        else:
+            for r in self.regions:
+                r.master.copy_(self.lp_shard[r.lo:r.hi].float())
+        if load_optimizer_states:
+            st = sd["optimizer_state_dict"]["state"].get(0, {})
+            for r in self.regions:
+                self._ensure_state(r, self._opt_kind)
+                for k, v in st.items():
+                    if k in r.state:
+                        r.state[k].copy_(v[r.lo:r.hi])
+            for g, saved in zip(self.param_groups, sd["optimizer_state_dict"]["param_groups"]):
+                for k, v in saved.items():
+                    g[k] = v
+        self._post_load_sync()
+
+    def _post_load_sync(self):
+        if self.shard_world > 1:
+            for u in self.units:
+                if self.keep_full or u.persistent:
+                    dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+
+    def refresh_from_params(self):
+        """Re-shard after module weights were loaded into the (gathered) parameters."""
+        for u in self.units:
+            if u.full is not None:
+                self._write_back_unit(u)
+
+    # ------------------------------------------------------------------ checkpoint-time parameter materialisation
+    def checkpoint_event_prologue(self):
+        pass
+
+    def checkpoint_event_epilogue(self):
+        pass
+
+    def gathered_unit(self, u):
+        return _GatheredUnit(self, u)
+
+
+class _GatheredUnit:
+
+    def __init__(self, opt, u):
+        self.opt, self.u = opt, u
+
+    def __enter__(self):
+        self.was = self.u.status
+        self.opt._fetch(self.u)
+        return self.u
+
+    def __exit__(self, *exc):
+        if self.was == ZeroParamStatus.NOT_AVAILABLE:
+            self.opt.release_unit(self.u)
+        return False
+
+
+class _nullctx:
+
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
