@@ -1,0 +1,163 @@
+"""Llama-2 family (7B / 13B / 70B shapes) built on the framework's sm_100a kernels.
+
+Per decoder layer: fused pre-RMSNorm(+residual add) -> one QKV GEMM (tcgen05) -> in-place RoPE on the packed q,k heads
+-> flash attention on the packed projection -> output GEMM -> fused RMSNorm(+residual) -> one gate|up GEMM -> SiGLU
+-> down GEMM.  The residual stream is carried as (x, residual) so every residual add is folded into the next norm
+kernel.  Weight gradients are accumulated by the wgrad GEMM epilogue straight into the ZeRO gradient buffers.
+The reference ships no model definitions (users bring HF modules); this module is the flagship workload of
+BASELINE.json (Llama-2-7B ZeRO-3) and the source of the AutoTP / FastGen Llama containers.
+"""
+import math
+from dataclasses import dataclass
+
+import torch
+import torch.nn as nn
+
+from ..ops import fused_ops as FO
+from ..ops.attention import attention
+from ..ops.gemm import linear
+
+
+@dataclass
+class LlamaConfig:
+    vocab_size: int = 32000
+    hidden_size: int = 4096
+    intermediate_size: int = 11008
+    num_hidden_layers: int = 32
+    num_attention_heads: int = 32
+    num_key_value_heads: int = 32
+    max_position_embeddings: int = 4096
+    rms_norm_eps: float = 1e-5
+    rope_theta: float = 10000.0
+    tie_word_embeddings: bool = False
+    activation_checkpointing: bool = False
+    initializer_range: float = 0.02
+
+    @property
+    def head_dim(self):
+        return self.hidden_size // self.num_attention_heads
+
+
+LLAMA2_7B = dict(hidden_size=4096, intermediate_size=11008, num_hidden_layers=32, num_attention_heads=32, num_key_value_heads=32)
+LLAMA2_13B = dict(hidden_size=5120, intermediate_size=13824, num_hidden_layers=40, num_attention_heads=40, num_key_value_heads=40)
+LLAMA2_70B = dict(hidden_size=8192, intermediate_size=28672, num_hidden_layers=80, num_attention_heads=64, num_key_value_heads=8)
+TINY = dict(vocab_size=512, hidden_size=128, intermediate_size=384, num_hidden_layers=2, num_attention_heads=2, num_key_value_heads=2,
+            max_position_embeddings=256)
+
+
+def llama_config(name="7b", **overrides):
+    base = {"7b": LLAMA2_7B, "13b": LLAMA2_13B, "70b": LLAMA2_70B, "tiny": TINY}[name.lower()]
+    kw = dict(base)
+    kw.update(overrides)
+    return LlamaConfig(**kw)
+
+
+class RMSNorm(nn.Module):
+
+    def __init__(self, hidden, eps):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(hidden))
+        self.eps = eps
+
+    def forward(self, x, residual=None):
+        return FO.rms_norm(x, self.weight, self.eps, residual)
+
+
+class LlamaDecoderLayer(nn.Module):
+
+    def __init__(self, cfg: LlamaConfig, layer_idx=0):
+        super().__init__()
+        self.cfg = cfg
+        h, d = cfg.hidden_size, cfg.head_dim
+        self.hq, self.hkv, self.d = cfg.num_attention_heads, cfg.num_key_value_heads, d
+        self.input_layernorm = RMSNorm(h, cfg.rms_norm_eps)
+        self.qkv_proj = nn.Parameter(torch.empty((self.hq + 2 * self.hkv) * d, h))
+        self.o_proj = nn.Parameter(torch.empty(h, self.hq * d))
+        self.post_attention_layernorm = RMSNorm(h, cfg.rms_norm_eps)
+        self.gate_up_proj = nn.Parameter(torch.empty(2 * cfg.intermediate_size, h))
+        self.down_proj = nn.Parameter(torch.empty(h, cfg.intermediate_size))
+        for w in (self.qkv_proj, self.o_proj, self.gate_up_proj, self.down_proj):
+            nn.init.normal_(w, mean=0.0, std=cfg.initializer_range)
+        self.register_buffer("inv_freq", FO.rope_inv_freq(d, cfg.rope_theta), persistent=False)
+
+    def forward(self, x, residual, positions=None):
+        """(x, residual) -> (mlp_out, new_residual); the true hidden state is x + residual."""
+        B, S, _ = x.shape
+        if residual is None:
+            residual = x
+            hn = self.input_layernorm(x)
+        else:
+            hn, residual = self.input_layernorm(x, residual)
+        qkv = linear(hn, self.qkv_proj)
+        qkv = FO.rope_(qkv.view(B * S, -1), self.inv_freq, S, 0, self.hq + self.hkv, self.d, positions)
+        attn = attention(qkv, B, S, self.hq, self.hkv, self.d, causal=True)
+        attn_out = linear(attn.view(B, S, -1), self.o_proj)
+        hn, residual = self.post_attention_layernorm(attn_out, residual)
+        act = FO.gated_act(linear(hn, self.gate_up_proj), "silu")
+        return linear(act, self.down_proj), residual
+
+
+class LlamaModel(nn.Module):
+
+    def __init__(self, cfg: LlamaConfig):
+        super().__init__()
+        self.cfg = cfg
+        self.embed_tokens = nn.Embedding(cfg.vocab_size, cfg.hidden_size)
+        nn.init.normal_(self.embed_tokens.weight, mean=0.0, std=cfg.initializer_range)
+        self.layers = nn.ModuleList([LlamaDecoderLayer(cfg, i) for i in range(cfg.num_hidden_layers)])
+        self.norm = RMSNorm(cfg.hidden_size, cfg.rms_norm_eps)
+
+    def forward(self, input_ids, positions=None):
+        x = self.embed_tokens(input_ids)
+        residual = None
+        for layer in self.layers:
+            if self.cfg.activation_checkpointing and self.training:
+                if residual is None:
+                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, l=layer: l(a, None, positions), x, use_reentrant=False)
+                else:
+                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, r, l=layer: l(a, r, positions), x, residual,
+                                                                     use_reentrant=False)
+            else:
+                x, residual = layer(x, residual, positions)
+        if residual is None:
+            return self.norm(x)
+        out, _ = self.norm(x, residual)
+        return out
+
+
+class LlamaForCausalLM(nn.Module):
+    """forward(input_ids, labels=None) -> loss (if labels) or logits.  Labels are next-token targets aligned with
+    input positions (already shifted by the data pipeline); ignore_index = -100."""
+
+    def __init__(self, cfg: LlamaConfig):
+        super().__init__()
+        self.cfg = cfg
+        self.model = LlamaModel(cfg)
+        if cfg.tie_word_embeddings:
+            self.lm_head = None
+        else:
+            self.lm_head = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden_size))
+            nn.init.normal_(self.lm_head, mean=0.0, std=cfg.initializer_range)
+
+    def head_weight(self):
+        return self.model.embed_tokens.weight if self.lm_head is None else self.lm_head
+
+    def forward(self, input_ids, labels=None, positions=None):
+        h = self.model(input_ids, positions)
+        logits = linear(h, self.head_weight())
+        if labels is None:
+            return logits
+        return FO.cross_entropy(logits.view(-1, logits.shape[-1]), labels.view(-1))
+
+    def num_parameters(self):
+        return sum(p.numel() for p in self.parameters())
+
+    def flops_per_token(self, seq_len, with_recompute=False):
+        """Training FLOPs per token (fwd+bwd = 3x fwd, +1 fwd with full recompute), attention included (causal)."""
+        c = self.cfg
+        d = c.head_dim
+        per_layer = 2 * c.hidden_size * ((c.num_attention_heads + 2 * c.num_key_value_heads) * d + c.num_attention_heads * d
+                                         + 3 * c.intermediate_size)
+        attn = 2 * 2 * c.num_attention_heads * d * seq_len / 2  # QK^T and PV, causal half
+        fwd = c.num_hidden_layers * (per_layer + attn) + 2 * c.hidden_size * c.vocab_size
+        return fwd * (4 if with_recompute else 3)

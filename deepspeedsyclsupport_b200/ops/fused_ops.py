@@ -26,7 +26,7 @@ def rms_norm_ref(x, weight, eps, residual=None):
 class _NormFn(torch.autograd.Function):
 
     @staticmethod
-    def forward(ctx, x, weight, bias, residual, eps, layer_norm, w_main_grad, b_main_grad):
+    def forward(ctx, x, weight, bias, residual, eps, layer_norm, w_param, b_param):
         hidden = x.shape[-1]
         x2 = x.reshape(-1, hidden)
         if not x2.is_contiguous():
@@ -46,7 +46,7 @@ class _NormFn(torch.autograd.Function):
         ctx.has_res = residual is not None
         ctx.has_bias = bias is not None
         ctx.shape = x.shape
-        ctx.w_main_grad, ctx.b_main_grad = w_main_grad, b_main_grad
+        ctx.w_param, ctx.b_param = w_param, b_param
         if residual is not None:
             return y.view(x.shape), res_out.view(x.shape)
         return y.view(x.shape)
@@ -68,37 +68,47 @@ class _NormFn(torch.autograd.Function):
         lib = native.lib()
         nscratch = lib.dsb200_norm_bwd_scratch_floats(rows, hidden, int(ctx.layer_norm))
         scratch = torch.empty(nscratch, dtype=torch.float32, device=xin.device)
-        use_main = ctx.w_main_grad is not None
+        use_main = ctx.w_param is not None
         if use_main:
-            dgamma, dbeta = ctx.w_main_grad, ctx.b_main_grad
+            dgamma = ctx.w_param.ds_get_main_grad()
+            dbeta = ctx.b_param.ds_get_main_grad() if ctx.b_param is not None else None
         else:
             dgamma = torch.empty_like(weight)
             dbeta = torch.empty_like(weight) if (ctx.layer_norm and ctx.has_bias) else None
         rc = lib.dsb200_norm_bwd(native.ptr(dy2), native.ptr(xin), native.ptr(weight), native.ptr(mean), native.ptr(rstd),
                                  native.ptr(dres2), native.ptr(dx), native.ptr(dgamma), native.ptr(dbeta), native.ptr(scratch),
-                                 rows, hidden, int(ctx.layer_norm), _dt(xin), int(use_main), int(use_main),
+                                 rows, hidden, int(ctx.layer_norm), _dt(xin), int(dgamma.dtype == torch.float32), int(use_main),
                                  native.stream_ptr())
         native.check(rc, 2)
+        if use_main:
+            ctx.w_param.ds_main_grad_done()
+            if ctx.b_param is not None:
+                ctx.b_param.ds_main_grad_done()
         dx = dx.view(ctx.shape)
         gw = None if use_main else dgamma
         gb = None if use_main else dbeta
         return dx, gw, gb, (dx if ctx.has_res else None), None, None, None, None
 
 
-def rms_norm(x, weight, eps=1e-6, residual=None, main_grad=None):
+def _fusable(p):
+    return p is not None and p.requires_grad and hasattr(p, "ds_get_main_grad") and torch.is_grad_enabled()
+
+
+def rms_norm(x, weight, eps=1e-6, residual=None):
     """y = RMSNorm(x [+ residual]) * weight.  With `residual`, returns (y, x + residual) -- the fused pre-norm form
     (reference: pre_rms_norm, inference/v2/kernels/core_ops/cuda_rms_norm/rms_norm.cu)."""
     if not x.is_cuda:
         return rms_norm_ref(x, weight, eps, residual)
-    return _NormFn.apply(x, weight, None, residual, eps, False, main_grad, None)
+    return _NormFn.apply(x, weight, None, residual, eps, False, weight if _fusable(weight) else None, None)
 
 
-def layer_norm(x, weight, bias=None, eps=1e-5, residual=None, main_grad=None, bias_main_grad=None):
+def layer_norm(x, weight, bias=None, eps=1e-5, residual=None):
     if not x.is_cuda:
         h = x + residual if residual is not None else x
         y = F.layer_norm(h.float(), (x.shape[-1],), weight.float(), bias.float() if bias is not None else None, eps).to(x.dtype)
         return (y, h) if residual is not None else y
-    return _NormFn.apply(x, weight, bias, residual, eps, True, main_grad, bias_main_grad)
+    fuse = _fusable(weight) and (bias is None or _fusable(bias))
+    return _NormFn.apply(x, weight, bias, residual, eps, True, weight if fuse else None, bias if (fuse and bias is not None) else None)
 
 
 # ----------------------------------------------------------------------------- RoPE

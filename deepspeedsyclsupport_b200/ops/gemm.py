@@ -52,9 +52,9 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
 class _LinearFn(torch.autograd.Function):
 
     @staticmethod
-    def forward(ctx, x, w, main_grad):
+    def forward(ctx, x, w, w_param):
         ctx.save_for_backward(x, w)
-        ctx.main_grad = main_grad
+        ctx.w_param = w_param
         x2 = x.reshape(-1, x.shape[-1])
         y = gemm(x2, w)
         return y.view(*x.shape[:-1], w.shape[0])
@@ -70,17 +70,21 @@ class _LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = gemm(dy2, w, b_mn=True).view_as(x)
         if ctx.needs_input_grad[1]:
-            mg = ctx.main_grad
-            if mg is not None:
-                # fused gradient accumulation: dW is reduced into the fp32 main grad by the epilogue
+            wp = ctx.w_param
+            if wp is not None:
+                # fused gradient accumulation: the wgrad epilogue reduces dW straight into the ZeRO gradient buffer
+                mg = wp.ds_get_main_grad()
                 gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
-                dw = None
+                wp.ds_main_grad_done()
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)
         return dx, dw, None
 
 
-def linear(x, w, main_grad=None):
-    """y = x @ w.T with w: [out, in].  If `main_grad` (fp32 [out,in]) is given, backward accumulates
-    the weight gradient into it and returns no .grad for w."""
-    return _LinearFn.apply(x, w, main_grad)
+def linear(x, w):
+    """y = x @ w.T with w: [out, in] on the tcgen05 GEMM.  When `w` is managed by the ZeRO store, backward accumulates
+    the weight gradient directly into the store's contiguous gradient buffer (no .grad tensor, no copy)."""
+    if not x.is_cuda:
+        return torch.nn.functional.linear(x, w)
+    fused = w.requires_grad and hasattr(w, "ds_get_main_grad") and torch.is_grad_enabled()
+    return _LinearFn.apply(x, w, w if fused else None)

@@ -53,10 +53,13 @@ class ParamUnit:
         self.device = device
         self.world, self.rank = world, rank
         self.offsets = []
+        self.numels = []
         off = 0
         for p in self.params:
+            n = int(p.ds_numel) if getattr(p, "ds_init_sharded", False) else p.numel()
+            self.numels.append(n)
             self.offsets.append(off)
-            off += _align_up(p.numel(), 8)  # 16-byte aligned starts for 16-bit dtypes
+            off += _align_up(n, 8)  # 16-byte aligned starts for 16-bit dtypes
         self.numel = off
         self.padded = _align_up(max(off, 1), world * ALIGN)
         self.shard_numel = self.padded // world
@@ -75,7 +78,7 @@ class ParamUnit:
 
     # ---- geometry helpers
     def param_slice(self, i):
-        return self.offsets[i], self.params[i].numel()
+        return self.offsets[i], self.numels[i]
 
     def shard_range(self):
         """[lo, hi) of the unit-flat index space owned by this rank."""
@@ -122,7 +125,7 @@ class ParamUnit:
         self.status = ZeroParamStatus.NOT_AVAILABLE
 
     def grad_views(self, buf):
-        return [buf[self.offsets[i]:self.offsets[i] + p.numel()].view(p.ds_shape) for i, p in enumerate(self.params)]
+        return [buf[self.offsets[i]:self.offsets[i] + self.numels[i]].view(p.ds_shape) for i, p in enumerate(self.params)]
 
 
 _EMPTY_CACHE = {}

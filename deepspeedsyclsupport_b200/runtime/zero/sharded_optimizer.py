@@ -153,9 +153,9 @@ class ZeroShardedOptimizer:
         pid = 0
         for u in self.units:
             for i, p in enumerate(u.params):
-                if not hasattr(p, "ds_shape"):
-                    p.ds_shape = p.shape if getattr(p, "ds_init_sharded", False) is False else p.ds_shape
-                p.ds_numel = int(math.prod(p.ds_shape)) if len(p.ds_shape) else 1
+                if not getattr(p, "ds_init_sharded", False):
+                    p.ds_shape = p.shape
+                p.ds_numel = u.numels[i]
                 p.ds_id = pid
                 pid += 1
                 p.ds_unit = u

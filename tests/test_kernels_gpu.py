@@ -1,0 +1,196 @@
+"""Numerics of every CUDA kernel against a plain PyTorch fp32 reference of the same op (GPU only)."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev():
+    return torch.device("cuda")
+
+
+@pytest.mark.parametrize("layout", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(256, 512, 128), (1000, 1096, 328), (2048, 4096, 1024), (192, 64, 128)])
+def test_gemm_bf16(layout, shape):
+    from deepspeedsyclsupport_b200.ops.gemm import gemm
+    a_mn, b_mn = layout
+    M, N, K = shape
+    torch.manual_seed(0)
+    a = torch.randn((K, M) if a_mn else (M, K), device=_dev(), dtype=torch.bfloat16)
+    b = torch.randn((K, N) if b_mn else (N, K), device=_dev(), dtype=torch.bfloat16)
+    ref = (a.t() if a_mn else a).float() @ (b if b_mn else b.t()).float()
+    c = gemm(a, b, a_mn=a_mn, b_mn=b_mn)
+    assert (c.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
+    c32 = gemm(a, b, a_mn=a_mn, b_mn=b_mn, out_dtype=torch.float32)
+    assert (c32 - ref).abs().max() <= 1e-4 * ref.abs().max()
+    acc = torch.randn(M, N, device=_dev())
+    want = acc + ref
+    gemm(a, b, a_mn=a_mn, b_mn=b_mn, out=acc, accumulate=True)
+    assert (acc - want).abs().max() <= 1e-4 * want.abs().max()
+
+
+def test_linear_autograd():
+    from deepspeedsyclsupport_b200.ops.gemm import linear
+    torch.manual_seed(0)
+    x = torch.randn(4, 96, 256, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    w = torch.randn(384, 256, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    y = linear(x, w)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr, wr = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    yr = torch.nn.functional.linear(xr, wr)
+    yr.backward(dy.float())
+    assert (y.float() - yr).abs().max() < 2e-2 * yr.abs().max()
+    assert (x.grad.float() - xr.grad).abs().max() < 2e-2 * xr.grad.abs().max()
+    assert (w.grad.float() - wr.grad).abs().max() < 2e-2 * wr.grad.abs().max()
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("hidden", [256, 4096, 5120, 8192])
+def test_rms_norm_fwd_bwd(dtype, hidden):
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    rows = 300
+    x = torch.randn(rows, hidden, device=_dev(), dtype=dtype, requires_grad=True)
+    res = torch.randn(rows, hidden, device=_dev(), dtype=dtype, requires_grad=True)
+    w = (1 + 0.1 * torch.randn(hidden, device=_dev())).to(dtype).requires_grad_()
+    y, h = FO.rms_norm(x, w, 1e-5, residual=res)
+    dy, dh = torch.randn_like(y), torch.randn_like(h)
+    torch.autograd.backward([y, h], [dy, dh])
+    xr, rr, wr = (t.detach().float().requires_grad_() for t in (x, res, w))
+    hr = xr + rr
+    yr = hr * torch.rsqrt(hr.pow(2).mean(-1, keepdim=True) + 1e-5) * wr
+    torch.autograd.backward([yr, hr], [dy.float(), dh.float()])
+    tol = 2e-2 if dtype != torch.float32 else 1e-4
+    assert (y.float() - yr).abs().max() < tol * max(1.0, yr.abs().max().item())
+    assert (x.grad.float() - xr.grad).abs().max() < tol * max(1.0, xr.grad.abs().max().item())
+    assert (res.grad.float() - rr.grad).abs().max() < tol * max(1.0, rr.grad.abs().max().item())
+    assert (w.grad.float() - wr.grad).abs().max() < 3 * tol * max(1.0, wr.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+def test_layer_norm_fwd_bwd(dtype):
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    rows, hidden = 257, 1024
+    x = torch.randn(rows, hidden, device=_dev(), dtype=dtype, requires_grad=True)
+    w = (1 + 0.1 * torch.randn(hidden, device=_dev())).to(dtype).requires_grad_()
+    b = (0.1 * torch.randn(hidden, device=_dev())).to(dtype).requires_grad_()
+    y = FO.layer_norm(x, w, b, 1e-5)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr, wr, br = (t.detach().float().requires_grad_() for t in (x, w, b))
+    yr = torch.nn.functional.layer_norm(xr, (hidden, ), wr, br, 1e-5)
+    yr.backward(dy.float())
+    tol = 2e-2 if dtype != torch.float32 else 1e-4
+    assert (y.float() - yr).abs().max() < tol * max(1.0, yr.abs().max().item())
+    assert (x.grad.float() - xr.grad).abs().max() < tol * max(1.0, xr.grad.abs().max().item())
+    assert (w.grad.float() - wr.grad).abs().max() < 3 * tol * max(1.0, wr.grad.abs().max().item())
+    assert (b.grad.float() - br.grad).abs().max() < 3 * tol * max(1.0, br.grad.abs().max().item())
+
+
+def test_rope_fwd_bwd():
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    B, S, hq, hkv, d = 2, 128, 4, 2, 128
+    inv = FO.rope_inv_freq(d, device=_dev())
+    qkv = torch.randn(B * S, (hq + 2 * hkv) * d, device=_dev(), dtype=torch.bfloat16)
+    pos = (torch.arange(B * S, device=_dev()) % S)
+    ref = FO.rope_ref(qkv.float(), inv, pos, 0, hq + hkv, d)
+    x = qkv.clone().requires_grad_()
+    y = FO.rope_(x * 1.0, inv, S, 0, hq + hkv, d)
+    assert (y.float() - ref).abs().max() < 3e-2
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    ref_b = FO.rope_ref(dy.float(), inv, pos, 0, hq + hkv, d, backward=True)
+    assert (x.grad.float() - ref_b).abs().max() < 3e-2
+
+
+@pytest.mark.parametrize("act", ["silu", "gelu", "relu"])
+def test_gated_act(act):
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    x = torch.randn(333, 2 * 1376, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    y = FO.gated_act(x, act)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    xr = x.detach().float().requires_grad_()
+    yr = FO.gated_act_ref(xr, act)
+    yr.backward(dy.float())
+    assert (y.float() - yr).abs().max() < 3e-2 * max(1.0, yr.abs().max().item())
+    assert (x.grad.float() - xr.grad).abs().max() < 3e-2 * max(1.0, xr.grad.abs().max().item())
+
+
+def test_cross_entropy():
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    T, V = 513, 32000
+    logits = (3 * torch.randn(T, V, device=_dev())).bfloat16()
+    labels = torch.randint(0, V, (T, ), device=_dev())
+    labels[::7] = -100
+    lr = logits.float().clone().requires_grad_()
+    ref = torch.nn.functional.cross_entropy(lr, labels, ignore_index=-100)
+    ref.backward()
+    l = logits.clone().requires_grad_()
+    loss = FO.cross_entropy(l * 1.0, labels)
+    loss.backward()
+    assert abs(loss.item() - ref.item()) < 2e-3 * abs(ref.item())
+    assert (l.grad.float() - lr.grad).abs().max() < 2e-2 * lr.grad.abs().max() + 1e-6
+
+
+@pytest.mark.parametrize("gdt", [torch.float32, torch.bfloat16])
+def test_fused_adam_flat(gdt):
+    from deepspeedsyclsupport_b200.ops.flat_optim import adam_ref, adam_step
+    torch.manual_seed(0)
+    n = 1_000_003
+    p = torch.randn(n, device=_dev())
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    p2, m2, v2 = p.clone(), m.clone(), v.clone()
+    lp = torch.empty(n, device=_dev(), dtype=torch.bfloat16)
+    inv = torch.tensor([0.5], device=_dev())
+    for step in range(1, 4):
+        g = torch.randn(n, device=_dev()).to(gdt)
+        adam_step(p, m, v, g, lr=1e-2, weight_decay=0.1, step=step, lp=lp, inv_scale=inv)
+        adam_ref(p2, m2, v2, g, 1e-2, 0.9, 0.999, 1e-8, 0.1, True, True, step, grad_scale=0.5)
+    assert (p - p2).abs().max() < 1e-5
+    assert (m - m2).abs().max() < 1e-5 and (v - v2).abs().max() < 1e-5
+    assert (lp.float() - p2).abs().max() < 1e-2 * p2.abs().max()
+
+
+def test_fused_adam_optimizer_class_and_lion_lamb():
+    from deepspeedsyclsupport_b200.ops.adam import FusedAdam
+    from deepspeedsyclsupport_b200.ops.lamb import FusedLamb
+    from deepspeedsyclsupport_b200.ops.lion import FusedLion
+    torch.manual_seed(0)
+    ws = [torch.randn(257, 33, device=_dev(), requires_grad=True), torch.randn(70000, device=_dev(), requires_grad=True)]
+    wr = [w.detach().clone().requires_grad_() for w in ws]
+    o, r = FusedAdam(ws, lr=1e-2, weight_decay=0.05), torch.optim.AdamW(wr, lr=1e-2, weight_decay=0.05)
+    for _ in range(3):
+        for a, b in zip(ws, wr):
+            g = torch.randn_like(a)
+            a.grad, b.grad = g.clone(), g.clone()
+        o.step()
+        r.step()
+    for a, b in zip(ws, wr):
+        assert (a - b).abs().max() < 1e-5
+    # Lion: sign update
+    w = torch.randn(5000, device=_dev(), requires_grad=True)
+    w0 = w.detach().clone()
+    g = torch.randn_like(w)
+    w.grad = g.clone()
+    FusedLion([w], lr=1e-2, betas=(0.9, 0.99), weight_decay=0.0).step()
+    assert torch.allclose(w.detach(), w0 - 1e-2 * torch.sign(0.1 * g), atol=1e-6)
+    # LAMB: trust ratio
+    w = torch.randn(40000, device=_dev(), requires_grad=True)
+    w0 = w.detach().clone()
+    g = torch.randn_like(w)
+    w.grad = g.clone()
+    opt = FusedLamb([w], lr=1e-2, weight_decay=0.01, bias_correction=True)
+    opt.step()
+    mm, vv = 0.1 * g, 0.001 * g * g
+    upd = (mm / 0.1) / ((vv / 0.001).sqrt() + 1e-8) + 0.01 * w0
+    ratio = min(max((w0.norm() / upd.norm()).item(), 0.01), 10.0)
+    assert torch.allclose(w.detach(), w0 - 1e-2 * ratio * upd, atol=1e-5)
+    assert abs(opt.get_lamb_coeffs()[0] - ratio) < 1e-4
