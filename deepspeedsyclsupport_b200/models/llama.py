@@ -15,7 +15,7 @@ import torch.nn as nn
 
 from ..ops import fused_ops as FO
 from ..ops.attention import attention
-from ..ops.gemm import linear
+from ..ops.gemm import linear, linear_rope
 
 
 @dataclass
@@ -88,8 +88,7 @@ class LlamaDecoderLayer(nn.Module):
             hn = self.input_layernorm(x)
         else:
             hn, residual = self.input_layernorm(x, residual)
-        qkv = linear(hn, self.qkv_proj)
-        qkv = FO.rope_(qkv.view(B * S, -1), self.inv_freq, S, 0, self.hq + self.hkv, self.d, positions)
+        qkv = linear_rope(hn, self.qkv_proj, self.inv_freq, S, self.hq + self.hkv, self.d, positions)
         attn = attention(qkv, B, S, self.hq, self.hkv, self.d, causal=True)
         attn_out = linear(attn.view(B, S, -1), self.o_proj)
         hn, residual = self.post_attention_layernorm(attn_out, residual)

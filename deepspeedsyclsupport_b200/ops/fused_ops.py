@@ -138,22 +138,22 @@ def _rope_apply(x2, inv_freq, positions, seq_len, head0, nheads, head_dim, backw
 
 
 class _RopeFn(torch.autograd.Function):
-    """In-place rotation of the q and k heads of a packed [tokens, (Hq + 2 Hkv) * D] projection."""
+    """Rotation of the q and k heads of a packed [tokens, (Hq + 2 Hkv) * D] projection (out of place; the in-place
+    form lives inside ops.gemm.linear_rope)."""
 
     @staticmethod
     def forward(ctx, x, inv_freq, positions, seq_len, head0, nheads, head_dim):
         ctx.save_for_backward(inv_freq, positions)
         ctx.args = (seq_len, head0, nheads, head_dim)
-        ctx.mark_dirty(x)
-        x2 = x.view(-1, x.shape[-1])
-        _rope_apply(x2, inv_freq, positions, seq_len, head0, nheads, head_dim, False)
-        return x
+        y = x.contiguous().clone()
+        _rope_apply(y.view(-1, y.shape[-1]), inv_freq, positions, seq_len, head0, nheads, head_dim, False)
+        return y
 
     @staticmethod
     def backward(ctx, dx):
         inv_freq, positions = ctx.saved_tensors
         seq_len, head0, nheads, head_dim = ctx.args
-        dx = dx.contiguous() if not dx.is_contiguous() else dx
+        dx = dx.contiguous().clone()
         dx2 = dx.view(-1, dx.shape[-1])
         _rope_apply(dx2, inv_freq, positions, seq_len, head0, nheads, head_dim, True)
         return dx, None, None, None, None, None, None

@@ -88,3 +88,51 @@ def linear(x, w):
         return torch.nn.functional.linear(x, w)
     fused = w.requires_grad and hasattr(w, "ds_get_main_grad") and torch.is_grad_enabled()
     return _LinearFn.apply(x, w, w if fused else None)
+
+
+class _LinearRopeFn(torch.autograd.Function):
+    """QKV projection with RoPE applied to the leading `nrot` heads inside the same autograd node: the rotation is done
+    in place on the GEMM output (forward) and on a private copy of the incoming gradient (backward)."""
+
+    @staticmethod
+    def forward(ctx, x, w, w_param, inv_freq, positions, seq_len, nrot, head_dim):
+        from .fused_ops import _rope_apply
+        x2 = x.reshape(-1, x.shape[-1])
+        y = gemm(x2, w)
+        _rope_apply(y, inv_freq, positions, seq_len, 0, nrot, head_dim, False)
+        ctx.save_for_backward(x, w, inv_freq, positions)
+        ctx.w_param = w_param
+        ctx.rope = (seq_len, nrot, head_dim)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from .fused_ops import _rope_apply
+        x, w, inv_freq, positions = ctx.saved_tensors
+        seq_len, nrot, head_dim = ctx.rope
+        dy2 = dy.reshape(-1, dy.shape[-1]).clone()
+        _rope_apply(dy2, inv_freq, positions, seq_len, 0, nrot, head_dim, True)
+        x2 = x.reshape(-1, x.shape[-1])
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = gemm(dy2, w, b_mn=True).view_as(x)
+        if ctx.needs_input_grad[1]:
+            wp = ctx.w_param
+            if wp is not None:
+                mg = wp.ds_get_main_grad()
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
+                wp.ds_main_grad_done()
+            else:
+                dw = gemm(dy2, x2, a_mn=True, b_mn=True)
+        return dx, dw, None, None, None, None, None, None
+
+
+def linear_rope(x, w, inv_freq, seq_len, nrot, head_dim, positions=None):
+    """[tokens, (hq + 2 hkv) * d] = x @ w.T with rotary embedding applied to heads [0, nrot) (q and k)."""
+    if not x.is_cuda:
+        from .fused_ops import rope_ref
+        y = torch.nn.functional.linear(x, w).reshape(-1, w.shape[0])
+        pos = positions if positions is not None else torch.arange(y.shape[0], device=y.device) % seq_len
+        return rope_ref(y, inv_freq, pos, 0, nrot, head_dim)
+    fused = w.requires_grad and hasattr(w, "ds_get_main_grad") and torch.is_grad_enabled()
+    return _LinearRopeFn.apply(x, w, w if fused else None, inv_freq, positions, seq_len, nrot, head_dim)
