@@ -294,6 +294,11 @@ def main():
     args = parse()
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29511")
+    # N == 1 is launched without torchrun: behave like a one-rank job (the reference would otherwise probe for MPI)
+    os.environ.setdefault("RANK", "0")
+    os.environ.setdefault("LOCAL_RANK", "0")
+    os.environ.setdefault("WORLD_SIZE", "1")
+    os.environ.setdefault("LOCAL_SIZE", os.environ["WORLD_SIZE"])
     if args.impl == "reference":
         run_reference(args)
     else:
