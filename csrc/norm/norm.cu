@@ -314,3 +314,59 @@ DSB_EXPORT int dsb200_norm_bwd(const void* dy, const void* x, const void* gamma,
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// RMSNorm backward without any allocation.
+//
+// Some callers of this library cannot obtain device memory at the moment they need a kernel: a serving process that
+// handed all free HBM to its paged KV-cache pool at start-up gets "out of memory" from any later cudaMalloc, and a
+// latency-critical loop cannot afford the device-wide serialisation that cudaMalloc / cudaFree imply.  For them the
+// per-CTA dgamma partials of the backward pass live in the fixed array below instead of a caller-supplied workspace.
+//
+//   * Capacity: DSB_NOALLOC_NORM_MAX_FLOATS floats (148 CTAs x hidden <= 8192, 4.6 MiB).  Every GPU that loads the
+//     library keeps this array resident until the process exits.  Larger problems are rejected with an error.
+//   * The first call on a device resolves the array's device address (cudaGetSymbolAddress, with that device
+//     current).  Make that first call before starting any stream capture.
+//   * All calls share the one array and it keeps whatever the previous call left in it.  Nothing has to start at
+//     zero: each CTA overwrites its whole row of partials before the column reduction reads it.  Two calls that
+//     overlap on the GPU (different streams) race on the array -- serialise them.
+//   * No cudaMalloc / cudaFree / allocating library routine is called.
+#define DSB_NOALLOC_NORM_MAX_PARTS 148
+#define DSB_NOALLOC_NORM_MAX_HIDDEN 8192
+#define DSB_NOALLOC_NORM_MAX_FLOATS (DSB_NOALLOC_NORM_MAX_PARTS * DSB_NOALLOC_NORM_MAX_HIDDEN)
+static __device__ __align__(256) float g_noalloc_norm_scratch[DSB_NOALLOC_NORM_MAX_FLOATS];
+
+DSB_EXPORT int dsb200_rms_norm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* rstd,
+                                           const void* dx_add, void* dx, void* dgamma, int rows, int hidden, int dtype,
+                                           int dparam_f32, int accumulate, cudaStream_t stream) {
+  static float* scratch_addr[64] = {nullptr};  // per device; in host code the symbol itself is NOT a device address
+  DSB_REQUIRE(hidden % 8 == 0 && hidden > 0, "rms_norm_bwd_noalloc: hidden=%d must be a positive multiple of 8", hidden);
+  DSB_REQUIRE(hidden <= DSB_NOALLOC_NORM_MAX_HIDDEN,
+              "rms_norm_bwd_noalloc: hidden=%d exceeds the built-in scratch (max hidden %d, %d floats); use dsb200_norm_bwd "
+              "with a caller-provided workspace",
+              hidden, DSB_NOALLOC_NORM_MAX_HIDDEN, DSB_NOALLOC_NORM_MAX_FLOATS);
+  if (rows == 0) return DSB_OK;
+  int dev = 0;
+  DSB_CHECK_CUDA(cudaGetDevice(&dev));
+  DSB_REQUIRE(dev >= 0 && dev < 64, "rms_norm_bwd_noalloc: device index %d out of range", dev);
+  if (scratch_addr[dev] == nullptr) {
+    float* p = nullptr;
+    DSB_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_norm_scratch));
+    scratch_addr[dev] = p;
+  }
+  float* scratch = scratch_addr[dev];
+  const int grid = rows < DSB_NOALLOC_NORM_MAX_PARTS ? rows : DSB_NOALLOC_NORM_MAX_PARTS;
+  DSB_REQUIRE(static_cast<long long>(grid) * hidden <= DSB_NOALLOC_NORM_MAX_FLOATS, "rms_norm_bwd_noalloc: scratch overflow");
+  DSB_NORM_DISPATCH(dtype, false, (norm_bwd_kernel<T, kLN, kNV><<<grid, THREADS, 0, stream>>>(
+                                      (const T*)dy, (const T*)x, (const T*)gamma, nullptr, rstd, (const T*)dx_add, (T*)dx,
+                                      scratch, nullptr, rows, hidden)));
+  const int cb = (hidden + 255) / 256;
+  if (dparam_f32 || dtype == 2)
+    colreduce_kernel<float><<<cb, 256, 0, stream>>>(scratch, (float*)dgamma, grid, hidden, accumulate);
+  else if (dtype == 0)
+    colreduce_kernel<__nv_bfloat16><<<cb, 256, 0, stream>>>(scratch, (__nv_bfloat16*)dgamma, grid, hidden, accumulate);
+  else
+    colreduce_kernel<__half><<<cb, 256, 0, stream>>>(scratch, (__half*)dgamma, grid, hidden, accumulate);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}

@@ -49,6 +49,7 @@ _SIGS = {
     "dsb200_norm_fwd": "pppppppp ii f ii p",
     "dsb200_norm_bwd_scratch_floats": "iii",
     "dsb200_norm_bwd": "pppppppppp ii iiii p",
+    "dsb200_rms_norm_bwd_noalloc": "ppppppp iiiii p",
     "dsb200_rope_inplace": "ppp l iiiiiii p",
     "dsb200_gated_act_fwd": "ppp l iiii p",
     "dsb200_gated_act_bwd": "ppp l iiii p",

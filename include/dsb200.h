@@ -56,6 +56,16 @@ int dsb200_norm_bwd(const void* dy, const void* x, const void* gamma, const floa
                     void* dx, void* dgamma, void* dbeta, float* scratch, int rows, int hidden, int layer_norm, int dtype,
                     int dparam_f32, int accumulate, dsb200_stream_t stream);
 
+/* RMSNorm backward that allocates nothing.  It has no counterpart in the reference.  For callers that cannot get device
+ * memory when they run (a server whose KV-cache pool already owns all free HBM; a latency-critical loop that must avoid
+ * the device-wide stall of cudaMalloc/cudaFree): the dgamma partials live in a fixed 4.6 MiB device array inside the
+ * library (148 CTAs x hidden <= 8192 floats) that every GPU loading the library holds until exit.  hidden > 8192 is
+ * rejected.  The first call on a device looks up the array's address -- make it before any stream capture.  All calls
+ * share the array (it keeps the previous call's contents; nothing needs zeroing), so calls overlapping on the GPU race. */
+int dsb200_rms_norm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* rstd, const void* dx_add,
+                                void* dx, void* dgamma, int rows, int hidden, int dtype, int dparam_f32, int accumulate,
+                                dsb200_stream_t stream);
+
 /* ---- element-wise transformer ops (reference: csrc/transformer/inference/csrc/apply_rotary_pos_emb.cu,
  * inference/v2/kernels/core_ops/gated_activations, core_ops/bias_activations, csrc/transformer/softmax_kernels.cu) */
 int dsb200_rope_inplace(void* x, const int* positions, const float* inv_freq, long long tokens, int row_stride, int head0,
