@@ -1,0 +1,393 @@
+// Flash attention backward for sm_100a on tcgen05 tensor cores (causal / full, MHA / GQA, head_dim 64/128).
+//
+// One CTA per (batch, kv-head, 128-key block); it keeps K and V resident in shared memory and dK, dV as fp32
+// accumulators in TMEM, and walks over every (q-head of the group, q block) that attends to its keys.  Per step, five
+// tcgen05 GEMMs run off the SAME swizzled smem tiles, only the UMMA descriptors (K-major vs MN-major) differ:
+//     S  = Q K^T            A = Q  (K-major)   B = K  (K-major)      -> TMEM [0,128)
+//     dP = dO V^T           A = dO (K-major)   B = V  (K-major)      -> TMEM [128,256)
+//     P  = exp2(S*c - lse), dS = P * (dP - delta) * scale            (softmax warps, thread == q row, bf16 to smem)
+//     dV += P^T dO          A = P  (MN-major)  B = dO (MN-major)     -> TMEM [256,256+D)
+//     dK += dS^T Q          A = dS (MN-major)  B = Q  (MN-major)     -> TMEM [384,384+D)
+//     dQ  = dS K            A = dS (K-major)   B = K  (MN-major)     -> TMEM [0,128) -> fp32 smem -> TMA reduce-add
+// dQ tiles from different key blocks are summed in an fp32 scratch buffer by TMA reduce-add and converted to bf16 by
+// a small follow-up kernel; delta = rowsum(dO * O) comes from a small pre-kernel.
+// Reference counterpart: csrc/transformer/softmax_kernels.cu (softmax_backward_kernel*) + cuBLAS strided-batched GEMMs
+// in ds_transformer_cuda.cpp (attention backward of the training kernel).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dsb {
+namespace attn {
+
+constexpr int BW_THREADS = 192;
+constexpr int BW_SM_THREADS = 128;
+constexpr int BW_CHUNK = 128 * 128;  // [128 rows x 64 bf16] swizzled chunk (also [128 rows x 32 fp32])
+
+template <int D>
+struct BwdSmem {
+  static constexpr int NCH = D / 64;
+  static constexpr int TILE = NCH * BW_CHUNK;
+  static constexpr int K_OFF = 0;
+  static constexpr int V_OFF = K_OFF + TILE;
+  static constexpr int Q_OFF = V_OFF + TILE;
+  static constexpr int DO_OFF = Q_OFF + TILE;
+  static constexpr int P_OFF = DO_OFF + TILE;           // 128 x 128 bf16 = 2 chunks
+  static constexpr int DS_OFF = P_OFF + 2 * BW_CHUNK;   // 128 x 128 bf16 = 2 chunks ; P+dS = 64 KB = dQ fp32 staging
+  static constexpr int BAR_OFF = DS_OFF + 2 * BW_CHUNK;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+};
+
+struct BwdParams {
+  int B, S, hq, hkv;
+  int causal;
+  float scale, scale_log2;
+  const float* lse;    // [B, hq, S] natural log
+  const float* delta;  // [B, hq, S]
+};
+
+// delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]   (one warp per (token, head))
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
+                                  float* __restrict__ delta, int B, int S, int hq, int D) {
+  const long long gw = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long total = static_cast<long long>(B) * S * hq;
+  if (gw >= total) return;
+  const long long tok = gw / hq;
+  const int h = static_cast<int>(gw - tok * hq);
+  const __nv_bfloat16* a = dout + (tok * hq + h) * D;
+  const __nv_bfloat16* b = out + (tok * hq + h) * D;
+  float acc = 0.f;
+  for (int i = lane * 2; i < D; i += 64) {
+    float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a + i));
+    float2 y = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(b + i));
+    acc += x.x * y.x + x.y * y.y;
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) {
+    const long long bidx = tok / S;
+    const long long s = tok - bidx * S;
+    delta[(bidx * hq + h) * S + s] = acc;
+  }
+}
+
+// dqkv[:, 0:hq*D] (bf16) <- dq_acc (fp32)
+__global__ void attn_dq_convert_kernel(const float* __restrict__ dq_acc, __nv_bfloat16* __restrict__ dqkv, long long tokens,
+                                       int qcols, int row_elems) {
+  const long long total = tokens * (qcols / 4);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long t = i / (qcols / 4);
+    const int c = static_cast<int>(i - t * (qcols / 4)) * 4;
+    float4 v = *reinterpret_cast<const float4*>(dq_acc + t * qcols + c);
+    uint2 o;
+    o.x = pack_bf16x2(v.x, v.y);
+    o.y = pack_bf16x2(v.z, v.w);
+    *reinterpret_cast<uint2*>(dqkv + t * row_elems + c) = o;
+  }
+}
+
+template <int D>
+__global__ void __launch_bounds__(BW_THREADS, 1)
+flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constant__ CUtensorMap tmDO,
+                 const __grid_constant__ CUtensorMap tmDQ, const __grid_constant__ CUtensorMap tmDQKV, const BwdParams p) {
+  using SMEM = BwdSmem<D>;
+  constexpr int NCH = SMEM::NCH;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM::BAR_OFF);
+  uint64_t* kv_full = bars + 0;
+  uint64_t* qdo_full = bars + 1;
+  uint64_t* qdo_empty = bars + 2;
+  uint64_t* sdp_full = bars + 3;
+  uint64_t* pds_full = bars + 4;
+  uint64_t* mma2_done = bars + 5;
+  uint64_t* dq_drained = bars + 6;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jb = blockIdx.x;  // key block
+  const int kv_head = blockIdx.y, batch = blockIdx.z;
+  const int group = p.hq / p.hkv;
+  const int n_qb = p.S / 128;
+  const int i_first = p.causal ? jb : 0;
+  const int steps_per_head = n_qb - i_first;
+  const int n_steps = group * steps_per_head;
+  const int krow0 = batch * p.S + jb * 128;
+  const int k_col = (p.hq + kv_head) * D;
+  const int v_col = (p.hq + p.hkv + kv_head) * D;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQKV);
+    tma_prefetch_desc(&tmDO);
+    tma_prefetch_desc(&tmDQ);
+    tma_prefetch_desc(&tmDQKV);
+    mbar_init(kv_full, 1);
+    mbar_init(qdo_full, 1);
+    mbar_init(qdo_empty, 1);
+    mbar_init(sdp_full, 1);
+    mbar_init(pds_full, BW_SM_THREADS);
+    mbar_init(mma2_done, 1);
+    mbar_init(dq_drained, BW_SM_THREADS);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc<1>(tmem_ptr, 512);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t TM_S = tmem_base, TM_DP = tmem_base + 128, TM_DV = tmem_base + 256, TM_DK = tmem_base + 384;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * SMEM::TILE);
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        tma_load_2d(&tmQKV, kv_full, smem + SMEM::K_OFF + c * BW_CHUNK, k_col + c * 64, krow0);
+        tma_load_2d(&tmQKV, kv_full, smem + SMEM::V_OFF + c * BW_CHUNK, v_col + c * 64, krow0);
+      }
+      for (int t = 0; t < n_steps; ++t) {
+        const int g = t / steps_per_head;
+        const int i = i_first + (t - g * steps_per_head);
+        const int head = kv_head * group + g;
+        const int qrow0 = batch * p.S + i * 128;
+        mbar_wait(qdo_empty, (t & 1) ^ 1);
+        mbar_expect_tx(qdo_full, 2 * SMEM::TILE);
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          tma_load_2d(&tmQKV, qdo_full, smem + SMEM::Q_OFF + c * BW_CHUNK, head * D + c * 64, qrow0);
+          tma_load_2d(&tmDO, qdo_full, smem + SMEM::DO_OFF + c * BW_CHUNK, head * D + c * 64, qrow0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = umma_idesc(128, 128, 1, 1, 0, 0);   // Q K^T, dO V^T : both K-major
+      constexpr uint32_t idesc_dkv = umma_idesc(128, D, 1, 1, 1, 1);   // P^T dO, dS^T Q: both MN-major
+      constexpr uint32_t idesc_dq = umma_idesc(128, D, 1, 1, 0, 1);    // dS K          : A K-major, B MN-major
+      const uint32_t k_s = smem_u32(smem + SMEM::K_OFF), v_s = smem_u32(smem + SMEM::V_OFF);
+      const uint32_t q_s = smem_u32(smem + SMEM::Q_OFF), do_s = smem_u32(smem + SMEM::DO_OFF);
+      const uint32_t p_s = smem_u32(smem + SMEM::P_OFF), ds_s = smem_u32(smem + SMEM::DS_OFF);
+      mbar_wait(kv_full, 0);
+      for (int t = 0; t < n_steps; ++t) {
+        mbar_wait(qdo_full, t & 1);
+        if (t > 0) mbar_wait(dq_drained, (t - 1) & 1);  // TMEM [0,128) and the P/dS smem (dQ staging) are free again
+        tc_fence_after();
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
+          umma_f16<1>(TM_S, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_s, kk != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
+          umma_f16<1>(TM_DP, umma_smem_desc(do_s + off, 16, 1024), umma_smem_desc(v_s + off, 16, 1024), idesc_s, kk != 0);
+        }
+        umma_commit<1>(sdp_full);
+        mbar_wait(pds_full, t & 1);
+        tc_fence_after();
+        // reduction dimension = the 128 q rows: 8 k-steps of 16 rows (2048 B apart in every [rows x 64] chunk)
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          umma_f16<1>(TM_DV, umma_smem_desc(p_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(do_s + kk * 2048, BW_CHUNK, 1024),
+                      idesc_dkv, (t | kk) != 0);
+        }
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          umma_f16<1>(TM_DK, umma_smem_desc(ds_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(q_s + kk * 2048, BW_CHUNK, 1024),
+                      idesc_dkv, (t | kk) != 0);
+        }
+        // dQ = dS K : reduction dimension = 128 keys
+#pragma unroll
+        for (int kk = 0; kk < 8; ++kk) {
+          const uint32_t a_off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
+          umma_f16<1>(TM_S, umma_smem_desc(ds_s + a_off, 16, 1024), umma_smem_desc(k_s + kk * 2048, BW_CHUNK, 1024), idesc_dq,
+                      kk != 0);
+        }
+        umma_commit<1>(mma2_done);
+        umma_commit<1>(qdo_empty);
+      }
+    }
+  } else {
+    const int q4 = warp & 3;
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
+    const int sw = row & 7;
+    const int epi_tid = threadIdx.x - 64;
+    for (int t = 0; t < n_steps; ++t) {
+      const int g = t / steps_per_head;
+      const int i = i_first + (t - g * steps_per_head);
+      const int head = kv_head * group + g;
+      const size_t stat_idx = (static_cast<size_t>(batch) * p.hq + head) * p.S + i * 128 + row;
+      const float lse2 = p.lse[stat_idx] * 1.4426950408889634f;
+      const float dlt = p.delta[stat_idx];
+      const bool diag = p.causal && (i == jb);
+      mbar_wait(sdp_full, t & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t sv[32], dv[32];
+        tmem_ld_32x32(TM_S + c * 32 + lane_off, sv);
+        tmem_ld_32x32(TM_DP + c * 32 + lane_off, dv);
+        tmem_ld_wait();
+        uint8_t* prow = smem + SMEM::P_OFF + (c >> 1) * BW_CHUNK + row * 128;
+        uint8_t* dsrow = smem + SMEM::DS_OFF + (c >> 1) * BW_CHUNK + row * 128;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          float pe[8], de[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int col = c * 32 + u * 8 + k;
+            float pv = exp2f(fmaf(__uint_as_float(sv[u * 8 + k]), p.scale_log2, -lse2));
+            if (diag && col > row) pv = 0.f;
+            pe[k] = pv;
+            de[k] = pv * (__uint_as_float(dv[u * 8 + k]) - dlt) * p.scale;
+          }
+          uint4 a, b;
+          a.x = pack_bf16x2(pe[0], pe[1]); a.y = pack_bf16x2(pe[2], pe[3]); a.z = pack_bf16x2(pe[4], pe[5]); a.w = pack_bf16x2(pe[6], pe[7]);
+          b.x = pack_bf16x2(de[0], de[1]); b.y = pack_bf16x2(de[2], de[3]); b.z = pack_bf16x2(de[4], de[5]); b.w = pack_bf16x2(de[6], de[7]);
+          const int unit = (c & 1) * 4 + u;
+          *reinterpret_cast<uint4*>(prow + ((unit ^ sw) << 4)) = a;
+          *reinterpret_cast<uint4*>(dsrow + ((unit ^ sw) << 4)) = b;
+        }
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(pds_full);
+
+      // ---- drain dQ: TMEM [0,D) fp32 -> swizzled fp32 staging (the P/dS buffers, free once mma2 retired) -> TMA reduce-add
+      mbar_wait(mma2_done, t & 1);
+      tc_fence_after();
+      uint8_t* stage = smem + SMEM::P_OFF;
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(TM_S + c * 32 + lane_off, v);
+        tmem_ld_wait();
+        uint8_t* rowp = stage + c * BW_CHUNK + row * 128;
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          *reinterpret_cast<uint4*>(rowp + ((u ^ sw) << 4)) = make_uint4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      named_bar_sync(1, BW_SM_THREADS);
+      if (epi_tid == 0) {
+        const int qrow0 = batch * p.S + i * 128;
+#pragma unroll
+        for (int c = 0; c < D / 32; ++c) tma_reduce_add_2d(&tmDQ, stage + c * BW_CHUNK, head * D + c * 32, qrow0);
+        tma_commit_group();
+        tma_wait_group_read<0>();
+      }
+      mbar_arrive(dq_drained);
+    }
+
+    // ---- dK, dV epilogue: TMEM -> bf16 -> swizzled staging (Q / dO tiles are dead) -> TMA store into packed dqkv
+    tc_fence_after();
+#pragma unroll
+    for (int which = 0; which < 2; ++which) {
+      const uint32_t tm = which == 0 ? TM_DK : TM_DV;
+      uint8_t* stage = smem + (which == 0 ? SMEM::Q_OFF : SMEM::DO_OFF);
+#pragma unroll
+      for (int c = 0; c < D / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(tm + c * 32 + lane_off, v);
+        tmem_ld_wait();
+        uint8_t* rowp = stage + (c >> 1) * BW_CHUNK + row * 128;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          uint4 val;
+          val.x = pack_bf16x2(__uint_as_float(v[8 * u + 0]), __uint_as_float(v[8 * u + 1]));
+          val.y = pack_bf16x2(__uint_as_float(v[8 * u + 2]), __uint_as_float(v[8 * u + 3]));
+          val.z = pack_bf16x2(__uint_as_float(v[8 * u + 4]), __uint_as_float(v[8 * u + 5]));
+          val.w = pack_bf16x2(__uint_as_float(v[8 * u + 6]), __uint_as_float(v[8 * u + 7]));
+          const int unit = (c & 1) * 4 + u;
+          *reinterpret_cast<uint4*>(rowp + ((unit ^ sw) << 4)) = val;
+        }
+      }
+    }
+    fence_proxy_async_smem();
+    named_bar_sync(1, BW_SM_THREADS);
+    if (epi_tid == 0) {
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        tma_store_2d(&tmDQKV, smem + SMEM::Q_OFF + c * BW_CHUNK, k_col + c * 64, krow0);
+        tma_store_2d(&tmDQKV, smem + SMEM::DO_OFF + c * BW_CHUNK, v_col + c * 64, krow0);
+      }
+      tma_commit_group();
+      tma_wait_group<0>();
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 512);
+  }
+}
+
+template <int D>
+static int launch_bwd(const void* dout, const void* qkv, const void* out, const float* lse, void* dqkv, float* dq_acc,
+                      float* delta, int B, int S, int hq, int hkv, int causal, float scale, cudaStream_t stream) {
+  using SMEM = BwdSmem<D>;
+  const long long tokens = static_cast<long long>(B) * S;
+  const int row_elems = (hq + 2 * hkv) * D;
+  {
+    const long long warps = tokens * hq;
+    const int threads = 256;
+    const long long blocks = (warps * 32 + threads - 1) / threads;
+    attn_delta_kernel<<<static_cast<unsigned>(blocks), threads, 0, stream>>>(
+        static_cast<const __nv_bfloat16*>(dout), static_cast<const __nv_bfloat16*>(out), delta, B, S, hq, D);
+  }
+  CUtensorMap tmQKV, tmDO, tmDQ, tmDQKV;
+  int rc = make_tensor_map_2d(&tmQKV, TMA_BF16, qkv, tokens, row_elems, row_elems, 128, 64, TMA_SW_128);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tmDO, TMA_BF16, dout, tokens, hq * D, hq * D, 128, 64, TMA_SW_128);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tmDQ, TMA_F32, dq_acc, tokens, hq * D, hq * D, 128, 32, TMA_SW_128);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tmDQKV, TMA_BF16, dqkv, tokens, row_elems, row_elems, 128, 64, TMA_SW_128);
+  if (rc) return rc;
+  auto kern = flash_bwd_kernel<D>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM::TOTAL));
+    attr_set = true;
+  }
+  BwdParams p;
+  p.B = B; p.S = S; p.hq = hq; p.hkv = hkv; p.causal = causal;
+  p.scale = scale;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  p.lse = lse;
+  p.delta = delta;
+  dim3 grid(S / 128, hkv, B);
+  kern<<<grid, BW_THREADS, SMEM::TOTAL, stream>>>(tmQKV, tmDO, tmDQ, tmDQKV, p);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  const int qcols = hq * D;
+  long long work = tokens * (qcols / 4);
+  int blocks = static_cast<int>((work + 255) / 256 < 148 * 16 ? (work + 255) / 256 : 148 * 16);
+  attn_dq_convert_kernel<<<blocks, 256, 0, stream>>>(dq_acc, static_cast<__nv_bfloat16*>(dqkv), tokens, qcols, row_elems);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+}  // namespace attn
+}  // namespace dsb
+
+// Gradient of dsb200_flash_attn_fwd.  dout/out: [B*S, hq*D] bf16; qkv, dqkv: packed [B*S, (hq+2*hkv)*D] bf16;
+// lse: [B, hq, S] from the forward.  Scratch supplied by the caller: dq_acc [B*S, hq*D] fp32 ZERO-INITIALISED,
+// delta [B, hq, S] fp32.
+DSB_EXPORT int dsb200_flash_attn_bwd(const void* dout, const void* qkv, const void* out, const float* lse, void* dqkv,
+                                     float* dq_acc, float* delta, int B, int S, int hq, int hkv, int head_dim, int causal,
+                                     float scale, cudaStream_t stream) {
+  using namespace dsb;
+  DSB_REQUIRE(head_dim == 64 || head_dim == 128, "flash_attn_bwd: head_dim %d unsupported (64 or 128)", head_dim);
+  DSB_REQUIRE(S % 128 == 0 && S > 0, "flash_attn_bwd: sequence length %d must be a multiple of 128", S);
+  DSB_REQUIRE(hq % hkv == 0, "flash_attn_bwd: hq %d not a multiple of hkv %d", hq, hkv);
+  if (head_dim == 128)
+    return attn::launch_bwd<128>(dout, qkv, out, lse, dqkv, dq_acc, delta, B, S, hq, hkv, causal, scale, stream);
+  return attn::launch_bwd<64>(dout, qkv, out, lse, dqkv, dq_acc, delta, B, S, hq, hkv, causal, scale, stream);
+}

@@ -194,3 +194,19 @@ def test_fused_adam_optimizer_class_and_lion_lamb():
     ratio = min(max((w0.norm() / upd.norm()).item(), 0.01), 10.0)
     assert torch.allclose(w.detach(), w0 - 1e-2 * ratio * upd, atol=1e-5)
     assert abs(opt.get_lamb_coeffs()[0] - ratio) < 1e-4
+
+
+@pytest.mark.parametrize("cfg", [(2, 256, 2, 2, 128, True), (2, 512, 4, 2, 128, True), (1, 384, 2, 2, 64, True), (2, 256, 2, 1, 128, False)])
+def test_flash_attention_fwd_bwd(cfg):
+    from deepspeedsyclsupport_b200.ops.attention import attention, attention_ref
+    B, S, hq, hkv, d, causal = cfg
+    torch.manual_seed(0)
+    qkv = torch.randn(B * S, (hq + 2 * hkv) * d, device=_dev(), dtype=torch.bfloat16, requires_grad=True)
+    out = attention(qkv, B, S, hq, hkv, d, causal=causal)
+    dout = torch.randn_like(out)
+    out.backward(dout)
+    qf = qkv.detach().float().requires_grad_()
+    ref = attention_ref(qf, B, S, hq, hkv, d, causal)
+    ref.backward(dout.float())
+    assert (out.float() - ref).abs().max() < 2e-2
+    assert (qkv.grad.float() - qf.grad).abs().max() < 2e-2 * max(1.0, qf.grad.abs().max().item())

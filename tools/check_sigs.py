@@ -12,7 +12,7 @@ def main():
     from deepspeedsyclsupport_b200.ops import native
     # importing op modules registers their signatures
     import importlib
-    for m in ("gemm", "fused_ops", "adam", "quantizer", "attention", "ragged_ops", "moe_ops", "misc_ops"):
+    for m in ("gemm", "fused_ops", "flat_optim", "quantizer", "attention", "flash_attention", "ragged_ops", "moe_ops", "misc_ops", "symm"):
         try:
             importlib.import_module("deepspeedsyclsupport_b200.ops." + m)
         except ImportError:
