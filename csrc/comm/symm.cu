@@ -1,0 +1,367 @@
+// Peer-memory ("symmetric memory") runtime and collective kernels over NVLink-5 / NVSwitch.
+//
+// Every rank allocates the same-sized buffer with cudaMalloc, exports a CUDA IPC handle, and maps all peers' buffers;
+// kernels then address peer memory directly with ld/st.global (NVSwitch gives every pair full bandwidth, so all
+// algorithms here are single-hop "pull" or "push" -- no rings, no hierarchy).  Cross-GPU ordering uses a flag pad in
+// the same symmetric allocation: writers publish with st.release.sys after their data stores, readers spin (bounded)
+// with ld.acquire.sys.  The reference has no counterpart: its only backend is torch.distributed/NCCL (oneCCL + a
+// POSIX-shm all-reduce on CPU, csrc/cpu/comm/ccl.cpp:540-611); these kernels take the role of the collectives at
+// call sites C1/C3/C7/C8/C11/C16 of SURVEY.md 2.5 and feed the fused paths (RS -> cast/scale -> Adam, AG -> GEMM).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dsb {
+namespace symm {
+
+constexpr int MAX_RANKS = 16;
+
+struct Peers {
+  void* ptr[MAX_RANKS];  // base of every rank's symmetric buffer (own rank included), as mapped in THIS process
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+// peer data may change between kernels: relaxed system-scope loads (never the non-coherent path)
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+
+// ---------------------------------------------------------------- device-wide barrier across ranks
+// flags: W uint32 slots at byte offset `flag_off` of every rank's symmetric buffer.  Rank r writes `epoch` into slot r of
+// every peer, then waits until all W local slots reached `epoch`.  One CTA, W threads.
+__global__ void barrier_kernel(Peers peers, size_t flag_off, int rank, int world, uint32_t epoch, int* error_flag) {
+  __threadfence_system();
+  const int t = threadIdx.x;
+  if (t < world) {
+    uint32_t* remote = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(peers.ptr[t]) + flag_off) + rank;
+    st_release_sys(remote, epoch);
+    const uint32_t* local = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(peers.ptr[rank]) + flag_off) + t;
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(local) - epoch) < 0) {
+      if (++spins > DSB_SPIN_LIMIT) {
+        if (error_flag) *error_flag = 1;
+        printf("dsb200: cross-GPU barrier timed out on rank %d waiting for rank %d (epoch %u)\n", rank, t, epoch);
+        __trap();
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  __threadfence_system();
+}
+
+// ---------------------------------------------------------------- all-gather (pull): out[p*n .. (p+1)*n) = peer p's shard
+// `src_off` = byte offset of the shard inside each rank's symmetric buffer; dst is local memory (any allocation).
+__global__ void allgather_pull_kernel(Peers peers, size_t src_off, uint8_t* __restrict__ dst, size_t bytes_per_rank, int rank,
+                                      int world) {
+  const size_t vecs = bytes_per_rank / 16;
+  const size_t total = vecs * world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    // start each rank on a different peer so the NVSwitch ports are loaded evenly
+    const int pi = static_cast<int>(i / vecs);
+    const int peer = (pi + rank) % world;
+    const size_t v = i - static_cast<size_t>(pi) * vecs;
+    const uint4 val = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + v * 16);
+    *reinterpret_cast<uint4*>(dst + static_cast<size_t>(peer) * bytes_per_rank + v * 16) = val;
+  }
+}
+
+// ---------------------------------------------------------------- reduce-scatter (pull) fused with scale / cast / norm
+// Every rank holds a full gradient buffer (bf16 or fp32) of world*n elements at `src_off` of its symmetric buffer.
+// Rank r sums slice r over all peers in fp32, multiplies by `scale`, and either stores or accumulates into `dst`
+// (fp32 or bf16).  Optionally adds sum(g^2) of the result into `sumsq` (one atomicAdd per CTA) for the gradient norm.
+template <bool SRC_BF16, bool DST_BF16>
+__global__ void reduce_scatter_pull_kernel(Peers peers, size_t src_off, void* __restrict__ dst, size_t n, int rank, int world,
+                                           float scale, int accumulate, float* __restrict__ sumsq) {
+  constexpr int EPV = SRC_BF16 ? 8 : 4;  // elements per 16-byte vector
+  const size_t vecs = n / EPV;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t esz = SRC_BF16 ? 2 : 4;
+  float local_sq = 0.f;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < vecs; v += stride) {
+    float acc[EPV];
+#pragma unroll
+    for (int k = 0; k < EPV; ++k) acc[k] = 0.f;
+    for (int pi = 0; pi < world; ++pi) {
+      const int peer = (pi + rank) % world;
+      const uint4 raw = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + (static_cast<size_t>(rank) * n + v * EPV) * esz);
+      if constexpr (SRC_BF16) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float2 f = __bfloat1622float2(h[k]);
+          acc[2 * k] += f.x;
+          acc[2 * k + 1] += f.y;
+        }
+      } else {
+        acc[0] += __uint_as_float(raw.x); acc[1] += __uint_as_float(raw.y);
+        acc[2] += __uint_as_float(raw.z); acc[3] += __uint_as_float(raw.w);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < EPV; ++k) acc[k] *= scale;
+    if constexpr (DST_BF16) {
+      __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst) + v * EPV;
+      if (accumulate) {
+#pragma unroll
+        for (int k = 0; k < EPV; ++k) acc[k] += __bfloat162float(d[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < EPV; k += 2) *reinterpret_cast<uint32_t*>(d + k) = pack_bf16x2(acc[k], acc[k + 1]);
+    } else {
+      float* d = static_cast<float*>(dst) + v * EPV;
+      if (accumulate) {
+#pragma unroll
+        for (int k = 0; k < EPV; ++k) acc[k] += d[k];
+      }
+#pragma unroll
+      for (int k = 0; k < EPV; k += 4) *reinterpret_cast<float4*>(d + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+    }
+    if (sumsq) {
+#pragma unroll
+      for (int k = 0; k < EPV; ++k) local_sq = fmaf(acc[k], acc[k], local_sq);
+    }
+  }
+  if (sumsq) {
+    __shared__ float red[32];
+    local_sq = warp_sum(local_sq);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) red[w] = local_sq;
+    __syncthreads();
+    if (w == 0) {
+      float t = l < (blockDim.x >> 5) ? red[l] : 0.f;
+      t = warp_sum(t);
+      if (l == 0) atomicAdd(sumsq, t);
+    }
+  }
+}
+
+// ---------------------------------------------------------------- reduce-scatter fused with the partitioned AdamW update
+// One pass: g = scale * sum_peers grad[peer][rank*n + i]; Adam on the fp32 master shard; bf16 parameter shard written.
+// Valid when no global-norm clipping is needed before the update (gradient_clipping == 0) -- otherwise use the
+// reduce-scatter above (which produces the norm) followed by the fused Adam kernel.
+struct RsAdamArgs {
+  float lr, beta1, beta2, eps, weight_decay, bc1, bc2_rsqrt, scale;
+  int adamw;
+};
+__global__ void rs_adam_kernel(Peers peers, size_t src_off, float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
+                               __nv_bfloat16* __restrict__ lp, size_t n, int rank, int world, RsAdamArgs a) {
+  const size_t vecs = n / 8;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t vi = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; vi < vecs; vi += stride) {
+    float g[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) g[k] = 0.f;
+    for (int pi = 0; pi < world; ++pi) {
+      const int peer = (pi + rank) % world;
+      const uint4 raw = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + (static_cast<size_t>(rank) * n + vi * 8) * 2);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float2 f = __bfloat1622float2(h[k]);
+        g[2 * k] += f.x;
+        g[2 * k + 1] += f.y;
+      }
+    }
+    const size_t e = vi * 8;
+    float pp[8], mm[8], vv[8];
+    *reinterpret_cast<float4*>(pp) = *reinterpret_cast<const float4*>(p + e);
+    *reinterpret_cast<float4*>(pp + 4) = *reinterpret_cast<const float4*>(p + e + 4);
+    *reinterpret_cast<float4*>(mm) = *reinterpret_cast<const float4*>(m + e);
+    *reinterpret_cast<float4*>(mm + 4) = *reinterpret_cast<const float4*>(m + e + 4);
+    *reinterpret_cast<float4*>(vv) = *reinterpret_cast<const float4*>(v + e);
+    *reinterpret_cast<float4*>(vv + 4) = *reinterpret_cast<const float4*>(v + e + 4);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      float gg = g[k] * a.scale;
+      if (!a.adamw) gg = fmaf(a.weight_decay, pp[k], gg);
+      mm[k] = fmaf(a.beta1, mm[k], (1.f - a.beta1) * gg);
+      vv[k] = fmaf(a.beta2, vv[k], (1.f - a.beta2) * gg * gg);
+      float upd = (mm[k] * a.bc1) / (sqrtf(vv[k]) * a.bc2_rsqrt + a.eps);
+      if (a.adamw) upd = fmaf(a.weight_decay, pp[k], upd);
+      pp[k] = fmaf(-a.lr, upd, pp[k]);
+    }
+    *reinterpret_cast<float4*>(p + e) = *reinterpret_cast<float4*>(pp);
+    *reinterpret_cast<float4*>(p + e + 4) = *reinterpret_cast<float4*>(pp + 4);
+    *reinterpret_cast<float4*>(m + e) = *reinterpret_cast<float4*>(mm);
+    *reinterpret_cast<float4*>(m + e + 4) = *reinterpret_cast<float4*>(mm + 4);
+    *reinterpret_cast<float4*>(v + e) = *reinterpret_cast<float4*>(vv);
+    *reinterpret_cast<float4*>(v + e + 4) = *reinterpret_cast<float4*>(vv + 4);
+    uint4 o;
+    o.x = pack_bf16x2(pp[0], pp[1]); o.y = pack_bf16x2(pp[2], pp[3]); o.z = pack_bf16x2(pp[4], pp[5]); o.w = pack_bf16x2(pp[6], pp[7]);
+    *reinterpret_cast<uint4*>(lp + e) = o;
+  }
+}
+
+// ---------------------------------------------------------------- one-shot all-reduce (small messages: TP inference)
+// in place on a region of the symmetric buffer: every rank reads all peers' copies, sums in fp32, writes `dst` (local,
+// may be ordinary memory).  Optional fused residual add + RMSNorm is done by the caller's next kernel.
+__global__ void allreduce_oneshot_kernel(Peers peers, size_t src_off, __nv_bfloat16* __restrict__ dst, size_t n, int rank,
+                                         int world) {
+  const size_t vecs = n / 8;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t vi = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; vi < vecs; vi += stride) {
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
+    for (int pi = 0; pi < world; ++pi) {
+      const int peer = (pi + rank) % world;
+      const uint4 raw = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + vi * 16);
+      const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float2 f = __bfloat1622float2(h[k]);
+        acc[2 * k] += f.x;
+        acc[2 * k + 1] += f.y;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]); o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+    *reinterpret_cast<uint4*>(dst + vi * 8) = o;
+  }
+}
+
+static int comm_grid(size_t vecs, int max_ctas) {
+  size_t b = (vecs + 255) / 256;
+  size_t cap = max_ctas > 0 ? static_cast<size_t>(max_ctas) : static_cast<size_t>(num_sms()) * 4;
+  if (b < 1) b = 1;
+  return static_cast<int>(b < cap ? b : cap);
+}
+
+static int make_peers(Peers* out, void* const* peer_ptrs, int world) {
+  if (world < 1 || world > MAX_RANKS) {
+    set_last_error("symm: world size %d unsupported (max %d)", world, MAX_RANKS);
+    return DSB_ERR_ARG;
+  }
+  for (int i = 0; i < MAX_RANKS; ++i) out->ptr[i] = i < world ? peer_ptrs[i] : nullptr;
+  return DSB_OK;
+}
+
+}  // namespace symm
+}  // namespace dsb
+
+using namespace dsb;
+using namespace dsb::symm;
+
+// ---- allocation / mapping (host pointers unless noted)
+DSB_EXPORT int dsb200_symm_alloc(long long bytes, void** ptr, unsigned char* handle64) {
+  DSB_CHECK_CUDA(cudaMalloc(ptr, static_cast<size_t>(bytes)));
+  DSB_CHECK_CUDA(cudaMemset(*ptr, 0, static_cast<size_t>(bytes)));
+  cudaIpcMemHandle_t h;
+  DSB_CHECK_CUDA(cudaIpcGetMemHandle(&h, *ptr));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return DSB_OK;
+}
+DSB_EXPORT int dsb200_symm_open(const unsigned char* handle64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DSB_CHECK_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return DSB_OK;
+}
+DSB_EXPORT int dsb200_symm_close(void* ptr) {
+  DSB_CHECK_CUDA(cudaIpcCloseMemHandle(ptr));
+  return DSB_OK;
+}
+DSB_EXPORT int dsb200_symm_free(void* ptr) {
+  DSB_CHECK_CUDA(cudaFree(ptr));
+  return DSB_OK;
+}
+
+// peer_ptrs: HOST array of `world` device pointers (this process's mappings of every rank's buffer, own included)
+DSB_EXPORT int dsb200_symm_barrier(void* const* peer_ptrs, long long flag_off, int rank, int world, unsigned int epoch,
+                                   cudaStream_t stream) {
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  barrier_kernel<<<1, 32, 0, stream>>>(P, static_cast<size_t>(flag_off), rank, world, epoch, nullptr);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_p2p_allgather(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
+                                    int world, int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(bytes_per_rank % 16 == 0 && src_off % 16 == 0, "p2p_allgather: sizes/offsets must be multiples of 16 bytes");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  const size_t vecs = static_cast<size_t>(bytes_per_rank) / 16 * world;
+  allgather_pull_kernel<<<comm_grid(vecs, max_ctas), 256, 0, stream>>>(P, static_cast<size_t>(src_off), static_cast<uint8_t*>(dst),
+                                                                         static_cast<size_t>(bytes_per_rank), rank, world);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// src dtype / dst dtype: 0 bf16, 2 fp32.  n = elements per rank (multiple of 8).  sumsq: optional device float (+= sum g^2).
+DSB_EXPORT int dsb200_p2p_reduce_scatter(void* const* peer_ptrs, long long src_off, int src_dtype, void* dst, int dst_dtype,
+                                         long long n, int rank, int world, float scale, int accumulate, float* sumsq,
+                                         int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(n % 8 == 0 && src_off % 16 == 0, "p2p_reduce_scatter: n must be a multiple of 8 and the offset 16-byte aligned");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  const size_t vecs = static_cast<size_t>(n) / (src_dtype == 0 ? 8 : 4);
+  const int grid = comm_grid(vecs, max_ctas);
+  const size_t off = static_cast<size_t>(src_off);
+  if (src_dtype == 0 && dst_dtype == 0)
+    reduce_scatter_pull_kernel<true, true><<<grid, 256, 0, stream>>>(P, off, dst, (size_t)n, rank, world, scale, accumulate, sumsq);
+  else if (src_dtype == 0 && dst_dtype == 2)
+    reduce_scatter_pull_kernel<true, false><<<grid, 256, 0, stream>>>(P, off, dst, (size_t)n, rank, world, scale, accumulate, sumsq);
+  else if (src_dtype == 2 && dst_dtype == 2)
+    reduce_scatter_pull_kernel<false, false><<<grid, 256, 0, stream>>>(P, off, dst, (size_t)n, rank, world, scale, accumulate, sumsq);
+  else {
+    set_last_error("p2p_reduce_scatter: unsupported dtype combination %d -> %d", src_dtype, dst_dtype);
+    return DSB_ERR_UNSUPPORTED;
+  }
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, float* m, float* v, void* lp, long long n,
+                                  int rank, int world, float scale, float lr, float beta1, float beta2, float eps,
+                                  float weight_decay, int adamw_mode, int bias_correction, int step, int max_ctas,
+                                  cudaStream_t stream) {
+  DSB_REQUIRE(n % 8 == 0 && src_off % 16 == 0, "p2p_rs_adam: n must be a multiple of 8 and the offset 16-byte aligned");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  RsAdamArgs a;
+  a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.adamw = adamw_mode; a.scale = scale;
+  a.bc1 = bias_correction ? 1.f / (1.f - powf(beta1, (float)step)) : 1.f;
+  a.bc2_rsqrt = bias_correction ? 1.f / sqrtf(1.f - powf(beta2, (float)step)) : 1.f;
+  rs_adam_kernel<<<comm_grid(static_cast<size_t>(n) / 8, max_ctas), 256, 0, stream>>>(
+      P, static_cast<size_t>(src_off), p, m, v, static_cast<__nv_bfloat16*>(lp), static_cast<size_t>(n), rank, world, a);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_p2p_allreduce_bf16(void* const* peer_ptrs, long long src_off, void* dst, long long n, int rank, int world,
+                                         int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(n % 8 == 0 && src_off % 16 == 0, "p2p_allreduce: n must be a multiple of 8 and the offset 16-byte aligned");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  allreduce_oneshot_kernel<<<comm_grid(static_cast<size_t>(n) / 8, max_ctas), 256, 0, stream>>>(
+      P, static_cast<size_t>(src_off), static_cast<__nv_bfloat16*>(dst), static_cast<size_t>(n), rank, world);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}

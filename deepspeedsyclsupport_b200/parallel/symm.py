@@ -1,0 +1,161 @@
+"""Symmetric (peer-mapped) device memory over CUDA IPC + the P2P collective kernels of csrc/comm/symm.cu.
+
+`SymmetricBuffer(group, nbytes)` gives every rank of `group` a buffer of the same size; each rank maps all peers'
+buffers, so kernels can load/store remote HBM directly over NVLink/NVSwitch.  Layout of a buffer:
+    [ data region : nbytes ][ flag pad : 4 KiB ]
+Cross-rank ordering uses `barrier()` -- a one-CTA kernel on the current stream that publishes an epoch to every peer's
+flag pad and waits for all peers (bounded spin) -- so no host synchronisation is involved.
+
+`EmulatedPeers` builds the same structure inside ONE process on ONE GPU (W local buffers); it is how the collective
+kernels are tested on a single GPU (each "rank's" kernel is launched in turn, no cross-kernel waiting).
+"""
+import ctypes
+
+import torch
+
+from .. import comm as dist
+from ..ops import native
+
+native.register_sigs({
+    "dsb200_symm_alloc": "l pp",
+    "dsb200_symm_open": "pp",
+    "dsb200_symm_close": "p",
+    "dsb200_symm_free": "p",
+    "dsb200_symm_barrier": "p l ii i p",
+    "dsb200_p2p_allgather": "p l p l iii p",
+    "dsb200_p2p_reduce_scatter": "p l i p i l ii f i p i p",
+    "dsb200_p2p_rs_adam": "p l pppp l ii f fffff iii i p",
+    "dsb200_p2p_allreduce_bf16": "p l p l iii p",
+})
+
+FLAG_PAD = 4096
+_DT = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
+
+
+class _RawCudaArray:
+    """Minimal __cuda_array_interface__ carrier so torch can alias raw device memory without copying."""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes, ), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+def _alias(ptr, nbytes, device):
+    t = torch.as_tensor(_RawCudaArray(ptr, nbytes), device=device)
+    return t
+
+
+class _PeerOps:
+    """Kernels shared by the real and the emulated flavour.  `self.ptrs` = list of W base pointers, `self.rank`."""
+
+    def _table(self):
+        arr = (ctypes.c_void_p * self.world)(*self.ptrs)
+        return arr
+
+    def view(self, offset, shape, dtype, rank=None):
+        """Tensor aliasing [offset, offset + numel*itemsize) of (this rank's, or `rank`'s mapped) buffer."""
+        n = 1
+        for s in shape:
+            n *= s
+        nbytes = n * torch.empty(0, dtype=dtype).element_size()
+        assert offset + nbytes <= self.nbytes, "symmetric buffer overflow"
+        base = self.ptrs[self.rank if rank is None else rank]
+        key = (base, offset, nbytes, dtype)
+        raw = _alias(base + offset, nbytes, self.device)
+        self._keep.append(raw)
+        return raw.view(dtype).view(*shape)
+
+    def all_gather(self, out, src_offset, bytes_per_rank, rank=None, max_ctas=0):
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_allgather(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(out),
+                                               bytes_per_rank, r, self.world, max_ctas, native.stream_ptr())
+        native.check(rc)
+        return out
+
+    def reduce_scatter(self, dst, src_offset, src_dtype, n_per_rank, scale=1.0, accumulate=False, sumsq=None, rank=None,
+                       max_ctas=0):
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_reduce_scatter(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, _DT[src_dtype],
+                                                    native.ptr(dst), _DT[dst.dtype], n_per_rank, r, self.world, float(scale),
+                                                    int(accumulate), native.ptr(sumsq), max_ctas, native.stream_ptr())
+        native.check(rc)
+        return dst
+
+    def rs_adam(self, src_offset, p, m, v, lp, n_per_rank, *, scale, lr, beta1, beta2, eps, weight_decay, adamw_mode=True,
+                bias_correction=True, step=1, rank=None, max_ctas=0):
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_rs_adam(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(p), native.ptr(m),
+                                             native.ptr(v), native.ptr(lp), n_per_rank, r, self.world, float(scale), lr, beta1, beta2,
+                                             eps, weight_decay, int(adamw_mode), int(bias_correction), int(step), max_ctas,
+                                             native.stream_ptr())
+        native.check(rc)
+
+    def all_reduce_bf16(self, dst, src_offset, n, rank=None, max_ctas=0):
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_allreduce_bf16(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(dst), n, r,
+                                                    self.world, max_ctas, native.stream_ptr())
+        native.check(rc)
+        return dst
+
+
+class SymmetricBuffer(_PeerOps):
+
+    def __init__(self, group, nbytes):
+        assert torch.cuda.is_available()
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        self.nbytes = (int(nbytes) + 255) // 256 * 256
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._keep = []
+        self._epoch = 0
+        lib = native.lib()
+        ptr = ctypes.c_void_p()
+        handle = (ctypes.c_ubyte * 64)()
+        rc = lib.dsb200_symm_alloc(self.nbytes + FLAG_PAD, ctypes.addressof(ptr), ctypes.addressof(handle))
+        native.check(rc, 0)
+        self.local_ptr = ptr.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        self.ptrs = []
+        self._opened = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.ptrs.append(self.local_ptr)
+                continue
+            hp = (ctypes.c_ubyte * 64).from_buffer_copy(h)
+            p = ctypes.c_void_p()
+            rc = lib.dsb200_symm_open(ctypes.addressof(hp), ctypes.addressof(p))
+            native.check(rc, 0)
+            self.ptrs.append(p.value)
+            self._opened.append(p.value)
+        dist.barrier(group=group)
+
+    def barrier(self):
+        """Device-side barrier across the group on the current stream (no host sync)."""
+        self._epoch += 1
+        rc = native.lib().dsb200_symm_barrier(ctypes.cast(self._table(), ctypes.c_void_p), self.nbytes, self.rank, self.world,
+                                              self._epoch, native.stream_ptr())
+        native.check(rc)
+
+    def close(self):
+        lib = native.lib()
+        torch.cuda.synchronize()
+        for p in self._opened:
+            lib.dsb200_symm_close(p)
+        self._opened = []
+        if self.local_ptr:
+            lib.dsb200_symm_free(self.local_ptr)
+            self.local_ptr = None
+
+
+class EmulatedPeers(_PeerOps):
+    """W peer buffers inside one process (single-GPU tests of the P2P kernels)."""
+
+    def __init__(self, world, nbytes):
+        self.world = world
+        self.rank = 0
+        self.nbytes = (int(nbytes) + 255) // 256 * 256
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        self._keep = []
+        self._bufs = [torch.zeros(self.nbytes + FLAG_PAD, dtype=torch.uint8, device=self.device) for _ in range(world)]
+        self.ptrs = [b.data_ptr() for b in self._bufs]

@@ -210,3 +210,49 @@ def test_flash_attention_fwd_bwd(cfg):
     ref.backward(dout.float())
     assert (out.float() - ref).abs().max() < 2e-2
     assert (qkv.grad.float() - qf.grad).abs().max() < 2e-2 * max(1.0, qf.grad.abs().max().item())
+
+
+def test_p2p_collectives_emulated_ranks():
+    """All 'ranks' live on one GPU (one buffer each); each rank's kernel is launched in turn (no cross-kernel waits)."""
+    from deepspeedsyclsupport_b200.parallel.symm import EmulatedPeers
+    torch.manual_seed(0)
+    W, n = 4, 8 * 1000
+    em = EmulatedPeers(W, nbytes=W * n * 4)
+    # all-gather: rank r's shard = n bf16 at offset 0 of its buffer
+    shards = [torch.randn(n, device=_dev()).bfloat16() for _ in range(W)]
+    for r in range(W):
+        em.view(0, (n, ), torch.bfloat16, rank=r).copy_(shards[r])
+    for r in range(W):
+        out = torch.empty(W * n, device=_dev(), dtype=torch.bfloat16)
+        em.all_gather(out, 0, n * 2, rank=r)
+        assert torch.equal(out, torch.cat(shards))
+    # reduce-scatter (+scale, +norm): every rank holds W*n bf16 gradients
+    grads = [torch.randn(W * n, device=_dev()).bfloat16() for _ in range(W)]
+    for r in range(W):
+        em.view(0, (W * n, ), torch.bfloat16, rank=r).copy_(grads[r])
+    total = sum(g.float() for g in grads) / W
+    for r in range(W):
+        dst = torch.zeros(n, device=_dev())
+        sq = torch.zeros(1, device=_dev())
+        em.reduce_scatter(dst, 0, torch.bfloat16, n, scale=1.0 / W, sumsq=sq, rank=r)
+        want = total[r * n:(r + 1) * n]
+        assert (dst - want).abs().max() < 1e-5
+        assert abs(sq.item() - want.square().sum().item()) < 1e-2 * want.square().sum().item()
+        dst16 = torch.zeros(n, device=_dev(), dtype=torch.bfloat16)
+        em.reduce_scatter(dst16, 0, torch.bfloat16, n, scale=1.0 / W, rank=r)
+        assert (dst16.float() - want).abs().max() < 2e-2
+    # fused reduce-scatter + AdamW
+    from deepspeedsyclsupport_b200.ops.flat_optim import adam_ref
+    for r in range(W):
+        p = torch.randn(n, device=_dev())
+        m, v = torch.zeros(n, device=_dev()), torch.zeros(n, device=_dev())
+        p2, m2, v2 = p.clone(), m.clone(), v.clone()
+        lp = torch.empty(n, device=_dev(), dtype=torch.bfloat16)
+        em.rs_adam(0, p, m, v, lp, n, scale=1.0 / W, lr=1e-2, beta1=0.9, beta2=0.95, eps=1e-8, weight_decay=0.1, step=1, rank=r)
+        adam_ref(p2, m2, v2, total[r * n:(r + 1) * n], 1e-2, 0.9, 0.95, 1e-8, 0.1, True, True, 1)
+        assert (p - p2).abs().max() < 1e-5 and (lp.float() - p2).abs().max() < 2e-2
+    # one-shot all-reduce
+    for r in range(W):
+        dst = torch.empty(W * n, device=_dev(), dtype=torch.bfloat16)
+        em.all_reduce_bf16(dst, 0, W * n, rank=r)
+        assert (dst.float() - total * W).abs().max() < 5e-2

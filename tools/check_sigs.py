@@ -17,6 +17,11 @@ def main():
             importlib.import_module("deepspeedsyclsupport_b200.ops." + m)
         except ImportError:
             pass
+    for m in ("parallel.symm", "parallel.fused"):
+        try:
+            importlib.import_module("deepspeedsyclsupport_b200." + m)
+        except ImportError:
+            pass
     src = "".join(open(f).read() for f in glob.glob(os.path.join(ROOT, "csrc", "**", "*.cu"), recursive=True))
     bad = 0
     exported = set(re.findall(r"DSB_EXPORT\s+[\w ]+?[\s\*]+(dsb200_\w+)\s*\(", src))
