@@ -215,7 +215,13 @@ class ZeroShardedOptimizer:
             u.shard_off = off
             off += u.shard_numel
         self.total_shard = off
-        self.lp_shard = torch.zeros(self.total_shard, dtype=self.dtype, device=self.device)
+        self.p2p = None
+        self._setup_p2p()
+        if self.p2p is not None:
+            self.lp_shard = self.p2p.view(self._p2p_lp_off, (self.total_shard, ), self.dtype)
+            self.lp_shard.zero_()
+        else:
+            self.lp_shard = torch.zeros(self.total_shard, dtype=self.dtype, device=self.device)
         keep_full = self.stage <= 2 or self.shard_world == 1
         self.lp_full = None
         if keep_full and self.shard_world > 1:
@@ -248,6 +254,9 @@ class ZeroShardedOptimizer:
                 p.ds_tensor = u.shard[s_lo - lo:s_hi - lo] if s_lo < s_hi else u.shard[0:0]
             del flat
         self.keep_full = keep_full
+        if self.p2p is not None:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.shard_group)  # every rank's shard is in place before anyone pulls from it
         # ---- optimizer-state regions (host / device split = Offload++ ratio)
         oc = self.zero_config.offload_optimizer
         offload = oc is not None and str(getattr(oc.device, "value", oc.device)) != "none"
@@ -267,6 +276,72 @@ class ZeroShardedOptimizer:
                 r.master = self.lp_shard[r.lo:r.hi]  # fp32 training: the parameters ARE the master weights
             else:
                 r.master.copy_(self.lp_shard[r.lo:r.hi].float())
+
+    # ------------------------------------------------------------------ peer-memory collectives (own kernels, no NCCL)
+    P2P_GRAD_SLOTS = 3
+
+    def _setup_p2p(self):
+        """Place this rank's parameter shard and a small ring of unit gradient buffers in symmetric (peer-mapped)
+        memory so the ZeRO-3 collectives run as our own pull kernels over NVLink (csrc/comm/symm.cu):
+        all-gather = every rank copies peers' shards; reduce-scatter = every rank sums its slice over peers' buffers,
+        fused with 1/world scaling, dtype cast, accumulation into the gradient shard and the grad-norm partial."""
+        want = (self.cuda and self.stage == 3 and self.shard_world > 1 and self.replica_world == 1 and
+                bool(getattr(self.zero_config, "fused_collectives", True)) and self.dtype == torch.bfloat16 and
+                not self.zero_config.zero_quantized_weights and not self.zero_config.zero_quantized_gradients and
+                os.environ.get("DSB200_DISABLE_P2P", "0") != "1" and self.shard_world <= 16)
+        if not want:
+            return
+        try:
+            from ...parallel.symm import SymmetricBuffer
+            esz = 2
+            max_unit = max(u.padded for u in self.units)
+            self._p2p_lp_off = 0
+            lp_bytes = (self.total_shard * esz + 255) // 256 * 256
+            self._p2p_slot_bytes = (max_unit * esz + 255) // 256 * 256
+            self._p2p_grad_off = lp_bytes
+            self.p2p = SymmetricBuffer(self.shard_group, lp_bytes + self.P2P_GRAD_SLOTS * self._p2p_slot_bytes)
+            self._p2p_slot_views = [self.p2p.view(self._p2p_grad_off + k * self._p2p_slot_bytes, (max_unit, ), torch.bfloat16)
+                                    for k in range(self.P2P_GRAD_SLOTS)]
+            self._p2p_next_slot = 0
+            self._p2p_reduce_count = 0
+            self._p2p_barrier_events = {}
+            self._p2p_sumsq = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self.comm_dtype = torch.bfloat16
+        except Exception as e:  # pragma: no cover - peer access unavailable: keep the NCCL path
+            logger.warning(f"peer-memory collectives unavailable ({e}); using NCCL")
+            self.p2p = None
+
+    def _p2p_take_slot(self, u):
+        """Assign the next gradient slot of the ring to unit `u` (compute stream waits until every peer has finished
+        reading the slot's previous contents: they have once this rank passed the barrier of reduce n-K+1)."""
+        k = self._p2p_next_slot % self.P2P_GRAD_SLOTS
+        n = self._p2p_next_slot
+        self._p2p_next_slot += 1
+        need = n - self.P2P_GRAD_SLOTS + 1
+        if need >= 0 and need in self._p2p_barrier_events:
+            torch.cuda.current_stream().wait_event(self._p2p_barrier_events[need])
+        u.p2p_slot = k
+        buf = self._p2p_slot_views[k][:u.padded]
+        buf.zero_()
+        return buf
+
+    def _p2p_reduce_unit(self, u):
+        stream = self.rs_stream
+        stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(stream):
+            self.p2p.barrier()  # every rank has finished writing this unit's gradients (and reading older slots)
+            ev = torch.cuda.Event()
+            ev.record(stream)
+            self._p2p_barrier_events[self._p2p_reduce_count] = ev
+            self._p2p_barrier_events.pop(self._p2p_reduce_count - 2 * self.P2P_GRAD_SLOTS, None)
+            self._p2p_reduce_count += 1
+            dst = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
+            fuse_norm = self.gas == 1
+            self.p2p.reduce_scatter(dst, self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes, torch.bfloat16, u.shard_numel,
+                                    scale=1.0 / self.grad_divisor, accumulate=self.gas > 1,
+                                    sumsq=self._p2p_sumsq if fuse_norm else None)
+        u.full_grad = None
+        u.reduced = True
 
     def _build_runs(self):
         """(group_id, lo, hi) runs over the rank-flat shard space, merged across unit boundaries."""
@@ -323,7 +398,10 @@ class ZeroShardedOptimizer:
         """Slice of the unit's contiguous gradient buffer for `p` (allocated on first use in a backward pass)."""
         u = p.ds_unit
         if u.full_grad is None:
-            u.full_grad = torch.zeros(u.padded, dtype=self.comm_dtype, device=self.device)
+            if self.p2p is not None:
+                u.full_grad = self._p2p_take_slot(u)
+            else:
+                u.full_grad = torch.zeros(u.padded, dtype=self.comm_dtype, device=self.device)
         off, n = u.param_slice(p.ds_index)
         self._grads_dirty = True
         return u.full_grad[off:off + n].view(p.ds_shape)
@@ -348,6 +426,8 @@ class ZeroShardedOptimizer:
         """reduce-scatter (+ replica all-reduce) of one unit's gradient buffer into the flat gradient shard."""
         if u.full_grad is None:
             return
+        if self.p2p is not None:
+            return self._p2p_reduce_unit(u)
         buf = u.full_grad
         stream = self.rs_stream if self.overlap_comm else None
         if stream is not None:
@@ -430,7 +510,9 @@ class ZeroShardedOptimizer:
         ctx = torch.cuda.stream(stream) if stream is not None else _nullctx()
         with ctx:
             u.full = torch.empty(u.padded, dtype=self.dtype, device=self.device)
-            if self.zero_config.zero_quantized_weights and self.cuda:
+            if self.p2p is not None:
+                self.p2p.all_gather(u.full, self._p2p_lp_off + u.shard_off * 2, u.shard_numel * 2)
+            elif self.zero_config.zero_quantized_weights and self.cuda:
                 from .zeropp import quantized_all_gather
                 quantized_all_gather(u.full, u.shard, self.shard_group)
             else:
@@ -599,6 +681,13 @@ class ZeroShardedOptimizer:
     def _compute_global_norm(self):
         """Device-side ||g||_2 of the (still loss-scaled) gradient over all shards."""
         g = self.grad_shard
+        if self.p2p is not None and self.gas == 1:
+            # sum(g^2) was accumulated by the fused reduce-scatter kernels while the gradients were being reduced
+            sq = self._p2p_sumsq.clone()
+            self._p2p_sumsq.zero_()
+            dist.all_reduce(sq, op=dist.ReduceOp.SUM, group=self.shard_group)
+            self._model_parallel_all_reduce(sq, dist.ReduceOp.SUM)
+            return sq.sqrt()
         sq = (g.float() if g.dtype != torch.float32 else g).square().sum().reshape(1) if g.numel() < (1 << 28) else \
             sum((c.float().square().sum() for c in g.split(1 << 27))).reshape(1)
         if dist.is_initialized():
@@ -729,6 +818,17 @@ class ZeroShardedOptimizer:
         if self.dtype == torch.float32 and self.shard_world >= 1:
             # fp32 training: master is a separate fp32 copy; lp_shard was updated by the kernels (lp write)
             pass
+        if self.p2p is not None:
+            # peers may pull the updated shards only after every rank finished its step: device barrier, no host sync
+            self.p2p.barrier()
+            for u in self.units:
+                if u.persistent:
+                    self.p2p.all_gather(u.full, self._p2p_lp_off + u.shard_off * 2, u.shard_numel * 2)
+            self.ag_stream.wait_stream(torch.cuda.current_stream())
+            self._p2p_next_slot = 0
+            self._p2p_reduce_count = 0
+            self._p2p_barrier_events = {}
+            return
         if self.shard_world > 1:
             if self.keep_full:
                 for u in self.units:
@@ -891,6 +991,9 @@ class ZeroShardedOptimizer:
         self._post_load_sync()
 
     def _post_load_sync(self):
+        if self.p2p is not None:
+            torch.cuda.synchronize()
+            dist.barrier(group=self.shard_group)
         if self.shard_world > 1:
             for u in self.units:
                 if self.keep_full or u.persistent:
