@@ -163,7 +163,6 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
 #pragma unroll
     for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
     float m_run = -INFINITY, l_run = 0.f;
-    float alpha_pending = 1.f;  // rescale to apply together with PV(j-1)
 
     auto accumulate_pv = [&](int j, float alpha) {
       const int st = j & 1;
