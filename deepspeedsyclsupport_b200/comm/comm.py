@@ -272,13 +272,15 @@ def all_gather_coalesced(output_tensors, input_tensors, group=None, async_op=Fal
 @timed_op
 def all_to_all_single(output, tensor, output_split_sizes=None, input_split_sizes=None, group=None, async_op=False):
     if tdist.get_backend(group) == "gloo":
-        ws = get_world_size(group)
-        ins = list(tensor.split(input_split_sizes, 0)) if input_split_sizes else list(tensor.chunk(ws, 0))
-        outs = list(output.split(output_split_sizes, 0)) if output_split_sizes else list(output.chunk(ws, 0))
-        outs_c = [torch.empty_like(o) for o in outs]
-        tdist.all_to_all(outs_c, [i.contiguous() for i in ins], group=group)
-        for o, c in zip(outs, outs_c):
-            o.copy_(c)
+        # gloo has no all-to-all: all-gather every rank's send buffer and keep the chunk addressed to this rank
+        # (host plumbing path only -- equal splits)
+        assert not output_split_sizes and not input_split_sizes, "uneven all_to_all_single is not supported on gloo"
+        ws, me = get_world_size(group), get_rank(group)
+        gathered = [torch.empty_like(tensor) for _ in range(ws)]
+        tdist.all_gather(gathered, tensor.contiguous(), group=group)
+        outs = list(output.chunk(ws, 0))
+        for src in range(ws):
+            outs[src].copy_(gathered[src].chunk(ws, 0)[me])
         return None
     return tdist.all_to_all_single(output, tensor, output_split_sizes, input_split_sizes, group=group, async_op=async_op)
 

@@ -157,7 +157,7 @@ def _ancestors_in(root, qualified_name):
     parts = qualified_name.split(".") if qualified_name else []
     out, cur = [], root
     for part in parts[:-1]:
-        cur = getattr(cur, part) if not part.isdigit() else cur[int(part)]
+        cur = cur._modules[part]
         out.append(cur)
     return out
 

@@ -282,3 +282,52 @@ def test_ag_gemm_emulated_ranks(world):
         assert torch.equal(w_local, W)
         ref = x.float() @ W.float().t()
         assert (out.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
+
+
+def test_fp8_block_quantizer_and_reduce():
+    from deepspeedsyclsupport_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    x = (torch.randn(128 * 1000, device=_dev()) * 3).bfloat16()
+    q, s = Q.quantize_fp8_block(x)
+    qr, sr = Q.quantize_fp8_block_ref(x)
+    assert torch.allclose(s, sr, rtol=1e-6)
+    d = Q.dequantize_fp8_block(q, s)
+    dr = Q.dequantize_fp8_block_ref(qr, sr)
+    assert (d.float() - dr.float()).abs().max() <= 0.07 * x.float().abs().max()  # at most one fp8 ulp apart
+    assert (d.float() - x.float()).abs().max() <= 0.07 * x.float().abs().max()
+    parts = 4
+    xs = torch.randn(parts, 128 * 50, device=_dev()).bfloat16()
+    q, s = Q.quantize_fp8_block(xs.view(-1))
+    out = Q.dequant_reduce_fp8_block(q, s, parts, dtype=torch.float32)
+    ref = Q.dequantize_fp8_block(q, s, dtype=torch.float32).view(parts, -1).sum(0)
+    assert (out - ref).abs().max() < 1e-4
+
+
+@pytest.mark.parametrize("bits,sym", [(8, True), (8, False), (4, True), (4, False)])
+def test_int_quantizer(bits, sym):
+    from deepspeedsyclsupport_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    groups, gs = 64, 512
+    x = torch.randn(groups * gs, device=_dev(), dtype=torch.float16)
+    q, params = Q.int_quantize(x, groups, bits, sym)
+    d = Q.int_dequantize(q, params, groups, bits, sym, torch.float32)
+    qr, pr = Q.int_quantize_ref(x, groups, bits, sym)
+    dr = Q.int_dequantize_ref(qr, pr).view(-1)
+    assert torch.allclose(params, pr, rtol=1e-5, atol=1e-7)
+    step = params[:, 0].max().item()
+    assert (d - dr).abs().max() <= step * 1.01  # rounding ties may differ by one level
+    assert (d - x.float()).abs().max() <= step * 1.01
+
+
+def test_fake_quantize():
+    from deepspeedsyclsupport_b200.ops import quantizer as Q
+    torch.manual_seed(0)
+    x = torch.randn(32, 256, device=_dev(), dtype=torch.float16)
+    for sym in (True, False):
+        y = Q.fake_quantize_(x.clone(), 32, 8, symmetric=sym)
+        yr = Q.fake_quantize_(x.clone().cpu(), 32, 8, symmetric=sym)
+        step = (x.float().abs().amax(1) * 2 / 256).max().item()
+        assert (y.cpu().float() - yr.float()).abs().max() <= step * 1.01
+    ys = Q.fake_quantize_(x.clone(), 32, 4, symmetric=True, stochastic=True, seed=7)
+    step4 = (x.float().abs().amax(1) * 2 / 16).max().item()
+    assert (ys.float() - x.float()).abs().max() <= step4 * 1.01
