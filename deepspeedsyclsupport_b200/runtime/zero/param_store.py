@@ -162,14 +162,14 @@ def _ancestors_in(root, qualified_name):
     return out
 
 
-def build_units(module, param_to_group, world, rank, dtype, device, max_unit_numel=None):
+def build_units(module, param_to_group, world, rank, dtype, device, max_unit_numel=None, param_filter=None):
     """Partition the parameters of `module` into units.  Shared (tied) parameters belong to the first unit that sees
     them.  Returns (units, param_id -> unit)."""
     seen = set()
     units, owner = [], {}
 
     def add_unit(name, plist, mods):
-        plist = [p for p in plist if id(p) not in seen]
+        plist = [p for p in plist if id(p) not in seen and (param_filter is None or param_filter(p))]
         if not plist:
             return None
         for p in plist:

@@ -65,7 +65,7 @@ class ZeroShardedOptimizer:
                  replica_group=None, static_loss_scale=1.0, dynamic_loss_scale=False, dynamic_loss_args=None,
                  clip_grad=0.0, gradient_accumulation_steps=1, grad_accum_dtype=None, communication_data_type=None,
                  mpu=None, timers=None, gradient_predivide_factor=1.0, prescale_gradients=False, grad_divisor=None,
-                 broadcast_src=0, elastic_checkpoint=False):
+                 broadcast_src=0, elastic_checkpoint=False, param_filter=None):
         self.module = module
         self.optimizer = init_optimizer
         self.stage = int(stage)
@@ -119,7 +119,8 @@ class ZeroShardedOptimizer:
         for p in module.parameters():
             if id(p) not in param_to_group:
                 param_to_group[id(p)] = -1  # frozen / not optimised
-        self.units, self.owner = build_units(module, param_to_group, self.shard_world, self.shard_rank, dtype, self.device)
+        self.units, self.owner = build_units(module, param_to_group, self.shard_world, self.shard_rank, dtype, self.device,
+                                             param_filter=param_filter)
         self.persistence_threshold = int(zero_config.param_persistence_threshold) if self.stage == 3 else 0
         self._setup_param_attrs()
         self._allocate(broadcast_src)
@@ -697,19 +698,29 @@ class ZeroShardedOptimizer:
         return sq.sqrt()
 
     def step(self, closure=None):
+        if self.begin_step():
+            return
+        norm = self._compute_global_norm()
+        self.finish_step(norm)
+
+    def begin_step(self):
+        """Overflow handling + loss-scale update.  Returns True when the step must be skipped."""
         self.micro_step_id = 0
-        if self.overlap_comm:
+        if self.overlap_comm or self.p2p is not None:
             torch.cuda.current_stream().wait_stream(self.rs_stream)
         self.overflow = self._check_overflow()
+        self._prev_scale = self.loss_scale
         if not self.custom_loss_scaler:
-            prev_scale = self.loss_scale
             self.loss_scaler.update_scale(self.overflow)
         if self.overflow:
             self.skipped_steps += 1
             self.zero_grad()
-            return
-        loss_scale = prev_scale if not self.custom_loss_scaler else self.external_loss_scale
-        norm = self._compute_global_norm()
+            return True
+        return False
+
+    def finish_step(self, norm):
+        """`norm`: device tensor with the (loss-scaled) global gradient norm over everything that is clipped together."""
+        loss_scale = self._prev_scale if not self.custom_loss_scaler else self.external_loss_scale
         self._global_grad_norm = norm / loss_scale
         inv = torch.full_like(norm, 1.0 / loss_scale)
         if self.clip_grad > 0.0:
