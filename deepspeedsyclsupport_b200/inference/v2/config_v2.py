@@ -1,0 +1,19 @@
+"""RaggedInferenceEngineConfig (parity: inference/v2/config_v2.py)."""
+from pydantic import Field
+
+from ...runtime.config_utils import DeepSpeedConfigModel
+from .ragged.manager_configs import DSStateManagerConfig
+
+
+class DeepSpeedTPConfig(DeepSpeedConfigModel):
+    tp_size: int = 1
+
+
+class QuantizationConfig(DeepSpeedConfigModel):
+    quantization_mode: str = ""  # "" (bf16) | "fp8_block" (block-scaled e4m3 weights)
+
+
+class RaggedInferenceEngineConfig(DeepSpeedConfigModel):
+    tensor_parallel: DeepSpeedTPConfig = Field(DeepSpeedTPConfig(), alias="tp")
+    state_manager: DSStateManagerConfig = Field(DSStateManagerConfig(), alias="manager")
+    quantization: QuantizationConfig = QuantizationConfig()

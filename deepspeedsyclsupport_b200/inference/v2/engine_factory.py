@@ -1,0 +1,157 @@
+"""Engine construction: HF checkpoint -> canonical parameter names -> RaggedTransformer -> InferenceEngineV2.
+Parity: inference/v2/engine_factory.py:28-123 (build_hf_engine, build_engine_from_ds_checkpoint) and the per-family
+policies/containers that map HF tensor names (model_implementations/*/policy.py, *_containers.py)."""
+import json
+import os
+import pickle
+import re
+
+import torch
+
+from .config_v2 import RaggedInferenceEngineConfig
+from .engine_v2 import InferenceEngineV2
+from .model_implementations import SPEC_FROM_HF, ArchSpec, RaggedTransformer
+
+
+def _map_llama(sd, cfg):
+    out = {"embed.weight": sd["model.embed_tokens.weight"], "final_norm.weight": sd["model.norm.weight"]}
+    if "lm_head.weight" in sd:
+        out["lm_head.weight"] = sd["lm_head.weight"]
+    for i in range(cfg["num_hidden_layers"]):
+        p, q = f"model.layers.{i}.", f"layers.{i}."
+        for a, b in (("self_attn.q_proj", "q"), ("self_attn.k_proj", "k"), ("self_attn.v_proj", "v"), ("self_attn.o_proj", "o")):
+            out[q + b + ".weight"] = sd[p + a + ".weight"]
+        out[q + "norm1.weight"] = sd[p + "input_layernorm.weight"]
+        out[q + "norm2.weight"] = sd[p + "post_attention_layernorm.weight"]
+        if p + "mlp.gate_proj.weight" in sd:
+            out[q + "gate.weight"], out[q + "up.weight"], out[q + "down.weight"] = (sd[p + "mlp.gate_proj.weight"],
+                                                                                     sd[p + "mlp.up_proj.weight"], sd[p + "mlp.down_proj.weight"])
+        else:  # mixtral
+            out[q + "router.weight"] = sd[p + "block_sparse_moe.gate.weight"]
+            for e in range(cfg["num_local_experts"]):
+                ep = f"{p}block_sparse_moe.experts.{e}."
+                out[f"{q}experts.{e}.gate.weight"] = sd[ep + "w1.weight"]
+                out[f"{q}experts.{e}.down.weight"] = sd[ep + "w2.weight"]
+                out[f"{q}experts.{e}.up.weight"] = sd[ep + "w3.weight"]
+    return out
+
+
+def _map_opt(sd, cfg):
+    pre = "model.decoder." if "model.decoder.embed_tokens.weight" in sd else "decoder."
+    out = {"embed.weight": sd[pre + "embed_tokens.weight"], "pos_embed.weight": sd[pre + "embed_positions.weight"],
+           "final_norm.weight": sd[pre + "final_layer_norm.weight"], "final_norm.bias": sd[pre + "final_layer_norm.bias"]}
+    for i in range(cfg["num_hidden_layers"]):
+        p, q = f"{pre}layers.{i}.", f"layers.{i}."
+        for a, b in (("self_attn.q_proj", "q"), ("self_attn.k_proj", "k"), ("self_attn.v_proj", "v"), ("self_attn.out_proj", "o"),
+                     ("fc1", "up"), ("fc2", "down")):
+            out[q + b + ".weight"], out[q + b + ".bias"] = sd[p + a + ".weight"], sd[p + a + ".bias"]
+        out[q + "norm1.weight"], out[q + "norm1.bias"] = sd[p + "self_attn_layer_norm.weight"], sd[p + "self_attn_layer_norm.bias"]
+        out[q + "norm2.weight"], out[q + "norm2.bias"] = sd[p + "final_layer_norm.weight"], sd[p + "final_layer_norm.bias"]
+    return out
+
+
+def _map_falcon(sd, cfg):
+    hq = cfg["num_attention_heads"]
+    hkv = cfg.get("num_kv_heads", 1 if cfg.get("multi_query", True) else hq)
+    d = cfg["hidden_size"] // hq
+    out = {"embed.weight": sd["transformer.word_embeddings.weight"], "final_norm.weight": sd["transformer.ln_f.weight"],
+           "final_norm.bias": sd["transformer.ln_f.bias"]}
+    if "lm_head.weight" in sd:
+        out["lm_head.weight"] = sd["lm_head.weight"]
+    for i in range(cfg["num_hidden_layers"]):
+        p, q = f"transformer.h.{i}.", f"layers.{i}."
+        w = sd[p + "self_attention.query_key_value.weight"]
+        if hkv == hq:  # interleaved [h, 3, d]
+            w3 = w.view(hq, 3, d, -1)
+            out[q + "q.weight"], out[q + "k.weight"], out[q + "v.weight"] = (w3[:, 0].reshape(hq * d, -1), w3[:, 1].reshape(hq * d, -1),
+                                                                             w3[:, 2].reshape(hq * d, -1))
+        else:  # grouped: [hkv, group + 2, d]
+            g = hq // hkv
+            wg = w.view(hkv, g + 2, d, -1)
+            out[q + "q.weight"] = wg[:, :g].reshape(hq * d, -1)
+            out[q + "k.weight"] = wg[:, g].reshape(hkv * d, -1)
+            out[q + "v.weight"] = wg[:, g + 1].reshape(hkv * d, -1)
+        out[q + "o.weight"] = sd[p + "self_attention.dense.weight"]
+        ln = "input_layernorm" if p + "input_layernorm.weight" in sd else "ln_attn"
+        out[q + "norm1.weight"], out[q + "norm1.bias"] = sd[p + ln + ".weight"], sd[p + ln + ".bias"]
+        out[q + "up.weight"], out[q + "down.weight"] = sd[p + "mlp.dense_h_to_4h.weight"], sd[p + "mlp.dense_4h_to_h.weight"]
+    return out
+
+
+def _map_phi(sd, cfg):
+    out = {"embed.weight": sd["model.embed_tokens.weight"], "final_norm.weight": sd["model.final_layernorm.weight"],
+           "final_norm.bias": sd["model.final_layernorm.bias"], "lm_head.weight": sd["lm_head.weight"]}
+    for i in range(cfg["num_hidden_layers"]):
+        p, q = f"model.layers.{i}.", f"layers.{i}."
+        for a, b in (("self_attn.q_proj", "q"), ("self_attn.k_proj", "k"), ("self_attn.v_proj", "v"), ("self_attn.dense", "o"),
+                     ("mlp.fc1", "up"), ("mlp.fc2", "down")):
+            out[q + b + ".weight"], out[q + b + ".bias"] = sd[p + a + ".weight"], sd[p + a + ".bias"]
+        out[q + "norm1.weight"], out[q + "norm1.bias"] = sd[p + "input_layernorm.weight"], sd[p + "input_layernorm.bias"]
+    return out
+
+
+_MAPPERS = {"llama": _map_llama, "mistral": _map_llama, "mixtral": _map_llama, "opt": _map_opt, "falcon": _map_falcon, "phi": _map_phi}
+
+
+def build_engine_from_state_dict(model_type, hf_config: dict, state_dict: dict, engine_config: RaggedInferenceEngineConfig,
+                                 dtype=torch.bfloat16):
+    """Engine from an in-memory HF-named state dict (used for random-init models when no checkpoint is on disk)."""
+    if model_type not in SPEC_FROM_HF:
+        raise ValueError(f"Unsupported model type {model_type}")
+    spec = SPEC_FROM_HF[model_type](hf_config)
+    canon = _MAPPERS[model_type](state_dict, hf_config)
+
+    def builder(tp_group, device):
+        return RaggedTransformer(spec, canon, tp_group=tp_group, dtype=dtype, device=device)
+
+    return InferenceEngineV2(builder, engine_config)
+
+
+def build_hf_engine(path: str, engine_config: RaggedInferenceEngineConfig, debug_level: int = 20):
+    if os.path.exists(os.path.join(path, "ds_model_config.pkl")):
+        return build_engine_from_ds_checkpoint(path, engine_config, debug_level=debug_level)
+    from .checkpoint.huggingface_engine import HuggingFaceCheckpointEngine
+    ck = HuggingFaceCheckpointEngine(path)
+    model_type = ck.model_config["model_type"]
+    sd = dict(ck.parameters())
+    return build_engine_from_state_dict(model_type, ck.model_config, sd, engine_config)
+
+
+def build_engine_from_ds_checkpoint(path: str, engine_config: RaggedInferenceEngineConfig, debug_level: int = 20):
+    """Rebuild from `InferenceEngineV2.serialize()` output (already TP-sharded, canonical names)."""
+    from ... import comm as dist
+    with open(os.path.join(path, "ds_model_config.pkl"), "rb") as f:
+        spec = pickle.load(f)
+
+    def builder(tp_group, device):
+        rank = dist.get_rank(tp_group) if tp_group is not None else 0
+        params = torch.load(os.path.join(path, f"params_rank_{rank}.pt"), map_location="cpu")
+        m = RaggedTransformer.__new__(RaggedTransformer)
+        m.spec, m.tp_group = spec, tp_group
+        m.tp = dist.get_world_size(tp_group) if tp_group is not None else 1
+        m.rank, m.dtype, m.device, m.symm = rank, torch.bfloat16, device, None
+        m.hq, m.hkv = spec.num_heads // m.tp, max(1, spec.num_kv_heads // m.tp)
+        m.kv_replicated = spec.num_kv_heads < m.tp
+        from ...ops import fused_ops as FO
+        m.inv_freq = FO.rope_inv_freq(spec.rotary_dim, spec.rope_theta, device=device) if spec.rotary_dim else None
+        m.embed, m.lm_head = params["embed"].to(device), params["lm_head"].to(device)
+        m.final_norm_w, m.final_norm_b, m.pos_embed = params["final_norm_w"].to(device), None, None
+        m.layers = []
+        for i in range(spec.num_layers):
+            L, experts = {}, {}
+            for k, v in params.items():
+                mm = re.match(rf"layers\.{i}\.(.*)", k)
+                if not mm:
+                    continue
+                name = mm.group(1)
+                em = re.match(r"experts\.(\d+)\.(gate_up|down)", name)
+                if em:
+                    experts.setdefault(int(em.group(1)), {})[em.group(2)] = v.to(device)
+                else:
+                    L[name] = v.to(device)
+            if experts:
+                L["experts"] = [(experts[e]["gate_up"], experts[e]["down"]) for e in sorted(experts)]
+            m.layers.append(L)
+        return m
+
+    return InferenceEngineV2(builder, engine_config)

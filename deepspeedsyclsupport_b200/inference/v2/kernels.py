@@ -1,0 +1,156 @@
+"""Python wrappers of the ragged device ops (csrc/ragged/ragged_ops.cu) with PyTorch oracles for CPU / tests."""
+import math
+
+import torch
+
+from ...ops import native
+
+native.register_sigs({
+    "dsb200_kv_rotary_append": "pppppp iiiiiii p",
+    "dsb200_paged_attention": "pppppp iiiiii f p",
+    "dsb200_ragged_embed": "ppppp iii p",
+    "dsb200_logits_gather": "ppp ii p",
+    "dsb200_top_k_gating": "ppppp iiii p",
+    "dsb200_moe_scatter": "ppppppp iiii p",
+    "dsb200_moe_gather": "pppp iii p",
+})
+
+
+def kv_rotary_append(qkv, kv_cache, tok_seq, tok_pos, block_table, inv_freq, hq, hkv, d, rot_dim=None):
+    """In place: RoPE on q,k heads of qkv [T, (hq+2hkv)*d]; k,v rows appended to kv_cache [blocks,2,bs,hkv,d]."""
+    T = qkv.shape[0]
+    bs = kv_cache.shape[2]
+    rot_dim = d if rot_dim is None else rot_dim
+    if qkv.is_cuda:
+        rc = native.lib().dsb200_kv_rotary_append(native.ptr(qkv), native.ptr(kv_cache), native.ptr(tok_seq), native.ptr(tok_pos),
+                                                  native.ptr(block_table), native.ptr(inv_freq), T, hq, hkv, d, bs,
+                                                  block_table.shape[1], int(rot_dim), native.stream_ptr())
+        native.check(rc)
+        return qkv
+    from ...ops.fused_ops import rope_ref
+    if rot_dim == d:
+        qkv.copy_(rope_ref(qkv, inv_freq, tok_pos, 0, hq + hkv, d))
+    elif rot_dim > 0:
+        xv = qkv.view(T, hq + 2 * hkv, d)
+        rot = rope_ref(xv[:, :hq + hkv, :rot_dim].reshape(T, -1).contiguous(), inv_freq, tok_pos, 0, hq + hkv, rot_dim)
+        xv[:, :hq + hkv, :rot_dim] = rot.view(T, hq + hkv, rot_dim)
+    x = qkv.view(T, hq + 2 * hkv, d)
+    for t in range(T):
+        pos, seq = int(tok_pos[t]), int(tok_seq[t])
+        blk = int(block_table[seq, pos // bs])
+        kv_cache[blk, 0, pos % bs] = x[t, hq:hq + hkv]
+        kv_cache[blk, 1, pos % bs] = x[t, hq + hkv:]
+    return qkv
+
+
+def paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale):
+    T = qkv.shape[0]
+    bs = kv_cache.shape[2]
+    out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
+    q = qkv.view(T, hq + 2 * hkv, d)[:, :hq].float()
+    for t in range(T):
+        n = int(tok_pos[t]) + 1
+        seq = int(tok_seq[t])
+        blocks = block_table[seq, :-(-n // bs)].long()
+        k = kv_cache[blocks, 0].reshape(-1, hkv, d)[:n].float().repeat_interleave(hq // hkv, 1)
+        v = kv_cache[blocks, 1].reshape(-1, hkv, d)[:n].float().repeat_interleave(hq // hkv, 1)
+        s = torch.einsum("hd,nhd->hn", q[t], k) * scale
+        out[t] = torch.einsum("hn,nhd->hd", torch.softmax(s, -1), v).reshape(-1).to(qkv.dtype)
+    return out
+
+
+def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None):
+    scale = scale if scale is not None else 1.0 / math.sqrt(d)
+    if not qkv.is_cuda:
+        return paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale)
+    T = qkv.shape[0]
+    out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
+    rc = native.lib().dsb200_paged_attention(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq),
+                                             native.ptr(tok_pos), native.ptr(block_table), T, hq, hkv, d, kv_cache.shape[2],
+                                             block_table.shape[1], float(scale), native.stream_ptr())
+    native.check(rc)
+    return out
+
+
+def ragged_embed(ids, wte, wpe=None, tok_pos=None, pos_offset=0):
+    if not wte.is_cuda or wte.dtype != torch.bfloat16:
+        x = wte[ids]
+        if wpe is not None:
+            x = x + wpe[tok_pos.long() + pos_offset]
+        return x
+    T, dim = ids.numel(), wte.shape[1]
+    out = torch.empty(T, dim, dtype=wte.dtype, device=wte.device)
+    rc = native.lib().dsb200_ragged_embed(native.ptr(ids), native.ptr(wte), native.ptr(wpe), native.ptr(tok_pos if wpe is not None else None),
+                                          native.ptr(out), T, dim, pos_offset, native.stream_ptr())
+    native.check(rc)
+    return out
+
+
+def logits_gather(hidden, last_tok):
+    if not hidden.is_cuda or hidden.dtype != torch.bfloat16:
+        return hidden[last_tok.long()]
+    out = torch.empty(last_tok.numel(), hidden.shape[1], dtype=hidden.dtype, device=hidden.device)
+    rc = native.lib().dsb200_logits_gather(native.ptr(hidden), native.ptr(last_tok), native.ptr(out), last_tok.numel(), hidden.shape[1],
+                                           native.stream_ptr())
+    native.check(rc)
+    return out
+
+
+def top_k_gating(logits, k, normalize=True):
+    """logits [T, E] fp32 -> (expert_counts [E] int32, scores [T,k] fp32, assignments [T,k] int32, offsets [T,k] int32)."""
+    T, E = logits.shape
+    if not logits.is_cuda:
+        probs = torch.softmax(logits.float(), -1)
+        sc, asg = probs.topk(k, dim=-1)
+        if normalize:
+            sc = sc / sc.sum(-1, keepdim=True)
+        counts = torch.zeros(E, dtype=torch.int32)
+        offsets = torch.zeros(T, k, dtype=torch.int32)
+        for t in range(T):
+            for j in range(k):
+                e = int(asg[t, j])
+                offsets[t, j] = counts[e]
+                counts[e] += 1
+        return counts, sc, asg.int(), offsets
+    counts = torch.zeros(E, dtype=torch.int32, device=logits.device)
+    scores = torch.empty(T, k, dtype=torch.float32, device=logits.device)
+    asg = torch.empty(T, k, dtype=torch.int32, device=logits.device)
+    off = torch.empty(T, k, dtype=torch.int32, device=logits.device)
+    rc = native.lib().dsb200_top_k_gating(native.ptr(logits.contiguous()), native.ptr(counts), native.ptr(scores), native.ptr(asg),
+                                          native.ptr(off), T, E, k, int(normalize), native.stream_ptr())
+    native.check(rc)
+    return counts, scores, asg, off
+
+
+def moe_scatter(x, counts, assignments, offsets):
+    """rows of x copied into expert-sorted order.  returns (moe_in [T*k, dim], expert_cumsum [E] int64, mapped_slots [T,k])."""
+    T, dim = x.shape
+    k = assignments.shape[1]
+    E = counts.numel()
+    if not x.is_cuda or x.dtype != torch.bfloat16:
+        cumsum = counts.long().cumsum(0)
+        start = torch.cat([cumsum.new_zeros(1), cumsum[:-1]])
+        slots = (start[assignments.long()] + offsets.long()).int()
+        moe_in = x.new_zeros(T * k, dim)
+        for j in range(k):
+            moe_in[slots[:, j].long()] = x
+        return moe_in, cumsum, slots
+    moe_in = torch.empty(T * k, dim, dtype=x.dtype, device=x.device)
+    cumsum = torch.empty(E, dtype=torch.int64, device=x.device)
+    slots = torch.empty(T, k, dtype=torch.int32, device=x.device)
+    rc = native.lib().dsb200_moe_scatter(native.ptr(x), native.ptr(counts), native.ptr(assignments), native.ptr(offsets),
+                                         native.ptr(cumsum), native.ptr(moe_in), native.ptr(slots), T, E, dim, k, native.stream_ptr())
+    native.check(rc, 2)
+    return moe_in, cumsum, slots
+
+
+def moe_gather(moe_out, scores, mapped_slots):
+    T, k = mapped_slots.shape
+    dim = moe_out.shape[1]
+    if not moe_out.is_cuda or moe_out.dtype != torch.bfloat16:
+        return (moe_out[mapped_slots.long()].float() * scores[..., None]).sum(1).to(moe_out.dtype)
+    out = torch.empty(T, dim, dtype=moe_out.dtype, device=moe_out.device)
+    rc = native.lib().dsb200_moe_gather(native.ptr(moe_out), native.ptr(scores), native.ptr(mapped_slots), native.ptr(out), T, dim, k,
+                                        native.stream_ptr())
+    native.check(rc)
+    return out

@@ -1,0 +1,110 @@
+"""Host natives: AVX-512 CPU optimizers, async file I/O, KV block allocator, atom builder."""
+import ctypes
+import os
+
+import pytest
+import torch
+
+
+def test_cpu_adam_matches_torch():
+    from deepspeedsyclsupport_b200.ops.adam import DeepSpeedCPUAdam
+    torch.manual_seed(0)
+    w = [torch.randn(1000, 17, requires_grad=True), torch.randn(333, requires_grad=True)]
+    r = [t.detach().clone().requires_grad_() for t in w]
+    o, ro = DeepSpeedCPUAdam(w, lr=1e-2, weight_decay=0.05), torch.optim.AdamW(r, lr=1e-2, weight_decay=0.05)
+    for _ in range(4):
+        for a, b in zip(w, r):
+            g = torch.randn_like(a)
+            a.grad, b.grad = g.clone(), g.clone()
+        o.step()
+        ro.step()
+    for a, b in zip(w, r):
+        assert torch.allclose(a, b, atol=2e-6)
+
+
+def test_cpu_adam_writes_bf16_copy():
+    from deepspeedsyclsupport_b200.ops.flat_optim import adam_step
+    p, m, v = torch.randn(5000), torch.zeros(5000), torch.zeros(5000)
+    g = torch.randn(5000).bfloat16()
+    lp = torch.empty(5000, dtype=torch.bfloat16)
+    adam_step(p, m, v, g, lr=1e-2, step=1, lp=lp)
+    assert torch.equal(lp, p.bfloat16())
+
+
+def test_cpu_lion_and_adagrad():
+    from deepspeedsyclsupport_b200.ops.adagrad import DeepSpeedCPUAdagrad
+    from deepspeedsyclsupport_b200.ops.lion import DeepSpeedCPULion
+    torch.manual_seed(0)
+    w = torch.randn(4096, requires_grad=True)
+    w0, g = w.detach().clone(), torch.randn(4096)
+    w.grad = g.clone()
+    DeepSpeedCPULion([w], lr=1e-2, betas=(0.9, 0.99)).step()
+    assert torch.allclose(w.detach(), w0 - 1e-2 * torch.sign(0.1 * g), atol=1e-6)
+    w = torch.randn(4096, requires_grad=True)
+    r = w.detach().clone().requires_grad_()
+    o, ro = DeepSpeedCPUAdagrad([w], lr=1e-2, eps=1e-10), torch.optim.Adagrad([r], lr=1e-2, eps=1e-10)
+    for _ in range(3):
+        g = torch.randn(4096)
+        w.grad, r.grad = g.clone(), g.clone()
+        o.step()
+        ro.step()
+    assert torch.allclose(w, r, atol=1e-5)
+
+
+def test_aio_roundtrip(tmp_path):
+    from deepspeedsyclsupport_b200.ops.aio import AsyncIOBuilder
+    h = AsyncIOBuilder().load().aio_handle(block_size=64 * 1024, queue_depth=4, single_submit=False, overlap_events=True, num_threads=2)
+    a = torch.randn(1 << 18)
+    f = str(tmp_path / "t.swp")
+    h.sync_pwrite(a, f)
+    b = torch.empty_like(a)
+    h.sync_pread(b, f)
+    assert torch.equal(a, b)
+    files = [str(tmp_path / f"x{i}.swp") for i in range(4)]
+    srcs = [torch.randn(100_003) for _ in files]
+    for s, p in zip(srcs, files):
+        h.async_pwrite(s, p)
+    assert h.wait() == 4
+    outs = [torch.empty(100_003) for _ in files]
+    for o, p in zip(outs, files):
+        h.async_pread(o, p)
+    h.wait()
+    assert all(torch.equal(s, o) for s, o in zip(srcs, outs))
+    with pytest.raises(IOError):
+        h.sync_pread(torch.empty(10), str(tmp_path / "missing.swp"))
+
+
+def test_optimizer_state_swapper(tmp_path):
+    from deepspeedsyclsupport_b200.runtime.swap_tensor import OptimizerStateSwapper
+    sw = OptimizerStateSwapper(tmp_path, {"block_size": 1 << 16, "queue_depth": 4, "thread_count": 1}, [1000, 2000])
+    st = [{n: torch.randn(k) for n in ("master", "exp_avg", "exp_avg_sq")} for k in (1000, 2000)]
+    for g, s in enumerate(st):
+        sw.initialize(g, s)
+    sw.prefetch(0)
+    a = sw.swap_in(0)
+    sw.prefetch(1)
+    assert torch.equal(a["master"], st[0]["master"])
+    a["master"].add_(1.0)
+    sw.swap_out(0)
+    b = sw.swap_in(1)
+    assert torch.equal(b["exp_avg_sq"], st[1]["exp_avg_sq"])
+    sw.flush()
+    assert torch.equal(sw.swap_in(0)["master"], st[0]["master"] + 1.0)
+
+
+def test_blocked_allocator_and_atoms():
+    from deepspeedsyclsupport_b200.inference.v2.ragged.blocked_allocator import BlockedAllocator
+    a = BlockedAllocator(16)
+    x = a.allocate(5)
+    assert a.free_blocks == 11 and len(set(x.tolist())) == 5
+    with pytest.raises(ValueError):
+        a.allocate(12)
+    a.free(x[:2])
+    assert a.free_blocks == 13
+    with pytest.raises(ValueError):
+        a.free(x[:1])  # double free
+    from deepspeedsyclsupport_b200.inference.v2.ragged.ragged_wrapper import build_atoms
+    atoms = build_atoms(seq_start=[0, 300], seq_ntok=[300, 1], seq_seen=[0, 77], q_block=128, kv_block=64)
+    assert atoms.shape == (4, 6)
+    assert atoms[2].tolist() == [0, 256, 44, 5, 300, 256]
+    assert atoms[3].tolist() == [1, 300, 1, 2, 78, 77]

@@ -1,0 +1,103 @@
+"""FastGen v2 engine on the host path: ragged put() with prefill + decode + chunked prefill must reproduce a dense
+causal forward of the same random-init Llama weights (HF naming)."""
+import pytest
+import torch
+
+
+def _hf_llama_state(cfg, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    h, inter, L, V = cfg["hidden_size"], cfg["intermediate_size"], cfg["num_hidden_layers"], cfg["vocab_size"]
+    hq, hkv = cfg["num_attention_heads"], cfg["num_key_value_heads"]
+    d = h // hq
+    r = lambda *s: torch.randn(*s, generator=g) * 0.05
+    sd = {"model.embed_tokens.weight": r(V, h), "model.norm.weight": 1 + r(h), "lm_head.weight": r(V, h)}
+    for i in range(L):
+        p = f"model.layers.{i}."
+        sd[p + "self_attn.q_proj.weight"] = r(hq * d, h)
+        sd[p + "self_attn.k_proj.weight"] = r(hkv * d, h)
+        sd[p + "self_attn.v_proj.weight"] = r(hkv * d, h)
+        sd[p + "self_attn.o_proj.weight"] = r(h, hq * d)
+        sd[p + "input_layernorm.weight"] = 1 + r(h)
+        sd[p + "post_attention_layernorm.weight"] = 1 + r(h)
+        sd[p + "mlp.gate_proj.weight"] = r(inter, h)
+        sd[p + "mlp.up_proj.weight"] = r(inter, h)
+        sd[p + "mlp.down_proj.weight"] = r(h, inter)
+    return sd
+
+
+def _dense_llama_logits(sd, cfg, ids):
+    """fp32 dense causal forward -> logits for every position [S, V]."""
+    import torch.nn.functional as F
+    from deepspeedsyclsupport_b200.ops.fused_ops import rope_inv_freq, rope_ref
+    h, hq, hkv = cfg["hidden_size"], cfg["num_attention_heads"], cfg["num_key_value_heads"]
+    d = h // hq
+    S = ids.numel()
+    x = sd["model.embed_tokens.weight"][ids].float()
+    inv = rope_inv_freq(d)
+    pos = torch.arange(S)
+    rms = lambda t, w: t * torch.rsqrt(t.pow(2).mean(-1, keepdim=True) + 1e-5) * w
+    for i in range(cfg["num_hidden_layers"]):
+        p = f"model.layers.{i}."
+        hn = rms(x, sd[p + "input_layernorm.weight"])
+        qkv = torch.cat([hn @ sd[p + "self_attn.q_proj.weight"].t(), hn @ sd[p + "self_attn.k_proj.weight"].t(),
+                         hn @ sd[p + "self_attn.v_proj.weight"].t()], -1)
+        qkv = rope_ref(qkv, inv, pos, 0, hq + hkv, d)
+        q, k, v = qkv.view(S, hq + 2 * hkv, d).split([hq, hkv, hkv], 1)
+        o = F.scaled_dot_product_attention(q.transpose(0, 1)[None], k.transpose(0, 1).repeat_interleave(hq // hkv, 0)[None],
+                                           v.transpose(0, 1).repeat_interleave(hq // hkv, 0)[None], is_causal=True)[0]
+        x = x + o.transpose(0, 1).reshape(S, -1) @ sd[p + "self_attn.o_proj.weight"].t()
+        hn = rms(x, sd[p + "post_attention_layernorm.weight"])
+        x = x + (F.silu(hn @ sd[p + "mlp.gate_proj.weight"].t()) * (hn @ sd[p + "mlp.up_proj.weight"].t())) @ sd[p + "mlp.down_proj.weight"].t()
+    return rms(x, sd["model.norm.weight"]) @ sd["lm_head.weight"].t()
+
+
+CFG = dict(vocab_size=97, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+           rms_norm_eps=1e-5)
+
+
+def _engine(dtype=torch.float32):
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 64, "max_ragged_sequence_count": 8, "max_context": 128,
+                                                      "memory_config": {"mode": "allocate", "size": 40}})
+    sd = _hf_llama_state(CFG)
+    return build_engine_from_state_dict("llama", CFG, sd, ecfg, dtype=dtype), sd
+
+
+def test_ragged_prefill_decode_matches_dense():
+    eng, sd = _engine()
+    torch.manual_seed(1)
+    a, b = torch.randint(0, 97, (21, )), torch.randint(0, 97, (9, ))
+    ref_a, ref_b = _dense_llama_logits(sd, CFG, a), _dense_llama_logits(sd, CFG, b)
+    # step 1: prefill a[:17] (chunk), full prefill of b minus its last token
+    out = eng.put([1, 2], [a[:17], b[:8]])
+    assert torch.allclose(out[0], ref_a[16], atol=5e-3) and torch.allclose(out[1], ref_b[7], atol=5e-3)
+    # step 2: rest of a's prompt chunk fused with a decode token of b
+    out = eng.put([1, 2], [a[17:20], b[8:9]])
+    assert torch.allclose(out[0], ref_a[19], atol=5e-3) and torch.allclose(out[1], ref_b[8], atol=5e-3)
+    out = eng.put([1], [a[20:21]])
+    assert torch.allclose(out[0], ref_a[20], atol=5e-3)
+    free_before = eng.free_blocks
+    eng.flush(2)
+    assert eng.free_blocks > free_before
+    assert eng.query(1, 5, 10)[0] == 5
+
+
+def test_scheduling_limits_and_splitfuse():
+    from deepspeedsyclsupport_b200.inference.v2 import SchedulingResult, SplitFuseScheduler
+    eng, sd = _engine()
+    assert eng.can_schedule([1], [65]) == SchedulingResult.BatchTokenLimitExceeded
+    assert eng.can_schedule(list(range(9)), [1] * 9) == SchedulingResult.BatchSequenceLimitExceeded
+    assert eng.can_schedule([1], [200]) == SchedulingResult.KVCacheLimitExceeded
+    sch = SplitFuseScheduler(eng, token_budget=16)
+    torch.manual_seed(3)
+    prompts = {10: torch.randint(0, 97, (40, )), 11: torch.randint(0, 97, (5, ))}
+    for uid, p in prompts.items():
+        sch.add_request(uid, p, max_new_tokens=3)
+    done = sch.run_to_completion()
+    for uid, p in prompts.items():
+        seq = p.clone()
+        for t in done[uid]:
+            nxt = int(_dense_llama_logits(sd, CFG, seq)[-1].argmax())
+            assert nxt == t
+            seq = torch.cat([seq, torch.tensor([t])])
+    assert eng.free_blocks == 40

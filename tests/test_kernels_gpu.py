@@ -331,3 +331,84 @@ def test_fake_quantize():
     ys = Q.fake_quantize_(x.clone(), 32, 4, symmetric=True, stochastic=True, seed=7)
     step4 = (x.float().abs().amax(1) * 2 / 16).max().item()
     assert (ys.float() - x.float()).abs().max() <= step4 * 1.01
+
+
+def test_ragged_kernels_vs_reference():
+    """kv append + RoPE, paged attention (decode + chunked prefill), embed, logits gather, top-k gating, scatter/gather."""
+    from deepspeedsyclsupport_b200.inference.v2 import kernels as K
+    from deepspeedsyclsupport_b200.ops.fused_ops import rope_inv_freq
+    torch.manual_seed(0)
+    dev = _dev()
+    hq, hkv, d, bs, nblocks = 8, 2, 128, 16, 64
+    inv = rope_inv_freq(d, device=dev)
+    # two sequences: seq0 has 37 cached tokens + 5 new, seq1 is new with 20 tokens
+    seen, ntok = [37, 0], [5, 20]
+    table = torch.zeros(2, 8, dtype=torch.int32, device=dev)
+    table[0, :3] = torch.tensor([5, 9, 2])
+    table[1, :2] = torch.tensor([7, 11])
+    cache = torch.zeros(nblocks, 2, bs, hkv, d, dtype=torch.bfloat16, device=dev)
+    cache_ref = cache.cpu().clone()
+    # history of seq 0
+    hist = torch.randn(37, hq + 2 * hkv, d, device=dev).bfloat16()
+    pos_h = torch.arange(37, dtype=torch.int32, device=dev)
+    seq_h = torch.zeros(37, dtype=torch.int32, device=dev)
+    K.kv_rotary_append(hist.view(37, -1).clone(), cache, seq_h, pos_h, table, inv, hq, hkv, d)
+    K.kv_rotary_append(hist.view(37, -1).cpu().clone(), cache_ref, seq_h.cpu(), pos_h.cpu(), table.cpu(), inv.cpu(), hq, hkv, d)
+    T = sum(ntok)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, device=dev).bfloat16()
+    tok_seq = torch.tensor([0] * 5 + [1] * 20, dtype=torch.int32, device=dev)
+    tok_pos = torch.tensor(list(range(37, 42)) + list(range(20)), dtype=torch.int32, device=dev)
+    q_gpu = qkv.clone()
+    K.kv_rotary_append(q_gpu, cache, tok_seq, tok_pos, table, inv, hq, hkv, d)
+    q_cpu = qkv.cpu().clone()
+    K.kv_rotary_append(q_cpu, cache_ref, tok_seq.cpu(), tok_pos.cpu(), table.cpu(), inv.cpu(), hq, hkv, d)
+    assert (q_gpu.cpu().float() - q_cpu.float()).abs().max() < 3e-2
+    assert (cache.cpu().float() - cache_ref.float()).abs().max() < 3e-2
+    out = K.paged_attention(q_gpu, cache, tok_seq, tok_pos, table, hq, hkv, d)
+    ref = K.paged_attention_ref(q_gpu.cpu(), cache.cpu(), tok_seq.cpu(), tok_pos.cpu(), table.cpu(), hq, hkv, d, 1.0 / d ** 0.5)
+    assert (out.cpu().float() - ref.float()).abs().max() < 2e-2
+    # embed / logits gather
+    wte = torch.randn(100, 256, device=dev).bfloat16()
+    ids = torch.randint(0, 100, (T, ), device=dev)
+    assert torch.equal(K.ragged_embed(ids, wte), wte[ids])
+    last = torch.tensor([4, 24], dtype=torch.int32, device=dev)
+    hid = torch.randn(T, 256, device=dev).bfloat16()
+    assert torch.equal(K.logits_gather(hid, last), hid[last.long()])
+    # MoE routing
+    E, k = 8, 2
+    logits = torch.randn(T, E, device=dev)
+    counts, scores, asg, off = K.top_k_gating(logits, k)
+    c2, s2, a2, o2 = K.top_k_gating(logits.cpu(), k)
+    assert torch.equal(counts.cpu(), c2) and torch.equal(asg.cpu(), a2)
+    assert torch.allclose(scores.cpu(), s2, atol=1e-5)
+    for e in range(E):  # offsets are a permutation of 0..count-1 inside every expert
+        sel = off[asg == e].sort().values.cpu()
+        assert torch.equal(sel, torch.arange(sel.numel(), dtype=torch.int32))
+    x = torch.randn(T, 256, device=dev).bfloat16()
+    moe_in, cumsum, slots = K.moe_scatter(x, counts, asg, off)
+    assert torch.equal(cumsum.cpu(), counts.cpu().long().cumsum(0))
+    for j in range(k):
+        assert torch.equal(moe_in[slots[:, j].long()], x)
+    y = K.moe_gather(moe_in, scores, slots)
+    assert (y.float() - x.float() * scores.sum(1, keepdim=True)).abs().max() < 3e-2
+
+
+def test_fastgen_engine_gpu_matches_dense():
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_inference_v2 import _dense_llama_logits, _hf_llama_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, SplitFuseScheduler, build_engine_from_state_dict
+    cfg = dict(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+               rms_norm_eps=1e-5)
+    sd = _hf_llama_state(cfg)
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 512, "max_ragged_sequence_count": 8, "max_context": 1024,
+                                                      "memory_config": {"mode": "allocate", "size": 64}})
+    eng = build_engine_from_state_dict("llama", cfg, sd, ecfg)
+    torch.manual_seed(1)
+    a = torch.randint(0, 512, (300, ))
+    ref = _dense_llama_logits({k: v.bfloat16().float() for k, v in sd.items()}, cfg, a)
+    out = eng.put([1], [a[:200]])
+    assert (out[0].float().cpu() - ref[199]).abs().max() < 0.06 * ref[199].abs().max() + 0.02
+    out = eng.put([1], [a[200:]])
+    assert (out[0].float().cpu() - ref[299]).abs().max() < 0.06 * ref[299].abs().max() + 0.02
+    assert out.dtype == torch.bfloat16 and out.is_cuda
