@@ -1,0 +1,258 @@
+"""AutoTP: automatic tensor parallelism for arbitrary HF-style transformer modules.
+Parity: deepspeed/module_inject/auto_tp.py:187-483 -- `tp_parser` walks the ModuleList blocks and finds the linears
+whose outputs must be all-reduced (the last linear before a norm / residual: o_proj, out_proj, down_proj, dense_4h_to_h,
+...); `_replace` row-slices those into `LinearAllreduce`, column-slices every other linear into `LinearLayer`
+(fused-QKV aware), slices embeddings and updates head-count attributes."""
+import re
+
+import torch
+from torch import nn
+
+from .. import comm as dist
+from ..accelerator import get_accelerator
+from .fusedqkv_utils import prepare_tp_fused_qkvw, require_tp_fused_qkvw
+from .layers import LinearAllreduce, LinearLayer, LmHeadLinearAllreduce
+
+
+class ReplaceWithTensorSlicing:
+
+    def __init__(self, mp_group=None, mp_size=1, out_dim=1, in_dim=0):
+        if mp_group is not None:
+            self.gpu_index = dist.get_rank(group=mp_group)
+        else:
+            self.gpu_index = 0
+        self.out_dim = out_dim
+        self.in_dim = in_dim
+        self.mp_size = mp_size
+
+    def copy(self, dst, src, int8=False, allocate_tensor=False):
+        if src is None:
+            return src
+        return torch.nn.parameter.Parameter(src.chunk(self.mp_size, dim=0)[self.gpu_index].clone(), requires_grad=False)
+
+
+class Loading:
+
+    @staticmethod
+    def is_load_module(module):
+        load_layers = [nn.Linear, nn.Embedding, nn.LayerNorm]
+        load_layer_names = ["LPLayerNorm", "SharedEmbedding", "OPTLearnedPositionalEmbedding", "LlamaRMSNorm", "FalconLinear",
+                            "MistralRMSNorm", "T5LayerNorm", "MixtralRMSNorm"]
+        return module.__class__ in load_layers or module._get_name() in load_layer_names
+
+
+class AutoTP:
+
+    def __init__(self, module, all_reduce_linears, prefix, state_dict, linear_layer_setting, orig_layer_impl):
+        self.module = module
+        self.all_reduce_linears = all_reduce_linears
+        self.prefix = prefix
+        self.state_dict = state_dict
+        self.mp_size = None
+        self.mp_group = None
+        self.linear_layer_setting = linear_layer_setting
+        self.orig_layer_impl = orig_layer_impl
+        self.linear_policies = None
+        self.conv_linear_layer = False
+
+    @staticmethod
+    def in_module_list(module, module_list):
+        for item in module_list:
+            if type(item).__name__ == type(module).__name__:
+                return True
+        return False
+
+    @staticmethod
+    def get_module_list(model):
+        mlist = []
+        for child in model.children():
+            if isinstance(child, nn.ModuleList):
+                for module in child.children():
+                    if not mlist:
+                        mlist = [module]
+                    elif not AutoTP.in_module_list(module, mlist):
+                        mlist = mlist + [module]
+            else:
+                mlist = mlist + AutoTP.get_module_list(child)
+        return mlist
+
+    @staticmethod
+    def supported(model):
+        unsupported = ["deberta", "flaubert", "fsmt", "gpt2", "led", "longformer", "xlm", "xlnet"]
+        model = str(model)
+        key = re.search(r": (.*?)Model", model)
+        if key is None:
+            key = re.search(r": (.*?)Stack", model)
+        if key is None:
+            key = re.match(r"(.*?)Model", model)
+        if key is None:
+            return True
+        return key.group(1).lower() not in unsupported
+
+    @staticmethod
+    def get_layers(parent, module):
+        layer_list = []
+        for key, submodule in module._modules.items():
+            if isinstance(submodule, nn.Linear):
+                layer_list = layer_list + [parent + "." + key]
+            elif isinstance(submodule, nn.LayerNorm) or key == "LayerNorm" or key == "layer_norm":
+                layer_list = layer_list + ["ln"]
+            else:
+                layer_list = layer_list + AutoTP.get_layers(key, submodule)
+        return layer_list
+
+    @staticmethod
+    def update_policy_list(policy_list, new_module, new_gems):
+        if len(policy_list):
+            for i, policy in enumerate(policy_list):
+                if policy[0] == type(new_module):
+                    new_gems = set(new_gems + policy[1])
+                    policy_list[i] = tuple([type(new_module), new_gems])
+                    return policy_list
+        policy_list.append(tuple([type(new_module), new_gems]))
+        return policy_list
+
+    @staticmethod
+    def kernel_supported(module_list):
+        policy = []
+        return False
+
+    @staticmethod
+    def tp_parser(model):
+        """[(block class, {names of linears that need an all-reduce})]"""
+        policy_list = []
+        module_list = AutoTP.get_module_list(model)
+        assert AutoTP.supported(model), "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
+        norm_layer_name_list = ["LayerNorm", "layer_norm", "ln_1", "ln_2"]
+        for module in module_list:
+            for key, submodule in module._modules.items():
+                if isinstance(submodule, nn.Linear):
+                    layer_list = ["." + key]
+                elif isinstance(submodule, nn.LayerNorm) or key in norm_layer_name_list:
+                    layer_list = ["ln"]
+                else:
+                    layer_list = AutoTP.get_layers(key, submodule)
+                gem_list = []
+                for i, layer in enumerate(layer_list):
+                    if layer == "ln":
+                        if i > 0 and layer_list[i - 1] != "ln":
+                            gem_list = gem_list + [layer_list[i - 1]]
+                    elif "out_proj" in layer or "o_proj" in layer or "down_proj" in layer or "attention.dense" in layer and "GPTNeoX" in str(model) \
+                            or "self_attention.dense" in layer and "falcon" in str(type(module)).lower() or "dense_4h_to_h" in layer \
+                            or "w2" in layer and "mixtral" in str(type(module)).lower():
+                        gem_list = gem_list + [layer]
+                if len(layer_list) > 0 and layer_list[-1] != "ln" and len(gem_list) == 0 and key in ("mlp", "feed_forward", "ffn"):
+                    gem_list = gem_list + [layer_list[-1]]
+                layer_list = []
+                if gem_list != []:
+                    gem_list = list(set(gem_list))
+                    policy_list = AutoTP.update_policy_list(policy_list, module, gem_list)
+                    gem_list = []
+        assert len(policy_list), "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
+        return policy_list
+
+    def set_tensor_parallel_config(self, mp_size, mp_group):
+        self.mp_size = mp_size
+        self.mp_group = mp_group
+
+    def _rank(self):
+        return dist.get_rank(self.mp_group) if (self.mp_group is not None and dist.is_initialized()) else 0
+
+    def _replace(self, child, name, conv_linear_layer=False):
+        if getattr(child, "replaced", False):
+            return child
+        weight_shape = child.weight.shape
+        mp, r = self.mp_size, self._rank()
+        dev = get_accelerator().current_device_name()
+        if name in self.all_reduce_linears:
+            # row parallel: slice input features, all-reduce output
+            data = child.weight.data.chunk(mp, dim=1)[r].contiguous().to(dev)
+            bias = None if child.bias is None else torch.nn.parameter.Parameter(child.bias.data.to(dev), requires_grad=False)
+            new = LinearAllreduce(torch.nn.parameter.Parameter(data, requires_grad=False), bias, self.mp_group)
+            new.replaced = True
+            return new
+        # column parallel
+        module_str = str(self.module).strip()
+        if require_tp_fused_qkvw(name, mp):
+            cfg = getattr(self.module, "config", None)
+            data = prepare_tp_fused_qkvw(module_str, child.weight.data, mp, r)
+            bias = prepare_tp_fused_qkvw(module_str, child.bias.data, mp, r) if child.bias is not None else None
+        else:
+            data = child.weight.data.chunk(mp, dim=0)[r]
+            bias = child.bias.data.chunk(mp, dim=0)[r] if child.bias is not None else None
+        new = LinearLayer(weight=torch.nn.parameter.Parameter(data.contiguous().to(dev), requires_grad=False),
+                          bias=None if bias is None else torch.nn.parameter.Parameter(bias.contiguous().to(dev), requires_grad=False))
+        new.replaced = True
+        return new
+
+    def _slice_embedding(self, child, name, conv_linear_layer=False):
+        if getattr(child, "replaced", False):
+            return child
+        mp, r = self.mp_size, self._rank()
+        data = child.weight.data.chunk(mp, dim=1)[r].contiguous().to(get_accelerator().current_device_name())
+        new_embedding = nn.Embedding(child.weight.shape[0], data.shape[1])
+        new_embedding.weight = torch.nn.parameter.Parameter(data, requires_grad=False)
+        new_embedding.replaced = True
+        return new_embedding
+
+    def update_mp_params(self, child):
+        if getattr(child, "replaced", False):
+            return
+        for param in ["n_heads", "inner_dim", "num_heads", "num_kv", "num_attention_heads", "num_attn_heads", "all_head_size",
+                      "embed_dim", "hidden_size", "num_key_value_heads", "num_kv_heads", "kv_n_heads", "d_model"]:
+            if hasattr(child, param):
+                param_val = getattr(child, param)
+                if isinstance(param_val, int) and param_val % self.mp_size == 0:
+                    setattr(child, param, param_val // self.mp_size)
+        setattr(child, "replaced", True)
+
+    def update_linear_policies(self):
+        self.conv_linear_layer = False
+        if self.linear_layer_setting is not None:
+            self.linear_policies = {self.linear_layer_setting[0]: self._replace}
+            if len(self.linear_layer_setting) == 2:
+                self.linear_policies.update({self.linear_layer_setting[1]: self._slice_embedding})
+        else:
+            self.linear_policies = {nn.Linear: self._replace}
+
+    def _replace_module(self, r_module, prev_name="", prev_class_name=""):
+        for name, child in r_module.named_children():
+            if prev_class_name == "":
+                class_name = prev_name
+            elif prev_name == "":
+                class_name = prev_class_name
+            else:
+                class_name = prev_class_name + "." + prev_name
+            checking_key = self.prefix + "." + class_name + "." + name + "." if class_name != "" else self.prefix + "." + name + "."
+            if child.__class__ in self.linear_policies:
+                setattr(r_module, name, self.linear_policies[child.__class__](child, prev_name + "." + name, self.conv_linear_layer))
+            else:
+                self.update_mp_params(child)
+                self._replace_module(child, name, class_name)
+        return r_module
+
+    def get_model_num_kv_heads(self, config):
+        num_kv_heads = None
+        for name in ["num_kv_heads", "num_key_value_heads", "num_attention_heads", "n_heads"]:
+            if hasattr(config, name):
+                num_kv_heads = getattr(config, name)
+                if num_kv_heads is not None:
+                    break
+        return num_kv_heads
+
+    def _replace_last_linear_module(self, r_module):
+        if hasattr(r_module, "lm_head"):
+            name = "lm_head"
+            child = r_module.lm_head
+        elif hasattr(r_module, "embed_out"):
+            name = "embed_out"
+            child = r_module.embed_out
+        else:
+            return r_module
+        if isinstance(child, nn.Linear) and child.weight.shape[1] % self.mp_size == 0 and self.mp_size > 1:
+            mp, r = self.mp_size, self._rank()
+            dev = get_accelerator().current_device_name()
+            data = child.weight.data.chunk(mp, dim=1)[r].contiguous().to(dev)
+            bias = None if child.bias is None else torch.nn.parameter.Parameter(child.bias.data.to(dev), requires_grad=False)
+            setattr(r_module, name, LmHeadLinearAllreduce(torch.nn.parameter.Parameter(data, requires_grad=False), r, mp, bias, self.mp_group))
+        return r_module
