@@ -4,6 +4,7 @@ import math
 import torch
 
 from . import native
+from ..profiling.flops_profiler import profiler as _prof
 
 native.register_sigs({
     "dsb200_flash_attn_fwd": "ppp iiiii i f p",
@@ -19,6 +20,9 @@ def flash_fwd(qkv, B, S, hq, hkv, d, causal=True, scale=None, need_lse=True):
     rc = native.lib().dsb200_flash_attn_fwd(native.ptr(qkv), native.ptr(out), native.ptr(lse), B, S, hq, hkv, d, int(causal),
                                             float(scale), native.stream_ptr())
     native.check(rc)
+    if _prof._ACTIVE:
+        macs = 2 * B * hq * S * S * d // (2 if causal else 1)
+        _prof.record_flops(2 * macs, macs, "dsb200_flash_attn_fwd")
     return out, lse
 
 

@@ -8,6 +8,7 @@ directly into an fp32 main-grad buffer with TMA reduce-add.
 import torch
 
 from . import native
+from ..profiling.flops_profiler import profiler as _prof
 
 
 def _gemm_ref(a, b, a_mn, b_mn, out_dtype, out=None, accumulate=False):
@@ -46,6 +47,8 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
                                        b.stride(0), out.stride(0), int(a_mn), int(b_mn), mode, int(max_ctas),
                                        native.stream_ptr())
     native.check(rc)
+    if _prof._ACTIVE:
+        _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_bf16")
     return out
 
 

@@ -808,9 +808,9 @@ class DeepSpeedEngine(Module):
             self.flops_profiler.stop_profile()
         return loss
 
-    def allreduce_gradients(self, bucket_size=MEMORY_OPT_ALLREDUCE_SIZE):
+    def allreduce_gradients(self, bucket_size=MEMORY_OPT_ALLREDUCE_SIZE, local_only=False):
         if self.optimizer is not None and hasattr(self.optimizer, "end_micro_step"):
-            self.optimizer.end_micro_step(self.is_gradient_accumulation_boundary())
+            self.optimizer.end_micro_step(self.is_gradient_accumulation_boundary(), local_only=local_only)
 
     def backward(self, loss, allreduce_gradients=True, release_loss=False, retain_graph=False, scale_wrt_gas=True):
         assert self.optimizer is not None, "must provide optimizer during init in order to use backward"
@@ -823,8 +823,10 @@ class DeepSpeedEngine(Module):
         self.optimizer.backward(loss, retain_graph=retain_graph)
         self._stop_timers(self.engine_timers.backward_inner_timers)
         self._start_timers(self.engine_timers.backward_reduce_timers)
-        if allreduce_gradients and self.enable_backward_allreduce:
-            self.allreduce_gradients()
+        if allreduce_gradients:
+            # enable_backward_allreduce is switched off by the communication-compressed optimizers once they start
+            # compressing: the micro-step bookkeeping still runs, only the dense data-parallel reduction is skipped
+            self.allreduce_gradients(local_only=not self.enable_backward_allreduce)
         self._stop_timers(self.engine_timers.backward_reduce_timers)
         self._stop_timers(self.engine_timers.backward_timers)
         if release_loss:
@@ -863,6 +865,12 @@ class DeepSpeedEngine(Module):
             report_progress = self.global_rank == 0 if self.global_rank else True
         self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report_progress)
         self._stop_timers(self.engine_timers.step_timers)
+        if self.flops_profiler is not None and self.flops_profiler.started and self.is_gradient_accumulation_boundary():
+            if self.global_rank == 0:
+                self.flops_profiler.print_model_profile(profile_step=self.global_steps - 1, module_depth=self.flops_profiler_module_depth(),
+                                                        top_modules=self.flops_profiler_top_modules(), detailed=self.flops_profiler_detailed(),
+                                                        output_file=self.flops_profiler_output_file())
+            self.flops_profiler.end_profile()
         if self.is_gradient_accumulation_boundary():
             if self.monitor.enabled and self.global_rank == 0:
                 events = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]

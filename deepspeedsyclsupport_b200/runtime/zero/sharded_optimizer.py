@@ -138,6 +138,7 @@ class ZeroShardedOptimizer:
         self._skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
 
         self._opt_kind = type(self.optimizer).__name__ if self.optimizer is not None else None
+        self._local_grads_only = False
         self._step_count = 0
         self._register_grad_hooks()
         self._trace = {"fwd": [], "bwd": []}
@@ -427,6 +428,15 @@ class ZeroShardedOptimizer:
         """reduce-scatter (+ replica all-reduce) of one unit's gradient buffer into the flat gradient shard."""
         if u.full_grad is None:
             return
+        if self._local_grads_only:
+            # communication-compressed optimizers (1-bit Adam & co.) consume the LOCAL gradient after their warm-up: no
+            # collective, no averaging (stage 0 only, where the "shard" is the whole unit)
+            assert self.shard_world == 1, "compressed-communication optimizers require ZeRO stage 0"
+            dst = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
+            if u.full_grad.data_ptr() != dst.data_ptr():
+                dst.add_(u.full_grad.to(dst.dtype) if u.full_grad.dtype != dst.dtype else u.full_grad)
+            u.reduced = True
+            return
         if self.p2p is not None:
             return self._p2p_reduce_unit(u)
         buf = u.full_grad
@@ -480,8 +490,10 @@ class ZeroShardedOptimizer:
     def overlapping_partition_gradients_reduce_epilogue(self):
         self.reduce_gradients()
 
-    def end_micro_step(self, boundary):
-        """Engine hook after every backward()."""
+    def end_micro_step(self, boundary, local_only=False):
+        """Engine hook after every backward().  local_only: skip the data-parallel reduction (the basic optimizer
+        communicates by itself, e.g. 1-bit Adam after its warm-up)."""
+        self._local_grads_only = bool(local_only)
         if self.stage >= 2 or boundary:
             if self.stage <= 1 and not boundary:
                 pass
@@ -746,8 +758,46 @@ class ZeroShardedOptimizer:
         elif kind in ("Adagrad", "DeepSpeedCPUAdagrad"):
             region.state = {"exp_avg_sq": region.zeros()}
 
+    def _is_fused_kind(self, kind):
+        return kind in _ADAM_TYPES or kind in ("FusedLion", "DeepSpeedCPULion", "Lion", "Adagrad", "DeepSpeedCPUAdagrad")
+
+    def _rebind_basic_optimizer(self):
+        """Client / non-fused optimizers (SGD, LAMB, 1-bit Adam, anything torch.optim): point the user's optimizer object
+        at fp32 views of the flat master regions -- one big tensor per (region, param group) -- and keep calling ITS step().
+        State, hyper-parameters, LR schedulers and custom communication (compressed all-reduce) all stay with that
+        object, which is what the reference's FP16/BF16/ZeRO wrappers do with their flattened fp32 groups."""
+        self._generic_bind = []
+        per_group = [[] for _ in self.param_groups]
+        for region in self.regions:
+            for gi, lo, hi in self.runs:
+                a, b = max(lo, region.lo), min(hi, region.hi)
+                if a >= b or gi < 0:
+                    continue
+                s = slice(a - region.lo, b - region.lo)
+                w = torch.nn.Parameter(region.master[s], requires_grad=True)
+                per_group[gi].append(w)
+                self._generic_bind.append((w, region, s))
+        self.optimizer.state.clear()
+        for g, ws in zip(self.optimizer.param_groups, per_group):
+            g["params"] = ws
+
+    def _generic_step(self):
+        if not hasattr(self, "_generic_bind"):
+            self._rebind_basic_optimizer()
+        scale = float(self._inv_scale.item())
+        for w, region, s in self._generic_bind:
+            g = self.grad_shard[region.lo:region.hi][s]
+            w.grad = g.to(device=w.device, dtype=torch.float32) * scale
+        self.optimizer.step()
+        for w, region, s in self._generic_bind:
+            w.grad = None
+            if self.dtype != torch.float32 or w.device != self.lp_shard.device:
+                self.lp_shard[region.lo:region.hi][s].copy_(w.data, non_blocking=True)
+
     def _optimizer_step(self):
         kind = self._opt_kind
+        if not self._is_fused_kind(kind):
+            return self._generic_step()
         for region in self.regions:
             self._ensure_state(region, kind)
             on_host = region.device.type == "cpu" and self.cuda
@@ -962,6 +1012,8 @@ class ZeroShardedOptimizer:
             "optimizer_state_dict": {"state": {0: state},
                                      "param_groups": [{k: v for k, v in g.items() if k != "params"} for g in self.param_groups]},
         }
+        if hasattr(self, "_generic_bind"):
+            sd["basic_optimizer_state_dict"] = self.optimizer.state_dict()  # client / non-fused optimizer on the flat views
         if self.stage == 3:
             sd["fp32_flat_groups"] = [master]
         else:
@@ -989,6 +1041,10 @@ class ZeroShardedOptimizer:
         else:
             for r in self.regions:
                 r.master.copy_(self.lp_shard[r.lo:r.hi].float())
+        if load_optimizer_states and "basic_optimizer_state_dict" in sd and not self._is_fused_kind(self._opt_kind):
+            if not hasattr(self, "_generic_bind"):
+                self._rebind_basic_optimizer()
+            self.optimizer.load_state_dict(sd["basic_optimizer_state_dict"])
         if load_optimizer_states:
             st = sd["optimizer_state_dict"]["state"].get(0, {})
             for r in self.regions:
