@@ -95,9 +95,9 @@ __global__ void unpack_kernel(const unsigned char* __restrict__ packed, const fl
 
 // x[n] fp32 (read only), err[n] fp32 (error feedback, updated), packed[n/8], scale_io[2] fp32 device scratch:
 // on return scale_io[0] = ||x+err||_2 / sqrt(n).  n must be a multiple of 8; x/err 16-byte aligned.
-DSB_EXPORT int dsb200_onebit_compress(void* x, void* err, void* packed, void* scale_io, long n, cudaStream_t stream) {
+DSB_EXPORT int dsb200_onebit_compress(void* x, void* err, void* packed, void* scale_io, long long n, cudaStream_t stream) {
   using namespace dsb;
-  DSB_REQUIRE(n > 0 && n % 8 == 0, "onebit_compress: n=%ld must be a positive multiple of 8", n);
+  DSB_REQUIRE(n > 0 && n % 8 == 0, "onebit_compress: n=%lld must be a positive multiple of 8", n);
   DSB_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)err & 15) == 0, "onebit_compress: 16-byte alignment required");
   DSB_CHECK_CUDA(cudaMemsetAsync(static_cast<float*>(scale_io) + 1, 0, sizeof(float), stream));
   const int threads = 256;
@@ -113,7 +113,7 @@ DSB_EXPORT int dsb200_onebit_compress(void* x, void* err, void* packed, void* sc
   return DSB_OK;
 }
 
-DSB_EXPORT int dsb200_onebit_decompress(const void* packed, const void* scales, void* out, int rows, long chunk_bytes,
+DSB_EXPORT int dsb200_onebit_decompress(const void* packed, const void* scales, void* out, int rows, long long chunk_bytes,
                                         int mode, cudaStream_t stream) {
   using namespace dsb;
   DSB_REQUIRE(rows > 0 && chunk_bytes > 0 && (mode == 0 || mode == 1), "onebit_decompress: bad arguments");

@@ -158,6 +158,12 @@ class DeepSpeedEngine(Module):
         if self.curriculum_enabled_legacy():
             from .data_pipeline.curriculum_scheduler import CurriculumScheduler
             self.curriculum_scheduler_legacy = CurriculumScheduler(self.curriculum_params_legacy())
+        if self.eigenvalue_enabled():
+            from .eigenvalue import Eigenvalue
+            c = self._config
+            self.eigenvalue = Eigenvalue(verbose=c.eigenvalue_verbose, max_iter=c.eigenvalue_max_iter, tol=c.eigenvalue_tol,
+                                         stability=c.eigenvalue_stability, gas_boundary_resolution=c.eigenvalue_gas_boundary_resolution,
+                                         layer_name=c.eigenvalue_layer_name, layer_num=c.eigenvalue_layer_num)
         self.compression_scheduler = None
         cc = self._config.compression_config
         if cc is not None and any(v.get("shared_parameters", {}).get("enabled", False) for k, v in cc.items() if k != "layer_reduction"):
@@ -837,7 +843,15 @@ class DeepSpeedEngine(Module):
         pass  # clipping is folded into the fused optimizer step (device-side coefficient)
 
     def _take_model_step(self, lr_kwargs, block_eigenvalue={}):
+        if self.eigenvalue is not None and self.gas_boundary_ctr % max(1, self._config.eigenvalue_gas_boundary_resolution) == 0:
+            # MoQ: curvature per block feeds the quantisation period of that block (engine.py:2108-2140 upstream)
+            self.block_eigenvalue = self.eigenvalue.compute_eigenvalue(self.module, self.device, self.optimizer.loss_scale
+                                                                       if hasattr(self.optimizer, "loss_scale") else 1.0)
+            if self.compression_scheduler is not None and hasattr(self.compression_scheduler, "set_block_eigenvalue"):
+                self.compression_scheduler.set_block_eigenvalue(self.block_eigenvalue)
         self.optimizer.step()
+        if self.progressive_layer_drop:
+            self.progressive_layer_drop.update_state(self.global_steps)
         self._global_grad_norm = self.optimizer.get_global_grad_norm()
         overflow = getattr(self.optimizer, "overflow", False)
         self._step_applied = not overflow
