@@ -1,14 +1,6 @@
-"""ReduceOp enum (parity: deepspeed/comm/reduce_op.py:9)."""
-from enum import Enum
+"""Reduction operator ids of the comm facade.  The numeric values follow torch.distributed / NCCL ordering so they can be
+logged and compared across backends (reference: deepspeed/comm/reduce_op.py)."""
+import enum
 
-
-class ReduceOp(Enum):
-    SUM = 0
-    PRODUCT = 1
-    MIN = 2
-    MAX = 3
-    BAND = 4
-    BOR = 5
-    BXOR = 6
-    AVG = 7
-    UNUSED = 8
+ReduceOp = enum.Enum("ReduceOp", ["SUM", "PRODUCT", "MIN", "MAX", "BAND", "BOR", "BXOR", "AVG", "UNUSED"], start=0)
+ReduceOp.__doc__ = "SUM, PRODUCT, MIN, MAX, BAND, BOR, BXOR, AVG, UNUSED (values 0..8)"

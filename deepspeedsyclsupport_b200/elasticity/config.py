@@ -1,67 +1,80 @@
-"""ElasticityConfig (parity: deepspeed/elasticity/config.py)."""
+"""`elasticity` config block: validated once, field by field, from a small spec table
+(schema: deepspeed/elasticity/config.py; keys/defaults in elasticity/constants.py)."""
 import json
 
-from .constants import *  # noqa: F401,F403
+from . import constants as K
 
 
 class ElasticityError(Exception):
-    pass
+    """Base exception for all elasticity related errors."""
 
 
 class ElasticityConfigError(ElasticityError):
-    pass
+    """Elasticity configuration error."""
 
 
 class ElasticityIncompatibleWorldSize(ElasticityError):
-    pass
+    """Attempting to run a world size that is incompatible with a given elastic config."""
 
 
-class ElasticityConfig:
+def _positive(name):
+
+    def check(v):
+        if v < 1:
+            raise ElasticityConfigError(f"{name} cannot be less than 1, given: {v}")
+
+    return check
+
+
+class ElasticityConfig(object):
+    """
+    "elasticity": {"enabled": true, "max_train_batch_size": 2000, "micro_batch_sizes": [2,4,6], "min_gpus": 1,
+                   "max_gpus": 10000, "min_time": 20, "prefer_larger_batch": true,
+                   "ignore_non_elastic_batch_info": false, "version": 0.1}
+    """
+
+    # attribute, key, default, validator
+    _OPTIONAL = (
+        ("min_gpus", K.MIN_GPUS, K.MIN_GPUS_DEFAULT, None),
+        ("max_gpus", K.MAX_GPUS, K.MAX_GPUS_DEFAULT, None),
+        ("model_parallel_size", K.MODEL_PARALLEL_SIZE, K.MODEL_PARALLEL_SIZE_DEFAULT, _positive("Model-Parallel size")),
+        ("num_gpus_per_node", K.NUM_GPUS_PER_NODE, K.NUM_GPUS_PER_NODE_DEFAULT, _positive("Number of GPUs per node")),
+        ("min_time", K.MIN_TIME, K.MIN_TIME_DEFAULT, None),
+        ("version", K.VERSION, K.VERSION_DEFAULT, None),
+        ("prefer_larger_batch_size", K.PREFER_LARGER_BATCH, K.PREFER_LARGER_BATCH_DEFAULT, None),
+        ("ignore_non_elastic_batch_info", K.IGNORE_NON_ELASTIC_BATCH_INFO, K.IGNORE_NON_ELASTIC_BATCH_INFO_DEFAULT, None),
+    )
 
     def __init__(self, param_dict):
-        self.enabled = param_dict.get(ENABLED, ENABLED_DEFAULT)
-        if self.enabled:
-            if MAX_ACCEPTABLE_BATCH_SIZE in param_dict:
-                self.max_acceptable_batch_size = param_dict[MAX_ACCEPTABLE_BATCH_SIZE]
-            else:
-                raise ElasticityConfigError(f"Elasticity config missing {MAX_ACCEPTABLE_BATCH_SIZE}")
-            if MICRO_BATCHES in param_dict:
-                self.micro_batches = param_dict[MICRO_BATCHES]
-            else:
-                raise ElasticityConfigError(f"Elasticity config missing {MICRO_BATCHES}")
-        else:
-            self.max_acceptable_batch_size = param_dict.get(MAX_ACCEPTABLE_BATCH_SIZE, MAX_ACCEPTABLE_BATCH_SIZE_DEFAULT)
-            self.micro_batches = param_dict.get(MICRO_BATCHES, MICRO_BATCHES_DEFAULT)
-        if not isinstance(self.micro_batches, list):
-            raise ElasticityConfigError(f"Elasticity expected value of {MICRO_BATCHES} to be a list of micro batches, "
-                                        f"instead is: {type(self.micro_batches)}, containing: {self.micro_batches}")
-        if not all(map(lambda m: isinstance(m, int), self.micro_batches)):
-            raise ElasticityConfigError(f"Elasticity expected {MICRO_BATCHES} to only contain a list of integers, "
-                                        f"instead contains: f{self.micro_batches}")
-        if not all(map(lambda m: m > 0, self.micro_batches)):
-            raise ElasticityConfigError(f"Elasticity expected {MICRO_BATCHES} to only contain positive integers, "
-                                        f"instead contains: f{self.micro_batches}")
-        self.min_gpus = param_dict.get(MIN_GPUS, MIN_GPUS_DEFAULT)
-        self.max_gpus = param_dict.get(MAX_GPUS, MAX_GPUS_DEFAULT)
-        if self.min_gpus < 1 or self.max_gpus < 1:
+        self.enabled = param_dict.get(K.ENABLED, K.ENABLED_DEFAULT)
+        required = {"max_acceptable_batch_size": (K.MAX_ACCEPTABLE_BATCH_SIZE, K.MAX_ACCEPTABLE_BATCH_SIZE_DEFAULT),
+                    "micro_batches": (K.MICRO_BATCHES, K.MICRO_BATCHES_DEFAULT)}
+        for attr, (key, default) in required.items():
+            if self.enabled and key not in param_dict:
+                raise ElasticityConfigError(f"Elasticity config missing {key}")
+            setattr(self, attr, param_dict.get(key, default))
+        mbs = self.micro_batches
+        if not isinstance(mbs, list):
+            raise ElasticityConfigError(f"Elasticity expected value of {K.MICRO_BATCHES} to be a list of micro batches, instead is: "
+                                        f"{type(mbs)}, containing: {mbs}")
+        if any(not isinstance(m, int) for m in mbs):
+            raise ElasticityConfigError(f"Elasticity expected {K.MICRO_BATCHES} to only contain a list of integers, instead contains: {mbs}")
+        if any(m <= 0 for m in mbs):
+            raise ElasticityConfigError(f"Elasticity expected {K.MICRO_BATCHES} to only contain positive integers, instead contains: {mbs}")
+        for attr, key, default, validator in self._OPTIONAL:
+            value = param_dict.get(key, default)
+            if validator is not None:
+                validator(value)
+            setattr(self, attr, value)
+        if min(self.min_gpus, self.max_gpus) < 1:
             raise ElasticityConfigError(f"Elasticity min/max gpus must be > 0, given min_gpus: {self.min_gpus}, max_gpus: {self.max_gpus}")
         if self.max_gpus < self.min_gpus:
             raise ElasticityConfigError(f"Elasticity min_gpus cannot be greater than max_gpus, given min_gpus: {self.min_gpus}, max_gpus: {self.max_gpus}")
-        self.model_parallel_size = param_dict.get(MODEL_PARALLEL_SIZE, MODEL_PARALLEL_SIZE_DEFAULT)
-        if self.model_parallel_size < 1:
-            raise ElasticityConfigError(f"Model-Parallel size cannot be less than 1, given model-parallel size: {self.model_parallel_size}")
-        self.num_gpus_per_node = param_dict.get(NUM_GPUS_PER_NODE, NUM_GPUS_PER_NODE_DEFAULT)
-        if self.num_gpus_per_node < 1:
-            raise ElasticityConfigError(f"Number of GPUs per node cannot be less than 1, given number of GPUs per node: {self.num_gpus_per_node}")
-        self.min_time = param_dict.get(MIN_TIME, MIN_TIME_DEFAULT)
         if self.min_time < 0:
             raise ElasticityConfigError(f"Elasticity min time needs to be >= 0: given {self.min_time}")
-        self.version = param_dict.get(VERSION, VERSION_DEFAULT)
-        self.prefer_larger_batch_size = param_dict.get(PREFER_LARGER_BATCH, PREFER_LARGER_BATCH_DEFAULT)
-        self.ignore_non_elastic_batch_info = param_dict.get(IGNORE_NON_ELASTIC_BATCH_INFO, IGNORE_NON_ELASTIC_BATCH_INFO_DEFAULT)
 
     def repr(self):
-        return self.__dict__
+        return dict(self.__dict__)
 
     def __repr__(self):
         return json.dumps(self.__dict__, sort_keys=True, indent=4)

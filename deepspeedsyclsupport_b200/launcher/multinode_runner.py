@@ -1,5 +1,13 @@
-"""Multi-node command builders: PDSH, OpenMPI, MPICH, Intel MPI, Slurm, MVAPICH.
-Parity: deepspeed/launcher/multinode_runner.py:18-458 (same command shapes; tested as pure functions)."""
+"""Multi-node command builders.  Each runner turns (args, world info, exported env) into the argv of ONE command that,
+run on the launch host, starts the job on every node:
+
+    pdsh     one `launcher.launch` per node over ssh; launch.py then forks the local ranks
+    openmpi / mpich / impi / mvapich     one process per rank directly under mpirun (ranks read their ids from MPI env)
+    slurm    srun -n <ranks>
+
+`get_cmd(environment, active_resources)` returns (argv, kill_argv, environment).  Everything here is pure string
+assembly so it is unit-tested without any of the launchers installed.
+(CLI/flag parity with deepspeed/launcher/multinode_runner.py.)"""
 import os
 import shutil
 import subprocess
@@ -11,11 +19,17 @@ from shlex import split
 from ..utils.logging import logger
 from .constants import MVAPICH_TMP_HOSTFILE, PDSH_MAX_FAN_OUT
 
+LAUNCH_MODULE = "deepspeedsyclsupport_b200.launcher.launch"
+
 
 class MultiNodeRunner(ABC):
+    name = "base"
+    # runners that start ranks directly under MPI cannot honour per-node include/exclude or --num_nodes/--num_gpus
+    supports_resource_filters = True
 
-    def __init__(self, args, world_info_base64):
+    def __init__(self, args, world_info_base64, resource_pool=None):
         self.args = args
+        self.resource_pool = resource_pool
         self.validate_args()
         self.user_arguments = self.parse_user_args()
         self.user_script = args.user_script
@@ -24,11 +38,11 @@ class MultiNodeRunner(ABC):
 
     @abstractmethod
     def backend_exists(self):
-        """Return whether the corresponding backend exists"""
+        """Is the launcher binary available on this host?"""
 
     @abstractmethod
     def get_cmd(self, environment, active_resources):
-        """Return the command to execute on node"""
+        """(argv, kill_argv, environment)"""
 
     def add_export(self, key, var):
         self.exports[key.strip()] = var.strip()
@@ -36,308 +50,195 @@ class MultiNodeRunner(ABC):
     def parse_user_args(self):
         return self.args.user_args
 
-    @property
-    def name(self):
-        return self.__class__.__name__
-
     def validate_args(self):
-        """Validate self.args"""
+        if self.supports_resource_filters:
+            return
+        if self.args.include != "" or self.args.exclude != "":
+            raise ValueError(f"{self.name} backend does not support worker include/exclusion")
+        if self.args.num_nodes != -1 or self.args.num_gpus != -1:
+            raise ValueError(f"{self.name} backend does not support limiting num nodes/gpus")
+
+    # ---- shared fragments
+    def _python(self):
+        """Interpreter prefix for the user script: [] with --no_python, else python -u [-m]."""
+        if self.args.no_python:
+            return []
+        return [sys.executable, "-u"] + (["-m"] if self.args.module else [])
+
+    def _user_command(self):
+        return [self.user_script] + list(self.user_arguments)
+
+    def _uniform_ranks_per_node(self, what):
+        per_node = list(self.resource_pool.values())
+        if any(n != per_node[0] for n in per_node):
+            raise ValueError(f"{what} requires same number of devices per node")
+        return per_node[0], sum(per_node)
+
+    def _rendezvous(self, flag, total, per_node):
+        pairs = (("MASTER_ADDR", self.args.master_addr), ("MASTER_PORT", self.args.master_port), ("WORLD_SIZE", total), ("LOCAL_SIZE", per_node))
+        out = []
+        for k, v in pairs:
+            out += [flag, k, str(v)]
+        return out
 
 
 class PDSHRunner(MultiNodeRunner):
-
-    def __init__(self, args, world_info_base64):
-        super().__init__(args, world_info_base64)
+    name = "pdsh"
 
     def backend_exists(self):
         return shutil.which("pdsh")
 
     def parse_user_args(self):
-        processed_args = []
-        for arg in self.args.user_args:
-            if arg.startswith("{") and arg.endswith("}"):
-                arg = "'{}'".format(arg)
-            processed_args.append(arg)
-        return processed_args
-
-    @property
-    def name(self):
-        return "pdsh"
+        # JSON blobs must survive the remote shell
+        return [f"'{a}'" if (a.startswith("{") and a.endswith("}")) else a for a in self.args.user_args]
 
     def get_cmd(self, environment, active_resources):
         environment["PDSH_RCMD_TYPE"] = "ssh"
         if self.args.ssh_port is not None:
             environment["PDSH_SSH_ARGS_APPEND"] = f"{environment.get('PDSH_SSH_ARGS_APPEND', '')} -p {self.args.ssh_port}"
-        active_workers = ",".join(active_resources.keys())
-        logger.info("Running on the following workers: %s" % active_workers)
-        pdsh_cmd_args = ["pdsh", "-S", "-f", str(PDSH_MAX_FAN_OUT), "-w", active_workers] + split(self.args.launcher_args)
-        exports = ""
-        for key, val in self.exports.items():
-            exports += "export {}={}; ".format(key, val)
-        deepspeed_launch = [exports, f"cd {os.path.abspath('.')};", sys.executable, "-u", "-m", "deepspeedsyclsupport_b200.launcher.launch",
-                            f"--world_info={self.world_info_base64}", "--node_rank=%n", f"--master_addr={self.args.master_addr}",
-                            f"--master_port={self.args.master_port}"]
-        if self.args.no_python:
-            deepspeed_launch.append("--no_python")
-        if self.args.module:
-            deepspeed_launch.append("--module")
-        if self.args.no_local_rank:
-            deepspeed_launch.append("--no_local_rank")
-        # every node launcher always records its own PID under /tmp/<runner pid>.deepspeed so that the kill command can
-        # signal exactly that process (which tears down its own children) instead of matching command lines by pattern
-        deepspeed_launch += ["--save_pid", f"{os.getpid()}"]
+        workers = ",".join(active_resources.keys())
+        logger.info("Running on the following workers: %s" % workers)
+        pdsh = ["pdsh", "-S", "-f", str(PDSH_MAX_FAN_OUT), "-w", workers] + split(self.args.launcher_args)
+        exports = "".join(f"export {k}={v}; " for k, v in self.exports.items())
+        # %n is replaced by pdsh with the node's index in the -w list = its node rank
+        launch = [exports, f"cd {os.path.abspath('.')};", sys.executable, "-u", "-m", LAUNCH_MODULE, f"--world_info={self.world_info_base64}",
+                  "--node_rank=%n", f"--master_addr={self.args.master_addr}", f"--master_port={self.args.master_port}"]
+        for flag, on in (("--no_python", self.args.no_python), ("--module", self.args.module), ("--no_local_rank", self.args.no_local_rank)):
+            if on:
+                launch.append(flag)
+        # every node launcher records its PID under /tmp/<runner pid>.deepspeed so the kill command can signal exactly
+        # that process (which tears down its own children) instead of matching command lines by pattern
+        launch += ["--save_pid", f"{os.getpid()}"]
         if self.args.elastic_training:
-            deepspeed_launch.append("--enable_elastic_training")
-            deepspeed_launch.append(f"--max_elastic_nodes={self.args.max_elastic_nodes}")
-            deepspeed_launch.append(f"--min_elastic_nodes={self.args.min_elastic_nodes}")
+            launch += ["--enable_elastic_training", f"--max_elastic_nodes={self.args.max_elastic_nodes}", f"--min_elastic_nodes={self.args.min_elastic_nodes}"]
         pid_file = f"/tmp/{os.getpid()}.deepspeed"
-        kill_command = pdsh_cmd_args + [f"test -f {pid_file} && kill -TERM $(cat {pid_file})"]
-        return pdsh_cmd_args + deepspeed_launch + [self.user_script] + self.user_arguments, kill_command, environment
+        kill = pdsh + [f"test -f {pid_file} && kill -TERM $(cat {pid_file})"]
+        return pdsh + launch + self._user_command(), kill, environment
 
 
 class OpenMPIRunner(MultiNodeRunner):
+    name = "openmpi"
+    supports_resource_filters = False
 
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+        super().__init__(args, world_info_base64, resource_pool)
         self.add_export("UCX_TLS", "tcp")
 
     def backend_exists(self):
         return shutil.which("ompi_info")
 
-    @property
-    def name(self):
-        return "openmpi"
-
-    def validate_args(self):
-        super().validate_args()
-        if self.args.include != "" or self.args.exclude != "":
-            raise ValueError(f"{self.name} backend does not support worker include/exclusion")
-        if self.args.num_nodes != -1 or self.args.num_gpus != -1:
-            raise ValueError(f"{self.name} backend does not support limiting num nodes/gpus")
-
     def get_cmd(self, environment, active_resources):
-        total_process_count = sum(self.resource_pool.values())
-        mpirun_cmd = ["mpirun", "-n", f"{total_process_count}", "-hostfile", f"{self.args.hostfile}", "--mca", "btl", "^openib", "--mca",
-                      "btl_tcp_if_include", "eth0"] + split(self.args.launcher_args)
-        export_cmd = []
+        total = sum(self.resource_pool.values())
+        mpirun = ["mpirun", "-n", f"{total}", "-hostfile", f"{self.args.hostfile}", "--mca", "btl", "^openib", "--mca", "btl_tcp_if_include", "eth0"]
+        mpirun += split(self.args.launcher_args)
         for k, v in self.exports.items():
-            export_cmd += ["-x", "{}={}".format(k, v)]
-        python_exec = []
-        if not self.args.no_python:
-            python_exec = [sys.executable, "-u"]
-            if self.args.module:
-                python_exec.append("-m")
-        return mpirun_cmd + export_cmd + python_exec + [self.user_script] + self.user_arguments, [], environment
+            mpirun += ["-x", f"{k}={v}"]
+        return mpirun + self._python() + self._user_command(), [], environment
 
 
 class MPICHRunner(MultiNodeRunner):
-
-    def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+    name = "mpich"
+    supports_resource_filters = False
 
     def backend_exists(self):
         return shutil.which("mpirun")
 
-    @property
-    def name(self):
-        return "mpich"
-
-    def validate_args(self):
-        super().validate_args()
-        if self.args.include != "" or self.args.exclude != "":
-            raise ValueError(f"{self.name} backend does not support worker include/exclusion")
-        if self.args.num_nodes != -1 or self.args.num_gpus != -1:
-            raise ValueError(f"{self.name} backend does not support limiting num nodes/gpus")
-
     def get_cmd(self, environment, active_resources):
-        devices_per_node = self.resource_pool.values()
-        total_process_count = sum(devices_per_node)
-        process_per_node = list(devices_per_node)[0]
-        if not all([n == process_per_node for n in devices_per_node]):
-            raise ValueError("MPICH requires same number of devices per node")
-        mpirun_cmd = ["mpirun"] + split(self.args.launcher_args)
-        export_cmd = []
+        per_node, total = self._uniform_ranks_per_node("MPICH")
+        mpirun = ["mpirun"] + split(self.args.launcher_args)
         for k, v in self.exports.items():
-            export_cmd += ["-genv", "{}".format(k), "{}".format(v)]
-        export_cmd += ["-genv", "MASTER_ADDR", str(self.args.master_addr)]
-        export_cmd += ["-genv", "MASTER_PORT", str(self.args.master_port)]
-        export_cmd += ["-genv", "WORLD_SIZE", str(total_process_count)]
-        export_cmd += ["-genv", "LOCAL_SIZE", str(process_per_node)]
-        export_cmd += ["-hosts"]
-        hosts = ""
-        for i, host in enumerate(self.resource_pool.keys()):
-            hosts += f",{host}" if i else host
-        export_cmd += [hosts]
-        helper_args = ["--launcher"] + [self.args.launcher]
-        python_exec = []
-        if not self.args.no_python:
-            python_exec += [sys.executable, "-u"]
-            if self.args.module:
-                python_exec.append("-m")
-                helper_args.append("--module")
-        else:
-            helper_args.append("--no_python")
-        helper_cmd = str(os.path.dirname(os.path.realpath(__file__))) + "/launcher_helper.py"
-        helper_cmd = [helper_cmd] + helper_args + [self.user_script] + self.user_arguments
-        return mpirun_cmd + export_cmd + python_exec + helper_cmd, [], environment
+            mpirun += ["-genv", f"{k}", f"{v}"]
+        mpirun += self._rendezvous("-genv", total, per_node)
+        mpirun += ["-hosts", ",".join(self.resource_pool.keys())]
+        # MPICH exports PMI_RANK etc.; the helper maps them to RANK / LOCAL_RANK before running the script
+        helper = [os.path.join(os.path.dirname(os.path.realpath(__file__)), "launcher_helper.py"), "--launcher", self.args.launcher]
+        if self.args.no_python:
+            helper.append("--no_python")
+        elif self.args.module:
+            helper.append("--module")
+        return mpirun + self._python() + helper + self._user_command(), [], environment
 
 
 class IMPIRunner(MultiNodeRunner):
-
-    def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+    name = "impi"
+    supports_resource_filters = False
 
     def backend_exists(self):
         return shutil.which("mpirun")
 
-    @property
-    def name(self):
-        return "impi"
-
-    def validate_args(self):
-        super().validate_args()
-        if self.args.include != "" or self.args.exclude != "":
-            raise ValueError(f"{self.name} backend does not support worker include/exclusion")
-        if self.args.num_nodes != -1 or self.args.num_gpus != -1:
-            raise ValueError(f"{self.name} backend does not support limiting num nodes/gpus")
-
     def get_cmd(self, environment, active_resources):
-        devices_per_node = self.resource_pool.values()
-        total_process_count = sum(devices_per_node)
-        process_per_node = list(devices_per_node)[0]
-        if not all([n == process_per_node for n in devices_per_node]):
-            raise ValueError("Intel MPI requires same number of devices per node")
-        mpirun_cmd = ["mpirun", "-ppn", f"{process_per_node}"] + split(self.args.launcher_args)
-        export_cmd = []
+        per_node, total = self._uniform_ranks_per_node("Intel MPI")
+        mpirun = ["mpirun", "-ppn", f"{per_node}"] + split(self.args.launcher_args)
         for k, v in self.exports.items():
-            export_cmd += ["-genv", f"{k}", f"{v}"]
+            mpirun += ["-genv", f"{k}", f"{v}"]
         if self.args.bind_cores_to_rank:
             from ..utils.numa import get_numactl_cmd
-            cores_per_rank, _ = get_numactl_cmd(self.args.bind_core_list, process_per_node, 0)
-            export_cmd += ["-genv", "OMP_NUM_THREADS", str(cores_per_rank)]
-        export_cmd += ["-genv", "MASTER_ADDR", str(self.args.master_addr)]
-        export_cmd += ["-genv", "MASTER_PORT", str(self.args.master_port)]
-        export_cmd += ["-genv", "WORLD_SIZE", str(total_process_count)]
-        export_cmd += ["-genv", "LOCAL_SIZE", str(process_per_node)]
-        export_cmd += ["-genv", "I_MPI_PIN", "0"]
-        export_cmd += ["-hosts"]
-        hosts = ""
-        for i, host in enumerate(self.resource_pool.keys()):
-            hosts += f",{host}" if i else host
-        export_cmd += [hosts]
-        per_host_cmd = []
-        for i in range(total_process_count):
-            local_rank = i % process_per_node
-            python_exec = []
-            if not self.args.no_python:
-                python_exec += [sys.executable, "-u"]
-                if self.args.module:
-                    python_exec.append("-m")
-            env_mapping = ["-env", "RANK", str(i)]
-            env_mapping += ["-env", "LOCAL_RANK", str(local_rank)]
-            if i == 0:
-                per_host_cmd = ["-n", "1"] + env_mapping + python_exec + [self.user_script] + self.user_arguments
-            else:
-                per_host_cmd = per_host_cmd + [":", "-n", "1"] + env_mapping + python_exec + [self.user_script] + self.user_arguments
-        return mpirun_cmd + export_cmd + per_host_cmd, [], environment
+            cores_per_rank, _ = get_numactl_cmd(self.args.bind_core_list, per_node, 0)
+            mpirun += ["-genv", "OMP_NUM_THREADS", str(cores_per_rank)]
+        mpirun += self._rendezvous("-genv", total, per_node)
+        mpirun += ["-genv", "I_MPI_PIN", "0", "-hosts", ",".join(self.resource_pool.keys())]
+        # MPMD form: one `-n 1 -env RANK r -env LOCAL_RANK l <cmd>` block per rank, joined by ':'
+        blocks = []
+        for rank in range(total):
+            blocks.append(["-n", "1", "-env", "RANK", str(rank), "-env", "LOCAL_RANK", str(rank % per_node)] + self._python() + self._user_command())
+        argv = list(mpirun)
+        for i, b in enumerate(blocks):
+            argv += ([":"] if i else []) + b
+        return argv, [], environment
 
 
 class SlurmRunner(MultiNodeRunner):
-
-    def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
+    name = "slurm"
 
     def backend_exists(self):
         return shutil.which("sinfo")
 
-    @property
-    def name(self):
-        return "slurm"
-
     def get_cmd(self, environment, active_resources):
         assert not getattr(self.args, "detect_nvlink_pairs", False), "slurm backend does not support remapping visible devices"
-        total_process_count = sum(self.resource_pool.values())
-        srun_cmd = ["srun", "-n", f"{total_process_count}"] + split(self.args.launcher_args)
+        srun = ["srun", "-n", f"{sum(self.resource_pool.values())}"] + split(self.args.launcher_args)
         if getattr(self.args, "slurm_comment", ""):
-            srun_cmd += ["--comment", self.args.slurm_comment]
-        if self.args.include != "":
-            srun_cmd.append("--include")
-            srun_cmd.append(f"{self.args.include}")
-        if self.args.exclude != "":
-            srun_cmd.append("--exclude")
-            srun_cmd.append(f"{self.args.exclude}")
-        if self.args.num_nodes > 0:
-            srun_cmd.append("--nodes")
-            srun_cmd.append(f"{self.args.num_nodes}")
-        if self.args.num_gpus > 0:
-            srun_cmd.append("--gpus")
-            srun_cmd.append(f"{self.args.num_gpus}")
-        exports = "--export=ALL"
-        for key, val in self.exports.items():
-            exports += f",{key}={val}"
-        python_exec = [sys.executable, "-u"]
-        return srun_cmd + [exports] + python_exec + [self.user_script] + self.user_arguments, [], environment
+            srun += ["--comment", self.args.slurm_comment]
+        for flag, value, on in (("--include", self.args.include, self.args.include != ""), ("--exclude", self.args.exclude, self.args.exclude != ""),
+                                ("--nodes", self.args.num_nodes, self.args.num_nodes > 0), ("--gpus", self.args.num_gpus, self.args.num_gpus > 0)):
+            if on:
+                srun += [flag, f"{value}"]
+        exports = "--export=ALL" + "".join(f",{k}={v}" for k, v in self.exports.items())
+        return srun + [exports, sys.executable, "-u"] + self._user_command(), [], environment
 
 
 class MVAPICHRunner(MultiNodeRunner):
+    name = "mvapich"
+    supports_resource_filters = False
+    _DEFAULT_EXPORTS = {
+        "MV2_SMP_USE_CMA": "0",  # CMA is unavailable in most containers
+        "MV2_DEBUG_SHOW_BACKTRACE": "1",
+        "MV2_USE_CUDA": "1",  # CUDA-aware MPI
+        "MV2_SUPPORT_DL": "1",
+        "MV2_ENABLE_AFFINITY": "0",
+        "MV2_INTER_ALLGATHER_TUNING": "5",
+        "MV2_CUDA_USE_NAIVE": "0",
+    }
 
     def __init__(self, args, world_info_base64, resource_pool):
-        super().__init__(args, world_info_base64)
-        self.resource_pool = resource_pool
-        self.add_export("MV2_SMP_USE_CMA", "0")
-        self.add_export("MV2_DEBUG_SHOW_BACKTRACE", "1")
-        self.add_export("MV2_USE_CUDA", "1")
-        self.add_export("MV2_SUPPORT_DL", "1")
-        self.add_export("MV2_ENABLE_AFFINITY", "0")
-        self.add_export("MV2_INTER_ALLGATHER_TUNING", "5")
-        self.add_export("MV2_CUDA_USE_NAIVE", "0")
+        super().__init__(args, world_info_base64, resource_pool)
+        for k, v in self._DEFAULT_EXPORTS.items():
+            self.add_export(k, v)
 
     def backend_exists(self):
-        mpiname_exists = shutil.which("mpiname")
-        exists = False
-        if not mpiname_exists:
+        if not shutil.which("mpiname"):
             warnings.warn("mpiname does not exist, mvapich is not installed properly")
-        else:
-            results = subprocess.check_output("mpiname", shell=True)
-            mpiname_results = results.decode("utf-8").strip()
-            if "MVAPICH2-GDR" in mpiname_results:
-                exists = True
-            else:
-                warnings.warn(f"Expected MVAPICH2-GDR as return for mpiname but received {mpiname_results}")
-        return exists
-
-    @property
-    def name(self):
-        return "mvapich"
-
-    def validate_args(self):
-        super().validate_args()
-        if self.args.include != "" or self.args.exclude != "":
-            raise ValueError(f"{self.name} backend does not support worker include/exclusion")
-        if self.args.num_nodes != -1 or self.args.num_gpus != -1:
-            raise ValueError(f"{self.name} backend does not support limiting num nodes/gpus")
+            return False
+        found = subprocess.check_output("mpiname", shell=True).decode("utf-8").strip()
+        if "MVAPICH2-GDR" in found:
+            return True
+        warnings.warn(f"Expected MVAPICH2-GDR as return for mpiname but received {found}")
+        return False
 
     def get_cmd(self, environment, active_resources):
-        devices_per_node = self.resource_pool.values()
-        total_process_count = sum(devices_per_node)
-        process_per_node = list(devices_per_node)[0]
-        if not all([n == process_per_node for n in devices_per_node]):
-            raise ValueError("mvapich requires same number of devices per node")
+        per_node, total = self._uniform_ranks_per_node("mvapich")
         with open(MVAPICH_TMP_HOSTFILE, "w") as fd:
-            for host in self.resource_pool.keys():
-                fd.write(f"{host}\n")
-        mpirun_cmd = ["mpirun", "-np", f"{total_process_count}", "-ppn", f"{process_per_node}", "--hostfile", f"{MVAPICH_TMP_HOSTFILE}"] + \
-            split(self.args.launcher_args)
-        export_cmd = []
+            fd.writelines(f"{host}\n" for host in self.resource_pool.keys())
+        mpirun = ["mpirun", "-np", f"{total}", "-ppn", f"{per_node}", "--hostfile", f"{MVAPICH_TMP_HOSTFILE}"] + split(self.args.launcher_args)
         for k, v in self.exports.items():
-            export_cmd += ["-env", "{}={}".format(k, v)]
-        python_exec = []
-        if not self.args.no_python:
-            python_exec = [sys.executable, "-u"]
-            if self.args.module:
-                python_exec.append("-m")
-        return mpirun_cmd + export_cmd + python_exec + [self.user_script] + self.user_arguments, [], environment
+            mpirun += ["-env", f"{k}={v}"]
+        return mpirun + self._python() + self._user_command(), [], environment

@@ -276,8 +276,7 @@ def main(args=None):
                       MVAPICH_LAUNCHER: MVAPICHRunner, SLURM_LAUNCHER: SlurmRunner}.get(args.launcher)
         if runner_cls is None:
             raise NotImplementedError(f"Unknown launcher {args.launcher}")
-        runner = runner_cls(args, world_info_base64, resource_pool) if runner_cls in (MVAPICHRunner, OpenMPIRunner, MPICHRunner, IMPIRunner, SlurmRunner) \
-            else runner_cls(args, world_info_base64)
+        runner = runner_cls(args, world_info_base64, resource_pool)
         if not runner.backend_exists():
             raise RuntimeError(f"launcher '{args.launcher}' not installed.")
         curr_path = os.path.abspath(".")

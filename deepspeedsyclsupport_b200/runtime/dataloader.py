@@ -33,6 +33,13 @@ class DeepSpeedDataLoader:
         self.tput_timer = tput_timer
         self.batch_size = batch_size
         self.curriculum_learning_enabled = bool(deepspeed_dataloader_config.get("curriculum_learning_enabled", False))
+        if self.curriculum_learning_enabled:
+            # curriculum learning: a batch sampler that draws every global batch from the currently eligible data clusters
+            from .data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
+            c = deepspeed_dataloader_config
+            data_sampler = DeepSpeedDataSampler(c["data_efficiency_config"], len(dataset), batch_size, data_parallel_rank, data_parallel_world_size,
+                                                c.get("data_parallel_group"), c.get("gradient_accumulation_steps", 1), c.get("global_rank", 0),
+                                                drop_last=dataloader_drop_last)
         if local_rank >= 0:
             if data_sampler is None:
                 data_sampler = DistributedSampler(dataset=dataset, num_replicas=data_parallel_world_size, rank=data_parallel_rank)
@@ -69,8 +76,11 @@ class DeepSpeedDataLoader:
         return next(self.data)
 
     def _create_dataloader(self):
-        kw = dict(batch_size=self.batch_size, pin_memory=self.pin_memory, sampler=self.data_sampler,
-                  num_workers=self.num_local_io_workers, drop_last=self.dataloader_drop_last)
+        if self.curriculum_learning_enabled:
+            kw = dict(pin_memory=self.pin_memory, batch_sampler=self.data_sampler, num_workers=self.num_local_io_workers)
+        else:
+            kw = dict(batch_size=self.batch_size, pin_memory=self.pin_memory, sampler=self.data_sampler,
+                      num_workers=self.num_local_io_workers, drop_last=self.dataloader_drop_last)
         if self.collate_fn is not None:
             kw["collate_fn"] = self.collate_fn
         self.dataloader = DataLoader(self.dataset, **kw)

@@ -158,6 +158,15 @@ class DeepSpeedEngine(Module):
         if self.curriculum_enabled_legacy():
             from .data_pipeline.curriculum_scheduler import CurriculumScheduler
             self.curriculum_scheduler_legacy = CurriculumScheduler(self.curriculum_params_legacy())
+        self.random_ltd_scheduler = None
+        self.training_data_sampler = None
+        if self.random_ltd_enabled():
+            from .data_pipeline import constants as K
+            from .data_pipeline.data_routing.scheduler import RandomLTDScheduler
+            ltd = self.random_ltd_config()
+            ltd[K.RANDOM_LTD_GLOBAL_BATCH_SIZE] = self.train_batch_size()
+            ltd[K.RANDOM_LTD_MICRO_BATCH_SIZE] = self.train_micro_batch_size_per_gpu()
+            self.random_ltd_scheduler = RandomLTDScheduler(ltd)
         if self.eigenvalue_enabled():
             from .eigenvalue import Eigenvalue
             c = self._config
@@ -753,10 +762,52 @@ class DeepSpeedEngine(Module):
             dp_world, dp_rank = self.dp_world_size, groups._get_data_parallel_rank()
         if data_sampler is None and route in ("predict", "eval"):
             data_sampler = torch.utils.data.DistributedSampler(dataset, num_replicas=dp_world, rank=dp_rank, shuffle=False)
-        return DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory, collate_fn=collate_fn,
-                                   local_rank=self.local_rank, tput_timer=None, num_local_io_workers=num_local_io_workers,
-                                   data_sampler=data_sampler, data_parallel_world_size=dp_world, data_parallel_rank=dp_rank,
-                                   dataloader_drop_last=self.dataloader_drop_last())
+        loader_config = {}
+        if route == "train" and self.curriculum_learning_enabled():
+            loader_config = {"curriculum_learning_enabled": True, "data_efficiency_config": self._data_efficiency_for_sampler(),
+                             "data_parallel_group": self.seq_data_parallel_group, "gradient_accumulation_steps": self.gradient_accumulation_steps(),
+                             "global_rank": self.global_rank}
+        loader = DeepSpeedDataLoader(dataset=dataset, batch_size=batch_size, pin_memory=pin_memory, collate_fn=collate_fn,
+                                     local_rank=self.local_rank, tput_timer=None, num_local_io_workers=num_local_io_workers,
+                                     data_sampler=data_sampler, data_parallel_world_size=dp_world, data_parallel_rank=dp_rank,
+                                     dataloader_drop_last=self.dataloader_drop_last(), deepspeed_dataloader_config=loader_config)
+        if loader_config:
+            self.training_data_sampler = loader.data_sampler
+        return loader
+
+    def _data_efficiency_for_sampler(self):
+        """data_efficiency config in the key layout of data_pipeline/constants.py (what DeepSpeedDataSampler indexes)."""
+        import copy
+        cfg = copy.deepcopy(self._config.data_efficiency_config)
+        cfg.setdefault("seed", 1234)
+        return cfg
+
+    def set_custom_curriculum_learning_schedule(self, schedule_func_dict):
+        if getattr(self, "training_data_sampler", None) is not None:
+            self.training_data_sampler.set_custom_curriculum_learning_schedule(schedule_func_dict)
+
+    # ------------------------------------------------------------------ random-LTD (data routing)
+    def random_ltd_config(self):
+        return self._config.data_efficiency_config["data_routing"]["random_ltd"]
+
+    def random_ltd_initialize(self):
+        """Bind every RandomLayerTokenDrop wrapper (see data_routing.helper.convert_to_random_ltd) to the scheduler, in the
+        order given by `random_ltd_layer_id`.  Parity: engine.py:556-577 upstream."""
+        from collections import deque
+        from .data_pipeline import constants as K
+        from .data_pipeline.data_routing.basic_layer import RandomLayerTokenDrop
+        assert self.random_ltd_enabled()
+        cfg = self.random_ltd_config()
+        wanted = deque(sorted(cfg[K.RANDOM_LTD_LAYER_ID]))
+        count = 0
+        for name, layer in self.module.named_modules():
+            if isinstance(layer, RandomLayerTokenDrop):
+                if len(wanted) != 0 and str(wanted[0]) in name:
+                    layer.init_config(cfg, self.random_ltd_scheduler, count)
+                    wanted.popleft()
+                    count += 1
+        if cfg[K.RANDOM_LTD_LAYER_NUM] != count:
+            raise ValueError(f"random_ltd_layer_num {cfg[K.RANDOM_LTD_LAYER_NUM]} must be equivalent to the len of random_ltd_layer_id {count}")
 
     # ------------------------------------------------------------------ train / eval
     def train(self, mode=True):
@@ -796,6 +847,8 @@ class DeepSpeedEngine(Module):
                                  and self.global_rank == 0)
         if flops_profiler_active:
             self.flops_profiler.start_profile(ignore_list=None)
+        if self.module.training and self.random_ltd_scheduler is not None:
+            self.random_ltd_scheduler.update_seq(self.global_steps)
         if self.module.training:
             if self.progressive_layer_drop:
                 kwargs.update(self.progressive_layer_drop.get_state())
@@ -1157,7 +1210,10 @@ class DeepSpeedEngine(Module):
                      frozen_param_shapes=None, frozen_param_fragments=None,
                      shared_params=self._get_shared_params() if zero_optimizer_state else None,
                      lr_scheduler=self.lr_scheduler.state_dict() if self.lr_scheduler is not None else None,
-                     data_sampler=None, random_ltd=None, sparse_tensor_module_names=[],
+                     data_sampler=(self.training_data_sampler.state_dict() if getattr(self, "training_data_sampler", None) is not None and
+                                   hasattr(self.training_data_sampler, "state_dict") else None),
+                     random_ltd=self.random_ltd_scheduler.state_dict() if self.random_ltd_scheduler is not None else None,
+                     sparse_tensor_module_names=[],
                      skipped_steps=self.skipped_steps, global_steps=self.global_steps, global_samples=self.global_samples,
                      dp_world_size=self.seq_dp_world_size, mp_world_size=self.mp_world_size, ds_config=self._config._param_dict,
                      ds_version=__version__)
@@ -1255,6 +1311,10 @@ class DeepSpeedEngine(Module):
             self.global_steps = checkpoint.get("global_steps", 0)
             self.global_samples = checkpoint.get("global_samples", self.global_steps * self.train_batch_size())
             self.skipped_steps = checkpoint.get("skipped_steps", 0)
+            if self.random_ltd_scheduler is not None and checkpoint.get("random_ltd") is not None:
+                self.random_ltd_scheduler.load_state_dict(checkpoint["random_ltd"])
+            if getattr(self, "training_data_sampler", None) is not None and checkpoint.get("data_sampler") is not None:
+                self.training_data_sampler.load_state_dict(checkpoint["data_sampler"])
             deepspeed_states = ["module", "sparse_tensor_module_names", "skipped_steps", "global_steps", "dp_world_size",
                                 "mp_world_size", "data_sampler", "random_ltd"]
         client_state = {}

@@ -1,10 +1,19 @@
-"""PipelineModule: a model expressed as a flat list of layers, partitioned across pipeline stages.
-Parity: deepspeed/runtime/pipe/module.py:86-636 (LayerSpec/TiedLayerSpec, _partition_layers :370 with
-uniform / parameters / type:regex methods, tied-weight groups :423-496, per-layer checkpoint files :532-623)."""
+"""PipelineModule: a model given as a flat sequence of layers, cut into contiguous stage slices.
+
+Pieces (public API parity: deepspeed/runtime/pipe/module.py:86-636):
+  LayerSpec / TiedLayerSpec   deferred construction -- a stage only ever instantiates the layers it owns
+  stage assignment            `uniform` (layer count), `parameters` (trainable parameter count), `type:<regex>` (count of
+                              layers whose class name matches); a prefix-sum balanced split in all three cases
+  forward                     the stage's layers run in segments of `activation_checkpoint_interval` layers, each
+                              segment optionally under activation checkpointing
+  tied layers                 one module per tie key per stage; the stages sharing a key form a process group used to
+                              broadcast the initial weight and to all-reduce the weight gradient every step
+  checkpoints                 one file per layer (`layer_XX-model_YY-model_states.pt`), so a checkpoint can be reloaded
+                              under a different stage assignment
+"""
 import glob
 import os
-import re as regex
-from collections import defaultdict
+import re
 from functools import partial
 
 import torch
@@ -22,15 +31,15 @@ class PipelineError(Exception):
     """Errors related to the use of deepspeed.PipelineModule"""
 
 
-class LayerSpec:
-    """Deferred layer construction: the layer is only built on the stage that owns it."""
+class LayerSpec(object):
+    """Recipe for a layer: LayerSpec(nn.Linear, 16, 16) builds nn.Linear(16, 16) on the owning stage only."""
 
     def __init__(self, typename, *module_args, **module_kwargs):
+        if not issubclass(typename, nn.Module):
+            raise RuntimeError("LayerSpec only supports torch.nn.Module types.")
         self.typename = typename
         self.module_args = module_args
         self.module_kwargs = module_kwargs
-        if not issubclass(typename, nn.Module):
-            raise RuntimeError("LayerSpec only supports torch.nn.Module types.")
         self.global_rank = dist.get_rank() if dist.is_initialized() else -1
 
     def __repr__(self):
@@ -43,6 +52,7 @@ class LayerSpec:
 
 
 class TiedLayerSpec(LayerSpec):
+    """A LayerSpec whose `tied_weight_attr` parameter is shared by every layer with the same `key` (e.g. embeddings)."""
 
     def __init__(self, key, typename, *module_args, forward_fn=None, tied_weight_attr="weight", **module_kwargs):
         super().__init__(typename, *module_args, **module_kwargs)
@@ -51,261 +61,227 @@ class TiedLayerSpec(LayerSpec):
         self.tied_weight_attr = tied_weight_attr
 
 
+def _display_name(layer):
+    if isinstance(layer, LayerSpec):
+        return layer.typename.__name__
+    if isinstance(layer, nn.Module):
+        return type(layer).__name__
+    return getattr(layer, "__name__", None)
+
+
+def _trainable_numel(layer):
+    if isinstance(layer, LayerSpec):
+        layer = layer.build()
+    if isinstance(layer, nn.Module):
+        return sum(p.numel() for p in layer.parameters() if p.requires_grad)
+    return 0
+
+
+def _stage_boundaries(specs, method, num_stages):
+    """List of num_stages + 1 layer indices; stage s owns [parts[s], parts[s+1])."""
+    method = method.lower()
+    if method == "uniform":
+        return ds_utils.partition_uniform(num_items=len(specs), num_parts=num_stages)
+    if method == "parameters":
+        return ds_utils.partition_balanced(weights=[_trainable_numel(l) for l in specs], num_parts=num_stages)
+    if method.startswith("type:"):
+        pattern = re.compile(method.split(":", 1)[1], re.IGNORECASE)
+        hits = [1 if (_display_name(l) is not None and pattern.search(_display_name(l))) else 0 for l in specs]
+        if not any(hits):
+            raise RuntimeError(f"Partitioning '{method.split(':', 1)[1]}' found no valid layers to partition.")
+        return ds_utils.partition_balanced(weights=hits, num_parts=num_stages)
+    raise NotImplementedError(f"Partitioning method {method} not implemented.")
+
+
 class PipelineModule(nn.Module):
+    checkpoint_parallel_write_pipeline = False
 
     def __init__(self, layers, num_stages=None, topology=None, loss_fn=None, seed_layers=False, seed_fn=None, base_seed=1234,
-                 partition_method="parameters", activation_checkpoint_interval=0,
-                 activation_checkpoint_func=checkpointing.checkpoint, checkpointable_layers=None):
+                 partition_method="parameters", activation_checkpoint_interval=0, activation_checkpoint_func=checkpointing.checkpoint,
+                 checkpointable_layers=None):
         super().__init__()
         if num_stages is None and topology is None:
             raise RuntimeError("must provide num_stages or topology")
-        self.micro_offset = 0
-        self.loss_fn = loss_fn
-        self.checkpointable_layers = checkpointable_layers
         if checkpointable_layers is not None:
             assert isinstance(checkpointable_layers, list), "param `checkpointable_layers` must be type of list."
-        self.seed_layers = seed_layers
-        self.seed_fn = seed_fn
-        self.base_seed = base_seed
-        if dist.is_initialized() and dist.get_rank() == 0:
-            try:
-                seed_str = self.seed_fn.__name__
-            except AttributeError:
-                seed_str = None
-            print(f"SEED_LAYERS={self.seed_layers} BASE_SEED={self.base_seed} SEED_FN={seed_str}")
+        self.loss_fn = loss_fn
+        self.checkpointable_layers = checkpointable_layers
+        self.seed_layers, self.seed_fn, self.base_seed = seed_layers, seed_fn, base_seed
+        self.activation_checkpoint_interval = activation_checkpoint_interval
+        self.activation_checkpoint_func = activation_checkpoint_func
+        self.micro_offset = 0
+
         self.world_group = dist.new_group(ranks=range(dist.get_world_size()))
         self.global_rank = dist.get_rank(group=self.world_group)
         self.world_size = dist.get_world_size(group=self.world_group)
-        self.local_rank = int(os.environ.get("LOCAL_RANK", None) or 0)
-        if topology:
-            self._topo = topology
-            self.num_stages = self._topo.get_dim("pipe")
-        else:
-            self.num_stages = num_stages
-            if topology is None:
-                if self.world_size % self.num_stages != 0:
-                    raise RuntimeError(f"num_stages ({self.num_stages}) must divide distributed world size ({self.world_size})")
-                dp = self.world_size // num_stages
-                topology = PipeDataParallelTopology(num_pp=num_stages, num_dp=dp)
-                self._topo = topology
-        self._grid = PipelineParallelGrid(process_group=self.world_group, topology=self._topo)
-        self.stage_id = self._topo.get_coord(self.global_rank).pipe
+        self.local_rank = int(os.environ.get("LOCAL_RANK") or 0)
+        if topology is None:
+            if self.world_size % num_stages != 0:
+                raise RuntimeError(f"num_stages ({num_stages}) must divide distributed world size ({self.world_size})")
+            topology = PipeDataParallelTopology(num_pp=num_stages, num_dp=self.world_size // num_stages)
+        self._topo = topology
+        self.num_stages = topology.get_dim("pipe")
+        self._grid = PipelineParallelGrid(process_group=self.world_group, topology=topology)
+        self.stage_id = topology.get_coord(self.global_rank).pipe
+
         self._layer_specs = list(layers)
         self._num_layers = len(self._layer_specs)
-        self._local_start = 0
-        self._local_stop = None
         self._partition_layers(method=partition_method)
+
         self.forward_funcs = []
         self.fwd_map = {}
         self.tied_modules = nn.ModuleDict()
         self.tied_weight_attrs = {}
         self._build()
-        self.to(get_accelerator().device_name(self.local_rank) if get_accelerator().device_name() == "cuda" else "cpu")
+        on_gpu = get_accelerator().device_name() == "cuda"
+        self.to(get_accelerator().device_name(self.local_rank) if on_gpu else "cpu")
         self.tied_comms = self._index_tied_modules()
         self._synchronize_tied_weights()
-        self.activation_checkpoint_interval = activation_checkpoint_interval
-        self.activation_checkpoint_func = activation_checkpoint_func
+
+    # ------------------------------------------------------------------ construction
+    def _seed_for(self, value):
+        (self.seed_fn or ds_utils.set_random_seed)(value)
+
+    def _register_layer(self, layer_idx, module):
+        self.fwd_map[str(layer_idx)] = len(self.forward_funcs)
+        self.forward_funcs.append(module)
+        self.add_module(str(layer_idx), module)
 
     def _build(self):
-        specs = self._layer_specs
-        for local_idx, layer in enumerate(specs[self._local_start:self._local_stop]):
-            layer_idx = local_idx + self._local_start
+        for layer_idx in range(self._local_start, self._local_stop):
+            spec = self._layer_specs[layer_idx]
             if self.seed_layers:
-                if self.seed_fn:
-                    self.seed_fn(self.base_seed + layer_idx)
-                else:
-                    ds_utils.set_random_seed(self.base_seed + layer_idx)
-            if isinstance(layer, PipelineModule):
+                self._seed_for(self.base_seed + layer_idx)
+            if isinstance(spec, PipelineModule):
                 raise NotImplementedError("RECURSIVE BUILD NOT YET IMPLEMENTED")
-            elif isinstance(layer, nn.Module):
-                name = str(layer_idx)
-                self.forward_funcs.append(layer)
-                self.fwd_map.update({name: len(self.forward_funcs) - 1})
-                self.add_module(name, layer)
-            elif isinstance(layer, TiedLayerSpec):
-                if layer.key not in self.tied_modules:
-                    self.tied_modules[layer.key] = layer.build()
-                    self.tied_weight_attrs[layer.key] = layer.tied_weight_attr
-                if layer.forward_fn is None:
-                    self.forward_funcs.append(self.tied_modules[layer.key])
-                else:
-                    self.forward_funcs.append(partial(layer.forward_fn, self.tied_modules[layer.key]))
-            elif isinstance(layer, LayerSpec):
-                module = layer.build()
-                name = str(layer_idx)
-                self.forward_funcs.append(module)
-                self.fwd_map.update({name: len(self.forward_funcs) - 1})
-                self.add_module(name, module)
+            if isinstance(spec, TiedLayerSpec):
+                if spec.key not in self.tied_modules:
+                    self.tied_modules[spec.key] = spec.build()
+                    self.tied_weight_attrs[spec.key] = spec.tied_weight_attr
+                owner = self.tied_modules[spec.key]
+                self.forward_funcs.append(owner if spec.forward_fn is None else partial(spec.forward_fn, owner))
+            elif isinstance(spec, LayerSpec):
+                self._register_layer(layer_idx, spec.build())
+            elif isinstance(spec, nn.Module):
+                self._register_layer(layer_idx, spec)
             else:
-                self.forward_funcs.append(layer)
+                self.forward_funcs.append(spec)  # plain callable (reshape lambdas etc.)
         for p in self.parameters():
             p.ds_pipe_replicated = False
 
     def _count_layer_params(self):
-        param_counts = [0] * len(self._layer_specs)
-        for idx, layer in enumerate(self._layer_specs):
-            if isinstance(layer, LayerSpec):
-                l = layer.build()
-                params = filter(lambda p: p.requires_grad, l.parameters())
-                param_counts[idx] = sum(p.numel() for p in params)
-            elif isinstance(layer, nn.Module):
-                params = filter(lambda p: p.requires_grad, layer.parameters())
-                param_counts[idx] = sum(p.numel() for p in params)
-        return param_counts
+        return [_trainable_numel(l) for l in self._layer_specs]
 
     def _find_layer_type(self, layername):
-        idxs = []
-        typeregex = regex.compile(layername, regex.IGNORECASE)
-        for idx, layer in enumerate(self._layer_specs):
-            name = None
-            if isinstance(layer, LayerSpec):
-                name = layer.typename.__name__
-            elif isinstance(layer, nn.Module):
-                name = layer.__class__.__name__
-            else:
-                try:
-                    name = layer.__name__
-                except AttributeError:
-                    continue
-            if typeregex.search(name):
-                idxs.append(idx)
-        if len(idxs) == 0:
+        pattern = re.compile(layername, re.IGNORECASE)
+        idxs = [i for i, l in enumerate(self._layer_specs) if _display_name(l) is not None and pattern.search(_display_name(l))]
+        if not idxs:
             raise RuntimeError(f"Partitioning '{layername}' found no valid layers to partition.")
         return idxs
 
-    def forward(self, forward_input):
-        self.micro_offset += 1
-
-        def exec_range_func(start, end):
-            local_micro_offset = self.micro_offset + 1
-
-            def exec_func(*inputs):
-                if len(inputs) == 1:
-                    inputs = inputs[0]
-                for idx, layer in enumerate(self.forward_funcs[start:end]):
-                    self.curr_layer = idx + self._local_start
-                    if self.seed_layers:
-                        new_seed = (self.base_seed * local_micro_offset) + self.curr_layer
-                        if self.seed_fn:
-                            self.seed_fn(new_seed)
-                        else:
-                            ds_utils.set_random_seed(new_seed)
-                    inputs = layer(inputs)
-                return inputs
-
-            return exec_func
-
-        if self.activation_checkpoint_interval == 0:
-            func = exec_range_func(0, len(self.forward_funcs))
-            x = func(forward_input)
-        else:
-            num_layers = len(self.forward_funcs)
-            x = forward_input
-            for start_idx in range(0, num_layers, self.activation_checkpoint_interval):
-                end_idx = min(start_idx + self.activation_checkpoint_interval, num_layers)
-                funcs = self.forward_funcs[start_idx:end_idx]
-                if not isinstance(x, tuple):
-                    x = (x, )
-                if self._is_checkpointable(funcs):
-                    x = self.activation_checkpoint_func(exec_range_func(start_idx, end_idx), *x)
-                else:
-                    x = exec_range_func(start_idx, end_idx)(*x)
-        return x
-
     def _partition_layers(self, method="uniform"):
         num_stages = self._topo.get_dim("pipe")
-        stage_id = self._topo.get_coord(self.global_rank).pipe
         if self.global_rank == 0:
             logger.info(f"Partitioning pipeline stages with method {method}")
-        method = method.lower()
-        if method == "uniform":
-            num_layers = len(self._layer_specs)
-            self.parts = ds_utils.partition_uniform(num_items=num_layers, num_parts=num_stages)
-        elif method == "parameters":
-            param_counts = self._count_layer_params()
-            self.parts = ds_utils.partition_balanced(weights=param_counts, num_parts=num_stages)
-        elif method.startswith("type:"):
-            layertype = method.split(":")[1]
-            binary_weights = [0] * len(self._layer_specs)
-            for idx in self._find_layer_type(layertype):
-                binary_weights[idx] = 1
-            self.parts = ds_utils.partition_balanced(weights=binary_weights, num_parts=num_stages)
-        elif method == "profile":
-            raise NotImplementedError(f"Partitioning method {method} not implemented.")
-        else:
-            raise NotImplementedError(f"Partitioning method {method} not implemented.")
+        self.parts = _stage_boundaries(self._layer_specs, method, num_stages)
         if self.global_rank == 0:
             for stage in range(num_stages):
-                start, stop = self.parts[stage], self.parts[stage + 1]
-                print(f"stage={stage} layers={stop - start}")
-                for idx, layer in enumerate(self._layer_specs[start:stop]):
-                    name = str(layer)
-                    if isinstance(layer, LayerSpec):
-                        name = layer.typename.__name__
-                    if isinstance(layer, nn.Module):
-                        name = layer.__class__.__name__
-                    else:
-                        try:
-                            name = layer.__name__
-                        except AttributeError:
-                            pass
-                    print(f"    {idx + start:2d}: {name}")
+                lo, hi = self.parts[stage], self.parts[stage + 1]
+                print(f"stage={stage} layers={hi - lo}")
+                for idx in range(lo, hi):
+                    print(f"    {idx:2d}: {_display_name(self._layer_specs[idx]) or str(self._layer_specs[idx])}")
             if self.loss_fn:
-                try:
-                    print(f"  loss: {self.loss_fn.__name__}")
-                except AttributeError:
-                    print(f"  loss: {self.loss_fn.__class__.__name__}")
-        self._set_bounds(start=self.parts[stage_id], stop=self.parts[stage_id + 1])
+                print(f"  loss: {getattr(self.loss_fn, '__name__', type(self.loss_fn).__name__)}")
+        self._set_bounds(start=self.parts[self.stage_id], stop=self.parts[self.stage_id + 1])
+
+    def _set_bounds(self, start=None, stop=None):
+        self._local_start, self._local_stop = start, stop
+
+    # ------------------------------------------------------------------ forward
+    def _segment_fn(self, start, end):
+        """Callable running forward_funcs[start:end]; reseeds per layer when seed_layers is on (so recomputation under
+        activation checkpointing sees the same dropout masks)."""
+        micro = self.micro_offset + 1
+
+        def run(*inputs):
+            x = inputs[0] if len(inputs) == 1 else inputs
+            for k in range(start, end):
+                self.curr_layer = k + self._local_start
+                if self.seed_layers:
+                    self._seed_for(self.base_seed * micro + self.curr_layer)
+                x = self.forward_funcs[k](x)
+            return x
+
+        return run
+
+    def forward(self, forward_input):
+        self.micro_offset += 1
+        n = len(self.forward_funcs)
+        interval = self.activation_checkpoint_interval
+        if interval == 0:
+            return self._segment_fn(0, n)(forward_input)
+        x = forward_input
+        for start in range(0, n, interval):
+            end = min(start + interval, n)
+            args = x if isinstance(x, tuple) else (x, )
+            seg = self._segment_fn(start, end)
+            x = self.activation_checkpoint_func(seg, *args) if self._is_checkpointable(self.forward_funcs[start:end]) else seg(*args)
+        return x
+
+    def _is_checkpointable(self, funcs):
+        if type(self).__name__ in ("GPTModelPipe", "GPT2ModelPipe"):  # Megatron convention: only the transformer blocks
+            return all("ParallelTransformerLayerPipe" in type(f).__name__ for f in funcs)
+        if self.checkpointable_layers is not None:
+            return all(type(f).__name__ in self.checkpointable_layers for f in funcs)
+        return any(isinstance(f, nn.Module) and next(f.parameters(), None) is not None for f in funcs)
+
+    # ------------------------------------------------------------------ tied weights
+    def _index_tied_modules(self):
+        """{key: {ranks, group, weight_attr, module}} for the tie groups this rank belongs to.  Group creation is
+        collective, so every rank creates every group (same order) and keeps its own."""
+        comms = {}
+        if self._topo.get_dim("pipe") == 1:
+            return comms
+        keys = []
+        for s in self._layer_specs:
+            if isinstance(s, TiedLayerSpec) and s.key not in keys:
+                keys.append(s.key)
+        slices = self._grid.get_slice_parallel_world_size()
+        for key in keys:
+            stages = sorted({self.stage_owner(i) for i, s in enumerate(self._layer_specs) if isinstance(s, TiedLayerSpec) and s.key == key})
+            for dp in range(self._grid.data_parallel_size):
+                for mp in range(slices):
+                    extra = {"model": mp} if slices > 1 else {}
+                    ranks = [self._grid.stage_to_global(stage_id=s, data=dp, **extra) for s in stages]
+                    group = dist.new_group(ranks=ranks)
+                    if self.global_rank not in ranks:
+                        continue
+                    assert key in self.tied_modules
+                    comms[key] = {"ranks": ranks, "group": group, "weight_attr": self.tied_weight_attrs[key], "module": self.tied_modules[key]}
+                    if self.global_rank != ranks[0]:
+                        # only the first owner counts the tied parameters (norms, checkpoints)
+                        for p in self.tied_modules[key].parameters():
+                            p.ds_pipe_replicated = True
+        return comms
+
+    def _tied_weight(self, key):
+        return getattr(self.tied_modules[key], self.tied_comms[key]["weight_attr"])
+
+    def _synchronize_tied_weights(self):
+        for key, comm in self.tied_comms.items():
+            dist.broadcast(self._tied_weight(key).data, src=min(comm["ranks"]), group=comm["group"])
 
     def allreduce_tied_weight_gradients(self):
         for key, comm in self.tied_comms.items():
-            weight = getattr(self.tied_modules[key], comm["weight_attr"])
-            grad = weight.grad if weight.grad is not None else getattr(weight, "ds_tied_grad", None)
+            w = self._tied_weight(key)
+            grad = w.grad if w.grad is not None else getattr(w, "ds_tied_grad", None)
             if grad is not None:
                 dist.all_reduce(grad, group=comm["group"])
 
     def get_tied_weights_and_groups(self):
-        out = []
-        for key, comm in self.tied_comms.items():
-            weight = getattr(self.tied_modules[key], comm["weight_attr"])
-            out.append((weight, comm["group"]))
-        return out
+        return [(self._tied_weight(key), comm["group"]) for key, comm in self.tied_comms.items()]
 
-    def _synchronize_tied_weights(self):
-        for key, comm in self.tied_comms.items():
-            dist.broadcast(getattr(comm["module"], comm["weight_attr"]).data, src=min(comm["ranks"]), group=comm["group"])
-
-    def _index_tied_modules(self):
-        tied_comms = {}
-        if self._topo.get_dim("pipe") == 1:
-            return tied_comms
-        specs = self._layer_specs
-        tie_keys = set(s.key for s in specs if isinstance(s, TiedLayerSpec))
-        for key in tie_keys:
-            tied_layers = []
-            for idx, layer in enumerate(specs):
-                if isinstance(layer, TiedLayerSpec) and layer.key == key:
-                    tied_layers.append(idx)
-            tied_stages = set(self.stage_owner(idx) for idx in tied_layers)
-            for dp in range(self._grid.data_parallel_size):
-                for mp in range(self._grid.get_slice_parallel_world_size()):
-                    tied_ranks = []
-                    for s in sorted(tied_stages):
-                        if self._grid.get_slice_parallel_world_size() > 1:
-                            tied_ranks.append(self._grid.stage_to_global(stage_id=s, data=dp, model=mp))
-                        else:
-                            tied_ranks.append(self._grid.stage_to_global(stage_id=s, data=dp))
-                    group = dist.new_group(ranks=tied_ranks)
-                    if self.global_rank in tied_ranks:
-                        assert key in self.tied_modules
-                        if key in self.tied_modules:
-                            tied_comms[key] = {"ranks": tied_ranks, "group": group, "weight_attr": self.tied_weight_attrs[key],
-                                               "module": self.tied_modules[key]}
-                            if self.global_rank != tied_ranks[0]:
-                                for p in self.tied_modules[key].parameters():
-                                    p.ds_pipe_replicated = True
-        return tied_comms
-
+    # ------------------------------------------------------------------ introspection
     def partitions(self):
         return self.parts
 
@@ -315,10 +291,6 @@ class PipelineModule(nn.Module):
             if self.parts[stage] <= layer_idx < self.parts[stage + 1]:
                 return stage
         raise RuntimeError(f"Layer {layer_idx} not owned? parts={self.parts}")
-
-    def _set_bounds(self, start=None, stop=None):
-        self._local_start = start
-        self._local_stop = stop
 
     def set_checkpoint_interval(self, interval):
         assert interval >= 0
@@ -333,72 +305,47 @@ class PipelineModule(nn.Module):
     def num_pipeline_stages(self):
         return self._topo.get_dim("pipe")
 
+    # ------------------------------------------------------------------ per-layer checkpoint files
     def ckpt_prefix(self, checkpoints_path, tag):
-        rank_name = "module"
-        omit_dims = frozenset(["data"])
-        axes = [a for a in self._grid._topo.get_axis_names() if a not in omit_dims]
-        for dim in axes:
-            rank = getattr(self._grid._topo.get_coord(rank=self.global_rank), dim)
-            rank_name += f"-{dim}_{rank:02d}"
-        return os.path.join(checkpoints_path, str(tag), rank_name)
+        coord = self._topo.get_coord(rank=self.global_rank)
+        tags = [f"{axis}_{getattr(coord, axis):02d}" for axis in self._topo.get_axis_names() if axis != "data"]
+        return os.path.join(checkpoints_path, str(tag), "-".join(["module"] + tags))
 
     def ckpt_layer_path(self, ckpt_dir, local_layer_idx):
-        idx = local_layer_idx + self._local_start
-        layer_ckpt_path = os.path.join(ckpt_dir, f"layer_{idx:02d}")
-        rank_repr = self._grid._topo.get_rank_repr(rank=self.global_rank)
-        if rank_repr != "":
-            layer_ckpt_path += f"-{rank_repr}"
-        layer_ckpt_path += "-model_states.pt"
-        return layer_ckpt_path
+        stem = f"layer_{local_layer_idx + self._local_start:02d}"
+        rank_repr = self._topo.get_rank_repr(rank=self.global_rank)
+        if rank_repr:
+            stem += f"-{rank_repr}"
+        return os.path.join(ckpt_dir, stem + "-model_states.pt")
 
     def ckpt_layer_path_list(self, ckpt_dir, local_layer_idx):
-        idx = local_layer_idx + self._local_start
-        layer_ckpt_path = os.path.join(ckpt_dir, f"layer_{idx:02d}-")
-        layer_ckpt_path += "*model_states.pt"
-        ckpt_files = glob.glob(layer_ckpt_path)
-        ckpt_files.sort()
-        return ckpt_files
+        return sorted(glob.glob(os.path.join(ckpt_dir, f"layer_{local_layer_idx + self._local_start:02d}-*model_states.pt")))
 
     def save_state_dict(self, save_dir, checkpoint_engine, exclude_frozen_params=False):
-        dp_rank = self._grid.data_parallel_id
-        dp_size = self._grid.data_parallel_size
-        num_layers = len(self.forward_funcs)
+        dp_rank, dp_size = self._grid.data_parallel_id, self._grid.data_parallel_size
+        n = len(self.forward_funcs)
         if self.checkpoint_parallel_write_pipeline:
-            offsets = ds_utils.partition_uniform(num_layers, dp_size)
-            start, end = offsets[dp_rank], offsets[dp_rank + 1]
+            bounds = ds_utils.partition_uniform(n, dp_size)  # spread the layer files over the data-parallel replicas
+            todo = range(bounds[dp_rank], bounds[dp_rank + 1])
+        elif dp_rank == 0:
+            todo = range(n)
         else:
-            if dp_rank != 0:
-                return
-            start, end = 0, num_layers
-        layer_list = self.forward_funcs[start:end]
+            return
         checkpoint_engine.makedirs(save_dir, exist_ok=True)
-        for idx, layer in enumerate(layer_list):
-            model_ckpt_path = self.ckpt_layer_path(save_dir, start + idx)
+        for k in todo:
+            layer = self.forward_funcs[k]
             if not hasattr(layer, "state_dict"):
                 continue
-            orig_state_dict = layer.state_dict()
-            final_state_dict = type(orig_state_dict)({k: v.clone() for k, v in orig_state_dict.items()})
-            checkpoint_engine.save(final_state_dict, model_ckpt_path)
-
-    checkpoint_parallel_write_pipeline = False
+            sd = layer.state_dict()
+            # clone: torch.save would otherwise serialise the whole flat storage a parameter view lives in
+            checkpoint_engine.save(type(sd)((name, t.clone()) for name, t in sd.items()), self.ckpt_layer_path(save_dir, k))
 
     def load_state_dir(self, load_dir, checkpoint_engine, strict=True):
-        for idx, layer in enumerate(self.forward_funcs):
+        mp_rank = self._grid.get_slice_parallel_rank()
+        for k, layer in enumerate(self.forward_funcs):
             if not hasattr(layer, "load_state_dict"):
                 continue
-            model_ckpt_list = self.ckpt_layer_path_list(load_dir, idx)
-            mp_rank = self._grid.get_slice_parallel_rank()
-            mp_world_size = self._grid.get_slice_parallel_world_size()
-            assert len(model_ckpt_list) >= 1, f"no checkpoint files for layer {idx + self._local_start} in {load_dir}"
-            path = model_ckpt_list[min(mp_rank, len(model_ckpt_list) - 1)]
-            sd = checkpoint_engine.load(path, map_location="cpu")
-            layer.load_state_dict(sd, strict=strict)
+            files = self.ckpt_layer_path_list(load_dir, k)
+            assert len(files) >= 1, f"no checkpoint files for layer {k + self._local_start} in {load_dir}"
+            layer.load_state_dict(checkpoint_engine.load(files[min(mp_rank, len(files) - 1)], map_location="cpu"), strict=strict)
         self._synchronize_tied_weights()
-
-    def _is_checkpointable(self, funcs):
-        if self.__class__.__name__ in ("GPTModelPipe", "GPT2ModelPipe"):
-            return all("ParallelTransformerLayerPipe" in f.__class__.__name__ for f in funcs)
-        if self.checkpointable_layers is not None:
-            return all(f.__class__.__name__ in self.checkpointable_layers for f in funcs)
-        params = [f.parameters() for f in funcs if isinstance(f, torch.nn.Module)]
-        return any(len(list(p)) > 0 for p in params)

@@ -1,35 +1,28 @@
-"""Progressive layer dropping schedule: theta(t) = (1 - theta) * exp(-gamma * t) + theta.
-Parity: deepspeed/runtime/progressive_layer_drop.py:10-40."""
-import numpy as np
+"""Progressive layer dropping (PLD, arXiv:2010.13369): the keep probability of the transformer layers decays from 1 to
+`theta` as  theta_t = (1 - theta) * exp(-gamma * t) + theta.  The engine calls update_state() once per optimizer step and
+merges get_state() into the forward kwargs (`progressive_layer_drop`, `pld_theta`).
+(reference: deepspeed/runtime/progressive_layer_drop.py)"""
+import math
 
 from ..utils.logging import log_dist
 
 
 class ProgressiveLayerDrop(object):
-    r"""Progressive Layer Dropping (PLD) for model training (https://arxiv.org/pdf/2010.13369.pdf).
-
-    Args:
-        theta (float): a hyper-parameter that controls the trade-off between training time and robustness (lower = faster).
-        gamma (float): a hyper-parameter that controls how fast the drop ratio increases.
-    """
 
     def __init__(self, theta=0.5, gamma=0.001):
-        super().__init__()
-        self.theta = theta
-        self.gamma = gamma
+        self.theta = float(theta)
+        self.gamma = float(gamma)
         self.current_theta = 1.0
         log_dist(f"Enabled progressive layer dropping (theta = {self.theta})", ranks=[0])
 
-    def get_state(self):
-        kwargs = {"progressive_layer_drop": True, "pld_theta": self.get_theta()}
-        return kwargs
+    def keep_probability(self, global_step):
+        return (1.0 - self.theta) * math.exp(-self.gamma * global_step) + self.theta
+
+    def update_state(self, global_step):
+        self.current_theta = self.keep_probability(global_step)
 
     def get_theta(self):
         return self.current_theta
 
-    def update_state(self, global_step):
-
-        def _prob(x, gamma, p):
-            return (1. - p) * np.exp(-gamma * x) + p
-
-        self.current_theta = _prob(global_step, self.gamma, self.theta)
+    def get_state(self):
+        return {"progressive_layer_drop": True, "pld_theta": self.current_theta}
