@@ -1,0 +1,2 @@
+from .compress import init_compression, redundancy_clean
+from .helper import convert_conv1d_to_linear

@@ -135,9 +135,9 @@ class MoEZeroOptimizer:
     def backward(self, loss, retain_graph=False):
         self.dense.backward(loss, retain_graph=retain_graph)
 
-    def end_micro_step(self, boundary):
+    def end_micro_step(self, boundary, local_only=False):
         for o in self._all():
-            o.end_micro_step(boundary)
+            o.end_micro_step(boundary, local_only=local_only)
 
     def zero_grad(self, set_to_none=True):
         for o in self._all():
