@@ -1,0 +1,31 @@
+"""Checkpoint file-name helpers and safe tensor cloning (parity: deepspeed/checkpoint/utils.py)."""
+import os
+
+import torch
+
+from .constants import BF16_ZERO_FILE_PREFIX, MODEL_FILE_PREFIX, MODEL_FILE_SUFFIX, OPTIM_FILE_SUFFIX, ZERO_FILE_PREFIX
+
+
+def get_model_ckpt_name_for_rank(base_folder, mp_rank_str):
+    return os.path.join(base_folder, MODEL_FILE_PREFIX + mp_rank_str + MODEL_FILE_SUFFIX)
+
+
+def get_zero_ckpt_name_for_rank(base_folder, dp_rank, mp_rank):
+    return os.path.join(base_folder, f"{ZERO_FILE_PREFIX}{dp_rank}_{MODEL_FILE_PREFIX}{mp_rank:02d}{OPTIM_FILE_SUFFIX}")
+
+
+def get_layer_ckpt_name_for_rank(base_folder, layer_id, tp_rank):
+    return os.path.join(base_folder, f"{layer_id}-model_{tp_rank:02d}{MODEL_FILE_SUFFIX}")
+
+
+def clone_tensors_for_torch_save(item, device=torch.device("cpu")):
+    """Deep copy of a (nested) container where every tensor is an independent clone on `device`.  torch.save writes the
+    whole underlying storage of a view, so saving slices of a big flat buffer without this would serialise the buffer
+    once per slice."""
+    if torch.is_tensor(item):
+        return item.detach().clone().to(device)
+    if isinstance(item, (list, tuple)):
+        return type(item)(clone_tensors_for_torch_save(v, device) for v in item)
+    if isinstance(item, dict):
+        return type(item)({k: clone_tensors_for_torch_save(v, device) for k, v in item.items()})
+    return item

@@ -66,3 +66,67 @@ def _ckpt_body(stage, tmp):
 def test_checkpoint_roundtrip_two_ranks(stage, tmp_path_factory):
     tmp = str(tmp_path_factory.mktemp(f"ckpt{stage}"))
     run_distributed(_ckpt_body, world_size=2, args=(stage, tmp))
+
+
+def _universal_save_body(tmp):
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.utils.tensor_fragment import safe_get_full_fp32_param, safe_get_full_optimizer_state
+    rank = dist.get_rank()
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}}, "zero_optimization": {"stage": 2}}
+    torch.manual_seed(1)
+    model = SimpleModel()
+    engine, _, _, _ = deepspeed.initialize(model=model, config=cfg)
+    for x, y in random_batches(3, 4, 32, seed=10 + rank):
+        engine.backward(engine(x, y))
+        engine.step()
+    engine.save_checkpoint(tmp)
+    if rank == 0:
+        ref = {n: (safe_get_full_fp32_param(p).clone(), safe_get_full_optimizer_state(p, "exp_avg_sq").clone()) for n, p in model.named_parameters()}
+        torch.save(ref, os.path.join(tmp, "expected.pt"))
+    else:
+        for n, p in model.named_parameters():
+            safe_get_full_fp32_param(p), safe_get_full_optimizer_state(p, "exp_avg_sq")  # collective on every rank
+
+
+def _universal_load_body(tmp, stage):
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.utils.tensor_fragment import safe_get_full_fp32_param, safe_get_full_optimizer_state
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+           "zero_optimization": {"stage": stage, "stage3_param_persistence_threshold": 0}, "checkpoint": {"load_universal": True}}
+    torch.manual_seed(5)
+    model = SimpleModel()
+    engine, _, _, _ = deepspeed.initialize(model=model, config=cfg)
+    path, _ = engine.load_checkpoint(tmp)
+    assert path is not None and engine.global_steps == 3
+    ref = torch.load(os.path.join(tmp, "expected.pt"), weights_only=False)
+    for n, p in model.named_parameters():
+        w, v = safe_get_full_fp32_param(p), safe_get_full_optimizer_state(p, "exp_avg_sq")
+        assert torch.allclose(w, ref[n][0], atol=1e-6), n
+        assert torch.allclose(v, ref[n][1], atol=1e-6), n
+    assert engine.optimizer._step_count == 3
+    x, y = random_batches(1, 4, 32, seed=3)[0]
+    engine.backward(engine(x, y))
+    engine.step()
+
+
+def test_universal_checkpoint_reshapes_world_and_stage(tmp_path):
+    """save at dp=2 / stage 2 -> ds_to_universal -> load at dp=1 / stage 3 and at dp=2 / stage 1."""
+    from deepspeedsyclsupport_b200.checkpoint.ds_to_universal import main as to_universal
+    tmp = str(tmp_path)
+    run_distributed(_universal_save_body, world_size=2, args=(tmp, ))
+    to_universal(["--input_folder", os.path.join(tmp, "global_step3"), "--output_folder", os.path.join(tmp, "global_step3_universal")])
+    assert open(os.path.join(tmp, "latest_universal")).read() == "global_step3_universal"
+    assert os.path.isfile(os.path.join(tmp, "global_step3_universal", "zero", "head.weight", "exp_avg.pt"))
+    run_distributed(_universal_load_body, world_size=1, args=(tmp, 3))
+    run_distributed(_universal_load_body, world_size=2, args=(tmp, 1))
+
+
+def test_reshape_maps():
+    from deepspeedsyclsupport_b200.checkpoint import model_3d_desc, reshape_meg_2d_parallel
+    m = reshape_meg_2d_parallel(old_pp_degree=2, old_tp_degree=4, new_pp_degree=1, new_tp_degree=2)
+    assert m.get_data(0, 0) == [0, 1, 4, 5] and m.get_data(0, 1) == [2, 3, 6, 7]
+    maps = model_3d_desc(pp_degree=2, tp_degree=2, dp_degree=4).reshape(model_3d_desc(pp_degree=2, tp_degree=1, dp_degree=2))
+    assert len(maps) == 2 and maps[0].get_data(0, 0) == [0, 1, 4, 5] and maps[1].get_data(1, 0) == [10, 11, 14, 15]
+    ok, err = model_3d_desc(1, 1, 1).can_reshape(model_3d_desc(2, 1, 1))
+    assert not ok and "Expansion" in err[0]
