@@ -858,6 +858,9 @@ class DeepSpeedEngine(Module):
                     kwargs.update({"curriculum_seqlen": self.curriculum_scheduler_legacy.get_current_difficulty()})
         if self.training_dataloader is None:
             self.tput_timer.start()
+        profile_model_info = self.autotuning_profile_model_info()
+        if profile_model_info:
+            mem_before = get_accelerator().memory_allocated() if get_accelerator().is_available() else 0
         self._start_timers(self.engine_timers.forward_timers)
         if self.fp16_auto_cast():
             inputs = tuple(t.half() if torch.is_tensor(t) and t.is_floating_point() else t for t in inputs)
@@ -865,6 +868,9 @@ class DeepSpeedEngine(Module):
         self._stop_timers(self.engine_timers.forward_timers)
         if flops_profiler_active:
             self.flops_profiler.stop_profile()
+        if profile_model_info:
+            mem_after = get_accelerator().memory_allocated() if get_accelerator().is_available() else 0
+            self._autotuning_write_model_info(mem_after - mem_before)
         return loss
 
     def allreduce_gradients(self, bucket_size=MEMORY_OPT_ALLREDUCE_SIZE, local_only=False):
@@ -891,6 +897,54 @@ class DeepSpeedEngine(Module):
         if release_loss:
             pass
         return loss
+
+    # ------------------------------------------------------------------ autotuning experiment protocol
+    def _autotuning_tick(self):
+        """An autotuning experiment runs the user script with `autotuning.enabled`: steps [start_profile_step,
+        end_profile_step] are timed (device-synchronised wall clock around whole steps), the metrics are written to
+        `metric_path` and the process exits (engine.py:2204-2260 upstream)."""
+        import time
+        acc = get_accelerator()
+        if self.global_steps == self.autotuning_start_profile_step():
+            if acc.is_available():
+                acc.synchronize()
+            self._autotuning_t0 = time.perf_counter()
+        elif self.global_steps == self.autotuning_end_profile_step() + 1 and getattr(self, "_autotuning_t0", None) is not None:
+            if acc.is_available():
+                acc.synchronize()
+            n = self.autotuning_end_profile_step() + 1 - self.autotuning_start_profile_step()
+            latency_ms = (time.perf_counter() - self._autotuning_t0) * 1e3 / max(n, 1)
+            if self.global_rank == 0:
+                import json
+                msg = {"latency": latency_ms, "throughput": self.train_batch_size() * 1e3 / latency_ms,
+                       "FLOPS_per_gpu": getattr(self, "_autotuning_flops", 0) * self.gradient_accumulation_steps() * 1e3 / latency_ms}
+                path = self.autotuning_metric_path()
+                os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+                with open(path, "w") as f:
+                    json.dump(msg, f)
+                log_dist(f"Wrote metrics to {path}, {os.path.abspath(path)}", ranks=[0])
+            if dist.is_initialized():
+                dist.barrier()
+            import sys
+            sys.exit(0)
+
+    def _autotuning_write_model_info(self, activation_mem):
+        import json
+        params = list(self.module.parameters())
+        info = {"num_params": sum(getattr(p, "ds_numel", p.numel()) for p in params) * self.mp_world_size,
+                "trainable_num_params": sum(getattr(p, "ds_numel", p.numel()) for p in params if p.requires_grad) * self.mp_world_size,
+                "hidden_size": (self._config.autotuning_config.model_info or {}).get("hidden_size"),
+                "num_layers": (self._config.autotuning_config.model_info or {}).get("num_layers"),
+                "activation_mem_per_gpu": activation_mem}
+        if self.global_rank == 0:
+            path = self.autotuning_model_info_path()
+            os.makedirs(os.path.dirname(os.path.abspath(path)), exist_ok=True)
+            with open(path, "w") as f:
+                json.dump(info, f)
+        if dist.is_initialized():
+            dist.barrier()
+        import sys
+        sys.exit(0)
 
     def clip_fp32_gradients(self):
         pass  # clipping is folded into the fused optimizer step (device-side coefficient)
@@ -933,11 +987,15 @@ class DeepSpeedEngine(Module):
         self.tput_timer.stop(global_step=self.is_gradient_accumulation_boundary(), report_speed=report_progress)
         self._stop_timers(self.engine_timers.step_timers)
         if self.flops_profiler is not None and self.flops_profiler.started and self.is_gradient_accumulation_boundary():
-            if self.global_rank == 0:
+            if self.autotuning_enabled():
+                self._autotuning_flops = self.flops_profiler.get_total_flops() * 3  # fwd + 2x for bwd
+            elif self.global_rank == 0:
                 self.flops_profiler.print_model_profile(profile_step=self.global_steps - 1, module_depth=self.flops_profiler_module_depth(),
                                                         top_modules=self.flops_profiler_top_modules(), detailed=self.flops_profiler_detailed(),
                                                         output_file=self.flops_profiler_output_file())
             self.flops_profiler.end_profile()
+        if self.autotuning_enabled() and self.is_gradient_accumulation_boundary():
+            self._autotuning_tick()
         if self.is_gradient_accumulation_boundary():
             if self.monitor.enabled and self.global_rank == 0:
                 events = [("Train/Samples/lr", self.get_lr()[0], self.global_samples)]
