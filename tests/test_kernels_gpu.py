@@ -412,3 +412,67 @@ def test_fastgen_engine_gpu_matches_dense():
     out = eng.put([1], [a[200:]])
     assert (out[0].float().cpu() - ref[299]).abs().max() < 0.06 * ref[299].abs().max() + 0.02
     assert out.dtype == torch.bfloat16 and out.is_cuda
+
+
+@pytest.mark.parametrize("n", [8 * 1024, 8 * 100_003])
+def test_onebit_compress_decompress(n):
+    """fused sign-pack + error feedback and the unpack kernels vs. the torch formulas (runtime/comm/compressed.py CPU path)."""
+    from deepspeedsyclsupport_b200.runtime.comm.compressed import onebit_compress, onebit_decompress
+    torch.manual_seed(0)
+    x = torch.randn(n, device=_dev())
+    err = torch.randn(n, device=_dev()) * 0.1
+    x_cpu, err_cpu = x.cpu().clone(), err.cpu().clone()
+    packed, scale = onebit_compress(x, err)
+    packed_ref, scale_ref = onebit_compress(x_cpu, err_cpu)
+    assert torch.equal(x.cpu(), x_cpu)  # input untouched
+    assert torch.allclose(scale.cpu(), scale_ref, rtol=1e-5)
+    assert (packed.cpu() != packed_ref).float().mean() < 1e-5  # ties at exactly 0 aside
+    assert torch.allclose(err.cpu(), err_cpu, atol=1e-4)
+    rows = 4
+    pk = torch.randint(0, 256, (rows, n // 8 // rows), dtype=torch.uint8, device=_dev())
+    sc = torch.rand(rows, device=_dev()) + 0.5
+    for mode in (0, 1):
+        got = onebit_decompress(pk, sc, mode)
+        want = onebit_decompress(pk.cpu(), sc.cpu(), mode)
+        assert torch.allclose(got.cpu(), want, atol=1e-6)
+
+
+@pytest.mark.parametrize("batch_first", [True, False])
+@pytest.mark.parametrize("dtype,hidden", [(torch.bfloat16, 4096), (torch.float32, 100), (torch.float16, 33)])
+def test_random_ltd_token_ops(batch_first, dtype, hidden):
+    from deepspeedsyclsupport_b200.ops.random_ltd import gpt_sample_tokens, token_gather, token_scatter_, token_sort_
+    torch.manual_seed(0)
+    B, S, R, L = 3, 257, 96, 2
+    idx, _ = gpt_sample_tokens(R, S, B, layers=L, device=_dev())
+    assert idx.dtype == torch.int32 and idx.shape == (L, B, R)
+    assert bool((idx[..., 1:] > idx[..., :-1]).all()) and int(idx.min()) >= 0 and int(idx.max()) < S
+    raw = torch.stack([torch.randperm(S, device=_dev())[:R] for _ in range(L * B)]).to(torch.int32).view(L, B, R).contiguous()
+    assert torch.equal(token_sort_(raw.clone(), S), raw.sort(dim=-1)[0])
+    x = torch.randn((B, S, hidden) if batch_first else (S, B, hidden), device=_dev()).to(dtype)
+    sel = idx[0]
+    got = token_gather(x, sel, batch_first)
+    want = token_gather(x.cpu(), sel.cpu(), batch_first)
+    assert torch.equal(got.cpu(), want)
+    part = torch.randn_like(got)
+    full = x.clone()
+    token_scatter_(full, part, sel, batch_first)
+    want_full = token_scatter_(x.cpu().clone(), part.cpu(), sel.cpu(), batch_first)
+    assert torch.equal(full.cpu(), want_full)
+
+
+def test_random_ltd_layer_autograd_gpu():
+    from deepspeedsyclsupport_b200.ops.random_ltd import GatherTokens, ScatterTokens, gpt_sample_tokens
+    torch.manual_seed(0)
+    B, S, R, H = 2, 64, 16, 128
+    idx, _ = gpt_sample_tokens(R, S, B, layers=1, device=_dev())
+    x = torch.randn(B, S, H, device=_dev(), requires_grad=True)
+    w = torch.randn(H, H, device=_dev(), requires_grad=True)
+    full, part = GatherTokens.apply(x, idx[0], True)
+    y = ScatterTokens.apply(full, part @ w, idx[0], True)
+    y.square().sum().backward()
+    xr = x.detach().clone().requires_grad_()
+    wr = w.detach().clone().requires_grad_()
+    ix = idx[0].long().unsqueeze(-1).expand(B, R, H)
+    yr = xr.scatter(1, ix, torch.gather(xr, 1, ix) @ wr)
+    yr.square().sum().backward()
+    assert torch.allclose(y, yr, atol=1e-5) and torch.allclose(x.grad, xr.grad, atol=1e-3) and torch.allclose(w.grad, wr.grad, atol=1e-2)
