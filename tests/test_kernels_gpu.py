@@ -476,3 +476,44 @@ def test_random_ltd_layer_autograd_gpu():
     yr = xr.scatter(1, ix, torch.gather(xr, 1, ix) @ wr)
     yr.square().sum().backward()
     assert torch.allclose(y, yr, atol=1e-5) and torch.allclose(x.grad, xr.grad, atol=1e-3) and torch.allclose(w.grad, wr.grad, atol=1e-2)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+def test_nhwc_bias_add_kernel(dtype):
+    from deepspeedsyclsupport_b200.ops.spatial import nhwc_bias_add, nhwc_bias_add_add, nhwc_bias_add_bias_add
+    torch.manual_seed(0)
+    x = torch.randn(2, 320, 17, 13, device=_dev(), dtype=dtype).contiguous(memory_format=torch.channels_last)
+    o = torch.randn_like(x).contiguous(memory_format=torch.channels_last)
+    b, ob = torch.randn(320, device=_dev(), dtype=dtype), torch.randn(320, device=_dev(), dtype=dtype)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    ref = x.float() + b.float().view(1, -1, 1, 1)
+    assert torch.allclose(nhwc_bias_add(x, b).float(), ref, atol=tol)
+    assert torch.allclose(nhwc_bias_add_add(x, b, o).float(), ref + o.float(), atol=tol)
+    got = nhwc_bias_add_bias_add(x, b, o, ob)
+    assert got.is_contiguous(memory_format=torch.channels_last)
+    assert torch.allclose(got.float(), ref + o.float() + ob.float().view(1, -1, 1, 1), atol=2 * tol)
+
+
+def test_transformer_layer_bf16_gpu():
+    """DeepSpeedTransformerLayer on the tcgen05 GEMM + fused norm / bias-gelu kernels vs. its own fp32 CPU math."""
+    from deepspeedsyclsupport_b200.ops.transformer import DeepSpeedTransformerConfig, DeepSpeedTransformerLayer
+    torch.manual_seed(0)
+    cfg = DeepSpeedTransformerConfig(batch_size=4, hidden_size=256, intermediate_size=1024, heads=4, attn_dropout_ratio=0.0, hidden_dropout_ratio=0.0,
+                                     num_hidden_layers=2, initializer_range=0.02, pre_layer_norm=True, layer_norm_eps=1e-5)
+    ref_layer = DeepSpeedTransformerLayer(cfg)
+    ref_layer.inter_b.data.normal_(std=0.05)
+    gpu_layer = DeepSpeedTransformerLayer(cfg)
+    gpu_layer.load_state_dict(ref_layer.state_dict())
+    gpu_layer = gpu_layer.to(_dev()).bfloat16()
+    x = torch.randn(4, 128, 256)
+    xg = x.to(_dev()).bfloat16().requires_grad_()
+    xr = x.bfloat16().float().requires_grad_()
+    y = gpu_layer(xg)
+    yr = ref_layer(xr)
+    assert (y.float().cpu() - yr).abs().max() < 0.08
+    y.float().square().mean().backward()
+    yr.square().mean().backward()
+    g, gr = gpu_layer.inter_w.grad.float().cpu(), ref_layer.inter_w.grad
+    assert (g - gr).abs().max() <= 0.05 * gr.abs().max() + 1e-5
+    gb, gbr = gpu_layer.inter_b.grad.float().cpu(), ref_layer.inter_b.grad
+    assert (gb - gbr).abs().max() <= 0.05 * gbr.abs().max() + 1e-5
