@@ -1,0 +1,99 @@
+"""State-dict factory (TP re-sharding of Megatron checkpoints), elastic agent, sparse tensor, OnDevice, misc glue."""
+import os
+import sys
+
+import pytest
+import torch
+
+
+def _megatron_sd(h=8, heads=2, tp=1, rank=0, ver=0, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    full = {
+        "transformer.layers.0.attention.query_key_value.weight": torch.randn(3 * h, h, generator=g),
+        "transformer.layers.0.attention.query_key_value.bias": torch.randn(3 * h, generator=g),
+        "transformer.layers.0.attention.dense.weight": torch.randn(h, h, generator=g),
+        "transformer.layers.0.attention.dense.bias": torch.randn(h, generator=g),
+        "transformer.layers.0.mlp.dense_h_to_4h.weight": torch.randn(4 * h, h, generator=g),
+        "transformer.layers.0.mlp.dense_h_to_4h.bias": torch.randn(4 * h, generator=g),
+        "transformer.layers.0.mlp.dense_4h_to_h.weight": torch.randn(h, 4 * h, generator=g),
+        "transformer.layers.0.mlp.dense_4h_to_h.bias": torch.randn(h, generator=g),
+        "transformer.layers.0.input_layernorm.weight": torch.randn(h, generator=g),
+        "word_embeddings.weight": torch.randn(16, h, generator=g),
+    }
+    if tp == 1:
+        return full
+    out = {}
+    for k, v in full.items():
+        if "query_key_value" in k:  # version 0: q, k, v thirds each split across ranks
+            q, kk, vv = v.chunk(3, 0)
+            out[k] = torch.cat([t.chunk(tp, 0)[rank] for t in (q, kk, vv)], 0)
+        elif "attention.dense.weight" in k or "dense_4h_to_h.weight" in k:
+            out[k] = v.chunk(tp, 1)[rank]
+        elif "dense_h_to_4h" in k or "word_embeddings" in k:
+            out[k] = v.chunk(tp, 0)[rank]
+        else:
+            out[k] = v
+    return out
+
+
+def test_megatron_sd_loader_merge_and_split(tmp_path):
+    from deepspeedsyclsupport_b200.runtime.state_dict_factory import SDLoaderFactory
+    full = _megatron_sd()
+    files = []
+    for r in range(2):
+        p = str(tmp_path / f"mp_rank_{r:02d}_model_states.pt")
+        torch.save({"module": _megatron_sd(tp=2, rank=r), "checkpoint_version": 0, "mp_world_size": 2}, p)
+        files.append(p)
+    loader = SDLoaderFactory.get_sd_loader(files, None, "Megatron")
+    _, sd, (scales, merge_count) = loader.load(mp_world_size=1, mp_rank=0)
+    assert merge_count == 2 and scales is None
+    for k, v in full.items():
+        assert torch.equal(sd["module"][k], v), k
+    for r in range(4):  # 2 files -> 4 ranks: split
+        _, sd4, _ = loader.load(mp_world_size=4, mp_rank=r)
+        want = _megatron_sd(tp=4, rank=r)
+        for k, v in want.items():
+            assert torch.equal(sd4["module"][k], v), (r, k)
+    _, sdq, (scales, _) = loader.load(mp_world_size=1, mp_rank=0, quantize=True, quantize_bits=8, quantize_groups=2)
+    assert sdq["module"]["transformer.layers.0.attention.dense.weight"].dtype == torch.int8 and scales is not None
+
+
+def test_elastic_agent_restarts_failed_worker(tmp_path):
+    from deepspeedsyclsupport_b200.elasticity.elastic_agent import DSElasticAgent, assign_ranks, pick_members
+    assert assign_ranks([3, 0, 5], 3, 2) == ([2, 3], 6)
+    assert pick_members([2, 0, 1], min_nodes=2, max_nodes=2) == [0, 1] and pick_members([4], 2, 4) is None
+    marker = tmp_path / "attempts.txt"
+    script = tmp_path / "worker.py"
+    script.write_text("import os, sys\n"
+                      f"open({str(marker)!r}, 'a').write(os.environ['TORCHELASTIC_RESTART_COUNT'] + ' ' + os.environ['RANK'] + ' ' + os.environ['WORLD_SIZE'] + '\\n')\n"
+                      "sys.exit(1 if os.environ['TORCHELASTIC_RESTART_COUNT'] == '0' else 0)\n")
+    agent = DSElasticAgent([sys.executable, str(script)], dict(os.environ), nproc_per_node=2, max_restarts=3, monitor_interval=0.2)
+    assert agent.run() == 0
+    lines = sorted(marker.read_text().split("\n")[:-1])
+    assert lines == ["0 0 2", "0 1 2", "1 0 2", "1 1 2"]
+    agent = DSElasticAgent([sys.executable, "-c", "import sys; sys.exit(3)"], dict(os.environ), max_restarts=1, monitor_interval=0.1)
+    assert agent.run() == 1
+
+
+def test_sparse_tensor_roundtrip():
+    from deepspeedsyclsupport_b200.runtime.sparse_tensor import SparseTensor
+    g = torch.zeros(10, 4)
+    g[[1, 7]] = torch.randn(2, 4)
+    st = SparseTensor(g)
+    assert st.indices.tolist() == [1, 7] and torch.equal(st.to_dense(), g)
+    st.add(SparseTensor(g))
+    assert torch.equal(st.to_dense(), 2 * g)
+    assert torch.equal(st.to_coo_tensor().to_dense(), 2 * g)
+
+
+def test_on_device_and_glue():
+    from deepspeedsyclsupport_b200.utils.init_on_device import OnDevice
+    with OnDevice(dtype=torch.bfloat16, device="meta"):
+        m = torch.nn.Linear(4, 4)
+    assert m.weight.is_meta and m.weight.dtype == torch.bfloat16
+    assert not torch.nn.Linear(2, 2).weight.is_meta
+    from deepspeedsyclsupport_b200 import git_version_info as gv
+    assert gv.version and isinstance(gv.installed_ops, dict) and "version" in gv.torch_info
+    from deepspeedsyclsupport_b200.pydantic_v1 import BaseModel  # noqa: F401
+    from deepspeedsyclsupport_b200.nebula.config import DeepSpeedNebulaConfig
+    assert DeepSpeedNebulaConfig({"nebula": {"enabled": True, "persistent_time_interval": 5}}).persistent_time_interval == 5
