@@ -44,6 +44,80 @@ __global__ void rope_kernel(T* __restrict__ x, const int* __restrict__ pos, cons
   }
 }
 
+// Vectorised bf16/fp16 RoPE: one thread owns 8 consecutive frequencies j..j+7 of one token, computes their sin/cos
+// ONCE (the angle does not depend on the head) and then walks the heads of its head group: per head two 16-byte loads
+// (first / second half of the head) and two 16-byte stores.  sincosf is evaluated tokens*half*head_groups times instead
+// of tokens*half*nheads, and every access is a full 16-byte vector.  Requires D % 16 == 0 and 16-byte aligned rows.
+template <typename T>
+__global__ void rope_vec_kernel(T* __restrict__ x, const int* __restrict__ pos, const float* __restrict__ inv_freq,
+                                long long tokens, int row_stride, int head0, int nheads, int D, int seq_len, float sign,
+                                int heads_per_group) {
+  const int half = D / 2;
+  const int vec_per_token = half / 8;
+  const long long total = tokens * vec_per_token;
+  const int hbeg = blockIdx.y * heads_per_group;
+  const int hend = min(nheads, hbeg + heads_per_group);
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long t = i / vec_per_token;
+    const int j = static_cast<int>(i - t * vec_per_token) * 8;
+    const float p = pos ? static_cast<float>(pos[t]) : static_cast<float>(t % seq_len);
+    float sn[8], cs[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      sincosf(p * inv_freq[j + k], &sn[k], &cs[k]);
+      sn[k] *= sign;
+    }
+    T* row = x + t * row_stride + static_cast<long long>(head0) * D + j;
+    for (int h = hbeg; h < hend; ++h) {
+      T* lo = row + static_cast<long long>(h) * D;
+      T* hi = lo + half;
+      T a[8], b[8], ra[8], rb[8];
+      *reinterpret_cast<uint4*>(a) = *reinterpret_cast<const uint4*>(lo);
+      *reinterpret_cast<uint4*>(b) = *reinterpret_cast<const uint4*>(hi);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float af = to_f(a[k]), bf = to_f(b[k]);
+        ra[k] = from_f<T>(af * cs[k] - bf * sn[k]);
+        rb[k] = from_f<T>(bf * cs[k] + af * sn[k]);
+      }
+      *reinterpret_cast<uint4*>(lo) = *reinterpret_cast<const uint4*>(ra);
+      *reinterpret_cast<uint4*>(hi) = *reinterpret_cast<const uint4*>(rb);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ sum of squares (gradient norm), accumulated into *out
+template <typename T, int VEC>
+__global__ void sumsq_kernel(const T* __restrict__ x, long long n, float* __restrict__ out) {
+  float acc = 0.f;
+  const long long nvec = n / VEC;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long v = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; v < nvec; v += stride) {
+    T e[VEC];
+    *reinterpret_cast<uint4*>(e) = *reinterpret_cast<const uint4*>(x + v * VEC);
+#pragma unroll
+    for (int k = 0; k < VEC; ++k) {
+      const float f = to_f(e[k]);
+      acc += f * f;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    for (long long i = nvec * VEC; i < n; ++i) {
+      const float f = to_f(x[i]);
+      acc += f * f;
+    }
+  acc = warp_sum(acc);
+  __shared__ float ws[32];
+  if ((threadIdx.x & 31) == 0) ws[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    acc = threadIdx.x < (blockDim.x >> 5) ? ws[threadIdx.x] : 0.f;
+    acc = warp_sum(acc);
+    if (threadIdx.x == 0) atomicAdd(out, acc);
+  }
+}
+
 // ------------------------------------------------------------------ gated activation: out = act(gate) * up
 // in: [rows, 2F] with gate = in[:, :F], up = in[:, F:]  (interleaved=1: gate = even cols, up = odd cols)
 enum Act { ACT_IDENTITY = 0, ACT_RELU = 1, ACT_GELU = 2, ACT_SILU = 3 };
@@ -264,9 +338,43 @@ DSB_EXPORT int dsb200_rope_inplace(void* x, const int* positions, const float* i
   DSB_REQUIRE(head_dim % 2 == 0, "rope: odd head_dim");
   const long long work = tokens * nheads * (head_dim / 2);
   if (work == 0) return DSB_OK;
-  DSB_EW_DISPATCH(dtype, (rope_kernel<T><<<ew_grid(work, 256), 256, 0, stream>>>((T*)x, positions, inv_freq, tokens, row_stride,
-                                                                              head0, nheads, head_dim, seq_len,
-                                                                              backward ? -1.f : 1.f)));
+  const float sign = backward ? -1.f : 1.f;
+  const bool vec_ok = dtype != 2 && head_dim % 16 == 0 && row_stride % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0;
+  if (vec_ok) {
+    // enough head groups to fill the machine, few enough to keep the sincos amortisation
+    const long long vecs = tokens * (head_dim / 16);
+    int groups = 1;
+    while (groups < nheads && vecs * groups < static_cast<long long>(num_sms()) * 2048) groups *= 2;
+    const int hpg = (nheads + groups - 1) / groups;
+    dim3 grid(ew_grid(vecs, 128), (nheads + hpg - 1) / hpg);
+    if (dtype == 0)
+      rope_vec_kernel<__nv_bfloat16><<<grid, 128, 0, stream>>>((__nv_bfloat16*)x, positions, inv_freq, tokens, row_stride, head0,
+                                                              nheads, head_dim, seq_len, sign, hpg);
+    else
+      rope_vec_kernel<__half><<<grid, 128, 0, stream>>>((__half*)x, positions, inv_freq, tokens, row_stride, head0, nheads,
+                                                       head_dim, seq_len, sign, hpg);
+  } else {
+    DSB_EW_DISPATCH(dtype, (rope_kernel<T><<<ew_grid(work, 256), 256, 0, stream>>>((T*)x, positions, inv_freq, tokens, row_stride,
+                                                                                head0, nheads, head_dim, seq_len, sign)));
+  }
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// out[0] += sum(x[i]^2) over n elements (dtype 0 bf16 / 1 fp16 / 2 fp32).  x must be 16-byte aligned.
+DSB_EXPORT int dsb200_sumsq(const void* x, long long n, int dtype, float* out, cudaStream_t stream) {
+  if (n == 0) return DSB_OK;
+  DSB_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0, "sumsq: x must be 16-byte aligned");
+  const int threads = 512;
+  long long want = (n / 8 + threads - 1) / threads;
+  const long long cap = static_cast<long long>(num_sms()) * 4;
+  const int grid = static_cast<int>(want < cap ? (want > 0 ? want : 1) : cap);
+  if (dtype == 0)
+    sumsq_kernel<__nv_bfloat16, 8><<<grid, threads, 0, stream>>>((const __nv_bfloat16*)x, n, out);
+  else if (dtype == 1)
+    sumsq_kernel<__half, 8><<<grid, threads, 0, stream>>>((const __half*)x, n, out);
+  else
+    sumsq_kernel<float, 4><<<grid, threads, 0, stream>>>((const float*)x, n, out);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

@@ -265,3 +265,17 @@ def cross_entropy(logits, labels, ignore_index=-100):
     if not logits.is_cuda:
         return F.cross_entropy(logits.float().view(-1, logits.shape[-1]), labels.reshape(-1), ignore_index=ignore_index)
     return _CrossEntropyFn.apply(logits.contiguous(), labels, ignore_index)
+
+
+# ----------------------------------------------------------------------------- reductions
+def sumsq(x, out=None):
+    """sum(x^2) as a 1-element fp32 device tensor in ONE pass over x (bf16 / fp16 / fp32), accumulated into `out` when
+    given.  Replaces the .float().square().sum() chain (three full-size temporaries per chunk) in the gradient-norm
+    computation (reference: multi_tensor_l2norm / get_grad_norm in runtime/utils.py:315-385)."""
+    if out is None:
+        out = torch.zeros(1, dtype=torch.float32, device=x.device)
+    if not x.is_cuda or x.dtype not in _DT or not x.is_contiguous() or x.data_ptr() % 16 != 0:
+        out += x.float().square().sum()
+        return out
+    native.check(native.lib().dsb200_sumsq(native.ptr(x), x.numel(), _dt(x), native.ptr(out), native.stream_ptr()))
+    return out

@@ -57,6 +57,7 @@ _SIGS = {
     "dsb200_cross_entropy_fwd": "pppp l i l l i p",
     "dsb200_cross_entropy_bwd": "pppp l i l l i p",
     "dsb200_add": "ppp l i p",
+    "dsb200_sumsq": "p l i p p",
 }
 _RESTYPE_LONG = {"dsb200_norm_bwd_scratch_floats"}
 

@@ -701,8 +701,11 @@ class ZeroShardedOptimizer:
             dist.all_reduce(sq, op=dist.ReduceOp.SUM, group=self.shard_group)
             self._model_parallel_all_reduce(sq, dist.ReduceOp.SUM)
             return sq.sqrt()
-        sq = (g.float() if g.dtype != torch.float32 else g).square().sum().reshape(1) if g.numel() < (1 << 28) else \
-            sum((c.float().square().sum() for c in g.split(1 << 27))).reshape(1)
+        if g.is_cuda:
+            from ...ops.fused_ops import sumsq
+            sq = sumsq(g)  # one fused pass over the flat gradient shard
+        else:
+            sq = (g.float() if g.dtype != torch.float32 else g).square().sum().reshape(1)
         if dist.is_initialized():
             if self.shard_world > 1:
                 dist.all_reduce(sq, op=dist.ReduceOp.SUM, group=self.shard_group)

@@ -517,3 +517,34 @@ def test_transformer_layer_bf16_gpu():
     assert (g - gr).abs().max() <= 0.05 * gr.abs().max() + 1e-5
     gb, gbr = gpu_layer.inter_b.grad.float().cpu(), ref_layer.inter_b.grad
     assert (gb - gbr).abs().max() <= 0.05 * gbr.abs().max() + 1e-5
+
+
+@pytest.mark.parametrize("shape", [(8192, 64, 128), (40, 6, 64), (7, 5, 96)])
+def test_rope_vectorised_matches_scalar_reference(shape):
+    """large position ids (up to S) and several head-group splits: the vector kernel against the fp32 torch formula"""
+    from deepspeedsyclsupport_b200.ops import fused_ops as FO
+    torch.manual_seed(0)
+    T, H, d = shape
+    S = 4096
+    inv = FO.rope_inv_freq(d, device=_dev())
+    x = torch.randn(T, (H + 2) * d, device=_dev(), dtype=torch.bfloat16)
+    pos = torch.randint(0, S, (T, ), device=_dev(), dtype=torch.int32)
+    ref = FO.rope_ref(x.float(), inv, pos, 1, H, d)
+    y = x.clone()
+    FO._rope_apply(y, inv, pos, S, 1, H, d, False)
+    assert (y.float() - ref).abs().max() < 4e-2
+    assert torch.equal(y[:, :d], x[:, :d]) and torch.equal(y[:, (H + 1) * d:], x[:, (H + 1) * d:])  # untouched heads
+    FO._rope_apply(y, inv, pos, S, 1, H, d, True)  # inverse rotation restores the input (up to bf16 rounding)
+    assert (y.float() - x.float()).abs().max() < 6e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_sumsq(dtype):
+    from deepspeedsyclsupport_b200.ops.fused_ops import sumsq
+    torch.manual_seed(0)
+    x = torch.randn(3_000_011, device=_dev()).to(dtype)
+    got = sumsq(x)
+    ref = x.double().square().sum()
+    assert abs(got.item() - ref.item()) <= 1e-4 * ref.item()
+    got2 = sumsq(x[:8 * 1000], out=got)
+    assert abs(got2.item() - (ref + x[:8000].double().square().sum()).item()) <= 1e-4 * ref.item()
