@@ -111,7 +111,9 @@ def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, l
         "config": {"model": f"llama-2-{args.model}" + (f"-{args.layers}layers-INVALID-debug" if args.layers else ""),
                    "global_batch": args.micro_batch * world, "seq_len": args.seq_len, "micro_batch_per_gpu": args.micro_batch,
                    "parallelism": f"zero{args.zero_stage}-dp{world}", "optimizer": "AdamW", "grad_clip": 1.0,
-                   "activation_checkpointing": not args.no_act_ckpt,
+                   "activation_checkpointing": (False if args.no_act_ckpt else
+                                                ("per-layer; attention core output+lse kept, everything else recomputed" if impl == "own"
+                                                 else "per-layer full recompute (HF gradient_checkpointing)")),
                    "l2_policy": "working set (weights+activations, >13 GB) far exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_tps, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "clocks": clocks,

@@ -15,6 +15,7 @@ import torch.nn as nn
 
 from ..ops import fused_ops as FO
 from ..ops.attention import attention
+from ..ops.flash_attention import attention_recompute_contexts
 from ..ops.gemm import linear, linear_rope
 
 
@@ -31,6 +32,7 @@ class LlamaConfig:
     rope_theta: float = 10000.0
     tie_word_embeddings: bool = False
     activation_checkpointing: bool = False
+    save_attention_in_checkpoint: bool = True  # selective recompute: do not re-run the attention core in backward
     initializer_range: float = 0.02
 
     @property
@@ -111,11 +113,14 @@ class LlamaModel(nn.Module):
         residual = None
         for layer in self.layers:
             if self.cfg.activation_checkpointing and self.training:
+                # per-layer checkpoint; the attention core's (out, lse) are kept and replayed during recomputation
+                kw = dict(use_reentrant=False)
+                if self.cfg.save_attention_in_checkpoint:
+                    kw["context_fn"] = attention_recompute_contexts
                 if residual is None:
-                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, l=layer: l(a, None, positions), x, use_reentrant=False)
+                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, l=layer: l(a, None, positions), x, **kw)
                 else:
-                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, r, l=layer: l(a, r, positions), x, residual,
-                                                                     use_reentrant=False)
+                    x, residual = torch.utils.checkpoint.checkpoint(lambda a, r, l=layer: l(a, r, positions), x, residual, **kw)
             else:
                 x, residual = layer(x, residual, positions)
         if residual is None:

@@ -28,10 +28,8 @@ def attention_ref(qkv, B, S, hq, hkv, d, causal=True, scale=None):
 def _have_own():
     global _own_kernel
     if _own_kernel is None:
-        try:
-            _own_kernel = hasattr(native.lib(), "dsb200_flash_attn_fwd")
-        except Exception:
-            _own_kernel = False
+        # a GPU box without the native library is a broken install: fail loudly instead of silently running a library path
+        _own_kernel = hasattr(native.lib(), "dsb200_flash_attn_fwd")
     return _own_kernel
 
 
