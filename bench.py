@@ -258,13 +258,34 @@ def run_reference(args):
         host_labels = torch.randint(0, V, (B, S), generator=g).pin_memory()
         dev_ids, dev_labels = host_ids.to(dev), host_labels.to(dev)
         last = {}
+        # Watchdog: the unmodified reference can dead-lock in its collectives on this torch/NCCL stack.  If the run makes no
+        # progress for DSB_REF_WATCHDOG seconds, dump every thread's stack (diagnosis) and report the arm as unavailable
+        # instead of hanging the caller until its own timeout.
+        import faulthandler
+        import threading
+        limit = float(os.environ.get("DSB_REF_WATCHDOG", "180"))
+        progress = {"t": time.time(), "done": False}
+
+        def _watch():
+            while not progress["done"]:
+                time.sleep(5)
+                if time.time() - progress["t"] > limit:
+                    faulthandler.dump_traceback(file=sys.stderr, all_threads=True)
+                    if rank == 0:
+                        print(json.dumps({"impl": "reference", "n_gpus": world,
+                                          "unavailable": f"reference training step made no progress for {int(limit)} s at world size {world} (dead-lock inside the unmodified reference on this torch/NCCL stack)"}), flush=True)
+                    os._exit(0)
+
+        threading.Thread(target=_watch, daemon=True).start()
 
         def step():
+            progress["t"] = time.time()
             loss = engine(input_ids=dev_ids, labels=dev_labels).loss
             engine.backward(loss)
             engine.step()
 
         def step_e2e():
+            progress["t"] = time.time()
             ids = host_ids.to(dev, non_blocking=True)
             labels = host_labels.to(dev, non_blocking=True)
             loss = engine(input_ids=ids, labels=labels).loss
@@ -278,6 +299,7 @@ def run_reference(args):
             ReduceOp = tdist.ReduceOp
 
         ms, e2e, _, clocks = timed_loops(args, step, step_e2e, world, _D, torch, lambda: 0)
+        progress["done"] = True
         if rank == 0:
             h2d = host_ids.numel() * 8 * 2
             extra = {"final_loss": last.get("loss_host"), "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
