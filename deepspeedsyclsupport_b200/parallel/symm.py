@@ -89,8 +89,24 @@ class _PeerOps:
                                              native.stream_ptr())
         native.check(rc)
 
-    def all_reduce_bf16(self, dst, src_offset, n, rank=None, max_ctas=0):
+    def all_reduce_bf16(self, dst, src_offset, n, rank=None, max_ctas=0, scratch_offset=None, algo="auto"):
+        """dst[n] = sum over ranks of the bf16 vector at `src_offset` of every rank's buffer.
+        one-shot : every rank reads all W vectors and reduces locally (W-1)*n remote reads, one launch: lowest latency,
+                   right for decode-sized messages.
+        two-shot : reduce-scatter into a symmetric scratch slice, device barrier, all-gather of the slices:
+                   2*(W-1)/W*n remote reads: right for large messages on many GPUs.  Needs `scratch_offset` (n/W
+                   bf16 elements of this symmetric buffer) and a real multi-process buffer (it uses the device barrier).
+        auto     : two-shot when a scratch region is given, W > 2 and the message is >= 4 MiB."""
         r = self.rank if rank is None else rank
+        can_two = scratch_offset is not None and rank is None and hasattr(self, "barrier") and n % (8 * self.world) == 0
+        if algo == "two_shot":
+            assert can_two, "two-shot all-reduce needs scratch_offset, a real SymmetricBuffer and n % (8*world) == 0"
+        if (algo == "two_shot") or (algo == "auto" and can_two and self.world > 2 and n * 2 >= (4 << 20)):
+            per = n // self.world
+            mine = self.view(scratch_offset, (per, ), torch.bfloat16)
+            self.reduce_scatter(mine, src_offset, torch.bfloat16, per, scale=1.0, max_ctas=max_ctas)
+            self.barrier()  # every rank's reduced slice is complete before anyone gathers it
+            return self.all_gather(dst, scratch_offset, per * 2, max_ctas=max_ctas)
         rc = native.lib().dsb200_p2p_allreduce_bf16(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(dst), n, r,
                                                     self.world, max_ctas, native.stream_ptr())
         native.check(rc)

@@ -35,6 +35,21 @@ def _symm_body():
     torch.cuda.synchronize()
     assert torch.equal(out, ref2)
     sb.barrier()
+    # all-reduce, one-shot and two-shot (reduce-scatter + barrier + all-gather through a symmetric scratch slice)
+    m = 16 * W * 1024
+    sb2 = SymmetricBuffer(dist.get_world_group(), m * 2 + m * 2 // W + 256)
+    v = torch.randn(m, device=dev).bfloat16()
+    sb2.view(0, (m, ), torch.bfloat16).copy_(v)
+    sb2.barrier()
+    want = v.float().clone()
+    dist.all_reduce(want)
+    for algo in ("one_shot", "two_shot"):
+        got = torch.empty(m, device=dev, dtype=torch.bfloat16)
+        sb2.all_reduce_bf16(got, 0, m, scratch_offset=m * 2, algo=algo)
+        sb2.barrier()
+        torch.cuda.synchronize()
+        assert (got.float() - want).abs().max() <= 2e-2 * want.abs().max(), algo
+    sb2.close()
     torch.cuda.synchronize()
     sb.close()
 

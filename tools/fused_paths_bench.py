@@ -195,7 +195,7 @@ def main():
             dist.all_reduce(ref_buf)
 
         def fused_ar():
-            sb.all_reduce_bf16(dst, 0, numel)
+            sb.all_reduce_bf16(dst, 0, numel, scratch_offset=numel * 2)  # auto: two-shot for >= 4 MiB on > 2 GPUs
 
         base = timed(nccl_ar)
         fused = timed(fused_ar, pre=sb.barrier)
