@@ -40,10 +40,12 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t smem_addr, uint32_t cta_ra
   return r;
 }
 
-template <int STAGES, bool A_MN, bool B_MN, bool OUT_F32>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
-gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                  const __grid_constant__ CUtensorMap tmC, const Params p) {
+// AG = true adds the all-gather of the sharded B operand (see AgArgs in gemm_core.cuh): two extra warps per CTA pull
+// 256-row chunks of B from the owning peers over NVLink in the order the (n-major) tile loop consumes them and publish
+// a completion counter per chunk; the TMA producers wait for the counter of their n-block.
+template <int STAGES, bool A_MN, bool B_MN, bool OUT_F32, bool AG>
+__device__ __forceinline__ void gemm2_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
+                                           const Params& p, const AgArgs* ag) {
   using S = Smem2<STAGES>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -92,9 +94,23 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int m_blk, n_blk;
-        tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+        if constexpr (AG) { n_blk = tile / p.tiles_m; m_blk = tile - n_blk * p.tiles_m; }
+        else tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
         const int m0 = m_blk * BM2 + static_cast<int>(rank) * BM;
         const int nb0 = n_blk * BN2 + static_cast<int>(rank) * BN2_CTA;
+        if constexpr (AG) {
+          const int target = static_cast<int>(gridDim.x);  // every CTA's copy warps landed their share of this chunk
+          uint32_t spins = 0;
+          int seen;
+          do {
+            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(ag->flags + n_blk) : "memory");
+            if (seen < target && ++spins > DSB_SPIN_LIMIT) {
+              printf("dsb200: AG-GEMM(2cta) wait for n-block %d timed out (%d/%d)\n", n_blk, seen, target);
+              __trap();
+            }
+          } while (seen < target);
+          asm volatile("fence.proxy.async;" ::: "memory");
+        }
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * S::STAGE_BYTES;
@@ -157,6 +173,47 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (acc == 0) acc_phase ^= 1;
       }
     }
+  } else if (AG && warp >= 6) {
+    // ------------------------------------------------------------- all-gather copy warps (AG only): peers -> b_local
+    if constexpr (AG) {
+      const int ct = threadIdx.x - 192;  // 0..63
+      const long long row_elems = p.K;
+      for (int nb = 0; nb < p.tiles_n; ++nb) {
+        const long long rows = min(BN2, p.N - nb * BN2);
+        const long long chunk_elems = rows * row_elems;
+        const long long chunk_off = static_cast<long long>(nb) * BN2 * row_elems;
+        const long long vecs = chunk_elems / 8;
+        const long long per_cta = (vecs + gridDim.x - 1) / gridDim.x;
+        const long long v_lo = per_cta * blockIdx.x;
+        const long long v_hi = min(vecs, v_lo + per_cta);
+        constexpr int UNR = 8;
+        for (long long v = v_lo + ct; v < v_hi; v += 64 * UNR) {
+          uint4 buf[UNR];
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) {
+            const long long vv = v + static_cast<long long>(u) * 64;
+            if (vv < v_hi) {
+              const long long e = ag->w_off + chunk_off + vv * 8;
+              const int peer = static_cast<int>(e / ag->shard_numel);
+              const long long le = e - static_cast<long long>(peer) * ag->shard_numel;
+              const void* src = static_cast<const __nv_bfloat16*>(ag->peer_shard[peer]) + le;
+              asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(buf[u].x), "=r"(buf[u].y), "=r"(buf[u].z), "=r"(buf[u].w)
+                           : "l"(src)
+                           : "memory");
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < UNR; ++u) {
+            const long long vv = v + static_cast<long long>(u) * 64;
+            if (vv < v_hi) *reinterpret_cast<uint4*>(ag->b_local + chunk_off + vv * 8) = buf[u];
+          }
+        }
+        __threadfence();
+        named_bar_sync(2, 64);
+        if (ct == 0) asm volatile("red.release.gpu.global.add.s32 [%0], 1;" ::"l"(ag->flags + nb) : "memory");
+      }
+    }
   } else {
     // ------------------------------------------------------------- epilogue (warps 2..5 of both CTAs)
     const int q = warp & 3;
@@ -169,7 +226,8 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     uint32_t buf_idx = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int m_blk, n_blk;
-      tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
+      if constexpr (AG) { n_blk = tile / p.tiles_m; m_blk = tile - n_blk * p.tiles_m; }
+      else tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
       const int m0 = m_blk * BM2 + static_cast<int>(rank) * BM, n0 = n_blk * BN2;
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
@@ -247,6 +305,20 @@ gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     tc_fence_after();
     tmem_dealloc<2>(tmem_base, 2 * BN2);
   }
+}
+
+template <int STAGES, bool A_MN, bool B_MN, bool OUT_F32>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS, 1)
+gemm2_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                  const __grid_constant__ CUtensorMap tmC, const Params p) {
+  gemm2_body<STAGES, A_MN, B_MN, OUT_F32, false>(tmA, tmB, tmC, p, nullptr);
+}
+
+template <int STAGES>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NUM_THREADS_AG, 1)
+gemm2_ag_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const __grid_constant__ CUtensorMap tmC, const Params p, const __grid_constant__ AgArgs ag) {
+  gemm2_body<STAGES, false, false, false, true>(tmA, tmB, tmC, p, &ag);
 }
 
 }  // namespace gemm

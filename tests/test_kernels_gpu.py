@@ -258,13 +258,14 @@ def test_p2p_collectives_emulated_ranks():
         assert (dst.float() - total * W).abs().max() < 5e-2
 
 
+@pytest.mark.parametrize("shape", [(1024, 1376, 512), (2048, 5120, 1024)])  # single-CTA core / CTA-pair core
 @pytest.mark.parametrize("world", [1, 4])
-def test_ag_gemm_emulated_ranks(world):
+def test_ag_gemm_emulated_ranks(world, shape):
     """All-gather fused into the GEMM: W is sharded over `world` flat shards (all on this GPU); the kernel pulls the
     shards through the peer-pointer table while the tcgen05 tiles run."""
     from deepspeedsyclsupport_b200.parallel.fused import ag_gemm
     torch.manual_seed(0)
-    M, N, K = 1024, 1376, 512
+    M, N, K = shape
     w_off = 64 * 5  # W starts in the middle of the unit
     unit = w_off + N * K + 128
     S = -(-unit // (world * 64)) * 64
@@ -551,13 +552,14 @@ def test_sumsq(dtype):
 
 
 def test_checkpoint_replays_saved_attention():
-    """activation checkpointing with the attention core saved (not recomputed) gives the same gradients and launches
-    the flash forward kernel once per layer instead of twice"""
+    """activation checkpointing with the attention core saved (not recomputed): the flash forward kernel runs once per
+    layer instead of twice and the gradients agree with full recomputation to within the backward's own run-to-run noise
+    (its dQ reduction order is not deterministic: TMA reduce-add)."""
     from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
     from deepspeedsyclsupport_b200.ops import flash_attention as FA
-    grads, calls = {}, {}
     ids = torch.randint(0, 512, (2, 256), device=_dev())
-    for save in (False, True):
+
+    def run(save):
         torch.manual_seed(0)
         cfg = llama_config("tiny", activation_checkpointing=True, save_attention_in_checkpoint=save, max_position_embeddings=256)
         model = LlamaForCausalLM(cfg).to(_dev()).bfloat16().train()
@@ -570,13 +572,15 @@ def test_checkpoint_replays_saved_attention():
 
         FA.flash_fwd = counting
         try:
-            loss = model(ids, ids)
-            loss.backward()
+            model(ids, ids).backward()
         finally:
             FA.flash_fwd = orig
-        calls[save] = n[0]
-        grads[save] = [p.grad.clone() for p in model.parameters()]
-    assert calls[False] == 2 * cfg.num_hidden_layers and calls[True] == cfg.num_hidden_layers
-    # the backward's dQ reduction order is not deterministic (TMA reduce-add), so compare with a tolerance
-    for a, b in zip(grads[False], grads[True]):
-        assert (a.float() - b.float()).abs().max() <= 2e-2 * a.float().abs().max() + 1e-6
+        return n[0], [p.grad.float().clone() for p in model.parameters()], cfg.num_hidden_layers
+
+    calls_a, grads_a, L = run(False)
+    _, grads_a2, _ = run(False)
+    calls_b, grads_b, _ = run(True)
+    assert calls_a == 2 * L and calls_b == L
+    for a, a2, b in zip(grads_a, grads_a2, grads_b):
+        noise = (a - a2).abs().max()
+        assert (a - b).abs().max() <= 4 * noise + 1e-3 * a.abs().max() + 1e-7

@@ -26,17 +26,14 @@ NVLINK_UNI_GBS = 900.0  # NVLink-5 per direction per GPU (B200_PROFILING.md)
 
 
 def peaks():
+    """(cuBLAS bf16 burst TFLOP/s, copy GB/s) from the driver-written MEASURED_PEAKS.json; documented fallbacks otherwise."""
     gemm_tflops, copy_gbs = 1600.0, 6000.0
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
         try:
             d = json.load(open(path))
-            for k, v in d.items():
-                if isinstance(v, (int, float)):
-                    if "tflop" in k.lower() or "gemm" in k.lower():
-                        gemm_tflops = float(v)
-                    if "copy" in k.lower() or "bandwidth" in k.lower() or "gbs" in k.lower():
-                        copy_gbs = float(v)
+            gemm_tflops = float(d.get("bf16_tflops", gemm_tflops))
+            copy_gbs = float(d.get("hbm_gbs", copy_gbs))
         except Exception:
             pass
     return gemm_tflops, copy_gbs
