@@ -74,11 +74,19 @@ class InferenceEngine(Module):
                         raise ValueError(f"Injection policy layer'{policy}' not valid.")
                 self._apply_injection_policy(config, client_module)
         else:
+            self._kernel_injected = False
             if config.replace_with_kernel_inject:
-                # the fused B200 kernels are reached through the framework's own model implementations
-                # (models/, inference/v2); foreign HF modules get AutoTP + per-op kernels (norms / GEMM) instead
-                logger.warning("replace_with_kernel_inject: no per-architecture fused containers for foreign modules; applying AutoTP")
-            if config.tensor_parallel.tp_size > 1:
+                from .kernel_inject import KernelInjectedCausalLM, can_inject
+                if can_inject(self.module):
+                    # supported HF architecture: its weights are mapped onto the fused ragged transformer (blocked KV cache,
+                    # fused norm/QKV/RoPE/attention/MLP kernels); tensor parallelism is handled inside that implementation
+                    self.module = KernelInjectedCausalLM(self.module, dtype=config.dtype if config.dtype in (torch.bfloat16, torch.float16,
+                                                                                                                torch.float32) else torch.bfloat16,
+                                                         tp_size=config.tensor_parallel.tp_size, max_context=getattr(config, "max_out_tokens", None))
+                    self._kernel_injected = True
+                else:
+                    logger.warning("replace_with_kernel_inject: unsupported architecture for kernel injection; applying AutoTP")
+            if config.tensor_parallel.tp_size > 1 and not self._kernel_injected:
                 parser_dict = AutoTP.tp_parser(model)
                 log_dist(f"AutoTP: {parser_dict}", ranks=[0])
                 for client_module, injection_policy in parser_dict:

@@ -95,6 +95,141 @@ int dsbh_lion_step(float* p, float* m, const void* g, int grad_type, void* lp, i
 int dsbh_cast_f32_lp(const float* src, void* dst, int lp_type, int64_t n);
 double dsbh_sumsq(const void* g, int grad_type, int64_t n);
 
+/* ==== generated by tools/gen_header.py from csrc/ -- do not edit below this line ==== */
+
+/* ---- csrc/attn/flash_bwd.cu */
+/* Gradient of dsb200_flash_attn_fwd.  dout/out: [B*S, hq*D] bf16; qkv, dqkv: packed [B*S, (hq+2*hkv)*D] bf16;
+ * lse: [B, hq, S] from the forward.  Scratch supplied by the caller: dq_acc [B*S, hq*D] fp32 ZERO-INITIALISED,
+ * delta [B, hq, S] fp32. */
+int dsb200_flash_attn_bwd(const void* dout, const void* qkv, const void* out, const float* lse, void* dqkv, float* dq_acc,
+                          float* delta, int B, int S, int hq, int hkv, int head_dim, int causal, float scale,
+                          dsb200_stream_t stream);
+
+/* ---- csrc/attn/flash_fwd.cu */
+/* out[B*S, hq*D] = softmax(Q K^T * scale [+ causal mask]) V with Q,K,V read from packed qkv [B*S, (hq+2*hkv)*D] (bf16).
+ * lse: optional [B, hq, S] fp32 (natural-log sum-exp of the scaled scores) for the backward pass. */
+int dsb200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int hq, int hkv, int head_dim, int causal,
+                          float scale, dsb200_stream_t stream);
+
+/* ---- csrc/comm/symm.cu */
+/* ---- allocation / mapping (host pointers unless noted) */
+int dsb200_symm_alloc(long long bytes, void** ptr, unsigned char* handle64);
+int dsb200_symm_open(const unsigned char* handle64, void** ptr);
+int dsb200_symm_close(void* ptr);
+int dsb200_symm_free(void* ptr);
+/* peer_ptrs: HOST array of `world` device pointers (this process's mappings of every rank's buffer, own included) */
+int dsb200_symm_barrier(void* const* peer_ptrs, long long flag_off, int rank, int world, unsigned int epoch,
+                        dsb200_stream_t stream);
+int dsb200_p2p_allgather(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
+                         int world, int max_ctas, dsb200_stream_t stream);
+/* src dtype / dst dtype: 0 bf16, 2 fp32.  n = elements per rank (multiple of 8).  sumsq: optional device float (+= sum g^2). */
+int dsb200_p2p_reduce_scatter(void* const* peer_ptrs, long long src_off, int src_dtype, void* dst, int dst_dtype,
+                              long long n, int rank, int world, float scale, int accumulate, float* sumsq, int max_ctas,
+                              dsb200_stream_t stream);
+int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, float* m, float* v, void* lp, long long n,
+                       int rank, int world, float scale, float lr, float beta1, float beta2, float eps, float weight_decay,
+                       int adamw_mode, int bias_correction, int step, int max_ctas, dsb200_stream_t stream);
+int dsb200_p2p_allreduce_bf16(void* const* peer_ptrs, long long src_off, void* dst, long long n, int rank, int world,
+                              int max_ctas, dsb200_stream_t stream);
+
+/* ---- csrc/elementwise/elementwise.cu */
+/* out[0] += sum(x[i]^2) over n elements (dtype 0 bf16 / 1 fp16 / 2 fp32).  x must be 16-byte aligned. */
+int dsb200_sumsq(const void* x, long long n, int dtype, float* out, dsb200_stream_t stream);
+
+/* ---- csrc/gemm/gemm_ag.cu */
+/* C[M,N] (bf16) = A[M,K] * W^T with W[N,K] gathered from peers INSIDE the kernel.
+ *   b_local     : [N,K] bf16 destination of the gather (kept for backward); also the GEMM's B operand
+ *   peer_shards : HOST array of `world` device pointers -- each rank's shard region of the unit (this process's mappings)
+ *   w_off       : flat element offset of W[0][0] inside the unit; shard_numel: elements per rank shard
+ *   flags       : device scratch, >= ceil(N/256) ints (zeroed by this call) */
+int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int K, int lda, int ldc,
+                        void* const* peer_shards, long long w_off, long long shard_numel, int* flags, int world,
+                        dsb200_stream_t stream);
+
+/* ---- csrc/host/aio.cpp */
+void* dsbh_aio_create(int64_t block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);
+void dsbh_aio_destroy(void* hp);
+int64_t dsbh_aio_block_size(void* hp);
+int dsbh_aio_queue_depth(void* hp);
+int dsbh_aio_thread_count(void* hp);
+/* Returns bytes waited for (>= 0) or -1 if any chunk failed since the last wait. */
+int64_t dsbh_aio_wait(void* hp);
+int dsbh_aio_pread(void* hp, void* buffer, int64_t nbytes, const char* path, int async, int64_t file_offset);
+int dsbh_aio_pwrite(void* hp, const void* buffer, int64_t nbytes, const char* path, int async, int64_t file_offset);
+
+/* ---- csrc/host/ragged_host.cpp */
+void* dsbh_allocator_create(int num_blocks);
+void dsbh_allocator_destroy(void* h);
+int dsbh_allocator_free_blocks(void* h);
+/* returns 0 on success, -1 when fewer than n blocks are free (nothing is allocated then) */
+int dsbh_allocator_allocate(void* h, int n, int32_t* out);
+/* returns 0 on success, -1 on an invalid / double free (allocator unchanged) */
+int dsbh_allocator_free(void* h, const int32_t* blocks, int n);
+/* seq_meta: per sequence (start token in batch, n new tokens, tokens already in the KV cache). Returns the atom count. */
+int dsbh_build_atoms(const int32_t* seq_start, const int32_t* seq_ntok, const int32_t* seq_seen, int n_seqs, int q_block,
+                     int kv_block, int32_t* atoms_out, int max_atoms);
+/* Pack the per-token metadata of a ragged batch: tok_seq[t], tok_pos[t], last_tok[s]. */
+int dsbh_pack_batch(const int32_t* seq_ntok, const int32_t* seq_seen, int n_seqs, int32_t* tok_seq, int32_t* tok_pos,
+                    int32_t* last_tok);
+
+/* ---- csrc/quant/onebit.cu */
+/* x[n] fp32 (read only), err[n] fp32 (error feedback, updated), packed[n/8], scale_io[2] fp32 device scratch:
+ * on return scale_io[0] = ||x+err||_2 / sqrt(n).  n must be a multiple of 8; x/err 16-byte aligned. */
+int dsb200_onebit_compress(void* x, void* err, void* packed, void* scale_io, long long n, dsb200_stream_t stream);
+int dsb200_onebit_decompress(const void* packed, const void* scales, void* out, int rows, long long chunk_bytes, int mode,
+                             dsb200_stream_t stream);
+
+/* ---- csrc/quant/quantizer.cu */
+/* x: n elements (n % 128 == 0) -> q: n bytes (e4m3), scales: n/128 floats */
+int dsb200_fp8_block_quantize(const void* x, void* q, float* scales, long long n, int dtype, dsb200_stream_t stream);
+int dsb200_fp8_block_dequantize(const void* q, const float* scales, void* out, long long n, int dtype,
+                                dsb200_stream_t stream);
+/* q: parts * n bytes, scales: parts * n/128 ; out: n elements = scale_out * sum over parts */
+int dsb200_fp8_block_dequant_reduce(const void* q, const float* scales, void* out, long long n, int parts, float scale_out,
+                                    int dtype, dsb200_stream_t stream);
+/* groups * group_size elements; params: groups*2 floats (scale, offset); bits 8 or 4; q bytes = n * bits / 8 */
+int dsb200_int_quantize(const void* x, void* q, float* params, long long groups, int group_size, int bits, int symmetric,
+                        int dtype, dsb200_stream_t stream);
+int dsb200_int_dequantize(const void* q, const float* params, void* out, long long groups, int group_size, int bits,
+                          int symmetric, int dtype, dsb200_stream_t stream);
+int dsb200_fake_quantize(void* x, long long groups, int group_size, int bits, int symmetric, int stochastic,
+                         long long seed, int dtype, dsb200_stream_t stream);
+
+/* ---- csrc/ragged/ragged_ops.cu */
+int dsb200_kv_rotary_append(void* qkv, void* kv_cache, const int* tok_seq, const int* tok_pos, const int* block_table,
+                            const float* inv_freq, int n_tokens, int hq, int hkv, int head_dim, int block_size,
+                            int max_blocks_per_seq, int rot_dim, dsb200_stream_t stream);
+int dsb200_paged_attention(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
+                           const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
+                           int max_blocks_per_seq, float scale, dsb200_stream_t stream);
+int dsb200_ragged_embed(const long long* ids, const void* wte, const void* wpe, const int* tok_pos, void* out,
+                        int n_tokens, int dim, int pos_offset, dsb200_stream_t stream);
+int dsb200_logits_gather(const void* hidden, const int* last_tok, void* out, int n_seqs, int dim, dsb200_stream_t stream);
+/* expert_counts must be zeroed by the caller.  K <= 8, E <= 2048. */
+int dsb200_top_k_gating(const float* logits, int* expert_counts, float* scores, int* assignments, int* offsets,
+                        int n_tokens, int n_experts, int top_k, int normalize, dsb200_stream_t stream);
+int dsb200_moe_scatter(const void* x, const int* expert_counts, const int* assignments, const int* offsets,
+                       long long* expert_cumsum, void* moe_in, int* mapped_slots, int n_tokens, int n_experts, int dim,
+                       int top_k, dsb200_stream_t stream);
+int dsb200_moe_gather(const void* moe_out, const float* scores, const int* mapped_slots, void* out, int n_tokens, int dim,
+                      int top_k, dsb200_stream_t stream);
+
+/* ---- csrc/random_ltd/token_ops.cu */
+/* idx: int32 [rows, reserved] of unique positions in [0, seq); sorted ascending in place, row by row. */
+int dsb200_token_sort(void* idx, int rows, int reserved, int seq, dsb200_stream_t stream);
+/* part[B,R,row] (batch_first) or part[R,B,row]  <-  all[B,S,row] / all[S,B,row] at idx[B,R] */
+int dsb200_token_gather(const void* all, void* part, const void* idx, int B, int S, int R, long long row_bytes,
+                        int batch_first, dsb200_stream_t stream);
+int dsb200_token_scatter(void* all, const void* part, const void* idx, int B, int S, int R, long long row_bytes,
+                         int batch_first, dsb200_stream_t stream);
+
+/* ---- csrc/spatial/bias_add.cu */
+/* dtype: 0 = fp32, 1 = fp16, 2 = bf16.  other / other_bias may be null.  channels * sizeof(T) must be a multiple of 16. */
+int dsb200_nhwc_bias_add(const void* act, const void* bias, const void* other, const void* other_bias, void* out,
+                         long long total, int channels, int dtype, dsb200_stream_t stream);
+
+/* ==== end of generated section ==== */
+
 #ifdef __cplusplus
 }
 #endif
