@@ -59,16 +59,18 @@ def sass_summary(out_md):
                         "LDG", "STG", "LDGSTS", "MUFU", "ATOM", "RED"):
                 if op.startswith(key):
                     per[cur][key] += 1
+            if op.startswith("UTCHMMA") and ".2CTA" in op:
+                per[cur]["2CTA"] += 1
     lines = ["# SASS evidence (cuobjdump -sass libdsb200.so, sm_100a)", "",
-             "Counts of Blackwell-specific mnemonics per kernel: `UTCHMMA` = tcgen05.mma (bf16), `UTMALDG/UTMASTG/UTMAREDG` = TMA "
+             "Counts of Blackwell-specific mnemonics per kernel: `UTCHMMA` = tcgen05.mma (bf16; `.2CTA` = cta_group::2 pair MMA), `UTMALDG/UTMASTG/UTMAREDG` = TMA "
              "load/store/reduce, `LDTM/STTM` = tcgen05.ld/st, `SYNCS` = mbarrier ops, `HMMA` = legacy mma.sync (must be 0).", "",
-             "| kernel | UTCHMMA | UTMALDG | UTMASTG | UTMAREDG | LDTM | SYNCS | HMMA | LDG | STG |", "|---|---|---|---|---|---|---|---|---|---|"]
+             "| kernel | UTCHMMA | of which .2CTA | UTMALDG | UTMASTG | UTMAREDG | LDTM | SYNCS | HMMA | LDG | STG |", "|---|---|---|---|---|---|---|---|---|---|---|"]
     for k, c in sorted(per.items()):
         if sum(c.values()) == 0:
             continue
         dem = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip()
         dem = re.sub(r"\(.*", "", dem)[:90]
-        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['LDTM']} | {c['SYNCS']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
+        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['2CTA']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['LDTM']} | {c['SYNCS']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
     open(out_md, "w").write("\n".join(lines) + "\n")
 
 
