@@ -15,7 +15,7 @@ import torch.nn as nn
 
 from ..ops import fused_ops as FO
 from ..ops.attention import attention
-from ..ops.flash_attention import attention_recompute_contexts
+from ..ops import recompute as RC
 from ..ops.gemm import linear, linear_rope
 
 
@@ -32,7 +32,9 @@ class LlamaConfig:
     rope_theta: float = 10000.0
     tie_word_embeddings: bool = False
     activation_checkpointing: bool = False
-    save_attention_in_checkpoint: bool = True  # selective recompute: do not re-run the attention core in backward
+    # what a checkpointed layer keeps instead of recomputing (ops/recompute.py): full | attention | gemm | auto
+    checkpoint_policy: str = "auto"
+    save_attention_in_checkpoint: bool = True  # legacy switch: False forces checkpoint_policy = "full"
     initializer_range: float = 0.02
 
     @property
@@ -90,12 +92,13 @@ class LlamaDecoderLayer(nn.Module):
             hn = self.input_layernorm(x)
         else:
             hn, residual = self.input_layernorm(x, residual)
-        qkv = linear_rope(hn, self.qkv_proj, self.inv_freq, S, self.hq + self.hkv, self.d, positions)
+        qkv = linear_rope(hn, self.qkv_proj, self.inv_freq, S, self.hq + self.hkv, self.d, positions, tag=RC.QKV)
         attn = attention(qkv, B, S, self.hq, self.hkv, self.d, causal=True)
-        attn_out = linear(attn.view(B, S, -1), self.o_proj)
+        attn_out = linear(attn.view(B, S, -1), self.o_proj, tag=RC.O_PROJ)
         hn, residual = self.post_attention_layernorm(attn_out, residual)
-        act = FO.gated_act(linear(hn, self.gate_up_proj), "silu")
-        return linear(act, self.down_proj), residual
+        act = FO.gated_act(linear(hn, self.gate_up_proj, tag=RC.GATE_UP), "silu")
+        # the down projection's output is the layer's result: no backward formula reads it, so recomputation skips it
+        return linear(act, self.down_proj, unused_in_recompute=True), residual
 
 
 class LlamaModel(nn.Module):
@@ -108,6 +111,21 @@ class LlamaModel(nn.Module):
         self.layers = nn.ModuleList([LlamaDecoderLayer(cfg, i) for i in range(cfg.num_hidden_layers)])
         self.norm = RMSNorm(cfg.hidden_size, cfg.rms_norm_eps)
 
+    def _checkpoint_policy(self, x):
+        """Resolved once per (tokens) shape: 'auto' keeps the GEMM outputs when they fit in half of the free memory."""
+        cfg = self.cfg
+        if not cfg.save_attention_in_checkpoint:
+            return "full"
+        tokens = x.shape[0] * x.shape[1]
+        cached = getattr(self, "_policy_cache", None)
+        if cached is None or cached[0] != tokens:
+            d = cfg.head_dim
+            per_token = 2 * (cfg.num_attention_heads * d * 2 + (cfg.num_attention_heads + 2 * cfg.num_key_value_heads) * d +
+                             2 * cfg.intermediate_size)  # bf16: attn out + o_proj out + qkv + gate_up
+            kept = per_token * tokens * cfg.num_hidden_layers
+            self._policy_cache = (tokens, RC.resolve_policy(cfg.checkpoint_policy, kept))
+        return self._policy_cache[1]
+
     def forward(self, input_ids, positions=None):
         x = self.embed_tokens(input_ids)
         residual = None
@@ -115,8 +133,9 @@ class LlamaModel(nn.Module):
             if self.cfg.activation_checkpointing and self.training:
                 # per-layer checkpoint; the attention core's (out, lse) are kept and replayed during recomputation
                 kw = dict(use_reentrant=False)
-                if self.cfg.save_attention_in_checkpoint:
-                    kw["context_fn"] = attention_recompute_contexts
+                policy = self._checkpoint_policy(x)
+                if policy != "full":
+                    kw["context_fn"] = lambda policy=policy: RC.contexts(policy)
                 if residual is None:
                     x, residual = torch.utils.checkpoint.checkpoint(lambda a, l=layer: l(a, None, positions), x, **kw)
                 else:

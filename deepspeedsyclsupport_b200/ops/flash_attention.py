@@ -4,6 +4,7 @@ import math
 import torch
 
 from . import native
+from . import recompute as _rc
 from ..profiling.flops_profiler import profiler as _prof
 
 native.register_sigs({
@@ -39,49 +40,22 @@ def flash_bwd(dout, qkv, out, lse, B, S, hq, hkv, d, causal=True, scale=None):
     return dqkv
 
 
-# ---- selective activation recomputation: keep the attention core's (out, lse) across a checkpointed region ----------
-# Under activation checkpointing the whole layer is re-run in backward.  The attention core is the one op whose output
-# is small (tokens x hidden bf16 + one fp32 per row per head) compared with what it costs to recompute (O(S^2) work), so
-# the checkpoint wrapper of the model records (out, lse) in the first forward and the recompute pass replays them
-# instead of launching the forward kernel again.  `attention_recompute_contexts()` plugs into
-# torch.utils.checkpoint(..., context_fn=...).  The reference's checkpointing (activation_checkpointing/checkpointing.py)
-# recomputes everything; with 180 GB of HBM the 64 MB/layer this keeps alive for a 7B model is noise.
-_REGION = None  # (mode, list) of the checkpointed region currently executing on this thread
-
-
-class _AttnRegion(object):
-
-    def __init__(self, mode, store):
-        self.mode, self.store = mode, store
-
-    def __enter__(self):
-        global _REGION
-        self._prev = _REGION
-        _REGION = (self.mode, self.store)
-
-    def __exit__(self, *exc):
-        global _REGION
-        _REGION = self._prev
-        return False
-
-
+# Under activation checkpointing the attention core's (out, lse) can be kept across the region and replayed during
+# recomputation (ops/recompute.py); `attention_recompute_contexts` is the "attention" policy of that module.
 def attention_recompute_contexts():
-    """-> (context for the original forward, context for the recomputation) sharing one store."""
-    store = []
-    return _AttnRegion("record", store), _AttnRegion("replay", store)
+    return _rc.contexts("attention")
 
 
 class _FlashPackedFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, qkv, B, S, hq, hkv, d, causal, scale):
-        region = _REGION
-        if region is not None and region[0] == "replay" and region[1]:
-            out, lse = region[1].pop(0)
+        kept = _rc.replayed(_rc.ATTN)
+        if kept is not None:
+            out, lse = kept
         else:
             out, lse = flash_fwd(qkv, B, S, hq, hkv, d, causal, scale)
-            if region is not None and region[0] == "record":
-                region[1].append((out, lse))
+            _rc.record(_rc.ATTN, (out, lse))
         ctx.save_for_backward(qkv, out, lse)
         ctx.cfg = (B, S, hq, hkv, d, causal, scale)
         return out

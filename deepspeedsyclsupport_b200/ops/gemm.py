@@ -8,6 +8,7 @@ directly into an fp32 main-grad buffer with TMA reduce-add.
 import torch
 
 from . import native
+from . import recompute as _rc
 from ..profiling.flops_profiler import profiler as _prof
 
 
@@ -55,11 +56,17 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
 class _LinearFn(torch.autograd.Function):
 
     @staticmethod
-    def forward(ctx, x, w, w_param):
+    def forward(ctx, x, w, w_param, tag, unused_in_recompute):
         ctx.save_for_backward(x, w)
         ctx.w_param = w_param
         x2 = x.reshape(-1, x.shape[-1])
-        y = gemm(x2, w)
+        y = _rc.replayed(tag)  # kept across the checkpointed region: no GEMM during recomputation
+        if y is None:
+            if unused_in_recompute and _rc.output_unused():
+                y = torch.empty(x2.shape[0], w.shape[0], dtype=x.dtype, device=x.device)  # nobody reads it
+            else:
+                y = gemm(x2, w)
+                _rc.record(tag, y)
         return y.view(*x.shape[:-1], w.shape[0])
 
     @staticmethod
@@ -81,16 +88,16 @@ class _LinearFn(torch.autograd.Function):
                 wp.ds_main_grad_done()
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)
-        return dx, dw, None
+        return dx, dw, None, None, None
 
 
-def linear(x, w):
+def linear(x, w, tag=None, unused_in_recompute=False):
     """y = x @ w.T with w: [out, in] on the tcgen05 GEMM.  When `w` is managed by the ZeRO store, backward accumulates
     the weight gradient directly into the store's contiguous gradient buffer (no .grad tensor, no copy)."""
     if not x.is_cuda:
         return torch.nn.functional.linear(x, w)
     fused = w.requires_grad and hasattr(w, "ds_get_main_grad") and torch.is_grad_enabled()
-    return _LinearFn.apply(x, w, w if fused else None)
+    return _LinearFn.apply(x, w, w if fused else None, tag, unused_in_recompute)
 
 
 class _LinearRopeFn(torch.autograd.Function):
@@ -98,11 +105,14 @@ class _LinearRopeFn(torch.autograd.Function):
     in place on the GEMM output (forward) and on a private copy of the incoming gradient (backward)."""
 
     @staticmethod
-    def forward(ctx, x, w, w_param, inv_freq, positions, seq_len, nrot, head_dim):
+    def forward(ctx, x, w, w_param, inv_freq, positions, seq_len, nrot, head_dim, tag):
         from .fused_ops import _rope_apply
         x2 = x.reshape(-1, x.shape[-1])
-        y = gemm(x2, w)
-        _rope_apply(y, inv_freq, positions, seq_len, 0, nrot, head_dim, False)
+        y = _rc.replayed(tag)  # the kept tensor is already rotated
+        if y is None:
+            y = gemm(x2, w)
+            _rope_apply(y, inv_freq, positions, seq_len, 0, nrot, head_dim, False)
+            _rc.record(tag, y)
         ctx.save_for_backward(x, w, inv_freq, positions)
         ctx.w_param = w_param
         ctx.rope = (seq_len, nrot, head_dim)
@@ -127,10 +137,10 @@ class _LinearRopeFn(torch.autograd.Function):
                 wp.ds_main_grad_done()
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)
-        return dx, dw, None, None, None, None, None, None
+        return dx, dw, None, None, None, None, None, None, None
 
 
-def linear_rope(x, w, inv_freq, seq_len, nrot, head_dim, positions=None):
+def linear_rope(x, w, inv_freq, seq_len, nrot, head_dim, positions=None, tag=None):
     """[tokens, (hq + 2 hkv) * d] = x @ w.T with rotary embedding applied to heads [0, nrot) (q and k)."""
     if not x.is_cuda:
         from .fused_ops import rope_ref
@@ -138,4 +148,4 @@ def linear_rope(x, w, inv_freq, seq_len, nrot, head_dim, positions=None):
         pos = positions if positions is not None else torch.arange(y.shape[0], device=y.device) % seq_len
         return rope_ref(y, inv_freq, pos, 0, nrot, head_dim)
     fused = w.requires_grad and hasattr(w, "ds_get_main_grad") and torch.is_grad_enabled()
-    return _LinearRopeFn.apply(x, w, w if fused else None, inv_freq, positions, seq_len, nrot, head_dim)
+    return _LinearRopeFn.apply(x, w, w if fused else None, inv_freq, positions, seq_len, nrot, head_dim, tag)

@@ -551,36 +551,45 @@ def test_sumsq(dtype):
     assert abs(got2.item() - (ref + x[:8000].double().square().sum()).item()) <= 1e-4 * ref.item()
 
 
-def test_checkpoint_replays_saved_attention():
-    """activation checkpointing with the attention core saved (not recomputed): the flash forward kernel runs once per
-    layer instead of twice and the gradients agree with full recomputation to within the backward's own run-to-run noise
-    (its dQ reduction order is not deterministic: TMA reduce-add)."""
+def test_checkpoint_policies_skip_kernels_and_keep_gradients():
+    """Selective recomputation (ops/recompute.py): "attention" runs the flash forward once per layer and drops the unused
+    down-projection recompute; "gemm" also replays the kept qkv / o_proj / gate_up outputs.  Gradients agree with full
+    recomputation to within the backward's own run-to-run noise (its dQ reduction order is not deterministic)."""
     from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
     from deepspeedsyclsupport_b200.ops import flash_attention as FA
+    from deepspeedsyclsupport_b200.ops import gemm as G
     ids = torch.randint(0, 512, (2, 256), device=_dev())
 
-    def run(save):
+    def run(policy):
         torch.manual_seed(0)
-        cfg = llama_config("tiny", activation_checkpointing=True, save_attention_in_checkpoint=save, max_position_embeddings=256)
+        cfg = llama_config("tiny", activation_checkpointing=True, checkpoint_policy=policy, max_position_embeddings=256)
         model = LlamaForCausalLM(cfg).to(_dev()).bfloat16().train()
-        n = [0]
-        orig = FA.flash_fwd
+        n = {"attn": 0, "gemm": 0}
+        orig_attn, orig_gemm = FA.flash_fwd, G.gemm
 
-        def counting(*a, **k):
-            n[0] += 1
-            return orig(*a, **k)
+        def count_attn(*a, **k):
+            n["attn"] += 1
+            return orig_attn(*a, **k)
 
-        FA.flash_fwd = counting
+        def count_gemm(*a, **k):
+            n["gemm"] += 1
+            return orig_gemm(*a, **k)
+
+        FA.flash_fwd, G.gemm = count_attn, count_gemm
         try:
             model(ids, ids).backward()
         finally:
-            FA.flash_fwd = orig
-        return n[0], [p.grad.float().clone() for p in model.parameters()], cfg.num_hidden_layers
+            FA.flash_fwd, G.gemm = orig_attn, orig_gemm
+        return n, [p.grad.float().clone() for p in model.parameters()], cfg.num_hidden_layers
 
-    calls_a, grads_a, L = run(False)
-    _, grads_a2, _ = run(False)
-    calls_b, grads_b, _ = run(True)
-    assert calls_a == 2 * L and calls_b == L
-    for a, a2, b in zip(grads_a, grads_a2, grads_b):
+    n_full, g_full, L = run("full")
+    _, g_full2, _ = run("full")
+    n_attn, g_attn, _ = run("attention")
+    n_gemm, g_gemm, _ = run("gemm")
+    assert n_full["attn"] == 2 * L and n_attn["attn"] == L and n_gemm["attn"] == L
+    assert n_attn["gemm"] == n_full["gemm"] - L          # down projection not recomputed
+    assert n_gemm["gemm"] == n_full["gemm"] - 4 * L      # no GEMM at all during recomputation
+    for a, a2, b, c in zip(g_full, g_full2, g_attn, g_gemm):
         noise = (a - a2).abs().max()
-        assert (a - b).abs().max() <= 4 * noise + 1e-3 * a.abs().max() + 1e-7
+        tol = 4 * noise + 1e-3 * a.abs().max() + 1e-7
+        assert (a - b).abs().max() <= tol and (a - c).abs().max() <= tol
