@@ -19,6 +19,8 @@
 namespace dsb {
 namespace attn {
 
+// One softmax thread per q row.  (Two threads per row -- 8 softmax warps -- was measured slower: the step is bound by
+// shared-memory bandwidth (SS MMAs with N = 128 read 128 B/clk) and by the MMA <-> softmax hand-offs, not by softmax math.)
 constexpr int BW_THREADS = 192;
 constexpr int BW_SM_THREADS = 128;
 constexpr int BW_CHUNK = 128 * 128;  // [128 rows x 64 bf16] swizzled chunk (also [128 rows x 32 fp32])
@@ -29,8 +31,8 @@ struct BwdSmem {
   static constexpr int TILE = NCH * BW_CHUNK;
   static constexpr int K_OFF = 0;
   static constexpr int V_OFF = K_OFF + TILE;
-  static constexpr int Q_OFF = V_OFF + TILE;
-  static constexpr int DO_OFF = Q_OFF + TILE;
+  static constexpr int Q_OFF = V_OFF + TILE;             // 2 stages: Q of the next step is prefetched
+  static constexpr int DO_OFF = Q_OFF + 2 * TILE;
   static constexpr int P_OFF = DO_OFF + TILE;           // 128 x 128 bf16 = 2 chunks
   static constexpr int DS_OFF = P_OFF + 2 * BW_CHUNK;   // 128 x 128 bf16 = 2 chunks ; P+dS = 64 KB = dQ fp32 staging
   static constexpr int BAR_OFF = DS_OFF + 2 * BW_CHUNK;
@@ -43,6 +45,7 @@ struct BwdParams {
   float scale, scale_log2;
   const float* lse;    // [B, hq, S] natural log
   const float* delta;  // [B, hq, S]
+  int debug_skip_dq;   // diagnostics only (DSB200_BWD_SKIP_DQ=1): skip the dQ reduce-add to measure its cost
 };
 
 // delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]   (one warp per (token, head))
@@ -96,13 +99,15 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM::BAR_OFF);
   uint64_t* kv_full = bars + 0;
-  uint64_t* qdo_full = bars + 1;
-  uint64_t* qdo_empty = bars + 2;
-  uint64_t* sdp_full = bars + 3;
-  uint64_t* pds_full = bars + 4;
-  uint64_t* mma2_done = bars + 5;
-  uint64_t* dq_drained = bars + 6;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* q_full = bars + 1;    // [2]
+  uint64_t* q_empty = bars + 3;   // [2]
+  uint64_t* do_full = bars + 5;
+  uint64_t* do_empty = bars + 6;  // dO is dead once the dV MMAs retire: its reload overlaps the dK / dQ MMAs
+  uint64_t* sdp_full = bars + 7;
+  uint64_t* pds_full = bars + 8;
+  uint64_t* mma2_done = bars + 9;
+  uint64_t* dq_drained = bars + 10;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int jb = blockIdx.x;  // key block
@@ -122,8 +127,12 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
     tma_prefetch_desc(&tmDQ);
     tma_prefetch_desc(&tmDQKV);
     mbar_init(kv_full, 1);
-    mbar_init(qdo_full, 1);
-    mbar_init(qdo_empty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
+    }
+    mbar_init(do_full, 1);
+    mbar_init(do_empty, 1);
     mbar_init(sdp_full, 1);
     mbar_init(pds_full, BW_SM_THREADS);
     mbar_init(mma2_done, 1);
@@ -153,13 +162,16 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
         const int i = i_first + (t - g * steps_per_head);
         const int head = kv_head * group + g;
         const int qrow0 = batch * p.S + i * 128;
-        mbar_wait(qdo_empty, (t & 1) ^ 1);
-        mbar_expect_tx(qdo_full, 2 * SMEM::TILE);
+        const int st = t & 1;
+        mbar_wait(&q_empty[st], ((t >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[st], SMEM::TILE);
 #pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          tma_load_2d(&tmQKV, qdo_full, smem + SMEM::Q_OFF + c * BW_CHUNK, head * D + c * 64, qrow0);
-          tma_load_2d(&tmDO, qdo_full, smem + SMEM::DO_OFF + c * BW_CHUNK, head * D + c * 64, qrow0);
-        }
+        for (int c = 0; c < NCH; ++c)
+          tma_load_2d(&tmQKV, &q_full[st], smem + SMEM::Q_OFF + st * SMEM::TILE + c * BW_CHUNK, head * D + c * 64, qrow0);
+        mbar_wait(do_empty, (t & 1) ^ 1);
+        mbar_expect_tx(do_full, SMEM::TILE);
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) tma_load_2d(&tmDO, do_full, smem + SMEM::DO_OFF + c * BW_CHUNK, head * D + c * 64, qrow0);
       }
     }
   } else if (warp == 1) {
@@ -168,18 +180,22 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       constexpr uint32_t idesc_dkv = umma_idesc(128, D, 1, 1, 1, 1);   // P^T dO, dS^T Q: both MN-major
       constexpr uint32_t idesc_dq = umma_idesc(128, D, 1, 1, 0, 1);    // dS K          : A K-major, B MN-major
       const uint32_t k_s = smem_u32(smem + SMEM::K_OFF), v_s = smem_u32(smem + SMEM::V_OFF);
-      const uint32_t q_s = smem_u32(smem + SMEM::Q_OFF), do_s = smem_u32(smem + SMEM::DO_OFF);
+      const uint32_t q_base = smem_u32(smem + SMEM::Q_OFF), do_s = smem_u32(smem + SMEM::DO_OFF);
       const uint32_t p_s = smem_u32(smem + SMEM::P_OFF), ds_s = smem_u32(smem + SMEM::DS_OFF);
       mbar_wait(kv_full, 0);
       for (int t = 0; t < n_steps; ++t) {
-        mbar_wait(qdo_full, t & 1);
-        if (t > 0) mbar_wait(dq_drained, (t - 1) & 1);  // TMEM [0,128) and the P/dS smem (dQ staging) are free again
+        const int st = t & 1;
+        const uint32_t q_s = q_base + st * SMEM::TILE;
+        mbar_wait(&q_full[st], (t >> 1) & 1);
+        if (t > 0) mbar_wait(dq_drained, (t - 1) & 1);  // dQ of the previous step has left TMEM [0,128)
         tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
           umma_f16<1>(TM_S, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_s, kk != 0);
         }
+        mbar_wait(do_full, t & 1);
+        tc_fence_after();
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
@@ -194,6 +210,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
           umma_f16<1>(TM_DV, umma_smem_desc(p_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(do_s + kk * 2048, BW_CHUNK, 1024),
                       idesc_dkv, (t | kk) != 0);
         }
+        umma_commit<1>(do_empty);  // dO(t) fully consumed: the producer reloads it while dK / dQ run
 #pragma unroll
         for (int kk = 0; kk < 8; ++kk) {
           umma_f16<1>(TM_DK, umma_smem_desc(ds_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(q_s + kk * 2048, BW_CHUNK, 1024),
@@ -207,11 +224,12 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
                       kk != 0);
         }
         umma_commit<1>(mma2_done);
-        umma_commit<1>(qdo_empty);
+        umma_commit<1>(&q_empty[st]);
       }
     }
   } else {
     const int q4 = warp & 3;
+    constexpr int half = 0, NSPLIT = 1;  // column split across softmax threads (kept general: NSPLIT = 2 needs 8 warps)
     const int row = q4 * 32 + lane;
     const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
     const int sw = row & 7;
@@ -226,8 +244,14 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       const bool diag = p.causal && (i == jb);
       mbar_wait(sdp_full, t & 1);
       tc_fence_after();
+      if (t > 0) {
+        // the previous step's dQ staging lives in the P/dS buffers: the TMA engine must have read it before we overwrite
+        if (epi_tid == 0) tma_wait_group_read<0>();
+        named_bar_sync(1, BW_SM_THREADS);
+      }
 #pragma unroll
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 0; cc < 4 / NSPLIT; ++cc) {
+        const int c = half * (4 / NSPLIT) + cc;
         uint32_t sv[32], dv[32];
         tmem_ld_32x32(TM_S + c * 32 + lane_off, sv);
         tmem_ld_32x32(TM_DP + c * 32 + lane_off, dv);
@@ -257,31 +281,35 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       tc_fence_before();
       mbar_arrive(pds_full);
 
-      // ---- drain dQ: TMEM [0,D) fp32 -> swizzled fp32 staging (the P/dS buffers, free once mma2 retired) -> TMA reduce-add
+      // ---- drain dQ: TMEM [0,D) fp32 -> registers; the TMEM region is then free, so the MMA warp may start S/dP of the
+      // next step while this warp group stages dQ (swizzled fp32 in the P/dS buffers, free once mma2 retired) and the TMA
+      // reduce-add runs.  The staging buffers are only written again by the next step's P/dS stores, which first wait
+      // for the TMA engine to have read them (top of the loop).
       mbar_wait(mma2_done, t & 1);
       tc_fence_after();
       uint8_t* stage = smem + SMEM::P_OFF;
+      constexpr int DQ_PER = D / 32 / NSPLIT;  // 32-column chunks of dQ per thread
+      uint32_t dq[DQ_PER][32];
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(TM_S + c * 32 + lane_off, v);
-        tmem_ld_wait();
-        uint8_t* rowp = stage + c * BW_CHUNK + row * 128;
+      for (int cc = 0; cc < DQ_PER; ++cc) tmem_ld_32x32(TM_S + (half * DQ_PER + cc) * 32 + lane_off, dq[cc]);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(dq_drained);
+#pragma unroll
+      for (int cc = 0; cc < DQ_PER; ++cc) {
+        uint8_t* rowp = stage + (half * DQ_PER + cc) * BW_CHUNK + row * 128;
 #pragma unroll
         for (int u = 0; u < 8; ++u)
-          *reinterpret_cast<uint4*>(rowp + ((u ^ sw) << 4)) = make_uint4(v[4 * u], v[4 * u + 1], v[4 * u + 2], v[4 * u + 3]);
+          *reinterpret_cast<uint4*>(rowp + ((u ^ sw) << 4)) = make_uint4(dq[cc][4 * u], dq[cc][4 * u + 1], dq[cc][4 * u + 2], dq[cc][4 * u + 3]);
       }
       fence_proxy_async_smem();
-      tc_fence_before();
       named_bar_sync(1, BW_SM_THREADS);
       if (epi_tid == 0) {
         const int qrow0 = batch * p.S + i * 128;
-#pragma unroll
-        for (int c = 0; c < D / 32; ++c) tma_reduce_add_2d(&tmDQ, stage + c * BW_CHUNK, head * D + c * 32, qrow0);
+        if (!p.debug_skip_dq)
+          for (int c = 0; c < D / 32; ++c) tma_reduce_add_2d(&tmDQ, stage + c * BW_CHUNK, head * D + c * 32, qrow0);
         tma_commit_group();
-        tma_wait_group_read<0>();
       }
-      mbar_arrive(dq_drained);
     }
 
     // ---- dK, dV epilogue: TMEM -> bf16 -> swizzled staging (Q / dO tiles are dead) -> TMA store into packed dqkv
@@ -291,7 +319,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       const uint32_t tm = which == 0 ? TM_DK : TM_DV;
       uint8_t* stage = smem + (which == 0 ? SMEM::Q_OFF : SMEM::DO_OFF);
 #pragma unroll
-      for (int c = 0; c < D / 32; ++c) {
+      for (int cc = 0; cc < D / 32 / NSPLIT; ++cc) {
+        const int c = half * (D / 32 / NSPLIT) + cc;
         uint32_t v[32];
         tmem_ld_32x32(tm + c * 32 + lane_off, v);
         tmem_ld_wait();
@@ -363,6 +392,8 @@ static int launch_bwd(const void* dout, const void* qkv, const void* out, const 
   p.scale_log2 = scale * 1.4426950408889634f;
   p.lse = lse;
   p.delta = delta;
+  static const int skip_dq = [] { const char* e = getenv("DSB200_BWD_SKIP_DQ"); return e ? atoi(e) : 0; }();
+  p.debug_skip_dq = skip_dq;
   dim3 grid(S / 128, hkv, B);
   kern<<<grid, BW_THREADS, SMEM::TOTAL, stream>>>(tmQKV, tmDO, tmDQ, tmDQKV, p);
   DSB_CHECK_CUDA(cudaGetLastError());
