@@ -97,7 +97,8 @@ def ds_config(args, world):
         "optimizer": {"type": "AdamW", "params": {"lr": 1e-5, "betas": [0.9, 0.95], "eps": 1e-8, "weight_decay": 0.1}},
         "gradient_clipping": 1.0,
         "zero_optimization": {"stage": args.zero_stage, "overlap_comm": True, "contiguous_gradients": True,
-                              "stage3_prefetch_bucket_size": 5e8, "stage3_max_live_parameters": 2e9,
+                              "stage3_prefetch_bucket_size": 5e8, "stage3_max_live_parameters": 1e10,  # 180 GB GPUs: gathered bf16 weights stay live fwd -> bwd
+                              
                               "stage3_param_persistence_threshold": 1e5, "reduce_bucket_size": 5e8},
     }
 

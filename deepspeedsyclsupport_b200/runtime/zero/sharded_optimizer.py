@@ -138,6 +138,7 @@ class ZeroShardedOptimizer:
         self._skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
 
         self._opt_kind = type(self.optimizer).__name__ if self.optimizer is not None else None
+        self._fwd_keep = None
         self._local_grads_only = False
         self._step_count = 0
         self._register_grad_hooks()
@@ -587,6 +588,28 @@ class ZeroShardedOptimizer:
                 live += nu.padded
             k += 1
 
+    def _keep_after_forward(self, u):
+        """ZeRO-3 releases a unit after its forward and gathers it again for backward.  Units whose gathered size, summed
+        from their position to the END of the forward order (= the units backward needs first), fits in
+        `stage3_max_live_parameters` stay resident instead: on a 180 GB GPU a 7B model keeps everything and the backward
+        all-gathers disappear.  (Reference semantics: max_live_parameters / max_reuse_distance in
+        partitioned_param_coordinator.py:262-270,428-433.)"""
+        if not self._trace_frozen:
+            return False
+        if self._fwd_keep is None:
+            budget = int(self.zero_config.max_live_parameters)
+            keep, seen, total = {}, set(), 0
+            for uid in reversed(self._trace["fwd"]):
+                if uid in seen:
+                    continue
+                seen.add(uid)
+                nu = self.units[uid]
+                if not nu.persistent:
+                    total += nu.padded
+                keep[uid] = total <= budget
+            self._fwd_keep = keep
+        return self._fwd_keep.get(u.uid, False)
+
     def _end_of_pass(self):
         if not self._trace_frozen and self._trace["fwd"]:
             self._trace_frozen = True
@@ -630,7 +653,10 @@ class ZeroShardedOptimizer:
         def post_fwd(mod, args, out):
             if _in_backward():
                 return  # recompute inside backward: parameters are still needed for dgrad/wgrad
+            keep_ok = mod.training and torch.is_grad_enabled()
             for u in units:
+                if keep_ok and opt._keep_after_forward(u):
+                    continue  # stays gathered until its backward: no second all-gather (stage3_max_live_parameters)
                 opt.release_unit(u)
 
         def pre_bwd(mod, grad_out):

@@ -27,7 +27,9 @@ def main():
     import deepspeedsyclsupport_b200 as deepspeed
     from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
     deepspeed.init_distributed()
-    dev = torch.device("cuda", 0)
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ["LOCAL_RANK"]))
+    torch.cuda.set_device(dev)
     over = {"activation_checkpointing": True}
     if a.layers:
         over["num_hidden_layers"] = a.layers
@@ -37,7 +39,7 @@ def main():
         model = LlamaForCausalLM(cfg)
     torch.set_default_dtype(torch.float32)
     args = argparse.Namespace(micro_batch=a.micro_batch, seq_len=a.seq_len, zero_stage=3, no_act_ckpt=False, gpus=1)
-    engine, _, _, _ = deepspeed.initialize(model=model, config=bench.ds_config(args, 1))
+    engine, _, _, _ = deepspeed.initialize(model=model, config=bench.ds_config(args, world))
     ids = torch.randint(0, cfg.vocab_size, (a.micro_batch, a.seq_len), device=dev)
 
     def step():
@@ -49,9 +51,17 @@ def main():
         step()
     torch.cuda.synchronize()
     from torch.profiler import ProfilerActivity, profile
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    step()
+    t1.record()
+    torch.cuda.synchronize()
+    plain_ms = t0.elapsed_time(t1)
     with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
         step()
         torch.cuda.synchronize()
+    if rank != 0:
+        return
     agg = defaultdict(lambda: [0.0, 0])
     for ev in prof.events():
         if ev.device_type == torch.autograd.DeviceType.CUDA:
@@ -59,7 +69,7 @@ def main():
             agg[name][0] += ev.device_time_total if hasattr(ev, "device_time_total") else ev.cuda_time_total
             agg[name][1] += 1
     total = sum(v[0] for v in agg.values())
-    lines = [f"model={a.model} layers={cfg.num_hidden_layers} mb={a.micro_batch} seq={a.seq_len}: sum of GPU kernel time {total / 1e3:.1f} ms (one step, under profiler)",
+    lines = [f"model={a.model} layers={cfg.num_hidden_layers} mb={a.micro_batch} seq={a.seq_len}: sum of GPU kernel time {total / 1e3:.1f} ms (one step, under profiler); step without profiler {plain_ms:.1f} ms; world {world}",
              f"{'kernel':<90} {'calls':>6} {'ms':>9} {'%':>6}"]
     for name, (us, n) in sorted(agg.items(), key=lambda kv: -kv[1][0])[:40]:
         lines.append(f"{name[:90]:<90} {n:>6} {us / 1e3:>9.2f} {100 * us / total:>6.1f}")
