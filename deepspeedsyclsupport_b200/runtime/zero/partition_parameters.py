@@ -21,6 +21,7 @@ from .param_store import ZeroParamStatus, ZeroParamType  # noqa: F401
 
 _zero_init_context = 0
 _orig_module_apply = None
+_next_init_id = 0  # provisional ds_id given at construction (client code tests `hasattr(p, "ds_id")`); the engine renumbers
 
 
 def is_zero_param(parameter):
@@ -54,6 +55,9 @@ def _shard_one(p, group, world, rank, device, dtype):
     flat = torch.zeros(per * world, dtype=data.dtype, device=device)
     flat[:p.ds_numel].copy_(data.reshape(-1))
     p.ds_tensor = flat[rank * per:(rank + 1) * per].clone()
+    global _next_init_id
+    p.ds_id = _next_init_id
+    _next_init_id += 1
     p.ds_init_sharded = True
     p.ds_init_world = world
     p.ds_process_group = group

@@ -1,0 +1,176 @@
+"""ZeRO feature matrix on the host path (gloo): CPU offload, MiCS, ZeRO++ (qwZ / qgZ), fp16 dynamic loss scaling, frozen
+parameters, zero.Init + GatheredParameters, tensor-fragment accessors, LR schedules driven from the config.
+(reference tests: tests/unit/runtime/zero/*, tests/unit/runtime/half_precision/*, tests/unit/runtime/test_lr_schedulers.py)"""
+import copy
+
+import pytest
+import torch
+
+from common import run_distributed
+from simple_model import SimpleFrozenModel, SimpleModel, random_batches
+from test_zero_stages import _train
+
+
+def test_cpu_offload_matches_plain_adamw_two_ranks():
+    run_distributed(_train, world_size=2, args=(2, True, 1, 4, 1.0, "AdamW", {"offload_optimizer": {"device": "cpu", "pin_memory": False}}))
+
+
+def test_zero3_cpu_offload_single_process():
+    run_distributed(_train, world_size=1, args=(3, True, 2, 4, 1.0, "AdamW", {"offload_optimizer": {"device": "cpu"}}))
+
+
+def _mics_body():
+    _train(3, gas=1, steps=4, extra_zero={"mics_shard_size": 1, "stage3_param_persistence_threshold": 0})
+
+
+def test_mics_shard_group_smaller_than_world():
+    """mics_shard_size=1 at world 2: every rank holds full shards, gradients are all-reduced across the replica group."""
+    run_distributed(_mics_body, world_size=2)
+
+
+def _zeropp_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+    torch.manual_seed(3)
+    model = SimpleModel(hidden_dim=128, nlayers=2)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "zero_quantized_weights": True,
+                                 "zero_quantized_gradients": True}}
+    eng, _, _, _ = deepspeed.initialize(model=model, config=cfg)
+    losses = []
+    x, y = random_batches(1, 4, 128, seed=7 + dist.get_rank())[0]  # one fixed batch per rank: the model must fit it
+    for _ in range(12):
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+        losses.append(loss.item())
+    assert all(torch.isfinite(torch.tensor(losses)))
+    assert sum(losses[-3:]) < sum(losses[:3])  # fp8 block-scaled traffic still trains
+
+
+def test_zeropp_quantized_weights_and_gradients_train():
+    run_distributed(_zeropp_body, world_size=2)
+
+
+def _fp16_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    torch.manual_seed(0)
+    model = SimpleModel(hidden_dim=16, nlayers=2)
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+           "fp16": {"enabled": True, "initial_scale_power": 40, "loss_scale_window": 2, "hysteresis": 1, "min_loss_scale": 1},
+           "zero_optimization": {"stage": 1}}
+    eng, opt, _, _ = deepspeed.initialize(model=model, config=cfg)
+    assert next(model.parameters()).dtype == torch.float16
+    scales, skipped = [], 0
+    for x, y in random_batches(40, 4, 16, seed=5, dtype=torch.float16):
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+        scales.append(opt.cur_scale)
+        skipped += int(opt.overflow)
+    assert skipped >= 1 and eng.skipped_steps == skipped  # 2^40 overflows: steps are skipped and the scale backs off
+    assert min(scales) < 2.0**40 and scales[-1] >= min(scales)
+    assert len(scales) - skipped >= 5  # and real steps are taken once the scale fits fp16
+
+
+def test_fp16_dynamic_loss_scale_skips_and_recovers():
+    run_distributed(_fp16_body, world_size=1)
+
+
+def _frozen_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.utils.tensor_fragment import (safe_get_full_fp32_param, safe_get_full_grad, safe_get_full_optimizer_state,
+                                                                  safe_set_full_fp32_param, safe_set_full_optimizer_state)
+    torch.manual_seed(0)
+    model = SimpleFrozenModel(hidden_dim=32)
+    frozen_before = [p.detach().clone() for p in model.linears[0].parameters()]
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+    eng, _, _, _ = deepspeed.initialize(model=model, config=cfg, model_parameters=[p for p in model.parameters() if p.requires_grad])
+    x, y = random_batches(1, 4, 32, seed=2)[0]
+    loss = eng(x, y)
+    eng.backward(loss)
+    p = model.head.weight
+    g = safe_get_full_grad(p)
+    assert g is not None and g.shape == (4, 32) and g.abs().sum() > 0
+    eng.step()
+    with deepspeed.zero.GatheredParameters(list(model.linears[0].parameters())):
+        for a, b in zip(frozen_before, model.linears[0].parameters()):
+            assert torch.equal(a, b.detach())
+    w = safe_get_full_fp32_param(p)
+    assert w.shape == (4, 32) and safe_get_full_optimizer_state(p, "exp_avg").shape == (4, 32)
+    safe_set_full_fp32_param(p, torch.full_like(w, 0.25))
+    safe_set_full_optimizer_state(p, torch.zeros_like(w), "exp_avg")
+    assert torch.allclose(safe_get_full_fp32_param(p), torch.full_like(w, 0.25))
+    assert safe_get_full_optimizer_state(p, "exp_avg").abs().sum() == 0
+    with deepspeed.zero.GatheredParameters([p]):
+        assert torch.allclose(p.detach().float(), torch.full_like(w, 0.25))
+
+
+def test_frozen_params_and_fragment_accessors_two_ranks():
+    run_distributed(_frozen_body, world_size=2)
+
+
+def _init_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+    cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+           "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}}
+    torch.manual_seed(11)
+    with deepspeed.zero.Init(config_dict_or_path=cfg):
+        model = SimpleModel(hidden_dim=32, nlayers=2)
+    p = model.linears[0].weight
+    assert hasattr(p, "ds_id") and p.ds_numel == 32 * 32 and p.numel() < p.ds_numel  # partitioned at construction
+    with deepspeed.zero.GatheredParameters([p], modifier_rank=0):
+        assert p.shape == (32, 32)
+        if dist.get_rank() == 0:
+            p.data.fill_(0.5)
+    with deepspeed.zero.GatheredParameters([p]):
+        assert torch.all(p.detach() == 0.5)  # rank 0's modification reached every shard
+    eng, _, _, _ = deepspeed.initialize(model=model, config=cfg)
+    losses = []
+    x, y = random_batches(1, 4, 32, seed=1)[0]
+    for _ in range(6):
+        loss = eng(x, y)
+        eng.backward(loss)
+        eng.step()
+        losses.append(loss.item())
+    assert losses[-1] < losses[0]
+
+
+def test_zero_init_partitions_at_construction_two_ranks():
+    run_distributed(_init_body, world_size=2)
+
+
+def test_lr_schedules_from_config():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.runtime import lr_schedules as S
+    model = SimpleModel(hidden_dim=8, nlayers=1)
+    opt = torch.optim.SGD(model.parameters(), lr=1.0)
+    w = S.WarmupLR(opt, warmup_min_lr=0.0, warmup_max_lr=0.1, warmup_num_steps=10, warmup_type="linear")
+    lrs = []
+    for _ in range(12):
+        w.step()
+        lrs.append(opt.param_groups[0]["lr"])
+    assert abs(lrs[5] - 0.05) < 1e-6 and abs(lrs[-1] - 0.1) < 1e-9
+    d = S.WarmupDecayLR(opt, total_num_steps=20, warmup_min_lr=0.0, warmup_max_lr=0.1, warmup_num_steps=10, warmup_type="linear")
+    for _ in range(20):
+        d.step()
+    assert opt.param_groups[0]["lr"] < 0.011
+    c = S.WarmupCosineLR(opt, total_num_steps=20, warmup_num_steps=5, warmup_min_ratio=0.0, cos_min_ratio=0.1)
+    vals = []
+    for _ in range(20):
+        c.step()
+        vals.append(opt.param_groups[0]["lr"])
+    assert max(vals) <= 1.0 + 1e-6 and vals[-1] < vals[6]
+    oc = S.OneCycle(opt, cycle_min_lr=0.01, cycle_max_lr=0.1, cycle_first_step_size=5)
+    seq = []
+    for _ in range(10):
+        oc.step()
+        seq.append(opt.param_groups[0]["lr"])
+    assert abs(max(seq) - 0.1) < 1e-6 and seq[0] < seq[3] and seq[-1] < seq[4]
+    rt = S.LRRangeTest(opt, lr_range_test_min_lr=0.001, lr_range_test_step_size=2, lr_range_test_step_rate=1.0)
+    rt.step()
+    rt.step()
+    rt.step()
+    assert opt.param_groups[0]["lr"] > 0.001
