@@ -148,6 +148,8 @@ def is_available():
 
 
 def destroy_process_group(group=None):
+    from . import shm
+    shm.shutdown()
     if is_initialized():
         tdist.destroy_process_group(group)
 
@@ -205,7 +207,14 @@ def all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
 @timed_op
 def inference_all_reduce(tensor, op=ReduceOp.SUM, group=None, async_op=False):
     """Low-latency all-reduce entry point for TP inference (reference: ccl.cpp:540-611 SHM all-reduce on CPU).
-    On B200 the fused GEMM->all-reduce kernel in parallel/fused is the fast path; this is the NCCL form."""
+    Host tensors of a single-host group go through the shared-memory segment of comm/shm.py (csrc/host/shm_comm.cpp);
+    device tensors use NCCL here -- the peer-memory one-/two-shot kernels are reached through parallel/symm.py."""
+    from . import shm
+    if not async_op and shm.usable(tensor, op == ReduceOp.SUM or _op(op) == tdist.ReduceOp.SUM):
+        seg = shm.for_group(group)
+        if seg is not None:
+            seg.all_reduce(tensor)
+            return None
     return tdist.all_reduce(tensor, op=_op(op), group=group, async_op=async_op)
 
 

@@ -16,7 +16,7 @@ import torch
 
 from .... import comm as dist
 from ....ops import fused_ops as FO
-from ....ops.gemm import gemm
+from ....ops.gemm import gemm, moe_gemm
 from .. import kernels as K
 
 
@@ -166,11 +166,14 @@ class RaggedTransformer:
                     L["norm2_b"] = self._t(sd[p + "norm2.bias"])
             if s.num_experts:
                 L["router_w"] = sd[p + "router.weight"].to(self.device, torch.float32).contiguous()
-                L["experts"] = []
+                # expert weights stacked [E, N, K]: one grouped GEMM launch covers every expert (ops/gemm.moe_gemm)
+                gus, dns = [], []
                 for e in range(s.num_experts):
                     ep = f"{p}experts.{e}."
-                    gu = torch.cat([_shard_rows(sd[ep + "gate.weight"], r, W), _shard_rows(sd[ep + "up.weight"], r, W)], 0)
-                    L["experts"].append((self._t(gu), self._t(_shard_cols(sd[ep + "down.weight"], r, W))))
+                    gus.append(torch.cat([_shard_rows(sd[ep + "gate.weight"], r, W), _shard_rows(sd[ep + "up.weight"], r, W)], 0))
+                    dns.append(_shard_cols(sd[ep + "down.weight"], r, W))
+                L["experts_gu"] = self._t(torch.stack(gus))
+                L["experts_dn"] = self._t(torch.stack(dns))
             elif s.gated_mlp:
                 L["mlp1_w"] = self._t(torch.cat([_shard_rows(sd[p + "gate.weight"], r, W), _shard_rows(sd[p + "up.weight"], r, W)], 0))
                 L["mlp2_w"] = self._t(_shard_cols(sd[p + "down.weight"], r, W))
@@ -206,14 +209,9 @@ class RaggedTransformer:
             logits = torch.nn.functional.linear(h.float(), L["router_w"])
             counts, scores, asg, off = K.top_k_gating(logits, s.top_k, normalize=True)
             moe_in, cumsum, slots = K.moe_scatter(h, counts, asg, off)
-            moe_out = torch.empty_like(moe_in)
-            bounds = [0] + cumsum.tolist()  # host sync: per-expert row ranges drive the expert GEMM loop
-            for e, (gu, dn) in enumerate(L["experts"]):
-                a, b = bounds[e], bounds[e + 1]
-                if b > a:
-                    act = FO.gated_act(self._linear(moe_in[a:b], gu), s.activation)
-                    moe_out[a:b] = self._linear(act, dn)
-            return K.moe_gather(moe_out, scores, slots)
+            # the row ranges stay on the device: no host synchronisation between gating and the expert GEMMs
+            act = FO.gated_act(moe_gemm(moe_in, L["experts_gu"], cumsum), s.activation)
+            return K.moe_gather(moe_gemm(act, L["experts_dn"], cumsum), scores, slots)
         if s.gated_mlp:
             return self._linear(FO.gated_act(self._linear(h, L["mlp1_w"]), s.activation), L["mlp2_w"])
         a = FO.bias_act(self._linear(h, L["mlp1_w"]), L.get("mlp1_b"), s.activation)

@@ -53,6 +53,43 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
     return out
 
 
+def moe_gemm_ref(x, w, cumsum):
+    """fp32 reference: per-expert loop over the row ranges in `cumsum` (host synchronisation)."""
+    E, N, K = w.shape
+    out = torch.zeros(x.shape[0], N, dtype=x.dtype, device=x.device)
+    bounds = [0] + [int(v) for v in cumsum.tolist()]
+    for e in range(E):
+        a, b = bounds[e], min(bounds[e + 1], x.shape[0])
+        if b > a:
+            out[a:b] = (x[a:b].float() @ w[e].float().t()).to(x.dtype)
+    return out
+
+
+def moe_gemm(x, w, cumsum, out=None):
+    """Grouped expert GEMM (csrc/gemm/gemm_grouped.cu): out[r] = x[r] @ w[expert(r)]^T for rows sorted by expert.
+
+    x: [R, K] bf16;  w: [E, N, K] bf16 (stacked nn.Linear weights);  cumsum: [E] int64 inclusive cumulative rows per
+    expert (device tensor -- the kernel reads it, the host never does).  Rows beyond cumsum[-1] are not written.
+    (reference: inference/v2/kernels/cutlass_ops/moe_gemm/moe_gemm.py MoEGEMM.__call__)"""
+    if not x.is_cuda:
+        return moe_gemm_ref(x, w, cumsum)
+    assert x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and cumsum.dtype == torch.int64
+    assert x.dim() == 2 and w.dim() == 3 and x.stride(1) == 1 and w.is_contiguous() and x.shape[1] == w.shape[2]
+    R, K = x.shape
+    E, N, _ = w.shape
+    assert cumsum.numel() == E and cumsum.is_cuda
+    if out is None:
+        out = torch.empty(R, N, dtype=torch.bfloat16, device=x.device)
+    if R == 0:
+        return out
+    rc = native.lib().dsb200_moe_gemm_bf16(native.ptr(x), native.ptr(w), native.ptr(out), native.ptr(cumsum), R, N, K, E,
+                                           x.stride(0), K, out.stride(0), native.stream_ptr())
+    native.check(rc)
+    if _prof._ACTIVE:
+        _prof.record_flops(2 * R * N * K, R * N * K, "dsb200_moe_gemm_bf16")
+    return out
+
+
 class _LinearFn(torch.autograd.Function):
 
     @staticmethod

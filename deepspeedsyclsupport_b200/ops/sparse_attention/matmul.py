@@ -13,14 +13,30 @@ Modes: sdd  = dense x dense -> sparse   (scores  = Q K^T restricted to the layou
 import torch
 
 
+def build_lut(layout):
+    """(head, row block, col block) of every non-zero block + CSR row pointer over the H*M block rows, built by the host
+    library in one pass (csrc/host/sparse_lut.cpp; reference: csrc/sparse_attention/utils.cpp sdd_segment)."""
+    import ctypes
+    from .. import native
+    lay = layout.detach().to("cpu", torch.int64).contiguous()
+    H, M, N = lay.shape
+    fn = native.host_lib().dsbh_sparse_lut
+    fn.restype = ctypes.c_longlong
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int] + [ctypes.c_void_p] * 4
+    row_ptr = torch.empty(H * M + 1, dtype=torch.int64)
+    nnz = fn(lay.data_ptr(), H, M, N, None, None, None, row_ptr.data_ptr())
+    h, r, c = (torch.empty(nnz, dtype=torch.int64) for _ in range(3))
+    fn(lay.data_ptr(), H, M, N, h.data_ptr(), r.data_ptr(), c.data_ptr(), row_ptr.data_ptr())
+    return h, r, c, row_ptr
+
+
 class _Lut(object):
 
     def __init__(self, layout, block):
         self.layout = layout
         self.block = block
-        nz = layout.nonzero(as_tuple=False)  # [nnz, 3] = (head, row block, col block), sorted head / row / col
-        self.h, self.r, self.c = nz[:, 0].contiguous(), nz[:, 1].contiguous(), nz[:, 2].contiguous()
-        self.nnz = nz.shape[0]
+        self.h, self.r, self.c, self.row_ptr = build_lut(layout)  # sorted head / row / col
+        self.nnz = self.h.numel()
         self.cache = {}
 
     def on(self, device):

@@ -146,6 +146,12 @@ int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int
                         void* const* peer_shards, long long w_off, long long shard_numel, int* flags, int world,
                         dsb200_stream_t stream);
 
+/* ---- csrc/gemm/gemm_grouped.cu */
+/* C[r, :] = A[r, :] * W[expert(r)]^T for rows sorted by expert; `cum` (device, int64[E]) holds inclusive cumulative row counts.
+ * Rows at or beyond cum[E-1] are left untouched.  N must be a multiple of 8; A, W, C 16-byte aligned with 16-byte row strides. */
+int dsb200_moe_gemm_bf16(const void* A, const void* W, void* C, const long long* cum, int R, int N, int K, int E, int lda,
+                         int ldw, int ldc, dsb200_stream_t stream);
+
 /* ---- csrc/host/aio.cpp */
 void* dsbh_aio_create(int64_t block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);
 void dsbh_aio_destroy(void* hp);
@@ -171,6 +177,19 @@ int dsbh_build_atoms(const int32_t* seq_start, const int32_t* seq_ntok, const in
 /* Pack the per-token metadata of a ragged batch: tok_seq[t], tok_pos[t], last_tok[s]. */
 int dsbh_pack_batch(const int32_t* seq_ntok, const int32_t* seq_seen, int n_seqs, int32_t* tok_seq, int32_t* tok_pos,
                     int32_t* last_tok);
+
+/* ---- csrc/host/shm_comm.cpp */
+/* Creates (rank 0) or attaches to the segment `/name`.  Returns an opaque handle or nullptr. */
+void* dsbh_shm_open(const char* name, int rank, int world, long long chunk_bytes, double timeout_s);
+/* In-place sum over all ranks of `numel` elements at `data`.  Returns 0, 1 (bad argument) or 2 (peer timeout). */
+int dsbh_shm_allreduce(void* handle, void* data, long long numel, int dtype, double timeout_s);
+int dsbh_shm_barrier(void* handle, double timeout_s);
+void dsbh_shm_close(void* handle);
+
+/* ---- csrc/host/sparse_lut.cpp */
+/* Returns the number of non-zero blocks.  With out_h == nullptr only counts (and fills row_ptr if given). */
+long long dsbh_sparse_lut(const int64_t* layout, int H, int M, int N, int64_t* out_h, int64_t* out_r, int64_t* out_c,
+                          int64_t* row_ptr);
 
 /* ---- csrc/quant/onebit.cu */
 /* x[n] fp32 (read only), err[n] fp32 (error feedback, updated), packed[n/8], scale_io[2] fp32 device scratch:

@@ -108,3 +108,46 @@ def test_blocked_allocator_and_atoms():
     assert atoms.shape == (4, 6)
     assert atoms[2].tolist() == [0, 256, 44, 5, 300, 256]
     assert atoms[3].tolist() == [1, 300, 1, 2, 78, 77]
+
+
+def _shm_body():
+    import torch
+    import deepspeedsyclsupport_b200.comm as dist
+    from deepspeedsyclsupport_b200.comm import shm
+    rank, world = dist.get_rank(), dist.get_world_size()
+    seg = shm.for_group(None)
+    assert seg is not None and seg.world == world
+    for dtype, n in ((torch.float32, 1000), (torch.bfloat16, 3 * (1 << 20) + 17), (torch.float16, 33), (torch.int32, 5)):
+        g = torch.Generator().manual_seed(5)
+        parts = [(torch.randn(n, generator=g) * 4).to(dtype) if dtype != torch.int32 else torch.arange(n, dtype=dtype) * (r + 1)
+                 for r in range(world)]
+        want = parts[0].float()
+        for p in parts[1:]:
+            want = want + p.float()
+        t = parts[rank].clone()
+        assert dist.inference_all_reduce(t) is None
+        tol = {torch.float32: 1e-6, torch.bfloat16: 2e-2, torch.float16: 2e-3, torch.int32: 0}[dtype]
+        assert (t.float() - want).abs().max() <= tol * max(1.0, want.abs().max().item())
+    # a non-contiguous tensor falls back to the backend collective and still sums
+    x = torch.ones(4, 6)[:, ::2] * (rank + 1)
+    dist.inference_all_reduce(x)
+    assert torch.all(x == sum(range(1, world + 1)))
+    seg.barrier()
+
+
+def test_shm_all_reduce_three_ranks():
+    """POSIX-shm all-reduce (csrc/host/shm_comm.cpp): several dtypes, multi-chunk sizes, fallback for strided tensors."""
+    from common import run_distributed
+    run_distributed(_shm_body, world_size=3)
+
+
+def test_sparse_lut_matches_nonzero():
+    import torch
+    from deepspeedsyclsupport_b200.ops.sparse_attention.matmul import build_lut
+    torch.manual_seed(0)
+    layout = (torch.rand(3, 7, 9) < 0.3).long()
+    h, r, c, rp = build_lut(layout)
+    nz = layout.nonzero()
+    assert torch.equal(torch.stack([h, r, c], 1), nz)
+    counts = layout.view(21, 9).sum(1)
+    assert torch.equal(rp[1:] - rp[:-1], counts) and rp[-1] == nz.shape[0]

@@ -101,3 +101,73 @@ def test_scheduling_limits_and_splitfuse():
             assert nxt == t
             seq = torch.cat([seq, torch.tensor([t])])
     assert eng.free_blocks == 40
+
+
+MOE_CFG = dict(CFG, num_local_experts=4, num_experts_per_tok=2)
+
+
+def _hf_mixtral_state(cfg, seed=0):
+    sd = _hf_llama_state(cfg, seed)
+    g = torch.Generator().manual_seed(seed + 100)
+    h, inter = cfg["hidden_size"], cfg["intermediate_size"]
+    r = lambda *s: torch.randn(*s, generator=g) * 0.05
+    for i in range(cfg["num_hidden_layers"]):
+        p = f"model.layers.{i}."
+        for k in ("gate_proj", "up_proj", "down_proj"):
+            del sd[p + f"mlp.{k}.weight"]
+        sd[p + "block_sparse_moe.gate.weight"] = r(cfg["num_local_experts"], h) * 10
+        for e in range(cfg["num_local_experts"]):
+            ep = f"{p}block_sparse_moe.experts.{e}."
+            sd[ep + "w1.weight"], sd[ep + "w2.weight"], sd[ep + "w3.weight"] = r(inter, h), r(h, inter), r(inter, h)
+    return sd
+
+
+def _dense_mixtral_logits(sd, cfg, ids):
+    """the Llama reference with the MLP swapped for a dense evaluation of the top-2 mixture"""
+    import torch.nn.functional as F
+    E, k = cfg["num_local_experts"], cfg["num_experts_per_tok"]
+    from deepspeedsyclsupport_b200.ops.fused_ops import rope_inv_freq, rope_ref
+    h, hq, hkv = cfg["hidden_size"], cfg["num_attention_heads"], cfg["num_key_value_heads"]
+    d = h // hq
+    S = ids.numel()
+    x = sd["model.embed_tokens.weight"][ids].float()
+    inv, pos = rope_inv_freq(d), torch.arange(S)
+    rms = lambda t, w: t * torch.rsqrt(t.pow(2).mean(-1, keepdim=True) + 1e-5) * w
+    for i in range(cfg["num_hidden_layers"]):
+        p = f"model.layers.{i}."
+        hn = rms(x, sd[p + "input_layernorm.weight"])
+        qkv = torch.cat([hn @ sd[p + "self_attn.q_proj.weight"].t(), hn @ sd[p + "self_attn.k_proj.weight"].t(),
+                         hn @ sd[p + "self_attn.v_proj.weight"].t()], -1)
+        qkv = rope_ref(qkv, inv, pos, 0, hq + hkv, d)
+        q, kk, v = qkv.view(S, hq + 2 * hkv, d).split([hq, hkv, hkv], 1)
+        o = F.scaled_dot_product_attention(q.transpose(0, 1)[None], kk.transpose(0, 1).repeat_interleave(hq // hkv, 0)[None],
+                                           v.transpose(0, 1).repeat_interleave(hq // hkv, 0)[None], is_causal=True)[0]
+        x = x + o.transpose(0, 1).reshape(S, -1) @ sd[p + "self_attn.o_proj.weight"].t()
+        hn = rms(x, sd[p + "post_attention_layernorm.weight"])
+        probs = F.softmax(hn @ sd[p + "block_sparse_moe.gate.weight"].t(), -1)
+        top, idx = probs.topk(k, -1)
+        top = top / top.sum(-1, keepdim=True)
+        y = torch.zeros_like(hn)
+        for e in range(E):
+            ep = f"{p}block_sparse_moe.experts.{e}."
+            ye = (F.silu(hn @ sd[ep + "w1.weight"].t()) * (hn @ sd[ep + "w3.weight"].t())) @ sd[ep + "w2.weight"].t()
+            wgt = (top * (idx == e)).sum(-1, keepdim=True)
+            y = y + wgt * ye
+        x = x + y
+    return rms(x, sd["model.norm.weight"]) @ sd["lm_head.weight"].t()
+
+
+def test_ragged_mixtral_grouped_experts_match_dense():
+    """top-2 MoE through gating -> scatter -> grouped expert GEMM -> gather (reference: model_implementations/mixtral)."""
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 64, "max_ragged_sequence_count": 8, "max_context": 128,
+                                                      "memory_config": {"mode": "allocate", "size": 40}})
+    sd = _hf_mixtral_state(MOE_CFG)
+    eng = build_engine_from_state_dict("mixtral", MOE_CFG, sd, ecfg, dtype=torch.float32)
+    torch.manual_seed(4)
+    a, b = torch.randint(0, 97, (19, )), torch.randint(0, 97, (6, ))
+    ref_a, ref_b = _dense_mixtral_logits(sd, MOE_CFG, a), _dense_mixtral_logits(sd, MOE_CFG, b)
+    out = eng.put([1, 2], [a[:18], b])
+    assert torch.allclose(out[0], ref_a[17], atol=5e-3) and torch.allclose(out[1], ref_b[5], atol=5e-3)
+    out = eng.put([1], [a[18:19]])
+    assert torch.allclose(out[0], ref_a[18], atol=5e-3)

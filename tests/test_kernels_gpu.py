@@ -593,3 +593,45 @@ def test_checkpoint_policies_skip_kernels_and_keep_gradients():
         noise = (a - a2).abs().max()
         tol = 4 * noise + 1e-3 * a.abs().max() + 1e-7
         assert (a - b).abs().max() <= tol and (a - c).abs().max() <= tol
+
+
+@pytest.mark.parametrize("case", [
+    # (rows per expert, N, K)
+    ([5, 0, 131, 128, 1, 300, 0, 77], 384, 256),      # empties, exact tile, tails, N = 3 n-blocks of 128
+    ([1, 1, 1, 1], 264, 64),                          # decode-sized, N not a multiple of the n-block
+    ([700, 513, 1024, 260], 1024, 512),               # wide-tile variant (>= 256 rows per expert on average)
+    ([0, 0, 0, 9], 128, 128),
+])
+def test_moe_grouped_gemm(case):
+    from deepspeedsyclsupport_b200.ops.gemm import moe_gemm, moe_gemm_ref
+    rows, N, K = case
+    E, R = len(rows), sum(rows)
+    torch.manual_seed(0)
+    pad = 37  # rows past cumsum[-1] (capacity padding) must stay untouched
+    x = torch.randn(R + pad, K, device=_dev(), dtype=torch.bfloat16)
+    w = torch.randn(E, N, K, device=_dev(), dtype=torch.bfloat16) * 0.1
+    cum = torch.tensor(rows, device=_dev()).cumsum(0)
+    out = torch.full((R + pad, N), 7.0, device=_dev(), dtype=torch.bfloat16)
+    moe_gemm(x, w, cum, out=out)
+    ref = moe_gemm_ref(x.float(), w.float(), cum)
+    assert (out[:R].float() - ref[:R]).abs().max() <= 1e-2 * ref.abs().max()
+    assert torch.all(out[R:] == 7.0)
+
+
+def test_ragged_mixtral_engine_bf16_gpu():
+    """v2 engine, Mixtral family on the device: gating / scatter / grouped GEMM / gather kernels vs the fp32 dense mixture."""
+    from test_inference_v2 import MOE_CFG, _dense_mixtral_logits, _hf_mixtral_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    cfg = dict(MOE_CFG, hidden_size=256, intermediate_size=512, num_attention_heads=4, num_key_value_heads=2)
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 256, "max_ragged_sequence_count": 8, "max_context": 256,
+                                                      "memory_config": {"mode": "allocate", "size": 40}})
+    sd = _hf_mixtral_state(cfg)
+    eng = build_engine_from_state_dict("mixtral", cfg, sd, ecfg, dtype=torch.bfloat16)
+    torch.manual_seed(4)
+    a, b = torch.randint(0, 97, (150, )), torch.randint(0, 97, (6, ))
+    ref_a, ref_b = _dense_mixtral_logits(sd, cfg, a), _dense_mixtral_logits(sd, cfg, b)
+    out = eng.put([1, 2], [a[:149], b])
+    tol = 0.06 * ref_a.abs().max()
+    assert (out[0].float().cpu() - ref_a[148]).abs().max() < tol and (out[1].float().cpu() - ref_b[5]).abs().max() < tol
+    out = eng.put([1], [a[149:150]])
+    assert (out[0].float().cpu() - ref_a[149]).abs().max() < tol
