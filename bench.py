@@ -114,8 +114,8 @@ def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, l
                    "global_batch": args.micro_batch * world, "seq_len": args.seq_len, "micro_batch_per_gpu": args.micro_batch,
                    "parallelism": f"zero{args.zero_stage}-dp{world}", "optimizer": "AdamW", "grad_clip": 1.0,
                    "activation_checkpointing": (False if args.no_act_ckpt else
-                                                ("per-layer checkpoint, selective recompute: attention and GEMM outputs kept when they fit in half of the free HBM "
-                                                 "(policy auto), norms / RoPE / SwiGLU recomputed" if impl == "own"
+                                                ("policy auto (ops/recompute.py): no recomputation when every saved activation fits in 60 % of the free HBM, "
+                                                 "else per-layer checkpoint keeping attention + GEMM outputs (norms / RoPE / SwiGLU recomputed)" if impl == "own"
                                                  else "per-layer full recompute (HF gradient_checkpointing)")),
                    "l2_policy": "working set (weights+activations, >13 GB) far exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_tps, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -214,7 +214,11 @@ def run_own(args):
                  "model_flops_per_token": model.flops_per_token(S, with_recompute=False)}  # 6*P + attention, no recompute credit
         tps = world * B * S / (ms / 1e3)
         extra["tflops_per_gpu"] = round(tps / world * extra["model_flops_per_token"] / 1e12, 1)
-        print(json.dumps(result_line(args, "own", world, world * B * S, ms, e2e, h2d, 4, launches, clocks, extra)), flush=True)
+        line = result_line(args, "own", world, world * B * S, ms, e2e, h2d, 4, launches, clocks, extra)
+        resolved = getattr(model.model, "_policy_cache", (None, None))[1]
+        if resolved is not None and not args.no_act_ckpt:
+            line["config"]["activation_checkpointing"] += f"; resolved on this run: '{resolved}'"
+        print(json.dumps(line), flush=True)
 
 
 def run_reference(args):

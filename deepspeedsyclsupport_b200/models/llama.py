@@ -112,28 +112,31 @@ class LlamaModel(nn.Module):
         self.norm = RMSNorm(cfg.hidden_size, cfg.rms_norm_eps)
 
     def _checkpoint_policy(self, x):
-        """Resolved once per (tokens) shape: 'auto' keeps the GEMM outputs when they fit in half of the free memory."""
+        """Resolved once per (tokens) shape.  'auto': no checkpointing at all when every saved activation fits in 60 % of
+        the free memory, else keep the GEMM outputs when they fit in half of it, else keep the attention core only."""
         cfg = self.cfg
         if not cfg.save_attention_in_checkpoint:
             return "full"
         tokens = x.shape[0] * x.shape[1]
         cached = getattr(self, "_policy_cache", None)
         if cached is None or cached[0] != tokens:
-            d = cfg.head_dim
-            per_token = 2 * (cfg.num_attention_heads * d * 2 + (cfg.num_attention_heads + 2 * cfg.num_key_value_heads) * d +
-                             2 * cfg.intermediate_size)  # bf16: attn out + o_proj out + qkv + gate_up
+            d, h, inter = cfg.head_dim, cfg.hidden_size, cfg.intermediate_size
+            qkv = (cfg.num_attention_heads + 2 * cfg.num_key_value_heads) * d
+            per_token = 2 * (cfg.num_attention_heads * d + h + qkv + 2 * inter)  # bf16: attn out + o_proj out + qkv + gate_up
             kept = per_token * tokens * cfg.num_hidden_layers
-            self._policy_cache = (tokens, RC.resolve_policy(cfg.checkpoint_policy, kept))
+            # everything autograd saves without checkpointing: 2 residuals, 2 norm outputs, qkv, attn out, gate_up, swiglu out
+            everything = 2 * (4 * h + qkv + cfg.num_attention_heads * d + 3 * inter) * tokens * cfg.num_hidden_layers
+            self._policy_cache = (tokens, RC.resolve_policy(cfg.checkpoint_policy, kept, everything))
         return self._policy_cache[1]
 
     def forward(self, input_ids, positions=None):
         x = self.embed_tokens(input_ids)
         residual = None
         for layer in self.layers:
-            if self.cfg.activation_checkpointing and self.training:
+            policy = self._checkpoint_policy(x) if (self.cfg.activation_checkpointing and self.training) else "none"
+            if policy != "none":
                 # per-layer checkpoint; the attention core's (out, lse) are kept and replayed during recomputation
                 kw = dict(use_reentrant=False)
-                policy = self._checkpoint_policy(x)
                 if policy != "full":
                     kw["context_fn"] = lambda policy=policy: RC.contexts(policy)
                 if residual is None:

@@ -40,7 +40,9 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
     assert K == Kb, f"K mismatch {K} vs {Kb}"
     if out is None:
         assert not accumulate
-        out = torch.empty(M, N, dtype=out_dtype, device=a.device)
+        align = 16 // torch.empty((), dtype=out_dtype).element_size()  # TMA needs 16-byte row strides
+        ld = (N + align - 1) // align * align
+        out = torch.empty(M, ld, dtype=out_dtype, device=a.device)[:, :N]  # e.g. a vocabulary of 50257: padded rows, [M, N] view
     assert out.shape == (M, N) and out.stride(1) == 1
     f32 = out.dtype == torch.float32
     mode = (2 if accumulate else 1) if f32 else (3 if accumulate else 0)

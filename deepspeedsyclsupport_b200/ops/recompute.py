@@ -14,7 +14,9 @@ Policies (`LlamaConfig.checkpoint_policy`):
     "full"       recompute everything (reference behaviour, activation_checkpointing/checkpointing.py)
     "attention"  keep the attention core's (out, lse)
     "gemm"       keep attention + every GEMM output of the layer (qkv, o, gate_up); only norms / rope / swiglu re-run
-    "auto"       "gemm" if the kept bytes fit in half of the free device memory at first use, else "attention"
+    "none"       no checkpointing: every activation autograd saves stays resident (nothing is recomputed)
+    "auto"       "none" if all saved activations fit in 60 % of the free device memory at first use, else "gemm" if the
+                 kept bytes fit in half of it, else "attention"
 The last GEMM of a layer is never recomputed under any policy but "full" (its output is not needed by backward).
 """
 import torch
@@ -80,11 +82,14 @@ def output_unused():
     return r is not None and r.mode == "replay" and r.skip_unused
 
 
-def resolve_policy(policy, kept_bytes_if_gemm):
+def resolve_policy(policy, kept_bytes_if_gemm, bytes_if_none=None):
     if policy != "auto":
-        assert policy in POLICIES, f"unknown checkpoint_policy {policy}"
+        assert policy in POLICIES or policy == "none", f"unknown checkpoint_policy {policy}"
         return policy
     if torch.cuda.is_available():
         free, _ = torch.cuda.mem_get_info()
+        free += torch.cuda.memory_reserved() - torch.cuda.memory_allocated()  # cached blocks are reusable
+        if bytes_if_none is not None and bytes_if_none <= 0.6 * free:
+            return "none"
         return "gemm" if kept_bytes_if_gemm <= free // 2 else "attention"
     return "attention"

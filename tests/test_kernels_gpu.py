@@ -586,13 +586,30 @@ def test_checkpoint_policies_skip_kernels_and_keep_gradients():
     _, g_full2, _ = run("full")
     n_attn, g_attn, _ = run("attention")
     n_gemm, g_gemm, _ = run("gemm")
+    n_none, g_none, _ = run("none")
     assert n_full["attn"] == 2 * L and n_attn["attn"] == L and n_gemm["attn"] == L
+    assert n_none["attn"] == L and n_none["gemm"] == n_full["gemm"] - 4 * L  # "none": nothing is recomputed
+    for a, a2, d in zip(g_full, g_full2, g_none):
+        assert (a - d).abs().max() <= 4 * (a - a2).abs().max() + 1e-3 * a.abs().max() + 1e-7
     assert n_attn["gemm"] == n_full["gemm"] - L          # down projection not recomputed
     assert n_gemm["gemm"] == n_full["gemm"] - 4 * L      # no GEMM at all during recomputation
     for a, a2, b, c in zip(g_full, g_full2, g_attn, g_gemm):
         noise = (a - a2).abs().max()
         tol = 4 * noise + 1e-3 * a.abs().max() + 1e-7
         assert (a - b).abs().max() <= tol and (a - c).abs().max() <= tol
+
+
+def test_gemm_odd_output_width():
+    """N not a multiple of 8 (a 97- or 50257-entry vocabulary): the wrapper pads the row stride, TMA clips the columns."""
+    from deepspeedsyclsupport_b200.ops.gemm import gemm
+    torch.manual_seed(0)
+    a = torch.randn(150, 64, device=_dev(), dtype=torch.bfloat16)
+    b = torch.randn(97, 64, device=_dev(), dtype=torch.bfloat16)
+    c = gemm(a, b)
+    ref = a.float() @ b.float().t()
+    assert c.shape == (150, 97) and (c.float() - ref).abs().max() <= 1e-2 * ref.abs().max()
+    c32 = gemm(a, b, out_dtype=torch.float32)
+    assert (c32 - ref).abs().max() <= 1e-4 * ref.abs().max()
 
 
 @pytest.mark.parametrize("case", [
@@ -631,7 +648,20 @@ def test_ragged_mixtral_engine_bf16_gpu():
     a, b = torch.randint(0, 97, (150, )), torch.randint(0, 97, (6, ))
     ref_a, ref_b = _dense_mixtral_logits(sd, cfg, a), _dense_mixtral_logits(sd, cfg, b)
     out = eng.put([1, 2], [a[:149], b])
-    tol = 0.06 * ref_a.abs().max()
-    assert (out[0].float().cpu() - ref_a[148]).abs().max() < tol and (out[1].float().cpu() - ref_b[5]).abs().max() < tol
+    # the same engine with the experts evaluated by a per-expert loop: isolates the grouped kernel from bf16 routing flips
+    import deepspeedsyclsupport_b200.inference.v2.model_implementations.ragged_transformer as RT
+    from deepspeedsyclsupport_b200.ops.gemm import moe_gemm_ref
+    grouped = RT.moe_gemm
+    RT.moe_gemm = lambda x, w, c, out=None: moe_gemm_ref(x, w, c)
+    try:
+        eng2 = build_engine_from_state_dict("mixtral", cfg, sd, ecfg, dtype=torch.bfloat16)
+        out2 = eng2.put([1, 2], [a[:149], b])
+    finally:
+        RT.moe_gemm = grouped
+    scale = ref_a.abs().max()
+    assert (out[0].float() - out2[0].float()).abs().max() < 0.02 * scale and (out[1].float() - out2[1].float()).abs().max() < 0.02 * scale
+    # against the fp32 dense mixture (a near-tie in the bf16 router may pick another expert for sequence b's last token)
+    assert (out[0].float().cpu() - ref_a[148]).abs().max() < 0.06 * scale
+    assert (out[1].float().cpu() - ref_b[5]).abs().max() < 0.15 * scale
     out = eng.put([1], [a[149:150]])
-    assert (out[0].float().cpu() - ref_a[149]).abs().max() < tol
+    assert (out[0].float().cpu() - ref_a[149]).abs().max() < 0.06 * scale
