@@ -10,6 +10,8 @@
 // Epilogue: O / l -> bf16 -> swizzled smem -> TMA store into [tokens, hq*D]; LSE (natural log) saved for backward.
 // Replaces csrc/transformer/softmax_kernels.cu + the strided-batched cuBLAS QK^T / PV of the reference's training
 // kernel (ds_transformer_cuda.cpp) and the user-supplied FlashAttention of its Ulysses path (sequence/layer.py:84).
+#include <stdlib.h>
+
 #include "../common/host.h"
 #include "../common/ptx.cuh"
 
@@ -304,7 +306,18 @@ static int launch_fwd(const void* qkv, void* out, float* lse, int B, int S, int 
 }
 
 }  // namespace attn
+
+// second-generation kernel (flash_fwd2.cu): two Q tiles per CTA, P / O in TMEM
+int flash_fwd2_launch(const void* qkv, void* out, float* lse, int B, int S, int hq, int hkv, int head_dim, int causal, float scale,
+                      cudaStream_t stream);
+void flash_fwd2_set_trace(long long* buf);
 }  // namespace dsb
+
+// debug hook: device buffer (>= 8192 int64) receiving clock64 stamps of one CTA of the next forward launches; nullptr = off
+DSB_EXPORT int dsb200_flash_fwd_trace(long long* buf) {
+  dsb::flash_fwd2_set_trace(buf);
+  return DSB_OK;
+}
 
 // out[B*S, hq*D] = softmax(Q K^T * scale [+ causal mask]) V with Q,K,V read from packed qkv [B*S, (hq+2*hkv)*D] (bf16).
 // lse: optional [B, hq, S] fp32 (natural-log sum-exp of the scaled scores) for the backward pass.
@@ -314,6 +327,12 @@ DSB_EXPORT int dsb200_flash_attn_fwd(const void* qkv, void* out, float* lse, int
   DSB_REQUIRE(head_dim == 64 || head_dim == 128, "flash_attn: head_dim %d unsupported (64 or 128)", head_dim);
   DSB_REQUIRE(S % 128 == 0 && S > 0, "flash_attn: sequence length %d must be a multiple of 128", S);
   DSB_REQUIRE(hq % hkv == 0, "flash_attn: hq %d not a multiple of hkv %d", hq, hkv);
+  // DSB200_FLASH_FWD=1 forces the first-generation kernel (one Q tile per CTA); sequences that are not a multiple of 256 use it too
+  static const int variant = [] {
+    const char* e = getenv("DSB200_FLASH_FWD");
+    return e ? atoi(e) : 0;
+  }();
+  if (variant != 1 && S % 256 == 0) return flash_fwd2_launch(qkv, out, lse, B, S, hq, hkv, head_dim, causal, scale, stream);
   if (head_dim == 128) return attn::launch_fwd<128>(qkv, out, lse, B, S, hq, hkv, causal, scale, stream);
   return attn::launch_fwd<64>(qkv, out, lse, B, S, hq, hkv, causal, scale, stream);
 }
