@@ -25,6 +25,34 @@ constexpr int BW_THREADS = 192;
 constexpr int BW_SM_THREADS = 128;
 constexpr int BW_CHUNK = 128 * 128;  // [128 rows x 64 bf16] swizzled chunk (also [128 rows x 32 fp32])
 
+// spin without the diagnostic printf of mbar_wait (its argument buffer costs stack and registers in the issue loop)
+__device__ __forceinline__ void bwd_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ float bwd_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__device__ __forceinline__ uint64_t bw_pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void bw_unpack2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t bw_fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t bw_mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
 template <int D>
 struct BwdSmem {
   static constexpr int NCH = D / 64;
@@ -34,7 +62,7 @@ struct BwdSmem {
   static constexpr int Q_OFF = V_OFF + TILE;             // 2 stages: Q of the next step is prefetched
   static constexpr int DO_OFF = Q_OFF + 2 * TILE;
   static constexpr int P_OFF = DO_OFF + TILE;           // 128 x 128 bf16 = 2 chunks
-  static constexpr int DS_OFF = P_OFF + 2 * BW_CHUNK;   // 128 x 128 bf16 = 2 chunks ; P+dS = 64 KB = dQ fp32 staging
+  static constexpr int DS_OFF = P_OFF + 2 * BW_CHUNK;   // 128 x 128 bf16 = 2 chunks
   static constexpr int BAR_OFF = DS_OFF + 2 * BW_CHUNK;
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;
 };
@@ -46,7 +74,11 @@ struct BwdParams {
   const float* lse;    // [B, hq, S] natural log
   const float* delta;  // [B, hq, S]
   int debug_skip_dq;   // diagnostics only (DSB200_BWD_SKIP_DQ=1): skip the dQ reduce-add to measure its cost
+  long long* trace;    // debug: clock64 stamps of CTA (0,0,0), [step][16 events]; nullptr in production
 };
+#define BWD_TRACE(ev, t) \
+  if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (t) < 256) p.trace[(t) * 16 + (ev)] = clock64();
+static long long* g_bwd_trace = nullptr;
 
 // delta[b,h,s] = sum_d dO[b,s,h,d] * O[b,s,h,d]   (one warp per (token, head))
 __global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ dout, const __nv_bfloat16* __restrict__ out,
@@ -107,7 +139,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
   uint64_t* pds_full = bars + 8;
   uint64_t* mma2_done = bars + 9;
   uint64_t* dq_drained = bars + 10;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 12);
+  uint64_t* q_stage_free = bars + 11;  // [2] the dQ staging that borrowed Q slot st has been read by the TMA engine
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int jb = blockIdx.x;  // key block
@@ -137,6 +170,8 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
     mbar_init(pds_full, BW_SM_THREADS);
     mbar_init(mma2_done, 1);
     mbar_init(dq_drained, BW_SM_THREADS);
+    mbar_init(&q_stage_free[0], 1);
+    mbar_init(&q_stage_free[1], 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -164,6 +199,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
         const int qrow0 = batch * p.S + i * 128;
         const int st = t & 1;
         mbar_wait(&q_empty[st], ((t >> 1) & 1) ^ 1);
+        if (t >= 2) mbar_wait(&q_stage_free[st], ((t >> 1) - 1) & 1);  // dQ(t-2) was staged through this slot
         mbar_expect_tx(&q_full[st], SMEM::TILE);
 #pragma unroll
         for (int c = 0; c < NCH; ++c)
@@ -175,56 +211,70 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    // The whole warp walks the loop convergently and one elected lane issues; operands are formed from kernel-uniform
+    // values with a low-word add per MMA (an `if (lane == 0)` region made every descriptor a per-thread value that had
+    // to be broadcast into uniform registers: ~100 cycles of issue overhead per 64-cycle MMA).
+    {
       constexpr uint32_t idesc_s = umma_idesc(128, 128, 1, 1, 0, 0);   // Q K^T, dO V^T : both K-major
       constexpr uint32_t idesc_dkv = umma_idesc(128, D, 1, 1, 1, 1);   // P^T dO, dS^T Q: both MN-major
       constexpr uint32_t idesc_dq = umma_idesc(128, D, 1, 1, 0, 1);    // dS K          : A K-major, B MN-major
-      const uint32_t k_s = smem_u32(smem + SMEM::K_OFF), v_s = smem_u32(smem + SMEM::V_OFF);
-      const uint32_t q_base = smem_u32(smem + SMEM::Q_OFF), do_s = smem_u32(smem + SMEM::DO_OFF);
-      const uint32_t p_s = smem_u32(smem + SMEM::P_OFF), ds_s = smem_u32(smem + SMEM::DS_OFF);
-      mbar_wait(kv_full, 0);
+      constexpr uint32_t HI = (1024u >> 4) | (1u << 14) | (2u << 29);  // SBO 1024, descriptor version, SWIZZLE_128B
+      constexpr uint32_t KM = (16u >> 4) << 16;                         // K-major : LBO 16
+      constexpr uint32_t MN = (uint32_t(BW_CHUNK) >> 4) << 16;          // MN-major: LBO = chunk stride
+      auto desc = [](uint32_t lo) { return (static_cast<uint64_t>(HI) << 32) | lo; };
+      const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const bool leader = elect_one();
+      const uint32_t base = smem_u32(smem);
+      const uint32_t k_a = (base + SMEM::K_OFF) >> 4, v_a = (base + SMEM::V_OFF) >> 4, do_a = (base + SMEM::DO_OFF) >> 4;
+      const uint32_t p_a = (base + SMEM::P_OFF) >> 4, ds_a = (base + SMEM::DS_OFF) >> 4;
+      bwd_wait(kv_full, 0);
       for (int t = 0; t < n_steps; ++t) {
         const int st = t & 1;
-        const uint32_t q_s = q_base + st * SMEM::TILE;
-        mbar_wait(&q_full[st], (t >> 1) & 1);
-        if (t > 0) mbar_wait(dq_drained, (t - 1) & 1);  // dQ of the previous step has left TMEM [0,128)
+        const uint32_t q_a = (base + SMEM::Q_OFF + st * SMEM::TILE) >> 4;
+        bwd_wait(&q_full[st], (t >> 1) & 1);
+        if (t > 0) bwd_wait(dq_drained, (t - 1) & 1);  // dQ of the previous step has left TMEM [0,128)
         tc_fence_after();
+        if (leader) {
+          BWD_TRACE(0, t)
 #pragma unroll
-        for (int kk = 0; kk < D / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
-          umma_f16<1>(TM_S, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_s, kk != 0);
+          for (int kk = 0; kk < D / 16; ++kk) {
+            const uint32_t off = ((kk >> 2) * BW_CHUNK + (kk & 3) * 32) >> 4;
+            umma_f16<1>(tm, desc(KM | (q_a + off)), desc(KM | (k_a + off)), idesc_s, kk != 0);
+          }
         }
-        mbar_wait(do_full, t & 1);
+        bwd_wait(do_full, t & 1);
         tc_fence_after();
+        if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < D / 16; ++kk) {
-          const uint32_t off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
-          umma_f16<1>(TM_DP, umma_smem_desc(do_s + off, 16, 1024), umma_smem_desc(v_s + off, 16, 1024), idesc_s, kk != 0);
+          for (int kk = 0; kk < D / 16; ++kk) {
+            const uint32_t off = ((kk >> 2) * BW_CHUNK + (kk & 3) * 32) >> 4;
+            umma_f16<1>(tm + 128, desc(KM | (do_a + off)), desc(KM | (v_a + off)), idesc_s, kk != 0);
+          }
+          umma_commit<1>(sdp_full);
+          BWD_TRACE(1, t)
         }
-        umma_commit<1>(sdp_full);
-        mbar_wait(pds_full, t & 1);
+        bwd_wait(pds_full, t & 1);
         tc_fence_after();
-        // reduction dimension = the 128 q rows: 8 k-steps of 16 rows (2048 B apart in every [rows x 64] chunk)
+        if (leader) {
+          BWD_TRACE(2, t)
+          // reduction dimension = the 128 q rows: 8 k-steps of 16 rows (2048 B apart in every [rows x 64] chunk)
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          umma_f16<1>(TM_DV, umma_smem_desc(p_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(do_s + kk * 2048, BW_CHUNK, 1024),
-                      idesc_dkv, (t | kk) != 0);
-        }
-        umma_commit<1>(do_empty);  // dO(t) fully consumed: the producer reloads it while dK / dQ run
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16<1>(tm + 256, desc(MN | (p_a + kk * 128)), desc(MN | (do_a + kk * 128)), idesc_dkv, (t | kk) != 0);
+          umma_commit<1>(do_empty);  // dO(t) fully consumed: the producer reloads it while dK / dQ run
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          umma_f16<1>(TM_DK, umma_smem_desc(ds_s + kk * 2048, BW_CHUNK, 1024), umma_smem_desc(q_s + kk * 2048, BW_CHUNK, 1024),
-                      idesc_dkv, (t | kk) != 0);
-        }
-        // dQ = dS K : reduction dimension = 128 keys
+          for (int kk = 0; kk < 8; ++kk)
+            umma_f16<1>(tm + 384, desc(MN | (ds_a + kk * 128)), desc(MN | (q_a + kk * 128)), idesc_dkv, (t | kk) != 0);
+          // dQ = dS K : reduction dimension = 128 keys
 #pragma unroll
-        for (int kk = 0; kk < 8; ++kk) {
-          const uint32_t a_off = (kk >> 2) * BW_CHUNK + (kk & 3) * 32;
-          umma_f16<1>(TM_S, umma_smem_desc(ds_s + a_off, 16, 1024), umma_smem_desc(k_s + kk * 2048, BW_CHUNK, 1024), idesc_dq,
-                      kk != 0);
+          for (int kk = 0; kk < 8; ++kk) {
+            const uint32_t a_off = ((kk >> 2) * BW_CHUNK + (kk & 3) * 32) >> 4;
+            umma_f16<1>(tm, desc(KM | (ds_a + a_off)), desc(MN | (k_a + kk * 128)), idesc_dq, kk != 0);
+          }
+          umma_commit<1>(mma2_done);
+          umma_commit<1>(&q_empty[st]);
+          BWD_TRACE(3, t)
         }
-        umma_commit<1>(mma2_done);
-        umma_commit<1>(&q_empty[st]);
       }
     }
   } else {
@@ -234,21 +284,39 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
     const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
     const int sw = row & 7;
     const int epi_tid = threadIdx.x - 64;
+    // lse / delta of step t+1 are fetched one step ahead: with the dQ reduce-adds of every CTA in flight a global load
+    // takes thousands of cycles, which used to land in the middle of the P / dS computation
+    auto stat_index = [&](int t) {
+      const int g = t / steps_per_head;
+      const int i = i_first + (t - g * steps_per_head);
+      return (static_cast<size_t>(batch) * p.hq + kv_head * group + g) * p.S + i * 128 + row;
+    };
+    float lse_next = p.lse[stat_index(0)], dlt_next = p.delta[stat_index(0)];
     for (int t = 0; t < n_steps; ++t) {
       const int g = t / steps_per_head;
       const int i = i_first + (t - g * steps_per_head);
       const int head = kv_head * group + g;
-      const size_t stat_idx = (static_cast<size_t>(batch) * p.hq + head) * p.S + i * 128 + row;
-      const float lse2 = p.lse[stat_idx] * 1.4426950408889634f;
-      const float dlt = p.delta[stat_idx];
+      const float lse2 = lse_next * 1.4426950408889634f;
+      const float dlt = dlt_next;
+      if (t + 1 < n_steps) {
+        const size_t nxt = stat_index(t + 1);
+        lse_next = p.lse[nxt];
+        dlt_next = p.delta[nxt];
+      }
       const bool diag = p.causal && (i == jb);
       mbar_wait(sdp_full, t & 1);
       tc_fence_after();
+      if (row == 0) { BWD_TRACE(4, t) }
       if (t > 0) {
-        // the previous step's dQ staging lives in the P/dS buffers: the TMA engine must have read it before we overwrite
-        if (epi_tid == 0) tma_wait_group_read<0>();
+        // the first half of dQ(t-1) was staged in the P buffer: the TMA engine must have read it before P(t) is stored
+        // (the younger group -- the half in the Q slot -- may still be pending)
+        if (epi_tid == 0) tma_wait_group_read<1>();
         named_bar_sync(1, BW_SM_THREADS);
       }
+      if (row == 0) { BWD_TRACE(9, t) }
+      // P = exp2(S c - lse), dS = P (dP - delta) scale with packed fp32x2 math (FFMA2 / FMUL2: half the issue slots)
+      const uint64_t sc2 = bw_pack2(p.scale_log2, p.scale_log2), nlse2 = bw_pack2(-lse2, -lse2);
+      const uint64_t scl2 = bw_pack2(p.scale, p.scale), ndlt2 = bw_pack2(-dlt * p.scale, -dlt * p.scale);
 #pragma unroll
       for (int cc = 0; cc < 4 / NSPLIT; ++cc) {
         const int c = half * (4 / NSPLIT) + cc;
@@ -256,63 +324,97 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
         tmem_ld_32x32(TM_S + c * 32 + lane_off, sv);
         tmem_ld_32x32(TM_DP + c * 32 + lane_off, dv);
         tmem_ld_wait();
+        if (diag) {
+#pragma unroll
+          for (int k = 0; k < 32; ++k)
+            if (c * 32 + k > row) sv[k] = 0xff800000u;  // -inf -> P = 0, dS = 0
+        }
         uint8_t* prow = smem + SMEM::P_OFF + (c >> 1) * BW_CHUNK + row * 128;
         uint8_t* dsrow = smem + SMEM::DS_OFF + (c >> 1) * BW_CHUNK + row * 128;
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          float pe[8], de[8];
+          uint32_t pp[4], dd[4];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            const int col = c * 32 + u * 8 + k;
-            float pv = exp2f(fmaf(__uint_as_float(sv[u * 8 + k]), p.scale_log2, -lse2));
-            if (diag && col > row) pv = 0.f;
-            pe[k] = pv;
-            de[k] = pv * (__uint_as_float(dv[u * 8 + k]) - dlt) * p.scale;
+          for (int k = 0; k < 4; ++k) {
+            const int e = u * 8 + 2 * k;
+            const uint64_t x2 = bw_fma2(bw_pack2(__uint_as_float(sv[e]), __uint_as_float(sv[e + 1])), sc2, nlse2);
+            float x0, x1;
+            bw_unpack2(x2, x0, x1);
+            const float p0 = bwd_ex2(x0), p1 = bwd_ex2(x1);
+            const uint64_t g2 = bw_fma2(bw_pack2(__uint_as_float(dv[e]), __uint_as_float(dv[e + 1])), scl2, ndlt2);
+            float d0, d1;
+            bw_unpack2(bw_mul2(bw_pack2(p0, p1), g2), d0, d1);
+            pp[k] = pack_bf16x2(p0, p1);
+            dd[k] = pack_bf16x2(d0, d1);
           }
-          uint4 a, b;
-          a.x = pack_bf16x2(pe[0], pe[1]); a.y = pack_bf16x2(pe[2], pe[3]); a.z = pack_bf16x2(pe[4], pe[5]); a.w = pack_bf16x2(pe[6], pe[7]);
-          b.x = pack_bf16x2(de[0], de[1]); b.y = pack_bf16x2(de[2], de[3]); b.z = pack_bf16x2(de[4], de[5]); b.w = pack_bf16x2(de[6], de[7]);
           const int unit = (c & 1) * 4 + u;
-          *reinterpret_cast<uint4*>(prow + ((unit ^ sw) << 4)) = a;
-          *reinterpret_cast<uint4*>(dsrow + ((unit ^ sw) << 4)) = b;
+          *reinterpret_cast<uint4*>(prow + ((unit ^ sw) << 4)) = make_uint4(pp[0], pp[1], pp[2], pp[3]);
+          *reinterpret_cast<uint4*>(dsrow + ((unit ^ sw) << 4)) = make_uint4(dd[0], dd[1], dd[2], dd[3]);
         }
       }
+      if (row == 0) { BWD_TRACE(10, t) }
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(pds_full);
+      if (row == 0) { BWD_TRACE(5, t) }
+      if (t > 0 && epi_tid == 0) {
+        // dQ(t-1) went out through Q slot (t-1)&1 a whole softmax phase ago: its TMA reads are long done, so this wait is free;
+        // the producer may now refill the slot with Q(t+1)
+        tma_wait_group_read<0>();
+        mbar_arrive(&q_stage_free[(t - 1) & 1]);
+      }
 
-      // ---- drain dQ: TMEM [0,D) fp32 -> registers; the TMEM region is then free, so the MMA warp may start S/dP of the
-      // next step while this warp group stages dQ (swizzled fp32 in the P/dS buffers, free once mma2 retired) and the TMA
-      // reduce-add runs.  The staging buffers are only written again by the next step's P/dS stores, which first wait
-      // for the TMA engine to have read them (top of the loop).
+      // ---- drain dQ: TMEM [0,D) fp32 -> registers; the TMEM region is then free, so the MMA warp starts S/dP of the next step
+      // while this warp group sends dQ out as swizzled fp32 tiles summed into the fp32 scratch by TMA reduce-add.  The
+      // reduce-adds of all CTAs are bound by the L2 atomic rate, so the engine reads its smem source slowly (~1300 cycles per
+      // 32 KB): the staging must not be needed soon.  Half of the columns go through the P buffer -- read while the next
+      // step's S/dP MMAs run, i.e. before the next softmax phase stores P -- and half through the Q slot of THIS step, dead
+      // once mma2 retired and refilled a full step later (the producer waits for q_stage_free).
       mbar_wait(mma2_done, t & 1);
       tc_fence_after();
-      uint8_t* stage = smem + SMEM::P_OFF;
-      constexpr int DQ_PER = D / 32 / NSPLIT;  // 32-column chunks of dQ per thread
+      if (row == 0) { BWD_TRACE(6, t) }
+      uint8_t* stage = smem + SMEM::Q_OFF + (t & 1) * SMEM::TILE;
+      constexpr int DQ_PER = D / 32;  // 32-column chunks of dQ per thread
       uint32_t dq[DQ_PER][32];
 #pragma unroll
-      for (int cc = 0; cc < DQ_PER; ++cc) tmem_ld_32x32(TM_S + (half * DQ_PER + cc) * 32 + lane_off, dq[cc]);
+      for (int cc = 0; cc < DQ_PER; ++cc) tmem_ld_32x32(TM_S + cc * 32 + lane_off, dq[cc]);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(dq_drained);
+      if (row == 0) { BWD_TRACE(7, t) }
+      const int qrow0 = batch * p.S + i * 128;
+      // first half -> P buffer (its reads finish under the next step's S/dP MMAs, before the next softmax phase stores P),
+      // second half -> Q slot of this step (refilled a full step later); the two reduce-adds are issued back to back
 #pragma unroll
-      for (int cc = 0; cc < DQ_PER; ++cc) {
-        uint8_t* rowp = stage + (half * DQ_PER + cc) * BW_CHUNK + row * 128;
+      for (int hh = 0; hh < 2; ++hh) {
+        uint8_t* stg = hh == 0 ? smem + SMEM::P_OFF : stage;
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
-          *reinterpret_cast<uint4*>(rowp + ((u ^ sw) << 4)) = make_uint4(dq[cc][4 * u], dq[cc][4 * u + 1], dq[cc][4 * u + 2], dq[cc][4 * u + 3]);
+        for (int cc = 0; cc < DQ_PER / 2; ++cc) {
+          uint8_t* rowp = stg + cc * BW_CHUNK + row * 128;
+          const int src = hh * (DQ_PER / 2) + cc;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            *reinterpret_cast<uint4*>(rowp + ((u ^ sw) << 4)) = make_uint4(dq[src][4 * u], dq[src][4 * u + 1], dq[src][4 * u + 2], dq[src][4 * u + 3]);
+        }
       }
       fence_proxy_async_smem();
       named_bar_sync(1, BW_SM_THREADS);
       if (epi_tid == 0) {
-        const int qrow0 = batch * p.S + i * 128;
-        if (!p.debug_skip_dq)
-          for (int c = 0; c < D / 32; ++c) tma_reduce_add_2d(&tmDQ, stage + c * BW_CHUNK, head * D + c * 32, qrow0);
-        tma_commit_group();
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          uint8_t* stg = hh == 0 ? smem + SMEM::P_OFF : stage;
+          if (!p.debug_skip_dq)
+            for (int cc = 0; cc < DQ_PER / 2; ++cc)
+              tma_reduce_add_2d(&tmDQ, stg + cc * BW_CHUNK, head * D + (hh * (DQ_PER / 2) + cc) * 32, qrow0);
+          tma_commit_group();  // one group per half: the P-buffer half is awaited alone at the top of the next step
+        }
       }
+      if (row == 0) { BWD_TRACE(8, t) }
     }
 
     // ---- dK, dV epilogue: TMEM -> bf16 -> swizzled staging (Q / dO tiles are dead) -> TMA store into packed dqkv
+    if (epi_tid == 0) tma_wait_group_read<0>();  // the last dQ halves have left the Q slots
+    named_bar_sync(1, BW_SM_THREADS);
     tc_fence_after();
 #pragma unroll
     for (int which = 0; which < 2; ++which) {
@@ -394,6 +496,7 @@ static int launch_bwd(const void* dout, const void* qkv, const void* out, const 
   p.delta = delta;
   static const int skip_dq = [] { const char* e = getenv("DSB200_BWD_SKIP_DQ"); return e ? atoi(e) : 0; }();
   p.debug_skip_dq = skip_dq;
+  p.trace = g_bwd_trace;
   dim3 grid(S / 128, hkv, B);
   kern<<<grid, BW_THREADS, SMEM::TOTAL, stream>>>(tmQKV, tmDO, tmDQ, tmDQKV, p);
   DSB_CHECK_CUDA(cudaGetLastError());
@@ -406,6 +509,7 @@ static int launch_bwd(const void* dout, const void* qkv, const void* out, const 
 }
 
 }  // namespace attn
+void flash_bwd_set_trace(long long* buf) { attn::g_bwd_trace = buf; }
 }  // namespace dsb
 
 // Gradient of dsb200_flash_attn_fwd.  dout/out: [B*S, hq*D] bf16; qkv, dqkv: packed [B*S, (hq+2*hkv)*D] bf16;

@@ -311,11 +311,13 @@ static int launch_fwd(const void* qkv, void* out, float* lse, int B, int S, int 
 int flash_fwd2_launch(const void* qkv, void* out, float* lse, int B, int S, int hq, int hkv, int head_dim, int causal, float scale,
                       cudaStream_t stream);
 void flash_fwd2_set_trace(long long* buf);
+void flash_bwd_set_trace(long long* buf);
 }  // namespace dsb
 
 // debug hook: device buffer (>= 8192 int64) receiving clock64 stamps of one CTA of the next forward launches; nullptr = off
 DSB_EXPORT int dsb200_flash_fwd_trace(long long* buf) {
   dsb::flash_fwd2_set_trace(buf);
+  dsb::flash_bwd_set_trace(buf);
   return DSB_OK;
 }
 

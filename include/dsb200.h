@@ -106,6 +106,8 @@ int dsb200_flash_attn_bwd(const void* dout, const void* qkv, const void* out, co
                           dsb200_stream_t stream);
 
 /* ---- csrc/attn/flash_fwd.cu */
+/* debug hook: device buffer (>= 8192 int64) receiving clock64 stamps of one CTA of the next forward launches; nullptr = off */
+int dsb200_flash_fwd_trace(long long* buf);
 /* out[B*S, hq*D] = softmax(Q K^T * scale [+ causal mask]) V with Q,K,V read from packed qkv [B*S, (hq+2*hkv)*D] (bf16).
  * lse: optional [B, hq, S] fp32 (natural-log sum-exp of the scaled scores) for the backward pass. */
 int dsb200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int hq, int hkv, int head_dim, int causal,
