@@ -19,8 +19,7 @@
 namespace dsb {
 namespace attn {
 
-// One softmax thread per q row.  (Two threads per row -- 8 softmax warps -- was measured slower: the step is bound by
-// shared-memory bandwidth (SS MMAs with N = 128 read 128 B/clk) and by the MMA <-> softmax hand-offs, not by softmax math.)
+// One softmax thread per q row (two threads per row were measured: no gain, see the dQ drain notes in the kernel).
 constexpr int BW_THREADS = 192;
 constexpr int BW_SM_THREADS = 128;
 constexpr int BW_CHUNK = 128 * 128;  // [128 rows x 64 bf16] swizzled chunk (also [128 rows x 32 fp32])
@@ -370,6 +369,10 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tmQKV, const __grid_constan
       // 32 KB): the staging must not be needed soon.  Half of the columns go through the P buffer -- read while the next
       // step's S/dP MMAs run, i.e. before the next softmax phase stores P -- and half through the Q slot of THIS step, dead
       // once mma2 retired and refilled a full step later (the producer waits for q_stage_free).
+      // Measured alternatives: red.global.add.v4.f32 straight from the registers (no staging) spends 4200 cycles per step
+      // issuing half-sector atomics against ~2600 for the TMA path -- the per-SM atomic rate of ~25 B/clk is the floor either
+      // way; eight softmax warps (two threads per row) leave the P/dS phase unchanged at ~2300 cycles: it is bound by MUFU +
+      // FMA-pipe throughput (which do not overlap), not by latency.
       mbar_wait(mma2_done, t & 1);
       tc_fence_after();
       if (row == 0) { BWD_TRACE(6, t) }
