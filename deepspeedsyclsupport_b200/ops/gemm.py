@@ -122,8 +122,8 @@ class _LinearFn(torch.autograd.Function):
             wp = ctx.w_param
             if wp is not None:
                 # fused gradient accumulation: the wgrad epilogue reduces dW straight into the ZeRO gradient buffer
-                mg = wp.ds_get_main_grad()
-                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
+                mg, fresh = wp.ds_take_main_grad()
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=not fresh)  # first gradient of the step: plain store
                 wp.ds_main_grad_done()
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)
@@ -171,8 +171,8 @@ class _LinearRopeFn(torch.autograd.Function):
         if ctx.needs_input_grad[1]:
             wp = ctx.w_param
             if wp is not None:
-                mg = wp.ds_get_main_grad()
-                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=True)
+                mg, fresh = wp.ds_take_main_grad()
+                gemm(dy2, x2, a_mn=True, b_mn=True, out=mg, accumulate=not fresh)  # first gradient of the step: plain store
                 wp.ds_main_grad_done()
             else:
                 dw = gemm(dy2, x2, a_mn=True, b_mn=True)

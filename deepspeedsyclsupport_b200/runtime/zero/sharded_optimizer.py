@@ -195,7 +195,9 @@ class ZeroShardedOptimizer:
         p.partition = partition
         p.ds_summary = ds_summary
         p.ds_get_main_grad = lambda q=p: opt.main_grad_view(q)
+        p.ds_take_main_grad = lambda q=p: opt.main_grad_take(q)
         p.ds_main_grad_done = lambda q=p: opt._param_grad_ready(q)
+        p.ds_grad_fresh = False
 
     def _unit_flat_from_params(self, u, broadcast_src):
         """Assemble the unit's full flat buffer from whatever form its parameters currently have."""
@@ -325,10 +327,15 @@ class ZeroShardedOptimizer:
             torch.cuda.current_stream().wait_event(self._p2p_barrier_events[need])
         u.p2p_slot = k
         buf = self._p2p_slot_views[k][:u.padded]
-        buf.zero_()
+        # the slot still holds another unit's gradients: parameters overwrite their slices on first touch (ds_grad_fresh),
+        # only the gaps between them are cleared
+        for off, n in self._unit_gaps(u):
+            buf[off:off + n].zero_()
+        self._mark_fresh([u])
         return buf
 
     def _p2p_reduce_unit(self, u):
+        self._settle_fresh([u])
         stream = self.rs_stream
         stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(stream):
@@ -361,6 +368,7 @@ class ZeroShardedOptimizer:
     def _allocate_grads(self):
         self.grad_shard = torch.zeros(self.total_shard, dtype=self.grad_accum_dtype, device=self.device)
         self.grad_full_persistent = None
+        self._grad_is_shard = self.shard_world == 1
         if self.shard_world == 1:
             # full gradient == shard: hooks / fused wgrad write straight into the accumulation buffer
             for u in self.units:
@@ -397,8 +405,7 @@ class ZeroShardedOptimizer:
 
         return hook
 
-    def main_grad_view(self, p):
-        """Slice of the unit's contiguous gradient buffer for `p` (allocated on first use in a backward pass)."""
+    def _grad_slice(self, p):
         u = p.ds_unit
         if u.full_grad is None:
             if self.p2p is not None:
@@ -408,6 +415,54 @@ class ZeroShardedOptimizer:
         off, n = u.param_slice(p.ds_index)
         self._grads_dirty = True
         return u.full_grad[off:off + n].view(p.ds_shape)
+
+    def main_grad_view(self, p):
+        """Slice of the unit's contiguous gradient buffer for `p` (allocated on first use in a backward pass), to be
+        ACCUMULATED into.  Buffers are not memset between steps: a parameter whose slice still holds stale data is
+        flagged `ds_grad_fresh` and zeroed here, on first touch."""
+        view = self._grad_slice(p)
+        if p.ds_grad_fresh:
+            view.zero_()
+            p.ds_grad_fresh = False
+        return view
+
+    def main_grad_take(self, p):
+        """-> (slice, fresh).  fresh=True: the caller must OVERWRITE the slice (first gradient of this parameter since the
+        buffer was recycled) -- the fused wgrad GEMM then stores instead of reduce-adding, and nobody zero-fills."""
+        view = self._grad_slice(p)
+        fresh = p.ds_grad_fresh
+        p.ds_grad_fresh = False
+        return view, fresh
+
+    def _mark_fresh(self, units):
+        for u in units:
+            for q in u.trainable:
+                q.ds_grad_fresh = True
+
+    def _settle_fresh(self, units):
+        """Parameters that received no gradient keep stale data in their slice: zero them before the buffer is consumed."""
+        for u in units:
+            for q in u.trainable:
+                if q.ds_grad_fresh:
+                    if u.full_grad is not None:
+                        off, n = u.param_slice(q.ds_index)
+                        u.full_grad[off:off + n].zero_()
+                    q.ds_grad_fresh = False
+
+    def _unit_gaps(self, u):
+        """[(off, len)] of the unit-flat space not covered by a trainable parameter (alignment padding, frozen weights)."""
+        gaps = getattr(u, "_grad_gaps", None)
+        if gaps is None:
+            spans = sorted(u.param_slice(q.ds_index) for q in u.trainable)
+            gaps, cur = [], 0
+            for off, n in spans:
+                if off > cur:
+                    gaps.append((cur, off - cur))
+                cur = max(cur, off + n)
+            if cur < u.padded:
+                gaps.append((cur, u.padded - cur))
+            u._grad_gaps = gaps
+        return gaps
 
     def _param_grad_ready(self, p):
         u = p.ds_unit
@@ -495,6 +550,8 @@ class ZeroShardedOptimizer:
         """Engine hook after every backward().  local_only: skip the data-parallel reduction (the basic optimizer
         communicates by itself, e.g. 1-bit Adam after its warm-up)."""
         self._local_grads_only = bool(local_only)
+        if self._grad_is_shard:
+            self._settle_fresh(self.units)
         if self.stage >= 2 or boundary:
             if self.stage <= 1 and not boundary:
                 pass
@@ -694,11 +751,15 @@ class ZeroShardedOptimizer:
         for u in self.units:
             for p in u.params:
                 p.grad = None
-        if self._grads_dirty or True:
+        if self._grad_is_shard:
+            # gradients are written straight into the accumulation buffer: mark instead of a 2-bytes-per-parameter memset;
+            # the first wgrad of every parameter stores, untouched parameters are zeroed in end_micro_step
+            self._mark_fresh(self.units)
+        else:
             self.grad_shard.zero_()
             if self.grad_full_persistent is not None:
                 self.grad_full_persistent.zero_()
-            self._grads_dirty = False
+        self._grads_dirty = False
 
     # ------------------------------------------------------------------ step
     def _model_parallel_all_reduce(self, tensor, op):

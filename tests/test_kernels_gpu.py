@@ -212,6 +212,28 @@ def test_flash_attention_fwd_bwd(cfg):
     assert (qkv.grad.float() - qf.grad).abs().max() < 2e-2 * max(1.0, qf.grad.abs().max().item())
 
 
+def test_flash_attention_forward_lazy_rescale_and_long_sequence():
+    """Scores that keep growing along the key axis force the forward's lazy O rescale (row max jumps by more than 2^8 between
+    key blocks); 2048 tokens exercise the two-Q-tile ping-pong over many key blocks.  Also checks LSE."""
+    from deepspeedsyclsupport_b200.ops.attention import attention_ref
+    from deepspeedsyclsupport_b200.ops.flash_attention import flash_fwd
+    B, S, hq, hkv, d = 1, 2048, 2, 1, 128
+    torch.manual_seed(0)
+    qkv = torch.randn(B * S, (hq + 2 * hkv) * d, device=_dev(), dtype=torch.float32)
+    ramp = torch.linspace(0.05, 12.0, S, device=_dev()).repeat(B)[:, None]
+    qkv[:, hq * d:(hq + hkv) * d] *= ramp  # keys grow with position: later blocks dominate the softmax
+    qkv = qkv.bfloat16()
+    for causal in (True, False):
+        out, lse = flash_fwd(qkv, B, S, hq, hkv, d, causal)
+        ref = attention_ref(qkv.float(), B, S, hq, hkv, d, causal)
+        assert torch.isfinite(out.float()).all() and (out.float() - ref).abs().max() < 3e-2
+        q = qkv.float().view(B, S, hq + 2 * hkv, d)
+        s = torch.einsum("bihd,bjd->bhij", q[:, :, :hq], q[:, :, hq]) / math.sqrt(d)
+        if causal:
+            s = s.masked_fill(torch.ones(S, S, device=_dev(), dtype=torch.bool).triu(1), float("-inf"))
+        assert (lse - torch.logsumexp(s, -1)).abs().max() < 2e-2 * max(1.0, s.abs().max().item() / 50)
+
+
 def test_p2p_collectives_emulated_ranks():
     """All 'ranks' live on one GPU (one buffer each); each rank's kernel is launched in turn (no cross-kernel waits)."""
     from deepspeedsyclsupport_b200.parallel.symm import EmulatedPeers
