@@ -9,6 +9,8 @@ from collections import Counter
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 WANT = ["gpu__time_duration.sum", "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed", "smsp__issue_active.avg.pct_of_peak_sustained_active",
         "sm__throughput.avg.pct_of_peak_sustained_elapsed", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
         "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread", "launch__grid_size",
         "launch__block_size", "launch__shared_mem_per_block_dynamic", "sm__warps_active.avg.pct_of_peak_sustained_active",
@@ -64,13 +66,13 @@ def sass_summary(out_md):
     lines = ["# SASS evidence (cuobjdump -sass libdsb200.so, sm_100a)", "",
              "Counts of Blackwell-specific mnemonics per kernel: `UTCHMMA` = tcgen05.mma (bf16; `.2CTA` = cta_group::2 pair MMA), `UTMALDG/UTMASTG/UTMAREDG` = TMA "
              "load/store/reduce, `LDTM/STTM` = tcgen05.ld/st, `SYNCS` = mbarrier ops, `HMMA` = legacy mma.sync (must be 0).", "",
-             "| kernel | UTCHMMA | of which .2CTA | UTMALDG | UTMASTG | UTMAREDG | LDTM | SYNCS | HMMA | LDG | STG |", "|---|---|---|---|---|---|---|---|---|---|---|"]
+             "| kernel | UTCHMMA | of which .2CTA | UTMALDG | UTMASTG | UTMAREDG | LDTM | STTM | SYNCS | HMMA | LDG | STG |", "|---|---|---|---|---|---|---|---|---|---|---|---|"]
     for k, c in sorted(per.items()):
         if sum(c.values()) == 0:
             continue
         dem = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip()
         dem = re.sub(r"\(.*", "", dem)[:90]
-        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['2CTA']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['LDTM']} | {c['SYNCS']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
+        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['2CTA']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['LDTM']} | {c['STTM']} | {c['SYNCS']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
     open(out_md, "w").write("\n".join(lines) + "\n")
 
 
