@@ -6,7 +6,9 @@ csrc/transformer/inference).  Here the fused kernels already exist as one generi
 (inference/v2/model_implementations/ragged_transformer.py: fused norm / QKV GEMM + RoPE + KV-append / paged attention /
 gated MLP, blocked KV cache), so injection means: map the HF module's weights onto that implementation once (no copy of
 the checkpoint files, tensor-parallel sharding included) and route `generate()` through it with continuous batching of
-the prompts.  Supported `config.model_type`s: llama, mistral, mixtral, opt, falcon, phi."""
+the prompts.  Supported `config.model_type`s: llama (incl. attention biases = internlm), mistral, mixtral, opt, falcon,
+phi, gpt2, gptj, gpt_neox.  (The reference's bloom / gpt-neo containers need ALiBi / windowed attention in the paged kernel:
+not implemented; those models run through AutoTP instead.)"""
 from types import SimpleNamespace
 
 import torch
@@ -14,7 +16,7 @@ from torch import nn
 
 from ..utils.logging import log_dist
 
-SUPPORTED = ("llama", "mistral", "mixtral", "opt", "falcon", "phi")
+SUPPORTED = ("llama", "mistral", "internlm", "mixtral", "opt", "falcon", "phi", "gpt2", "gptj", "gpt_neox")
 
 
 def can_inject(model):

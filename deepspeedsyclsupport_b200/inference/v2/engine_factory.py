@@ -21,6 +21,8 @@ def _map_llama(sd, cfg):
         p, q = f"model.layers.{i}.", f"layers.{i}."
         for a, b in (("self_attn.q_proj", "q"), ("self_attn.k_proj", "k"), ("self_attn.v_proj", "v"), ("self_attn.o_proj", "o")):
             out[q + b + ".weight"] = sd[p + a + ".weight"]
+            if p + a + ".bias" in sd:  # internlm / llama with attention_bias
+                out[q + b + ".bias"] = sd[p + a + ".bias"]
         out[q + "norm1.weight"] = sd[p + "input_layernorm.weight"]
         out[q + "norm2.weight"] = sd[p + "post_attention_layernorm.weight"]
         if p + "mlp.gate_proj.weight" in sd:
@@ -90,7 +92,73 @@ def _map_phi(sd, cfg):
     return out
 
 
-_MAPPERS = {"llama": _map_llama, "mistral": _map_llama, "mixtral": _map_llama, "opt": _map_opt, "falcon": _map_falcon, "phi": _map_phi}
+def _map_gpt2(sd, cfg):
+    """GPT-2: Conv1D weights are stored [in, out]; c_attn is q | k | v along the output axis."""
+    pre = "transformer." if "transformer.wte.weight" in sd else ""
+    h = cfg["n_embd"]
+    out = {"embed.weight": sd[pre + "wte.weight"], "pos_embed.weight": sd[pre + "wpe.weight"], "final_norm.weight": sd[pre + "ln_f.weight"],
+           "final_norm.bias": sd[pre + "ln_f.bias"]}
+    for i in range(cfg["n_layer"]):
+        p, q = f"{pre}h.{i}.", f"layers.{i}."
+        w, b = sd[p + "attn.c_attn.weight"].t(), sd[p + "attn.c_attn.bias"]
+        for j, n in enumerate("qkv"):
+            out[q + n + ".weight"], out[q + n + ".bias"] = w[j * h:(j + 1) * h].contiguous(), b[j * h:(j + 1) * h]
+        out[q + "o.weight"], out[q + "o.bias"] = sd[p + "attn.c_proj.weight"].t().contiguous(), sd[p + "attn.c_proj.bias"]
+        out[q + "up.weight"], out[q + "up.bias"] = sd[p + "mlp.c_fc.weight"].t().contiguous(), sd[p + "mlp.c_fc.bias"]
+        out[q + "down.weight"], out[q + "down.bias"] = sd[p + "mlp.c_proj.weight"].t().contiguous(), sd[p + "mlp.c_proj.bias"]
+        for a, b2 in (("ln_1", "norm1"), ("ln_2", "norm2")):
+            out[q + b2 + ".weight"], out[q + b2 + ".bias"] = sd[p + a + ".weight"], sd[p + a + ".bias"]
+    return out
+
+
+def _map_gptj(sd, cfg):
+    """GPT-J rotates interleaved pairs (2i, 2i+1) of the first rotary_dim features of every head; the kernels rotate
+    (i, i + rot/2).  Permuting those rows of W_q and W_k the same way (evens first, then odds) leaves q.k unchanged."""
+    import torch
+    hq = cfg["n_head"]
+    d = cfg["n_embd"] // hq
+    rot = cfg.get("rotary_dim") or d
+    perm = torch.cat([torch.arange(0, rot, 2), torch.arange(1, rot, 2), torch.arange(rot, d)])
+    rows = (torch.arange(hq)[:, None] * d + perm[None, :]).reshape(-1)
+    out = {"embed.weight": sd["transformer.wte.weight"], "final_norm.weight": sd["transformer.ln_f.weight"],
+           "final_norm.bias": sd["transformer.ln_f.bias"], "lm_head.weight": sd["lm_head.weight"]}
+    if "lm_head.bias" in sd:
+        out["lm_head.bias"] = sd["lm_head.bias"]
+    for i in range(cfg["n_layer"]):
+        p, q = f"transformer.h.{i}.", f"layers.{i}."
+        out[q + "q.weight"], out[q + "k.weight"] = sd[p + "attn.q_proj.weight"][rows], sd[p + "attn.k_proj.weight"][rows]
+        out[q + "v.weight"], out[q + "o.weight"] = sd[p + "attn.v_proj.weight"], sd[p + "attn.out_proj.weight"]
+        out[q + "up.weight"], out[q + "up.bias"] = sd[p + "mlp.fc_in.weight"], sd[p + "mlp.fc_in.bias"]
+        out[q + "down.weight"], out[q + "down.bias"] = sd[p + "mlp.fc_out.weight"], sd[p + "mlp.fc_out.bias"]
+        out[q + "norm1.weight"], out[q + "norm1.bias"] = sd[p + "ln_1.weight"], sd[p + "ln_1.bias"]
+    return out
+
+
+def _map_gpt_neox(sd, cfg):
+    hq = cfg["num_attention_heads"]
+    d = cfg["hidden_size"] // hq
+    out = {"embed.weight": sd["gpt_neox.embed_in.weight"], "final_norm.weight": sd["gpt_neox.final_layer_norm.weight"],
+           "final_norm.bias": sd["gpt_neox.final_layer_norm.bias"], "lm_head.weight": sd["embed_out.weight"]}
+    for i in range(cfg["num_hidden_layers"]):
+        p, q = f"gpt_neox.layers.{i}.", f"layers.{i}."
+        w = sd[p + "attention.query_key_value.weight"].view(hq, 3, d, -1)  # interleaved [head, (q k v), d]
+        for j, n in enumerate("qkv"):
+            out[q + n + ".weight"] = w[:, j].reshape(hq * d, -1)
+        if p + "attention.query_key_value.bias" in sd:
+            b = sd[p + "attention.query_key_value.bias"].view(hq, 3, d)
+            for j, n in enumerate("qkv"):
+                out[q + n + ".bias"] = b[:, j].reshape(hq * d)
+        for a, n in (("attention.dense", "o"), ("mlp.dense_h_to_4h", "up"), ("mlp.dense_4h_to_h", "down")):
+            out[q + n + ".weight"] = sd[p + a + ".weight"]
+            if p + a + ".bias" in sd:
+                out[q + n + ".bias"] = sd[p + a + ".bias"]
+        for a, n in (("input_layernorm", "norm1"), ("post_attention_layernorm", "norm2")):
+            out[q + n + ".weight"], out[q + n + ".bias"] = sd[p + a + ".weight"], sd[p + a + ".bias"]
+    return out
+
+
+_MAPPERS = {"llama": _map_llama, "mistral": _map_llama, "internlm": _map_llama, "mixtral": _map_llama, "opt": _map_opt,
+            "falcon": _map_falcon, "phi": _map_phi, "gpt2": _map_gpt2, "gptj": _map_gptj, "gpt_neox": _map_gpt_neox}
 
 
 def build_engine_from_state_dict(model_type, hf_config: dict, state_dict: dict, engine_config: RaggedInferenceEngineConfig,

@@ -1,7 +1,7 @@
 """One ragged-batch decoder implementation parameterised by an `ArchSpec`, covering the model families the reference
 ships as separate containers/policies (inference/v2/model_implementations/{llama_v2,mistral,mixtral,opt,falcon,phi}):
 
-  llama / mistral : RMSNorm, rotary, gated SiLU MLP, GQA           mixtral : + top-2 MoE MLP (experts TP-sharded)
+  llama / mistral / internlm (attention biases) : RMSNorm, rotary, gated SiLU MLP, GQA           mixtral : + top-2 MoE MLP (experts TP-sharded)
   opt             : LayerNorm, learned positions (+2), ReLU MLP, biases      falcon / phi : parallel attention + MLP block
 
 Forward of a layer: fused (residual-add +) norm -> QKV GEMM -> RoPE + paged-KV append -> paged attention -> output GEMM ->
@@ -37,7 +37,8 @@ class ArchSpec:
     rotary_dim: int = 128        # 0 = no rotary
     rope_theta: float = 10000.0
     learned_pos_offset: Optional[int] = None   # OPT: 2
-    parallel_block: bool = False               # falcon / phi: attention and MLP read the same normed input
+    parallel_block: bool = False               # falcon / phi / gpt-j: attention and MLP read the same normed input
+    parallel_norm2: bool = False               # gpt-neox: parallel residual, but the MLP has its own LayerNorm of the input
     attn_bias: bool = False
     mlp_bias: bool = False
     num_experts: int = 0
@@ -46,12 +47,20 @@ class ArchSpec:
     max_positions: int = 4096
 
 
+def _rope(c, default_partial=1.0):
+    """(theta, partial rotary factor) from either the flat keys of older HF configs or the `rope_parameters` dict of newer ones."""
+    rp = c.get("rope_parameters") or {}
+    theta = c.get("rope_theta", c.get("rotary_emb_base", rp.get("rope_theta", 10000.0)))
+    partial = c.get("partial_rotary_factor", c.get("rotary_pct", rp.get("partial_rotary_factor", default_partial)))
+    return float(theta), float(partial)
+
+
 def _spec_llama(c):
     return ArchSpec(family="llama", vocab_size=c["vocab_size"], hidden_size=c["hidden_size"], intermediate_size=c["intermediate_size"],
                     num_layers=c["num_hidden_layers"], num_heads=c["num_attention_heads"],
                     num_kv_heads=c.get("num_key_value_heads", c["num_attention_heads"]),
                     head_dim=c["hidden_size"] // c["num_attention_heads"], norm_eps=c.get("rms_norm_eps", 1e-5),
-                    rotary_dim=c["hidden_size"] // c["num_attention_heads"], rope_theta=c.get("rope_theta", 10000.0),
+                    rotary_dim=c["hidden_size"] // c["num_attention_heads"], rope_theta=_rope(c)[0],
                     tie_embeddings=c.get("tie_word_embeddings", False), max_positions=c.get("max_position_embeddings", 4096))
 
 
@@ -73,7 +82,7 @@ def _spec_falcon(c):
     return ArchSpec(family="falcon", vocab_size=c["vocab_size"], hidden_size=c["hidden_size"], intermediate_size=4 * c["hidden_size"],
                     num_layers=c["num_hidden_layers"], num_heads=hq, num_kv_heads=c.get("num_kv_heads", 1 if c.get("multi_query", True) else hq),
                     head_dim=c["hidden_size"] // hq, norm="ln", activation="gelu", gated_mlp=False, rotary_dim=c["hidden_size"] // hq,
-                    parallel_block=c.get("parallel_attn", True), attn_bias=c.get("bias", False), mlp_bias=c.get("bias", False))
+                    rope_theta=_rope(c)[0], parallel_block=c.get("parallel_attn", True), attn_bias=c.get("bias", False), mlp_bias=c.get("bias", False))
 
 
 def _spec_phi(c):
@@ -82,11 +91,38 @@ def _spec_phi(c):
     return ArchSpec(family="phi", vocab_size=c["vocab_size"], hidden_size=c["hidden_size"], intermediate_size=c.get("intermediate_size", 4 * c["hidden_size"]),
                     num_layers=c["num_hidden_layers"], num_heads=hq, num_kv_heads=c.get("num_key_value_heads", hq) or hq, head_dim=d, norm="ln",
                     norm_eps=c.get("layer_norm_eps", 1e-5), activation="gelu", gated_mlp=False,
-                    rotary_dim=int(d * c.get("partial_rotary_factor", 0.5)), parallel_block=True, attn_bias=True, mlp_bias=True)
+                    rotary_dim=int(d * _rope(c, 0.5)[1]), rope_theta=_rope(c)[0], parallel_block=True, attn_bias=True, mlp_bias=True)
 
 
-SPEC_FROM_HF = {"llama": _spec_llama, "mistral": _spec_llama, "mixtral": _spec_mixtral, "opt": _spec_opt, "falcon": _spec_falcon,
-                "phi": _spec_phi}
+def _spec_gpt2(c):
+    h = c["n_embd"]
+    return ArchSpec(family="gpt2", vocab_size=c["vocab_size"], hidden_size=h, intermediate_size=c.get("n_inner") or 4 * h,
+                    num_layers=c["n_layer"], num_heads=c["n_head"], num_kv_heads=c["n_head"], head_dim=h // c["n_head"], norm="ln",
+                    norm_eps=c.get("layer_norm_epsilon", 1e-5), activation="gelu", gated_mlp=False, rotary_dim=0, learned_pos_offset=0,
+                    attn_bias=True, mlp_bias=True, tie_embeddings=True, max_positions=c.get("n_positions", 1024))
+
+
+def _spec_gptj(c):
+    h, hq = c["n_embd"], c["n_head"]
+    return ArchSpec(family="gptj", vocab_size=c["vocab_size"], hidden_size=h, intermediate_size=c.get("n_inner") or 4 * h,
+                    num_layers=c["n_layer"], num_heads=hq, num_kv_heads=hq, head_dim=h // hq, norm="ln",
+                    norm_eps=c.get("layer_norm_epsilon", 1e-5), activation="gelu", gated_mlp=False,
+                    rotary_dim=c.get("rotary_dim") or h // hq, parallel_block=True, mlp_bias=True, max_positions=c.get("n_positions", 2048))
+
+
+def _spec_gpt_neox(c):
+    h, hq = c["hidden_size"], c["num_attention_heads"]
+    d = h // hq
+    par = c.get("use_parallel_residual", True)
+    return ArchSpec(family="gpt_neox", vocab_size=c["vocab_size"], hidden_size=h, intermediate_size=c.get("intermediate_size", 4 * h),
+                    num_layers=c["num_hidden_layers"], num_heads=hq, num_kv_heads=hq, head_dim=d, norm="ln",
+                    norm_eps=c.get("layer_norm_eps", 1e-5), activation="gelu", gated_mlp=False,
+                    rotary_dim=int(d * _rope(c, 0.25)[1]), rope_theta=_rope(c)[0], parallel_block=par, parallel_norm2=par,
+                    attn_bias=True, mlp_bias=True, max_positions=c.get("max_position_embeddings", 2048))
+
+
+SPEC_FROM_HF = {"llama": _spec_llama, "mistral": _spec_llama, "internlm": _spec_llama, "mixtral": _spec_mixtral, "opt": _spec_opt,
+                "falcon": _spec_falcon, "phi": _spec_phi, "gpt2": _spec_gpt2, "gptj": _spec_gptj, "gpt_neox": _spec_gpt_neox}
 
 
 def _shard_rows(w, rank, world):
@@ -136,6 +172,12 @@ class RaggedTransformer:
         if vpad != head.shape[0]:
             head = torch.cat([head, head.new_zeros(vpad - head.shape[0], head.shape[1])])
         self.lm_head = self._t(_shard_rows(head, r, W))
+        self.lm_head_b = None
+        if "lm_head.bias" in sd:  # gpt-j
+            hb = sd["lm_head.bias"]
+            if vpad != hb.shape[0]:
+                hb = torch.cat([hb, hb.new_zeros(vpad - hb.shape[0])])
+            self.lm_head_b = self._t(hb.view(W, -1)[r])
         self.layers = []
         for i in range(s.num_layers):
             p = f"layers.{i}."
@@ -148,7 +190,7 @@ class RaggedTransformer:
             else:
                 ks, vs = _shard_rows(k, r, W), _shard_rows(v, r, W)
             L["qkv_w"] = self._t(torch.cat([qs, ks, vs], 0))
-            if s.attn_bias and p + "q.bias" in sd:
+            if p + "q.bias" in sd:
                 qb, kb, vb = sd[p + "q.bias"], sd[p + "k.bias"], sd[p + "v.bias"]
                 qbs = qb.view(W, -1)[r]
                 kbs = kb[g * d:(g + 1) * d] if self.kv_replicated else kb.view(W, -1)[r]
@@ -235,7 +277,9 @@ class RaggedTransformer:
             attn = K.paged_attention(qkv, cache, tok_seq, tok_pos, bt, self.hq, self.hkv, s.head_dim)
             attn_out = self._linear(attn, L["o_w"])
             if s.parallel_block:
-                mlp_out = self._mlp(L, hn)
+                # gpt-neox gives the MLP its own LayerNorm of the block input (= the residual stream after the fused add)
+                mlp_in = self._norm(residual, L["norm2_w"], L.get("norm2_b")) if s.parallel_norm2 else hn
+                mlp_out = self._mlp(L, mlp_in)
                 x = self._all_reduce(attn_out + mlp_out)
                 if "o_b" in L:
                     x = x + L["o_b"]
@@ -252,7 +296,7 @@ class RaggedTransformer:
         last = K.logits_gather(x, batch.last_tokens())
         last_res = K.logits_gather(residual, batch.last_tokens())
         hn, _ = self._norm(last, self.final_norm_w, self.final_norm_b, last_res)
-        logits = self._linear(hn, self.lm_head)
+        logits = self._linear(hn, self.lm_head, self.lm_head_b)
         if self.tp > 1:
             full = torch.empty(self.tp, *logits.shape, dtype=logits.dtype, device=logits.device)
             dist.all_gather_into_tensor(full, logits.contiguous(), group=self.tp_group)

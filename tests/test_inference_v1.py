@@ -1,4 +1,5 @@
 """init_inference: AutoTP parser finds the all-reduce linears; TP=2 output equals the un-sharded model (gloo)."""
+import pytest
 import torch
 from torch import nn
 
@@ -124,3 +125,46 @@ def test_kernel_inject_generate_matches_hf_greedy():
         ref = hf(prompts[0][None]).logits[0, -1]
     assert torch.allclose(last[0, 0], ref, atol=2e-3)
     assert engine.module.engine.free_blocks == engine.module.engine.free_blocks  # nothing leaked: all sequences flushed
+
+
+def _hf_family(name):
+    import transformers as T
+    if name == "gpt2":
+        return T.GPT2LMHeadModel(T.GPT2Config(vocab_size=101, n_embd=64, n_layer=2, n_head=4, n_positions=128))
+    if name == "gptj":
+        return T.GPTJForCausalLM(T.GPTJConfig(vocab_size=101, n_embd=64, n_layer=2, n_head=4, rotary_dim=8, n_positions=128))
+    if name == "gpt_neox":
+        return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(vocab_size=101, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                                                     num_attention_heads=4, rotary_pct=0.5, max_position_embeddings=128, hidden_act="gelu_new"))
+    if name == "gpt_neox_sequential":
+        return T.GPTNeoXForCausalLM(T.GPTNeoXConfig(vocab_size=101, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                                                     num_attention_heads=4, rotary_pct=0.25, max_position_embeddings=128, hidden_act="gelu_new",
+                                                     use_parallel_residual=False))
+    if name == "llama_bias":  # InternLM layout: Llama with biases on the attention projections
+        return T.LlamaForCausalLM(T.LlamaConfig(vocab_size=101, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                                                num_attention_heads=4, num_key_value_heads=4, max_position_embeddings=128,
+                                                attention_bias=True, tie_word_embeddings=False))
+    raise KeyError(name)
+
+
+@pytest.mark.parametrize("family", ["gpt2", "gptj", "gpt_neox", "gpt_neox_sequential", "llama_bias"])
+def test_kernel_inject_model_families_match_hf(family):
+    """Policy coverage of the reference's v1 containers (gpt2 / gptj / gptneox / internlm): weights of a tiny random HF model
+    mapped onto the ragged transformer reproduce HF's last-token logits and greedy continuation (fp32, CPU)."""
+    pytest.importorskip("transformers")
+    import deepspeedsyclsupport_b200 as deepspeed
+    torch.manual_seed(0)
+    hf = _hf_family(family).eval()
+    with torch.no_grad():  # random biases everywhere: default init leaves them at zero, which would hide mapping mistakes
+        for n, p in hf.named_parameters():
+            if n.endswith("bias"):
+                p.normal_(0, 0.05)
+    prompt = torch.randint(3, 101, (11, ))
+    with torch.no_grad():
+        ref = hf(prompt[None]).logits[0, -1]
+        want = hf.generate(prompt[None], max_new_tokens=5, do_sample=False, pad_token_id=0)[0]
+    engine = deepspeed.init_inference(hf, replace_with_kernel_inject=True, dtype=torch.float32)
+    last = engine(prompt[None]).logits
+    assert torch.allclose(last[0, 0], ref, atol=3e-3), (last[0, 0] - ref).abs().max()
+    out = engine.generate(prompt[None], max_new_tokens=5, do_sample=False, pad_token_id=0)
+    assert out[0, :len(want)].tolist() == want.tolist()
