@@ -687,3 +687,44 @@ def test_ragged_mixtral_engine_bf16_gpu():
     assert (out[1].float().cpu() - ref_b[5]).abs().max() < 0.15 * scale
     out = eng.put([1], [a[149:150]])
     assert (out[0].float().cpu() - ref_a[149]).abs().max() < 0.06 * scale
+
+
+def test_cuda_graph_wrappers_replay_matches_eager():
+    """DSUNet / DSVAE (model_implementations/): the captured graph is replayed with refilled static inputs, one graph per input
+    signature, and reproduces the eager forward."""
+    from test_misc_components import _FakeUNet, _FakeVAE
+    from deepspeedsyclsupport_b200.model_implementations import DSVAE, DSUNet
+    torch.manual_seed(0)
+    unet, vae = _FakeUNet().to(_dev()), _FakeVAE().to(_dev())
+    w = DSUNet(unet, enable_cuda_graph=True)
+    for step in range(4):
+        x, t, e = torch.randn(2, 4, 8, 8, device=_dev()), torch.rand(2, device=_dev()), torch.randn(2, 5, 8, device=_dev())
+        got = w(x, t, e).clone()
+        assert torch.allclose(got, unet(x.contiguous(memory_format=torch.channels_last), t, e), atol=1e-5)
+    assert w.cuda_graph_created and len(w._graphs) == 1
+    w(torch.randn(1, 4, 8, 8, device=_dev()), torch.rand(1, device=_dev()), torch.randn(1, 5, 8, device=_dev()))
+    assert len(w._graphs) == 2  # a new batch size gets its own graph
+    v = DSVAE(vae)
+    z = torch.randn(2, 4, 8, 8, device=_dev())
+    assert torch.allclose(v.decode(z), vae.decode(z), atol=1e-5) and torch.allclose(v.decode(z * 2), vae.decode(z * 2), atol=1e-5)
+
+
+def test_quantized_linear_on_device_matches_host_format():
+    """inference/quantization on the device: the kernels' int8 / int4 payload equals the host restatement bit for bit, and the
+    bf16 forward (dequantise -> tcgen05 GEMM) stays within quantization error of the dense layer."""
+    from deepspeedsyclsupport_b200.inference.quantization import QuantizedLinear
+    from deepspeedsyclsupport_b200.inference.quantization.utils import Quantizer
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(256, 384).to(_dev()).bfloat16()
+    x = torch.randn(50, 256, device=_dev(), dtype=torch.bfloat16)
+    ref = lin(x).float()
+    for bits, tol in ((8, 0.03), (4, 0.3)):
+        cfg = {"num_bits": bits, "group_size": 64, "group_dim": 1, "symmetric": False}
+        pd, sd, _ = Quantizer(cfg).quantize(lin.weight.data)
+        ph, sh, _ = Quantizer(cfg).quantize(lin.weight.data.cpu())
+        assert torch.allclose(sd.cpu(), sh, rtol=1e-5, atol=1e-8)
+        assert (pd.cpu() != ph).float().mean() < 1e-3  # identical up to rounding ties of the bf16 -> fp32 division
+        q = QuantizedLinear(cfg, lin)
+        assert q.qweight.numel() == 256 * 384 * bits // 8
+        out = q(x).float()
+        assert (out - ref).abs().max() < tol * ref.abs().max()

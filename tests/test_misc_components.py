@@ -97,3 +97,80 @@ def test_on_device_and_glue():
     from deepspeedsyclsupport_b200.pydantic_v1 import BaseModel  # noqa: F401
     from deepspeedsyclsupport_b200.nebula.config import DeepSpeedNebulaConfig
     assert DeepSpeedNebulaConfig({"nebula": {"enabled": True, "persistent_time_interval": 5}}).persistent_time_interval == 5
+
+
+@pytest.mark.parametrize("bits,group_dim", [(8, 1), (4, 1), (8, 0)])
+def test_post_init_weight_quantization(bits, group_dim):
+    """weight_quantization.post_init_quant: matching Linear / Embedding modules become int8 / int4 drop-ins whose outputs stay
+    within the quantization error of the original; tied weights stay tied (one quantized copy)."""
+    from deepspeedsyclsupport_b200.inference.quantization import (QuantizedEmbedding, QuantizedLinear,
+                                                                   _init_group_wise_weight_quantization)
+
+    class Tiny(torch.nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.embed = torch.nn.Embedding(64, 64)
+            self.attn = torch.nn.ModuleDict({"q_proj": torch.nn.Linear(64, 64), "keep": torch.nn.Linear(64, 64)})
+            self.head = torch.nn.Linear(64, 64, bias=False)
+            self.head.weight = self.embed.weight  # tied
+
+        def forward(self, ids):
+            return self.head(self.attn["keep"](self.attn["q_proj"](self.embed(ids))))
+
+    torch.manual_seed(0)
+    m = Tiny().eval()
+    ids = torch.randint(0, 64, (3, 9))
+    ref = m(ids)
+    spec = {"num_bits": bits, "group_size": 32, "group_dim": group_dim, "symmetric": False}
+    cfg = {"weight_quantization": {"post_init_quant": {"q_proj": spec, "embed": spec, "head": spec}}}
+    _init_group_wise_weight_quantization(m, cfg)
+    assert isinstance(m.attn["q_proj"], QuantizedLinear) and isinstance(m.embed, QuantizedEmbedding) and isinstance(m.head, QuantizedLinear)
+    assert isinstance(m.attn["keep"], torch.nn.Linear)  # no key matched
+    assert m.head.qweight.data_ptr() == m.embed.qweight.data_ptr()  # tied weights share one payload
+    assert m.embed.qweight.numel() == 64 * 64 * bits // 8
+    out = m(ids)
+    tol = 0.02 if bits == 8 else 0.25
+    assert (out - ref).abs().max() < tol * ref.abs().max()
+
+
+class _FakeUNet(torch.nn.Module):
+    in_channels = 4
+
+    def __init__(self):
+        super().__init__()
+        self.conv = torch.nn.Conv2d(4, 4, 3, padding=1)
+        self.proj = torch.nn.Linear(8, 4)
+
+    def forward(self, sample, t, enc, return_dict=True):
+        return self.conv(sample) * t.view(-1, 1, 1, 1) + self.proj(enc).mean(1)[:, :, None, None]
+
+
+class _FakeVAE(torch.nn.Module):
+
+    def __init__(self):
+        super().__init__()
+        self.d = torch.nn.Conv2d(4, 3, 1)
+        self.e = torch.nn.Conv2d(3, 4, 1)
+
+    def decode(self, x, return_dict=True):
+        return self.d(x)
+
+    def encode(self, x, return_dict=True):
+        return self.e(x)
+
+
+def test_diffusers_wrappers_pass_through_on_host():
+    from deepspeedsyclsupport_b200.model_implementations import DSVAE, DSClipEncoder, DSUNet
+    torch.manual_seed(0)
+    unet, vae = _FakeUNet(), _FakeVAE()
+    w = DSUNet(unet, enable_cuda_graph=True)
+    x, t, e = torch.randn(2, 4, 8, 8), torch.tensor([0.5, 0.25]), torch.randn(2, 5, 8)
+    assert torch.allclose(w(x, t, e), unet(x, t, e)) and w.in_channels == 4 and w.fwd_count == 1
+    assert all(not p.requires_grad for p in w.parameters())
+    v = DSVAE(vae)
+    assert torch.allclose(v.decode(x), vae.decode(x)) and v.encode(torch.randn(1, 3, 4, 4)).shape == torch.Size([1, 4, 4, 4])
+    enc = DSClipEncoder(torch.nn.Linear(8, 8))
+    assert torch.allclose(enc(e), enc.enc(e))
+    m = DSClipEncoder._build_causal_attention_mask(2, 4, torch.float32)
+    assert m.shape == (2, 1, 4, 4) and m[0, 0, 0, 1] < -1e30 and m[0, 0, 1, 0] == 0
