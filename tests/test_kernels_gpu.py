@@ -723,7 +723,13 @@ def test_quantized_linear_on_device_matches_host_format():
         pd, sd, _ = Quantizer(cfg).quantize(lin.weight.data)
         ph, sh, _ = Quantizer(cfg).quantize(lin.weight.data.cpu())
         assert torch.allclose(sd.cpu(), sh, rtol=1e-5, atol=1e-8)
-        assert (pd.cpu() != ph).float().mean() < 1e-3  # identical up to rounding ties of the bf16 -> fp32 division
+        # same storage format: the host restatement decodes the device payload; values differ by at most one step where
+        # (x - min) * (1 / scale) and (x - min) / scale round differently
+        from deepspeedsyclsupport_b200.inference.quantization.utils import dequantize_host
+        wd = dequantize_host(pd.cpu(), sd.cpu(), bits, False, torch.float32)
+        wh = dequantize_host(ph, sh, bits, False, torch.float32)
+        step = sh[:, 0].repeat_interleave(64)
+        assert ((wd - wh).abs() <= step * 1.001).all() and ((wd - wh).abs() > 0.5 * step).float().mean() < 0.02
         q = QuantizedLinear(cfg, lin)
         assert q.qweight.numel() == 256 * 384 * bits // 8
         out = q(x).float()
