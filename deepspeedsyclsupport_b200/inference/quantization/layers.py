@@ -13,7 +13,7 @@ quantized_weight_registry = {}
 
 
 def _quantize_once(weight, config):
-    key = id(weight)
+    key = (id(weight), config["num_bits"], config["group_size"], config.get("group_dim", 1), config.get("symmetric", False))
     if key not in quantized_weight_registry:
         quantized_weight_registry[key] = Quantizer(config).quantize(weight.data)
     return quantized_weight_registry[key]
