@@ -263,3 +263,45 @@ def load_moe_state_dict(engine, load_dir, tag, checkpoint):
     opt_path = engine._get_optimizer_ckpt_name(load_dir, tag, groups._get_expert_parallel_rank(groups._get_max_expert_size_name()))
     if os.path.exists(opt_path) and engine.optimizer is not None:
         engine._moe_optimizer_state = engine.checkpoint_engine.load(opt_path, map_location="cpu")["optimizer"]
+
+
+def load_moe_expert_files(checkpoint_path, tag, state_dict, old_moe_load, model, mpu=None, num_experts=1, checkpoint_engine=None):
+    """Engine-free form of the expert merge (reference: DeepSpeedEngine.load_moe_state_dict, a static method used by the
+    inference engine as well): reads `layer_{L}_expert_{E}_mp_rank_{R}_model_states.pt` for this rank's experts and writes
+    their tensors into `state_dict` under local expert ids.  `old_moe_load`: one expert-parallel group with `num_experts[0]`
+    experts and file names without the layer id grouping of newer checkpoints."""
+    from .layer import MoE
+    if checkpoint_engine is None:
+        from ..runtime.checkpoint_engine.torch_checkpoint_engine import TorchCheckpointEngine
+        checkpoint_engine = TorchCheckpointEngine()
+    mp_rank = 0 if mpu is None else mpu.get_model_parallel_rank()
+
+    def expert_file(layer_id, expert_id):
+        name = f"layer_{layer_id}_expert_{expert_id}_mp_rank_{mp_rank:02d}_model_states.pt"
+        return os.path.join(checkpoint_path, name if tag is None else os.path.join(str(tag), name))
+
+    if old_moe_load:
+        expp_rank = groups._get_expert_data_parallel_rank(groups._get_max_expert_size_name())
+        n = num_experts[0] if isinstance(num_experts, (list, tuple)) else num_experts
+        num_local = max(n // groups._get_expert_parallel_world_size(groups._get_max_expert_size_name()), 1)
+        for local in range(num_local):
+            glob = expp_rank * num_local + local
+            expert_sd = checkpoint_engine.load(expert_file(0, glob), map_location="cpu")
+            for key in list(expert_sd.keys()):
+                state_dict[key.replace(f"expert_{glob}", f"deepspeed_moe.experts.deepspeed_experts.{local}")] = expert_sd.pop(key)
+        return state_dict
+    layer_id = 0
+    for n_module, module in model.named_modules():
+        if not isinstance(module, MoE):
+            continue
+        expp_rank = groups._get_expert_parallel_rank(module.expert_group_name)
+        prefix = f"{n_module}.deepspeed_moe.experts.deepspeed_experts."
+        for local in range(module.num_local_experts):
+            glob = expp_rank * module.num_local_experts + local
+            expert_sd = checkpoint_engine.load(expert_file(layer_id, glob), map_location="cpu")
+            gp = f"{prefix}{glob}."
+            for key, val in expert_sd.items():
+                if key.startswith(gp):
+                    state_dict[f"{prefix}{local}." + key[len(gp):]] = val
+        layer_id += 1
+    return state_dict

@@ -39,6 +39,8 @@ DeepSpeedOptimizerCallable = None
 DeepSpeedSchedulerCallable = None
 
 
+from .engine_compat import EngineCompatMixin
+
 class EngineTimers:
     """Names of the wall-clock timers the engine maintains (parity: engine.py:144-176)."""
 
@@ -68,7 +70,7 @@ class EngineTimers:
                                    BACKWARD_REDUCE_GLOBAL_TIMER, STEP_GLOBAL_TIMER]
 
 
-class DeepSpeedEngine(Module):
+class DeepSpeedEngine(EngineCompatMixin, Module):
 
     def __init__(self, args, model, optimizer=None, model_parameters=None, training_data=None, lr_scheduler=None, mpu=None,
                  dist_init_required=None, collate_fn=None, config=None, config_class=None, dont_change_device=False):

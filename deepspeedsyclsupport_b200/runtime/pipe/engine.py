@@ -85,8 +85,8 @@ class PipelineEngine(DeepSpeedEngine):
         self.has_attention_mask = self.module.__class__.__name__ == "GPT2ModelPipe"
         if self.is_pipe_parallel:
             p2p.init_process_groups(self.grid)
-        self.is_last_stage = self.stage_id == self.num_stages - 1
-        self.is_first_stage = self.stage_id == 0
+        self._last_stage = self.stage_id == self.num_stages - 1
+        self._first_stage = self.stage_id == 0
 
     def set_has_attention_mask(self, value):
         assert isinstance(value, bool)
@@ -165,7 +165,7 @@ class PipelineEngine(DeepSpeedEngine):
         with torch.no_grad():
             self._exec_schedule(sched)
         eval_output = None
-        if self.is_last_stage:
+        if self._last_stage:
             eval_output = self._reduce_outputs(self.fwd_outputs, reduce=reduce_output, micro_batches=micro_batches)
         if compute_loss and (bcast_loss or self.monitor.enabled):
             eval_output = self._bcast_pipe_scalar(eval_output)
@@ -179,6 +179,13 @@ class PipelineEngine(DeepSpeedEngine):
     def set_train_batch_size(self, train_batch_size):
         super().set_train_batch_size(train_batch_size)
         self.micro_batches = self.gradient_accumulation_steps()
+
+    def is_first_stage(self):
+        """True if this process is in the first stage of the pipeline (reference: pipe/engine.py:509)."""
+        return self._first_stage
+
+    def is_last_stage(self):
+        return self._last_stage
 
     def is_first_stage_fn(self):
         return self.stage_id == 0
@@ -218,7 +225,7 @@ class PipelineEngine(DeepSpeedEngine):
         return result
 
     def _aggregate_total_loss(self):
-        if self.is_last_stage:
+        if self._last_stage:
             loss = self._scale_loss_by_gas(self.total_loss)
             self.dp_group_loss = loss.clone().detach()
             agg_loss = self.dp_group_loss.clone().detach()
@@ -239,12 +246,12 @@ class PipelineEngine(DeepSpeedEngine):
         return agg_loss
 
     def set_dataloader(self, loader):
-        if self.is_first_stage or self.is_last_stage:
+        if self._first_stage or self._last_stage:
             self.training_dataloader = loader
             self.data_iterator = iter(self.training_dataloader)
 
     def set_dataiterator(self, iterator):
-        if self.is_first_stage or self.is_last_stage:
+        if self._first_stage or self._last_stage:
             self.training_dataloader = None
             self.data_iterator = iterator
 
@@ -271,7 +278,7 @@ class PipelineEngine(DeepSpeedEngine):
         self._zero_grads(inputs)
         outputs = self.module.forward(inputs) if not isinstance(inputs, tuple) or len(inputs) > 1 else self.module.forward(inputs[0])
         self.pipe_buffers["outputs"][buffer_id] = outputs
-        if self.is_last_stage:
+        if self._last_stage:
             if self._compute_loss and self.module.loss_fn is not None:
                 labels = self.pipe_buffers["labels"][buffer_id]
                 self.loss = self.module.loss_fn(outputs, labels)
@@ -293,7 +300,7 @@ class PipelineEngine(DeepSpeedEngine):
 
     def _exec_backward_pass(self, buffer_id):
         assert self.optimizer is not None, "must provide optimizer during init in order to use backward"
-        if self.is_last_stage:
+        if self._last_stage:
             loss = self._scale_loss_by_gas(self.loss.float()) if self.gradient_accumulation_steps() > 1 else self.loss
             self.optimizer.backward(loss)
             self.optimizer.micro_step_id += 1
@@ -312,7 +319,7 @@ class PipelineEngine(DeepSpeedEngine):
 
     def _exec_load_micro_batch(self, buffer_id):
         batch = self._next_batch()
-        if self.is_first_stage:
+        if self._first_stage:
             loaded = None
             if torch.is_tensor(batch[0]):
                 loaded = batch[0].clone().to(self.device).detach()
@@ -327,7 +334,7 @@ class PipelineEngine(DeepSpeedEngine):
                     loaded.append(mine)
                 loaded = tuple(loaded)
             self.pipe_buffers["inputs"][buffer_id] = loaded
-        if self.is_last_stage:
+        if self._last_stage:
             loaded = batch[1]
             if torch.is_tensor(batch[1]):
                 loaded = batch[1].to(self.device)

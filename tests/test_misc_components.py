@@ -174,3 +174,50 @@ def test_diffusers_wrappers_pass_through_on_host():
     assert torch.allclose(enc(e), enc.enc(e))
     m = DSClipEncoder._build_causal_attention_mask(2, 4, torch.float32)
     assert m.shape == (2, 1, 4, 4) and m[0, 0, 0, 1] < -1e30 and m[0, 0, 1, 0] == 0
+
+
+def _fallback_allreduce_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+
+    class Net(torch.nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.emb = torch.nn.Embedding(20, 8, sparse=True)
+            self.lin = torch.nn.Linear(8, 4)
+
+        def forward(self, ids):
+            return self.lin(self.emb(ids)).sum()
+
+    torch.manual_seed(0)
+    net = Net()
+    engine_net = Net()  # the engine's own parameters have their gradients consumed by the flat store: use a free-standing copy
+    eng, _, _, _ = deepspeed.initialize(model=engine_net, optimizer=torch.optim.SGD(engine_net.parameters(), lr=0.1),
+                                        config={"train_micro_batch_size_per_gpu": 2, "sparse_gradients": True})
+    rank, world = dist.get_rank(), dist.get_world_size()
+    ids = torch.tensor([[1, 3], [3, 5]]) + rank  # different rows per rank
+    net.zero_grad()
+    loss = net(ids)
+    loss.backward()
+    assert net.emb.weight.grad.is_sparse
+    dense_before = [net.emb.weight.grad.to_dense().clone(), net.lin.weight.grad.clone()]
+    gathered = [[torch.zeros_like(t) for _ in range(world)] for t in dense_before]
+    for t, g in zip(dense_before, gathered):
+        dist.all_gather(g, t)
+    want = [sum(g) / world for g in gathered]
+    lin_bias_before = net.lin.bias.grad.clone()
+    eng.buffered_allreduce_fallback(grads=[(n, p.grad) for n, p in net.named_parameters()])
+    assert torch.allclose(net.emb.weight.grad.to_dense(), want[0], atol=1e-6)
+    assert torch.allclose(net.lin.weight.grad, want[1], atol=1e-6)
+    # variable-length gather and a few getters of the reference surface
+    parts = eng.sparse_all_gather(torch.arange(rank + 2).float())
+    assert [p.numel() for p in parts] == [r + 2 for r in range(world)]
+    assert eng.eigenvalue_max_iter() == 100 and eng.zero_partial_offload() == 1.0 and eng.dump_state() is False
+    assert eng.is_map_style_dataset([1, 2]) and not eng.is_iterable_style_dataset([1, 2])
+    eng.update_optimizer_step(7)
+
+
+def test_engine_fallback_allreduce_dense_and_sparse_two_ranks():
+    from common import run_distributed
+    run_distributed(_fallback_allreduce_body, world_size=2)
