@@ -1065,6 +1065,109 @@ class ZeroShardedOptimizer:
         elif u.persistent and self.shard_world > 1:
             dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
 
+    # ---- local (this rank's shard) views of one parameter: flat fp32 fragments, possibly empty
+    # (reference: stage3.py get_local_fp32_param / get_local_fp32_grad_for_param / set_local_hp_param)
+    def _local_span(self, p):
+        u = p.ds_unit
+        off, n = u.param_slice(p.ds_index)
+        lo, hi = u.shard_range()
+        a, b = max(off, lo), min(off + n, hi)
+        if a >= b:
+            return None
+        return u.shard_off + a - lo, u.shard_off + b - lo
+
+    def get_local_fp32_param(self, p, optim_state_key=None):
+        span = self._local_span(p)
+        if span is None:
+            return torch.empty(0, dtype=torch.float32, device=self.device)
+        if optim_state_key is None:
+            return self._master_slice(*span).clone()
+        return self._state_slice(optim_state_key, *span).clone()
+
+    def get_local_fp32_grad_for_param(self, p):
+        span = self._local_span(p)
+        if span is None:
+            return torch.empty(0, dtype=torch.float32, device=self.device)
+        inv = 1.0 / self.loss_scale if self.loss_scale else 1.0
+        return self.grad_shard[span[0]:span[1]].float() * inv
+
+    def set_local_hp_param(self, value, p, optim_state_key=None):
+        span = self._local_span(p)
+        if span is None:
+            return
+        lo, hi = span
+        v = value.reshape(-1).to(self.device, torch.float32)
+        assert v.numel() == hi - lo, f"local fragment has {hi - lo} elements, got {v.numel()}"
+        for r in self.regions:
+            a, b = max(lo, r.lo), min(hi, r.hi)
+            if a >= b:
+                continue
+            if optim_state_key is None:
+                r.master[a - r.lo:b - r.lo].copy_(v[a - lo:b - lo])
+            else:
+                self._ensure_state(r, self._opt_kind)
+                r.state[optim_state_key][a - r.lo:b - r.lo].copy_(v[a - lo:b - lo])
+        if optim_state_key is None:
+            self.lp_shard[lo:hi].copy_(v)
+
+    # names of the reference optimizers for the same operations
+    def get_full_hp_param(self, p, optim_state_key=None):
+        return self.get_full_fp32_param(p) if optim_state_key is None else self.get_full_optimizer_state(p, optim_state_key)
+
+    def set_full_hp_param(self, value, p, optim_state_key=None):
+        if optim_state_key is None:
+            return self.set_full_fp32_param(p, value)
+        return self.set_full_optimizer_state(p, value, optim_state_key)
+
+    def get_fp32_grad_for_param(self, p):
+        return self.get_full_grad(p)
+
+    def set_lr(self, lr):
+        for g in self.param_groups:
+            g["lr"] = lr
+
+    def override_loss_scale(self, loss_scale):
+        """Freeze the loss scale at `loss_scale` (reference: stage3.py override_loss_scale / stage_1_and_2.py)."""
+        if loss_scale != self.external_loss_scale:
+            log_dist(f"[deepspeed] setting loss scale from {self.external_loss_scale} -> {loss_scale}", ranks=[0])
+        self.custom_loss_scaler = True
+        self.external_loss_scale = loss_scale
+
+    def has_overflow(self, partition_gradients=True):
+        return self._check_overflow()
+
+    def check_overflow(self, partition_gradients=True):
+        self.overflow = self._check_overflow()
+        return self.overflow
+
+    def scaled_global_norm(self, norm_type=2):
+        assert norm_type == 2, "only L2 norm supported as of now"
+        return self._compute_global_norm()
+
+    def refresh_fp32_params(self):
+        """fp32 masters <- current 16-bit parameters (after the module weights were overwritten from outside)."""
+        return self.refresh_from_params()
+
+    def initialize_optimizer_states(self):
+        """Materialise the optimizer state (zeros) before the first step, e.g. for checkpoint loading into a fresh engine."""
+        for r in self.regions:
+            self._ensure_state(r, self._opt_kind)
+
+    def get_lean_optimizer_state(self):
+        """Per-region optimizer state without padding (reference name: _get_lean_tensors / get_lean_optimizer_state)."""
+        return [{k: v for k, v in (r.state or {}).items()} for r in self.regions]
+
+    def destroy(self):
+        for h in getattr(self, "_hook_handles", []):
+            h.remove()
+        self._hook_handles = []
+        if getattr(self, "p2p", None) is not None:
+            try:
+                self.p2p.close()
+            except Exception:
+                pass
+            self.p2p = None
+
     def set_full_optimizer_state(self, p, value, key):
         def setter(lo, hi, v):
             for r in self.regions:

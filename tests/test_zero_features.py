@@ -105,6 +105,21 @@ def _frozen_body():
     assert safe_get_full_optimizer_state(p, "exp_avg").abs().sum() == 0
     with deepspeed.zero.GatheredParameters([p]):
         assert torch.allclose(p.detach().float(), torch.full_like(w, 0.25))
+    # the optimizer's own names for the same accessors + local (per-rank) fragments
+    from deepspeedsyclsupport_b200 import comm as dist
+    opt = eng.optimizer
+    local = opt.get_local_fp32_param(p)
+    n = torch.tensor([local.numel()])
+    dist.all_reduce(n)
+    assert n.item() == p.ds_numel and torch.all(local == 0.25)
+    opt.set_local_hp_param(torch.full_like(local, 0.5), p)
+    assert torch.allclose(opt.get_full_hp_param(p), torch.full_like(w, 0.5))
+    assert opt.get_local_fp32_param(p, "exp_avg").numel() == local.numel() and opt.get_local_fp32_grad_for_param(p).numel() == local.numel()
+    opt.set_lr(0.125)
+    assert opt.get_lr()[0] == 0.125 and not opt.check_overflow()
+    opt.override_loss_scale(4.0)
+    assert opt.loss_scale == 4.0
+    opt.destroy()
 
 
 def test_frozen_params_and_fragment_accessors_two_ranks():
