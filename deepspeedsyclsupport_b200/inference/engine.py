@@ -259,3 +259,79 @@ class InferenceEngine(Module):
             raise NotImplementedError("DeepSpeed does not support `num_beams` > 1, if this is important to you please "
                                       "add your request to: https://github.com/microsoft/DeepSpeed/issues/2506")
         return self.module.generate(*inputs, **kwargs)
+
+    # ------------------------------------------------------------------ ALiBi / attention-bias hooks for tensor parallelism
+    # (reference: inference/engine.py:211-236 + module_inject/auto_tp_model_utils.py: HF BLOOM / MPT / Baichuan build an
+    # alibi tensor for ALL heads; a tensor-parallel rank holds only its slice of the heads)
+    def remove_mask_prepare_for_bloom(self):
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_prepare_attn_mask"):
+            tr._prepare_attn_mask = lambda attention_mask, *args, **kwargs: attention_mask
+
+    def _tp_rank_world(self):
+        if self.mp_group is not None and dist.is_initialized():
+            return dist.get_rank(group=self.mp_group), dist.get_world_size(group=self.mp_group)
+        return 0, 1
+
+    def build_alibi_tensor(self):
+        from ..module_inject.auto_tp_model_utils import build_bloom_alibi_tensor, build_mpt_alibi_tensor, get_alibi_mask
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None:
+            if hasattr(tr, "build_alibi_tensor"):
+                tr.build_alibi_tensor = build_bloom_alibi_tensor
+            if hasattr(tr, "build_mpt_alibi_tensor"):
+                tr.build_mpt_alibi_tensor_orig = tr.build_mpt_alibi_tensor
+                tr.__class__.build_mpt_alibi_tensor = build_mpt_alibi_tensor
+        inner = getattr(self.module, "model", None)
+        if inner is not None and hasattr(inner, "get_alibi_mask"):
+            inner.get_alibi_mask_orig = inner.get_alibi_mask
+            inner.__class__.get_alibi_mask = get_alibi_mask
+
+    def build_attn_bias(self):
+        from ..module_inject.auto_tp_model_utils import build_mpt_atten_bias_tensor
+        tr = getattr(self.module, "transformer", None)
+        if tr is not None and hasattr(tr, "_attn_bias"):
+            tr._attn_bias_orig = tr._attn_bias
+            tr.__class__._attn_bias = build_mpt_atten_bias_tensor
+
+    # ------------------------------------------------------------------ checkpoints
+    def load_model_with_checkpoint(self, r_module):
+        """Fill `r_module` (possibly built on the meta device) from `config.checkpoint`: a DeepSpeed checkpoint description
+        ({"type", "checkpoints": [...], "version"} dict or json path), a directory of torch state-dict shards, or one file.
+        Tensor-parallel merge / split of Megatron-style shards goes through SDLoaderFactory."""
+        import glob
+        import os
+        from ..runtime.checkpoint_engine.torch_checkpoint_engine import TorchCheckpointEngine
+        from ..runtime.state_dict_factory import SDLoaderFactory
+        self.checkpoint_engine = self.checkpoint_engine or TorchCheckpointEngine()
+        ckpt = self.checkpoint
+        rank, world = self._tp_rank_world()
+        if isinstance(ckpt, dict) or (isinstance(ckpt, str) and ckpt.endswith(".json")):
+            loader = SDLoaderFactory.get_sd_loader_json(ckpt, self.checkpoint_engine)
+            if isinstance(loader, tuple) or isinstance(loader, list):  # (type, list, version) for non-Megatron descriptions
+                files = loader[1] if len(loader) > 1 else []
+                sds = [self.checkpoint_engine.load(f, map_location="cpu") for f in files]
+            else:
+                _, sd, _ = loader.load(world, rank)
+                sds = [loader.get_module(sd) if hasattr(loader, "get_module") else sd]
+        else:
+            files = [ckpt] if os.path.isfile(ckpt) else sorted(glob.glob(os.path.join(ckpt, "*.pt")) + glob.glob(os.path.join(ckpt, "*.bin")))
+            assert files, f"no checkpoint files under {ckpt}"
+            sds = [self.checkpoint_engine.load(f, map_location="cpu") for f in files]
+        merged = {}
+        for sd in sds:
+            merged.update(sd.get("module", sd.get("model", sd)) if isinstance(sd, dict) else sd)
+        if any(p.is_meta for p in r_module.parameters()):
+            r_module.to_empty(device=get_accelerator().current_device_name())
+        missing, unexpected = r_module.load_state_dict(merged, strict=False)
+        log_dist(f"load_model_with_checkpoint: {len(merged)} tensors, {len(missing)} missing, {len(unexpected)} unexpected", ranks=[0])
+        return r_module
+
+    def destroy(self):
+        """Release graphs / workspaces held by the engine (reference: InferenceEngine.destroy frees the kernel workspace)."""
+        self._graphs = {}
+        self.cuda_graph_created = False
+        inner = getattr(self.module, "engine", None)  # kernel-injected model: flush every tracked sequence
+        if inner is not None and hasattr(inner, "_state_manager"):
+            for uid in list(getattr(inner._state_manager, "tracked_sequences", {}).keys()):
+                inner.flush(uid)

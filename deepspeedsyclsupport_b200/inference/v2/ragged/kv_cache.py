@@ -57,3 +57,25 @@ class BlockedKVCache:
     @property
     def block_size(self):
         return self._config.block_size
+
+    @property
+    def num_caches(self):
+        """Number of cache groups (one: every layer shares the block table; reference supports several KVCacheConfigs)."""
+        return 1
+
+    def offload(self, blocks) -> torch.Tensor:
+        """Copy the given blocks of every layer to pinned host memory and return the host tensor
+        [layers, n, 2, block, heads, head_size]; the blocks themselves stay allocated (reference: kv_cache.offload)."""
+        idx = torch.as_tensor(blocks, dtype=torch.long, device=self._cache.device)
+        picked = self._cache.index_select(1, idx)
+        host = torch.empty(picked.shape, dtype=picked.dtype, device="cpu",
+                           pin_memory=self._cache.is_cuda)
+        host.copy_(picked, non_blocking=self._cache.is_cuda)
+        if self._cache.is_cuda:
+            torch.cuda.current_stream().synchronize()
+        return host
+
+    def restore(self, blocks, host) -> None:
+        """Inverse of `offload`: write host data back into the given blocks."""
+        idx = torch.as_tensor(blocks, dtype=torch.long, device=self._cache.device)
+        self._cache.index_copy_(1, idx, host.to(self._cache.device, non_blocking=True))

@@ -69,3 +69,7 @@ class DSStateManager:
     @property
     def free_blocks(self):
         return self._kv_cache.free_blocks
+
+    @property
+    def n_kv_cache_groups(self):
+        return self._kv_cache.num_caches

@@ -119,3 +119,35 @@ class RaggedBatchWrapper:
     def is_pure_prefill(self):
         """every sequence of the batch is new (no KV history) -- the dense flash kernel can be used per sequence"""
         return all(s == 0 for s in self._seq_seen)
+
+    # ---- reference-named accessors (inference/v2/ragged/ragged_wrapper.py: tensor_toks / tokens_to_seq / ...)
+    @property
+    def tensor_toks(self):
+        return self._n_tokens
+
+    def tokens_to_seq(self, on_device=True):
+        """For every token the index of its sequence in the batch."""
+        return self._d_tok_seq[:self._n_tokens] if on_device else self._h_tok_seq[:self._n_tokens]
+
+    def batch_metadata_buffer(self, on_device=True):
+        """[2] int32: (tokens, sequences) in flight."""
+        t = torch.tensor([self._n_tokens, self._n_seqs], dtype=torch.int32)
+        return t.to(self._d_ids.device) if on_device else t
+
+    def inflight_seq_descriptors(self, on_device=True):
+        """[n_seqs, 4] int32: (first token of the sequence in the batch, tokens in flight, tokens seen before, 0)."""
+        t = torch.zeros(self._n_seqs, 4, dtype=torch.int32)
+        if self._n_seqs:
+            t[:, 0] = torch.tensor(self._seq_start, dtype=torch.int32)
+            t[:, 1] = torch.tensor(self._seq_ntok, dtype=torch.int32)
+            t[:, 2] = torch.tensor(self._seq_seen, dtype=torch.int32)
+        return t.to(self._d_ids.device) if on_device else t
+
+    def kv_ptrs(self, on_device=True):
+        """The block table of the batch ([n_seqs, max_blocks] int32 block ids): the kernels index the cache by block id
+        rather than by raw pointer."""
+        return self._d_block_table[:self._n_seqs] if on_device else self._h_block_table[:self._n_seqs]
+
+    def masks(self, on_device=True):
+        """Placeholder for mask metadata (none: causal masking is derived from tok_pos in the kernels)."""
+        return None

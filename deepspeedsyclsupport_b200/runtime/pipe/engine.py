@@ -187,6 +187,33 @@ class PipelineEngine(DeepSpeedEngine):
     def is_last_stage(self):
         return self._last_stage
 
+    def log_for_device(self, *msg):
+        """Print from every pipeline stage / data-parallel replica selected by DSB200_PIPE_LOG_STAGE / _DP (-1 = all)."""
+        import os
+        want_stage, want_dp = int(os.environ.get("DSB200_PIPE_LOG_STAGE", "-2")), int(os.environ.get("DSB200_PIPE_LOG_DP", "-1"))
+        if want_stage in (-1, self.stage_id) and want_dp in (-1, self.grid.data_parallel_id):
+            print(f"RANK={dist.get_rank()} PIPE-ID={self.stage_id} DATA-ID={self.grid.data_parallel_id} STEP-ID={self.global_steps}", *msg, flush=True)
+
+    def tput_log(self, *msg):
+        if self.global_rank == 0 and self.global_steps % self.steps_per_print() == 0:
+            print(*msg)
+
+    def mem_status(self, msg, print_rank=-1, reset_max=False):
+        """Allocated / cached device memory and their change since the previous call, on one rank."""
+        acc = get_accelerator()
+        if not acc.is_available() or (print_rank != -1 and self.global_rank != print_rank):
+            return
+        acc.synchronize()
+        if reset_max:
+            acc.reset_max_memory_allocated()
+        alloc, cached = acc.memory_allocated(), acc.memory_reserved() if hasattr(acc, "memory_reserved") else 0
+        prev = getattr(self, "_mem_status_prev", (0, 0))
+        self._mem_status_prev = (alloc, cached)
+        gib = 1024**3
+        print(f"RANK={self.global_rank} STAGE={self.stage_id} STEP={self.global_steps} MEMSTATS {msg} "
+              f"current alloc={alloc / gib:0.4f}GB (delta={(alloc - prev[0]) / gib:0.4f}GB max={acc.max_memory_allocated() / gib:0.4f}GB) "
+              f"current cache={cached / gib:0.4f}GB (delta={(cached - prev[1]) / gib:0.4f}GB)", flush=True)
+
     def is_first_stage_fn(self):
         return self.stage_id == 0
 

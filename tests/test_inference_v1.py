@@ -168,3 +168,33 @@ def test_kernel_inject_model_families_match_hf(family):
     assert torch.allclose(last[0, 0], ref, atol=3e-3), (last[0, 0] - ref).abs().max()
     out = engine.generate(prompt[None], max_new_tokens=5, do_sample=False, pad_token_id=0)
     assert out[0, :len(want)].tolist() == want.tolist()
+
+
+def test_bloom_alibi_matches_hf_and_engine_surface():
+    """ALiBi builder used under AutoTP reproduces HF BLOOM's (all heads without a process group, incl. non-power-of-two head
+    counts); InferenceEngine exposes the reference's hook / checkpoint / destroy methods."""
+    T = pytest.importorskip("transformers")
+    from transformers.models.bloom.modeling_bloom import build_alibi_tensor
+    from deepspeedsyclsupport_b200.module_inject.auto_tp_model_utils import build_bloom_alibi_tensor
+    mask = torch.ones(2, 9, dtype=torch.long)
+    mask[1, :3] = 0
+    for heads in (8, 12):
+        assert torch.allclose(build_bloom_alibi_tensor(mask, heads, torch.float32), build_alibi_tensor(mask, heads, torch.float32), atol=1e-6)
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.inference.engine import InferenceEngine
+    for name in ("destroy", "remove_mask_prepare_for_bloom", "build_alibi_tensor", "build_attn_bias", "load_model_with_checkpoint"):
+        assert callable(getattr(InferenceEngine, name))
+
+
+def test_inference_engine_loads_checkpoint_into_meta_model(tmp_path):
+    import deepspeedsyclsupport_b200 as deepspeed
+    torch.manual_seed(0)
+    src = nn.Sequential(nn.Linear(8, 8), nn.ReLU(), nn.Linear(8, 4))
+    torch.save(src.state_dict(), tmp_path / "model.pt")
+    with torch.device("meta"):
+        dst = nn.Sequential(nn.Linear(8, 8), nn.ReLU(), nn.Linear(8, 4))
+    eng = deepspeed.init_inference(nn.Sequential(nn.Linear(8, 8), nn.ReLU(), nn.Linear(8, 4)), dtype=torch.float32, checkpoint=str(tmp_path))
+    eng.load_model_with_checkpoint(dst)
+    x = torch.randn(3, 8)
+    assert torch.allclose(dst(x), src(x)) and not any(p.is_meta for p in dst.parameters())
+    eng.destroy()

@@ -171,3 +171,31 @@ def test_ragged_mixtral_grouped_experts_match_dense():
     assert torch.allclose(out[0], ref_a[17], atol=5e-3) and torch.allclose(out[1], ref_b[5], atol=5e-3)
     out = eng.put([1], [a[18:19]])
     assert torch.allclose(out[0], ref_a[18], atol=5e-3)
+
+
+def test_ragged_surface_accessors_and_kv_offload():
+    """reference-named accessors of the ragged batch / sequence descriptor / KV cache (offload -> restore round trip)."""
+    eng, _ = _engine()
+    sm = eng._state_manager
+    torch.manual_seed(0)
+    eng.put([7], [torch.randint(0, 97, (20, ))])
+    seq = sm.get_sequence(7)
+    assert seq.tracking_id == 7 and seq.max_context >= 128 and seq.kv_cache_ids().numel() == seq.cur_allocated_blocks
+    assert sm.n_kv_cache_groups == 1 and sm._kv_cache.num_caches == 1
+    ids = seq.kv_cache_ids().tolist()
+    before = sm.get_cache(0)[ids].clone()
+    host = sm._kv_cache.offload(ids)
+    sm.get_cache(0)[ids] = 0
+    sm.get_cache(1)[ids] = 0
+    sm._kv_cache.restore(ids, host)
+    assert torch.equal(sm.get_cache(0)[ids], before)
+    b = eng._batch
+    b.clear()
+    b.insert_sequence(seq, torch.randint(0, 97, (3, )))
+    b.finalize()
+    assert b.tensor_toks == 3 and b.tokens_to_seq(False).tolist() == [0, 0, 0]
+    assert b.batch_metadata_buffer(False).tolist() == [3, 1] and b.inflight_seq_descriptors(False)[0].tolist() == [0, 3, 20, 0]
+    assert b.kv_ptrs(False).shape[0] == 1 and b.masks() is None
+    n = seq.cur_allocated_blocks
+    seq.free_kv_cache(ids[:1])
+    assert seq.cur_allocated_blocks == n - 1 and seq.kv_cache_ids().tolist() == ids[1:]
