@@ -272,6 +272,73 @@ class Autotuner(object):
         step = (max_micro_batch_size - min_micro_batch_size) / (n - 1)
         return sorted({max(1, int(round(min_micro_batch_size + i * step))) for i in range(n)})
 
+    def get_plateau_mbs(self, tuning_space_name):
+        """Largest micro-batch size before the metric stops improving (< 5 % gain or a drop) in a space's records."""
+        recs = [(e[DS_CONFIG][TRAIN_MICRO_BATCH_SIZE_PER_GPU], v) for e, v, _ in self.records.get(tuning_space_name, []) if v is not None]
+        prev_val, plateau = None, 0
+        for mbs, val in sorted(recs):
+            if prev_val is not None and (val < prev_val or (val - prev_val) / prev_val < 0.05):
+                break
+            prev_val, plateau = val, mbs
+        return plateau
+
+    def get_val_from_user_args(self, ds_name):
+        """Value the user script received on its command line for the argument mapped to `ds_name` (autotuning.arg_mappings)."""
+        mappings = self.autotuning_config.arg_mappings
+        user_args = list(getattr(self.args, "user_args", []) or [])
+        if mappings and ds_name in mappings and mappings[ds_name] in user_args:
+            i = user_args.index(mappings[ds_name])
+            if i + 1 < len(user_args) and str(user_args[i + 1]).isnumeric():
+                return user_args[i + 1]
+        return None
+
+    def get_min_max_micro_batch_size(self, stage, min_micro_batch_size, calculated_max_micro_batch_size):
+        """(smallest runnable, largest runnable) micro-batch size of a ZeRO stage: probe the minimum, then double up to
+        the calculated maximum and bisect between the last success and the first failure."""
+        space, name = self._user_overlaid_space(DEFAULT_TUNING_SPACES[stage]), f"z{stage}"
+
+        def runs(mbs):
+            cfg = self._base_config(space, mbs)
+            exp, val = self.run_ds_config(cfg, canonical_name(cfg, tuning_keys=[], prefix=f"{name}_probe"))
+            self.update_records(name, exp, val, 1)
+            return val is not None
+
+        if not runs(min_micro_batch_size):
+            return -1, -1
+        lo, hi = min_micro_batch_size, None
+        mbs = min_micro_batch_size * 2
+        while mbs <= calculated_max_micro_batch_size:
+            if runs(mbs):
+                lo = mbs
+                mbs *= 2
+            else:
+                hi = mbs
+                break
+        while hi is not None and hi - lo > 1:
+            mid = (lo + hi) // 2
+            if runs(mid):
+                lo = mid
+            else:
+                hi = mid
+        return min_micro_batch_size, lo
+
+    def run_tuning_micro_batch_sizes(self, tuning_micro_batch_sizes, max_train_batch_size_per_gpu, tuning_micro_batch_sizes_overwritten,
+                                     stage, tuning_space_name):
+        """Run one experiment per candidate micro-batch size (gradient accumulation chosen to respect the batch-size cap);
+        returns the largest size that ran."""
+        space = self._user_overlaid_space(DEFAULT_TUNING_SPACES[stage])
+        largest = 0
+        for mbs in sorted(tuning_micro_batch_sizes):
+            cfg = self._base_config(space, mbs)
+            if max_train_batch_size_per_gpu and not tuning_micro_batch_sizes_overwritten:
+                cfg[GRADIENT_ACCUMULATION_STEPS] = max(1, int(max_train_batch_size_per_gpu) // mbs)
+            exp, val = self.run_ds_config(cfg, canonical_name(cfg, tuning_keys=[], prefix=tuning_space_name))
+            self.update_records(tuning_space_name, exp, val, 1)
+            if val is None:
+                break
+            largest = mbs
+        return largest
+
     def _sweep_micro_batch(self, space, space_name, start_mbs, cap):
         """Doubling sweep; returns (largest runnable mbs, best mbs, best metric)."""
         mbs, largest, best_mbs, best_val = max(1, start_mbs), 0, 0, None

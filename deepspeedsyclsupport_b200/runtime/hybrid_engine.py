@@ -189,3 +189,39 @@ class DeepSpeedHybridEngine(DeepSpeedEngine):
         if self._training_start_time is not None:
             self._training_latency += time.time() - self._training_start_time
             self._training_start_time = time.time()
+
+    # ------------------------------------------------------------------ reference container surface
+    # The reference builds one inference "container" per transformer layer that aliases the training weights into its
+    # fused-kernel module (hybrid_engine.py:214-300).  Here the training layers already run on the fused kernels, so a
+    # container is just a record of (layer, index, architecture): these methods keep the names for code that introspects
+    # the hybrid engine, and `_inference_containers` lists the layers whose parameter units are pinned around generate().
+    def populate_all_inference_policies(self):
+        from ..inference.kernel_inject import SUPPORTED
+        self.inference_policies = {name: name for name in SUPPORTED}
+        return self.inference_policies
+
+    def new_inference_container(self, orig_layer, policy_cls, layer_id):
+        return {"layer": orig_layer, "policy": policy_cls, "layer_id": layer_id,
+                "units": sorted({id(getattr(p, "ds_unit", None)) for p in orig_layer.parameters() if hasattr(p, "ds_unit")})}
+
+    def create_inference_containers(self, module, layer_id=0):
+        """Transformer blocks of `module` in execution order: the children of the longest ModuleList found."""
+        lists = [m for m in module.modules() if isinstance(m, torch.nn.ModuleList) and len(m) > 0]
+        blocks = max(lists, key=len) if lists else []
+        policy = getattr(getattr(self.module, "config", None), "model_type", None)
+        self._inference_containers = [self.new_inference_container(b, policy, layer_id + i) for i, b in enumerate(blocks)]
+        return self._inference_containers
+
+    def create_inference_module(self):
+        """(Re)bind generation to this engine: containers are rebuilt and `module.generate` routes through `generate()`."""
+        self.populate_all_inference_policies()
+        self.create_inference_containers(self.module)
+        if hasattr(self.module, "generate") and getattr(self.module.generate, "__self__", None) is not self:
+            self._generate = self.module.generate
+            self.module.generate = self.generate
+        return self.module
+
+    def convert_to_linear_transposed(self, model):
+        """The reference transposes nn.Linear weights for its inference GEMMs; the tcgen05 GEMM takes [out, in] weights
+        natively (K-major B operand), so nothing is rewritten."""
+        return model
