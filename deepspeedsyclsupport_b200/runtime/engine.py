@@ -703,6 +703,7 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
             return MoEZeroOptimizer(self.module, basic_optimizer, stage=stage, dp_group=self.seq_data_parallel_group,
                                     expert_data_parallel_group=self.expert_data_parallel_group, **common)
         if stage == 3:
+            common["aio_config"] = self.aio_config()
             if self.mics_shard_size() > 0:
                 from .zero.mics import MiCS_Optimizer
                 return MiCS_Optimizer(self.module, basic_optimizer, mics_shard_size=self.mics_shard_size(),

@@ -59,14 +59,89 @@ class _Region:
         return t.pin_memory() if self.pin else t
 
 
+class _NvmeRegion(_Region):
+    """Optimizer state of [lo, hi) kept in files (ZeRO-Infinity): the fp32 master and the moments are cut into sub-groups of
+    `sub_group` elements and streamed through two pinned buffers around each sub-group's update (reads of group g+1 overlap
+    the update of g, writes of g overlap the update of g+1; runtime/swap_tensor/optimizer_swapper.py over csrc/host/aio.cpp).
+    Everything else (fragment accessors, checkpoints, client optimizers) sees ordinary host tensors: touching `.master` /
+    `.state` makes the region resident, the next step writes it back to the files and drops the host copy.
+    (reference: stage3.py:561-595,926-942 + swap_tensor/partitioned_optimizer_swapper.py, pipelined_optimizer_swapper.py)"""
+    is_nvme = True
+
+    def __init__(self, lo, hi, folder, aio_config, sub_group, rank, pin):
+        self.lo, self.hi, self.device = lo, hi, torch.device("cpu")
+        self.pin = pin and torch.cuda.is_available()
+        self.host_grad = self.host_lp = None
+        n = hi - lo
+        sub_group = max(1, min(int(sub_group), n))
+        self.bounds = [(a, min(a + sub_group, n)) for a in range(0, n, sub_group)]
+        self.folder, self.aio_config, self.rank = folder, dict(aio_config or {}), rank
+        self._master = torch.empty(n, dtype=torch.float32)  # resident until the first step
+        self._state = {}
+        self.swapper = None
+
+    # resident view (slow paths)
+    def _materialize(self):
+        if self._master is not None:
+            return
+        n = self.hi - self.lo
+        names = self.swapper.state_names
+        full = {k: torch.empty(n, dtype=torch.float32) for k in names}
+        for g, (a, b) in enumerate(self.bounds):
+            bufs = self.swapper.swap_in(g)
+            for k in names:
+                full[k][a:b].copy_(bufs[k])
+        self._master = full.pop("master")
+        self._state = full
+
+    @property
+    def master(self):
+        self._materialize()
+        return self._master
+
+    @master.setter
+    def master(self, v):
+        self._master = v
+
+    @property
+    def state(self):
+        self._materialize()
+        return self._state
+
+    @state.setter
+    def state(self, v):
+        self._materialize()
+        self._state = v
+
+    @property
+    def resident(self):
+        return self._master is not None
+
+    def swap_out_all(self):
+        """Resident tensors -> files (creating the swapper on first use); the host copy is dropped."""
+        if self._master is None:
+            return
+        from ..swap_tensor.optimizer_swapper import OptimizerStateSwapper
+        names = ("master", ) + tuple(sorted(self._state.keys()))
+        if self.swapper is None or tuple(self.swapper.state_names) != names:
+            self.swapper = OptimizerStateSwapper(self.folder, self.aio_config, [b - a for a, b in self.bounds], rank=self.rank,
+                                                 state_names=names)
+        for g, (a, b) in enumerate(self.bounds):
+            tensors = {"master": self._master[a:b]}
+            tensors.update({k: v[a:b] for k, v in self._state.items()})
+            self.swapper.initialize(g, tensors)
+        self._master, self._state = None, {}
+
+
 class ZeroShardedOptimizer:
 
     def __init__(self, module, init_optimizer, *, stage, zero_config, dtype, dp_group=None, shard_group=None,
                  replica_group=None, static_loss_scale=1.0, dynamic_loss_scale=False, dynamic_loss_args=None,
                  clip_grad=0.0, gradient_accumulation_steps=1, grad_accum_dtype=None, communication_data_type=None,
                  mpu=None, timers=None, gradient_predivide_factor=1.0, prescale_gradients=False, grad_divisor=None,
-                 broadcast_src=0, elastic_checkpoint=False, param_filter=None):
+                 broadcast_src=0, elastic_checkpoint=False, param_filter=None, aio_config=None):
         self.module = module
+        self.aio_config = aio_config
         self.optimizer = init_optimizer
         self.stage = int(stage)
         self.zero_config = zero_config
@@ -271,7 +346,13 @@ class ZeroShardedOptimizer:
             ratio = float(oc.ratio)
             cut = int(self.total_shard * ratio) // 64 * 64 if ratio < 1.0 else self.total_shard
             if cut > 0:
-                self.regions.append(_Region(0, cut, torch.device("cpu"), oc.pin_memory))
+                if str(getattr(oc.device, "value", oc.device)) == "nvme":
+                    assert oc.nvme_path is not None, "offload_optimizer.device = nvme needs offload_optimizer.nvme_path"
+                    rank = dist.get_rank() if dist.is_initialized() else 0
+                    self.regions.append(_NvmeRegion(0, cut, os.path.join(str(oc.nvme_path), "zero_stage_3"), getattr(self, "aio_config", None),
+                                                    self.zero_config.sub_group_size, rank, oc.pin_memory))
+                else:
+                    self.regions.append(_Region(0, cut, torch.device("cpu"), oc.pin_memory))
             if cut < self.total_shard:
                 self.regions.append(_Region(cut, self.total_shard, self.device, False))
         else:
@@ -902,6 +983,11 @@ class ZeroShardedOptimizer:
                 grads = self.grad_shard[region.lo:region.hi]
                 lp_all = self.lp_shard[region.lo:region.hi]
                 inv_dev, gs = (self._inv_scale if self.cuda else None), (1.0 if self.cuda else float(self._inv_scale.item()))
+            if getattr(region, "is_nvme", False):
+                self._nvme_region_step(kind, region, grads, lp_all, inv_dev, gs)
+                if on_host:
+                    self.lp_shard[region.lo:region.hi].copy_(region.host_lp, non_blocking=True)
+                continue
             for gi, lo, hi in self.runs:
                 a, b = max(lo, region.lo), min(hi, region.hi)
                 if a >= b or gi < 0:
@@ -914,6 +1000,32 @@ class ZeroShardedOptimizer:
                     lp_all[s].copy_(region.master[s])
             if on_host:
                 self.lp_shard[region.lo:region.hi].copy_(region.host_lp, non_blocking=True)
+
+    def _nvme_region_step(self, kind, region, grads, lp_all, inv_dev, gs):
+        """Sub-group by sub-group update of a file-backed region with double-buffered reads / writes."""
+        from types import SimpleNamespace
+        region.swap_out_all()  # no-op unless a slow path made the region resident since the last step
+        sw = region.swapper
+        sw.prefetch(0)
+        for g, (ga, gb) in enumerate(region.bounds):
+            bufs = sw.swap_in(g)
+            if g + 1 < len(region.bounds):
+                sw.handle.wait()  # the buffer group g+1 reads into was last written out by group g-1
+                sw.prefetch(g + 1)
+            view = SimpleNamespace(master=bufs["master"], state={k: v for k, v in bufs.items() if k != "master"})
+            glo, ghi = region.lo + ga, region.lo + gb
+            for gi, lo, hi in self.runs:
+                a, b = max(lo, glo), min(hi, ghi)
+                if a >= b or gi < 0:
+                    continue
+                s_grp = slice(a - glo, b - glo)        # inside the sub-group buffers
+                s_reg = slice(a - region.lo, b - region.lo)  # inside the region-wide gradient / 16-bit buffers
+                lp = lp_all[s_reg] if self.dtype != torch.float32 else None
+                self._apply_update(kind, view, s_grp, grads[s_reg], lp, self.param_groups[gi], inv_dev, gs)
+                if lp is None:
+                    lp_all[s_reg].copy_(view.master[s_grp])
+            sw.swap_out(g, async_op=True)
+        sw.handle.wait()
 
     def _apply_update(self, kind, region, s, g, lp, hp, inv_dev, gs):
         p = region.master[s]

@@ -33,7 +33,7 @@ class DeepSpeedZeroOptimizer_Stage3(ZeroShardedOptimizer):
                          gradient_accumulation_steps=gradient_accumulation_steps, grad_accum_dtype=gradient_accumulation_dtype,
                          communication_data_type=communication_data_type, mpu=mpu, timers=timers,
                          gradient_predivide_factor=gradient_predivide_factor, prescale_gradients=not postscale_gradients,
-                         grad_divisor=grad_divisor, elastic_checkpoint=elastic_checkpoint)
+                         grad_divisor=grad_divisor, elastic_checkpoint=elastic_checkpoint, aio_config=aio_config)
 
     def empty_partition_cache(self):
         """Release every gathered unit (parity: stage3.empty_partition_cache)."""

@@ -189,3 +189,44 @@ def test_lr_schedules_from_config():
     rt.step()
     rt.step()
     assert opt.param_groups[0]["lr"] > 0.001
+
+
+def _nvme_body(path):
+    """ZeRO-Infinity optimizer tier: state streamed from files in sub-groups must reproduce the host-offload run exactly, and the
+    slow paths (fragment accessors, state_dict round trip) must see / persist the same values."""
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.utils.tensor_fragment import safe_get_full_fp32_param, safe_get_full_optimizer_state
+
+    def run(offload):
+        torch.manual_seed(0)
+        model = SimpleModel(hidden_dim=64, nlayers=3)
+        cfg = {"train_micro_batch_size_per_gpu": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}},
+               "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "sub_group_size": 3000, "offload_optimizer": offload},
+               "aio": {"block_size": 262144, "queue_depth": 4, "thread_count": 1}}
+        eng, _, _, _ = deepspeed.initialize(model=model, config=cfg)
+        losses = []
+        for i, (x, y) in enumerate(random_batches(5, 4, 64, seed=3)):
+            loss = eng(x, y)
+            eng.backward(loss)
+            eng.step()
+            losses.append(loss.item())
+            if i == 2:  # a slow path in the middle of training: the region becomes resident and is written back by the next step
+                p = model.linears[1].weight
+                assert safe_get_full_optimizer_state(p, "exp_avg").abs().sum() > 0
+        p = model.linears[0].weight
+        return losses, safe_get_full_fp32_param(p).clone(), eng
+
+    l_cpu, w_cpu, _ = run({"device": "cpu"})
+    l_nvme, w_nvme, eng = run({"device": "nvme", "nvme_path": path})
+    assert l_cpu == l_nvme and torch.equal(w_cpu, w_nvme)
+    region = eng.optimizer.regions[0]
+    assert getattr(region, "is_nvme", False) and len(region.bounds) > 1
+    import os
+    files = [f for _, _, fs in os.walk(path) for f in fs if f.endswith(".swp")]
+    assert len(files) == 3 * len(region.bounds)  # master, exp_avg, exp_avg_sq per sub-group
+    sd = eng.optimizer.state_dict()
+    eng.optimizer.load_state_dict(sd)
+
+
+def test_nvme_optimizer_state_matches_host_offload(tmp_path):
+    run_distributed(_nvme_body, world_size=1, args=(str(tmp_path), ))
