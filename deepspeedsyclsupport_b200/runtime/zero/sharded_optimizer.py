@@ -220,7 +220,7 @@ class ZeroShardedOptimizer:
         self._trace = {"fwd": [], "bwd": []}
         self._trace_frozen = False
         self._trace_pos = {"fwd": 0, "bwd": 0}
-        if self.stage == 3 and self.shard_world > 1:
+        if self._fetching:
             self._register_module_hooks()
         log_dist(f"ZeRO stage {self.stage}: {len(self.units)} units, shard world {self.shard_world}, replica world "
                  f"{self.replica_world}, {self.total_shard * self.shard_world / 1e6:.1f}M padded elements, "
@@ -295,14 +295,35 @@ class ZeroShardedOptimizer:
             u.shard_off = off
             off += u.shard_numel
         self.total_shard = off
+        # ---- ZeRO-Infinity parameter tier: the 16-bit shards live in (pinned) host memory, or in a memory-mapped file for
+        # device = nvme; a unit exists on the device only between its fetch and its release, also at shard world 1
+        # (reference: offload_param, partition_parameters.py remote_device / partitioned_param_swapper.py)
+        op = getattr(self.zero_config, "offload_param", None)
+        op_dev = str(getattr(op.device, "value", op.device)) if op is not None else "none"
+        self.offload_param = self.stage == 3 and op_dev in ("cpu", "nvme")
         self.p2p = None
         self._setup_p2p()
         if self.p2p is not None:
             self.lp_shard = self.p2p.view(self._p2p_lp_off, (self.total_shard, ), self.dtype)
             self.lp_shard.zero_()
+        elif self.offload_param and op_dev == "nvme":
+            assert op.nvme_path is not None, "offload_param.device = nvme needs offload_param.nvme_path"
+            rank = dist.get_rank() if dist.is_initialized() else 0
+            folder = os.path.join(str(op.nvme_path), "zero_stage_3", f"rank{rank}")
+            os.makedirs(folder, exist_ok=True)
+            self._lp_file = os.path.join(folder, "lp_params.swp")
+            nbytes = max(self.total_shard, 1) * torch.empty(0, dtype=self.dtype).element_size()
+            with open(self._lp_file, "wb") as f:
+                f.truncate(nbytes)
+            self.lp_shard = torch.from_file(self._lp_file, shared=True, size=max(self.total_shard, 1), dtype=self.dtype)[:self.total_shard]
+        elif self.offload_param:
+            self.lp_shard = torch.zeros(self.total_shard, dtype=self.dtype)
+            if self.cuda and getattr(op, "pin_memory", False):
+                self.lp_shard = self.lp_shard.pin_memory()
         else:
             self.lp_shard = torch.zeros(self.total_shard, dtype=self.dtype, device=self.device)
-        keep_full = self.stage <= 2 or self.shard_world == 1
+        self._fetching = self.stage == 3 and (self.shard_world > 1 or self.offload_param)
+        keep_full = self.stage <= 2 or (self.shard_world == 1 and not self.offload_param)
         self.lp_full = None
         if keep_full and self.shard_world > 1:
             self.lp_full = torch.empty(sum(u.padded for u in self.units), dtype=self.dtype, device=self.device)
@@ -312,7 +333,7 @@ class ZeroShardedOptimizer:
             flat = self._unit_flat_from_params(u, broadcast_src)
             lo, hi = u.shard_range()
             u.shard.copy_(flat[lo:hi])
-            if self.shard_world == 1:
+            if self.shard_world == 1 and keep_full:
                 u.full = u.shard  # parameters alias the shard: gather/release are the identity
                 u.bind_params()
             elif keep_full:
@@ -358,7 +379,7 @@ class ZeroShardedOptimizer:
         else:
             self.regions.append(_Region(0, self.total_shard, self.device, False))
         for r in self.regions:
-            if self.dtype == torch.float32 and r.device == self.device:
+            if self.dtype == torch.float32 and r.device == self.lp_shard.device and not getattr(r, "is_nvme", False):
                 r.master = self.lp_shard[r.lo:r.hi]  # fp32 training: the parameters ARE the master weights
             else:
                 r.master.copy_(self.lp_shard[r.lo:r.hi].float())
@@ -371,7 +392,7 @@ class ZeroShardedOptimizer:
         memory so the ZeRO-3 collectives run as our own pull kernels over NVLink (csrc/comm/symm.cu):
         all-gather = every rank copies peers' shards; reduce-scatter = every rank sums its slice over peers' buffers,
         fused with 1/world scaling, dtype cast, accumulation into the gradient shard and the grad-norm partial."""
-        want = (self.cuda and self.stage == 3 and self.shard_world > 1 and self.replica_world == 1 and
+        want = (self.cuda and self.stage == 3 and self.shard_world > 1 and self.replica_world == 1 and not self.offload_param and
                 bool(getattr(self.zero_config, "fused_collectives", True)) and self.dtype == torch.bfloat16 and
                 not self.zero_config.zero_quantized_weights and not self.zero_config.zero_quantized_gradients and
                 os.environ.get("DSB200_DISABLE_P2P", "0") != "1" and self.shard_world <= 16)
@@ -558,7 +579,7 @@ class ZeroShardedOptimizer:
         elif self.stage >= 2 and self.shard_world > 1:
             self._reduce_unit(u)
         # stage 0/1: reduction happens once at the accumulation boundary (reduce_gradients)
-        if self.stage == 3 and self.shard_world > 1 and not u.persistent and _in_backward():
+        if self._fetching and not u.persistent and _in_backward():
             self.release_unit(u)
 
     def _reduce_unit(self, u):
@@ -641,7 +662,7 @@ class ZeroShardedOptimizer:
         for u in self.units:
             u.reduced = False
             u.ready = 0
-        if self.stage == 3 and self.shard_world > 1:
+        if self._fetching:
             for u in self.units:
                 if not u.persistent and u.status == ZeroParamStatus.AVAILABLE:
                     self.release_unit(u)
@@ -666,13 +687,23 @@ class ZeroShardedOptimizer:
                 self.p2p.all_gather(u.full, self._p2p_lp_off + u.shard_off * 2, u.shard_numel * 2)
             elif self.zero_config.zero_quantized_weights and self.cuda:
                 from .zeropp import quantized_all_gather
-                quantized_all_gather(u.full, u.shard, self.shard_group)
+                quantized_all_gather(u.full, u.shard.to(self.device, non_blocking=True) if self.offload_param else u.shard, self.shard_group)
             else:
-                dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+                self._gather_unit_into(u.full, u)
             if stream is not None:
                 u.gather_event = torch.cuda.Event()
                 u.gather_event.record(stream)
         u.status = ZeroParamStatus.INFLIGHT
+
+    def _gather_unit_into(self, full, u):
+        """full[padded] <- every rank's shard of the unit (host-resident shards are staged to the device first)."""
+        shard = u.shard
+        if self.shard_world == 1:
+            full[:u.shard_numel].copy_(shard, non_blocking=True)
+            return
+        if shard.device != full.device:
+            shard = shard.to(full.device, non_blocking=True)
+        dist.all_gather_into_tensor(full, shard, group=self.shard_group)
 
     def _fetch(self, u):
         if u.status == ZeroParamStatus.AVAILABLE:
@@ -982,6 +1013,8 @@ class ZeroShardedOptimizer:
             else:
                 grads = self.grad_shard[region.lo:region.hi]
                 lp_all = self.lp_shard[region.lo:region.hi]
+                if lp_all.device != region.device:  # device-side update with host-resident shards: stage the 16-bit output
+                    lp_all = torch.empty(region.hi - region.lo, dtype=self.dtype, device=region.device)
                 inv_dev, gs = (self._inv_scale if self.cuda else None), (1.0 if self.cuda else float(self._inv_scale.item()))
             if getattr(region, "is_nvme", False):
                 self._nvme_region_step(kind, region, grads, lp_all, inv_dev, gs)
@@ -1000,6 +1033,8 @@ class ZeroShardedOptimizer:
                     lp_all[s].copy_(region.master[s])
             if on_host:
                 self.lp_shard[region.lo:region.hi].copy_(region.host_lp, non_blocking=True)
+            elif lp_all.data_ptr() != self.lp_shard[region.lo:region.hi].data_ptr() and self.dtype != torch.float32:
+                self.lp_shard[region.lo:region.hi].copy_(lp_all)
 
     def _nvme_region_step(self, kind, region, grads, lp_all, inv_dev, gs):
         """Sub-group by sub-group update of a file-backed region with double-buffered reads / writes."""
@@ -1092,14 +1127,14 @@ class ZeroShardedOptimizer:
             self._p2p_reduce_count = 0
             self._p2p_barrier_events = {}
             return
-        if self.shard_world > 1:
+        if self.shard_world > 1 or self.offload_param:
             if self.keep_full:
                 for u in self.units:
                     dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
             else:
                 for u in self.units:
                     if u.persistent:
-                        dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+                        self._gather_unit_into(u.full, u)
             if self.cuda:
                 self.ag_stream.wait_stream(torch.cuda.current_stream())
         elif self.cuda and self.ag_stream is not None:
@@ -1174,8 +1209,8 @@ class ZeroShardedOptimizer:
         u = p.ds_unit
         if self.keep_full and self.shard_world > 1:
             dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
-        elif u.persistent and self.shard_world > 1:
-            dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+        elif u.persistent and (self.shard_world > 1 or self.offload_param):
+            self._gather_unit_into(u.full, u)
 
     # ---- local (this rank's shard) views of one parameter: flat fp32 fragments, possibly empty
     # (reference: stage3.py get_local_fp32_param / get_local_fp32_grad_for_param / set_local_hp_param)
@@ -1366,10 +1401,10 @@ class ZeroShardedOptimizer:
         if self.p2p is not None:
             torch.cuda.synchronize()
             dist.barrier(group=self.shard_group)
-        if self.shard_world > 1:
+        if self.shard_world > 1 or self.offload_param:
             for u in self.units:
                 if self.keep_full or u.persistent:
-                    dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
+                    self._gather_unit_into(u.full, u)
 
     def refresh_from_params(self):
         """Re-shard after module weights were loaded into the (gathered) parameters."""

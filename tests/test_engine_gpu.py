@@ -82,3 +82,45 @@ def test_engine_trains_llama(stage):
     assert losses[-1] < losses[0] - 0.5, losses
     assert native.launch_count - n0 > 100
     assert engine.get_global_grad_norm() > 0
+
+
+@pytest.mark.parametrize("tier", ["cpu", "nvme", "nvme_optimizer"])
+def test_engine_zero_infinity_tiers_match_plain_zero3(tier, tmp_path):
+    """offload_param (pinned host / memory-mapped file) and the NVMe optimizer tier on the device path: the loss trajectory must
+    equal plain ZeRO-3 with host optimizer offload (same CPU Adam math), and units must not stay resident."""
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
+
+    def run(zero_extra):
+        torch.manual_seed(0)
+        cfg = llama_config("tiny", hidden_size=256, intermediate_size=768, num_attention_heads=2, num_key_value_heads=2,
+                           num_hidden_layers=2, vocab_size=1024, activation_checkpointing=False)
+        model = LlamaForCausalLM(cfg).cuda().bfloat16()
+        engine, _, _, _ = deepspeed.initialize(model=model, config={
+            "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "optimizer": {"type": "AdamW", "params": {"lr": 2e-3}},
+            "zero_optimization": dict({"stage": 3, "sub_group_size": 200000}, **zero_extra), "aio": {"block_size": 262144, "queue_depth": 4}})
+        g = torch.Generator(device="cuda").manual_seed(1)
+        ids = torch.randint(0, 1024, (2, 128), device="cuda", generator=g)
+        losses = []
+        for _ in range(5):
+            loss = engine(ids, ids)
+            engine.backward(loss)
+            engine.step()
+            losses.append(loss.item())
+        return losses, engine
+
+    base, _ = run({"offload_optimizer": {"device": "cpu", "pin_memory": True}})
+    if tier == "cpu":
+        extra = {"offload_optimizer": {"device": "cpu", "pin_memory": True}, "offload_param": {"device": "cpu", "pin_memory": True}}
+    elif tier == "nvme":
+        extra = {"offload_optimizer": {"device": "cpu", "pin_memory": True}, "offload_param": {"device": "nvme", "nvme_path": str(tmp_path)}}
+    else:
+        extra = {"offload_optimizer": {"device": "nvme", "nvme_path": str(tmp_path), "pin_memory": True}}
+    got, engine = run(extra)
+    assert all(abs(a - b) <= 2e-3 * max(1.0, abs(a)) for a, b in zip(base, got)), (base, got)
+    assert got[-1] < got[0] - 0.3
+    opt = engine.optimizer
+    if tier != "nvme_optimizer":
+        assert opt.offload_param and opt.lp_shard.device.type == "cpu" and all(u.full is None for u in opt.units if not u.persistent)
+    else:
+        assert getattr(opt.regions[0], "is_nvme", False) and len(opt.regions[0].bounds) > 1
