@@ -381,12 +381,15 @@ def in_dlts():
     return "DLTS_JOB_ID" in os.environ
 
 
+cdb = None  # backend object (comm/torch.py TorchBackend), set by init_distributed
+
+
 def init_distributed(dist_backend=None, auto_mpi_discovery=True, distributed_port=TORCH_DISTRIBUTED_DEFAULT_PORT,
                      verbose=True, timeout=DEFAULT_PG_TIMEOUT, init_method=None, dist_init_required=None, config=None,
                      rank=-1, world_size=-1):
     """Initialise torch.distributed (NCCL on GPUs, gloo on hosts).  One process per GPU; the device is
     bound to LOCAL_RANK before the process group is created so NCCL picks the right NVLink peer."""
-    global _initialized_here
+    global _initialized_here, cdb
     configure(deepspeed_config=config)
     if dist_init_required is False:
         return
@@ -423,3 +426,5 @@ def init_distributed(dist_backend=None, auto_mpi_discovery=True, distributed_por
             pass
     tdist.init_process_group(backend=dist_backend, timeout=timeout, init_method=init_method, **kwargs)
     _initialized_here = True
+    from .torch import TorchBackend
+    cdb = TorchBackend(dist_backend)

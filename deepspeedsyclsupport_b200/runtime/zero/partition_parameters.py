@@ -105,6 +105,22 @@ class Init:
             if not is_zero_param(p):
                 _shard_one(p, self.group, self.world, self.rank, self.device, self.dtype)
 
+    # -- group introspection (reference: partition_parameters.py:1981-1995)
+    def get_partition_dp_group(self, param):
+        return getattr(param, "ds_process_group", self.group)
+
+    def get_partition_rank(self):
+        """Relative rank inside the parameter-partition group (MiCS overloads the group)."""
+        return self.rank
+
+    @property
+    def num_partitions(self):
+        return self.world
+
+    def get_dp_process_group(self):
+        """The communication group with all data-parallel ranks."""
+        return self.group
+
     # -- nn.Module patching
     def __enter__(self):
         global _zero_init_context, _orig_module_apply
