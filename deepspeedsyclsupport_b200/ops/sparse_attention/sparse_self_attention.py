@@ -11,13 +11,13 @@ from .sparsity_config import SparsityConfig
 
 
 class SparseSelfAttention(nn.Module):
-    ops = dict()
 
     def __init__(self, sparsity_config=SparsityConfig(num_heads=4), key_padding_mask_mode="add", attn_mask_mode="mul", max_seq_length=2048):
         super().__init__()
         self.sparsity_config = sparsity_config
         self.register_buffer("master_layout", self.sparsity_config.make_layout(max_seq_length))
         self._need_layout_synchronization = True
+        self.ops = {}  # sequence length -> (sdd, dsd, softmax) built for THIS module's layout
         self.key_padding_mask_mode = key_padding_mask_mode
         self.attn_mask_mode = attn_mask_mode
 
@@ -32,13 +32,13 @@ class SparseSelfAttention(nn.Module):
         return self.master_layout[..., :nb, :nb].cpu()
 
     def get_ops(self, H, L):
-        key = (id(self), L)
-        if key not in SparseSelfAttention.ops:
+        key = L
+        if key not in self.ops:
             layout = self.get_layout(L)
             blk = self.sparsity_config.block
-            SparseSelfAttention.ops[key] = (MatMul(layout, blk, "sdd", trans_a=False, trans_b=True), MatMul(layout, blk, "dsd", trans_a=False, trans_b=False),
+            self.ops[key] = (MatMul(layout, blk, "sdd", trans_a=False, trans_b=True), MatMul(layout, blk, "dsd", trans_a=False, trans_b=False),
                                             Softmax(layout, blk))
-        return SparseSelfAttention.ops[key]
+        return self.ops[key]
 
     def transpose_key_for_scores(self, x, L):
         return x.permute(0, 1, 3, 2) if x.size(2) != L else x
