@@ -55,6 +55,53 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
     return out
 
 
+FP8_MAX = 448.0  # largest finite e4m3 value
+
+
+def quantize_fp8_rowwise(x):
+    """-> (e4m3 tensor of x's shape, fp32 scale per row): x ~= q * scale[:, None]."""
+    xf = x.float()
+    amax = xf.abs().amax(dim=-1).clamp_min(1e-12)
+    scale = amax / FP8_MAX
+    q = (xf / scale[:, None]).clamp(-FP8_MAX, FP8_MAX).to(torch.float8_e4m3fn)
+    return q, scale
+
+
+def gemm_fp8(a_q, b_q, a_scale=None, b_scale=None, out=None, max_ctas=0):
+    """C[M,N] (bf16) = diag(a_scale) (A B^T) diag(b_scale) on the fp8 tensor-core path (csrc/gemm/gemm_fp8.cu).
+
+    a_q: [M,K] float8_e4m3fn (per-token quantised activations), b_q: [N,K] float8_e4m3fn (per-output-feature quantised
+    weights), scales fp32 [M] / [N] (None = 1).  K must be a multiple of 16."""
+    assert a_q.dtype == torch.float8_e4m3fn and b_q.dtype == torch.float8_e4m3fn
+    M, K = a_q.shape
+    N = b_q.shape[0]
+    assert b_q.shape[1] == K and a_q.stride(1) == 1 and b_q.stride(1) == 1
+    if not a_q.is_cuda:
+        r = a_q.float() @ b_q.float().t()
+        if a_scale is not None:
+            r = r * a_scale[:, None]
+        if b_scale is not None:
+            r = r * b_scale[None, :]
+        return r.to(torch.bfloat16)
+    if out is None:
+        ld = (N + 7) // 8 * 8
+        out = torch.empty(M, ld, dtype=torch.bfloat16, device=a_q.device)[:, :N]
+    rc = native.lib().dsb200_gemm_fp8(native.ptr(a_q), native.ptr(b_q), native.ptr(out), native.ptr(a_scale), native.ptr(b_scale), M, N, K,
+                                      a_q.stride(0), b_q.stride(0), out.stride(0), int(max_ctas), native.stream_ptr())
+    native.check(rc)
+    if _prof._ACTIVE:
+        _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_fp8")
+    return out
+
+
+def linear_fp8(x, w_q, w_scale, bias=None):
+    """W8A8 linear for inference: activations quantised per token on the fly, weights pre-quantised per output feature."""
+    x2 = x.reshape(-1, x.shape[-1])
+    xq, xs = quantize_fp8_rowwise(x2)
+    y = gemm_fp8(xq, w_q, xs, w_scale).view(*x.shape[:-1], w_q.shape[0])
+    return y if bias is None else y + bias
+
+
 def moe_gemm_ref(x, w, cumsum):
     """fp32 reference: per-expert loop over the row ranges in `cumsum` (host synchronisation)."""
     E, N, K = w.shape

@@ -41,6 +41,7 @@ _T = {"p": ctypes.c_void_p, "i": ctypes.c_int, "l": ctypes.c_longlong, "f": ctyp
 _SIGS = {
     "dsb200_gemm_bf16": "pppiiiiiiiiiip",
     "dsb200_moe_gemm_bf16": "pppp iiii iii p",
+    "dsb200_gemm_fp8": "ppppp iii iii i p",
     "dsb200_flash_fwd_trace": "p",
     "dsb200_fused_adam_flat": "ppppipil fffff iii ppp",
     "dsb200_fused_lion_flat": "pp pipil ffff ppp",

@@ -148,6 +148,12 @@ int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int
                         void* const* peer_shards, long long w_off, long long shard_numel, int* flags, int world,
                         dsb200_stream_t stream);
 
+/* ---- csrc/gemm/gemm_fp8.cu */
+/* C[M,N] (bf16) = diag(sa) * (A * B^T) * diag(sb) with A [M][K], B [N][K] in e4m3 (one byte per element, K contiguous).
+ * sa [M] / sb [N] fp32 scales, either may be null (= 1).  lda / ldb in elements (= bytes), multiples of 16; ldc multiple of 8. */
+int dsb200_gemm_fp8(const void* A, const void* B, void* C, const float* sa, const float* sb, int M, int N, int K, int lda,
+                    int ldb, int ldc, int max_ctas, dsb200_stream_t stream);
+
 /* ---- csrc/gemm/gemm_grouped.cu */
 /* C[r, :] = A[r, :] * W[expert(r)]^T for rows sorted by expert; `cum` (device, int64[E]) holds inclusive cumulative row counts.
  * Rows at or beyond cum[E-1] are left untouched.  N must be a multiple of 8; A, W, C 16-byte aligned with 16-byte row strides. */

@@ -734,3 +734,23 @@ def test_quantized_linear_on_device_matches_host_format():
         assert q.qweight.numel() == 256 * 384 * bits // 8
         out = q(x).float()
         assert (out - ref).abs().max() < tol * ref.abs().max()
+
+
+@pytest.mark.parametrize("shape", [(256, 512, 256), (1000, 1096, 336), (4096, 4096, 4096), (77, 264, 128)])
+def test_gemm_fp8_rowwise_scaled(shape):
+    """fp8 (e4m3) tcgen05 GEMM with per-row / per-column scales against the fp32 product of the SAME quantised operands (exact up
+    to accumulation order and the bf16 output rounding), and against the unquantised product within fp8 tolerance."""
+    from deepspeedsyclsupport_b200.ops.gemm import gemm_fp8, quantize_fp8_rowwise
+    M, N, K = shape
+    torch.manual_seed(0)
+    a = torch.randn(M, K, device=_dev()) * torch.rand(M, 1, device=_dev()) * 3
+    b = torch.randn(N, K, device=_dev()) * 0.05
+    aq, sa = quantize_fp8_rowwise(a)
+    bq, sb = quantize_fp8_rowwise(b)
+    c = gemm_fp8(aq, bq, sa, sb).float()
+    ref_q = (aq.float() @ bq.float().t()) * sa[:, None] * sb[None, :]
+    assert (c - ref_q).abs().max() <= 1e-2 * ref_q.abs().max()
+    ref = a @ b.t()
+    assert (c - ref).abs().max() <= 0.08 * ref.abs().max()
+    c1 = gemm_fp8(aq, bq).float()  # no scales
+    assert (c1 - aq.float() @ bq.float().t()).abs().max() <= 1e-2 * (aq.float() @ bq.float().t()).abs().max()
