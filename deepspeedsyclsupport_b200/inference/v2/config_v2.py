@@ -10,7 +10,7 @@ class DeepSpeedTPConfig(DeepSpeedConfigModel):
 
 
 class QuantizationConfig(DeepSpeedConfigModel):
-    quantization_mode: str = ""  # "" (bf16) | "fp8_block" (block-scaled e4m3 weights)
+    quantization_mode: str = ""  # "" (16-bit weights) | "wf8af8" (e4m3 weights per output feature x e4m3 activations per token)
 
 
 class RaggedInferenceEngineConfig(DeepSpeedConfigModel):

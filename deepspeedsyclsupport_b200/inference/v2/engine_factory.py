@@ -170,7 +170,8 @@ def build_engine_from_state_dict(model_type, hf_config: dict, state_dict: dict, 
     canon = _MAPPERS[model_type](state_dict, hf_config)
 
     def builder(tp_group, device):
-        return RaggedTransformer(spec, canon, tp_group=tp_group, dtype=dtype, device=device)
+        return RaggedTransformer(spec, canon, tp_group=tp_group, dtype=dtype, device=device,
+                                 quantization_mode=engine_config.quantization.quantization_mode)
 
     return InferenceEngineV2(builder, engine_config)
 

@@ -140,8 +140,9 @@ def _shard_cols(w, rank, world):
 class RaggedTransformer:
     """Holds the TP shard of the weights and runs ragged batches against a DSStateManager."""
 
-    def __init__(self, spec: ArchSpec, state_dict, tp_group=None, dtype=torch.bfloat16, device=None, symm=None):
+    def __init__(self, spec: ArchSpec, state_dict, tp_group=None, dtype=torch.bfloat16, device=None, symm=None, quantization_mode=""):
         self.spec = spec
+        self.quantization_mode = quantization_mode or ""
         self.tp_group = tp_group
         self.tp = dist.get_world_size(tp_group) if (tp_group is not None and dist.is_initialized()) else 1
         self.rank = dist.get_rank(tp_group) if self.tp > 1 else 0
@@ -226,10 +227,21 @@ class RaggedTransformer:
                 L["mlp2_w"] = self._t(_shard_cols(sd[p + "down.weight"], r, W))
                 if p + "down.bias" in sd:
                     L["mlp2_b"] = self._t(sd[p + "down.bias"])
+            if self.quantization_mode == "wf8af8":
+                # W8A8: dense projection weights stored as e4m3 with one scale per output feature; activations are quantised per
+                # token inside _linear and the product runs on the fp8 tensor-core GEMM (csrc/gemm/gemm_fp8.cu)
+                from ....ops.gemm import quantize_fp8_rowwise
+                for key in ("qkv_w", "o_w", "mlp1_w", "mlp2_w"):
+                    if key in L and L[key].shape[1] % 16 == 0:
+                        L[key] = quantize_fp8_rowwise(L[key])
             self.layers.append(L)
 
     # ---- building blocks
     def _linear(self, x, w, b=None):
+        if isinstance(w, tuple):  # (e4m3 weight, per-row scale)
+            from ....ops.gemm import linear_fp8
+            y = linear_fp8(x, w[0], w[1])
+            return y if b is None else y + b
         y = gemm(x, w) if x.is_cuda else torch.nn.functional.linear(x, w)
         if b is not None:
             y = y + b

@@ -99,6 +99,8 @@ def linear_fp8(x, w_q, w_scale, bias=None):
     x2 = x.reshape(-1, x.shape[-1])
     xq, xs = quantize_fp8_rowwise(x2)
     y = gemm_fp8(xq, w_q, xs, w_scale).view(*x.shape[:-1], w_q.shape[0])
+    if y.dtype != x.dtype:
+        y = y.to(x.dtype)
     return y if bias is None else y + bias
 
 

@@ -199,3 +199,20 @@ def test_ragged_surface_accessors_and_kv_offload():
     n = seq.cur_allocated_blocks
     seq.free_kv_cache(ids[:1])
     assert seq.cur_allocated_blocks == n - 1 and seq.kv_cache_ids().tolist() == ids[1:]
+
+
+def test_ragged_engine_w8a8_mode_tracks_dense():
+    """quantization_mode = wf8af8: projections run as fp8 x fp8 with row scales (host restatement here, tcgen05 kernel on the
+    device); logits stay within fp8 tolerance of the dense fp32 model and greedy tokens mostly agree."""
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 64, "max_ragged_sequence_count": 8, "max_context": 128,
+                                                      "memory_config": {"mode": "allocate", "size": 40}},
+                                       quantization={"quantization_mode": "wf8af8"})
+    sd = _hf_llama_state(CFG)
+    eng = build_engine_from_state_dict("llama", CFG, sd, ecfg, dtype=torch.float32)
+    assert isinstance(eng._model.layers[0]["qkv_w"], tuple) and eng._model.layers[0]["qkv_w"][0].dtype == torch.float8_e4m3fn
+    torch.manual_seed(1)
+    a = torch.randint(0, 97, (21, ))
+    ref = _dense_llama_logits(sd, CFG, a)
+    out = eng.put([1], [a])
+    assert (out[0].float() - ref[20]).abs().max() < 0.2 * ref[20].abs().max()

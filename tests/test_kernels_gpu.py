@@ -754,3 +754,30 @@ def test_gemm_fp8_rowwise_scaled(shape):
     assert (c - ref).abs().max() <= 0.08 * ref.abs().max()
     c1 = gemm_fp8(aq, bq).float()  # no scales
     assert (c1 - aq.float() @ bq.float().t()).abs().max() <= 1e-2 * (aq.float() @ bq.float().t()).abs().max()
+
+
+def test_ragged_engine_w8a8_gpu():
+    """FastGen with quantization_mode = wf8af8 on the device: fp8 tensor-core projections, logits close to the bf16 engine."""
+    from test_inference_v2 import _hf_llama_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    cfg = dict(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+               rms_norm_eps=1e-5)
+    sd = _hf_llama_state(cfg)
+    mk = lambda mode: RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 256, "max_ragged_sequence_count": 8, "max_context": 256,
+                                                                 "memory_config": {"mode": "allocate", "size": 40}},
+                                                  quantization={"quantization_mode": mode})
+    torch.manual_seed(2)
+    a = torch.randint(0, 512, (130, ))
+    ref = build_engine_from_state_dict("llama", cfg, sd, mk(""), dtype=torch.bfloat16).put([1], [a])[0].float()
+    eng = build_engine_from_state_dict("llama", cfg, sd, mk("wf8af8"), dtype=torch.bfloat16)
+    assert eng._model.layers[0]["mlp1_w"][0].dtype == torch.float8_e4m3fn
+    out = eng.put([1], [a])[0].float()
+    # the same quantised model evaluated on the host in fp32 (restated fp8 product): isolates the kernels from fp8 noise
+    import deepspeedsyclsupport_b200.inference.v2.model_implementations.ragged_transformer as RT
+    from deepspeedsyclsupport_b200.inference.v2.engine_factory import SPEC_FROM_HF, _MAPPERS
+    host = RT.RaggedTransformer(SPEC_FROM_HF["llama"](cfg), _MAPPERS["llama"](sd, cfg), dtype=torch.float32, device=torch.device("cpu"),
+                                quantization_mode="wf8af8")
+    w_dev, w_host = eng._model.layers[1]["mlp2_w"], host.layers[1]["mlp2_w"]
+    assert (w_dev[0].float().cpu() - w_host[0].float()).abs().max() <= 0.13 * w_host[0].float().abs().max()  # bf16 vs fp32 source weights
+    assert (out - ref).abs().max() < 0.35 * ref.abs().max()  # fp8 noise of four projections per layer on random weights
+    assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
