@@ -85,6 +85,24 @@ __global__ void allgather_pull_kernel(Peers peers, size_t src_off, uint8_t* __re
   }
 }
 
+// ---------------------------------------------------------------- all-to-all (pull), equal splits:
+// every rank holds world chunks of `bytes_per_chunk` at `src_off` (chunk j = what it sends to rank j); rank r gathers
+// out[p] = peer p's chunk r.  Used for MoE dispatch / combine and the Ulysses head <-> sequence exchanges
+// (reference: all_to_all_single call sites in moe/sharded_moe.py:95-111 and sequence/layer.py:15-41, NCCL there).
+__global__ void alltoall_pull_kernel(Peers peers, size_t src_off, uint8_t* __restrict__ dst, size_t bytes_per_chunk, int rank,
+                                     int world) {
+  const size_t vecs = bytes_per_chunk / 16;
+  const size_t total = vecs * world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int pi = static_cast<int>(i / vecs);
+    const int peer = (pi + rank) % world;  // stagger the peers so every NVSwitch port is busy
+    const size_t v = i - static_cast<size_t>(pi) * vecs;
+    const uint4 val = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + static_cast<size_t>(rank) * bytes_per_chunk + v * 16);
+    *reinterpret_cast<uint4*>(dst + static_cast<size_t>(peer) * bytes_per_chunk + v * 16) = val;
+  }
+}
+
 // ---------------------------------------------------------------- reduce-scatter (pull) fused with scale / cast / norm
 // Every rank holds a full gradient buffer (bf16 or fp32) of world*n elements at `src_off` of its symmetric buffer.
 // Rank r sums slice r over all peers in fp32, multiplies by `scale`, and either stores or accumulates into `dst`
@@ -307,6 +325,20 @@ DSB_EXPORT int dsb200_p2p_allgather(void* const* peer_ptrs, long long src_off, v
   const size_t vecs = static_cast<size_t>(bytes_per_rank) / 16 * world;
   allgather_pull_kernel<<<comm_grid(vecs, max_ctas), 256, 0, stream>>>(P, static_cast<size_t>(src_off), static_cast<uint8_t*>(dst),
                                                                          static_cast<size_t>(bytes_per_rank), rank, world);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// dst[p * bytes_per_chunk ...] = chunk `rank` of peer p's buffer at src_off (equal-split all_to_all_single); dst is local memory.
+DSB_EXPORT int dsb200_p2p_alltoall(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_chunk, int rank, int world,
+                                   int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(bytes_per_chunk % 16 == 0 && src_off % 16 == 0, "p2p_alltoall: sizes/offsets must be multiples of 16 bytes");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  const size_t vecs = static_cast<size_t>(bytes_per_chunk) / 16 * world;
+  alltoall_pull_kernel<<<comm_grid(vecs, max_ctas), 256, 0, stream>>>(P, static_cast<size_t>(src_off), static_cast<uint8_t*>(dst),
+                                                                        static_cast<size_t>(bytes_per_chunk), rank, world);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

@@ -280,6 +280,18 @@ def all_gather_coalesced(output_tensors, input_tensors, group=None, async_op=Fal
 
 @timed_op
 def all_to_all_single(output, tensor, output_split_sizes=None, input_split_sizes=None, group=None, async_op=False):
+    if (not async_op and not output_split_sizes and not input_split_sizes and tensor.is_cuda and _single_node_job()
+            and os.environ.get("DSB200_PEER_A2A", "1") != "0"):
+        # equal splits inside one NVSwitch domain: own pull kernel over peer memory instead of NCCL (MoE dispatch / combine,
+        # Ulysses head <-> sequence exchanges)
+        from ..parallel.symm import PeerAllToAll
+        if PeerAllToAll.usable(tensor, group) and output.is_contiguous() and output.numel() * output.element_size() == tensor.numel() * tensor.element_size():
+            try:
+                PeerAllToAll.for_group(group, tensor.numel() * tensor.element_size())(output, tensor)
+                return None
+            except Exception as e:  # peer access not available: NCCL below
+                logger.warning(f"peer-memory all-to-all unavailable ({e}); using NCCL")
+                os.environ["DSB200_PEER_A2A"] = "0"
     if tdist.get_backend(group) == "gloo":
         # gloo has no all-to-all: all-gather every rank's send buffer and keep the chunk addressed to this rank
         # (host plumbing path only -- equal splits)
@@ -379,6 +391,14 @@ def in_aws_sm():
 
 def in_dlts():
     return "DLTS_JOB_ID" in os.environ
+
+
+def _single_node_job():
+    """Every rank of the job runs on this host (peer-memory paths need CUDA IPC between all ranks of a group)."""
+    try:
+        return tdist.is_initialized() and int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("LOCAL_SIZE", "0"))) == tdist.get_world_size()
+    except Exception:
+        return False
 
 
 cdb = None  # backend object (comm/torch.py TorchBackend), set by init_distributed

@@ -23,6 +23,7 @@ native.register_sigs({
     "dsb200_symm_free": "p",
     "dsb200_symm_barrier": "p l ii i p",
     "dsb200_p2p_allgather": "p l p l iii p",
+    "dsb200_p2p_alltoall": "p l p l iii p",
     "dsb200_p2p_reduce_scatter": "p l i p i l ii f i p i p",
     "dsb200_p2p_rs_adam": "p l pppp l ii f fffff iii i p",
     "dsb200_p2p_allreduce_bf16": "p l p l iii p",
@@ -68,6 +69,15 @@ class _PeerOps:
         r = self.rank if rank is None else rank
         rc = native.lib().dsb200_p2p_allgather(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(out),
                                                bytes_per_rank, r, self.world, max_ctas, native.stream_ptr())
+        native.check(rc)
+        return out
+
+    def all_to_all(self, out, src_offset, bytes_per_chunk, rank=None, max_ctas=0):
+        """Equal-split all_to_all_single: out[p] = chunk `rank` of peer p's buffer (the caller has written its `world` send
+        chunks at `src_offset` and every rank has passed a barrier since)."""
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_alltoall(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(out),
+                                              bytes_per_chunk, r, self.world, max_ctas, native.stream_ptr())
         native.check(rc)
         return out
 
@@ -175,3 +185,45 @@ class EmulatedPeers(_PeerOps):
         self._keep = []
         self._bufs = [torch.zeros(self.nbytes + FLAG_PAD, dtype=torch.uint8, device=self.device) for _ in range(world)]
         self.ptrs = [b.data_ptr() for b in self._bufs]
+
+
+class PeerAllToAll(object):
+    """Equal-split all_to_all_single over NVLink peer memory for one process group: the send tensor is copied into a symmetric
+    staging buffer, a device barrier publishes it, every rank pulls its chunks from the peers (csrc/comm/symm.cu
+    alltoall_pull_kernel), a second barrier frees the staging buffer.  No NCCL call, no host synchronisation.  The staging
+    buffer grows on demand (collective: every rank of the group sees the same sizes)."""
+    _instances = {}
+
+    def __init__(self, group, nbytes):
+        self.group = group
+        self.buf = SymmetricBuffer(group, nbytes)
+
+    @classmethod
+    def for_group(cls, group, nbytes):
+        key = id(group) if group is not None else 0
+        inst = cls._instances.get(key)
+        if inst is None or inst.buf.nbytes < nbytes:
+            if inst is not None:
+                inst.buf.close()
+            inst = cls(group, max(int(nbytes), 1 << 22))
+            cls._instances[key] = inst
+        return inst
+
+    @staticmethod
+    def usable(tensor, group):
+        import os
+        if not (tensor.is_cuda and tensor.is_contiguous() and os.environ.get("DSB200_DISABLE_P2P", "0") != "1"):
+            return False
+        world = dist.get_world_size(group)
+        nbytes = tensor.numel() * tensor.element_size()
+        return 1 < world <= 16 and nbytes % (16 * world) == 0 and world <= torch.cuda.device_count()
+
+    def __call__(self, output, input):
+        world = self.buf.world
+        nbytes = input.numel() * input.element_size()
+        stage = self.buf.view(0, (nbytes, ), torch.uint8)
+        stage.copy_(input.reshape(-1).view(torch.uint8))
+        self.buf.barrier()   # every rank's send chunks are in place
+        self.buf.all_to_all(output, 0, nbytes // world)
+        self.buf.barrier()   # everyone has pulled: the staging buffer may be overwritten by the next call
+        return output

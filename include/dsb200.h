@@ -124,6 +124,9 @@ int dsb200_symm_barrier(void* const* peer_ptrs, long long flag_off, int rank, in
                         dsb200_stream_t stream);
 int dsb200_p2p_allgather(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
                          int world, int max_ctas, dsb200_stream_t stream);
+/* dst[p * bytes_per_chunk ...] = chunk `rank` of peer p's buffer at src_off (equal-split all_to_all_single); dst is local memory. */
+int dsb200_p2p_alltoall(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_chunk, int rank,
+                        int world, int max_ctas, dsb200_stream_t stream);
 /* src dtype / dst dtype: 0 bf16, 2 fp32.  n = elements per rank (multiple of 8).  sumsq: optional device float (+= sum g^2). */
 int dsb200_p2p_reduce_scatter(void* const* peer_ptrs, long long src_off, int src_dtype, void* dst, int dst_dtype,
                               long long n, int rank, int world, float scale, int accumulate, float* sumsq, int max_ctas,

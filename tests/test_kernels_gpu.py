@@ -248,6 +248,14 @@ def test_p2p_collectives_emulated_ranks():
         out = torch.empty(W * n, device=_dev(), dtype=torch.bfloat16)
         em.all_gather(out, 0, n * 2, rank=r)
         assert torch.equal(out, torch.cat(shards))
+    # all-to-all: rank r's send buffer holds W chunks; rank q must receive chunk q of every rank
+    sends = [torch.randn(W * n, device=_dev()).bfloat16() for _ in range(W)]
+    for r in range(W):
+        em.view(0, (W * n, ), torch.bfloat16, rank=r).copy_(sends[r])
+    for q in range(W):
+        out = torch.empty(W * n, device=_dev(), dtype=torch.bfloat16)
+        em.all_to_all(out, 0, n * 2, rank=q)
+        assert torch.equal(out, torch.cat([sends[r][q * n:(q + 1) * n] for r in range(W)]))
     # reduce-scatter (+scale, +norm): every rank holds W*n bf16 gradients
     grads = [torch.randn(W * n, device=_dev()).bfloat16() for _ in range(W)]
     for r in range(W):

@@ -86,3 +86,57 @@ def _zero3_body():
 
 def test_zero3_two_gpus_trains():
     run_distributed(_zero3_body, world_size=2, backend="nccl")
+
+
+def _peer_a2a_body():
+    """comm.all_to_all_single on device tensors takes the peer-memory pull kernel inside one node and must equal NCCL; the
+    Ulysses exchange built on it must round-trip; timing of both paths is printed (device events, max over ranks)."""
+    import os
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.parallel.symm import PeerAllToAll
+    from deepspeedsyclsupport_b200.sequence.layer import single_all_to_all
+    rank, world = dist.get_rank(), dist.get_world_size()
+    torch.manual_seed(rank)
+    for n in (world * 1024, world * (1 << 20)):
+        x = torch.randn(n, device="cuda").bfloat16()
+        want = torch.empty_like(x)
+        os.environ["DSB200_PEER_A2A"] = "0"
+        dist.all_to_all_single(want, x)
+        os.environ["DSB200_PEER_A2A"] = "1"
+        got = torch.empty_like(x)
+        dist.all_to_all_single(got, x)
+        assert torch.equal(got, want)
+    assert PeerAllToAll._instances, "the peer path was not taken"
+    q = torch.randn(64, 2, 4 * world, 32, device="cuda").bfloat16()  # [s/P, b, h, d]
+    full = single_all_to_all(q, 2, 0, None)
+    assert full.shape == (64 * world, 2, 4, 32)
+    back = single_all_to_all(full, 0, 2, None)
+    assert torch.equal(back, q)
+
+    def timed(flag):
+        os.environ["DSB200_PEER_A2A"] = flag
+        x = torch.randn(world * (4 << 20), device="cuda").bfloat16()
+        y = torch.empty_like(x)
+        for _ in range(3):
+            dist.all_to_all_single(y, x)
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(10):
+            dist.all_to_all_single(y, x)
+        e.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([s.elapsed_time(e) / 10], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    t_nccl, t_peer = timed("0"), timed("1")
+    if rank == 0:
+        mb = world * (4 << 20) * 2 / 2**20
+        print(f"ALLTOALL {mb:.0f} MiB per rank, world {world}: nccl {t_nccl:.3f} ms, peer {t_peer:.3f} ms, speedup {t_nccl / t_peer:.2f}x", flush=True)
+    os.environ["DSB200_PEER_A2A"] = "1"
+
+
+def test_peer_memory_all_to_all_matches_nccl():
+    run_distributed(_peer_a2a_body, world_size=2, backend="nccl")
