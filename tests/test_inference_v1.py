@@ -198,3 +198,85 @@ def test_inference_engine_loads_checkpoint_into_meta_model(tmp_path):
     x = torch.randn(3, 8)
     assert torch.allclose(dst(x), src(x)) and not any(p.is_meta for p in dst.parameters())
     eng.destroy()
+
+
+def _fill(mod, gen):
+    with torch.no_grad():
+        for n, p in mod.named_parameters():
+            if n.endswith(("norm_w", "attn_nw")):
+                p.copy_(1 + 0.1 * torch.randn(p.shape, generator=gen))
+            else:
+                p.copy_(0.08 * torch.randn(p.shape, generator=gen))
+
+
+def _ref_block(m, x, past_kv, variant):
+    """plain fp32 restatement of the block for the three layouts exercised below"""
+    import torch.nn.functional as F
+    from deepspeedsyclsupport_b200.ops.transformer.inference.ds_attention import apply_rotary
+    cfg, A, M = m.config, m.attention, m.mlp
+    B, S, H = x.shape
+    ln = lambda t, w, b: F.layer_norm(t, (H, ), w, b, cfg.epsilon)
+    rms = lambda t, w: t * torch.rsqrt(t.pow(2).mean(-1, keepdim=True) + cfg.epsilon) * w
+    n1 = (lambda t: rms(t, m.norm_w)) if variant == "llama" else (lambda t: ln(t, m.norm_w, m.norm_b))
+    n2 = (lambda t: rms(t, M.attn_nw)) if variant == "llama" else (lambda t: ln(t, M.attn_nw, M.attn_nb))
+    hn = n1(x) if cfg.pre_layer_norm else x
+    qkv = F.linear(hn, A.attn_qkvw, A.attn_qkvb).view(B, S, A.heads + 2 * A.kv_heads, A.head_dim)
+    q, k, v = qkv.split([A.heads, A.kv_heads, A.kv_heads], 2)
+    past = 0 if past_kv is None else past_kv[0].shape[2]
+    if cfg.rotary_dim > 0:
+        pos = torch.arange(past, past + S)
+        q, k = apply_rotary(q, pos, cfg.rotary_dim, cfg.rope_theta, cfg.rotate_half), apply_rotary(k, pos, cfg.rotary_dim, cfg.rope_theta, cfg.rotate_half)
+    k, v = k.transpose(1, 2), v.transpose(1, 2)
+    if past_kv is not None:
+        k, v = torch.cat([past_kv[0], k], 2), torch.cat([past_kv[1], v], 2)
+    rep = A.heads // A.kv_heads
+    s = (q.transpose(1, 2) @ k.repeat_interleave(rep, 1).transpose(-1, -2)) / (A.head_dim**0.5)
+    if cfg.triangular_masking:
+        T = k.shape[2]
+        s = s.masked_fill(torch.arange(T)[None, :] > torch.arange(past, past + S)[:, None], float("-inf"))
+    ctx = (torch.softmax(s, -1) @ v.repeat_interleave(rep, 1)).transpose(1, 2).reshape(B, S, -1)
+    attn = F.linear(ctx, A.attn_ow, A.attn_ob)
+
+    def mlp(t):
+        u = F.linear(t, M.inter_w, M.inter_b)
+        if M.gated:
+            g, up = u.chunk(2, -1)
+            u = F.silu(g) * up
+        else:
+            u = F.gelu(u, approximate="tanh")
+        return F.linear(u, M.output_w, M.output_b)
+
+    if variant == "gptj":
+        return x + attn + mlp(hn), (k, v)
+    if variant == "bert":
+        h = n2(x + attn)
+        return n1(h + mlp(h)), (k, v)
+    x1 = x + attn
+    return x1 + mlp(n2(x1)), (k, v)
+
+
+@pytest.mark.parametrize("variant", ["llama", "gptj", "bert"])
+def test_ds_transformer_inference_block_matches_reference_math(variant):
+    """DeepSpeedTransformerInference (reference module / parameter names) on three layouts: pre-LN RMS + gated SiLU + rotary + GQA
+    with a prompt followed by two cached decode steps; GPT-J parallel block with interleaved rotary; BERT post-LN bidirectional."""
+    from deepspeedsyclsupport_b200.model_implementations import DeepSpeedTransformerInference
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    from deepspeedsyclsupport_b200.utils.types import ActivationFuncType, NormType
+    common = dict(hidden_size=64, heads=4, intermediate_size=128, num_hidden_layers=1, dtype=torch.float32, layer_norm_eps=1e-5, return_tuple=False)
+    cfg = {"llama": DeepSpeedInferenceConfig(norm_type=NormType.RMSNorm, mlp_act_func_type=ActivationFuncType.GATED_SILU, rotary_dim=16, rotate_half=True,
+                                             rotate_every_two=False, num_kv=2, **common),
+           "gptj": DeepSpeedInferenceConfig(mlp_after_attn=False, rotary_dim=8, rotate_half=False, rotate_every_two=True, **common),
+           "bert": DeepSpeedInferenceConfig(pre_layer_norm=False, triangular_masking=False, **common)}[variant]
+    m = DeepSpeedTransformerInference(cfg)
+    _fill(m, torch.Generator().manual_seed(0))
+    torch.manual_seed(1)
+    x = torch.randn(2, 7, 64)
+    want, kv = _ref_block(m, x, None, variant)
+    got = m(x)
+    assert torch.allclose(got, want, atol=2e-4), (got - want).abs().max()
+    if variant != "bert":
+        for _ in range(2):  # decode with the module's own KV cache
+            x1 = torch.randn(2, 1, 64)
+            want, kv = _ref_block(m, x1, kv, variant)
+            got, present = m(x1, use_cache=True)
+            assert torch.allclose(got, want, atol=2e-4) and present[0].shape[2] == kv[0].shape[2]
