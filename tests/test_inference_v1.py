@@ -280,3 +280,42 @@ def test_ds_transformer_inference_block_matches_reference_math(variant):
             want, kv = _ref_block(m, x1, kv, variant)
             got, present = m(x1, use_cache=True)
             assert torch.allclose(got, want, atol=2e-4) and present[0].shape[2] == kv[0].shape[2]
+
+
+@pytest.mark.parametrize("mlp_type", ["standard", "residual"])
+def test_ds_moe_inference_block_matches_dense_mixture(mlp_type):
+    """DeepSpeedMoEInference: top-2 routing through scatter -> grouped expert GEMM -> gather equals the dense evaluation of the
+    mixture (and PR-MoE's residual branch when mlp_type = residual)."""
+    import torch.nn.functional as F
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedMoEInference, DeepSpeedMoEInferenceConfig
+    from deepspeedsyclsupport_b200.utils.types import ActivationFuncType
+    cfg = DeepSpeedMoEInferenceConfig(moe_experts=4, k=2, mlp_type=mlp_type, hidden_size=64, heads=4, intermediate_size=96, num_hidden_layers=1,
+                                      dtype=torch.float32, layer_norm_eps=1e-5, return_tuple=False, mlp_act_func_type=ActivationFuncType.GELU)
+    m = DeepSpeedMoEInference(cfg)
+    _fill(m, torch.Generator().manual_seed(0))
+    with torch.no_grad():
+        m.gate_w.mul_(20)
+    torch.manual_seed(2)
+    x = torch.randn(2, 9, 64)
+    got = m(x)
+    # reference
+    ln = lambda t, w, b: F.layer_norm(t, (64, ), w, b, 1e-5)
+    hn = ln(x, m.norm_w, m.norm_b)
+    m.attention.reset_cache()
+    attn, _, _ = m.attention(hn)
+    m.attention.reset_cache()
+    x1 = x + attn
+    h2 = ln(x1, m.attn_nw, m.attn_nb)
+    probs = torch.softmax(h2 @ m.gate_w.t(), -1)
+    top, idx = probs.topk(2, -1)
+    top = top / top.sum(-1, keepdim=True)
+    mix = torch.zeros_like(h2)
+    for e in range(4):
+        ye = F.linear(F.gelu(F.linear(h2, m.inter_w[e], m.inter_b[e]), approximate="tanh"), m.output_w[e], m.output_b[e])
+        mix = mix + (top * (idx == e)).sum(-1, keepdim=True) * ye
+    if mlp_type == "residual":
+        R = m.res_mlp
+        dense = F.linear(F.gelu(F.linear(h2, R.inter_w, R.inter_b), approximate="tanh"), R.output_w, R.output_b)
+        coef = torch.softmax(h2 @ m.res_coef.t(), -1)
+        mix = mix * coef[..., 0:1] + dense * coef[..., 1:2]
+    assert torch.allclose(got, x1 + mix, atol=3e-4), (got - (x1 + mix)).abs().max()
