@@ -14,6 +14,7 @@ from ..ops.gemm import gemm
 
 native.register_sigs({
     "dsb200_gemm_ag_bf16": "ppp iiiii p ll p i p",
+    "dsb200_gemm_ar_bf16": "ppp ll i pp iii iiii ii i p",
 })
 
 
@@ -42,3 +43,45 @@ def gemm_allreduce(x, w_shard, symm, offset=0, out=None):
     symm.all_reduce_bf16(out, offset, M * N)
     symm.barrier()  # nobody overwrites its partial before every peer has read it
     return out
+
+
+class FusedGemmAllReduce(object):
+    """Row-parallel linear + all-reduce as ONE kernel per call (csrc/gemm/gemm_ar.cu): every rank's GEMM epilogue stores its
+    partial tiles into its own symmetric buffer and raises a per-tile flag; reducer warps of the same kernel pull the peers'
+    tiles as their flags arrive and write the sum, tile by tile under the remaining MMAs.
+
+    `symm`: a SymmetricBuffer (or EmulatedPeers with world 1) holding, from `offset`: two partial areas of max_m * n * 2 bytes
+    (double-buffered by call parity) followed by the per-tile flags.  Every rank must make the same sequence of calls."""
+
+    def __init__(self, symm, max_m, n, offset=0):
+        self.symm, self.n, self.max_m = symm, n, max_m
+        self.part_bytes = (max_m * n * 2 + 255) // 256 * 256
+        self.part_off = [offset, offset + self.part_bytes]
+        self.flag_off = offset + 2 * self.part_bytes
+        self.n_flags = ((max_m + 127) // 128) * ((n + 255) // 256)
+        self.nbytes = 2 * self.part_bytes + self.n_flags * 4
+        assert offset + self.nbytes <= symm.nbytes, "symmetric buffer too small for FusedGemmAllReduce"
+        symm.view(self.flag_off, (self.n_flags, ), torch.int32).zero_()
+        self.epoch = 0
+
+    @staticmethod
+    def bytes_needed(max_m, n):
+        part = (max_m * n * 2 + 255) // 256 * 256
+        return 2 * part + ((max_m + 127) // 128) * ((n + 255) // 256) * 4
+
+    def __call__(self, x, w_shard, residual=None, out=None, max_ctas=0):
+        """x: [M, K_local] bf16, w_shard: [N, K_local] bf16 -> sum over ranks of x @ w_shard^T (+ residual), [M, N] bf16."""
+        M, K = x.shape
+        N = w_shard.shape[0]
+        assert N == self.n and M <= self.max_m and w_shard.shape[1] == K and x.stride(1) == 1 and w_shard.stride(1) == 1
+        if out is None:
+            out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+        self.epoch += 1
+        s = self.symm
+        arr = (ctypes.c_void_p * s.world)(*s.ptrs)
+        rc = native.lib().dsb200_gemm_ar_bf16(native.ptr(x), native.ptr(w_shard), ctypes.cast(arr, ctypes.c_void_p), self.part_off[self.epoch & 1],
+                                              self.flag_off, self.epoch, native.ptr(out), native.ptr(residual), M, N, K, x.stride(0),
+                                              w_shard.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0, s.rank, s.world,
+                                              int(max_ctas), native.stream_ptr())
+        native.check(rc)
+        return out

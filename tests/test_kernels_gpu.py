@@ -789,3 +789,24 @@ def test_ragged_engine_w8a8_gpu():
     assert (w_dev[0].float().cpu() - w_host[0].float()).abs().max() <= 0.13 * w_host[0].float().abs().max()  # bf16 vs fp32 source weights
     assert (out - ref).abs().max() < 0.35 * ref.abs().max()  # fp8 noise of four projections per layer on random weights
     assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
+
+
+@pytest.mark.parametrize("shape", [(300, 512, 256), (128, 4096, 1024), (1000, 1096, 328)])
+def test_fused_gemm_allreduce_single_rank(shape):
+    """GEMM -> all-reduce kernel at world 1 (the reducers wait on this rank's own tile flags only): equals the plain product,
+    with and without the residual, over repeated calls (epoch / parity handling)."""
+    from deepspeedsyclsupport_b200.parallel.fused import FusedGemmAllReduce
+    from deepspeedsyclsupport_b200.parallel.symm import EmulatedPeers
+    M, N, K = shape
+    em = EmulatedPeers(1, FusedGemmAllReduce.bytes_needed(M, N) + 4096)
+    op = FusedGemmAllReduce(em, M, N)
+    torch.manual_seed(0)
+    w = (torch.randn(N, K, device=_dev()) * 0.05).bfloat16()
+    for it in range(3):
+        x = torch.randn(M, K, device=_dev()).bfloat16()
+        res = torch.randn(M, N, device=_dev()).bfloat16() if it == 1 else None
+        out = op(x, w, residual=res).float()
+        ref = x.float() @ w.float().t()
+        # the partial is rounded to bf16 before the reduction (as it is when it crosses NVLink)
+        want = ref.bfloat16().float() + (res.float() if res is not None else 0)
+        assert (out - want).abs().max() <= 1e-2 * want.abs().max()
