@@ -72,6 +72,76 @@ __device__ __forceinline__ void acc_bf16x8(float (&a)[8], const uint4& v) {
   }
 }
 
+// Sum of one tile over the ranks, compile-time world W, U vectors per thread in one batch, so W*U 16-byte loads are in flight
+// per thread before the first add, 16 KB per SM (a peer load is a ~2-3 us NVLink round trip; 128 threads x 1 load could not cover it).
+template <int W, int U>
+__device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int rt) {
+  constexpr int VEC_PER_ROW = BN / 8;
+  constexpr int NW = W;
+  constexpr int world = W;
+#pragma unroll 1
+  for (int v0 = rt; v0 < BM * VEC_PER_ROW; v0 += RED_THREADS * U) {
+    uint4 part[U][NW];
+    uint32_t off[U];  // in 16-byte vectors (M*N/8 < 2^32)
+    bool ok[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int v = v0 + u * RED_THREADS;
+      const int r = v / VEC_PER_ROW, cv = v - r * VEC_PER_ROW;
+      const int gr = m0 + r, gc = n0 + cv * 8;
+      ok[u] = gr < p.M && gc < p.N;
+      off[u] = ok[u] ? static_cast<uint32_t>((static_cast<size_t>(gr) * p.N + gc) >> 3) : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+      if (k < world) {
+        const int src = (k + p.rank) % world;
+        const uint8_t* base = static_cast<const uint8_t*>(p.peer[src]) + p.part_off;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (ok[u]) part[u][k] = ld_peer_v4(base + static_cast<size_t>(off[u]) * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (!ok[u]) continue;
+      float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k = 0; k < NW; ++k)
+        if (k < world) acc_bf16x8(a, part[u][k]);
+      const int v = v0 + u * RED_THREADS;
+      const int r = v / VEC_PER_ROW, cv = v - r * VEC_PER_ROW;
+      const int gr = m0 + r, gc = n0 + cv * 8;
+      if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(gr) * p.ldr + gc));
+      uint4 o;
+      o.x = pack_bf16x2(a[0], a[1]);
+      o.y = pack_bf16x2(a[2], a[3]);
+      o.z = pack_bf16x2(a[4], a[5]);
+      o.w = pack_bf16x2(a[6], a[7]);
+      *reinterpret_cast<uint4*>(p.out + static_cast<size_t>(gr) * p.ldo + gc) = o;
+    }
+  }
+}
+
+// Any world size: one vector at a time, peers summed in arrival order of the loads the compiler can keep in flight.
+__device__ __noinline__ void reduce_tile_any(const Params& p, int m0, int n0, int rt) {
+  for (int v = rt; v < BM * (BN / 8); v += RED_THREADS) {
+    const int r = v / (BN / 8), cv = v - r * (BN / 8);
+    const int gr = m0 + r, gc = n0 + cv * 8;
+    if (gr >= p.M || gc >= p.N) continue;
+    const size_t off = p.part_off + (static_cast<size_t>(gr) * p.N + gc) * 2;
+    float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int k = 0; k < p.world; ++k) acc_bf16x8(a, ld_peer_v4(static_cast<const uint8_t*>(p.peer[(k + p.rank) % p.world]) + off));
+    if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(gr) * p.ldr + gc));
+    uint4 o;
+    o.x = pack_bf16x2(a[0], a[1]);
+    o.y = pack_bf16x2(a[2], a[3]);
+    o.z = pack_bf16x2(a[4], a[5]);
+    o.w = pack_bf16x2(a[6], a[7]);
+    *reinterpret_cast<uint4*>(p.out + static_cast<size_t>(gr) * p.ldo + gc) = o;
+  }
+}
+
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmP, const __grid_constant__ Params p) {
@@ -246,26 +316,12 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
       named_bar_sync(2, RED_THREADS);
-      for (int v = rt; v < BM * (BN / 8); v += RED_THREADS) {
-        const int r = v / (BN / 8), cv = v - r * (BN / 8);
-        const int gr = m0 + r, gc = n0 + cv * 8;
-        if (gr >= p.M || gc >= p.N) continue;
-        const size_t off = p.part_off + (static_cast<size_t>(gr) * p.N + gc) * 2;
-        float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        uint4 part[MAX_RANKS];
-#pragma unroll
-        for (int k = 0; k < MAX_RANKS; ++k)
-          if (k < p.world) part[k] = ld_peer_v4(static_cast<const uint8_t*>(p.peer[(k + p.rank) % p.world]) + off);
-#pragma unroll
-        for (int k = 0; k < MAX_RANKS; ++k)
-          if (k < p.world) acc_bf16x8(a, part[k]);
-        if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(gr) * p.ldr + gc));
-        uint4 o;
-        o.x = pack_bf16x2(a[0], a[1]);
-        o.y = pack_bf16x2(a[2], a[3]);
-        o.z = pack_bf16x2(a[4], a[5]);
-        o.w = pack_bf16x2(a[6], a[7]);
-        *reinterpret_cast<uint4*>(p.out + static_cast<size_t>(gr) * p.ldo + gc) = o;
+      switch (p.world) {
+        case 1: reduce_tile<1, 4>(p, m0, n0, rt); break;
+        case 2: reduce_tile<2, 4>(p, m0, n0, rt); break;
+        case 4: reduce_tile<4, 2>(p, m0, n0, rt); break;
+        case 8: reduce_tile<8, 1>(p, m0, n0, rt); break;
+        default: reduce_tile_any(p, m0, n0, rt); break;
       }
     }
   }

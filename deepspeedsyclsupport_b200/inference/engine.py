@@ -99,12 +99,46 @@ class InferenceEngine(Module):
         is_meta = any(p.is_meta for p in self.module.parameters())
         if not is_meta:
             self.module.to(device)
+        if config.tensor_parallel.tp_size > 1 and not is_meta and not getattr(self, "_kernel_injected", False) and not config.enable_cuda_graph:
+            self._attach_fused_allreduce()
         if config.tensor_parallel.tp_size > 1:
             _rng_state = get_accelerator().get_rng_state().to(device)
             dist.broadcast(_rng_state, 0)
             get_accelerator().set_rng_state(_rng_state.cpu())
         self.local_cuda_graph = config.enable_cuda_graph and get_accelerator().device_name() == "cuda"
         self._graphs = {}
+
+    def _attach_fused_allreduce(self):
+        """Row-parallel layers of a single-node bf16 TP group run GEMM + all-reduce as one kernel over peer memory (one symmetric
+        buffer and one FusedGemmAllReduce per distinct output width).  DSB200_FUSED_TP_AR=0 keeps NCCL; DSB200_FUSED_TP_MAX_TOKENS
+        bounds the token count served by the fused path (larger inputs fall through to GEMM + NCCL).  Not used under CUDA-graph
+        capture: the call epoch is a host-side counter."""
+        import os
+        from ..comm.comm import _single_node_job
+        from ..module_inject.layers import LinearAllreduce
+        if (os.environ.get("DSB200_FUSED_TP_AR", "1") == "0" or get_accelerator().device_name() != "cuda" or not _single_node_job()
+                or self.mp_group is None or dist.get_world_size(self.mp_group) not in (2, 4, 8)):
+            return
+        layers = [m for m in self.module.modules() if isinstance(m, LinearAllreduce) and m.weight.dtype == torch.bfloat16
+                  and m.weight.is_cuda and m.weight.shape[0] % 8 == 0]
+        if not layers:
+            return
+        max_m = int(os.environ.get("DSB200_FUSED_TP_MAX_TOKENS", "4096"))
+        try:
+            from ..parallel.fused import FusedGemmAllReduce
+            from ..parallel.symm import SymmetricBuffer
+            self._fused_ar = {}
+            for n in sorted({m.weight.shape[0] for m in layers}):
+                sb = SymmetricBuffer(self.mp_group, FusedGemmAllReduce.bytes_needed(max_m, n))
+                self._fused_ar[n] = FusedGemmAllReduce(sb, max_m, n)
+                sb.barrier()
+            for m in layers:
+                m.attach_fused(self._fused_ar[m.weight.shape[0]])
+            log_dist(f"tensor-parallel all-reduce fused into {len(layers)} row-parallel GEMMs (widths {sorted(self._fused_ar)})", ranks=[0])
+        except Exception as e:  # no peer access between the ranks: NCCL
+            logger.warning(f"fused GEMM + all-reduce unavailable ({e}); using NCCL")
+            for m in layers:
+                m._fused = None
 
     def profile_model_time(self, use_cuda_events=True):
         if not self.model_profile_enabled and not self._config.enable_cuda_graph:

@@ -1,8 +1,9 @@
 """Tensor-parallel layer replacements used by AutoTP (parity: deepspeed/module_inject/layers.py:16-59 + lm-head variant).
 
 `LinearAllreduce` = row-parallel linear: local GEMM on the input-feature shard, then all-reduce over the TP group, then
-bias.  On CUDA the GEMM is the tcgen05 kernel and, when a symmetric buffer is attached (`attach_symm`), the reduction
-is the one-shot peer-memory all-reduce (parallel/fused.gemm_allreduce) instead of NCCL."""
+bias.  On CUDA the GEMM is the tcgen05 kernel.  With `attach_fused` (the inference engine does it for single-node bf16 TP) GEMM
+and all-reduce are ONE kernel over peer memory (parallel/fused.FusedGemmAllReduce, csrc/gemm/gemm_ar.cu); with only a symmetric
+buffer attached (`attach_symm`) the reduction is the one-shot peer-memory all-reduce after the GEMM; otherwise NCCL."""
 import torch
 from torch import nn
 from torch.nn import functional as F
@@ -31,6 +32,7 @@ class LinearAllreduce(nn.Module):
         self.bias = bias
         self.mp_group = mp_group
         self._symm = None
+        self._fused = None
 
     @property
     def out_features(self):
@@ -43,8 +45,21 @@ class LinearAllreduce(nn.Module):
     def attach_symm(self, symm, offset=0):
         self._symm, self._symm_off = symm, offset
 
+    def attach_fused(self, op):
+        """op: a parallel.fused.FusedGemmAllReduce for this layer's out_features, shared by every layer with the same width
+        (one epoch counter per flag area)."""
+        assert op.n == self.weight.shape[0]
+        self._fused = op
+
     def forward(self, input):
-        if self._symm is not None and input.is_cuda and input.dtype == torch.bfloat16:
+        fused = self._fused
+        if (fused is not None and input.is_cuda and input.dtype == torch.bfloat16 and self.weight.dtype == torch.bfloat16
+                and input.numel() // input.shape[-1] <= fused.max_m and input.shape[-1] % 8 == 0):
+            x2 = input.reshape(-1, input.shape[-1])
+            if not x2.is_contiguous():
+                x2 = x2.contiguous()
+            output = fused(x2, self.weight).view(*input.shape[:-1], self.weight.shape[0])
+        elif self._symm is not None and input.is_cuda and input.dtype == torch.bfloat16:
             from ..parallel.fused import gemm_allreduce
             x2 = input.reshape(-1, input.shape[-1]).contiguous()
             output = gemm_allreduce(x2, self.weight, self._symm, self._symm_off).view(*input.shape[:-1], self.weight.shape[0])
