@@ -6,8 +6,10 @@ import os
 
 import torch
 
+from .base_engine import CheckpointEngineBase
 
-class HuggingFaceCheckpointEngine:
+
+class HuggingFaceCheckpointEngine(CheckpointEngineBase):
 
     def __init__(self, model_name_or_path: str, auth_token: str = None):
         assert os.path.isdir(model_name_or_path), f"{model_name_or_path} is not a local directory (no network access)"

@@ -171,7 +171,7 @@ def build_engine_from_state_dict(model_type, hf_config: dict, state_dict: dict, 
 
     def builder(tp_group, device):
         return RaggedTransformer(spec, canon, tp_group=tp_group, dtype=dtype, device=device,
-                                 quantization_mode=engine_config.quantization.quantization_mode)
+                                 quantization_mode=engine_config.quantization.quantization_mode, engine_config=engine_config)
 
     return InferenceEngineV2(builder, engine_config)
 
@@ -187,40 +187,22 @@ def build_hf_engine(path: str, engine_config: RaggedInferenceEngineConfig, debug
 
 
 def build_engine_from_ds_checkpoint(path: str, engine_config: RaggedInferenceEngineConfig, debug_level: int = 20):
-    """Rebuild from `InferenceEngineV2.serialize()` output (already TP-sharded, canonical names)."""
-    from ... import comm as dist
-    with open(os.path.join(path, "ds_model_config.pkl"), "rb") as f:
-        spec = pickle.load(f)
+    """Rebuild from `InferenceEngineV2.serialize()` output: per rank one flat byte buffer (already TP-sharded and laid out for the
+    kernels, fp8 scales included) + its description; the containers are pointed at slices of the buffer."""
+    from .inference_parameter import STR_TO_DTYPE
+    from .model_implementations.flat_model_helpers import (make_metadata_filename, make_model_config_filename, make_param_filename,
+                                                           restore_inference_model)
+    with open(make_model_config_filename(path), "rb") as f:
+        saved = pickle.load(f)
 
     def builder(tp_group, device):
-        rank = dist.get_rank(tp_group) if tp_group is not None else 0
-        params = torch.load(os.path.join(path, f"params_rank_{rank}.pt"), map_location="cpu")
-        m = RaggedTransformer.__new__(RaggedTransformer)
-        m.spec, m.tp_group = spec, tp_group
-        m.tp = dist.get_world_size(tp_group) if tp_group is not None else 1
-        m.rank, m.dtype, m.device, m.symm = rank, torch.bfloat16, device, None
-        m.hq, m.hkv = spec.num_heads // m.tp, max(1, spec.num_kv_heads // m.tp)
-        m.kv_replicated = spec.num_kv_heads < m.tp
-        from ...ops import fused_ops as FO
-        m.inv_freq = FO.rope_inv_freq(spec.rotary_dim, spec.rope_theta, device=device) if spec.rotary_dim else None
-        m.embed, m.lm_head = params["embed"].to(device), params["lm_head"].to(device)
-        m.final_norm_w, m.final_norm_b, m.pos_embed = params["final_norm_w"].to(device), None, None
-        m.layers = []
-        for i in range(spec.num_layers):
-            L, experts = {}, {}
-            for k, v in params.items():
-                mm = re.match(rf"layers\.{i}\.(.*)", k)
-                if not mm:
-                    continue
-                name = mm.group(1)
-                em = re.match(r"experts\.(\d+)\.(gate_up|down)", name)
-                if em:
-                    experts.setdefault(int(em.group(1)), {})[em.group(2)] = v.to(device)
-                else:
-                    L[name] = v.to(device)
-            if experts:
-                L["experts"] = [(experts[e]["gate_up"], experts[e]["down"]) for e in sorted(experts)]
-            m.layers.append(L)
+        m = RaggedTransformer(saved["spec"], None, tp_group=tp_group, dtype=STR_TO_DTYPE[saved["dtype"]], device=device,
+                              quantization_mode=saved.get("quantization_mode", ""), engine_config=engine_config)
+        buffer = torch.load(make_param_filename(path, m.tp_rank, m.tp_size), map_location="cpu").to(device)
+        with open(make_metadata_filename(path, m.tp_rank, m.tp_size)) as f:
+            restore_inference_model(buffer, json.load(f), m.named_containers())
+        m.flattened_params = buffer
+        m.check_populated()
         return m
 
     return InferenceEngineV2(builder, engine_config)

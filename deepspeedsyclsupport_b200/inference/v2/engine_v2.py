@@ -131,21 +131,16 @@ class InferenceEngineV2:
         self._state_manager.flush_sequence(uid)
 
     def serialize(self, save_path: str) -> None:
-        """Write this TP rank's flattened parameters + metadata (parity: engine_v2.serialize)."""
+        """Write this TP rank's flattened parameters + their description; rank 0 also writes the model spec
+        (parity: engine_v2.serialize :237-254)."""
+        from .model_implementations.flat_model_helpers import (flatten_inference_model, make_metadata_filename, make_model_config_filename,
+                                                               make_param_filename)
         os.makedirs(save_path, exist_ok=True)
-        rank = self._model.rank
-        tensors = {"embed": self._model.embed, "lm_head": self._model.lm_head, "final_norm_w": self._model.final_norm_w}
-        for i, L in enumerate(self._model.layers):
-            for k, v in L.items():
-                if torch.is_tensor(v):
-                    tensors[f"layers.{i}.{k}"] = v
-                elif k == "experts":
-                    for e, (gu, dn) in enumerate(v):
-                        tensors[f"layers.{i}.experts.{e}.gate_up"] = gu
-                        tensors[f"layers.{i}.experts.{e}.down"] = dn
-        torch.save({k: v.cpu() for k, v in tensors.items()}, os.path.join(save_path, f"params_rank_{rank}.pt"))
-        if rank == 0:
-            with open(os.path.join(save_path, "ds_model_config.pkl"), "wb") as f:
-                pickle.dump(self._model.spec, f)
-            with open(os.path.join(save_path, "metadata_rank_0.json"), "w") as f:
-                json.dump({k: list(v.shape) for k, v in tensors.items()}, f)
+        m = self._model
+        buffer, metadata = flatten_inference_model(m.named_containers(), type(m).__name__)
+        torch.save(buffer.cpu(), make_param_filename(save_path, m.tp_rank, m.tp_size))
+        with open(make_metadata_filename(save_path, m.tp_rank, m.tp_size), "w") as f:
+            json.dump(metadata.model_dump(), f)
+        if m.tp_rank == 0:
+            with open(make_model_config_filename(save_path), "wb") as f:
+                pickle.dump({"spec": m.spec, "dtype": str(m.dtype), "quantization_mode": m.quantization_mode}, f)

@@ -3,7 +3,7 @@ import math
 
 import torch
 
-from ...ops import native
+from ....ops import native
 
 native.register_sigs({
     "dsb200_kv_rotary_append": "pppppp iiiiiii p",
@@ -27,7 +27,7 @@ def kv_rotary_append(qkv, kv_cache, tok_seq, tok_pos, block_table, inv_freq, hq,
                                                   block_table.shape[1], int(rot_dim), native.stream_ptr())
         native.check(rc)
         return qkv
-    from ...ops.fused_ops import rope_ref
+    from ....ops.fused_ops import rope_ref
     if rot_dim == d:
         qkv.copy_(rope_ref(qkv, inv_freq, tok_pos, 0, hq + hkv, d))
     elif rot_dim > 0:

@@ -6,18 +6,27 @@ ships as separate containers/policies (inference/v2/model_implementations/{llama
 
 Forward of a layer: fused (residual-add +) norm -> QKV GEMM -> RoPE + paged-KV append -> paged attention -> output GEMM ->
 tensor-parallel all-reduce -> norm -> MLP GEMMs -> all-reduce (reference: llama_v2/model.py:151-213).
-Weights are sharded per tensor-parallel rank when they are loaded (column slices of qkv/up/gate, row slices of o/down,
-vocab-parallel unembedding) -- reference: model_implementations/sharding/*.py."""
+Building blocks come from the module registry (`modules/heuristics.py` picks the implementation: 16-bit or fp8 linear, ...).
+Weights live in layer containers (`layer_container_base.py`); a container parameter is complete once its checkpoint tensors have
+arrived and is then sharded for this tensor-parallel rank (`sharding/`: column slices of qkv/up/gate, row slices of o/down,
+vocabulary-parallel unembedding) and re-laid-out by the module that will consume it (`transform_*_param`)."""
 import math
+import re
 from dataclasses import dataclass, field
 from typing import Optional
 
 import torch
 
 from .... import comm as dist
-from ....ops import fused_ops as FO
-from ....ops.gemm import gemm, moe_gemm
-from .. import kernels as K
+from ..inference_utils import ActivationType, DtypeEnum, NormTypeEnum
+from ..modules import heuristics
+from ..modules.configs import (DSEmbeddingsConfig, DSLinearConfig, DSMoEConfig, DSNormConfig, DSSelfAttentionConfig, DSUnembedConfig,
+                               PositionalEmbeddingType, RotateHalfConfig)
+from . import sharding
+from .common_parameters import (AttentionOutputParameter, EmbeddingParameter, GatedMLPParameter, MLP1Parameter, MLP2Parameter,
+                                MoEGatingWeightParameter, NormParameter, UnembedParameter, UnfusedMoEGatedMLPParameter, UnfusedMoEMLP2Parameter,
+                                UnfusedQKVParameter)
+from .layer_container_base import LayerContainer
 
 
 @dataclass
@@ -125,24 +134,78 @@ SPEC_FROM_HF = {"llama": _spec_llama, "mistral": _spec_llama, "internlm": _spec_
                 "falcon": _spec_falcon, "phi": _spec_phi, "gpt2": _spec_gpt2, "gptj": _spec_gptj, "gpt_neox": _spec_gpt_neox}
 
 
-def _shard_rows(w, rank, world):
-    """column-parallel linear: slice output features"""
-    n = w.shape[0] // world
-    return w[rank * n:(rank + 1) * n].contiguous()
+# ---- containers addressed by the canonical parameter names (every family's checkpoint names are mapped onto these sources,
+#      either by its own container class under model_implementations/<family>/ or by engine_factory's name mappers)
+class _AttnNormContainer(LayerContainer):
+    qkv_w: UnfusedQKVParameter
+    qkv_b: Optional[UnfusedQKVParameter]
+    o_w: AttentionOutputParameter
+    o_b: Optional[AttentionOutputParameter]
+    norm1_w: NormParameter
+    norm1_b: Optional[NormParameter]
+    norm2_w: Optional[NormParameter]
+    norm2_b: Optional[NormParameter]
+
+    PARAM_MAPPING = {
+        "q.weight": "qkv_w.q_params", "k.weight": "qkv_w.k_params", "v.weight": "qkv_w.v_params",
+        "q.bias": "qkv_b.q_params", "k.bias": "qkv_b.k_params", "v.bias": "qkv_b.v_params",
+        "o.weight": "o_w.params", "o.bias": "o_b.params",
+        "norm1.weight": "norm1_w.params", "norm1.bias": "norm1_b.params",
+        "norm2.weight": "norm2_w.params", "norm2.bias": "norm2_b.params",
+    }
 
 
-def _shard_cols(w, rank, world):
-    """row-parallel linear: slice input features"""
-    n = w.shape[1] // world
-    return w[:, rank * n:(rank + 1) * n].contiguous()
+class GatedLayerContainer(_AttnNormContainer):
+    mlp1_w: GatedMLPParameter
+    mlp2_w: MLP2Parameter
+    PARAM_MAPPING = {"gate.weight": "mlp1_w.gate_params", "up.weight": "mlp1_w.up_params", "down.weight": "mlp2_w.params"}
+
+
+class PlainLayerContainer(_AttnNormContainer):
+    mlp1_w: MLP1Parameter
+    mlp1_b: Optional[MLP1Parameter]
+    mlp2_w: MLP2Parameter
+    mlp2_b: Optional[MLP2Parameter]
+    PARAM_MAPPING = {"up.weight": "mlp1_w.params", "up.bias": "mlp1_b.params", "down.weight": "mlp2_w.params", "down.bias": "mlp2_b.params"}
+
+
+class MoELayerContainer(_AttnNormContainer):
+    router_w: MoEGatingWeightParameter
+    experts_gu: UnfusedMoEGatedMLPParameter
+    experts_dn: UnfusedMoEMLP2Parameter
+    PARAM_MAPPING = {"router.weight": "router_w.params", "experts.*.gate.weight": "experts_gu.gating_experts",
+                     "experts.*.up.weight": "experts_gu.up_experts", "experts.*.down.weight": "experts_dn.experts"}
+
+
+class NonTransformerContainer(LayerContainer):
+    embed: EmbeddingParameter
+    pos_embed: Optional[EmbeddingParameter]
+    final_norm_w: NormParameter
+    final_norm_b: Optional[NormParameter]
+    lm_head: UnembedParameter
+    lm_head_b: Optional[UnembedParameter]
+    PARAM_MAPPING = {"embed.weight": "embed.params", "pos_embed.weight": "pos_embed.params", "final_norm.weight": "final_norm_w.params",
+                     "final_norm.bias": "final_norm_b.params", "lm_head.weight": "lm_head.params", "lm_head.bias": "lm_head_b.params"}
+
+
+def layer_container_class(spec: ArchSpec):
+    if spec.num_experts:
+        return MoELayerContainer
+    return GatedLayerContainer if spec.gated_mlp else PlainLayerContainer
+
+
+_ACT = {("silu", True): ActivationType.SiGLU, ("gelu", True): ActivationType.GEGLU, ("relu", True): ActivationType.ReGLU,
+        ("silu", False): ActivationType.SILU, ("gelu", False): ActivationType.GELU, ("relu", False): ActivationType.RELU}
 
 
 class RaggedTransformer:
     """Holds the TP shard of the weights and runs ragged batches against a DSStateManager."""
 
-    def __init__(self, spec: ArchSpec, state_dict, tp_group=None, dtype=torch.bfloat16, device=None, symm=None, quantization_mode=""):
+    def __init__(self, spec: ArchSpec, state_dict=None, tp_group=None, dtype=torch.bfloat16, device=None, symm=None, quantization_mode="",
+                 engine_config=None, layer_container_cls=None, non_transformer_container_cls=None):
         self.spec = spec
         self.quantization_mode = quantization_mode or ""
+        self.engine_config = engine_config
         self.tp_group = tp_group
         self.tp = dist.get_world_size(tp_group) if (tp_group is not None and dist.is_initialized()) else 1
         self.rank = dist.get_rank(tp_group) if self.tp > 1 else 0
@@ -151,148 +214,200 @@ class RaggedTransformer:
         self.symm = symm
         s = spec
         assert s.num_heads % self.tp == 0, "num_heads must be divisible by tp_size"
-        self.hq = s.num_heads // self.tp
-        self.hkv = max(1, s.num_kv_heads // self.tp)
+        self.hq, self.hkv = sharding.get_local_heads(self.rank, self.tp, s.num_heads, s.num_kv_heads)
         self.kv_replicated = s.num_kv_heads < self.tp
-        self.inv_freq = FO.rope_inv_freq(s.rotary_dim, s.rope_theta, device=self.device) if s.rotary_dim else None
-        self._load(state_dict)
+        self.vocab_padded = -(-s.vocab_size // self.tp) * self.tp
+        self._build_modules()
+        self.layers = [(layer_container_cls or layer_container_class(s))(self) for _ in range(s.num_layers)]
+        self.non_transformer = (non_transformer_container_cls or NonTransformerContainer)(self)
+        if state_dict is not None:
+            self.load_canonical(state_dict)
 
-    # ---- weight loading (canonical names; engine_factory maps HF names onto these)
-    def _t(self, x):
-        return x.to(self.device, self.dtype).contiguous()
+    # ---- facts the parameter classes ask for
+    @property
+    def head_size(self):
+        return self.spec.head_dim
 
-    def _load(self, sd):
-        s, r, W = self.spec, self.rank, self.tp
-        d = s.head_dim
-        self.embed = self._t(sd["embed.weight"])
-        self.pos_embed = self._t(sd["pos_embed.weight"]) if "pos_embed.weight" in sd else None
-        self.final_norm_w = self._t(sd["final_norm.weight"])
-        self.final_norm_b = self._t(sd["final_norm.bias"]) if "final_norm.bias" in sd else None
-        head = sd["embed.weight"] if s.tie_embeddings or "lm_head.weight" not in sd else sd["lm_head.weight"]
-        vpad = -(-head.shape[0] // W) * W
-        if vpad != head.shape[0]:
-            head = torch.cat([head, head.new_zeros(vpad - head.shape[0], head.shape[1])])
-        self.lm_head = self._t(_shard_rows(head, r, W))
-        self.lm_head_b = None
-        if "lm_head.bias" in sd:  # gpt-j
-            hb = sd["lm_head.bias"]
-            if vpad != hb.shape[0]:
-                hb = torch.cat([hb, hb.new_zeros(vpad - hb.shape[0])])
-            self.lm_head_b = self._t(hb.view(W, -1)[r])
-        self.layers = []
-        for i in range(s.num_layers):
-            p = f"layers.{i}."
-            L = {}
-            q, k, v = sd[p + "q.weight"], sd[p + "k.weight"], sd[p + "v.weight"]
-            qs = _shard_rows(q, r, W)
-            if self.kv_replicated:
-                g = r * s.num_kv_heads // W
-                ks, vs = k[g * d:(g + 1) * d], v[g * d:(g + 1) * d]
-            else:
-                ks, vs = _shard_rows(k, r, W), _shard_rows(v, r, W)
-            L["qkv_w"] = self._t(torch.cat([qs, ks, vs], 0))
-            if p + "q.bias" in sd:
-                qb, kb, vb = sd[p + "q.bias"], sd[p + "k.bias"], sd[p + "v.bias"]
-                qbs = qb.view(W, -1)[r]
-                kbs = kb[g * d:(g + 1) * d] if self.kv_replicated else kb.view(W, -1)[r]
-                vbs = vb[g * d:(g + 1) * d] if self.kv_replicated else vb.view(W, -1)[r]
-                L["qkv_b"] = self._t(torch.cat([qbs, kbs, vbs]))
-            L["o_w"] = self._t(_shard_cols(sd[p + "o.weight"], r, W))
-            if p + "o.bias" in sd:
-                L["o_b"] = self._t(sd[p + "o.bias"])
-            L["norm1_w"] = self._t(sd[p + "norm1.weight"])
-            if p + "norm1.bias" in sd:
-                L["norm1_b"] = self._t(sd[p + "norm1.bias"])
-            if p + "norm2.weight" in sd:
-                L["norm2_w"] = self._t(sd[p + "norm2.weight"])
-                if p + "norm2.bias" in sd:
-                    L["norm2_b"] = self._t(sd[p + "norm2.bias"])
-            if s.num_experts:
-                L["router_w"] = sd[p + "router.weight"].to(self.device, torch.float32).contiguous()
-                # expert weights stacked [E, N, K]: one grouped GEMM launch covers every expert (ops/gemm.moe_gemm)
-                gus, dns = [], []
-                for e in range(s.num_experts):
-                    ep = f"{p}experts.{e}."
-                    gus.append(torch.cat([_shard_rows(sd[ep + "gate.weight"], r, W), _shard_rows(sd[ep + "up.weight"], r, W)], 0))
-                    dns.append(_shard_cols(sd[ep + "down.weight"], r, W))
-                L["experts_gu"] = self._t(torch.stack(gus))
-                L["experts_dn"] = self._t(torch.stack(dns))
-            elif s.gated_mlp:
-                L["mlp1_w"] = self._t(torch.cat([_shard_rows(sd[p + "gate.weight"], r, W), _shard_rows(sd[p + "up.weight"], r, W)], 0))
-                L["mlp2_w"] = self._t(_shard_cols(sd[p + "down.weight"], r, W))
-            else:
-                L["mlp1_w"] = self._t(_shard_rows(sd[p + "up.weight"], r, W))
-                if p + "up.bias" in sd:
-                    L["mlp1_b"] = self._t(sd[p + "up.bias"].view(W, -1)[r])
-                L["mlp2_w"] = self._t(_shard_cols(sd[p + "down.weight"], r, W))
-                if p + "down.bias" in sd:
-                    L["mlp2_b"] = self._t(sd[p + "down.bias"])
-            if self.quantization_mode == "wf8af8":
-                # W8A8: dense projection weights stored as e4m3 with one scale per output feature; activations are quantised per
-                # token inside _linear and the product runs on the fp8 tensor-core GEMM (csrc/gemm/gemm_fp8.cu)
-                from ....ops.gemm import quantize_fp8_rowwise
-                for key in ("qkv_w", "o_w", "mlp1_w", "mlp2_w"):
-                    if key in L and L[key].shape[1] % 16 == 0:
-                        L[key] = quantize_fp8_rowwise(L[key])
-            self.layers.append(L)
+    @property
+    def n_heads_q(self):
+        return self.spec.num_heads
 
-    # ---- building blocks
-    def _linear(self, x, w, b=None):
-        if isinstance(w, tuple):  # (e4m3 weight, per-row scale)
-            from ....ops.gemm import linear_fp8
-            y = linear_fp8(x, w[0], w[1])
-            return y if b is None else y + b
-        y = gemm(x, w) if x.is_cuda else torch.nn.functional.linear(x, w)
-        if b is not None:
-            y = y + b
-        return y
+    @property
+    def n_heads_kv(self):
+        return self.spec.num_kv_heads
 
-    def _norm(self, x, w, b, residual=None):
-        if self.spec.norm == "rms":
-            return FO.rms_norm(x, w, self.spec.norm_eps, residual)
-        return FO.layer_norm(x, w, b, self.spec.norm_eps, residual)
+    @property
+    def n_experts(self):
+        return self.spec.num_experts
 
+    @property
+    def tp_rank(self):
+        return self.rank
+
+    @property
+    def tp_size(self):
+        return self.tp
+
+    # convenience views of the non-transformer parameters
+    embed = property(lambda self: self.non_transformer.embed)
+    pos_embed = property(lambda self: self.non_transformer.get("pos_embed"))
+    final_norm_w = property(lambda self: self.non_transformer.final_norm_w)
+    final_norm_b = property(lambda self: self.non_transformer.get("final_norm_b"))
+    lm_head = property(lambda self: self.non_transformer.lm_head)
+    lm_head_b = property(lambda self: self.non_transformer.get("lm_head_b"))
+
+    # ---- building blocks (modules/heuristics.py chooses the implementation of each)
+    def _build_modules(self):
+        s, ec, dt = self.spec, self.engine_config, DtypeEnum(self.dtype)
+        sm = getattr(ec, "state_manager", None)
+        max_tokens = getattr(sm, "max_ragged_batch_size", 768)
+        max_seqs = getattr(sm, "max_ragged_sequence_count", 512)
+        if ec is None and self.quantization_mode:
+            from ..config_v2 import QuantizationConfig, RaggedInferenceEngineConfig
+            ec = RaggedInferenceEngineConfig(quantization=QuantizationConfig(quantization_mode=self.quantization_mode))
+        H, d = s.hidden_size, s.head_dim
+        f_lo, f_hi = sharding.get_shard_endpoints(s.intermediate_size, self.rank, self.tp, self._mlp_granularity())
+        norm_type = NormTypeEnum.RMSNorm if s.norm == "rms" else NormTypeEnum.LayerNorm
+        act = _ACT[(s.activation, bool(s.gated_mlp or s.num_experts))]
+        common = dict(input_dtype=dt, output_dtype=dt)
+        self.embed_mod = heuristics.instantiate_embed(DSEmbeddingsConfig(max_tokens=max_tokens, residual_dtype=dt, embedding_dim=H,
+                                                                         positional_embedding=s.learned_pos_offset is not None,
+                                                                         positional_offset=s.learned_pos_offset or 0), ec)
+        self.norm_mod = heuristics.instantiate_pre_norm(DSNormConfig(max_tokens=max_tokens, type=norm_type, channels=H, residual_dtype=dt,
+                                                                      eps=s.norm_eps, **common), ec)
+        rotary = dict(positional_embedding_type=PositionalEmbeddingType.rotate_half,
+                      positional_embedding_config=RotateHalfConfig(theta_base=s.rope_theta, rotate_dim=s.rotary_dim)) if s.rotary_dim else {}
+        self.attn_mod = heuristics.instantiate_attention(DSSelfAttentionConfig(max_tokens=max_tokens, n_heads_q=self.hq, n_heads_kv=self.hkv,
+                                                                               head_size=d, max_sequences=max_seqs, **common, **rotary), ec)
+        self.qkv_lin = heuristics.instantiate_linear(DSLinearConfig(max_tokens=max_tokens, in_channels=H, out_channels=(self.hq + 2 * self.hkv) * d,
+                                                                    **common), ec)
+        self.o_lin = heuristics.instantiate_linear(DSLinearConfig(max_tokens=max_tokens, in_channels=self.hq * d, out_channels=H, **common), ec)
+        self.mlp1_lin = self.mlp2_lin = self.moe_mod = None
+        if s.num_experts:
+            self.moe_mod = heuristics.instantiate_moe(DSMoEConfig(max_tokens=max_tokens, model_dim=H, intermediate_features=f_hi - f_lo,
+                                                                  n_experts=s.num_experts, top_k=s.top_k, activation=act, normalize_scores=True,
+                                                                  **common), ec)
+        else:
+            self.mlp1_lin = heuristics.instantiate_linear(DSLinearConfig(max_tokens=max_tokens, in_channels=H, out_channels=f_hi - f_lo,
+                                                                         activation=act, **common), ec)
+            self.mlp2_lin = heuristics.instantiate_linear(DSLinearConfig(max_tokens=max_tokens, in_channels=f_hi - f_lo, out_channels=H, **common), ec)
+        self.unembed_mod = heuristics.instantiate_unembed(DSUnembedConfig(max_tokens=max_tokens, dtype=dt, norm_type=norm_type, model_dim=H,
+                                                                          max_sequences=max_seqs, vocab_size=self.vocab_padded // self.tp,
+                                                                          eps=s.norm_eps), ec)
+
+    def _mlp_granularity(self):
+        g = sharding.DEFAULT_SHARD_GRANULARITY
+        return g if self.spec.intermediate_size % g == 0 else 1
+
+    # ---- parameter transforms: shard for this rank, then let the consuming module lay the tensor out
+    def _dev(self, t):
+        return t.to(self.device)
+
+    def transform_embedding_param(self, param):
+        return self._dev(self.embed_mod.transform_param(param))  # whole table on every rank: one gather launch, no collective
+
+    def transform_qkv_param(self, param):
+        s = self.spec
+        local = sharding.shard_qkv_param(param, self.rank, self.tp, s.head_dim, s.num_heads, s.num_kv_heads)
+        return self._dev(self.qkv_lin.transform_param(local))
+
+    def transform_attn_out_param(self, param):
+        s = self.spec
+        if param.ndim == 1:  # the bias is added after the all-reduce, on every rank
+            return self._dev(param.to(self.dtype).contiguous())
+        local = sharding.shard_attn_out_param(param, self.rank, self.tp, s.head_dim, s.num_heads, s.num_kv_heads)
+        return self._dev(self.o_lin.transform_param(local))
+
+    def transform_mlp_1_param(self, param, gated=False):
+        local = sharding.shard_param(param, sharding.ShardingType.OUTER_DIMENSION, self.rank, self.tp,
+                                     num_concatenated_matrices=2 if gated else 1, granularity=self._mlp_granularity())
+        return self._dev(self.mlp1_lin.transform_param(local))
+
+    def transform_mlp_2_param(self, param):
+        if param.ndim == 1:
+            return self._dev(param.to(self.dtype).contiguous())
+        local = sharding.shard_param(param, sharding.ShardingType.INNER_DIMENSION, self.rank, self.tp, granularity=self._mlp_granularity())
+        return self._dev(self.mlp2_lin.transform_param(local))
+
+    def transform_norm_param(self, param):
+        return self._dev(self.norm_mod.transform_param(param))
+
+    def transform_inv_freq_param(self, param):
+        return self._dev(param.to(torch.float32).contiguous())
+
+    def transform_unembed_param(self, param):
+        pad = self.vocab_padded - param.shape[0]
+        if pad:  # equal vocabulary ranges on every rank (the logits all-gather wants one size)
+            param = torch.cat([param, param.new_zeros(pad, *param.shape[1:])])
+        return self._dev(sharding.shard_unembed_param(param, self.rank, self.tp).to(self.dtype).contiguous())
+
+    def transform_moe_gate_param(self, param):
+        return self._dev(self.moe_mod.transform_gate_param(param))
+
+    def transform_moe_mlp_1_param(self, param, gated=True):
+        local = sharding.shard_param(param, sharding.ShardingType.OUTER_DIMENSION, self.rank, self.tp,
+                                     num_concatenated_matrices=2 if gated else 1, granularity=self._mlp_granularity(), bias_dims=2)
+        return self._dev(self.moe_mod.transform_moe_mlp_1_param(local))
+
+    def transform_moe_mlp_2_param(self, param):
+        local = sharding.shard_param(param, sharding.ShardingType.INNER_DIMENSION, self.rank, self.tp, granularity=self._mlp_granularity())
+        return self._dev(self.moe_mod.transform_moe_mlp_2_param(local))
+
+    # ---- loading
+    _LAYER_RX = re.compile(r"^layers\.(\d+)\.(.*)$")
+
+    def set_dependency(self, name: str, tensor: torch.Tensor) -> bool:
+        """Route one canonically named checkpoint tensor to the container that owns it."""
+        m = self._LAYER_RX.match(name)
+        if m:
+            return self.layers[int(m.group(1))].set_dependency(m.group(2), tensor)
+        return self.non_transformer.set_dependency(name, tensor)
+
+    def load_canonical(self, sd):
+        for name, tensor in sd.items():
+            if not self.set_dependency(name, tensor):
+                raise KeyError(f"unexpected parameter '{name}' for family {self.spec.family}")
+        if self.spec.tie_embeddings or "lm_head.weight" not in sd:
+            self.non_transformer.set_dependency("lm_head.weight", sd["embed.weight"])
+        self.check_populated()
+
+    def check_populated(self):
+        for i, c in enumerate(list(self.layers) + [self.non_transformer]):
+            if not c.is_populated:
+                where = f"layer {i}" if i < len(self.layers) else "non-transformer parameters"
+                raise RuntimeError(f"{where}: missing checkpoint tensors for {c.missing()}")
+
+    def named_containers(self):
+        for i, c in enumerate(self.layers):
+            yield f"layers.{i}", c
+        yield "non_transformer", self.non_transformer
+
+    # ---- forward
     def _all_reduce(self, x):
         if self.tp > 1:
             dist.all_reduce(x, group=self.tp_group)
         return x
 
     def _mlp(self, L, h):
-        s = self.spec
-        if s.num_experts:
-            logits = torch.nn.functional.linear(h.float(), L["router_w"])
-            counts, scores, asg, off = K.top_k_gating(logits, s.top_k, normalize=True)
-            moe_in, cumsum, slots = K.moe_scatter(h, counts, asg, off)
-            # the row ranges stay on the device: no host synchronisation between gating and the expert GEMMs
-            act = FO.gated_act(moe_gemm(moe_in, L["experts_gu"], cumsum), s.activation)
-            return K.moe_gather(moe_gemm(act, L["experts_dn"], cumsum), scores, slots)
-        if s.gated_mlp:
-            return self._linear(FO.gated_act(self._linear(h, L["mlp1_w"]), s.activation), L["mlp2_w"])
-        a = FO.bias_act(self._linear(h, L["mlp1_w"]), L.get("mlp1_b"), s.activation)
-        return self._linear(a, L["mlp2_w"])
+        if self.moe_mod is not None:
+            return self.moe_mod(h, L["router_w"], L["experts_gu"], L["experts_dn"])
+        return self.mlp2_lin(self.mlp1_lin(h, L["mlp1_w"], L.get("mlp1_b")), L["mlp2_w"])
 
     def forward(self, batch, state_manager):
         """batch: RaggedBatchWrapper (finalized).  Returns logits [n_seqs, vocab] for the last token of every sequence."""
-        s = self.spec
-        ids, tok_seq, tok_pos, bt = batch.input_ids(), batch.tok_seq(), batch.tok_pos(), batch.block_table()
-        x = K.ragged_embed(ids, self.embed, self.pos_embed, tok_pos, s.learned_pos_offset or 0)
+        s, nt = self.spec, self.non_transformer
+        x = self.embed_mod(batch, nt.embed, nt.get("pos_embed"))
         residual = None
         for li, L in enumerate(self.layers):
-            if residual is None:
-                residual = x
-                hn = self._norm(x, L["norm1_w"], L.get("norm1_b"))
-            else:
-                hn, residual = self._norm(x, L["norm1_w"], L.get("norm1_b"), residual)
-            qkv = self._linear(hn, L["qkv_w"], L.get("qkv_b"))
-            cache = state_manager.get_cache(li)
-            K.kv_rotary_append(qkv, cache, tok_seq, tok_pos, bt, self.inv_freq, self.hq, self.hkv, s.head_dim, rot_dim=s.rotary_dim)
-            attn = K.paged_attention(qkv, cache, tok_seq, tok_pos, bt, self.hq, self.hkv, s.head_dim)
-            attn_out = self._linear(attn, L["o_w"])
+            # residual += x (the previous layer's MLP output), hn = norm(residual)
+            residual, hn = self.norm_mod(x if residual is None else residual, None if residual is None else x, L["norm1_w"], L.get("norm1_b"))
+            qkv = self.qkv_lin(hn, L["qkv_w"], L.get("qkv_b"))
+            attn = self.attn_mod(qkv, state_manager.get_cache(li), batch)
+            attn_out = self.o_lin(attn, L["o_w"])
             if s.parallel_block:
                 # gpt-neox gives the MLP its own LayerNorm of the block input (= the residual stream after the fused add)
-                mlp_in = self._norm(residual, L["norm2_w"], L.get("norm2_b")) if s.parallel_norm2 else hn
-                mlp_out = self._mlp(L, mlp_in)
-                x = self._all_reduce(attn_out + mlp_out)
+                mlp_in = self.norm_mod(residual, None, L["norm2_w"], L.get("norm2_b"))[1] if s.parallel_norm2 else hn
+                x = self._all_reduce(attn_out + self._mlp(L, mlp_in))
                 if "o_b" in L:
                     x = x + L["o_b"]
                 if "mlp2_b" in L:
@@ -301,14 +416,12 @@ class RaggedTransformer:
             attn_out = self._all_reduce(attn_out)
             if "o_b" in L:
                 attn_out = attn_out + L["o_b"]
-            hn, residual = self._norm(attn_out, L["norm2_w"], L.get("norm2_b"), residual)
+            residual, hn = self.norm_mod(residual, attn_out, L["norm2_w"], L.get("norm2_b"))
             x = self._all_reduce(self._mlp(L, hn))
             if "mlp2_b" in L:
                 x = x + L["mlp2_b"]
-        last = K.logits_gather(x, batch.last_tokens())
-        last_res = K.logits_gather(residual, batch.last_tokens())
-        hn, _ = self._norm(last, self.final_norm_w, self.final_norm_b, last_res)
-        logits = self._linear(hn, self.lm_head, self.lm_head_b)
+        logits = self.unembed_mod(x, nt.lm_head, batch, bias=nt.get("lm_head_b"), gamma=nt.final_norm_w, beta=nt.get("final_norm_b"),
+                                  residual=residual)
         if self.tp > 1:
             full = torch.empty(self.tp, *logits.shape, dtype=logits.dtype, device=logits.device)
             dist.all_gather_into_tensor(full, logits.contiguous(), group=self.tp_group)

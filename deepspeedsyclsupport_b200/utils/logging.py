@@ -25,6 +25,16 @@ def _create_logger(name="DeepSpeedB200", level=logging.INFO):
     return lg
 
 
+class LoggerFactory:
+    """(parity: deepspeed/utils/logging.py LoggerFactory.create_logger)"""
+
+    @staticmethod
+    def create_logger(name=None, level=logging.INFO):
+        if name is None:
+            raise ValueError("name for logger cannot be None")
+        return _create_logger(name, level)
+
+
 logger = _create_logger(level=log_levels.get(os.environ.get("DSB200_LOG_LEVEL", "info"), logging.INFO))
 
 

@@ -210,7 +210,9 @@ def test_ragged_engine_w8a8_mode_tracks_dense():
                                        quantization={"quantization_mode": "wf8af8"})
     sd = _hf_llama_state(CFG)
     eng = build_engine_from_state_dict("llama", CFG, sd, ecfg, dtype=torch.float32)
-    assert isinstance(eng._model.layers[0]["qkv_w"], tuple) and eng._model.layers[0]["qkv_w"][0].dtype == torch.float8_e4m3fn
+    qkv_w = eng._model.layers[0]["qkv_w"]
+    assert qkv_w.dtype == torch.float8_e4m3fn and qkv_w.scales.shape == (qkv_w.shape[0], )
+    assert type(eng._model.qkv_lin).__name__ == "FP8Linear"  # picked by modules/heuristics from the engine's quantization mode
     torch.manual_seed(1)
     a = torch.randint(0, 97, (21, ))
     ref = _dense_llama_logits(sd, CFG, a)
