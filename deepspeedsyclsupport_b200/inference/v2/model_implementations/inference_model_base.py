@@ -33,7 +33,8 @@ class DSInferenceModelBase(ABC):
     def kv_cache_config(self):
         from ..ragged.manager_configs import KVCacheConfig
         s = self.spec
-        return KVCacheConfig(block_size=128, cache_shape=(s.num_layers, self.hkv, s.head_dim), cache_dtype=self.dtype,
+        name = {torch.bfloat16: "bf16", torch.float16: "fp16", torch.float32: "fp32"}[self.dtype]
+        return KVCacheConfig(block_size=128, cache_shape=(s.num_layers, self.hkv, s.head_dim), cache_dtype=name,
                              max_blocks_per_allocation_group=-(-s.max_positions // 128))
 
     def get_kv_requirements(self, sequence, max_new_tokens: int, max_new_blocks: int, block_size: int = 128) -> Tuple[int, int]:

@@ -52,7 +52,7 @@ class ContainerMap:
         return self._non_transformer
 
     def map_param(self, name: str, tensor: torch.Tensor) -> None:
-        if any(name == u or name.endswith(u) for u in self._unmapped):
+        if any(name == u or name.endswith("." + u) for u in self._unmapped):
             return
         m = self._rx.match(name) if self._prefix is not None else None
         if m:
@@ -93,6 +93,10 @@ class InferenceV2Policy(ABC):
     def build_container_map(self) -> ContainerMap:
         """ContainerMap over `self.model`'s containers."""
 
+    def rename(self, name: str) -> str:
+        """Hook for checkpoints saved from the bare model (without the CausalLM wrapper's prefix)."""
+        return name
+
     def prepare_tensor(self, name: str, tensor: torch.Tensor) -> torch.Tensor:
         """Hook for layouts that need the whole tensor changed before routing (GPT-2's Conv1D transposes)."""
         return tensor
@@ -105,6 +109,7 @@ class InferenceV2Policy(ABC):
         if self._checkpoint_engine is None:
             raise ValueError("a checkpoint engine is required to populate the model")
         for name, tensor in self._checkpoint_engine.parameters():
+            name = self.rename(name)
             cmap.map_param(name, self.prepare_tensor(name, tensor))
         self.finish_loading(cmap)
         cmap.validate()

@@ -34,7 +34,9 @@ def attn_out_in_features(out_features: int, shard_rank: int, num_shards: int, he
                          n_heads_kv: Optional[int] = None) -> int:
     """Columns of this rank's attention-output weight (= local query heads * head size)."""
     if n_heads_kv is None or n_heads_kv == n_heads_q:
-        lo, hi = get_shard_endpoints(out_features, shard_rank, num_shards, granularity=head_size)
+        # square projection in every MHA model: the head dimension equals out_features unless the head count says otherwise
+        dim = n_heads_q * head_size if n_heads_q is not None else out_features
+        lo, hi = get_shard_endpoints(dim, shard_rank, num_shards, granularity=head_size)
         return hi - lo
     from .attn import get_local_heads
     return get_local_heads(shard_rank, num_shards, n_heads_q, n_heads_kv)[0] * head_size

@@ -782,10 +782,9 @@ def test_ragged_engine_w8a8_gpu():
     assert eng._model.layers[0]["mlp1_w"].dtype == torch.float8_e4m3fn and eng._model.layers[0]["mlp1_w"].scales.is_cuda
     out = eng.put([1], [a])[0].float()
     # the same quantised model evaluated on the host in fp32 (restated fp8 product): isolates the kernels from fp8 noise
-    import deepspeedsyclsupport_b200.inference.v2.model_implementations.ragged_transformer as RT
-    from deepspeedsyclsupport_b200.inference.v2.engine_factory import SPEC_FROM_HF, _MAPPERS
-    host = RT.RaggedTransformer(SPEC_FROM_HF["llama"](cfg), _MAPPERS["llama"](sd, cfg), dtype=torch.float32, device=torch.device("cpu"),
-                                quantization_mode="wf8af8")
+    from deepspeedsyclsupport_b200.inference.v2.checkpoint import InMemoryModelEngine
+    from deepspeedsyclsupport_b200.inference.v2.engine_factory import build_model_from_checkpoint
+    host = build_model_from_checkpoint("llama", cfg, InMemoryModelEngine(sd), mk("wf8af8"), device=torch.device("cpu"), dtype=torch.float32)
     w_dev, w_host = eng._model.layers[1]["mlp2_w"], host.layers[1]["mlp2_w"]
     assert (w_dev.float().cpu() - w_host.float()).abs().max() <= 0.13 * w_host.float().abs().max()  # bf16 vs fp32 source weights
     assert (out - ref).abs().max() < 0.35 * ref.abs().max()  # fp8 noise of four projections per layer on random weights
