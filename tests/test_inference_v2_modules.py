@@ -307,3 +307,103 @@ def test_serialize_writes_one_flat_buffer_and_restores_identically(tmp_path, mod
     base = eng2._model.flattened_params
     p = eng2._model.layers[1]["mlp2_w"]
     assert base.data_ptr() <= p.data_ptr() < base.data_ptr() + base.numel()
+
+
+# ------------------------------------------------------------------ kernel objects
+def test_kernel_objects_validate_at_construction_and_write_into_outputs():
+    import torch.nn.functional as F
+    from deepspeedsyclsupport_b200.inference.v2.kernels.core_ops import (BlasLibLinear, CUDABiasActivation, CUDAFPPostLN, CUDAFPPreLN, CUDAGatedActivation,
+                                                                      CUDARMSNorm, CUDARMSPreNorm)
+    from deepspeedsyclsupport_b200.inference.v2.kernels.cutlass_ops import MixedGEMM, MoEGEMM
+    from deepspeedsyclsupport_b200.inference.v2.kernels.ds_kernel import DSKernelBase
+    x, h, g, b = torch.randn(4, 32), torch.randn(4, 32), torch.rand(32) + 0.5, torch.randn(32)
+    for bad in (lambda: CUDARMSNorm(30, "bf16"), lambda: CUDARMSNorm(32, torch.int8), lambda: CUDAGatedActivation(32, "fp32", ActivationType.GELU),
+                lambda: CUDABiasActivation(32, "fp32", ActivationType.SiGLU), lambda: MixedGEMM("bf16", ActivationType.IDENTITY, 3),
+                lambda: MoEGEMM("fp32", ActivationType.SILU)):
+        with pytest.raises(ValueError):
+            bad()
+    assert issubclass(CUDARMSNorm, DSKernelBase)
+    z = torch.empty_like(x)
+    rms = lambda t: t * torch.rsqrt(t.pow(2).mean(-1, keepdim=True) + 1e-5) * g
+    assert CUDARMSNorm(32, "fp32")(z, x, g) is z and torch.allclose(z, rms(x), atol=1e-5)
+    zr, zh = torch.empty_like(x), torch.empty_like(x)
+    CUDARMSPreNorm(32, "fp32")(zr, zh, x, h, g)
+    assert torch.allclose(zr, x + h) and torch.allclose(zh, rms(x + h), atol=1e-5)
+    CUDAFPPreLN(32, "fp32")(zr, zh, x, h, g, b)
+    assert torch.allclose(zh, F.layer_norm(x + h, (32, ), g, b), atol=1e-5)
+    CUDAFPPostLN(32, "fp32")(z, x, h, g, b)
+    assert torch.allclose(z, F.layer_norm(x + h, (32, ), g, b), atol=1e-5)
+    act = x.clone()
+    CUDABiasActivation(32, "fp32", ActivationType.RELU)(act, b)
+    assert torch.allclose(act, F.relu(x + b))
+    out = torch.empty(4, 16)
+    CUDAGatedActivation(16, "fp32", ActivationType.SiGLU)(out, x, b)
+    assert torch.allclose(out, F.silu((x + b)[:, :16]) * (x + b)[:, 16:], atol=1e-6)
+    w = torch.randn(24, 32)
+    o = torch.empty(4, 24)
+    BlasLibLinear("fp32")(o, x, w)
+    assert torch.allclose(o, x @ w.t(), atol=1e-5)
+    # weight-only quantised GEMMs: 8-bit and packed 4-bit, one scale per group of 8 input features
+    w8, sc = torch.randint(-127, 127, (24, 32), dtype=torch.int8), torch.rand(24, 4) * 0.01
+    MixedGEMM("bf16", ActivationType.IDENTITY, 8)(o, x, w8, sc)
+    assert torch.allclose(o, x @ (w8.float().view(24, 4, 8) * sc[..., None]).view(24, 32).t(), atol=1e-4)
+    q4 = torch.randint(0, 16, (24, 32))
+    packed = (q4[:, 0::2] | (q4[:, 1::2] << 4)).to(torch.uint8)
+    MixedGEMM("bf16", ActivationType.IDENTITY, 4)(o, x, packed, sc)
+    assert torch.allclose(o, x @ ((q4 - 8).float().view(24, 4, 8) * sc[..., None]).view(24, 32).t(), atol=1e-4)
+    xs, W, cum, oo = torch.randn(6, 32), torch.randn(2, 8, 32), torch.tensor([4, 6]), torch.empty(6, 8)
+    MoEGEMM("bf16", ActivationType.SILU)(oo, xs, W, cum, torch.ones(2, 8))
+    assert torch.allclose(oo, F.silu(torch.cat([xs[:4] @ W[0].t(), xs[4:] @ W[1].t()]) + 1), atol=1e-5)
+
+
+def test_ragged_kernel_objects_against_a_live_batch():
+    from deepspeedsyclsupport_b200.inference.v2.kernels.ragged_ops import (AtomBuilder, BlockedFlashAttn, BlockedRotaryEmbeddings, LinearBlockedKVCopy,
+                                                                        MoEGather, MoEScatter, RaggedEmbeddingKernel, RaggedLogitsGather,
+                                                                        RaggedTopKGating)
+    with pytest.raises(ValueError):
+        BlockedFlashAttn(72, "bf16")
+    with pytest.raises(ValueError):
+        RaggedEmbeddingKernel(torch.float32, torch.float32, 64)
+    sd = _hf_llama_state(CFG)
+    eng = build_engine_from_state_dict("llama", CFG, sd, _ecfg(), dtype=torch.float32)
+    a, b = torch.arange(5), torch.arange(10, 13)
+    eng.put([1, 2], [a, b])
+    batch, model = eng._batch, eng._model
+    T = 8
+    emb = torch.empty(T, 64)
+    RaggedEmbeddingKernel(torch.float32, torch.int64, 64)(emb, batch, model.embed)
+    assert torch.equal(emb, sd["model.embed_tokens.weight"][torch.cat([a, b])])
+    last = torch.empty(2, 64)
+    RaggedLogitsGather(64, torch.float32)(last, emb, batch)
+    assert torch.equal(last, emb[[4, 7]])
+    atoms, n = AtomBuilder()(None, batch, 128, 16)
+    assert n == 2
+    # KV copy without rotation, then attention == per-sequence causal softmax(q k^T) v
+    hq, hkv, d = 4, 2, 16
+    qkv = torch.randn(T, (hq + 2 * hkv) * d)
+    cache = torch.zeros(eng._state_manager.get_cache(0).shape)  # fp32 cache: exact comparison
+    LinearBlockedKVCopy(d, hq, hkv, torch.float32)(cache, qkv, batch)
+    out = torch.empty(T, hq * d)
+    BlockedFlashAttn(d, torch.float32)(out, qkv, cache, batch, hq, hkv)
+    q, k, v = qkv.view(T, hq + 2 * hkv, d).split([hq, hkv, hkv], 1)
+    for lo, hi in ((0, 5), (5, 8)):
+        ref = torch.nn.functional.scaled_dot_product_attention(q[lo:hi].transpose(0, 1), k[lo:hi].transpose(0, 1).repeat_interleave(2, 0),
+                                                               v[lo:hi].transpose(0, 1).repeat_interleave(2, 0), is_causal=True)
+        assert torch.allclose(out[lo:hi], ref.transpose(0, 1).reshape(hi - lo, -1), atol=1e-5)
+    rot = qkv.clone()
+    BlockedRotaryEmbeddings(d, hq, hkv, torch.float32, d, 10000.0)(cache, rot, batch)
+    assert torch.equal(rot[:, (hq + hkv) * d:], qkv[:, (hq + hkv) * d:]) and not torch.equal(rot[1, :d], qkv[1, :d])
+    assert torch.allclose(rot[0, :hq * d], qkv[0, :hq * d], atol=1e-6)  # position 0 is not rotated
+    # gating -> scatter -> gather with identity experts gives back the input (normalised top-2 weights sum to one)
+    E, k2 = 4, 2
+    logits = torch.randn(T, E)
+    counts, scores, asg, off = torch.empty(E, dtype=torch.int32), torch.empty(T, k2), torch.empty(T, k2, dtype=torch.int32), torch.empty(
+        T, k2, dtype=torch.int32)
+    RaggedTopKGating(torch.float32)(counts, scores, asg, off, logits, batch)
+    assert counts.sum() == T * k2 and torch.allclose(scores.sum(-1), torch.ones(T))
+    moe_in, cumsum, slots = torch.empty(T * k2, 64), torch.empty(E, dtype=torch.int64), torch.empty(T, k2, dtype=torch.int32)
+    MoEScatter(torch.float32, 64)(moe_in, cumsum, slots, emb, counts, asg, off)
+    assert cumsum[-1] == T * k2
+    back = torch.empty(T, 64)
+    MoEGather(torch.float32, 64)(back, moe_in, scores, slots)
+    assert torch.allclose(back, emb, atol=1e-6)
