@@ -1,10 +1,8 @@
-"""Event fan-out to TensorBoard / W&B / CSV on rank 0 (parity: deepspeed/monitor/monitor.py:29-53 and backends)."""
-import csv
-import os
+"""Event fan-out to TensorBoard / W&B / CSV on rank 0 (parity: deepspeed/monitor/monitor.py:29-53; backends in tensorboard.py,
+wandb.py, csv_monitor.py)."""
 from abc import ABC, abstractmethod
 
 from .. import comm as dist
-from ..utils.logging import logger
 
 
 class Monitor(ABC):
@@ -18,98 +16,6 @@ class Monitor(ABC):
         pass
 
 
-class TensorBoardMonitor(Monitor):
-
-    def __init__(self, tensorboard_config):
-        super().__init__(tensorboard_config)
-        self.enabled = tensorboard_config.enabled
-        self.output_path = tensorboard_config.output_path
-        self.job_name = tensorboard_config.job_name
-        self.summary_writer = None
-        if self.enabled and dist.get_rank() == 0:
-            self.get_summary_writer()
-
-    def get_summary_writer(self, base=os.path.join(os.path.expanduser("~"), "tensorboard")):
-        try:
-            from torch.utils.tensorboard import SummaryWriter
-        except ImportError:
-            logger.warning("tensorboard is not installed: TensorBoard monitor disabled")
-            self.enabled = False
-            return None
-        log_dir = os.path.join(self.output_path, self.job_name) if self.output_path else os.path.join(base, self.job_name)
-        os.makedirs(log_dir, exist_ok=True)
-        self.summary_writer = SummaryWriter(log_dir=log_dir)
-        return self.summary_writer
-
-    def write_events(self, event_list, flush=True):
-        if self.enabled and self.summary_writer is not None and dist.get_rank() == 0:
-            for event in event_list:
-                self.summary_writer.add_scalar(*event)
-            if flush:
-                self.summary_writer.flush()
-
-    def flush(self):
-        if self.summary_writer is not None:
-            self.summary_writer.flush()
-
-
-class WandbMonitor(Monitor):
-
-    def __init__(self, wandb_config):
-        super().__init__(wandb_config)
-        self.enabled = wandb_config.enabled
-        if self.enabled and dist.get_rank() == 0:
-            try:
-                import wandb
-                wandb.init(project=wandb_config.project, group=wandb_config.group, entity=wandb_config.team)
-                self._wandb = wandb
-            except ImportError:
-                logger.warning("wandb is not installed: W&B monitor disabled")
-                self.enabled = False
-
-    def log(self, data, step=None, commit=None, sync=None):
-        if self.enabled and dist.get_rank() == 0:
-            return self._wandb.log(data, step=step, commit=commit, sync=sync)
-
-    def write_events(self, event_list):
-        if self.enabled and dist.get_rank() == 0:
-            for event in event_list:
-                label, value, step = event[0], event[1], event[2]
-                self.log({label: value}, step=step)
-
-
-class csvMonitor(Monitor):
-
-    def __init__(self, csv_config):
-        super().__init__(csv_config)
-        self.filenames = []
-        self.enabled = csv_config.enabled
-        self.output_path = csv_config.output_path
-        self.job_name = csv_config.job_name
-        self.log_dir = self.setup_log_dir()
-
-    def setup_log_dir(self, base=os.path.join(os.path.expanduser("~"), "csv_monitor")):
-        if self.enabled and dist.get_rank() == 0:
-            log_dir = os.path.join(self.output_path, self.job_name) if self.output_path else os.path.join(base, self.job_name)
-            os.makedirs(log_dir, exist_ok=True)
-            return log_dir
-
-    def write_events(self, event_list):
-        if self.enabled and dist.get_rank() == 0:
-            for event in event_list:
-                log_name, value, step = event[0], event[1], event[2]
-                header = ["step", log_name.split("/")[-1]]
-                fname = os.path.join(self.log_dir, log_name.replace("/", "_") + ".csv")
-                new = fname not in self.filenames and not os.path.exists(fname)
-                with open(fname, "a+") as f:
-                    w = csv.writer(f)
-                    if new:
-                        w.writerow(header)
-                    if fname not in self.filenames:
-                        self.filenames.append(fname)
-                    w.writerow([step, value])
-
-
 class MonitorMaster(Monitor):
 
     def __init__(self, monitor_config):
@@ -117,6 +23,9 @@ class MonitorMaster(Monitor):
         self.tb_monitor = self.wandb_monitor = self.csv_monitor = None
         self.enabled = monitor_config.enabled
         if dist.get_rank() == 0:
+            from .csv_monitor import csvMonitor
+            from .tensorboard import TensorBoardMonitor
+            from .wandb import WandbMonitor
             if monitor_config.tensorboard.enabled:
                 self.tb_monitor = TensorBoardMonitor(monitor_config.tensorboard)
             if monitor_config.wandb.enabled:
@@ -129,3 +38,16 @@ class MonitorMaster(Monitor):
             for m in (self.tb_monitor, self.wandb_monitor, self.csv_monitor):
                 if m is not None:
                     m.write_events(event_list)
+
+
+def __getattr__(name):  # the backends used to live in this module
+    if name == "TensorBoardMonitor":
+        from .tensorboard import TensorBoardMonitor
+        return TensorBoardMonitor
+    if name == "WandbMonitor":
+        from .wandb import WandbMonitor
+        return WandbMonitor
+    if name == "csvMonitor":
+        from .csv_monitor import csvMonitor
+        return csvMonitor
+    raise AttributeError(name)

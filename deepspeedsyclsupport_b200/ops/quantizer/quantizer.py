@@ -5,7 +5,7 @@ fp8 block-scaled (e4m3 + fp32 scale / 128 elements): `quantize_fp8_block`, `dequ
 the reference's `Quantizer` / `ds_quantizer` API (deepspeed/ops/quantizer/quantizer.py, runtime/quantize.py)."""
 import torch
 
-from . import native
+from .. import native
 
 native.register_sigs({
     "dsb200_fp8_block_quantize": "ppp l i p",

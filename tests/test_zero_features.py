@@ -268,3 +268,101 @@ def _offload_param_body(path, device, world_check):
 @pytest.mark.parametrize("device,world", [("cpu", 1), ("cpu", 2), ("nvme", 1)])
 def test_offload_param_matches_plain_zero3(tmp_path, device, world):
     run_distributed(_offload_param_body, world_size=world, args=(str(tmp_path), device, world))
+
+
+def test_contiguous_memory_allocator_compacts_and_repoints():
+    from deepspeedsyclsupport_b200.runtime.zero.contiguous_memory_allocator import ContiguousMemoryAllocator
+    a = ContiguousMemoryAllocator(64, torch.float32, "cpu")
+    ts = [a.allocate_tensor(16) for _ in range(4)]
+    for i, t in enumerate(ts):
+        t.fill_(i + 1)
+    p = torch.nn.Parameter(torch.empty(0))
+    a.assign_to_param(ts[3], p, 12, (3, 4))
+    a.release_tensor(ts[0])
+    a.release_tensor(ts[2])
+    assert a.total_free == 32 and a._largest_contiguous() == 16 and sorted(a.contiguous_sizes.values()) == [16, 16]
+    big = a.allocate_tensor(32)  # only possible after sliding the two live tensors together
+    big.fill_(9)
+    assert ts[1].eq(2).all() and ts[3].eq(4).all() and p.data.eq(4).all() and p.shape == (3, 4)
+    assert ts[1].data_ptr() == a.buffer.data_ptr() and p.data_ptr() == ts[3].data_ptr() and a.max_allocated == 64
+    a.release_tensor(ts[3])
+    assert p.numel() == 0 and a.total_free == 16
+    with pytest.raises(AssertionError):
+        a.allocate_tensor(17)
+
+
+def test_zero3_linear_function_matches_torch_linear():
+    from deepspeedsyclsupport_b200.runtime.zero.linear import LinearModuleForZeroStage3, zero3_linear_wrap
+    torch.manual_seed(0)
+    x = torch.randn(2, 5, 8, requires_grad=True)
+    ref = torch.nn.Linear(8, 6)
+    mod = LinearModuleForZeroStage3(8, 6)
+    mod.load_state_dict(ref.state_dict())
+    (mod(x) ** 2).sum().backward()
+    gx, gw, gb = x.grad.clone(), mod.weight.grad.clone(), mod.bias.grad.clone()
+    x.grad = None
+    (ref(x) ** 2).sum().backward()
+    assert torch.allclose(gx, x.grad, atol=1e-5) and torch.allclose(gw, ref.weight.grad, atol=1e-5) and torch.allclose(gb, ref.bias.grad, atol=1e-5)
+    assert torch.allclose(zero3_linear_wrap(x, ref.weight), torch.nn.functional.linear(x, ref.weight), atol=1e-6)
+
+
+def test_mics_group_arithmetic_and_profiler_counters():
+    from deepspeedsyclsupport_b200.runtime.zero.mics_utils import _generate_mics_config, _sizes_all_same, scale_tensors
+    from deepspeedsyclsupport_b200.runtime.zero.partitioned_param_profiler import PartitionedParameterProfiler
+    from deepspeedsyclsupport_b200.utils.timer import SynchronizedWallClockTimer
+    cfg = _generate_mics_config(world_size=16, ndev_per_node=8, shard_size=4)
+    assert cfg["shard_groups"][1] == [4, 5, 6, 7] and cfg["replicate_groups"][2] == [2, 6, 10, 14] and _sizes_all_same(cfg["shard_groups"])
+    with pytest.raises(AssertionError):
+        _generate_mics_config(world_size=10, ndev_per_node=8, shard_size=4)
+    t = [torch.ones(3), torch.full((2, ), 4.0)]
+    scale_tensors(t, 2)
+    assert t[0].tolist() == [0.5] * 3 and t[1].tolist() == [2.0, 2.0]
+    prof = PartitionedParameterProfiler(SynchronizedWallClockTimer())
+    for n in (10, 20):
+        prof.start_event("fetch")
+        prof.stop_event("fetch", n)
+    c = prof.event_counters["fetch"]
+    assert (c.count, c.num_elem) == (2, 30)
+    prof.reset_events()
+    assert prof.event_counters["fetch"].count == 0
+
+
+def _offload_body():
+    import deepspeedsyclsupport_b200 as ds  # noqa: F401
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.runtime.zero.parameter_offload import DeepSpeedZeRoOffload
+    from deepspeedsyclsupport_b200.runtime.zero.partitioned_param_coordinator import ZeRoTraceMode
+    from deepspeedsyclsupport_b200.runtime.zero.utils import assert_ints_same_as_other_ranks, get_lst_from_rank0
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.ReLU(), torch.nn.Linear(32, 8))
+    x = torch.randn(4, 16)
+    with torch.no_grad():
+        ref = model(x)
+    off = DeepSpeedZeRoOffload(model, param_persistence_threshold=0, dtype=torch.float32)
+    # parameters are sharded: nothing gathered between forwards
+    assert all(p.numel() == 0 or p.ds_status.name == "NOT_AVAILABLE" for p in model.parameters())
+    coord = off.get_param_coordinator(training=False)
+    assert coord.trace_mode == ZeRoTraceMode.RECORD
+    with torch.no_grad():
+        out = model(x)
+        coord.reset_step()
+        assert coord.is_complete_trace()
+        out2 = model(x)
+    assert torch.allclose(out, ref, atol=1e-6) and torch.allclose(out2, ref, atol=1e-6)
+    coord.fetch_sub_module(model[0], forward=True)
+    assert model[0].weight.shape == (32, 16)
+    coord.release_sub_module(model[0], backward=False)
+    off.partition_all_parameters()
+    assert get_lst_from_rank0([dist.get_rank() + 5, 7]) == [5, 7]
+    assert_ints_same_as_other_ranks([1, 2, 3])
+    if dist.get_rank() == 1:
+        with pytest.raises(RuntimeError):
+            assert_ints_same_as_other_ranks([9])
+    else:
+        assert_ints_same_as_other_ranks([0])
+    off.destroy()
+
+
+def test_zero_offload_facade_runs_sharded_inference_two_ranks():
+    from common import run_distributed
+    run_distributed(_offload_body, world_size=2)
