@@ -180,6 +180,7 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
         if cc is not None and any(v.get("shared_parameters", {}).get("enabled", False) for k, v in cc.items() if k != "layer_reduction"):
             from ..compression.scheduler import compression_scheduler
             self.compression_scheduler = compression_scheduler(self.module, cc)
+        self.quantizer = self._configure_quantization()
         if self.global_rank == 0 and self._config.dump_state:
             self._config.print("DeepSpeedEngine configuration")
         self.unflatten = torch._utils._unflatten_dense_tensors
@@ -952,6 +953,27 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
     def clip_fp32_gradients(self):
         pass  # clipping is folded into the fused optimizer step (device-side coefficient)
 
+    def _configure_quantization(self):
+        """MoQ (quantise the 16-bit weights in the optimizer step, reference engine.py:1371-1401): enabled by the compression
+        config's weight_quantization block unless it asks for quantisation in the forward pass instead."""
+        (in_forward, enabled, q_groups, q_mixed_fp16, q_change_ratio, q_type, q_rounding, q_verbose, use_kernel) = self.quantize_training()
+        if not enabled or in_forward:
+            return None
+        assert self.fp16_enabled() or self.bfloat16_enabled(), "MoQ weight quantization needs 16-bit training (fp16 or bf16)"
+        from .quantize import Quantizer
+        return Quantizer(q_groups, q_mixed_fp16, q_change_ratio, q_type, q_rounding, q_verbose, self.eigenvalue_enabled(), use_kernel,
+                         self.eigenvalue_layer_num() if self.eigenvalue_enabled() else 0)
+
+    def _moq_quantize(self, block_eigenvalue=None):
+        """Re-quantise the marked module weights after a step.  The module's 16-bit parameters are views into the flat store,
+        so they are the tensors the next forward reads; sharded (stage 3) weights are left to forward-time quantisation."""
+        if self.quantizer is None or (self.compression_scheduler is not None
+                                      and not getattr(self.compression_scheduler, "weight_quantization_enabled", True)):
+            return
+        params = [p for p in self.module.parameters() if getattr(p, "start_bits", None) and p.numel() > 0]
+        overflow = bool(getattr(self.optimizer, "overflow", False)) if self.fp16_enabled() else False
+        self.quantizer.quantize([params], overflow, self.eigenvalue_enabled(), block_eigenvalue)
+
     def _take_model_step(self, lr_kwargs, block_eigenvalue={}):
         if self.eigenvalue is not None and self.gas_boundary_ctr % max(1, self._config.eigenvalue_gas_boundary_resolution) == 0:
             # MoQ: curvature per block feeds the quantisation period of that block (engine.py:2108-2140 upstream)
@@ -960,6 +982,7 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
             if self.compression_scheduler is not None and hasattr(self.compression_scheduler, "set_block_eigenvalue"):
                 self.compression_scheduler.set_block_eigenvalue(self.block_eigenvalue)
         self.optimizer.step()
+        self._moq_quantize(getattr(self, "block_eigenvalue", None) if self.eigenvalue is not None else None)
         if self.progressive_layer_drop:
             self.progressive_layer_drop.update_state(self.global_steps)
         self._global_grad_norm = self.optimizer.get_global_grad_norm()

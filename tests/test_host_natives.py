@@ -180,3 +180,96 @@ def test_partitioned_param_swapper_roundtrip(tmp_path):
     sw.remove_partition_and_release_buffers(params[:3])
     sw.swap_in(params[3:], async_op=False)
     assert torch.equal(params[4].ds_tensor, want[4])
+
+
+def _ccl_body():
+    import deepspeedsyclsupport_b200 as ds  # noqa: F401
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.comm.ccl import CCLBackend, CCLHandler
+    be = CCLBackend(rank=dist.get_rank(), world_size=dist.get_world_size())
+    assert be.is_initialized() and be.name == "ccl" and "inference_all_reduce" in be.get_all_available_coll()
+    r, W = dist.get_rank(), dist.get_world_size()
+    t = torch.full((1000, ), float(r + 1), dtype=torch.bfloat16)
+    h = be.inference_all_reduce(t)
+    assert isinstance(h, CCLHandler) and h.is_completed()  # went through the shared-memory segment
+    assert torch.all(t == sum(range(1, W + 1)))
+    m = torch.tensor([float(r)])
+    be.all_reduce(m, op=dist.ReduceOp.MAX)  # not a sum: gloo
+    assert m.item() == W - 1
+    be.run_collective("all_reduce", tensor=t)
+    assert torch.all(t == W * sum(range(1, W + 1)))
+
+
+def test_ccl_backend_uses_shared_memory_for_sums():
+    from common import run_distributed
+    run_distributed(_ccl_body, world_size=2)
+
+
+def test_comm_utils_find_the_payload(monkeypatch):
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.comm import utils as U
+    from deepspeedsyclsupport_b200.comm.constants import COMMS_LOGGER_PROF_ALL_DEFAULT, NCCL_BACKEND
+    from deepspeedsyclsupport_b200.constants import TORCH_DISTRIBUTED_DEFAULT_PORT, default_pg_timeout
+
+    def all_reduce(tensor, op=None, group=None, async_op=False):
+        pass
+
+    def all_gather(tensor_list, tensor, group=None):
+        pass
+
+    def coalesced(tensors, group=None):
+        pass
+
+    t = torch.zeros(10, dtype=torch.bfloat16)
+    assert U.get_tensor_position(all_reduce) == 0 and U.get_tensor_position(all_gather) == 1
+    assert U.get_msg_size_from_args(all_reduce, t) == 20 and U.get_msg_size_from_args(all_reduce, tensor=t) == 20
+    assert U.get_msg_size_from_args(coalesced, [t, t.float()]) == 60
+    assert U.get_default_args(all_reduce) == {"op": None, "group": None, "async_op": False}
+    assert U.get_debug_log_name({"log_name": "x"}, "caller") == "x | [Caller Func: caller]" and U.get_debug_log_name({"log_name": "x"}, None) == "x"
+    for k in ("LOCAL_RANK", "RANK", "WORLD_SIZE", "OMPI_COMM_WORLD_LOCAL_RANK", "SLURM_LOCALID", "OMPI_COMM_WORLD_RANK", "SLURM_PROCID",
+              "OMPI_COMM_WORLD_SIZE", "SLURM_NPROCS"):
+        monkeypatch.delenv(k, raising=False)
+    assert (U.get_local_rank_from_launcher(), U.get_world_rank_from_launcher(), U.get_world_size_from_launcher()) == (0, 0, 1)
+    monkeypatch.setenv("OMPI_COMM_WORLD_RANK", "5")
+    monkeypatch.setenv("SLURM_NPROCS", "8")
+    assert U.get_world_rank_from_launcher() == 5 and U.get_world_size_from_launcher() == 8
+    assert NCCL_BACKEND == "nccl" and COMMS_LOGGER_PROF_ALL_DEFAULT is True and TORCH_DISTRIBUTED_DEFAULT_PORT == 29500
+    assert default_pg_timeout.total_seconds() > 0 and dist.ReduceOp.SUM is not None
+
+
+def test_async_tensor_swapper_and_gradient_bookkeeping(tmp_path):
+    from deepspeedsyclsupport_b200.ops.aio import aio_handle
+    from deepspeedsyclsupport_b200.runtime.swap_tensor.async_swapper import AsyncTensorSwapper
+    from deepspeedsyclsupport_b200.runtime.swap_tensor.optimizer_utils import OptimizerStateSwapInfo, OptimizerSwapper
+    h = aio_handle(block_size=4096, queue_depth=4)
+    sw = AsyncTensorSwapper(h, numel_alignment=256)
+    sw.add_buffers([torch.zeros(1024), torch.zeros(1024)])
+    torch.manual_seed(0)
+    tensors = [torch.randn(n) for n in (300, 500, 256, 900, 100, 700)]  # several buffers' worth: forces waits and reuse
+    paths = [str(tmp_path / f"t{i}.swp") for i in range(len(tensors))]
+    sw.swap_out_tensors(tensors, paths)
+    buffers = sw.release_buffers()
+    assert len(buffers) == 2 and not sw.has_buffers()
+    for t, p in zip(tensors, paths):
+        back = torch.empty(sw._io_aligned_numel(t.numel()))
+        h.sync_pread(back, p)
+        assert torch.equal(back[:t.numel()], t)
+    # optimizer-side bookkeeping: big aligned gradient slices go to disk, small ones stay in memory, both come back in place
+    p = torch.nn.Parameter(torch.zeros(4096))
+    opt = torch.optim.Adam([p])
+    osw = OptimizerSwapper(None, {"block_size": 1024, "thread_count": 1}, str(tmp_path), opt, largest_numel=4096, device="cpu", dtype=torch.float32)
+    osw.min_aio_bytes = 1024  # tiny threshold for the test
+    info = osw._create_param_swap_info(p, p.numel())
+    assert isinstance(info, OptimizerStateSwapInfo) and osw.swappable_tensor(numel=256) and not osw.swappable_tensor(numel=100)
+    grads = {0: torch.randn(1024), 1024: torch.randn(100), 2048: torch.randn(768)}
+    gsw = AsyncTensorSwapper(h, osw.numel_alignment)
+    gsw.add_buffers(buffers)
+    osw._swap_out_gradients(p, list(grads), list(grads.values()), gsw)
+    assert sorted(info.swapped_gradients) == [0, 2048] and sorted(info.unswapped_gradients) == [1024]
+    osw._flush_gradient_swapper(gsw)
+    dest = torch.zeros(4096)
+    n = osw._swap_in_gradients(h, p, dest)
+    assert n == 1024 + 100 + 768
+    for off, g in grads.items():
+        assert torch.equal(dest[off:off + g.numel()], g)
+    assert not info.unswapped_gradients

@@ -221,3 +221,17 @@ def _fallback_allreduce_body():
 def test_engine_fallback_allreduce_dense_and_sparse_two_ranks():
     from common import run_distributed
     run_distributed(_fallback_allreduce_body, world_size=2)
+
+
+def test_activation_checkpointing_config_object_and_cupy_packing():
+    from deepspeedsyclsupport_b200.runtime.activation_checkpointing.config import DeepSpeedActivationCheckpointingConfig
+    from deepspeedsyclsupport_b200.runtime.compression.cupy import CupyBackend
+    c = DeepSpeedActivationCheckpointingConfig({"activation_checkpointing": {"partition_activations": True, "number_checkpoints": 4}})
+    assert c.partition_activations is True and c.number_checkpoints == 4 and c.cpu_checkpointing is False and c.profile is False
+    d = DeepSpeedActivationCheckpointingConfig({})
+    assert d.partition_activations is False and d.number_checkpoints is None
+    be = CupyBackend()
+    signs = torch.tensor([1, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 0, 0, 0, 0], dtype=torch.bool)
+    chunks = be.compress_by_chunk(be.torch2cupy(signs), 2)
+    assert [int(c) for c in chunks] == [0b10000001, 0b11110000]
+    assert torch.equal(be.unpackbits(torch.cat(chunks)), signs) and be.cupy2torch(chunks[0]) is chunks[0]

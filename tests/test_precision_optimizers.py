@@ -67,3 +67,42 @@ def test_pld_and_eigenvalue():
     loss.backward(create_graph=True)
     ev = Eigenvalue(layer_name="linears", layer_num=2, max_iter=50, tol=1e-3).compute_eigenvalue(model)
     assert len(ev) == 4 and all(0 <= v[0] <= 1.0 for v in ev.values()) and max(v[0] for v in ev.values()) == 1.0
+
+
+def test_moq_quantizer_lowers_bits_over_periods():
+    from deepspeedsyclsupport_b200.runtime.quantize import Quantizer
+    torch.manual_seed(0)
+    w = torch.nn.Parameter(torch.randn(16, 32))
+    w.start_bits, w.target_bits, w.q_period = 8, 4, 2
+    q = Quantizer(q_groups=4, q_mixed_fp16=False, q_type="symmetric", q_rounding="nearest")
+    levels = []
+    for step in range(40):
+        w.data = torch.randn(16, 32)
+        q.quantize([[w]], overflow=False, eigenvalue_enabled=False)
+        levels.append((w.start_bits, w.data.reshape(4, -1)[0].unique().numel()))
+    bits = [b for b, _ in levels]
+    assert bits[0] == 8 and bits[-1] == 4 and sorted(set(bits), reverse=True) == [8, 7, 6, 5, 4]
+    assert bits.index(7) == 1 and bits.index(6) == 3 and bits.index(5) == 7 and bits.index(4) == 15  # the period doubles at every drop
+    assert all(n <= 2**b for b, n in levels)
+    # an eigenvalue stretches the next period: factor 1 + floor(4 * 0.5) = 3
+    v = torch.nn.Parameter(torch.randn(8, 8))
+    v.start_bits, v.target_bits, v.q_period = 8, 6, 1
+    q2 = Quantizer(q_groups=1)
+    q2.quantize([[v]], False, True, {id(v): (0.5, 0)})
+    assert v.start_bits == 7 and v.q_period == 2 * 3
+    # overflow skips the step (unless eigenvalues drive the schedule); ternary / binary forms
+    q2.quantize([[v]], True, False)
+    assert q2.qsteps == 1
+    t = Quantizer(q_groups=2).quantize_tenary(torch.randn(4, 16))
+    assert all(g.unique().numel() <= 3 for g in t.reshape(2, -1))
+    b = Quantizer(q_groups=2).quantize_binary(torch.randn(4, 16))
+    assert all(g.abs().unique().numel() == 1 for g in b.reshape(2, -1))
+    # mixed-precision blending moves from unquantised to quantised at q_change_ratio per step
+    m = torch.nn.Parameter(torch.randn(4, 8))
+    m.start_bits, m.target_bits, m.q_period = 3, 3, 100
+    qm = Quantizer(q_groups=1, q_mixed_fp16=True, q_change_ratio=0.5)
+    orig = m.data.clone()
+    qm.quantize([[m]], False, False)
+    half = m.data.clone()
+    full = Quantizer(q_groups=1).quantize_highbit(orig, 3)
+    assert torch.allclose(half, 0.5 * orig + 0.5 * full, atol=1e-6)
