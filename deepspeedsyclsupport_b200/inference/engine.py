@@ -85,7 +85,17 @@ class InferenceEngine(Module):
                                                          tp_size=config.tensor_parallel.tp_size, max_context=getattr(config, "max_out_tokens", None))
                     self._kernel_injected = True
                 else:
-                    logger.warning("replace_with_kernel_inject: unsupported architecture for kernel injection; applying AutoTP")
+                    # not a ragged-engine family (BERT, DistilBERT, GPT-Neo, BLOOM, CLIP, Megatron ...): convert layer by layer
+                    from ..module_inject.replace_module import replace_with_kernel_policies
+                    if config.dtype in (torch.float16, torch.bfloat16):
+                        self.module.to(config.dtype)
+                    n = replace_with_kernel_policies(self.module, config, getattr(self.module, "config", None))
+                    if n:
+                        self._kernel_injected = True
+                        self._layer_injected = n
+                        log_dist(f"kernel injection: {n} layers replaced by DeepSpeedTransformerInference blocks", ranks=[0])
+                    else:
+                        logger.warning("replace_with_kernel_inject: no layer policy matches this model; applying AutoTP")
             if config.tensor_parallel.tp_size > 1 and not self._kernel_injected:
                 parser_dict = AutoTP.tp_parser(model)
                 log_dist(f"AutoTP: {parser_dict}", ranks=[0])

@@ -33,6 +33,11 @@ class DeepSpeedTransformerInference(nn.Module):
             self.norm_w = nn.Parameter(torch.empty(config.hidden_size, dtype=dt, device=dev), requires_grad=False)
             self.norm_b = nn.Parameter(torch.empty(config.hidden_size, dtype=dt, device=dev), requires_grad=False)
         self.layer_past = None
+        # parallel-residual blocks whose MLP has its own LayerNorm of the block input (GPT-NeoX); GPT-J style blocks feed the
+        # MLP the same normalised input as the attention
+        self.parallel_mlp_norm = False
+        # client layers that return the bare hidden states even when caching (newer HF decoder layers): presents stay internal
+        self.tensor_output_only = False
 
     @classmethod
     def reset_cache(cls):
@@ -61,18 +66,23 @@ class DeepSpeedTransformerInference(nn.Module):
             self.attention.reset_cache()
             self._seen_epoch = epoch
         past = layer_past if layer_past is not None else past_key_value
+        if past is not None and not isinstance(past, (tuple, list)):
+            past = None  # a framework-managed cache object (HF Cache): the block keeps its own K / V, as the reference's does
         with torch.no_grad():
             hn = block_norm(input, self.norm_w, self.norm_b, cfg) if cfg.pre_layer_norm else input
             attn_out, key, value = self.attention(hn, mask, head_mask, past, get_present, encoder_hidden_states, encoder_attention_mask,
                                                   output_attentions, self.norm_w, self.norm_b, alibi)
             if not cfg.mlp_after_attn:
                 # parallel block (GPT-J / NeoX style): attention and MLP read the same normed input
-                output = input + attn_out + self.mlp.mlp_only(hn)
+                mlp_in = block_norm(input, self.mlp.attn_nw, self.mlp.attn_nb, cfg) if self.parallel_mlp_norm else hn
+                output = input + attn_out + self.mlp.mlp_only(mlp_in)
             elif cfg.pre_layer_norm:
                 output = self.mlp(attn_out, input)
             else:  # post-LN (BERT): LN_attn(x + attn) -> + mlp -> LN_out
                 output = block_norm(self.mlp(attn_out, input), self.norm_w, self.norm_b, cfg)
         output = output.to(in_dtype)
+        if self.tensor_output_only:
+            return output
         presents = (key, value)
         if get_present:
             output = (output, presents)

@@ -15,20 +15,62 @@ from .layers import LinearAllreduce, LinearLayer, LmHeadLinearAllreduce
 
 
 class ReplaceWithTensorSlicing:
+    """Copies a full (un-sharded) tensor into a destination parameter that may be this rank's tensor-parallel slice of it
+    (parity: deepspeed/module_inject/auto_tp.py:22-119).  Which dimension is cut follows from comparing the shapes; weights are
+    in nn.Linear layout [out, in]."""
 
     def __init__(self, mp_group=None, mp_size=1, out_dim=1, in_dim=0):
-        if mp_group is not None:
-            self.gpu_index = dist.get_rank(group=mp_group)
-        else:
-            self.gpu_index = 0
+        self.gpu_index = dist.get_rank(group=mp_group) if mp_group is not None else 0
         self.out_dim = out_dim
         self.in_dim = in_dim
         self.mp_size = mp_size
 
+    def merge_assert(self, dim1, dim2):
+        assert dim1 > dim2, "Merging tensors is not allowed here! Please use deepspeed load_checkpoint for merging your checkpoints " \
+            "before replacing the transformer layer with inference-kernels"
+
+    def _param(self, t):
+        return torch.nn.parameter.Parameter(t, requires_grad=False)
+
+    def strided_copy(self, dst, src, num_splits: int, int8=False, allocate_tensor=False):
+        """`src` is `num_splits` matrices stacked along dim 0 (fused QKV: 3, [gate; up]: 2): every part is cut alike, so the
+        slices of one rank stay aligned (its q heads with its k and v heads)."""
+        if src is None:
+            return src
+        if dst is not None and tuple(src.shape) == tuple(dst.shape):
+            return self._store(dst, src)
+        parts = torch.chunk(src, num_splits, dim=0)
+        if dst is not None and src.dim() > 1 and src.shape[0] == dst.shape[0]:  # row-parallel use of a fused tensor: cut the input dim
+            return self._store(dst, torch.cat([p.chunk(self.mp_size, dim=1)[self.gpu_index] for p in parts], dim=0))
+        for p in parts:
+            assert p.shape[0] % self.mp_size == 0, f"fused tensor part of {p.shape[0]} rows is not divisible by mp_size {self.mp_size}"
+        return self._store(dst, torch.cat([p.chunk(self.mp_size, dim=0)[self.gpu_index] for p in parts], dim=0))
+
+    qkv_copy = strided_copy
+
     def copy(self, dst, src, int8=False, allocate_tensor=False):
         if src is None:
             return src
-        return torch.nn.parameter.Parameter(src.chunk(self.mp_size, dim=0)[self.gpu_index].clone(), requires_grad=False)
+        if dst is None or allocate_tensor:  # no destination to compare with: column-parallel slice
+            return self._param(src.chunk(self.mp_size, dim=0)[self.gpu_index].clone())
+        if tuple(src.shape) == tuple(dst.shape):
+            return self._store(dst, src)
+        if src.dim() == 1:
+            self.merge_assert(src.shape[0], dst.shape[0])
+            return self._store(dst, src.chunk(self.mp_size, dim=0)[self.gpu_index])
+        if src.shape[0] != dst.shape[0]:  # output features differ: column-parallel
+            self.merge_assert(src.shape[0], dst.shape[0])
+            return self._store(dst, src.chunk(self.mp_size, dim=0)[self.gpu_index])
+        self.merge_assert(src.shape[1], dst.shape[1])  # input features differ: row-parallel
+        return self._store(dst, src.chunk(self.mp_size, dim=1)[self.gpu_index])
+
+    def _store(self, dst, piece):
+        if dst is None:
+            return self._param(piece.clone())
+        assert tuple(dst.shape) == tuple(piece.shape), f"slice {tuple(piece.shape)} does not fit destination {tuple(dst.shape)}"
+        with torch.no_grad():
+            dst.data.copy_(piece.to(dst.dtype))
+        return dst if isinstance(dst, torch.nn.Parameter) else self._param(dst)
 
 
 class Loading:

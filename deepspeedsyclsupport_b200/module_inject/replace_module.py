@@ -62,6 +62,86 @@ def replace_transformer_layer(orig_layer_impl, model, checkpoint_dict, config, m
     return replaced
 
 
+def _client_returns_tuple(layer):
+    """Does the client layer's forward return a tuple or the bare hidden states?  HF changed this per architecture over time and
+    the surrounding model code indexes (or does not index) the result accordingly, so the replacement must return the same kind.
+    Decided from the last `return` statement of the client's forward; None when the source is unavailable."""
+    import inspect
+    try:
+        src = inspect.getsource(type(layer).forward)
+    except (OSError, TypeError):
+        return None
+    returns = [ln.strip() for ln in src.splitlines() if ln.strip().startswith("return ")]
+    if not returns:
+        return None
+    expr, depth = returns[-1][len("return "):].split("#")[0], 0
+    for ch in expr:
+        depth += ch in "([{"
+        depth -= ch in ")]}"
+        if ch == "," and depth == 0:
+            return True
+    return expr.strip().startswith("(") and expr.strip().endswith(",)")
+
+
+def replace_with_kernel_policies(model, config, model_config):
+    """Kernel injection, layer by layer: every layer whose class a policy of `replace_policies` recognises is rebuilt as a
+    DeepSpeedTransformerInference block through that policy's container (reference replace_module.py:182-390 replace_with_policy).
+    Returns the number of converted layers."""
+    from .policy import TransformerPolicy
+    from .replace_policy import replace_policies
+    from .utils import policy_to_ds_container
+    mp_size, mp_group = config.tensor_parallel.tp_size, config.tensor_parallel.tp_group
+    mp_replace = ReplaceWithTensorSlicing(mp_group=mp_group, mp_size=mp_size)
+    TransformerPolicy.hf_model_config = model_config
+    table = {}
+    for policy_cls in replace_policies:
+        try:
+            probe = policy_cls(None)  # resolves the client layer class (imports transformers lazily)
+        except Exception:
+            continue
+        classes = policy_cls._orig_layer_class if policy_cls._orig_layer_class is not None else getattr(probe, "_orig_layer_class", None)
+        for c in (classes if isinstance(classes, (list, tuple)) else [classes]):
+            if c is not None:
+                table.setdefault(c, policy_cls)
+    converted = [0]
+
+    def build(child, policy_cls, layer_id):
+        policy = policy_cls(child, inference=True)
+        container = policy_to_ds_container(policy=policy, config=config, model_config=model_config, layer_id=layer_id, child=child)
+        container.set_tensor_parallel_config(mp_size, mp_group)
+        container.create_ds_model_config()
+        container.create_module()
+        container.initialize_tensors()
+        if getattr(container, "is_meta", False):
+            # the client lives on the meta device: the block is filled later from a checkpoint (load_checkpoint.py); start from
+            # zero biases and identity norms so tensors the checkpoint does not have (GPT-Neo / GPT-J attention biases) are neutral
+            with torch.no_grad():
+                for n, prm in container.module.named_parameters():
+                    prm.fill_(1.0) if n.endswith(("norm_w", "attn_nw")) else prm.zero_()
+        container.transpose()
+        container.apply_tensor_parallelism(mp_replace)
+        container.copy_data_to_new_module()
+        container.module.config.layer_id = layer_id
+        as_tuple = _client_returns_tuple(child)
+        if as_tuple is not None:
+            container.module.config.return_tuple = as_tuple
+            container.module.config.return_single_tuple = False
+            container.module.tensor_output_only = not as_tuple
+        return container.module
+
+    def walk(module):
+        for name, child in module.named_children():
+            policy_cls = table.get(child.__class__)
+            if policy_cls is not None:
+                setattr(module, name, build(child, policy_cls, converted[0]))
+                converted[0] += 1
+            else:
+                walk(child)
+
+    walk(model)
+    return converted[0]
+
+
 def replace_module(model, orig_class, replace_fn, _replace_policy, checkpoint=None):
     policy = {}
     if orig_class is not None:
@@ -91,6 +171,20 @@ def revert_transformer_layer(orig_layer_impl, model, config, preln=False):
 
 
 def generic_injection(module, dtype=None, enable_cuda_graph=True):
-    """Diffusers kernel injection hook of the reference (UNet/VAE/CLIP wrappers): no-op here -- the diffusion pipelines
-    run through torch; spatial bias-add kernels are exposed in ops/spatial."""
+    """Diffusers pipelines (reference replace_module.py:85-180): sub-modules matched by a generic policy (UNet, VAE) are wrapped
+    in their CUDA-graph replay wrappers; a CLIP text encoder is wrapped in DSClipEncoder.  Returns the module (pipeline) itself."""
+    from .replace_policy import generic_policies
+    policies = [p() for p in generic_policies]
+    for name in ("unet", "vae", "text_encoder"):
+        sub = getattr(module, name, None)
+        if sub is None:
+            continue
+        for policy in policies:
+            if policy.match(sub):
+                setattr(module, name, policy.apply(sub, enable_cuda_graph=enable_cuda_graph))
+                break
+        else:
+            if name == "text_encoder" and type(sub).__name__.startswith("CLIPText"):
+                from ..model_implementations.transformers.clip_encoder import DSClipEncoder
+                setattr(module, name, DSClipEncoder(sub, enable_cuda_graph=enable_cuda_graph))
     return module

@@ -319,3 +319,166 @@ def test_ds_moe_inference_block_matches_dense_mixture(mlp_type):
         coef = torch.softmax(h2 @ m.res_coef.t(), -1)
         mix = mix * coef[..., 0:1] + dense * coef[..., 1:2]
     assert torch.allclose(got, x1 + mix, atol=3e-4), (got - (x1 + mix)).abs().max()
+
+
+def _tiny_hf(name):
+    import transformers as T
+    torch.manual_seed(0)
+    if name == "bert":
+        cfg = T.BertConfig(vocab_size=90, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128, hidden_act="gelu_new",
+                           max_position_embeddings=64)
+        return T.BertModel(cfg).eval(), "encoder"
+    if name == "distilbert":
+        cfg = T.DistilBertConfig(vocab_size=90, dim=64, n_layers=2, n_heads=4, hidden_dim=128, activation="gelu", max_position_embeddings=64)
+        return T.DistilBertModel(cfg).eval(), "encoder"
+    if name == "gpt_neo":
+        cfg = T.GPTNeoConfig(vocab_size=90, hidden_size=64, num_layers=2, num_heads=4, intermediate_size=128, attention_types=[[["global", "local"], 1]],
+                             window_size=4, max_position_embeddings=64, activation_function="gelu_new")
+        return T.GPTNeoForCausalLM(cfg).eval(), "decoder"
+    if name == "gpt_neox":
+        cfg = T.GPTNeoXConfig(vocab_size=90, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, intermediate_size=128, rotary_pct=0.5,
+                              max_position_embeddings=64, hidden_act="gelu_new", use_parallel_residual=True)
+        return T.GPTNeoXForCausalLM(cfg).eval(), "decoder"
+    if name == "bloom":
+        cfg = T.BloomConfig(vocab_size=90, hidden_size=64, n_layer=2, n_head=4)
+        return T.BloomForCausalLM(cfg).eval(), "decoder"
+    if name == "opt":
+        cfg = T.OPTConfig(vocab_size=90, hidden_size=64, num_hidden_layers=2, num_attention_heads=4, ffn_dim=128, max_position_embeddings=64,
+                          word_embed_proj_dim=64)
+        return T.OPTForCausalLM(cfg).eval(), "decoder"
+    if name == "gpt2":
+        cfg = T.GPT2Config(vocab_size=90, n_embd=64, n_layer=2, n_head=4, n_positions=64, n_inner=128)
+        return T.GPT2LMHeadModel(cfg).eval(), "decoder"
+    raise KeyError(name)
+
+
+def _layer_policy_and_container(model, layer_cls_name):
+    from deepspeedsyclsupport_b200.inference.config import DeepSpeedInferenceConfig as EngineConfig
+    from deepspeedsyclsupport_b200.module_inject.auto_tp import ReplaceWithTensorSlicing
+    from deepspeedsyclsupport_b200.module_inject.replace_policy import replace_policies
+    from deepspeedsyclsupport_b200.module_inject.utils import policy_to_ds_container
+    layer = next(m for m in model.modules() if type(m).__name__ == layer_cls_name)
+    for pc in replace_policies:
+        pc(None)
+        classes = pc._orig_layer_class if isinstance(pc._orig_layer_class, (list, tuple)) else [pc._orig_layer_class]
+        if type(layer) in [c for c in classes if c is not None]:
+            policy = pc(layer, inference=True)
+            cont = policy_to_ds_container(policy=policy, config=EngineConfig(dtype=torch.float32), model_config=model.config, layer_id=0, child=layer)
+            return layer, policy, cont, ReplaceWithTensorSlicing(mp_size=1)
+    raise AssertionError(f"no policy recognises {layer_cls_name}")
+
+
+@pytest.mark.parametrize("name,layer_cls", [("bert", "BertLayer"), ("distilbert", "TransformerBlock"), ("gpt_neo", "GPTNeoBlock"),
+                                            ("gpt_neox", "GPTNeoXLayer"), ("bloom", "BloomBlock"), ("opt", "OPTDecoderLayer"), ("gpt2", "GPT2Block")])
+def test_layer_policies_read_hf_layers_into_ds_blocks(name, layer_cls):
+    """Policy + container of every architecture: the tensors land in the block with the right layout (fused [Q; K; V], [out, in])."""
+    model, _ = _tiny_hf(name)
+    layer, policy, cont, mp_replace = _layer_policy_and_container(model, layer_cls)
+    hidden, heads, eps, inter = policy.get_hidden_heads()
+    want_inter = 256 if name == "bloom" else 128  # BLOOM's MLP is always 4 x hidden
+    assert (hidden, heads, inter) == (64, 4, want_inter) and 0 < eps < 1e-3
+    cont.create_ds_model_config()
+    block = cont.create_module()
+    cont.initialize_tensors()
+    cont.transpose()
+    cont.apply_tensor_parallelism(mp_replace)
+    cont.copy_data_to_new_module()
+    a, m = block.attention, block.mlp
+    assert a.attn_qkvw.shape == (192, 64) and a.attn_ow.shape == (64, 64) and m.inter_w.shape == (want_inter, 64) and \
+        m.output_w.shape == (64, want_inter)
+    # the q rows of the fused projection are the client's query projection (after undoing per-head interleaving where it applies)
+    x = torch.randn(3, 64)
+    q_block = torch.nn.functional.linear(x, a.attn_qkvw[:64], a.attn_qkvb[:64])
+    if name in ("bert", ):
+        q_ref = layer.attention.self.query(x)
+    elif name == "distilbert":
+        q_ref = layer.attention.q_lin(x)
+    elif name == "gpt_neo":
+        q_ref = layer.attn.attention.q_proj(x)
+    elif name == "opt":
+        q_ref = layer.self_attn.q_proj(x)
+    elif name == "gpt2":
+        q_ref = layer.attn.c_attn(x)[:, :64]
+    else:  # gpt_neox / bloom: [heads, (q k v), d] interleaved in the client
+        qkv = (layer.attention.query_key_value if name == "gpt_neox" else layer.self_attention.query_key_value)(x)
+        q_ref = qkv.view(3, 4, 3, 16)[:, :, 0].reshape(3, 64)
+    assert torch.allclose(q_block, q_ref, atol=1e-5)
+    cfg = block.config
+    assert cfg.pre_layer_norm == (name not in ("bert", "distilbert")) and cfg.triangular_masking == (name not in ("bert", "distilbert", "bloom"))
+    if name == "gpt_neo":
+        assert cfg.scale_attention is False and cfg.window_size == 4
+    if name == "gpt_neox":
+        assert cfg.rotary_dim == 8 and cfg.rotate_half and not cfg.mlp_after_attn and block.parallel_mlp_norm
+    if name == "bloom":
+        assert cfg.bigscience_bloom
+    if name == "opt":
+        from deepspeedsyclsupport_b200.utils.types import ActivationFuncType
+        assert cfg.mlp_act_func_type == ActivationFuncType.ReLU
+
+
+@pytest.mark.parametrize("name", ["bert", "distilbert", "gpt_neo", "gpt_neox", "bloom"])
+def test_kernel_inject_layer_policies_match_hf_outputs(name):
+    """init_inference(replace_with_kernel_inject=True) on architectures outside the ragged engine: layers become
+    DeepSpeedTransformerInference blocks and the model's outputs stay the same."""
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.model_implementations import DeepSpeedTransformerInference
+    model, kind = _tiny_hf(name)
+    ids = torch.randint(0, 90, (2, 11))
+    with torch.no_grad():
+        ref = model(ids)
+        ref = ref.last_hidden_state if kind == "encoder" else ref.logits
+    if name == "gpt_neox":  # init_inference would pick the ragged engine for this family: drive the layer path directly
+        from deepspeedsyclsupport_b200.inference.config import DeepSpeedInferenceConfig as EngineConfig
+        from deepspeedsyclsupport_b200.module_inject.replace_module import replace_with_kernel_policies
+        assert replace_with_kernel_policies(model, EngineConfig(dtype=torch.float32), model.config) == 2
+        engine = model
+    else:
+        engine = deepspeed.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True)
+        assert len([m for m in engine.module.modules() if isinstance(m, DeepSpeedTransformerInference)]) == 2
+    with torch.no_grad():
+        out = engine(ids)
+        out = out.last_hidden_state if kind == "encoder" else out.logits
+    tol = 2e-3 if name == "distilbert" else 2e-4  # DistilBERT uses the exact GELU; the fused kernel's is the tanh form
+    assert (out - ref).abs().max() < tol * max(1.0, ref.abs().max().item()), (out - ref).abs().max()
+
+
+def test_module_quantize_inject_and_checkpoint_loading():
+    import transformers as T
+    from deepspeedsyclsupport_b200.inference.config import DeepSpeedInferenceConfig as EngineConfig
+    from deepspeedsyclsupport_b200.module_inject import (ReplaceWithTensorSlicing, load_model_with_checkpoint, module_inject,
+                                                         quantize_transformer_layer, replace_with_kernel_policies)
+    from deepspeedsyclsupport_b200.module_inject.containers import DS_GPTNEOContainer, HFGPTNEOLayerPolicy
+    from deepspeedsyclsupport_b200.module_inject.module_quantize import dequantize_weight
+    from deepspeedsyclsupport_b200.ops.transformer import DeepSpeedTransformerLayer
+    # 1. int8 group quantisation of the layers' projections
+    model, _ = _tiny_hf("bert")
+    w0 = model.encoder.layer[0].attention.self.query.weight.data.clone()
+    quantize_transformer_layer(type(model.encoder.layer[0]), model, group_size=16)
+    q = model.encoder.layer[0].attention.self.query.weight
+    assert q.dtype == torch.int8 and q.scale.numel() == 4 and (dequantize_weight(q) - w0).abs().max() <= q.scale.max() * 1.01
+    # 2. training-kernel injection: BertLayer -> DeepSpeedTransformerLayer with the same weights
+    model, _ = _tiny_hf("bert")
+    layer_cls = type(model.encoder.layer[0])
+    qw = model.encoder.layer[1].attention.self.key.weight.data.clone()
+    module_inject(layer_cls, model, model.config, micro_batch_size=2, max_seq_length=16, seed=1, preln=False, fp16=False)
+    new = model.encoder.layer[1]
+    assert isinstance(new, DeepSpeedTransformerLayer) and torch.equal(new.attn_qkvw[64:128], qw)
+    # 3. a converted model built on the meta device is filled from a checkpoint state dict through the container's load_params
+    src, _ = _tiny_hf("gpt_neo")
+    sd = {k: v.clone() for k, v in src.state_dict().items()}
+    ids = torch.randint(0, 90, (1, 9))
+    with torch.no_grad():
+        ref = src(ids).logits
+    with torch.device("meta"):
+        meta = T.GPTNeoForCausalLM(src.config).eval()
+    cfg = EngineConfig(dtype=torch.float32)
+    assert replace_with_kernel_policies(meta, cfg, meta.config) == 2
+    block = meta.transformer.h[0]
+    assert not block.attention.attn_qkvw.is_meta and meta.transformer.wte.weight.is_meta  # blocks are real, the rest still meta
+    policy = HFGPTNEOLayerPolicy(src.transformer.h[0])
+    cont = DS_GPTNEOContainer(policy=policy, config=cfg, model_config=src.config, layer_id=0, child=src.transformer.h[0])
+    load_model_with_checkpoint(meta, [sd], ReplaceWithTensorSlicing(mp_size=1), "pp", 1, container=cont)
+    assert not any(p.is_meta for p in meta.parameters())
+    with torch.no_grad():
+        out = meta(ids).logits
+    assert (out - ref).abs().max() < 2e-4 * max(1.0, ref.abs().max().item())
