@@ -2,8 +2,8 @@
 (model_implementations/transformers/ds_transformer.py:23-199): `norm_w / norm_b` (input norm), `attention` (DeepSpeedSelfAttention
 with its KV cache), `mlp` (DeepSpeedMLP with the post-attention norm).  Runs on this framework's kernels: tcgen05 GEMM for the
 projections, fused norm / bias-activation kernels; attention over the cached K / V.
-The per-architecture subclasses of the reference (ds_bert / ds_gpt / ds_opt / ds_llama2 / ds_megatron_gpt / ds_bloom) only pin
-config flags; they are provided as thin subclasses below."""
+The per-architecture subclasses of the reference (ds_bert / ds_gpt / ds_opt / ds_llama2 / ds_megatron_gpt / ds_bloom) live in
+their own modules next to this one; they differ only in what the containers configure."""
 import torch
 from torch import nn
 
@@ -91,27 +91,3 @@ class DeepSpeedTransformerInference(nn.Module):
         if cfg.return_tuple:
             return output if isinstance(output, tuple) else (output, mask)
         return output
-
-
-class DeepSpeedBERTInference(DeepSpeedTransformerInference):
-    """BERT: bidirectional, post-LN."""
-
-
-class DeepSpeedGPTInference(DeepSpeedTransformerInference):
-    """GPT-2 / GPT-Neo family."""
-
-
-class DeepSpeedMegatronGPTInference(DeepSpeedTransformerInference):
-    """Megatron-LM GPT."""
-
-
-class DeepSpeedOPTInference(DeepSpeedTransformerInference):
-    """OPT."""
-
-
-class DeepSpeedLlama2Inference(DeepSpeedTransformerInference):
-    """Llama-2 (RMSNorm, gated SiLU, rotary, GQA through config.num_kv)."""
-
-
-class DeepSpeedBloomInference(DeepSpeedTransformerInference):
-    """BLOOM (ALiBi passed through `alibi=`)."""

@@ -1,7 +1,7 @@
 """BERT encoder layer (parity: deepspeed/module_inject/containers/bert.py): bidirectional, post-LN, returns a tuple."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedBERTInference
+from ...model_implementations.transformers.ds_bert import DeepSpeedBERTInference
 from ..policy import DEFAULT_INTERMEDIATE_SIZE, TransformerPolicy
 from .base import BaseTransformerContainer
 

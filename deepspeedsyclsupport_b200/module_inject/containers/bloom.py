@@ -1,6 +1,6 @@
 """BLOOM block (parity: deepspeed/module_inject/containers/bloom.py): fused QKV per head as (q, k, v) triples, ALiBi position
 biases handed to the block by the model's forward (`alibi=`), no rotary."""
-from ...model_implementations.transformers.ds_transformer import DeepSpeedBloomInference
+from ...model_implementations.transformers.ds_bloom import DeepSpeedBloomInference
 from ..policy import TransformerPolicy, _transpose, maybe_copy
 from .base import BaseTransformerContainer
 from .features.hybrid_engine import HybridEngineContainer

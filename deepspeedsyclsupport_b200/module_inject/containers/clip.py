@@ -1,7 +1,7 @@
 """CLIP text-encoder layer (parity: deepspeed/module_inject/containers/clip.py): pre-LN, causal, separate q / k / v with biases."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedGPTInference
+from ...model_implementations.transformers.ds_gpt import DeepSpeedGPTInference
 from ..policy import TransformerPolicy
 from .base import BaseTransformerContainer
 

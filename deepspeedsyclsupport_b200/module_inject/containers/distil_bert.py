@@ -1,7 +1,7 @@
 """DistilBERT TransformerBlock (parity: deepspeed/module_inject/containers/distil_bert.py)."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedBERTInference
+from ...model_implementations.transformers.ds_bert import DeepSpeedBERTInference
 from ..policy import TransformerPolicy
 from .base import BaseTransformerContainer
 

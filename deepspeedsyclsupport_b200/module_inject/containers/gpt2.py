@@ -1,5 +1,5 @@
 """GPT-2 block (parity: deepspeed/module_inject/containers/gpt2.py): Conv1D projections ([in, out]), pre-LN, causal."""
-from ...model_implementations.transformers.ds_transformer import DeepSpeedGPTInference
+from ...model_implementations.transformers.ds_gpt import DeepSpeedGPTInference
 from ..policy import TransformerPolicy
 from .base import BaseTransformerContainer
 

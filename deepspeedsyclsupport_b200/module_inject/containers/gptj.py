@@ -2,7 +2,7 @@
 (rotate-every-two) rotary on the first rotary_dim features, no attention biases."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedGPTInference
+from ...model_implementations.transformers.ds_gpt import DeepSpeedGPTInference
 from ..policy import TransformerPolicy, maybe_copy, maybe_copy_qkv
 from .base import BaseTransformerContainer
 from .features.meta_tensor import MetaTensorContainer

@@ -1,6 +1,6 @@
 """GPT-NeoX layer (parity: deepspeed/module_inject/containers/gptneox.py): fused QKV stored per head as (q, k, v) triples,
 partial rotate-half rotary, parallel residual where the MLP reads its own LayerNorm of the block input."""
-from ...model_implementations.transformers.ds_transformer import DeepSpeedGPTInference
+from ...model_implementations.transformers.ds_gpt import DeepSpeedGPTInference
 from ..policy import TransformerPolicy, maybe_copy
 from .base import BaseTransformerContainer
 from .features.hybrid_megatron import HybridMegatronContainer

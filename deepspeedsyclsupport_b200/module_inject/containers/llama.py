@@ -2,7 +2,7 @@
 whole head, gated SiLU MLP ([gate; up] fused), grouped-query attention through num_kv."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedLlama2Inference
+from ...model_implementations.transformers.ds_llama2 import DeepSpeedLlama2Inference
 from ...utils.types import ActivationFuncType, NormType
 from ..policy import TransformerPolicy, maybe_copy, maybe_copy_geglu, maybe_copy_qkv
 from .base import BaseTransformerContainer

@@ -1,6 +1,6 @@
 """Megatron-LM GPT layer (parity: deepspeed/module_inject/containers/megatron_gpt.py).  Version 0 checkpoints name the attention
 module `attention`, later ones `self_attention`; v2 stores the fused QKV per head as (q, k, v) triples."""
-from ...model_implementations.transformers.ds_transformer import DeepSpeedMegatronGPTInference
+from ...model_implementations.transformers.ds_megatron_gpt import DeepSpeedMegatronGPTInference
 from ..policy import TransformerPolicy
 from .base import BaseTransformerContainer
 from .features.megatron import MegatronContainer

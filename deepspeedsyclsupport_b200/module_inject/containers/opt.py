@@ -2,7 +2,7 @@
 pre- or post-LN by config.do_layer_norm_before."""
 import torch
 
-from ...model_implementations.transformers.ds_transformer import DeepSpeedOPTInference
+from ...model_implementations.transformers.ds_opt import DeepSpeedOPTInference
 from ...utils.types import ActivationFuncType
 from ..policy import TransformerPolicy, maybe_copy, maybe_copy_qkv
 from .base import BaseTransformerContainer

@@ -482,3 +482,101 @@ def test_module_quantize_inject_and_checkpoint_loading():
     with torch.no_grad():
         out = meta(ids).logits
     assert (out - ref).abs().max() < 2e-4 * max(1.0, ref.abs().max().item())
+
+
+def test_diffusers_attention_and_transformer_block_match_plain_math():
+    """DeepSpeedDiffusersAttention (self and cross) and DeepSpeedDiffusersTransformerBlock against a plain restatement of the
+    diffusers BasicTransformerBlock (diffusers itself is not installed: the client module is a structural stand-in)."""
+    import torch.nn.functional as F
+    from torch import nn
+    from deepspeedsyclsupport_b200.ops.transformer.inference import (DeepSpeedDiffusersAttention, DeepSpeedDiffusersTransformerBlock,
+                                                                  DeepSpeedInferenceConfig, Diffusers2DTransformerConfig)
+    torch.manual_seed(0)
+    H, heads, ctx_w = 64, 4, 48
+    cfg = lambda: DeepSpeedInferenceConfig(hidden_size=H, heads=heads, dtype=torch.float32)
+
+    def filled(attn, cross):
+        with torch.no_grad():
+            for n, p in attn.named_parameters():
+                p.copy_(0.1 * torch.randn(p.shape))
+            if cross:
+                attn.attn_kw = nn.Parameter(0.1 * torch.randn(H, ctx_w), requires_grad=False)
+                attn.attn_vw = nn.Parameter(0.1 * torch.randn(H, ctx_w), requires_grad=False)
+        return attn
+
+    def ref_attn(a, x, context=None):
+        if context is None:
+            q, k, v = F.linear(x, a.attn_qkvw, a.attn_qkvb).chunk(3, -1)
+        else:
+            q, k, v = x @ a.attn_qw.t(), context @ a.attn_kw.t(), context @ a.attn_vw.t()
+        sp = lambda t: t.view(t.shape[0], t.shape[1], heads, -1).transpose(1, 2)
+        s = torch.softmax(sp(q) @ sp(k).transpose(-1, -2) / (H // heads)**0.5, -1) @ sp(v)
+        return s.transpose(1, 2).reshape(x.shape) @ a.attn_ow.t()
+
+    a1, a2 = filled(DeepSpeedDiffusersAttention(cfg()), False), filled(DeepSpeedDiffusersAttention(cfg()), True)
+    x, context = torch.randn(2, 10, H), torch.randn(2, 7, ctx_w)
+    assert torch.allclose(a1(x), ref_attn(a1, x) + a1.attn_ob, atol=1e-5)
+    assert torch.allclose(a2(x, context), ref_attn(a2, x, context) + a2.attn_ob, atol=1e-5)
+
+    class GEGLU(nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.proj = nn.Linear(H, 2 * 4 * H)
+
+    class Client(nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.norm1, self.norm2, self.norm3 = nn.LayerNorm(H), nn.LayerNorm(H), nn.LayerNorm(H)
+            self.attn1, self.attn2 = a1, a2
+            self.ff = nn.Module()
+            self.ff.net = nn.ModuleList([GEGLU(), nn.Dropout(0.0), nn.Linear(4 * H, H)])
+
+    client = Client()
+    with torch.no_grad():
+        for norm in (client.norm1, client.norm2, client.norm3):
+            norm.weight.copy_(1 + 0.1 * torch.randn(H))
+            norm.bias.copy_(0.1 * torch.randn(H))
+    block = DeepSpeedDiffusersTransformerBlock(client, Diffusers2DTransformerConfig())
+    assert a1.do_out_bias is False and block.attn_1_bias is a1.attn_ob
+    got = block(x, context=context)
+    h = x + ref_attn(a1, client.norm1(x)) + a1.attn_ob
+    h = h + ref_attn(a2, client.norm2(h), context) + a2.attn_ob
+    value, gate = client.ff.net[0].proj(client.norm3(h)).chunk(2, -1)
+    want = h + client.ff.net[2](F.gelu(gate) * value)
+    assert torch.allclose(got, want, atol=1e-4), (got - want).abs().max()
+
+
+def test_op_binding_ops_compose_into_a_pre_ln_block():
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    from deepspeedsyclsupport_b200.ops.transformer.inference.op_binding import (GELUGemmOp, MLPGemmOp, QKVGemmOp, ResidualAddOp, SoftmaxContextOp,
+                                                                             SoftmaxOp, VectorMatMulOp)
+    import torch.nn.functional as F
+    torch.manual_seed(0)
+    H, heads = 32, 4
+    cfg = DeepSpeedInferenceConfig(hidden_size=H, heads=heads, dtype=torch.float32, layer_norm_eps=1e-5)
+    x = torch.randn(2, 6, H)
+    g, b = 1 + 0.1 * torch.randn(H), 0.1 * torch.randn(H)
+    wqkv, bqkv, wo = 0.1 * torch.randn(3 * H, H), 0.1 * torch.randn(3 * H), 0.1 * torch.randn(H, H)
+    w1, b1, w2, b2 = 0.1 * torch.randn(4 * H, H), 0.1 * torch.randn(4 * H), 0.1 * torch.randn(H, 4 * H), 0.1 * torch.randn(H)
+    qkv, normed = QKVGemmOp(cfg)(x, wqkv, bqkv, g, b)
+    assert torch.allclose(normed, F.layer_norm(x, (H, ), g, b, 1e-5), atol=1e-5) and torch.allclose(qkv, F.linear(normed, wqkv, bqkv), atol=1e-5)
+    sc = SoftmaxContextOp(cfg)
+    ctx, k, v = sc(qkv, None, heads, heads, (H // heads)**-0.25, False, 0, 1, None)
+    q_, k_, v_ = [t.view(2, 6, heads, -1).transpose(1, 2) for t in qkv.chunk(3, -1)]
+    scores = q_ @ k_.transpose(-1, -2) / (H // heads)**0.5
+    probs = SoftmaxOp(cfg)(scores, None, None, True)
+    assert torch.allclose(ctx, (probs @ v_).transpose(1, 2).reshape(2, 6, H), atol=1e-5) and k.shape == (2, heads, 6, H // heads)
+    attn = VectorMatMulOp(cfg)(ctx, wo)
+    mlp_out, res = MLPGemmOp(cfg)(attn, x, w1, w2, None, b1, g, b)
+    assert torch.allclose(res, attn + x, atol=1e-6)
+    want_mlp = F.linear(F.gelu(F.linear(F.layer_norm(res, (H, ), g, b, 1e-5), w1, b1), approximate="tanh"), w2)
+    assert torch.allclose(mlp_out, want_mlp, atol=1e-5)
+    assert torch.allclose(GELUGemmOp(cfg)(normed, w1, b1, w2), F.linear(F.gelu(F.linear(normed, w1, b1), approximate="tanh"), w2), atol=1e-5)
+    out = ResidualAddOp(cfg)(mlp_out, res, True, final_bias=b2)
+    assert torch.allclose(out, mlp_out + res + b2, atol=1e-6)
+    step = torch.randn(2, 1, H)  # a decode step reuses the layer's cached K / V
+    qkv1, _ = QKVGemmOp(cfg)(step, wqkv, bqkv, g, b)
+    _, k1, _ = sc(qkv1, None, heads, heads, (H // heads)**-0.25, False, 0, 1, None)
+    assert k1.shape[2] == 7
