@@ -810,3 +810,40 @@ def test_fused_gemm_allreduce_single_rank(shape):
         # the partial is rounded to bf16 before the reduction (as it is when it crosses NVLink)
         want = ref.bfloat16().float() + (res.float() if res is not None else 0)
         assert (out - want).abs().max() <= 1e-2 * want.abs().max()
+
+
+def test_grouped_experts_training_path_gpu(monkeypatch):
+    """MoE training experts on the grouped tcgen05 GEMM (forward and dgrad) against the per-expert loop, bf16."""
+    from torch import nn
+    from deepspeedsyclsupport_b200.moe.experts import Experts
+
+    class MLP(nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.up, self.down = nn.Linear(256, 512), nn.Linear(512, 256)
+
+        def forward(self, x):
+            return self.down(torch.nn.functional.gelu(self.up(x)))
+
+    torch.manual_seed(0)
+    grouped = Experts(MLP(), num_local_experts=4).to(_dev(), torch.bfloat16)
+    assert grouped._grouped_act is not None
+    with torch.no_grad():
+        for e in grouped.deepspeed_experts:
+            for p in e.parameters():
+                p.add_(0.05 * torch.randn_like(p))
+    monkeypatch.setenv("DSB200_GROUPED_EXPERTS", "0")
+    loop = Experts(MLP(), num_local_experts=4).to(_dev(), torch.bfloat16)
+    loop.load_state_dict(grouped.state_dict())
+    x = torch.randn(1, 4, 150, 256, device=_dev(), dtype=torch.bfloat16, requires_grad=True)  # 150 rows per expert: partial tiles
+    x2 = x.detach().clone().requires_grad_(True)
+    w = torch.randn_like(x)
+    yg, yl = grouped(x), loop(x2)
+    (yg * w).sum().backward()
+    (yl * w).sum().backward()
+    scale = yl.float().abs().max()
+    assert (yg.float() - yl.float()).abs().max() <= 2e-2 * scale
+    assert (x.grad.float() - x2.grad.float()).abs().max() <= 3e-2 * x2.grad.float().abs().max()
+    for (n, p), (_, q) in zip(grouped.named_parameters(), loop.named_parameters()):
+        assert (p.grad.float() - q.grad.float()).abs().max() <= 3e-2 * q.grad.float().abs().max() + 1e-3, n

@@ -84,3 +84,64 @@ def _ep_body():
 
 def test_moe_expert_parallel_two_ranks():
     run_distributed(_ep_body, world_size=2)
+
+
+def test_grouped_experts_match_the_expert_loop_forward_and_backward(monkeypatch):
+    """Two-layer MLP experts are detected by probing and run as grouped GEMMs; outputs and every gradient equal the per-expert
+    loop.  Experts the probe cannot prove (extra parameters, dropout) keep the loop."""
+    from torch import nn
+    from deepspeedsyclsupport_b200.moe.experts import Experts
+
+    class MLP(nn.Module):
+
+        def __init__(self, act):
+            super().__init__()
+            self.up, self.down, self.act = nn.Linear(16, 40), nn.Linear(40, 16), act
+
+        def forward(self, x):
+            return self.down(self.act(self.up(x)))
+
+    torch.manual_seed(0)
+    for act, name in ((nn.GELU(), "gelu"), (nn.ReLU(), "relu"), (nn.SiLU(), "silu")):
+        grouped = Experts(MLP(act), num_local_experts=3)
+        assert grouped._grouped_act is not None and grouped._grouped_act[0] == name
+        with torch.no_grad():
+            for e in grouped.deepspeed_experts:  # deepcopy made the experts identical: make them differ
+                for p in e.parameters():
+                    p.add_(0.1 * torch.randn_like(p))
+        monkeypatch.setenv("DSB200_GROUPED_EXPERTS", "0")
+        loop = Experts(MLP(act), num_local_experts=3)
+        monkeypatch.delenv("DSB200_GROUPED_EXPERTS")
+        assert loop._grouped_act is None
+        loop.load_state_dict(grouped.state_dict())
+        x = torch.randn(2, 3, 5, 16, requires_grad=True)  # [ep, local experts, capacity, model dim]
+        x2 = x.detach().clone().requires_grad_(True)
+        w = torch.randn(2, 3, 5, 16)
+        (grouped(x) * w).sum().backward()
+        (loop(x2) * w).sum().backward()
+        assert torch.allclose(grouped(x), loop(x2), atol=1e-5) and torch.allclose(x.grad, x2.grad, atol=1e-5)
+        for (n, p), (_, q) in zip(grouped.named_parameters(), loop.named_parameters()):
+            assert torch.allclose(p.grad, q.grad, atol=1e-5), n
+
+    class WithNorm(MLP):
+
+        def __init__(self):
+            super().__init__(nn.GELU())
+            self.norm = nn.LayerNorm(16)
+
+        def forward(self, x):
+            return super().forward(self.norm(x))
+
+    class WithDropout(MLP):
+
+        def __init__(self):
+            super().__init__(nn.GELU())
+            self.drop = nn.Dropout(0.1)
+
+    class Residual(MLP):
+
+        def forward(self, x):
+            return x + super().forward(x)
+
+    for other in (WithNorm(), WithDropout(), Residual(nn.GELU())):
+        assert Experts(other, num_local_experts=2)._grouped_act is None
