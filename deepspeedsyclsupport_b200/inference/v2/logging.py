@@ -1,14 +1,14 @@
-"""Logger of the FastGen engine (parity: inference/v2/logging.py)."""
+"""Logger of the FastGen engine (parity: inference/v2/logging.py): one process-wide logger, created on first use."""
 import logging
 
 from ...utils.logging import LoggerFactory
 
-inf_logger = None
+_INSTANCE = []
 
 
 def inference_logger(level: int = logging.INFO) -> logging.Logger:
-    global inf_logger
-    if inf_logger is None:
-        inf_logger = LoggerFactory.create_logger(name="DS-Inference", level=level)
-        inf_logger.debug("Inference logger created.")
-    return inf_logger
+    """`level` only matters for the call that creates the logger."""
+    if not _INSTANCE:
+        _INSTANCE.append(LoggerFactory.create_logger(name="DS-Inference", level=level))
+        _INSTANCE[0].debug("Inference logger created.")
+    return _INSTANCE[0]

@@ -1,6 +1,8 @@
-"""(parity: inference/v2/modules/configs/attention_configs.py:16-110)"""
+"""Configuration of the self-attention modules (parity: inference/v2/modules/configs/attention_configs.py:16-110)."""
 from enum import Enum
 from typing import Dict, Optional
+
+from pydantic import model_validator
 
 from .....runtime.config_utils import DeepSpeedConfigModel
 from ...inference_utils import DtypeEnum
@@ -40,3 +42,19 @@ class DSSelfAttentionConfig(DSModuleConfig):
     masking_args: Dict = {}
     positional_embedding_type: PositionalEmbeddingType = PositionalEmbeddingType.none
     positional_embedding_config: Optional[RotateHalfConfig] = None
+
+    @model_validator(mode="after")
+    def _consistent_heads(self):
+        if self.n_heads_q <= 0 or self.n_heads_kv <= 0 or self.head_size <= 0:
+            raise ValueError("head counts and head size must be positive")
+        if self.n_heads_q % self.n_heads_kv != 0:
+            raise ValueError(f"n_heads_q ({self.n_heads_q}) must be a multiple of n_heads_kv ({self.n_heads_kv})")
+        rc = self.positional_embedding_config
+        if rc is not None and rc.rotate_dim is not None and not (0 < rc.rotate_dim <= self.head_size and rc.rotate_dim % 2 == 0):
+            raise ValueError(f"rotate_dim must be even and at most head_size ({self.head_size}), got {rc.rotate_dim}")
+        return self
+
+    @property
+    def group_size(self) -> int:
+        """query heads served by one key/value head"""
+        return self.n_heads_q // self.n_heads_kv

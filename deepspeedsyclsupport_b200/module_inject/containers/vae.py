@@ -1,17 +1,30 @@
-"""diffusers AutoencoderKL -> DSVAE (parity: deepspeed/module_inject/containers/vae.py)."""
+"""diffusers AutoencoderKL -> DSVAE, the CUDA-graph replay wrapper around encode / decode (parity:
+deepspeed/module_inject/containers/vae.py).  The VAE is wrapped whole: there are no per-layer tensors to extract."""
 from ..policy import DSPolicy
+
+
+def _autoencoder_class():
+    """diffusers moved AutoencoderKL between modules across releases; None when diffusers is not installed."""
+    try:
+        import diffusers
+    except ImportError:
+        return None
+    for path in ("vae", "autoencoder_kl", "autoencoders.autoencoder_kl"):
+        mod = diffusers.models
+        try:
+            for part in path.split("."):
+                mod = getattr(mod, part)
+            return mod.AutoencoderKL
+        except AttributeError:
+            continue
+    return getattr(diffusers, "AutoencoderKL", None)
 
 
 class VAEPolicy(DSPolicy):
 
     def __init__(self):
         super().__init__()
-        try:
-            import diffusers
-            self._orig_layer_class = (diffusers.models.vae.AutoencoderKL if hasattr(diffusers.models, "vae") else
-                                      diffusers.models.autoencoder_kl.AutoencoderKL)
-        except (ImportError, AttributeError):
-            self._orig_layer_class = None
+        self._orig_layer_class = _autoencoder_class()
 
     def match(self, module):
         return self._orig_layer_class is not None and isinstance(module, self._orig_layer_class)
@@ -25,4 +38,4 @@ class VAEPolicy(DSPolicy):
         return DSVAE(module, enable_cuda_graph=enable_cuda_graph)
 
     def attention(self, client_module):
-        """The VAE is wrapped whole; it has no per-layer tensors to extract."""
+        return None

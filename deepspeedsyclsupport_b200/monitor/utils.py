@@ -1,17 +1,19 @@
-"""(parity: deepspeed/monitor/utils.py)"""
+"""Availability checks of the optional monitoring back ends (parity: deepspeed/monitor/utils.py)."""
+import importlib
+
+
+def _require(module: str, hint: str):
+    try:
+        return importlib.import_module(module)
+    except ImportError:
+        print(hint)
+        raise
 
 
 def check_tb_availability():
-    try:
-        import tensorboard  # noqa: F401
-    except ImportError:
-        print('If you want to use tensorboard logging, please `pip install tensorboard`')
-        raise
+    _require("tensorboard", "If you want to use tensorboard logging, please `pip install tensorboard`")
 
 
 def check_wandb_availability():
-    try:
-        import wandb  # noqa: F401
-    except ImportError:
-        print('If you want to use wandb logging, please `pip install wandb` and follow the instructions at https://docs.wandb.ai/quickstart')
-        raise
+    _require("wandb", "If you want to use wandb logging, please `pip install wandb` and follow the instructions at "
+             "https://docs.wandb.ai/quickstart")

@@ -1,37 +1,22 @@
-"""(parity: deepspeed/profiling/constants.py)"""
-FLOPS_PROFILER_FORMAT = '''
-flops profiler should be enabled as:
-"session_params": {
-  "flops_profiler": {
-    "enabled": true,
+"""Key names and defaults of the `flops_profiler` config section (parity: deepspeed/profiling/constants.py).  The names are
+generated from one table so a key and its default cannot drift apart: FLOPS_PROFILER_<KEY> is the key string and
+FLOPS_PROFILER_<KEY>_DEFAULT its default value."""
+FLOPS_PROFILER = "flops_profiler"
+
+_SECTION_DEFAULTS = {
+    "enabled": False,
     "recompute_fwd_factor": 0.0,
     "profile_step": 1,
     "module_depth": -1,
-    "top_modules": 3,
-    "detailed": true,
-    "output_file": null
-    }
+    "top_modules": 1,
+    "detailed": True,
+    "output_file": None,
 }
-'''
-FLOPS_PROFILER = "flops_profiler"
 
-FLOPS_PROFILER_ENABLED = "enabled"
-FLOPS_PROFILER_ENABLED_DEFAULT = False
+for _key, _default in _SECTION_DEFAULTS.items():
+    globals()[f"FLOPS_PROFILER_{_key.upper()}"] = _key
+    globals()[f"FLOPS_PROFILER_{_key.upper()}_DEFAULT"] = _default
+del _key, _default
 
-FLOPS_PROFILER_RECOMPUTE_FWD_FACTOR = "recompute_fwd_factor"
-FLOPS_PROFILER_RECOMPUTE_FWD_FACTOR_DEFAULT = 0.0
-
-FLOPS_PROFILER_PROFILE_STEP = "profile_step"
-FLOPS_PROFILER_PROFILE_STEP_DEFAULT = 1
-
-FLOPS_PROFILER_MODULE_DEPTH = "module_depth"
-FLOPS_PROFILER_MODULE_DEPTH_DEFAULT = -1
-
-FLOPS_PROFILER_TOP_MODULES = "top_modules"
-FLOPS_PROFILER_TOP_MODULES_DEFAULT = 1
-
-FLOPS_PROFILER_DETAILED = "detailed"
-FLOPS_PROFILER_DETAILED_DEFAULT = True
-
-FLOPS_PROFILER_OUTPUT_FILE = "output_file"
-FLOPS_PROFILER_OUTPUT_FILE_DEFAULT = None
+FLOPS_PROFILER_FORMAT = "flops profiler should be enabled as:\n\"session_params\": {\n  \"flops_profiler\": {\n" + "".join(
+    f"    \"{k}\": {'null' if v is None else str(v).lower() if isinstance(v, bool) else v},\n" for k, v in _SECTION_DEFAULTS.items()) + "  }\n}\n"

@@ -1,21 +1,13 @@
-"""(parity: deepspeed/runtime/swap_tensor/constants.py)"""
-AIO_FORMAT = '''
-"aio": {
-  "block_size": 1048576,
-  "queue_depth": 8,
-  "thread_count": 1,
-  "single_submit": false,
-  "overlap_events": true
-}
-'''
+"""Key names and defaults of the `aio` config section (parity: deepspeed/runtime/swap_tensor/constants.py), generated from the
+table the config reader itself uses (aio_config.AIO_DEFAULT_DICT): AIO_<KEY> is the key string, AIO_<KEY>_DEFAULT its default."""
+import json
+
+from .aio_config import AIO_DEFAULT_DICT
+
 AIO = "aio"
-AIO_BLOCK_SIZE = "block_size"
-AIO_BLOCK_SIZE_DEFAULT = 1048576
-AIO_QUEUE_DEPTH = "queue_depth"
-AIO_QUEUE_DEPTH_DEFAULT = 8
-AIO_THREAD_COUNT = "thread_count"
-AIO_THREAD_COUNT_DEFAULT = 1
-AIO_SINGLE_SUBMIT = "single_submit"
-AIO_SINGLE_SUBMIT_DEFAULT = False
-AIO_OVERLAP_EVENTS = "overlap_events"
-AIO_OVERLAP_EVENTS_DEFAULT = True
+for _key, _default in AIO_DEFAULT_DICT.items():
+    globals()[f"AIO_{_key.upper()}"] = _key
+    globals()[f"AIO_{_key.upper()}_DEFAULT"] = _default
+del _key, _default
+
+AIO_FORMAT = '"aio": ' + json.dumps(AIO_DEFAULT_DICT, indent=2)

@@ -1,55 +1,55 @@
-"""Counters of parameter-movement events (parity: deepspeed/runtime/zero/partitioned_param_profiler.py:10-63)."""
-from dataclasses import dataclass
-
+"""Counts and times parameter-movement events of ZeRO stage 3 -- fetches, releases, gathers -- by event name (parity:
+deepspeed/runtime/zero/partitioned_param_profiler.py:10-63).  A profiler without timers is inert, so call sites need no
+`if profiling:` guards."""
 from ...utils.logging import log_dist
 
 
+class _Event:
+    __slots__ = ("name", "count", "num_elem")
+
+    def __init__(self, name):
+        self.name, self.count, self.num_elem = name, 0, 0
+
+    def reset(self):
+        self.count = self.num_elem = 0
+
+    def increment(self, numel):
+        self.count += 1
+        self.num_elem += numel
+
+    def __repr__(self):
+        return f"{self.name}: count = {self.count}, numel = {self.num_elem}"
+
+
 class PartitionedParameterProfiler(object):
-
-    @dataclass
-    class EventCounter:
-        name: str
-        count: int
-        num_elem: int
-
-        def reset(self):
-            self.count = 0
-            self.num_elem = 0
-
-        def increment(self, numel):
-            self.count += 1
-            self.num_elem += numel
+    EventCounter = _Event
 
     def __init__(self, timers):
         self.timers = timers
         self.event_counters = {}
 
+    @property
+    def _active(self):
+        return self.timers is not None
+
     def reset_events(self):
-        for c in self.event_counters.values():
-            c.reset()
+        for event in self.event_counters.values():
+            event.reset()
 
     def start_event(self, name):
-        if self.timers is None:
-            return
-        if name not in self.event_counters:
-            self.event_counters[name] = self.EventCounter(name=name, count=0, num_elem=0)
-        self.timers(name).start()
+        if self._active:
+            self.event_counters.setdefault(name, _Event(name))
+            self.timers(name).start()
 
     def stop_event(self, name, num_elem):
-        if self.timers is None:
-            return
-        assert name in self.event_counters, f"unknown event {name}"
-        self.event_counters[name].increment(num_elem)
-        self.timers(name).stop()
-
-    def _log_timers(self):
-        if self.timers is not None:
-            self.timers.log(names=list(self.event_counters.keys()))
-
-    def _log_event_counters(self):
-        for c in self.event_counters.values():
-            log_dist(f"{c.name}: count = {c.count}, numel = {c.num_elem}", ranks=[0])
+        if self._active:
+            if name not in self.event_counters:
+                raise AssertionError(f"stop_event('{name}') without a matching start_event")
+            self.event_counters[name].increment(num_elem)
+            self.timers(name).stop()
 
     def log_events(self):
-        self._log_event_counters()
-        self._log_timers()
+        for event in self.event_counters.values():
+            log_dist(repr(event), ranks=[0])
+        if self._active and self.event_counters:
+            self.timers.log(names=list(self.event_counters))
