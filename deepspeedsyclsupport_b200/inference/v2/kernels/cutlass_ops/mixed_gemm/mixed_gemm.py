@@ -1,0 +1,3 @@
+"""(parity: inference/v2/kernels/cutlass_ops/mixed_gemm/mixed_gemm.py)  The kernel objects of this group are defined together in
+kernels/cutlass_ops/__init__.py; this module keeps the reference import path."""
+from .. import MixedGEMM  # noqa: F401

@@ -1,0 +1,3 @@
+"""(parity: inference/v2/kernels/cutlass_ops/moe_gemm/mixed_moe_gemm.py)  The kernel objects of this group are defined together in
+kernels/cutlass_ops/__init__.py; this module keeps the reference import path."""
+from .. import MixedMoEGEMM  # noqa: F401

@@ -1,0 +1,3 @@
+"""(parity: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.py)  The kernel objects of this group are defined together in
+kernels/ragged_ops/__init__.py; this module keeps the reference import path."""
+from .. import BlockedFlashAttn  # noqa: F401
