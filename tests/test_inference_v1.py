@@ -580,3 +580,25 @@ def test_op_binding_ops_compose_into_a_pre_ln_block():
     qkv1, _ = QKVGemmOp(cfg)(step, wqkv, bqkv, g, b)
     _, k1, _ = sc(qkv1, None, heads, heads, (H // heads)**-0.25, False, 0, 1, None)
     assert k1.shape[2] == 7
+
+
+def _tp_layer_policy_body():
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200.model_implementations import DeepSpeedTransformerInference
+    for name in ("gpt_neo", "bert"):
+        model, kind = _tiny_hf(name)  # same seed on both ranks: identical weights
+        ids = torch.randint(0, 90, (2, 11), generator=torch.Generator().manual_seed(5))
+        with torch.no_grad():
+            ref = model(ids)
+            ref = ref.last_hidden_state if kind == "encoder" else ref.logits
+        engine = deepspeed.init_inference(model, dtype=torch.float32, replace_with_kernel_inject=True, tensor_parallel={"tp_size": 2})
+        blocks = [m for m in engine.module.modules() if isinstance(m, DeepSpeedTransformerInference)]
+        assert len(blocks) == 2 and blocks[0].attention.attn_qkvw.shape == (96, 64) and blocks[0].mlp.output_w.shape == (64, 64)
+        with torch.no_grad():
+            out = engine(ids)
+            out = out.last_hidden_state if kind == "encoder" else out.logits
+        assert (out - ref).abs().max() < 3e-4 * max(1.0, ref.abs().max().item()), (name, (out - ref).abs().max())
+
+
+def test_kernel_inject_layer_policies_tensor_parallel_two_ranks():
+    run_distributed(_tp_layer_policy_body, world_size=2)
