@@ -42,8 +42,9 @@ struct Params {
   int rank, world;
   __nv_bfloat16* out;
   int ldo;
-  const __nv_bfloat16* residual;  // optional [M][N] added once (same on every rank)
+  const __nv_bfloat16* residual;  // optional, added once (same on every rank); indexed like `out`
   int ldr;
+  int row_lo, row_hi;  // rows this rank reduces and writes: [0, M) = all-reduce, its own slice = reduce-scatter; out row = r - row_lo
 };
 
 __device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) {
@@ -89,7 +90,7 @@ __device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int
       const int v = v0 + u * RED_THREADS;
       const int r = v / VEC_PER_ROW, cv = v - r * VEC_PER_ROW;
       const int gr = m0 + r, gc = n0 + cv * 8;
-      ok[u] = gr < p.M && gc < p.N;
+      ok[u] = gr < p.row_hi && gr >= p.row_lo && gc < p.N;
       off[u] = ok[u] ? static_cast<uint32_t>((static_cast<size_t>(gr) * p.N + gc) >> 3) : 0u;
     }
 #pragma unroll
@@ -112,13 +113,14 @@ __device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int
       const int v = v0 + u * RED_THREADS;
       const int r = v / VEC_PER_ROW, cv = v - r * VEC_PER_ROW;
       const int gr = m0 + r, gc = n0 + cv * 8;
-      if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(gr) * p.ldr + gc));
+      const size_t lr = static_cast<size_t>(gr - p.row_lo);
+      if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + lr * p.ldr + gc));
       uint4 o;
       o.x = pack_bf16x2(a[0], a[1]);
       o.y = pack_bf16x2(a[2], a[3]);
       o.z = pack_bf16x2(a[4], a[5]);
       o.w = pack_bf16x2(a[6], a[7]);
-      *reinterpret_cast<uint4*>(p.out + static_cast<size_t>(gr) * p.ldo + gc) = o;
+      *reinterpret_cast<uint4*>(p.out + lr * p.ldo + gc) = o;
     }
   }
 }
@@ -128,17 +130,18 @@ __device__ __noinline__ void reduce_tile_any(const Params& p, int m0, int n0, in
   for (int v = rt; v < BM * (BN / 8); v += RED_THREADS) {
     const int r = v / (BN / 8), cv = v - r * (BN / 8);
     const int gr = m0 + r, gc = n0 + cv * 8;
-    if (gr >= p.M || gc >= p.N) continue;
+    if (gr >= p.row_hi || gr < p.row_lo || gc >= p.N) continue;
     const size_t off = p.part_off + (static_cast<size_t>(gr) * p.N + gc) * 2;
+    const size_t lr = static_cast<size_t>(gr - p.row_lo);
     float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int k = 0; k < p.world; ++k) acc_bf16x8(a, ld_peer_v4(static_cast<const uint8_t*>(p.peer[(k + p.rank) % p.world]) + off));
-    if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + static_cast<size_t>(gr) * p.ldr + gc));
+    if (p.residual != nullptr) acc_bf16x8(a, *reinterpret_cast<const uint4*>(p.residual + lr * p.ldr + gc));
     uint4 o;
     o.x = pack_bf16x2(a[0], a[1]);
     o.y = pack_bf16x2(a[2], a[3]);
     o.z = pack_bf16x2(a[4], a[5]);
     o.w = pack_bf16x2(a[6], a[7]);
-    *reinterpret_cast<uint4*>(p.out + static_cast<size_t>(gr) * p.ldo + gc) = o;
+    *reinterpret_cast<uint4*>(p.out + lr * p.ldo + gc) = o;
   }
 }
 
@@ -304,6 +307,7 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       int m_blk, n_blk;
       gemm::tile_coords(tile, p.tiles_m, p.tiles_n, m_blk, n_blk);
       const int m0 = m_blk * BM, n0 = n_blk * BN;
+      if (m0 >= p.row_hi || m0 + BM <= p.row_lo) continue;  // reduce-scatter: another rank reduces this tile (uniform per CTA)
       if (rt < p.world) {
         const uint32_t* f = reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(p.peer[rt]) + p.flag_off) + tile;
         uint32_t spins = 0;
@@ -342,11 +346,12 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 //   * two partial areas of M*N*2 bytes (16-byte aligned): pass part_off = area[epoch & 1]
 //   * flags: ceil(M/128)*ceil(N/256) uint32, zero-initialised once (flag_off, 4-byte aligned)
 // and passes the same, strictly increasing `epoch` (>= 1) on every rank for each call.  N must be a multiple of 8.
-DSB_EXPORT int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
-                                   unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo,
-                                   int ldr, int rank, int world, int max_ctas, cudaStream_t stream) {
+static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off, unsigned int epoch,
+                          void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo, int ldr, int rank, int world,
+                          int row_lo, int row_hi, int max_ctas, cudaStream_t stream) {
   using namespace dsb;
   namespace G = gemm_ar;
+  DSB_REQUIRE(row_lo >= 0 && row_lo <= row_hi && row_hi <= M, "gemm_ar: rows [%d, %d) outside [0, %d)", row_lo, row_hi, M);
   DSB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_ar: empty problem M=%d N=%d K=%d", M, N, K);
   DSB_REQUIRE(world >= 1 && world <= G::MAX_RANKS && rank >= 0 && rank < world, "gemm_ar: rank %d / world %d", rank, world);
   DSB_REQUIRE(N % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldo % 8 == 0, "gemm_ar: N, lda, ldb, ldo must be multiples of 8");
@@ -382,6 +387,8 @@ DSB_EXPORT int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* pe
   p.ldo = ldo;
   p.residual = static_cast<const __nv_bfloat16*>(residual);
   p.ldr = ldr;
+  p.row_lo = row_lo;
+  p.row_hi = row_hi;
   int grid = p.tiles_m * p.tiles_n;
   int cap = num_sms();
   if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;
@@ -389,4 +396,22 @@ DSB_EXPORT int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* pe
   G::gemm_ar_kernel<<<grid, G::NUM_THREADS, G::SMEM_TOTAL, stream>>>(tmA, tmB, tmP, p);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
+                                   unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo,
+                                   int ldr, int rank, int world, int max_ctas, cudaStream_t stream) {
+  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world, 0, M, max_ctas,
+                        stream);
+}
+
+// GEMM -> reduce-scatter over rows (sequence-parallel tensor parallelism): same kernel, but this rank reduces and writes only rows
+// [row_lo, row_hi) of the sum -- out and residual are [row_hi - row_lo][N].  Every rank still publishes its whole partial (the
+// owners of the other rows need it); the row ranges of the ranks must cover [0, M) and every rank must own at least one row.
+DSB_EXPORT int dsb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
+                                   unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo,
+                                   int ldr, int rank, int world, int row_lo, int row_hi, int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(row_hi > row_lo, "gemm_rs: rank %d owns no rows", rank);
+  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world, row_lo, row_hi,
+                        max_ctas, stream);
 }

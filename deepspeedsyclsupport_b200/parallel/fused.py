@@ -15,6 +15,7 @@ from ..ops.gemm import gemm
 native.register_sigs({
     "dsb200_gemm_ag_bf16": "ppp iiiii p ll p i p",
     "dsb200_gemm_ar_bf16": "ppp ll i pp iii iiii ii i p",
+    "dsb200_gemm_rs_bf16": "ppp ll i pp iii iiii ii ii i p",
 })
 
 
@@ -69,19 +70,36 @@ class FusedGemmAllReduce(object):
         part = (max_m * n * 2 + 255) // 256 * 256
         return 2 * part + ((max_m + 127) // 128) * ((n + 255) // 256) * 4
 
-    def __call__(self, x, w_shard, residual=None, out=None, max_ctas=0):
-        """x: [M, K_local] bf16, w_shard: [N, K_local] bf16 -> sum over ranks of x @ w_shard^T (+ residual), [M, N] bf16."""
+    def __call__(self, x, w_shard, residual=None, out=None, max_ctas=0, rows=None):
+        """x: [M, K_local] bf16, w_shard: [N, K_local] bf16 -> sum over ranks of x @ w_shard^T (+ residual), [M, N] bf16.
+        rows = (lo, hi): reduce-scatter form -- this rank reduces and returns only rows [lo, hi) of the sum ([hi - lo, N]; `residual`
+        has that shape too); the ranks' row ranges must tile [0, M)."""
         M, K = x.shape
         N = w_shard.shape[0]
         assert N == self.n and M <= self.max_m and w_shard.shape[1] == K and x.stride(1) == 1 and w_shard.stride(1) == 1
+        lo, hi = (0, M) if rows is None else rows
         if out is None:
-            out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+            out = torch.empty(hi - lo, N, dtype=torch.bfloat16, device=x.device)
+        assert out.shape[0] == hi - lo and (residual is None or residual.shape[0] == hi - lo)
         self.epoch += 1
         s = self.symm
         arr = (ctypes.c_void_p * s.world)(*s.ptrs)
-        rc = native.lib().dsb200_gemm_ar_bf16(native.ptr(x), native.ptr(w_shard), ctypes.cast(arr, ctypes.c_void_p), self.part_off[self.epoch & 1],
-                                              self.flag_off, self.epoch, native.ptr(out), native.ptr(residual), M, N, K, x.stride(0),
-                                              w_shard.stride(0), out.stride(0), residual.stride(0) if residual is not None else 0, s.rank, s.world,
-                                              int(max_ctas), native.stream_ptr())
+        common = (native.ptr(x), native.ptr(w_shard), ctypes.cast(arr, ctypes.c_void_p), self.part_off[self.epoch & 1], self.flag_off, self.epoch,
+                  native.ptr(out), native.ptr(residual), M, N, K, x.stride(0), w_shard.stride(0), out.stride(0),
+                  residual.stride(0) if residual is not None else 0, s.rank, s.world)
+        if rows is None:
+            rc = native.lib().dsb200_gemm_ar_bf16(*common, int(max_ctas), native.stream_ptr())
+        else:
+            rc = native.lib().dsb200_gemm_rs_bf16(*common, int(lo), int(hi), int(max_ctas), native.stream_ptr())
         native.check(rc)
         return out
+
+
+class FusedGemmReduceScatter(FusedGemmAllReduce):
+    """Row-parallel linear whose output stays sharded over tokens (sequence-parallel tensor parallelism): rank r gets rows
+    [r * M / W, (r + 1) * M / W) of the reduced product.  Same kernel as the all-reduce form; each rank pulls 1 / W of the tiles."""
+
+    def __call__(self, x, w_shard, residual=None, out=None, max_ctas=0):
+        M, W, r = x.shape[0], self.symm.world, self.symm.rank
+        assert M % W == 0, f"rows ({M}) must divide evenly over the {W} ranks"
+        return super().__call__(x, w_shard, residual=residual, out=out, max_ctas=max_ctas, rows=(r * M // W, (r + 1) * M // W))

@@ -152,14 +152,16 @@ int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int
                         dsb200_stream_t stream);
 
 /* ---- csrc/gemm/gemm_ar.cu */
-/* out[M,N] (bf16, local) = sum_r A_r B_r^T (+ residual).  A [M][K] / B [N][K] bf16 are this rank's operands; peer_ptrs[world] are the
- * bases of every rank's symmetric buffer (own included) as mapped here.  The caller reserves inside the symmetric buffer
- *   * two partial areas of M*N*2 bytes (16-byte aligned): pass part_off = area[epoch & 1]
- *   * flags: ceil(M/128)*ceil(N/256) uint32, zero-initialised once (flag_off, 4-byte aligned)
- * and passes the same, strictly increasing `epoch` (>= 1) on every rank for each call.  N must be a multiple of 8. */
 int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
                         unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb,
                         int ldo, int ldr, int rank, int world, int max_ctas, dsb200_stream_t stream);
+/* GEMM -> reduce-scatter over rows (sequence-parallel tensor parallelism): same kernel, but this rank reduces and writes only rows
+ * [row_lo, row_hi) of the sum -- out and residual are [row_hi - row_lo][N].  Every rank still publishes its whole partial (the
+ * owners of the other rows need it); the row ranges of the ranks must cover [0, M) and every rank must own at least one row. */
+int dsb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
+                        unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb,
+                        int ldo, int ldr, int rank, int world, int row_lo, int row_hi, int max_ctas,
+                        dsb200_stream_t stream);
 
 /* ---- csrc/gemm/gemm_fp8.cu */
 /* C[M,N] (bf16) = diag(sa) * (A * B^T) * diag(sb) with A [M][K], B [N][K] in e4m3 (one byte per element, K contiguous).

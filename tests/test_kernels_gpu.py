@@ -847,3 +847,24 @@ def test_grouped_experts_training_path_gpu(monkeypatch):
     assert (x.grad.float() - x2.grad.float()).abs().max() <= 3e-2 * x2.grad.float().abs().max()
     for (n, p), (_, q) in zip(grouped.named_parameters(), loop.named_parameters()):
         assert (p.grad.float() - q.grad.float()).abs().max() <= 3e-2 * q.grad.float().abs().max() + 1e-3, n
+
+
+def test_fused_gemm_reduce_scatter_rows_single_rank():
+    """Reduce-scatter form of the fused GEMM kernel at world 1: only the requested row range is reduced and written (ranges that cut
+    through tiles, start inside a tile, or cover everything)."""
+    from deepspeedsyclsupport_b200.parallel.fused import FusedGemmAllReduce
+    from deepspeedsyclsupport_b200.parallel.symm import EmulatedPeers
+    M, N, K = 700, 512, 256
+    em = EmulatedPeers(1, FusedGemmAllReduce.bytes_needed(M, N) + 4096)
+    op = FusedGemmAllReduce(em, M, N)
+    torch.manual_seed(0)
+    x = torch.randn(M, K, device=_dev()).bfloat16()
+    w = (torch.randn(N, K, device=_dev()) * 0.05).bfloat16()
+    ref = (x.float() @ w.float().t()).bfloat16().float()
+    for lo, hi in ((0, 350), (350, 700), (130, 131), (0, 700), (255, 513)):
+        res = torch.randn(hi - lo, N, device=_dev()).bfloat16()
+        out = torch.full((hi - lo + 1, N), 7.0, device=_dev(), dtype=torch.bfloat16)  # one guard row
+        op(x, w, residual=res, out=out[:hi - lo], rows=(lo, hi))
+        want = ref[lo:hi] + res.float()
+        assert (out[:hi - lo].float() - want).abs().max() <= 1e-2 * want.abs().max(), (lo, hi)
+        assert torch.all(out[hi - lo] == 7.0)

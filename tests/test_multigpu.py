@@ -191,6 +191,30 @@ def _gemm_ar_body():
             dist.all_reduce(y)
             return y
 
+        if M % W == 0:  # reduce-scatter form: each rank keeps its slice of the rows
+            from deepspeedsyclsupport_b200.parallel.fused import FusedGemmReduceScatter
+            rs = FusedGemmReduceScatter.__new__(FusedGemmReduceScatter)
+            rs.__dict__.update(op.__dict__)  # same symmetric areas and epoch counter as `op`
+            lo, hi = rank * M // W, (rank + 1) * M // W
+            for it in range(3):
+                got = rs(x, w, residual=res[lo:hi] if it == 1 else None).float()
+                op.epoch = rs.epoch
+                torch.cuda.synchronize()
+                ref = want[lo:hi] + (res[lo:hi].float() if it == 1 else 0)
+                err = (got - ref).abs().max().item()
+                assert got.shape == (hi - lo, N) and err <= 2e-2 * ref.abs().max().item(), ("rs", M, N, K, it, err)
+
+            def base_rs():
+                y = gemm(x, w)
+                o = torch.empty(M // W, N, dtype=y.dtype, device=dev)
+                dist.reduce_scatter_tensor(o, y)
+                return o
+
+            t_rs, t_rs_base = t(lambda: rs(x, w)), t(base_rs)
+            op.epoch = rs.epoch
+            if rank == 0:
+                print(f"GEMM_RS M={M} N={N} K_local={K} world {W}: gemm+nccl {t_rs_base:.3f} ms, fused {t_rs:.3f} ms, "
+                      f"speedup {t_rs_base / t_rs:.2f}x", flush=True)
         t_fused, t_base = t(lambda: op(x, w)), t(base)
         if rank == 0:
             print(f"GEMM_AR M={M} N={N} K_local={K} world {W}: gemm+nccl {t_base:.3f} ms, fused {t_fused:.3f} ms, "
