@@ -44,8 +44,9 @@ class _Stopwatch(object):
         self.started_ = False
         self._on_host = get_accelerator().use_host_timers()
         self._open = None  # start marker of the running interval
-        self._spans = []  # [(start, end)] events or perf_counter floats
-        self.elapsed_records = None  # resolved milliseconds of the last read
+        self._spans = []  # [(start, end)] events or perf_counter floats, not yet resolved
+        self._resolved = []  # milliseconds of the intervals resolved since the last reset
+        self.elapsed_records = None  # resolved milliseconds as of the last read
 
     def _mark(self):
         if self._on_host:
@@ -74,13 +75,15 @@ class _Stopwatch(object):
                 b.synchronize()
                 ms.append(a.elapsed_time(b))
         self._spans = []
-        self.elapsed_records = ms
-        return sum(ms)
+        self._resolved += ms  # a read without reset keeps what was measured so far
+        self.elapsed_records = list(self._resolved)
+        return sum(self._resolved)
 
     def reset(self):
         self.started_ = False
         self._open = None
         self._spans = []
+        self._resolved = []
         self.elapsed_records = None
 
     def elapsed(self, reset=True):
