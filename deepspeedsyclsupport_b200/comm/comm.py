@@ -295,21 +295,49 @@ def all_to_all_single(output, tensor, output_split_sizes=None, input_split_sizes
                 logger.warning(f"peer-memory all-to-all unavailable ({e}); using NCCL")
                 os.environ["DSB200_PEER_A2A"] = "0"
     if tdist.get_backend(group) == "gloo":
-        # gloo has no all-to-all: all-gather every rank's send buffer and keep the chunk addressed to this rank
-        # (host plumbing path only -- equal splits)
-        assert not output_split_sizes and not input_split_sizes, "uneven all_to_all_single is not supported on gloo"
+        # gloo has no all-to-all (host plumbing path): equal splits as one all-gather keeping the chunk addressed to this rank,
+        # unequal splits as pairwise non-blocking sends / receives
         ws, me = get_world_size(group), get_rank(group)
-        gathered = [torch.empty_like(tensor) for _ in range(ws)]
-        tdist.all_gather(gathered, tensor.contiguous(), group=group)
-        outs = list(output.chunk(ws, 0))
-        for src in range(ws):
-            outs[src].copy_(gathered[src].chunk(ws, 0)[me])
+        if not output_split_sizes and not input_split_sizes:
+            gathered = [torch.empty_like(tensor) for _ in range(ws)]
+            tdist.all_gather(gathered, tensor.contiguous(), group=group)
+            outs = list(output.chunk(ws, 0))
+            for src in range(ws):
+                outs[src].copy_(gathered[src].chunk(ws, 0)[me])
+            return None
+        _pairwise_exchange(list(output.split(list(output_split_sizes) if output_split_sizes else output.shape[0] // ws, 0)),
+                           list(tensor.split(list(input_split_sizes) if input_split_sizes else tensor.shape[0] // ws, 0)), group)
         return None
     return tdist.all_to_all_single(output, tensor, output_split_sizes, input_split_sizes, group=group, async_op=async_op)
 
 
+def _pairwise_exchange(outs, ins, group):
+    """outs[j] <- what rank j addressed to this rank; ins[j] -> rank j.  Non-blocking sends and receives, all posted before waiting."""
+    ws, me = get_world_size(group), get_rank(group)
+    outs[me].copy_(ins[me])
+    reqs, staged = [], []
+    for j in range(ws):
+        if j == me:
+            continue
+        peer = get_global_rank(group, j)
+        if ins[j].numel():
+            reqs.append(tdist.isend(ins[j].contiguous(), dst=peer, group=group))
+        if outs[j].numel():
+            buf = outs[j] if outs[j].is_contiguous() else torch.empty_like(outs[j])
+            staged.append((outs[j], buf))
+            reqs.append(tdist.irecv(buf, src=peer, group=group))
+    for q in reqs:
+        q.wait()
+    for dst, buf in staged:
+        if dst is not buf:
+            dst.copy_(buf)
+
+
 @timed_op
 def all_to_all(output_tensor_list, input_tensor_list, group=None, async_op=False):
+    if tdist.get_backend(group) == "gloo":
+        _pairwise_exchange(output_tensor_list, input_tensor_list, group)
+        return None
     return tdist.all_to_all(output_tensor_list, input_tensor_list, group=group, async_op=async_op)
 
 
