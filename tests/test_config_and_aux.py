@@ -145,3 +145,54 @@ def test_timers_and_throughput():
         time.sleep(0.005)
         tp.stop(global_step=True)
     assert tp.global_step_count == 4 and 0 < tp.avg_samples_per_sec() < 8 / 0.004
+
+
+# ------------------------------------------------------------------ deepspeed.initialize argument handling
+def test_initialize_accepts_the_reference_argument_combinations(tmp_path):
+    """(reference: tests/unit/runtime/test_ds_initialize.py)  config by dict / path / args.deepspeed_config; optimizer from the config,
+    as an instance, or as a callable over the parameters; scheduler from the config, as an instance, or as a callable."""
+    import argparse
+    import deepspeedsyclsupport_b200 as deepspeed
+    from simple_model import SimpleModel
+    base = {"train_batch_size": 4, "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}}}
+    path = tmp_path / "cfg.json"
+    path.write_text(json.dumps(base))
+
+    def run(**kw):
+        model = SimpleModel(16)
+        engine, opt, _, sched = deepspeed.initialize(model=model, model_parameters=model.parameters(), **kw)
+        x, y = torch.randn(4, 16), torch.randint(0, 4, (4, ))
+        loss = engine(x, y)
+        engine.backward(loss)
+        engine.step()
+        return engine, opt, sched
+
+    e, opt, sched = run(config=base)
+    assert opt is not None and sched is None and e.train_batch_size() == 4
+    run(config=str(path))
+    run(args=argparse.Namespace(deepspeed_config=str(path), local_rank=0))
+    run(config_params=base)  # legacy keyword
+    with pytest.raises(AssertionError):
+        run(args=argparse.Namespace(deepspeed_config=str(path)), config=base)  # configuration given twice
+    with pytest.raises(AssertionError):
+        deepspeed.initialize(model=SimpleModel(16))  # no configuration at all
+    no_opt = {"train_batch_size": 4}
+    # client optimizer instance / callable, client scheduler instance / callable
+    model = SimpleModel(16)
+    client = torch.optim.SGD(model.parameters(), lr=0.1)
+    engine, opt, _, _ = deepspeed.initialize(model=model, optimizer=client, config=no_opt)
+    assert getattr(opt, "optimizer", opt) is client or opt is client
+    model = SimpleModel(16)
+    engine, opt, _, sched = deepspeed.initialize(model=model, model_parameters=model.parameters(), config=no_opt,
+                                                 optimizer=lambda params: torch.optim.Adam(params, lr=1e-2),
+                                                 lr_scheduler=lambda o: torch.optim.lr_scheduler.StepLR(o, step_size=1, gamma=0.5))
+    assert isinstance(sched, torch.optim.lr_scheduler.StepLR)
+    x, y = torch.randn(4, 16), torch.randint(0, 4, (4, ))
+    lr0 = engine.get_lr()[0]
+    engine.backward(engine(x, y))
+    engine.step()
+    assert engine.get_lr()[0] == pytest.approx(lr0 * 0.5)
+    # a scheduler named in the config wins over none given; both given -> the config's
+    cfg = dict(base, scheduler={"type": "WarmupLR", "params": {"warmup_min_lr": 0.0, "warmup_max_lr": 1e-3, "warmup_num_steps": 10}})
+    _, _, sched = run(config=cfg)
+    assert type(sched).__name__ == "WarmupLR"
