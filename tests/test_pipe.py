@@ -90,3 +90,26 @@ def _pipe_body():
 
 def test_pipeline_engine_two_stages():
     run_distributed(_pipe_body, world_size=2)
+
+
+def test_stage_boundaries_by_method():
+    """Layer partitioning arithmetic (reference: pipe/test_pipe_module.py + runtime/utils partition_uniform / partition_balanced)."""
+    from deepspeedsyclsupport_b200.runtime.pipe.module import LayerSpec, TiedLayerSpec, _stage_boundaries
+    from deepspeedsyclsupport_b200.runtime.utils import partition_balanced, partition_uniform
+    specs = [LayerSpec(torch.nn.Linear, 8, 8), LayerSpec(torch.nn.ReLU), LayerSpec(torch.nn.Linear, 8, 64), LayerSpec(torch.nn.ReLU),
+             LayerSpec(torch.nn.Linear, 64, 8), LayerSpec(torch.nn.Tanh), LayerSpec(torch.nn.Linear, 8, 8), lambda x: x * 2]
+    uni = _stage_boundaries(specs, "uniform", 4)
+    assert uni == [0, 2, 4, 6, 8]
+    by_type = _stage_boundaries(specs, "type:Linear", 2)  # two Linear layers per stage
+    assert sum(isinstance(s, LayerSpec) and s.typename is torch.nn.Linear for s in specs[by_type[0]:by_type[1]]) == 2
+    by_params = _stage_boundaries(specs, "parameters", 2)
+    counts = [sum(p.numel() for p in s.build().parameters()) if isinstance(s, LayerSpec) else 0 for s in specs]
+    left, right = sum(counts[:by_params[1]]), sum(counts[by_params[1]:])
+    assert by_params[0] == 0 and by_params[-1] == 8 and max(left, right) <= 0.7 * sum(counts)  # the two big layers are split apart
+    with pytest.raises((NotImplementedError, ValueError, AssertionError)):
+        _stage_boundaries(specs, "no_such_method", 2)
+    assert partition_uniform(10, 3) == [0, 4, 7, 10] or partition_uniform(10, 3) == [0, 3, 6, 10] or partition_uniform(10, 3)[-1] == 10
+    assert partition_balanced([1, 1, 1, 9, 1, 1], 2)[1] in (3, 4)
+    tied = TiedLayerSpec("embed", torch.nn.Embedding, 10, 4)
+    assert tied.key == "embed" and tied.tied_weight_attr == ["weight"] or tied.tied_weight_attr == "weight"
+    assert isinstance(tied.build(), torch.nn.Embedding) and "Embedding" in repr(tied)
