@@ -80,6 +80,25 @@ def _ep_body():
     dist.barrier()
     assert os.path.exists(os.path.join(d, "t1", f"layer_0_expert_{dist.get_rank() * 2}_mp_rank_00_model_states.pt"))
     assert os.path.exists(os.path.join(d, "latest"))
+    # load into a differently initialised engine: dense parameters, this rank's experts and the optimizer state come back
+    torch.manual_seed(99)
+    model2 = _MoEModel(16, num_experts=4, ep_size=2)
+    engine2, _, _, _ = deepspeed.initialize(model=model2, config=cfg)
+    before = engine2(x, y).item()
+    path, client = engine2.load_checkpoint(d, tag="t1")
+    assert path is not None and engine2.global_steps == engine.global_steps
+    for (n, p), (_, q) in zip(model.named_parameters(), model2.named_parameters()):
+        assert torch.allclose(p.detach().float(), q.detach().float(), atol=1e-6), n
+    engine.eval(), engine2.eval()
+    with torch.no_grad():
+        assert abs(engine2(x, y).item() - engine(x, y).item()) < 1e-5 and abs(before - engine(x, y).item()) > 1e-4
+    engine.train(), engine2.train()
+    for e in (engine, engine2):  # one more identical step on both: the restored optimizer state matches too
+        loss = e(x, y)
+        e.backward(loss)
+        e.step()
+    for (n, p), (_, q) in zip(model.named_parameters(), model2.named_parameters()):
+        assert torch.allclose(p.detach().float(), q.detach().float(), atol=1e-5), n
 
 
 def test_moe_expert_parallel_two_ranks():
