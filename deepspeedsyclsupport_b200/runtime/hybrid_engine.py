@@ -196,12 +196,25 @@ class DeepSpeedHybridEngine(DeepSpeedEngine):
     # container is just a record of (layer, index, architecture): these methods keep the names for code that introspects
     # the hybrid engine, and `_inference_containers` lists the layers whose parameter units are pinned around generate().
     def populate_all_inference_policies(self):
+        """Architectures generation knows about: the ragged-engine families by `model_type`, and every client layer class a
+        layer policy of module_inject/replace_policy recognises (reference hybrid_engine.py:118-127)."""
         from ..inference.kernel_inject import SUPPORTED
+        from ..module_inject.replace_policy import replace_policies
         self.inference_policies = {name: name for name in SUPPORTED}
+        for policy_cls in replace_policies:
+            try:
+                policy_cls(None)
+            except Exception:
+                continue
+            classes = policy_cls._orig_layer_class
+            for c in (classes if isinstance(classes, (list, tuple)) else [classes]):
+                if c is not None:
+                    self.inference_policies[c] = policy_cls
         return self.inference_policies
 
     def new_inference_container(self, orig_layer, policy_cls, layer_id):
-        return {"layer": orig_layer, "policy": policy_cls, "layer_id": layer_id,
+        policies = getattr(self, "inference_policies", {})
+        return {"layer": orig_layer, "policy": policies.get(type(orig_layer), policy_cls), "layer_id": layer_id,
                 "units": sorted({id(getattr(p, "ds_unit", None)) for p in orig_layer.parameters() if hasattr(p, "ds_unit")})}
 
     def create_inference_containers(self, module, layer_id=0):
