@@ -22,7 +22,7 @@ from .accelerator import get_accelerator, set_accelerator  # noqa: F401
 from .comm.comm import init_distributed  # noqa: F401
 from .runtime import zero  # noqa: F401
 from .runtime.config import DeepSpeedConfig, DeepSpeedConfigError  # noqa: F401
-from .runtime.engine import DeepSpeedEngine, DeepSpeedOptimizerCallable, DeepSpeedSchedulerCallable  # noqa: F401
+from .runtime.engine import ADAM_OPTIMIZER, LAMB_OPTIMIZER, DeepSpeedEngine, DeepSpeedOptimizerCallable, DeepSpeedSchedulerCallable  # noqa: F401
 from .utils import groups  # noqa: F401
 from .utils.logging import log_dist, logger  # noqa: F401
 from .version import __version__, __version_major__, __version_minor__, __version_patch__  # noqa: F401

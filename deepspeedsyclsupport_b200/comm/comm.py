@@ -419,6 +419,42 @@ def in_aws_sm():
     return "SM_TRAINING_ENV" in os.environ
 
 
+def patch_aml_env_for_torch_nccl_backend(master_port=6105, verbose=True):
+    """Translate the OpenMPI variables of an Azure ML job into RANK / WORLD_SIZE / LOCAL_RANK / MASTER_*
+    (parity: comm.py:728-757)."""
+    env = os.environ
+    env["RANK"], env["WORLD_SIZE"] = env["OMPI_COMM_WORLD_RANK"], env["OMPI_COMM_WORLD_SIZE"]
+    if int(env["OMPI_COMM_WORLD_LOCAL_SIZE"]) == int(env["WORLD_SIZE"]):
+        env["MASTER_ADDR"] = env["AZ_BATCHAI_MPI_MASTER_NODE"]
+        env["MASTER_PORT"] = str(TORCH_DISTRIBUTED_DEFAULT_PORT)
+    else:
+        env["MASTER_ADDR"] = env["AZ_BATCH_MASTER_NODE"].split(":")[0]
+        env.setdefault("MASTER_PORT", str(master_port))
+    env["LOCAL_RANK"] = env["OMPI_COMM_WORLD_LOCAL_RANK"]
+    if verbose:
+        logger.info("Azure ML job: rank %s, local rank %s, world size %s, master %s:%s", env["RANK"], env["LOCAL_RANK"],
+                    env["WORLD_SIZE"], env["MASTER_ADDR"], env["MASTER_PORT"])
+
+
+def patch_aws_sm_env_for_torch_nccl_backend(verbose=True):
+    """Translate the OpenMPI variables of a SageMaker job into RANK / LOCAL_RANK / WORLD_SIZE
+    (parity: comm.py:760-771)."""
+    env = os.environ
+    env["RANK"], env["LOCAL_RANK"] = env["OMPI_COMM_WORLD_RANK"], env["OMPI_COMM_WORLD_LOCAL_RANK"]
+    env["WORLD_SIZE"] = env["OMPI_COMM_WORLD_SIZE"]
+    if verbose:
+        logger.info("SageMaker job: rank %s, local rank %s, world size %s", env["RANK"], env["LOCAL_RANK"], env["WORLD_SIZE"])
+
+
+def set_backend():
+    """Point ``cdb`` at the backend matching the accelerator's communication library (parity: comm.py:198-218).
+    There is one backend object here (NCCL on the device, gloo on the host), so this only re-validates it."""
+    global cdb
+    if cdb is not None and not cdb.is_initialized():
+        cdb = None
+    return cdb
+
+
 def in_dlts():
     return "DLTS_JOB_ID" in os.environ
 

@@ -9,3 +9,4 @@ from .policy import DSPolicy, TransformerPolicy  # noqa: F401
 from .replace_module import replace_with_kernel_policies  # noqa: F401
 from .replace_policy import generic_policies, replace_policies  # noqa: F401
 from .utils import policy_to_ds_container  # noqa: F401
+from .containers import HFBertLayerPolicy  # noqa: F401,E402

@@ -45,6 +45,52 @@ def add_tuning_arguments(parser):
     return parser
 
 
+# command-line flag -> schedule parameter, per schedule family (flag names are the parameter names)
+_ARG_PARAMS = {
+    LR_RANGE_TEST: ("lr_range_test_min_lr", "lr_range_test_step_rate", "lr_range_test_step_size",
+                    "lr_range_test_staircase"),
+    ONE_CYCLE: ("cycle_first_step_size", "cycle_first_stair_count", "cycle_second_step_size",
+                "cycle_second_stair_count", "decay_step_size", "cycle_min_lr", "cycle_max_lr", "decay_lr_rate",
+                "cycle_min_mom", "cycle_max_mom", "decay_mom_rate"),
+    "warmup": ("warmup_min_lr", "warmup_max_lr", "warmup_num_steps", "warmup_type"),
+}
+
+
+def parse_arguments():
+    """Parse the convergence-tuning flags out of ``sys.argv`` (parity: runtime/lr_schedules.py:158-164)."""
+    import argparse
+    parser = add_tuning_arguments(argparse.ArgumentParser())
+    lr_sched_args, unknown_args = parser.parse_known_args()
+    return lr_sched_args, unknown_args
+
+
+def get_config_from_args(args):
+    """Build a ``{"type", "params"}`` scheduler config from parsed tuning flags; returns ``(config, error)``
+    (parity: runtime/lr_schedules.py:212-232).  Flags left at ``None`` are not copied."""
+    name = getattr(args, LR_SCHEDULE, None)
+    if name is None:
+        return None, "--{} not specified on command line".format(LR_SCHEDULE)
+    if name not in VALID_LR_SCHEDULES:
+        return None, "{} is not supported LR schedule".format(name)
+    family = name if name in (LR_RANGE_TEST, ONE_CYCLE) else "warmup"
+    params = {k: getattr(args, k) for k in _ARG_PARAMS[family] if getattr(args, k, None) is not None}
+    return {"type": name, "params": params}, None
+
+
+def get_lr_from_config(config):
+    """The learning rate a scheduler config starts from / peaks at; returns ``(lr, error)``
+    (parity: runtime/lr_schedules.py:235-255)."""
+    if "type" not in config:
+        return None, "LR schedule type not defined in config"
+    if "params" not in config:
+        return None, "LR schedule params not defined in config"
+    name, params = config["type"], config["params"]
+    if name not in VALID_LR_SCHEDULES:
+        return None, "{} is not a valid LR schedule".format(name)
+    key = {LR_RANGE_TEST: "lr_range_test_min_lr", ONE_CYCLE: "cycle_max_lr"}.get(name, "warmup_max_lr")
+    return params[key], ""
+
+
 def get_torch_optimizer(optimizer):
     if isinstance(optimizer, Optimizer):
         return optimizer

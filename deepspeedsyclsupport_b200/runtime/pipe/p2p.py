@@ -12,6 +12,11 @@ _groups = None
 _grid = None
 
 
+def can_send_recv() -> bool:
+    """Point-to-point send/recv is always available on this stack (parity: runtime/pipe/p2p.py:23-26)."""
+    return True
+
+
 def init_process_groups(grid):
     global _groups, _grid
     _grid = grid

@@ -347,3 +347,224 @@ def all_gather_dp_groups(groups_flat, partitioned_param_groups, dp_process_group
     for group_id, partitioned_params in enumerate(partitioned_param_groups):
         partition_id = dist.get_rank(group=dp_process_group[group_id])
         dist.all_gather_into_tensor(groups_flat[group_id], partitioned_params[partition_id], group=dp_process_group[group_id])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Overflow check, tensor-list norms / clipping, CUDA-graph helper and small shims.
+# ---------------------------------------------------------------------------------------------------------------------
+_graphs = {}
+
+
+def graph_process(replay_first_step, func, *args, **kwargs):
+    """Capture ``func(*args, **kwargs)`` in a CUDA graph on first use and replay it afterwards
+    (parity: runtime/utils.py:53-68).  The arguments must be static tensors; on a host-only build the
+    function simply runs."""
+    if not torch.cuda.is_available():
+        func(*args, **kwargs)
+        return
+    key = func.__name__ + "_graph"
+    first = key not in _graphs
+    if first:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):  # warm-up outside capture so lazy inits do not land in the graph
+            func(*args, **kwargs)
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            func(*args, **kwargs)
+        _graphs[key] = g
+    if not first or replay_first_step:
+        _graphs[key].replay()
+
+
+def copy_to_device(item, device, criterion_func):
+    """Like ``move_to_device`` but always makes a fresh copy of matching tensors
+    (parity: runtime/utils.py:158-181)."""
+    if criterion_func(item):
+        return item.to(device, copy=True)
+    if isinstance(item, list):
+        return [copy_to_device(v, device, criterion_func) for v in item]
+    if isinstance(item, tuple):
+        return tuple(copy_to_device(v, device, criterion_func) for v in item)
+    if isinstance(item, dict):
+        return {k: copy_to_device(v, device, criterion_func) for k, v in item.items()}
+    return item
+
+
+class CheckOverflow:
+    """inf/nan detection over gradients with the result agreed on by every rank that shares them
+    (parity: runtime/utils.py:208-322).  One fused ``_foreach_norm`` pass replaces the per-tensor sum."""
+
+    def __init__(self, param_groups=None, mpu=None, zero_reduce_scatter=False, deepspeed=None):
+        self.mpu = mpu
+        self.params = [] if param_groups else None
+        self.zero_reduce_scatter = zero_reduce_scatter
+        self.deepspeed = deepspeed
+        self.has_moe_params = False
+        if param_groups:
+            for group in param_groups:
+                for p in group:
+                    self.params.append(p)
+                    if getattr(p, "allreduce", True) is False:
+                        self.has_moe_params = True
+
+    def _agree(self, overflow, has_moe_params=None):
+        flag = torch.tensor([float(overflow)], device=get_accelerator().current_device_name()
+                            if torch.cuda.is_available() else "cpu")
+        if not dist.is_initialized():
+            return bool(flag.item())
+        if has_moe_params is None:
+            has_moe_params = self.has_moe_params
+        if has_moe_params:
+            from ..utils import groups
+            try:
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=groups._get_max_expert_parallel_group())
+            except Exception:
+                pass
+        if self.zero_reduce_scatter:
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=dist.get_world_group())
+        elif self.mpu is not None:
+            if self.deepspeed is not None and getattr(self.deepspeed, "pipeline_enable_backward_allreduce", True) is False:
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.mpu.get_data_parallel_group())
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=self.mpu.get_model_parallel_group())
+        elif self.deepspeed is not None and getattr(self.deepspeed, "pipeline_enable_backward_allreduce", True) is False:
+            dist.all_reduce(flag, op=dist.ReduceOp.MAX, group=dist.get_world_group())
+        return bool(flag.item())
+
+    def check_using_norm(self, norm_group, reduce_overflow=True):
+        overflow = -1 in norm_group
+        if not reduce_overflow:
+            return bool(overflow)
+        return self._agree(overflow, has_moe_params=False)
+
+    def check(self, param_groups=None):
+        if param_groups is None:
+            assert self.params is not None, "CheckOverflow.check: no parameters given at construction or call"
+            params = self.params
+            has_moe = self.has_moe_params
+        else:
+            assert param_groups, "CheckOverflow.check: empty param_groups"
+            params = [p for g in param_groups for p in g]
+            has_moe = any(getattr(p, "allreduce", True) is False for p in params)
+        return self.has_overflow(params, has_moe_params=has_moe)
+
+    def has_overflow_serial(self, params):
+        grads = [p.grad.data for p in params if p.grad is not None]
+        if not grads:
+            return False
+        dense = [g.float() if g.dtype not in (torch.float32, torch.float16, torch.bfloat16) else g for g in grads
+                 if not g.is_sparse]
+        sparse = [g.coalesce().values() for g in grads if g.is_sparse]
+        norms = torch._foreach_norm(dense + sparse) if (dense or sparse) else []
+        total = torch.stack([n.float() for n in norms]).sum() if norms else torch.zeros(())
+        return not bool(torch.isfinite(total).item())
+
+    def has_overflow(self, params, has_moe_params=None):
+        return self._agree(self.has_overflow_serial(params), has_moe_params=has_moe_params)
+
+    @staticmethod
+    def _has_inf_or_nan(x, i=None):
+        return not bool(torch.isfinite(x.float().sum()).item())
+
+
+def empty_cache():
+    """Release cached device blocks and reset the peak counters (parity: runtime/utils.py:776-778)."""
+    get_accelerator().empty_cache()
+    if torch.cuda.is_available():
+        get_accelerator().reset_peak_memory_stats()
+
+
+def get_global_norm_of_tensors(input_tensors, norm_type=2, mpu=None, use_graph=False):
+    """p-norm of a list of tensors viewed as one vector, reduced over the model-parallel group; -1 when the
+    result is inf/nan (parity: runtime/utils.py:855-905).  A single multi-tensor norm launch covers the list, so
+    ``use_graph`` needs no separate capture and is accepted for signature parity."""
+    input_tensors = list(input_tensors)
+    assert all(torch.is_tensor(t) for t in input_tensors), "expected an iterable of tensors"
+    norm_type = float(norm_type)
+    if not input_tensors:
+        return 0.0
+    device = input_tensors[0].device
+    if norm_type == math.inf:
+        total = torch.stack([t.detach().abs().max().float() for t in input_tensors]).max().reshape(1).to(device)
+        if mpu is not None:
+            dist.all_reduce(total, op=dist.ReduceOp.MAX, group=mpu.get_model_parallel_group())
+        total_norm = total.item()
+    else:
+        per = torch._foreach_norm([t.detach().float() for t in input_tensors], norm_type)
+        total = (torch.stack(per) ** norm_type).sum().reshape(1)
+        if mpu is not None:
+            dist.all_reduce(total, op=dist.ReduceOp.SUM, group=mpu.get_model_parallel_group())
+        total_norm = total.item() ** (1.0 / norm_type)
+    if math.isinf(total_norm) or math.isnan(total_norm):
+        total_norm = -1
+    return total_norm
+
+
+def clip_tensors_by_global_norm(input_tensors, max_norm=1.0, global_norm=None, mpu=None, eps=1e-6, use_graph=False):
+    """Scale the tensors in place so their global norm is at most ``max_norm``; returns the norm before clipping
+    (parity: runtime/utils.py:908-939)."""
+    input_tensors = list(input_tensors)
+    if global_norm is None:
+        global_norm = get_global_norm_of_tensors(input_tensors, mpu=mpu, use_graph=use_graph)
+    clip_coef = max_norm / (global_norm + eps)
+    if clip_coef < 1 and input_tensors:
+        torch._foreach_mul_([t.detach() for t in input_tensors], clip_coef)
+    return global_norm
+
+
+def align_dense_tensors(tensor_list, alignment):
+    """Append a zero pad tensor so the total element count is a multiple of ``alignment``
+    (parity: runtime/utils.py:942-953)."""
+    numel = sum(t.numel() for t in tensor_list)
+    rem = numel % alignment
+    if rem == 0:
+        return tensor_list
+    pad = torch.zeros(alignment - rem, device=tensor_list[0].device, dtype=tensor_list[0].dtype)
+    return list(tensor_list) + [pad]
+
+
+def all_gather_into_tensor_dp_groups(groups_flat, partitioned_param_groups, dp_process_group):
+    """One ``all_gather_into_tensor`` per flat group, each rank contributing its own partition
+    (parity: runtime/utils.py:956-961)."""
+    for group_id, (flat, partitions) in enumerate(zip(groups_flat, partitioned_param_groups)):
+        rank = dist.get_rank(group=dp_process_group[group_id])
+        if dist.get_world_size(group=dp_process_group[group_id]) <= 1:
+            continue
+        dist.all_gather_into_tensor(flat, partitions[rank], group=dp_process_group[group_id])
+
+
+class TLinear(torch.nn.Linear):
+    """Linear built from a layer whose weight is held as ``[in, out]`` (the layout hybrid-engine containers keep):
+    the weight is transposed once at construction, the forward is a plain linear (parity: runtime/utils.py:1005-1021)."""
+
+    def __init__(self, orig_layer, name=""):
+        self.name = name
+        w = orig_layer.weight
+        torch.nn.Module.__init__(self)
+        self.in_features, self.out_features = w.shape[0], w.shape[1]
+        self.weight = torch.nn.Parameter(w.data.t().contiguous(), requires_grad=w.requires_grad)
+        self.bias = orig_layer.bias
+
+    def forward(self, input):
+        return torch.nn.functional.linear(input, self.weight, self.bias)
+
+
+def get_inactive_params(param_list):
+    """ZeRO-3 parameters of ``param_list`` whose full tensor is not resident (parity: runtime/utils.py:1024-1027)."""
+    from .zero.partition_parameters import ZeroParamStatus
+    return [p for p in param_list if hasattr(p, "ds_id") and p.ds_status == ZeroParamStatus.NOT_AVAILABLE]
+
+
+def required_torch_version(min_version=None, max_version=None):
+    """True when the installed torch ``major.minor`` lies in ``[min_version, max_version]``
+    (parity: runtime/utils.py:1030-1041)."""
+    assert min_version or max_version, "give min_version, max_version or both"
+    from packaging import version as pkg_version
+    parts = torch.__version__.split("+")[0].split(".")
+    cur = pkg_version.parse(f"{parts[0]}.{parts[1]}")
+    if min_version and cur < pkg_version.parse(str(min_version)):
+        return False
+    if max_version and cur > pkg_version.parse(str(max_version)):
+        return False
+    return True

@@ -28,6 +28,26 @@ def create_mics_comm_groups(shard_size, dp_group=None, hierarchical_allgather=Fa
     return shard_group, replica_group
 
 
+class MiCS_AllGatherCoalescedHandle:
+    """Completion handle of a shard-group all-gather: ``wait()`` blocks on the collective, then flips every
+    covered parameter from in-flight to available (parity: runtime/zero/mics.py:34-59)."""
+
+    def __init__(self, allgather_handle, params, partitions, world_size):
+        self.allgather_handle, self.params, self.partitions, self.world_size = allgather_handle, params, partitions, world_size
+        self.complete = False
+
+    def wait(self):
+        if self.complete:
+            return
+        from .partition_parameters import ZeroParamStatus
+        if self.allgather_handle is not None:
+            self.allgather_handle.wait()
+        for p in self.params:
+            assert p.ds_status == ZeroParamStatus.INFLIGHT, f"expected param {getattr(p, 'ds_id', '?')} to be inflight"
+            p.ds_status = ZeroParamStatus.AVAILABLE
+        self.complete = True
+
+
 class MiCS_Init(Init):
 
     def __init__(self, *args, **kwargs):
