@@ -136,8 +136,11 @@ def test_env_patching(monkeypatch):
     for k, v in dict(OMPI_COMM_WORLD_RANK="3", OMPI_COMM_WORLD_LOCAL_RANK="1", OMPI_COMM_WORLD_SIZE="8",
                      OMPI_COMM_WORLD_LOCAL_SIZE="4", AZ_BATCH_MASTER_NODE="10.0.0.4:6000").items():
         monkeypatch.setenv(k, v)
+    # the helpers write os.environ directly: register every key they touch with monkeypatch first, so that the
+    # values are rolled back and cannot leak a fake rendezvous address into later tests
     for k in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT"):
-        monkeypatch.delenv(k, raising=False)
+        monkeypatch.setenv(k, "placeholder")
+        del os.environ[k]
     dist.patch_aml_env_for_torch_nccl_backend(verbose=False)
     assert (os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"]) == ("3", "1", "8")
     assert os.environ["MASTER_ADDR"] == "10.0.0.4" and os.environ["MASTER_PORT"] == "6105"
@@ -155,3 +158,7 @@ def test_mics_handle():
     h = MiCS_AllGatherCoalescedHandle(types.SimpleNamespace(wait=lambda: waited.append(1)), [p], [None], 2)
     h.wait(); h.wait()
     assert waited == [1] and p.ds_status == ZeroParamStatus.AVAILABLE
+
+
+def test_env_patching_left_no_trace():
+    assert os.environ.get("MASTER_ADDR") != "10.0.0.4" and os.environ.get("WORLD_SIZE") != "8"
