@@ -103,7 +103,7 @@ def ds_config(args, world):
     }
 
 
-def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, launches, clocks, extra=None):
+def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, launches, clocks, extra=None, act_ckpt=False):
     value = tokens_per_step / (ms_own / 1e3)
     out = {
         "metric": "tokens/sec/box Llama-2-7B ZeRO-3 bf16 (training step: fwd+bwd+AdamW)",
@@ -113,10 +113,8 @@ def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, l
         "config": {"model": f"llama-2-{args.model}" + (f"-{args.layers}layers-INVALID-debug" if args.layers else ""),
                    "global_batch": args.micro_batch * world, "seq_len": args.seq_len, "micro_batch_per_gpu": args.micro_batch,
                    "parallelism": f"zero{args.zero_stage}-dp{world}", "optimizer": "AdamW", "grad_clip": 1.0,
-                   "activation_checkpointing": (False if args.no_act_ckpt else
-                                                ("policy auto (ops/recompute.py): no recomputation when every saved activation fits in 60 % of the free HBM, "
-                                                 "else per-layer checkpoint keeping attention + GEMM outputs (norms / RoPE / SwiGLU recomputed)" if impl == "own"
-                                                 else "per-layer full recompute (HF gradient_checkpointing)")),
+                   # resolved value, same vocabulary in both arms: False = nothing is recomputed, else the recompute policy
+                   "activation_checkpointing": act_ckpt,
                    "l2_policy": "working set (weights+activations, >13 GB) far exceeds the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_tps, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
         "gpu_launches": launches, "clocks": clocks,
@@ -208,16 +206,38 @@ def run_own(args):
         last["loss_host"] = loss.item()
 
     ms, e2e, launches, clocks = timed_loops(args, step, step_e2e, world, dist, torch, lambda: native.launch_count)
+    # exposed communication: separate pass with the optimizer's comm probe on (not inside the timed region)
+    exposed_ms, exposed_sites = 0.0, {}
+    opt = engine.optimizer
+    if world > 1 and hasattr(opt, "comm_probe_start"):
+        k = max(2, min(args.steps, 4))
+        torch.cuda.synchronize()
+        dist.barrier()
+        opt.comm_probe_start()
+        for _ in range(k):
+            step()
+        total, sites = opt.comm_probe_stop(detail=True)
+        t = torch.tensor([total / k], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        exposed_ms = round(t.item(), 3)
+        exposed_sites = {s_: round(v / k, 3) for s_, v in sorted(sites.items())}  # rank 0's split, for orientation
     if rank == 0:
         h2d = host_ids.numel() * host_ids.element_size() + host_labels.numel() * host_labels.element_size()
         extra = {"final_loss": last.get("loss_host"), "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
                  "model_flops_per_token": model.flops_per_token(S, with_recompute=False)}  # 6*P + attention, no recompute credit
         tps = world * B * S / (ms / 1e3)
         extra["tflops_per_gpu"] = round(tps / world * extra["model_flops_per_token"] / 1e12, 1)
-        line = result_line(args, "own", world, world * B * S, ms, e2e, h2d, 4, launches, clocks, extra)
         resolved = getattr(model.model, "_policy_cache", (None, None))[1]
-        if resolved is not None and not args.no_act_ckpt:
-            line["config"]["activation_checkpointing"] += f"; resolved on this run: '{resolved}'"
+        act = False if (args.no_act_ckpt or resolved in (None, "none")) else resolved
+        extra["exposed_comm_ms"] = exposed_ms
+        extra["exposed_comm_sites_rank0"] = exposed_sites
+        extra["exposed_comm_how"] = ("CUDA-event pairs around every point where the compute stream waits for a gather / reduce stream or "
+                                     "runs a collective itself (grad-norm all-reduce, post-step barrier + persistent gathers); "
+                                     "per step, max over ranks, measured in a separate pass after the timed one")
+        extra["zero_collectives"] = getattr(engine.optimizer, "_p2p_rs_mode", None) and {
+            "all_gather": engine.optimizer._p2p_ag_mode, "reduce_scatter": engine.optimizer._p2p_rs_mode,
+            "symm_backend": engine.optimizer.p2p.backend} or "nccl"
+        line = result_line(args, "own", world, world * B * S, ms, e2e, h2d, 4, launches, clocks, extra, act_ckpt=act)
         print(json.dumps(line), flush=True)
 
 
@@ -231,6 +251,9 @@ def run_reference(args):
         import torch
         import deepspeed
         from transformers import LlamaConfig, LlamaForCausalLM
+        # the reference's init_distributed() does not select a device (its engine does, later): do it here, the way its
+        # launcher-driven examples do with args.local_rank, so the model and the inputs of rank r live on GPU r
+        torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", "0")))
         deepspeed.init_distributed()
         import torch.distributed as tdist
         world, rank = tdist.get_world_size(), tdist.get_rank()
@@ -248,7 +271,10 @@ def run_reference(args):
         with torch.device(dev):
             model = LlamaForCausalLM(hf_cfg)
         torch.set_default_dtype(prev)
-        if not args.no_act_ckpt:
+        # N == 1 runs both variants (run_reference_best_of); at N > 1 the sharded model leaves even more room, so the arm
+        # runs the variant that won at N == 1 -- no recomputation, the same setting the own arm resolves to
+        use_ckpt = not args.no_act_ckpt and world == 1
+        if use_ckpt:
             model.gradient_checkpointing_enable()
         model.train()
         cfg = ds_config(args, world)
@@ -265,9 +291,8 @@ def run_reference(args):
         host_labels = torch.randint(0, V, (B, S), generator=g).pin_memory()
         dev_ids, dev_labels = host_ids.to(dev), host_labels.to(dev)
         last = {}
-        # Watchdog: the unmodified reference can dead-lock in its collectives on this torch/NCCL stack.  If the run makes no
-        # progress for DSB_REF_WATCHDOG seconds, dump every thread's stack (diagnosis) and report the arm as unavailable
-        # instead of hanging the caller until its own timeout.
+        # Watchdog: if a rank makes no progress for DSB_REF_WATCHDOG seconds (e.g. a peer died and left this one inside a
+        # collective), dump every thread's stack and report the arm as unavailable instead of hanging the caller.
         import faulthandler
         import threading
         limit = float(os.environ.get("DSB_REF_WATCHDOG", "180"))
@@ -280,7 +305,7 @@ def run_reference(args):
                     faulthandler.dump_traceback(file=sys.stderr, all_threads=True)
                     if rank == 0:
                         print(json.dumps({"impl": "reference", "n_gpus": world,
-                                          "unavailable": f"reference training step made no progress for {int(limit)} s at world size {world} (dead-lock inside the unmodified reference on this torch/NCCL stack)"}), flush=True)
+                                          "unavailable": f"reference training step made no progress for {int(limit)} s at world size {world} (see the stack dump on stderr)"}), flush=True)
                     os._exit(0)
 
         threading.Thread(target=_watch, daemon=True).start()
@@ -311,12 +336,13 @@ def run_reference(args):
             h2d = host_ids.numel() * 8 * 2
             extra = {"final_loss": last.get("loss_host"), "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2),
                      "reference": "DeepSpeed 0.12.7 (baseline/_ref, unmodified) + transformers LlamaForCausalLM sdpa", "notes": notes}
-            line = result_line(args, "reference", world, world * B * S, ms, e2e, h2d, 4, 0, clocks, extra)
+            line = result_line(args, "reference", world, world * B * S, ms, e2e, h2d, 4, 0, clocks, extra,
+                               act_ckpt="full" if use_ckpt else False)
             print(json.dumps(line), flush=True)
     except Exception as e:
+        import traceback
+        traceback.print_exc(file=sys.stderr)  # every rank: a failure on rank > 0 must not look like a hang of rank 0
         if int(os.environ.get("RANK", "0")) == 0:
-            import traceback
-            traceback.print_exc(file=sys.stderr)
             print(json.dumps({"impl": "reference", "unavailable": f"{type(e).__name__}: {str(e)[:300]}"}), flush=True)
         sys.exit(0)
 

@@ -24,11 +24,7 @@ constexpr int BW_THREADS = 192;
 constexpr int BW_SM_THREADS = 128;
 constexpr int BW_CHUNK = 128 * 128;  // [128 rows x 64 bf16] swizzled chunk (also [128 rows x 32 fp32])
 
-// spin without the diagnostic printf of mbar_wait (its argument buffer costs stack and registers in the issue loop)
-__device__ __forceinline__ void bwd_wait(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
+__device__ __forceinline__ void bwd_wait(uint64_t* bar, uint32_t parity) { mbar_wait_lean(bar, parity); }
 __device__ __forceinline__ float bwd_ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));

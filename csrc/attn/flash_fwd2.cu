@@ -37,11 +37,6 @@ __device__ __forceinline__ void reg_inc() {
   asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(N));
 }
 
-// spin without the diagnostic printf of mbar_wait (its argument buffer costs stack and registers in the issue loop)
-__device__ __forceinline__ void mbar_wait_lean(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
 
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;

@@ -103,6 +103,50 @@ __global__ void alltoall_pull_kernel(Peers peers, size_t src_off, uint8_t* __res
   }
 }
 
+// scale, (accumulate into) store and sum-of-squares of one reduced 16-byte vector: shared by the P2P and NVLS reduce-scatters
+template <int EPV, bool DST_BF16>
+__device__ __forceinline__ float rs_finish(float (&acc)[EPV], void* __restrict__ dst, size_t v, float scale, int accumulate, bool want_sq) {
+#pragma unroll
+  for (int k = 0; k < EPV; ++k) acc[k] *= scale;
+  if constexpr (DST_BF16) {
+    __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst) + v * EPV;
+    if (accumulate) {
+#pragma unroll
+      for (int k = 0; k < EPV; ++k) acc[k] += __bfloat162float(d[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < EPV; k += 2) *reinterpret_cast<uint32_t*>(d + k) = pack_bf16x2(acc[k], acc[k + 1]);
+  } else {
+    float* d = static_cast<float*>(dst) + v * EPV;
+    if (accumulate) {
+#pragma unroll
+      for (int k = 0; k < EPV; ++k) acc[k] += d[k];
+    }
+#pragma unroll
+    for (int k = 0; k < EPV; k += 4) *reinterpret_cast<float4*>(d + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
+  }
+  float sq = 0.f;
+  if (want_sq) {
+#pragma unroll
+    for (int k = 0; k < EPV; ++k) sq = fmaf(acc[k], acc[k], sq);
+  }
+  return sq;
+}
+
+// one atomicAdd per CTA
+__device__ __forceinline__ void block_atomic_sum(float local, float* __restrict__ out) {
+  __shared__ float red[32];
+  local = warp_sum(local);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) red[w] = local;
+  __syncthreads();
+  if (w == 0) {
+    float t = l < (blockDim.x >> 5) ? red[l] : 0.f;
+    t = warp_sum(t);
+    if (l == 0) atomicAdd(out, t);
+  }
+}
+
 // ---------------------------------------------------------------- reduce-scatter (pull) fused with scale / cast / norm
 // Every rank holds a full gradient buffer (bf16 or fp32) of world*n elements at `src_off` of its symmetric buffer.
 // Rank r sums slice r over all peers in fp32, multiplies by `scale`, and either stores or accumulates into `dst`
@@ -111,6 +155,7 @@ template <bool SRC_BF16, bool DST_BF16>
 __global__ void reduce_scatter_pull_kernel(Peers peers, size_t src_off, void* __restrict__ dst, size_t n, int rank, int world,
                                            float scale, int accumulate, float* __restrict__ sumsq) {
   constexpr int EPV = SRC_BF16 ? 8 : 4;  // elements per 16-byte vector
+  constexpr int BATCH = 8;               // peer loads issued back to back before the first add (a peer load is a 2-3 us round trip)
   const size_t vecs = n / EPV;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   const size_t esz = SRC_BF16 ? 2 : 4;
@@ -119,58 +164,34 @@ __global__ void reduce_scatter_pull_kernel(Peers peers, size_t src_off, void* __
     float acc[EPV];
 #pragma unroll
     for (int k = 0; k < EPV; ++k) acc[k] = 0.f;
-    for (int pi = 0; pi < world; ++pi) {
-      const int peer = (pi + rank) % world;
-      const uint4 raw = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + (static_cast<size_t>(rank) * n + v * EPV) * esz);
-      if constexpr (SRC_BF16) {
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+    const size_t byte_off = src_off + (static_cast<size_t>(rank) * n + v * EPV) * esz;
+    for (int p0 = 0; p0 < world; p0 += BATCH) {
+      uint4 raw[BATCH];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          float2 f = __bfloat1622float2(h[k]);
-          acc[2 * k] += f.x;
-          acc[2 * k + 1] += f.y;
+      for (int b = 0; b < BATCH; ++b) {
+        const int pi = p0 + b;
+        if (pi < world) raw[b] = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[(pi + rank) % world]) + byte_off);
+      }
+#pragma unroll
+      for (int b = 0; b < BATCH; ++b) {
+        if (p0 + b >= world) continue;
+        if constexpr (SRC_BF16) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[b]);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float2 f = __bfloat1622float2(h[k]);
+            acc[2 * k] += f.x;
+            acc[2 * k + 1] += f.y;
+          }
+        } else {
+          acc[0] += __uint_as_float(raw[b].x); acc[1] += __uint_as_float(raw[b].y);
+          acc[2] += __uint_as_float(raw[b].z); acc[3] += __uint_as_float(raw[b].w);
         }
-      } else {
-        acc[0] += __uint_as_float(raw.x); acc[1] += __uint_as_float(raw.y);
-        acc[2] += __uint_as_float(raw.z); acc[3] += __uint_as_float(raw.w);
       }
     }
-#pragma unroll
-    for (int k = 0; k < EPV; ++k) acc[k] *= scale;
-    if constexpr (DST_BF16) {
-      __nv_bfloat16* d = static_cast<__nv_bfloat16*>(dst) + v * EPV;
-      if (accumulate) {
-#pragma unroll
-        for (int k = 0; k < EPV; ++k) acc[k] += __bfloat162float(d[k]);
-      }
-#pragma unroll
-      for (int k = 0; k < EPV; k += 2) *reinterpret_cast<uint32_t*>(d + k) = pack_bf16x2(acc[k], acc[k + 1]);
-    } else {
-      float* d = static_cast<float*>(dst) + v * EPV;
-      if (accumulate) {
-#pragma unroll
-        for (int k = 0; k < EPV; ++k) acc[k] += d[k];
-      }
-#pragma unroll
-      for (int k = 0; k < EPV; k += 4) *reinterpret_cast<float4*>(d + k) = make_float4(acc[k], acc[k + 1], acc[k + 2], acc[k + 3]);
-    }
-    if (sumsq) {
-#pragma unroll
-      for (int k = 0; k < EPV; ++k) local_sq = fmaf(acc[k], acc[k], local_sq);
-    }
+    local_sq += rs_finish<EPV, DST_BF16>(acc, dst, v, scale, accumulate, sumsq != nullptr);
   }
-  if (sumsq) {
-    __shared__ float red[32];
-    local_sq = warp_sum(local_sq);
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
-    if (l == 0) red[w] = local_sq;
-    __syncthreads();
-    if (w == 0) {
-      float t = l < (blockDim.x >> 5) ? red[l] : 0.f;
-      t = warp_sum(t);
-      if (l == 0) atomicAdd(sumsq, t);
-    }
-  }
+  if (sumsq) block_atomic_sum(local_sq, sumsq);
 }
 
 // ---------------------------------------------------------------- reduce-scatter fused with the partitioned AdamW update
@@ -256,6 +277,110 @@ __global__ void allreduce_oneshot_kernel(Peers peers, size_t src_off, __nv_bfloa
     o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]); o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
     *reinterpret_cast<uint4*>(dst + vi * 8) = o;
   }
+}
+
+// ---------------------------------------------------------------- NVLS (NVSwitch multicast) collectives
+// `mc` is the multicast mapping of the SAME symmetric buffer: a multimem.ld_reduce at offset x returns the sum over every
+// rank's bytes at x, added inside the switch (each GPU receives 1x the slice instead of reading W-1 peers); a multimem.st
+// writes the value into every rank's copy.  Callers order these against the producers with the device barrier above.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const void* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+
+// reduce-scatter: rank r reduces slice r of the W*n-element buffer at `src_off` in the switch, then scale / cast /
+// accumulate / sum-of-squares exactly like the pull kernel.  U loads in flight per thread.
+template <bool SRC_BF16, bool DST_BF16>
+__global__ void nvls_reduce_scatter_kernel(const uint8_t* __restrict__ mc, size_t src_off, void* __restrict__ dst, size_t n, int rank,
+                                           float scale, int accumulate, float* __restrict__ sumsq) {
+  constexpr int EPV = SRC_BF16 ? 8 : 4;
+  constexpr int U = 4;
+  const size_t vecs = n / EPV;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const uint8_t* base = mc + src_off + static_cast<size_t>(rank) * n * (SRC_BF16 ? 2 : 4);
+  float local_sq = 0.f;
+  for (size_t v0 = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < vecs; v0 += stride * U) {
+    uint4 raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v < vecs) {
+        if constexpr (SRC_BF16) {
+          raw[u] = multimem_ld_reduce_bf16x8(base + v * 16);
+        } else {
+          const float4 f = multimem_ld_reduce_f32x4(base + v * 16);
+          raw[u] = make_uint4(__float_as_uint(f.x), __float_as_uint(f.y), __float_as_uint(f.z), __float_as_uint(f.w));
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v >= vecs) continue;
+      float acc[EPV];
+      if constexpr (SRC_BF16) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[u]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          float2 f = __bfloat1622float2(h[k]);
+          acc[2 * k] = f.x;
+          acc[2 * k + 1] = f.y;
+        }
+      } else {
+        acc[0] = __uint_as_float(raw[u].x); acc[1] = __uint_as_float(raw[u].y);
+        acc[2] = __uint_as_float(raw[u].z); acc[3] = __uint_as_float(raw[u].w);
+      }
+      local_sq += rs_finish<EPV, DST_BF16>(acc, dst, v, scale, accumulate, sumsq != nullptr);
+    }
+  }
+  if (sumsq) block_atomic_sum(local_sq, sumsq);
+}
+
+// all-reduce, in place in the symmetric buffer: rank r reduces vectors [r*per, (r+1)*per) in the switch and multicasts the
+// sums back into every rank's copy (one NVLink crossing each way per element).  bf16.
+__global__ void nvls_allreduce_kernel(uint8_t* __restrict__ mc, size_t off, size_t vecs_per_rank, int rank) {
+  constexpr int U = 4;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  uint8_t* base = mc + off + static_cast<size_t>(rank) * vecs_per_rank * 16;
+  for (size_t v0 = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v0 < vecs_per_rank; v0 += stride * U) {
+    uint4 raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v < vecs_per_rank) raw[u] = multimem_ld_reduce_bf16x8(base + v * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t v = v0 + u * stride;
+      if (v < vecs_per_rank) multimem_st_v4(base + v * 16, raw[u]);
+    }
+  }
+}
+
+// all-gather (push): this rank's `bytes` at local `src` are multicast into every rank's buffer at dst_off + rank*bytes.
+__global__ void nvls_allgather_kernel(uint8_t* __restrict__ mc, size_t dst_off, const uint8_t* __restrict__ src, size_t bytes, int rank) {
+  const size_t vecs = bytes / 16;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  uint8_t* base = mc + dst_off + static_cast<size_t>(rank) * bytes;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < vecs; v += stride)
+    multimem_st_v4(base + v * 16, ld_nc_v4(src + v * 16));
 }
 
 static int comm_grid(size_t vecs, int max_ctas) {
@@ -394,6 +519,69 @@ DSB_EXPORT int dsb200_p2p_allreduce_bf16(void* const* peer_ptrs, long long src_o
   if (rc) return rc;
   allreduce_oneshot_kernel<<<comm_grid(static_cast<size_t>(n) / 8, max_ctas), 256, 0, stream>>>(
       P, static_cast<size_t>(src_off), static_cast<__nv_bfloat16*>(dst), static_cast<size_t>(n), rank, world);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// All-gather on the copy engines: one peer -> local cudaMemcpyAsync per rank (NVLink DMA, zero SMs), staggered so that at any
+// moment the ranks read from different peers.  dst is local memory; the peers' shards sit at src_off of their symmetric buffers.
+DSB_EXPORT int dsb200_p2p_allgather_ce(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
+                                       int world, cudaStream_t stream) {
+  DSB_REQUIRE(world >= 1 && world <= MAX_RANKS, "p2p_allgather_ce: world size %d unsupported", world);
+  for (int pi = 0; pi < world; ++pi) {
+    const int peer = (pi + rank + 1) % world;  // own shard last: it is the only copy that does not cross NVLink
+    DSB_CHECK_CUDA(cudaMemcpyAsync(static_cast<uint8_t*>(dst) + static_cast<size_t>(peer) * bytes_per_rank,
+                                   static_cast<const uint8_t*>(peer_ptrs[peer]) + src_off, static_cast<size_t>(bytes_per_rank),
+                                   cudaMemcpyDeviceToDevice, stream));
+  }
+  return DSB_OK;
+}
+
+// ---- NVLS entry points.  `mc_base` = multicast mapping of the symmetric buffer (every rank bound), DEVICE pointer.
+// src dtype / dst dtype: 0 bf16, 2 fp32.  n = elements per rank (multiple of 8).
+DSB_EXPORT int dsb200_nvls_reduce_scatter(void* mc_base, long long src_off, int src_dtype, void* dst, int dst_dtype, long long n,
+                                          int rank, int world, float scale, int accumulate, float* sumsq, int max_ctas,
+                                          cudaStream_t stream) {
+  DSB_REQUIRE(mc_base != nullptr, "nvls_reduce_scatter: no multicast mapping");
+  DSB_REQUIRE(n % 8 == 0 && src_off % 16 == 0 && (n * (src_dtype == 0 ? 2 : 4)) % 16 == 0,
+              "nvls_reduce_scatter: n must be a multiple of 8 and the offset 16-byte aligned");
+  (void)world;
+  const size_t vecs = static_cast<size_t>(n) / (src_dtype == 0 ? 8 : 4);
+  const int grid = comm_grid((vecs + 3) / 4, max_ctas > 0 ? max_ctas : 64);
+  const uint8_t* mc = static_cast<const uint8_t*>(mc_base);
+  const size_t off = static_cast<size_t>(src_off);
+  if (src_dtype == 0 && dst_dtype == 0)
+    nvls_reduce_scatter_kernel<true, true><<<grid, 256, 0, stream>>>(mc, off, dst, (size_t)n, rank, scale, accumulate, sumsq);
+  else if (src_dtype == 0 && dst_dtype == 2)
+    nvls_reduce_scatter_kernel<true, false><<<grid, 256, 0, stream>>>(mc, off, dst, (size_t)n, rank, scale, accumulate, sumsq);
+  else if (src_dtype == 2 && dst_dtype == 2)
+    nvls_reduce_scatter_kernel<false, false><<<grid, 256, 0, stream>>>(mc, off, dst, (size_t)n, rank, scale, accumulate, sumsq);
+  else {
+    set_last_error("nvls_reduce_scatter: unsupported dtype combination %d -> %d", src_dtype, dst_dtype);
+    return DSB_ERR_UNSUPPORTED;
+  }
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// In-place bf16 all-reduce of n elements at `off` (n % (8*world) == 0).  The caller brackets it with dsb200_symm_barrier.
+DSB_EXPORT int dsb200_nvls_allreduce_bf16(void* mc_base, long long off, long long n, int rank, int world, int max_ctas,
+                                          cudaStream_t stream) {
+  DSB_REQUIRE(mc_base != nullptr, "nvls_allreduce: no multicast mapping");
+  DSB_REQUIRE(world > 0 && n % (8LL * world) == 0 && off % 16 == 0, "nvls_allreduce: n must be a multiple of 8*world, offset 16-byte aligned");
+  const size_t per = static_cast<size_t>(n) / 8 / world;
+  nvls_allreduce_kernel<<<comm_grid((per + 3) / 4, max_ctas > 0 ? max_ctas : 64), 256, 0, stream>>>(
+      static_cast<uint8_t*>(mc_base), static_cast<size_t>(off), per, rank);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_nvls_allgather(void* mc_base, long long dst_off, const void* src, long long bytes, int rank, int max_ctas,
+                                     cudaStream_t stream) {
+  DSB_REQUIRE(mc_base != nullptr, "nvls_allgather: no multicast mapping");
+  DSB_REQUIRE(bytes % 16 == 0 && dst_off % 16 == 0, "nvls_allgather: sizes/offsets must be multiples of 16 bytes");
+  nvls_allgather_kernel<<<comm_grid(static_cast<size_t>(bytes) / 16, max_ctas > 0 ? max_ctas : 64), 256, 0, stream>>>(
+      static_cast<uint8_t*>(mc_base), static_cast<size_t>(dst_off), static_cast<const uint8_t*>(src), static_cast<size_t>(bytes), rank);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

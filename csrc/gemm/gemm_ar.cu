@@ -47,10 +47,7 @@ struct Params {
   int row_lo, row_hi;  // rows this rank reduces and writes: [0, M) = all-reduce, its own slice = reduce-scatter; out row = r - row_lo
 };
 
-__device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
+__device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) { mbar_wait_lean(bar, parity); }
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }

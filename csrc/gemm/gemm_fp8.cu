@@ -33,10 +33,7 @@ struct Params {
   const float* sb;  // [N] or nullptr (= 1)
 };
 
-__device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
+__device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) { mbar_wait_lean(bar, parity); }
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_fp8_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,

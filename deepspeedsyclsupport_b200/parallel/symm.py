@@ -27,6 +27,10 @@ native.register_sigs({
     "dsb200_p2p_reduce_scatter": "p l i p i l ii f i p i p",
     "dsb200_p2p_rs_adam": "p l pppp l ii f fffff iii i p",
     "dsb200_p2p_allreduce_bf16": "p l p l iii p",
+    "dsb200_p2p_allgather_ce": "p l p l ii p",
+    "dsb200_nvls_reduce_scatter": "p l i p i l ii f i p i p",
+    "dsb200_nvls_allreduce_bf16": "p l l ii i p",
+    "dsb200_nvls_allgather": "p l p l i i p",
 })
 
 FLAG_PAD = 4096
@@ -38,6 +42,11 @@ class _RawCudaArray:
 
     def __init__(self, ptr, nbytes):
         self.__cuda_array_interface__ = {"shape": (nbytes, ), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+def os_env_flag(name):
+    import os
+    return os.environ.get(name, "0") == "1"
 
 
 def _alias(ptr, nbytes, device):
@@ -61,9 +70,47 @@ class _PeerOps:
         assert offset + nbytes <= self.nbytes, "symmetric buffer overflow"
         base = self.ptrs[self.rank if rank is None else rank]
         key = (base, offset, nbytes, dtype)
-        raw = _alias(base + offset, nbytes, self.device)
-        self._keep.append(raw)
-        return raw.view(dtype).view(*shape)
+        flat = self._views.get(key)
+        if flat is None:
+            flat = self._views[key] = _alias(base + offset, nbytes, self.device).view(dtype)
+        return flat.view(*shape)
+
+    mc_ptr = 0  # multicast (NVLS) mapping of the buffer; 0 = not available
+
+    def all_gather_ce(self, out, src_offset, bytes_per_rank, rank=None):
+        """All-gather on the copy engines (peer -> local DMA per rank, no SMs): the form used under compute."""
+        r = self.rank if rank is None else rank
+        rc = native.lib().dsb200_p2p_allgather_ce(ctypes.cast(self._table(), ctypes.c_void_p), src_offset, native.ptr(out),
+                                                  bytes_per_rank, r, self.world, native.stream_ptr())
+        native.check(rc)
+        return out
+
+    def nvls_reduce_scatter(self, dst, src_offset, src_dtype, n_per_rank, scale=1.0, accumulate=False, sumsq=None, max_ctas=0):
+        """Reduce-scatter through the NVSwitch: `multimem.ld_reduce` over the multicast mapping sums slice `rank` of every
+        rank's buffer inside the switch, so this GPU receives n elements instead of reading (W-1)*n from peers."""
+        assert self.mc_ptr, "no multicast mapping for this buffer"
+        rc = native.lib().dsb200_nvls_reduce_scatter(self.mc_ptr, src_offset, _DT[src_dtype], native.ptr(dst), _DT[dst.dtype],
+                                                     n_per_rank, self.rank, self.world, float(scale), int(accumulate),
+                                                     native.ptr(sumsq), max_ctas, native.stream_ptr())
+        native.check(rc)
+        return dst
+
+    def nvls_all_reduce_bf16(self, offset, n, max_ctas=0):
+        """In-place bf16 all-reduce of the n elements at `offset` of every rank's buffer (ld_reduce + multicast store)."""
+        assert self.mc_ptr, "no multicast mapping for this buffer"
+        self.barrier()  # every rank's addend is written
+        rc = native.lib().dsb200_nvls_allreduce_bf16(self.mc_ptr, offset, n, self.rank, self.world, max_ctas, native.stream_ptr())
+        native.check(rc)
+        self.barrier()  # every slice's sums have landed everywhere
+
+    def nvls_all_gather(self, dst_offset, src, max_ctas=0):
+        """Push all-gather: `src` (local, contiguous) is multicast-stored into every rank's buffer at dst_offset + rank*nbytes.
+        The caller runs `barrier()` before readers consume it."""
+        assert self.mc_ptr, "no multicast mapping for this buffer"
+        nbytes = src.numel() * src.element_size()
+        rc = native.lib().dsb200_nvls_allgather(self.mc_ptr, dst_offset, native.ptr(src), nbytes, self.rank, max_ctas,
+                                                native.stream_ptr())
+        native.check(rc)
 
     def all_gather(self, out, src_offset, bytes_per_rank, rank=None, max_ctas=0):
         r = self.rank if rank is None else rank
@@ -124,16 +171,72 @@ class _PeerOps:
 
 
 class SymmetricBuffer(_PeerOps):
+    """backend: "torch" = torch.distributed._symmetric_memory (CUDA VMM allocation, also bound to an NVSwitch multicast
+    object when the fabric supports it -> `mc_ptr` for the NVLS kernels); "ipc" = cudaMalloc + CUDA-IPC handles (P2P only).
+    Default: DSB200_SYMM_BACKEND, else "torch" with a fall-back to "ipc"."""
 
-    def __init__(self, group, nbytes):
+    def __init__(self, group, nbytes, backend=None):
+        import os
         assert torch.cuda.is_available()
         self.group = group
         self.world = dist.get_world_size(group)
         self.rank = dist.get_rank(group)
         self.nbytes = (int(nbytes) + 255) // 256 * 256
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self._keep = []
+        self._views = {}
         self._epoch = 0
+        self._opened = []
+        self.local_ptr = None
+        self.mc_ptr = 0
+        backend = backend or os.environ.get("DSB200_SYMM_BACKEND", "torch")
+        self.backend = None
+        if backend == "torch":
+            ok = 0
+            try:
+                self._init_torch(group)
+                ok = 1
+            except Exception as e:  # allocator / rendezvous not available on this stack
+                self._torch_error = f"{type(e).__name__}: {e}"
+            # the choice is collective: one rank without it moves every rank to the IPC flavour
+            flag = torch.tensor([ok], dtype=torch.int32, device=self.device)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+            if int(flag.item()) == 1:
+                self.backend = "torch"
+            else:
+                self._symm_tensor = self._symm_handle = None
+                self.mc_ptr = 0
+        if self.backend is None:
+            self._init_ipc(group)
+            self.backend = "ipc"
+        dist.barrier(group=group)
+
+    def _init_torch(self, group):
+        import torch.distributed as tdist
+        import torch.distributed._symmetric_memory as symm_mem
+        pg = group if group is not None else tdist.group.WORLD
+        t = symm_mem.empty(self.nbytes + FLAG_PAD, dtype=torch.uint8, device=self.device)
+        t.zero_()
+        torch.cuda.synchronize()
+        hdl = symm_mem.rendezvous(t, pg)
+        self._symm_tensor, self._symm_handle = t, hdl
+        off = int(getattr(hdl, "offset", 0) or 0)  # the tensor may sit inside a larger symmetric allocation
+        self.ptrs = [int(p) + off for p in hdl.buffer_ptrs]
+        if self.ptrs[self.rank] != t.data_ptr():
+            off = t.data_ptr() - int(hdl.buffer_ptrs[self.rank])
+            self.ptrs = [int(p) + off for p in hdl.buffer_ptrs]
+        assert len(self.ptrs) == self.world and 0 <= off and off % 256 == 0
+        self.local_ptr = None
+        mc = 0
+        if not os_env_flag("DSB200_DISABLE_NVLS"):
+            try:
+                mc = int(hdl.multicast_ptr or 0)
+                if mc:
+                    mc += off
+            except Exception:
+                mc = 0
+        self.mc_ptr = mc
+
+    def _init_ipc(self, group):
         lib = native.lib()
         ptr = ctypes.c_void_p()
         handle = (ctypes.c_ubyte * 64)()
@@ -143,7 +246,6 @@ class SymmetricBuffer(_PeerOps):
         handles = [None] * self.world
         dist.all_gather_object(handles, bytes(handle), group=group)
         self.ptrs = []
-        self._opened = []
         for r, h in enumerate(handles):
             if r == self.rank:
                 self.ptrs.append(self.local_ptr)
@@ -154,7 +256,6 @@ class SymmetricBuffer(_PeerOps):
             native.check(rc, 0)
             self.ptrs.append(p.value)
             self._opened.append(p.value)
-        dist.barrier(group=group)
 
     def barrier(self):
         """Device-side barrier across the group on the current stream (no host sync)."""
@@ -172,6 +273,8 @@ class SymmetricBuffer(_PeerOps):
         if self.local_ptr:
             lib.dsb200_symm_free(self.local_ptr)
             self.local_ptr = None
+        self._views = {}
+        self._symm_tensor = self._symm_handle = None
 
 
 class EmulatedPeers(_PeerOps):
@@ -182,7 +285,7 @@ class EmulatedPeers(_PeerOps):
         self.rank = 0
         self.nbytes = (int(nbytes) + 255) // 256 * 256
         self.device = torch.device("cuda", torch.cuda.current_device())
-        self._keep = []
+        self._views = {}
         self._bufs = [torch.zeros(self.nbytes + FLAG_PAD, dtype=torch.uint8, device=self.device) for _ in range(world)]
         self.ptrs = [b.data_ptr() for b in self._bufs]
 
@@ -200,7 +303,7 @@ class PeerAllToAll(object):
 
     @classmethod
     def for_group(cls, group, nbytes):
-        key = id(group) if group is not None else 0
+        key = tuple(dist.get_all_ranks_from_group(group)) if group is not None and hasattr(dist, "get_all_ranks_from_group") else group
         inst = cls._instances.get(key)
         if inst is None or inst.buf.nbytes < nbytes:
             if inst is not None:

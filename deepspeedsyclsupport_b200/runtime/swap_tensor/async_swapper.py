@@ -1,175 +1,146 @@
-"""Asynchronous swap-out of many small tensors through a few large pinned staging buffers (parity:
-deepspeed/runtime/swap_tensor/async_swapper.py:19-176).
+"""Write-behind of many small tensors to files through a few large pinned staging buffers.
 
-Typical use: gradient partitions leaving for NVMe while backward keeps producing more.  Tensors are packed back to back (each
-start aligned for O_DIRECT) into the current staging buffer; a full buffer is handed to the AIO engine -- one write per tensor,
-from its slice of the buffer to its own file -- and packing continues in the next buffer.  Only when every buffer is in flight
-does the caller wait."""
+Role of the reference's deepspeed/runtime/swap_tensor/async_swapper.py:19-176 (gradient partitions leaving for NVMe while
+backward keeps producing more), built differently: the staging buffers form a pipeline
+
+    idle  --open-->  filling  --seal-->  (writes submitted) in flight  --aio wait-->  idle
+
+kept as three deques of `_Stage` objects.  A tensor is appended to the filling stage at an offset aligned for O_DIRECT; when it
+does not fit, the stage is sealed (one AIO write per packed tensor, slice of the pinned buffer -> its own file) and the next
+idle stage is opened.  The caller only blocks in `aio_handle.wait()` when no idle stage is left, or when it takes the buffers
+back with `release_buffers()`.
+"""
+from collections import deque
+
 import torch
 
 from ...utils.logging import logger
 from .utils import MIN_AIO_BYTES, swap_out_tensors
 
-INVALID_BUFFER_INDEX = -1
 ASYNC_SWAPPER_WAIT_TIMER = "async_swap_gradient_wait"
 
 
-class _Staging:
-    """One pinned buffer with an append cursor and the (slice, path) pairs packed into it."""
+class _Stage:
+    """A pinned buffer plus what has been packed into it since it was opened."""
+    __slots__ = ("buffer", "cursor", "slices", "files", "payload")
 
     def __init__(self, buffer):
         self.buffer = buffer
-        self.reset()
+        self.open()
 
-    def reset(self):
-        self.offset, self.tensors, self.paths, self.num_elem = 0, [], [], 0
+    def open(self):
+        self.cursor, self.slices, self.files, self.payload = 0, [], [], 0
 
-    def has_space(self, numel):
-        return self.offset + numel <= self.buffer.numel()
+    def fits(self, span):
+        return self.cursor + span <= self.buffer.numel()
 
-    def insert(self, tensor, path, aligned_numel):
-        dst = self.buffer.narrow(0, self.offset, aligned_numel)
-        dst.narrow(0, 0, tensor.numel()).copy_(tensor.reshape(-1))
-        self.tensors.append(dst)
-        self.paths.append(path)
-        self.offset += aligned_numel
-        self.num_elem += tensor.numel()
+    def pack(self, tensor, path, span):
+        window = self.buffer.narrow(0, self.cursor, span)
+        window[:tensor.numel()].copy_(tensor.reshape(-1))
+        self.slices.append(window)
+        self.files.append(path)
+        self.cursor += span
+        self.payload += tensor.numel()
 
 
 class AsyncTensorSwapper(object):
 
     def __init__(self, aio_handle, numel_alignment, timers=None):
-        self.free_buffer_index = []
-        self.swapping_buffer_index = []
-        self.ready_buffer_index = []
-        self.current_buffer_index = INVALID_BUFFER_INDEX
-        self.all_buffers = []
         self.aio_handle = aio_handle
         self.numel_alignment = numel_alignment
-        self.max_numel = 0
-        self.num_pending_swaps = 0
         self.timers = timers
-        self.timer_names = set()
+        self._idle, self._inflight, self._filling = deque(), deque(), None
+        self._writes_pending = 0
+        self._timer_names = set()
         self.num_elements_swapped = 0
+        self.max_numel = 0
         self.dtype = None
 
+    # ---- buffer ownership
     def has_buffers(self):
-        return len(self.all_buffers) > 0
+        return self._filling is not None or bool(self._idle) or bool(self._inflight)
 
     def add_buffers(self, buffer_list):
-        assert len(self.all_buffers) == 0 and all(b.device.type == "cpu" for b in buffer_list)
-        dtype = buffer_list[0].dtype
-        assert all(b.dtype == dtype for b in buffer_list)
-        self.dtype = dtype
-        self.all_buffers = [_Staging(b) for b in buffer_list]
-        self.free_buffer_index = list(range(len(self.all_buffers)))
+        assert not self.has_buffers(), "release_buffers() before handing in a new set"
+        assert buffer_list and all(b.device.type == "cpu" and b.dtype == buffer_list[0].dtype for b in buffer_list)
+        self.dtype = buffer_list[0].dtype
         self.max_numel = max(b.numel() for b in buffer_list)
-        self.timer_names = set()
-
-    def get_timer_names(self):
-        return list(self.timer_names)
+        self._idle.extend(_Stage(b) for b in buffer_list)
+        self._timer_names = set()
 
     def release_buffers(self):
-        """Write out whatever is packed, wait for everything in flight and give the pinned buffers back."""
-        self._report_statistics("Swapped out[Before flush]")
-        self._flush_buffers_until_complete()
-        self._report_statistics("Swapped out[After flush]")
-        buffers = [s.buffer for s in self.all_buffers]
-        self.all_buffers, self.free_buffer_index, self.current_buffer_index = [], [], INVALID_BUFFER_INDEX
-        self.num_elements_swapped = 0
-        self.dtype = None
+        """Submit what is packed, wait for every write, and hand the pinned buffers back to the caller."""
+        self._log_volume("before flush")
+        self._drain()
+        self._log_volume("after flush")
+        buffers = [s.buffer for s in self._idle]
+        self._idle.clear()
+        self.num_elements_swapped, self.dtype, self.max_numel = 0, None, 0
         return buffers
 
-    def swap_out_tensors(self, tensor_list, path_list):
-        for tensor, path in zip(tensor_list, path_list):
-            self._swap_out_tensor(tensor, path)
+    def get_timer_names(self):
+        return sorted(self._timer_names)
 
-    # ---- internals
-    def _report_statistics(self, message):
-        if self.dtype is not None and self.num_elements_swapped:
-            gb = self.num_elements_swapped * torch.empty((), dtype=self.dtype).element_size() / 1024**3
-            logger.debug(f"{message} num_elems = {self.num_elements_swapped}, {gb:5.2f} GB")
+    # ---- producer side
+    def swap_out_tensors(self, tensor_list, path_list):
+        assert self.has_buffers(), "add_buffers() first"
+        for tensor, path in zip(tensor_list, path_list):
+            span = self._io_aligned_numel(tensor.numel())
+            assert span <= self.max_numel, f"a tensor of {tensor.numel()} elements does not fit a staging buffer of {self.max_numel}"
+            self._stage_for(span).pack(tensor, path, span)
 
     def _io_aligned_numel(self, numel):
-        r = numel % self.numel_alignment
-        return numel if r == 0 else numel + self.numel_alignment - r
+        a = self.numel_alignment
+        return (numel + a - 1) // a * a
 
-    def _swap_out_tensor(self, tensor, swap_path):
-        assert len(self.all_buffers) > 0, "add_buffers first"
-        aligned = self._io_aligned_numel(tensor.numel())
-        assert aligned <= self.max_numel, f"tensor of {tensor.numel()} elements does not fit a staging buffer of {self.max_numel}"
-        self._make_swap_space(aligned)
-        self._get_current_buffer().insert(tensor, swap_path, aligned)
+    def _stage_for(self, span):
+        """The filling stage if `span` fits, otherwise seal it and open the next one (waiting for writes only if none is idle)."""
+        if self._filling is not None and self._filling.fits(span):
+            return self._filling
+        self._seal()
+        if not self._idle:
+            self._wait_writes()
+        self._filling = self._idle.popleft()
+        self._filling.open()
+        return self._filling
 
-    def _make_swap_space(self, numel):
-        if self.current_buffer_index == INVALID_BUFFER_INDEX:
-            self._allocate_buffer()
+    # ---- pipeline transitions
+    def _seal(self):
+        stage, self._filling = self._filling, None
+        if stage is None:
             return
-        if not self._get_current_buffer().has_space(numel):
-            # the current buffer is full: it becomes ready; start its writes if a free buffer lets packing continue
-            if self.free_buffer_index:
-                self._flush_ready_buffers()
-            else:
-                self._flush_buffers_until_complete()
-            self._allocate_buffer()
+        if stage.slices:
+            swap_out_tensors(self.aio_handle, stage.slices, stage.files)
+            self._writes_pending += len(stage.slices)
+        self._inflight.append(stage)
 
-    def _allocate_buffer(self):
-        assert self.current_buffer_index == INVALID_BUFFER_INDEX and self.free_buffer_index
-        self.current_buffer_index = self.free_buffer_index.pop()
-        self._get_current_buffer().reset()
-
-    def _flush_ready_buffers(self):
-        if self.current_buffer_index != INVALID_BUFFER_INDEX:
-            self.ready_buffer_index.append(self.current_buffer_index)
-            self.current_buffer_index = INVALID_BUFFER_INDEX
-        self._swap_out_ready_buffers()
-
-    def _flush_buffers_until_complete(self):
-        self._flush_ready_buffers()
-        assert len(self.ready_buffer_index) == 0
-        self._wait_for_swap_complete()
-        assert len(self.swapping_buffer_index) == 0 and len(self.free_buffer_index) == len(self.all_buffers)
-
-    def _swap_out_ready_buffers(self):
-        for idx in self.ready_buffer_index:
-            s = self.all_buffers[idx]
-            if s.tensors:
-                swap_out_tensors(self.aio_handle, s.tensors, s.paths)
-                self.num_pending_swaps += len(s.tensors)
-        self.swapping_buffer_index += self.ready_buffer_index
-        self.ready_buffer_index = []
-
-    def _wait_for_swap_complete(self):
-        self._start_timer(ASYNC_SWAPPER_WAIT_TIMER)
-        if self.num_pending_swaps:
+    def _wait_writes(self):
+        self._timed(True)
+        if self._writes_pending:
             self.aio_handle.wait()
-        self._stop_timer(ASYNC_SWAPPER_WAIT_TIMER)
-        self.timer_names.add(ASYNC_SWAPPER_WAIT_TIMER)
-        self.num_pending_swaps = 0
-        for idx in self.swapping_buffer_index:
-            self.num_elements_swapped += self.all_buffers[idx].num_elem
-            self.all_buffers[idx].reset()
-        self.free_buffer_index += self.swapping_buffer_index
-        self.swapping_buffer_index = []
+        self._timed(False)
+        self._writes_pending = 0
+        while self._inflight:
+            stage = self._inflight.popleft()
+            self.num_elements_swapped += stage.payload
+            stage.open()
+            self._idle.append(stage)
 
-    def _get_buffer(self, index):
-        assert index != INVALID_BUFFER_INDEX
-        return self.all_buffers[index]
+    def _drain(self):
+        self._seal()
+        self._wait_writes()
 
-    def _get_current_buffer(self):
-        return self._get_buffer(self.current_buffer_index)
-
-    def _start_timer(self, name):
+    # ---- diagnostics
+    def _timed(self, start):
         if self.timers:
-            self.timers(name).start()
+            t = self.timers(ASYNC_SWAPPER_WAIT_TIMER)
+            t.start() if start else t.stop()
+            self._timer_names.add(ASYNC_SWAPPER_WAIT_TIMER)
 
-    def _stop_timer(self, name):
-        if self.timers:
-            self.timers(name).stop()
-
-    def _log_timers(self, name_list, force=False):
-        if self.timers and force:
-            self.timers.log(name_list)
+    def _log_volume(self, when):
+        if self.dtype is not None and self.num_elements_swapped:
+            gib = self.num_elements_swapped * torch.empty((), dtype=self.dtype).element_size() / 2 ** 30
+            logger.debug(f"async swap-out [{when}]: {self.num_elements_swapped} elements, {gib:.2f} GiB")
 
 
 __all__ = ["AsyncTensorSwapper", "MIN_AIO_BYTES"]

@@ -413,6 +413,14 @@ class ZeroShardedOptimizer:
             self._p2p_reduce_count = 0
             self._p2p_barrier_events = {}
             self._p2p_sumsq = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self._p2p_shards_synced = False
+            self._p2p_ag_mode = os.environ.get("DSB200_AG_MODE", "ce")       # ce = copy engines, sm = pull kernel
+            self._p2p_rs_mode = os.environ.get("DSB200_RS_MODE", "nvls" if self.p2p.mc_ptr else "pull")
+            if self._p2p_rs_mode == "nvls" and not self.p2p.mc_ptr:
+                self._p2p_rs_mode = "pull"
+            self._p2p_comm_ctas = int(os.environ.get("DSB200_COMM_CTAS", "0"))
+            logger.info(f"ZeRO-3 peer-memory collectives: backend={self.p2p.backend} all-gather={self._p2p_ag_mode} "
+                        f"reduce-scatter={self._p2p_rs_mode}")
             self.comm_dtype = torch.bfloat16
         except Exception as e:  # pragma: no cover - peer access unavailable: keep the NCCL path
             logger.warning(f"peer-memory collectives unavailable ({e}); using NCCL")
@@ -426,7 +434,9 @@ class ZeroShardedOptimizer:
         self._p2p_next_slot += 1
         need = n - self.P2P_GRAD_SLOTS + 1
         if need >= 0 and need in self._p2p_barrier_events:
+            t = self._probe_begin("grad_slot_wait")
             torch.cuda.current_stream().wait_event(self._p2p_barrier_events[need])
+            self._probe_end(t)
         u.p2p_slot = k
         buf = self._p2p_slot_views[k][:u.padded]
         # the slot still holds another unit's gradients: parameters overwrite their slices on first touch (ds_grad_fresh),
@@ -449,9 +459,10 @@ class ZeroShardedOptimizer:
             self._p2p_reduce_count += 1
             dst = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
             fuse_norm = self.gas == 1
-            self.p2p.reduce_scatter(dst, self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes, torch.bfloat16, u.shard_numel,
-                                    scale=1.0 / self.grad_divisor, accumulate=self.gas > 1,
-                                    sumsq=self._p2p_sumsq if fuse_norm else None)
+            rs = self.p2p.nvls_reduce_scatter if self._p2p_rs_mode == "nvls" else self.p2p.reduce_scatter
+            rs(dst, self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes, torch.bfloat16, u.shard_numel,
+               scale=1.0 / self.grad_divisor, accumulate=self.gas > 1, sumsq=self._p2p_sumsq if fuse_norm else None,
+               max_ctas=self._p2p_comm_ctas)
         u.full_grad = None
         u.reduced = True
 
@@ -641,7 +652,9 @@ class ZeroShardedOptimizer:
             elif self.shard_world == 1 and self.replica_world > 1 and not u.reduced:
                 self._reduce_unit(u)
         if self.overlap_comm:
+            t = self._probe_begin("reduce_drain")
             torch.cuda.current_stream().wait_stream(self.rs_stream)
+            self._probe_end(t)
         if boundary_only and self.grad_full_persistent is not None:
             self.grad_full_persistent.zero_()
 
@@ -681,10 +694,12 @@ class ZeroShardedOptimizer:
             return
         stream = self.ag_stream if self.cuda else None
         ctx = torch.cuda.stream(stream) if stream is not None else _nullctx()
+        main = torch.cuda.current_stream() if self.cuda else None
         with ctx:
             u.full = torch.empty(u.padded, dtype=self.dtype, device=self.device)
             if self.p2p is not None:
-                self.p2p.all_gather(u.full, self._p2p_lp_off + u.shard_off * 2, u.shard_numel * 2)
+                self._p2p_sync_shards(stream, main)
+                self._p2p_gather_unit(u)
             elif self.zero_config.zero_quantized_weights and self.cuda:
                 from .zeropp import quantized_all_gather
                 quantized_all_gather(u.full, u.shard.to(self.device, non_blocking=True) if self.offload_param else u.shard, self.shard_group)
@@ -694,6 +709,35 @@ class ZeroShardedOptimizer:
                 u.gather_event = torch.cuda.Event()
                 u.gather_event.record(stream)
         u.status = ZeroParamStatus.INFLIGHT
+
+    P2P_CE_MIN_BYTES = 1 << 20
+
+    def _p2p_gather_unit(self, u):
+        """Pull every rank's shard of `u` into u.full.  Large shards go over the copy engines (NVLink DMA, no SMs: the
+        persistent GEMMs keep all 148 SMs); small ones (norm weights) use one pull kernel, cheaper than W tiny DMAs."""
+        nbytes = u.shard_numel * 2
+        off = self._p2p_lp_off + u.shard_off * 2
+        if nbytes >= self.P2P_CE_MIN_BYTES and self._p2p_ag_mode == "ce":
+            self.p2p.all_gather_ce(u.full, off, nbytes)
+        else:
+            self.p2p.all_gather(u.full, off, nbytes, max_ctas=self._p2p_comm_ctas)
+
+    def _p2p_shards_written(self):
+        """Call after writing this rank's 16-bit shard outside step() (write-back of gathered parameters, checkpoint load,
+        safe_set_*): peers pull shards with one-sided loads, so the next gather must first pass a cross-rank barrier that is
+        stream-ordered after the write.  The write sites are collective by contract, so every rank re-arms together."""
+        self._p2p_shards_synced = False
+
+    def _p2p_sync_shards(self, stream, main):
+        """Device barrier (once per pass, and after any out-of-step shard write) before the first one-sided pull: a faster
+        rank must not read a shard its owner is still writing.  Runs on the gather stream, ordered after everything the
+        compute stream `main` has enqueued (the shard writes)."""
+        if self._p2p_shards_synced:
+            return
+        if stream is not None and main is not None:
+            stream.wait_stream(main)
+        self.p2p.barrier()
+        self._p2p_shards_synced = True
 
     def _gather_unit_into(self, full, u):
         """full[padded] <- every rank's shard of the unit (host-resident shards are staged to the device first)."""
@@ -711,10 +755,45 @@ class ZeroShardedOptimizer:
         if u.status == ZeroParamStatus.NOT_AVAILABLE:
             self._launch_gather(u)
         if u.gather_event is not None:
+            t = self._probe_begin("gather_wait")
             torch.cuda.current_stream().wait_event(u.gather_event)
+            self._probe_end(t)
             u.full.record_stream(torch.cuda.current_stream())
             u.gather_event = None
         u.bind_params()
+
+    # ---- exposed-communication probe: CUDA-event pairs around every point where the compute stream waits for, or itself
+    # runs, communication.  Off by default (no events recorded); bench.py turns it on for a separate measurement phase.
+    _probe = None
+
+    def comm_probe_start(self):
+        self._probe = []
+
+    def comm_probe_stop(self, detail=False):
+        """-> total milliseconds the compute stream spent stalled on / executing communication since comm_probe_start()
+        (detail=True: also {site: ms} for gather_wait / grad_slot_wait / reduce_drain / grad_norm / post_step)."""
+        pairs, self._probe = self._probe or [], None
+        if self.cuda:
+            torch.cuda.synchronize()
+        by_site = {}
+        for site, a, b in pairs:
+            by_site[site] = by_site.get(site, 0.0) + a.elapsed_time(b)
+        total = float(sum(by_site.values()))
+        return (total, by_site) if detail else total
+
+    def _probe_begin(self, site="other"):
+        if self._probe is None or not self.cuda:
+            return None
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return site, e
+
+    def _probe_end(self, t):
+        if t is None:
+            return
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record()
+        self._probe.append((t[0], t[1], e1))
 
     def release_unit(self, u):
         if self.keep_full or u.persistent or u.status == ZeroParamStatus.NOT_AVAILABLE:
@@ -729,6 +808,8 @@ class ZeroShardedOptimizer:
         lo, hi = u.shard_range()
         if u.full is not None and u.full.data_ptr() != u.shard.data_ptr():
             u.shard.copy_(u.full[lo:hi])
+            if self.p2p is not None:
+                self._p2p_shards_written()
         self._refresh_master(u.shard_off, u.shard_off + u.shard_numel)
 
     def _refresh_master(self, lo, hi):
@@ -780,6 +861,8 @@ class ZeroShardedOptimizer:
         return self._fwd_keep.get(u.uid, False)
 
     def _end_of_pass(self):
+        if self.p2p is not None:
+            self._p2p_shards_synced = False  # the next pass (or step()'s own barrier) re-synchronises before any pull
         if not self._trace_frozen and self._trace["fwd"]:
             self._trace_frozen = True
         self._trace_pos = {"fwd": 0, "bwd": 0}
@@ -914,14 +997,18 @@ class ZeroShardedOptimizer:
     def step(self, closure=None):
         if self.begin_step():
             return
+        t = self._probe_begin("grad_norm") if self.shard_world * self.replica_world > 1 else None
         norm = self._compute_global_norm()
+        self._probe_end(t)
         self.finish_step(norm)
 
     def begin_step(self):
         """Overflow handling + loss-scale update.  Returns True when the step must be skipped."""
         self.micro_step_id = 0
         if self.overlap_comm or self.p2p is not None:
+            t = self._probe_begin("reduce_drain")
             torch.cuda.current_stream().wait_stream(self.rs_stream)
+            self._probe_end(t)
         self.overflow = self._check_overflow()
         self._prev_scale = self.loss_scale
         if not self.custom_loss_scaler:
@@ -943,7 +1030,9 @@ class ZeroShardedOptimizer:
         self._inv_scale.copy_(inv)
         self._step_count += 1
         self._optimizer_step()
+        t = self._probe_begin("post_step") if self.shard_world * self.replica_world > 1 else None
         self._post_step()
+        self._probe_end(t)
         self.zero_grad()
 
     def _hyper(self, gi):
@@ -1119,9 +1208,10 @@ class ZeroShardedOptimizer:
         if self.p2p is not None:
             # peers may pull the updated shards only after every rank finished its step: device barrier, no host sync
             self.p2p.barrier()
+            self._p2p_shards_synced = True
             for u in self.units:
                 if u.persistent:
-                    self.p2p.all_gather(u.full, self._p2p_lp_off + u.shard_off * 2, u.shard_numel * 2)
+                    self._p2p_gather_unit(u)
             self.ag_stream.wait_stream(torch.cuda.current_stream())
             self._p2p_next_slot = 0
             self._p2p_reduce_count = 0
@@ -1207,6 +1297,8 @@ class ZeroShardedOptimizer:
             self.lp_shard[lo:hi].copy_(v)
         self._scatter_param_to_flat(p, value.to(self.device), setter)
         u = p.ds_unit
+        if self.p2p is not None:
+            self._p2p_shards_written()  # on every rank, whether or not it owns a piece of p
         if self.keep_full and self.shard_world > 1:
             dist.all_gather_into_tensor(u.full, u.shard, group=self.shard_group)
         elif u.persistent and (self.shard_world > 1 or self.offload_param):

@@ -136,6 +136,20 @@ int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, floa
                        int adamw_mode, int bias_correction, int step, int max_ctas, dsb200_stream_t stream);
 int dsb200_p2p_allreduce_bf16(void* const* peer_ptrs, long long src_off, void* dst, long long n, int rank, int world,
                               int max_ctas, dsb200_stream_t stream);
+/* All-gather on the copy engines: one peer -> local cudaMemcpyAsync per rank (NVLink DMA, zero SMs), staggered so that at any
+ * moment the ranks read from different peers.  dst is local memory; the peers' shards sit at src_off of their symmetric buffers. */
+int dsb200_p2p_allgather_ce(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
+                            int world, dsb200_stream_t stream);
+/* ---- NVLS entry points.  `mc_base` = multicast mapping of the symmetric buffer (every rank bound), DEVICE pointer.
+ * src dtype / dst dtype: 0 bf16, 2 fp32.  n = elements per rank (multiple of 8). */
+int dsb200_nvls_reduce_scatter(void* mc_base, long long src_off, int src_dtype, void* dst, int dst_dtype, long long n,
+                               int rank, int world, float scale, int accumulate, float* sumsq, int max_ctas,
+                               dsb200_stream_t stream);
+/* In-place bf16 all-reduce of n elements at `off` (n % (8*world) == 0).  The caller brackets it with dsb200_symm_barrier. */
+int dsb200_nvls_allreduce_bf16(void* mc_base, long long off, long long n, int rank, int world, int max_ctas,
+                               dsb200_stream_t stream);
+int dsb200_nvls_allgather(void* mc_base, long long dst_off, const void* src, long long bytes, int rank, int max_ctas,
+                          dsb200_stream_t stream);
 
 /* ---- csrc/elementwise/elementwise.cu */
 /* out[0] += sum(x[i]^2) over n elements (dtype 0 bf16 / 1 fp16 / 2 fp32).  x must be 16-byte aligned. */

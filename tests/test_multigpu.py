@@ -250,3 +250,228 @@ def _tp_fused_body():
 
 def test_init_inference_tp_uses_fused_gemm_allreduce():
     run_distributed(_tp_fused_body, world_size=2, backend="nccl")
+
+
+def _nvls_ce_body():
+    """NVLS (multimem) reduce-scatter / all-reduce / all-gather and the copy-engine all-gather against NCCL."""
+    import deepspeedsyclsupport_b200 as ds  # noqa: F401
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.parallel.symm import SymmetricBuffer
+    rank, W = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    n = 8 * 4096 * 4
+    sb = SymmetricBuffer(dist.get_world_group(), 2 * W * n * 4)
+    if rank == 0:
+        print(f"SYMM backend={sb.backend} multicast={'yes' if sb.mc_ptr else 'no'} {getattr(sb, '_torch_error', '')}", flush=True)
+    torch.manual_seed(100 + rank)
+    grad = torch.randn(W * n, device=dev).bfloat16()
+    sb.view(0, (W * n, ), torch.bfloat16).copy_(grad)
+    sb.barrier()
+    # copy-engine all-gather == NCCL all-gather
+    out = torch.empty(W * n, device=dev, dtype=torch.bfloat16)
+    sb.all_gather_ce(out, 0, n * 2)
+    ref2 = torch.empty(W * n, device=dev, dtype=torch.bfloat16)
+    dist.all_gather_into_tensor(ref2, grad[:n].contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(out, ref2)
+    ref = grad.float().clone()
+    dist.all_reduce(ref)
+    if not sb.mc_ptr:
+        sb.barrier()
+        torch.cuda.synchronize()
+        sb.close()
+        pytest.skip("no NVSwitch multicast mapping on this box: NVLS kernels not exercised")
+    # reduce-scatter with scale, fp32 and bf16 destinations, accumulate, fused sum of squares
+    sq = torch.zeros(1, device=dev)
+    dst = torch.zeros(n, device=dev)
+    sb.nvls_reduce_scatter(dst, 0, torch.bfloat16, n, scale=1.0 / W, sumsq=sq)
+    want = ref[rank * n:(rank + 1) * n] / W
+    torch.cuda.synchronize()
+    tol = 1e-2 * want.abs().max().item()  # the switch returns the sum rounded to bf16 once
+    assert (dst - want).abs().max().item() <= tol, (dst - want).abs().max()
+    assert abs(sq.item() - dst.square().sum().item()) <= 1e-3 * sq.item()
+    sb.nvls_reduce_scatter(dst, 0, torch.bfloat16, n, scale=1.0 / W, accumulate=True)
+    torch.cuda.synchronize()
+    assert (dst - 2 * want).abs().max().item() <= 2 * tol
+    dst16 = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+    sb.nvls_reduce_scatter(dst16, 0, torch.bfloat16, n, scale=1.0)
+    torch.cuda.synchronize()
+    assert (dst16.float() - want * W).abs().max().item() <= 2 * tol * W
+    # fp32 source
+    off32 = W * n * 2
+    g32 = torch.randn(W * n, device=dev)
+    sb.view(off32, (W * n, ), torch.float32).copy_(g32)
+    sb.barrier()
+    d32 = torch.zeros(n, device=dev)
+    sb.nvls_reduce_scatter(d32, off32, torch.float32, n, scale=0.5)
+    r32 = g32.clone()
+    dist.all_reduce(r32)
+    torch.cuda.synchronize()
+    assert (d32 - 0.5 * r32[rank * n:(rank + 1) * n]).abs().max().item() <= 1e-5 * r32.abs().max().item()
+    sb.barrier()
+    # in-place all-reduce
+    sb.view(0, (W * n, ), torch.bfloat16).copy_(grad)
+    sb.nvls_all_reduce_bf16(0, W * n)
+    torch.cuda.synchronize()
+    got = sb.view(0, (W * n, ), torch.bfloat16).float()
+    assert (got - ref).abs().max().item() <= 1e-2 * ref.abs().max().item()
+    # push all-gather
+    sb.barrier()
+    mine = torch.full((n, ), float(rank + 1), device=dev, dtype=torch.bfloat16)
+    sb.nvls_all_gather(0, mine)
+    sb.barrier()
+    torch.cuda.synchronize()
+    got = sb.view(0, (W, n), torch.bfloat16).float()
+    assert torch.equal(got[:, 0].cpu(), torch.arange(1, W + 1, dtype=torch.float32)) and bool((got == got[:, :1]).all())
+
+    def timed(fn, iters=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(iters):
+            fn()
+        e.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([s.elapsed_time(e) / iters], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    big = 8 * (1 << 20) * W  # elements: 16 MiB of bf16 per rank slice
+    sbb = SymmetricBuffer(dist.get_world_group(), big * 2)
+    src = torch.randn(big, device=dev).bfloat16()
+    sbb.view(0, (big, ), torch.bfloat16).copy_(src)
+    sbb.barrier()
+    o32 = torch.empty(big // W, device=dev)
+    o16 = torch.empty(big // W, device=dev, dtype=torch.bfloat16)
+    full = torch.empty(big, device=dev, dtype=torch.bfloat16)
+    t_nvls = timed(lambda: sbb.nvls_reduce_scatter(o32, 0, torch.bfloat16, big // W))
+    t_pull = timed(lambda: sbb.reduce_scatter(o32, 0, torch.bfloat16, big // W))
+    t_nccl = timed(lambda: dist.reduce_scatter_tensor(o16, src))
+    t_ce = timed(lambda: sbb.all_gather_ce(full, 0, big // W * 2))
+    t_sm = timed(lambda: sbb.all_gather(full, 0, big // W * 2))
+    t_ag_nccl = timed(lambda: dist.all_gather_into_tensor(full, src[:big // W]))
+    if rank == 0:
+        mib = big * 2 / 2**20
+        print(f"RS {mib:.0f} MiB world {W}: nvls {t_nvls:.3f} ms, pull {t_pull:.3f} ms, nccl {t_nccl:.3f} ms", flush=True)
+        print(f"AG {mib:.0f} MiB world {W}: copy-engine {t_ce:.3f} ms, pull kernel {t_sm:.3f} ms, nccl {t_ag_nccl:.3f} ms", flush=True)
+    sbb.barrier()
+    sb.barrier()
+    torch.cuda.synchronize()
+    sbb.close()
+    sb.close()
+
+
+def test_nvls_and_copy_engine_collectives_match_nccl():
+    run_distributed(_nvls_ce_body, world_size=min(torch.cuda.device_count(), 8) if torch.cuda.device_count() in (2, 4, 8) else 2,
+                    backend="nccl")
+
+
+def _zero3_train(steps, disable_p2p):
+    import os
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
+    os.environ["DSB200_DISABLE_P2P"] = "1" if disable_p2p else "0"
+    rank = dist.get_rank()
+    torch.manual_seed(0)
+    cfg = llama_config("tiny", hidden_size=256, intermediate_size=768, num_attention_heads=2, num_key_value_heads=2,
+                       num_hidden_layers=3, vocab_size=1024, activation_checkpointing=False)
+    model = LlamaForCausalLM(cfg).cuda().bfloat16()
+    # eps far above the gradient scale makes AdamW respond linearly to small gradients (update ~ lr * g / eps) instead of
+    # turning the bf16 / atomic-order noise of near-zero gradients into +-lr steps, so parameter differences between the two
+    # runs measure the communication path and not the optimizer's sign amplification
+    engine, _, _, _ = deepspeed.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "eps": 1e-1, "weight_decay": 0.0}},
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}})
+    opt = engine.optimizer
+    assert (opt.p2p is None) == bool(disable_p2p)
+    init = {n: opt.get_full_fp32_param(p).float().cpu() for n, p in model.named_parameters()}
+    g = torch.Generator().manual_seed(5 + rank)
+    ids = torch.randint(0, 1024, (2, 128), generator=g).cuda()
+    labels = torch.randint(0, 1024, (2, 128), generator=g).cuda()
+    losses, grads = [], None
+    for i in range(steps):
+        loss = engine(ids, labels)
+        engine.backward(loss)
+        if i == 0:  # reduced gradient shard of the first backward: identical parameters in both runs
+            torch.cuda.synchronize()
+            grads = opt.grad_shard.float().cpu().clone()
+        engine.step()
+        losses.append(loss.item())
+    delta = {n: opt.get_full_fp32_param(p).float().cpu() - init[n] for n, p in model.named_parameters()}
+    mode = getattr(opt, "_p2p_rs_mode", "nccl")
+    return losses, delta, grads, mode
+
+
+def _zero3_paths_equal_body():
+    """The peer-memory ZeRO-3 path (copy-engine all-gather, NVLS / pull reduce-scatter fused with scale + norm) must give the
+    same reduced gradients and the same parameter updates after 5 steps as the NCCL path (DSB200_DISABLE_P2P=1), to bf16
+    tolerance; a second NCCL run gives the run-to-run noise floor (atomic-order dQ accumulation) for the log."""
+    from deepspeedsyclsupport_b200 import comm as dist
+    l_p2p, d_p2p, g_p2p, mode = _zero3_train(5, disable_p2p=False)
+    l_nccl, d_nccl, g_nccl, _ = _zero3_train(5, disable_p2p=True)
+    _, d_again, g_again, _ = _zero3_train(5, disable_p2p=True)
+
+    def rel(a, b):
+        return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+    g_err, g_floor = rel(g_p2p, g_nccl), rel(g_again, g_nccl)
+    assert g_err < 2e-2, ("reduced gradient shard", g_err, g_floor)
+    worst, floor = 0.0, 0.0
+    for n in d_p2p:
+        worst, floor = max(worst, rel(d_p2p[n], d_nccl[n])), max(floor, rel(d_again[n], d_nccl[n]))
+        assert rel(d_p2p[n], d_nccl[n]) < 5e-2, (n, rel(d_p2p[n], d_nccl[n]), rel(d_again[n], d_nccl[n]))
+    assert all(abs(x - y) < 5e-2 for x, y in zip(l_p2p, l_nccl)), (l_p2p, l_nccl)
+    if dist.get_rank() == 0:
+        print(f"ZERO3 p2p({mode}) vs nccl: first-step gradient shard rel diff {g_err:.2e} (nccl run-to-run {g_floor:.2e}); "
+              f"worst parameter-update rel diff after 5 steps {worst:.2e} (run-to-run {floor:.2e}); losses {l_p2p} vs {l_nccl}", flush=True)
+
+
+def test_zero3_peer_path_equals_nccl_path():
+    run_distributed(_zero3_paths_equal_body, world_size=2, backend="nccl", timeout=400)
+
+
+def _shard_write_race_body():
+    """A rank that is late writing its shard (GatheredParameters(modifier_rank=0) exit) must not be read early by a peer's
+    one-sided pull: the write sites re-arm a device barrier that the next gather passes first."""
+    import deepspeedsyclsupport_b200 as deepspeed
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
+    rank = dist.get_rank()
+    torch.manual_seed(0)
+    cfg = llama_config("tiny", hidden_size=256, intermediate_size=768, num_attention_heads=2, num_key_value_heads=2,
+                       num_hidden_layers=2, vocab_size=1024, activation_checkpointing=False)
+    model = LlamaForCausalLM(cfg).cuda().bfloat16()
+    engine, _, _, _ = deepspeed.initialize(model=model, config={
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True},
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-3}},
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}})
+    assert engine.optimizer.p2p is not None
+    ids = torch.randint(0, 1024, (2, 64)).cuda()
+    engine(ids, ids)  # one forward so the gather trace exists
+    w = model.model.layers[0].o_proj
+    opt = engine.optimizer
+    if rank == 0:  # make this rank's shard write land late on its stream: ~0.1 s of device-side delay in front of it
+        orig = opt._write_back_unit
+
+        def slow_write_back(u):
+            torch.cuda._sleep(200_000_000)
+            orig(u)
+
+        opt._write_back_unit = slow_write_back
+    for trial in range(3):
+        with deepspeed.zero.GatheredParameters([w], modifier_rank=0):
+            if rank == 0:
+                w.data.fill_(float(trial + 2))
+        with deepspeed.zero.GatheredParameters([w]):
+            got = w.data.float().clone()
+        torch.cuda.synchronize()
+        assert bool((got == float(trial + 2)).all()), (rank, trial, got.unique()[:4])
+
+
+def test_zero3_peer_path_shard_write_is_ordered_before_pulls():
+    run_distributed(_shard_write_race_body, world_size=2, backend="nccl")
