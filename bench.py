@@ -34,6 +34,7 @@ def parse():
     p.add_argument("--seq-len", type=int, default=4096)
     p.add_argument("--no-act-ckpt", action="store_true")
     p.add_argument("--zero-stage", type=int, default=3)
+    p.add_argument("--zeropp", action="store_true", help="ZeRO++: zero_quantized_weights + zero_quantized_gradients (config #2, second half)")
     p.add_argument("--local_rank", type=int, default=-1)
     p.add_argument("--ref-child", action="store_true", help="internal: run one reference configuration in this process")
     return p.parse_args()
@@ -89,6 +90,13 @@ class ClockSampler:
 
 
 def ds_config(args, world):
+    cfg = _ds_config(args, world)
+    if args.zeropp:
+        cfg["zero_optimization"].update({"zero_quantized_weights": True, "zero_quantized_gradients": True})
+    return cfg
+
+
+def _ds_config(args, world):
     return {
         "train_micro_batch_size_per_gpu": args.micro_batch,
         "gradient_accumulation_steps": 1,
@@ -112,7 +120,7 @@ def result_line(args, impl, world, tokens_per_step, ms_own, e2e_tps, h2d, d2h, l
         "data": "synthetic tokens (uniform random ids), random-init weights", "impl": impl,
         "config": {"model": f"llama-2-{args.model}" + (f"-{args.layers}layers-INVALID-debug" if args.layers else ""),
                    "global_batch": args.micro_batch * world, "seq_len": args.seq_len, "micro_batch_per_gpu": args.micro_batch,
-                   "parallelism": f"zero{args.zero_stage}-dp{world}", "optimizer": "AdamW", "grad_clip": 1.0,
+                   "parallelism": f"zero{args.zero_stage}{'++(qwZ+qgZ)' if args.zeropp else ''}-dp{world}", "optimizer": "AdamW", "grad_clip": 1.0,
                    # resolved value, same vocabulary in both arms: False = nothing is recomputed, else the recompute policy
                    "activation_checkpointing": act_ckpt,
                    "l2_policy": "working set (weights+activations, >13 GB) far exceeds the 126 MB L2; no explicit flush"},
@@ -371,7 +379,7 @@ def run_reference_best_of(args):
     HF gradient checkpointing, and the faster configuration that works is reported (both results are listed in `tried`)."""
     base = [sys.executable, os.path.abspath(__file__), "--impl", "reference", "--ref-child", "--gpus", "1", "--steps", str(args.steps),
             "--warmup", str(args.warmup), "--model", args.model, "--micro-batch", str(args.micro_batch), "--seq-len", str(args.seq_len),
-            "--zero-stage", str(args.zero_stage)] + (["--layers", str(args.layers)] if args.layers else [])
+            "--zero-stage", str(args.zero_stage)] + (["--layers", str(args.layers)] if args.layers else []) + (["--zeropp"] if args.zeropp else [])
     tried, best = [], None
     for extra in (["--no-act-ckpt"], []):
         line = None

@@ -103,6 +103,29 @@ __global__ void alltoall_pull_kernel(Peers peers, size_t src_off, uint8_t* __res
   }
 }
 
+// ---- NVLS (multimem) primitives; the kernels that use them are further down
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const void* mc) {
+  float4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+               : "memory");
+}
+
 // scale, (accumulate into) store and sum-of-squares of one reduced 16-byte vector: shared by the P2P and NVLS reduce-scatters
 template <int EPV, bool DST_BF16>
 __device__ __forceinline__ float rs_finish(float (&acc)[EPV], void* __restrict__ dst, size_t v, float scale, int accumulate, bool want_sq) {
@@ -194,6 +217,77 @@ __global__ void reduce_scatter_pull_kernel(Peers peers, size_t src_off, void* __
   if (sumsq) block_atomic_sum(local_sq, sumsq);
 }
 
+// ---------------------------------------------------------------- qgZ: reduce-scatter of block-scaled fp8 gradients (pull)
+// Every rank has quantised its W*n-element gradient buffer into e4m3 payload (1 byte/element at q_off) + one fp32 scale per
+// 128 elements (at s_off) inside its symmetric buffer (csrc/quant/quantizer.cu fp8_quant_kernel).  Rank r pulls slice r of
+// payload + scales from every peer -- half the NVLink bytes of the bf16 reduce-scatter --, dequantises and sums in fp32,
+// then scale / cast / accumulate / sum-of-squares as above.  16 payload bytes per thread per peer, W loads in flight.
+__device__ __forceinline__ float ld_peer_f32(const void* p) {
+  float r;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(r) : "l"(p) : "memory");
+  return r;
+}
+__device__ __forceinline__ void fp8x4_to_float(uint32_t w, float s, float* acc) {
+  // e4m3 x4 -> half2 x2 (cvt.rn.f16x2.e4m3x2), then fp32 multiply-add with the block scale
+  uint32_t lo, hi;
+  asm("{\n\t.reg .b16 a, b;\n\tmov.b32 {a, b}, %2;\n\tcvt.rn.f16x2.e4m3x2 %0, a;\n\tcvt.rn.f16x2.e4m3x2 %1, b;\n\t}"
+      : "=r"(lo), "=r"(hi)
+      : "r"(w));
+  const __half2 h0 = *reinterpret_cast<const __half2*>(&lo), h1 = *reinterpret_cast<const __half2*>(&hi);
+  const float2 f0 = __half22float2(h0), f1 = __half22float2(h1);
+  acc[0] = fmaf(f0.x, s, acc[0]); acc[1] = fmaf(f0.y, s, acc[1]);
+  acc[2] = fmaf(f1.x, s, acc[2]); acc[3] = fmaf(f1.y, s, acc[3]);
+}
+template <bool DST_BF16>
+__global__ void fp8_reduce_scatter_pull_kernel(Peers peers, size_t q_off, size_t s_off, void* __restrict__ dst, size_t n, int rank,
+                                               int world, float scale, int accumulate, float* __restrict__ sumsq) {
+  constexpr int BATCH = 8;
+  const size_t vecs = n / 16;  // 16 fp8 elements per 16-byte vector
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  float local_sq = 0.f;
+  for (size_t v = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; v < vecs; v += stride) {
+    const size_t elem = static_cast<size_t>(rank) * n + v * 16;
+    const size_t qb = q_off + elem, sb = s_off + (elem >> 7) * 4;
+    float acc[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+    for (int p0 = 0; p0 < world; p0 += BATCH) {
+      uint4 raw[BATCH];
+      float sc[BATCH];
+#pragma unroll
+      for (int b = 0; b < BATCH; ++b) {
+        if (p0 + b < world) {
+          const uint8_t* base = static_cast<const uint8_t*>(peers.ptr[(p0 + b + rank) % world]);
+          raw[b] = ld_peer_v4(base + qb);
+          sc[b] = ld_peer_f32(base + sb);
+        }
+      }
+#pragma unroll
+      for (int b = 0; b < BATCH; ++b) {
+        if (p0 + b >= world) continue;
+        fp8x4_to_float(raw[b].x, sc[b], acc);
+        fp8x4_to_float(raw[b].y, sc[b], acc + 4);
+        fp8x4_to_float(raw[b].z, sc[b], acc + 8);
+        fp8x4_to_float(raw[b].w, sc[b], acc + 12);
+      }
+    }
+    float lo8[8], hi8[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { lo8[k] = acc[k]; hi8[k] = acc[8 + k]; }
+    if constexpr (DST_BF16) {
+      local_sq += rs_finish<8, true>(lo8, dst, v * 2, scale, accumulate, sumsq != nullptr);
+      local_sq += rs_finish<8, true>(hi8, dst, v * 2 + 1, scale, accumulate, sumsq != nullptr);
+    } else {
+      float q4[4][4];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) q4[k >> 2][k & 3] = acc[k];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) local_sq += rs_finish<4, false>(q4[j], dst, v * 4 + j, scale, accumulate, sumsq != nullptr);
+    }
+  }
+  if (sumsq) block_atomic_sum(local_sq, sumsq);
+}
+
 // ---------------------------------------------------------------- reduce-scatter fused with the partitioned AdamW update
 // One pass: g = scale * sum_peers grad[peer][rank*n + i]; Adam on the fp32 master shard; bf16 parameter shard written.
 // Valid when no global-norm clipping is needed before the update (gradient_clipping == 0) -- otherwise use the
@@ -202,23 +296,50 @@ struct RsAdamArgs {
   float lr, beta1, beta2, eps, weight_decay, bc1, bc2_rsqrt, scale;
   int adamw;
 };
-__global__ void rs_adam_kernel(Peers peers, size_t src_off, float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
-                               __nv_bfloat16* __restrict__ lp, size_t n, int rank, int world, RsAdamArgs a) {
+// `peers` (pull: every rank's buffer) or `mc` (NVLS: the switch adds) delivers the gradients of elements
+// [elem_lo, elem_lo + n) of this rank's slice, whose first element sits at byte `slice_off` of the symmetric buffers.
+// p / m / v / lp / g_out point at element elem_lo of the rank-local shard.  g_out (bf16, optional) keeps the reduced,
+// scaled gradient for inspection; sumsq (optional) accumulates its squared norm.
+template <bool NVLS>
+__global__ void rs_adam_kernel(Peers peers, const uint8_t* __restrict__ mc, size_t slice_off, float* __restrict__ p,
+                               float* __restrict__ m, float* __restrict__ v, __nv_bfloat16* __restrict__ lp,
+                               __nv_bfloat16* __restrict__ g_out, float* __restrict__ sumsq, size_t n, int rank, int world,
+                               RsAdamArgs a) {
   const size_t vecs = n / 8;
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  float local_sq = 0.f;
   for (size_t vi = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; vi < vecs; vi += stride) {
     float g[8];
-#pragma unroll
-    for (int k = 0; k < 8; ++k) g[k] = 0.f;
-    for (int pi = 0; pi < world; ++pi) {
-      const int peer = (pi + rank) % world;
-      const uint4 raw = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[peer]) + src_off + (static_cast<size_t>(rank) * n + vi * 8) * 2);
+    const size_t byte_off = slice_off + vi * 16;
+    if constexpr (NVLS) {
+      const uint4 raw = multimem_ld_reduce_bf16x8(mc + byte_off);
       const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         float2 f = __bfloat1622float2(h[k]);
-        g[2 * k] += f.x;
-        g[2 * k + 1] += f.y;
+        g[2 * k] = f.x;
+        g[2 * k + 1] = f.y;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) g[k] = 0.f;
+      constexpr int BATCH = 8;
+      for (int p0 = 0; p0 < world; p0 += BATCH) {
+        uint4 raw[BATCH];
+#pragma unroll
+        for (int b = 0; b < BATCH; ++b)
+          if (p0 + b < world) raw[b] = ld_peer_v4(static_cast<const uint8_t*>(peers.ptr[(p0 + b + rank) % world]) + byte_off);
+#pragma unroll
+        for (int b = 0; b < BATCH; ++b) {
+          if (p0 + b >= world) continue;
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw[b]);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float2 f = __bfloat1622float2(h[k]);
+            g[2 * k] += f.x;
+            g[2 * k + 1] += f.y;
+          }
+        }
       }
     }
     const size_t e = vi * 8;
@@ -232,6 +353,8 @@ __global__ void rs_adam_kernel(Peers peers, size_t src_off, float* __restrict__ 
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       float gg = g[k] * a.scale;
+      g[k] = gg;
+      local_sq = fmaf(gg, gg, local_sq);
       if (!a.adamw) gg = fmaf(a.weight_decay, pp[k], gg);
       mm[k] = fmaf(a.beta1, mm[k], (1.f - a.beta1) * gg);
       vv[k] = fmaf(a.beta2, vv[k], (1.f - a.beta2) * gg * gg);
@@ -248,7 +371,12 @@ __global__ void rs_adam_kernel(Peers peers, size_t src_off, float* __restrict__ 
     uint4 o;
     o.x = pack_bf16x2(pp[0], pp[1]); o.y = pack_bf16x2(pp[2], pp[3]); o.z = pack_bf16x2(pp[4], pp[5]); o.w = pack_bf16x2(pp[6], pp[7]);
     *reinterpret_cast<uint4*>(lp + e) = o;
+    if (g_out) {
+      o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]); o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
+      *reinterpret_cast<uint4*>(g_out + e) = o;
+    }
   }
+  if (sumsq) block_atomic_sum(local_sq, sumsq);
 }
 
 // ---------------------------------------------------------------- one-shot all-reduce (small messages: TP inference)
@@ -283,28 +411,6 @@ __global__ void allreduce_oneshot_kernel(Peers peers, size_t src_off, __nv_bfloa
 // `mc` is the multicast mapping of the SAME symmetric buffer: a multimem.ld_reduce at offset x returns the sum over every
 // rank's bytes at x, added inside the switch (each GPU receives 1x the slice instead of reading W-1 peers); a multimem.st
 // writes the value into every rank's copy.  Callers order these against the producers with the device barrier above.
-__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
-  uint4 r;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "l"(mc)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ float4 multimem_ld_reduce_f32x4(const void* mc) {
-  float4 r;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
-               : "l"(mc)
-               : "memory");
-  return r;
-}
-__device__ __forceinline__ void multimem_st_v4(void* mc, const uint4& v) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(__uint_as_float(v.x)),
-               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
-               : "memory");
-}
-
 // reduce-scatter: rank r reduces slice r of the W*n-element buffer at `src_off` in the switch, then scale / cast /
 // accumulate / sum-of-squares exactly like the pull kernel.  U loads in flight per thread.
 template <bool SRC_BF16, bool DST_BF16>
@@ -493,11 +599,17 @@ DSB_EXPORT int dsb200_p2p_reduce_scatter(void* const* peer_ptrs, long long src_o
   return DSB_OK;
 }
 
-DSB_EXPORT int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, float* m, float* v, void* lp, long long n,
-                                  int rank, int world, float scale, float lr, float beta1, float beta2, float eps,
-                                  float weight_decay, int adamw_mode, int bias_correction, int step, int max_ctas,
-                                  cudaStream_t stream) {
-  DSB_REQUIRE(n % 8 == 0 && src_off % 16 == 0, "p2p_rs_adam: n must be a multiple of 8 and the offset 16-byte aligned");
+// Range form: Adam on elements [elem_lo, elem_lo + n) of this rank's slice (slice length n_per_rank) of the W*n_per_rank
+// bf16 gradient buffer at src_off.  p/m/v/lp/g_out point at element elem_lo of the local shard.  mc_base != NULL: the sum
+// comes from the NVSwitch (multimem.ld_reduce); NULL: pulled from the peers.  g_out / sumsq optional (may be NULL).
+DSB_EXPORT int dsb200_p2p_rs_adam_range(void* const* peer_ptrs, void* mc_base, long long src_off, long long n_per_rank,
+                                        long long elem_lo, long long n, float* p, float* m, float* v, void* lp, void* g_out,
+                                        float* sumsq, int rank, int world, float scale, float lr, float beta1, float beta2,
+                                        float eps, float weight_decay, int adamw_mode, int bias_correction, int step,
+                                        int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(n % 8 == 0 && elem_lo % 8 == 0 && n_per_rank % 8 == 0 && src_off % 16 == 0,
+              "p2p_rs_adam: element counts must be multiples of 8 and the offset 16-byte aligned");
+  DSB_REQUIRE(elem_lo >= 0 && elem_lo + n <= n_per_rank, "p2p_rs_adam: range outside the rank's slice");
   Peers P;
   int rc = make_peers(&P, peer_ptrs, world);
   if (rc) return rc;
@@ -505,10 +617,25 @@ DSB_EXPORT int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, flo
   a.lr = lr; a.beta1 = beta1; a.beta2 = beta2; a.eps = eps; a.weight_decay = weight_decay; a.adamw = adamw_mode; a.scale = scale;
   a.bc1 = bias_correction ? 1.f / (1.f - powf(beta1, (float)step)) : 1.f;
   a.bc2_rsqrt = bias_correction ? 1.f / sqrtf(1.f - powf(beta2, (float)step)) : 1.f;
-  rs_adam_kernel<<<comm_grid(static_cast<size_t>(n) / 8, max_ctas), 256, 0, stream>>>(
-      P, static_cast<size_t>(src_off), p, m, v, static_cast<__nv_bfloat16*>(lp), static_cast<size_t>(n), rank, world, a);
+  const size_t slice_off = static_cast<size_t>(src_off) + (static_cast<size_t>(rank) * n_per_rank + elem_lo) * 2;
+  const int grid = comm_grid(static_cast<size_t>(n) / 8, max_ctas);
+  if (mc_base)
+    rs_adam_kernel<true><<<grid, 256, 0, stream>>>(P, static_cast<const uint8_t*>(mc_base), slice_off, p, m, v,
+                                                    static_cast<__nv_bfloat16*>(lp), static_cast<__nv_bfloat16*>(g_out), sumsq,
+                                                    static_cast<size_t>(n), rank, world, a);
+  else
+    rs_adam_kernel<false><<<grid, 256, 0, stream>>>(P, nullptr, slice_off, p, m, v, static_cast<__nv_bfloat16*>(lp),
+                                                     static_cast<__nv_bfloat16*>(g_out), sumsq, static_cast<size_t>(n), rank, world, a);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
+}
+
+DSB_EXPORT int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, float* m, float* v, void* lp, long long n,
+                                  int rank, int world, float scale, float lr, float beta1, float beta2, float eps,
+                                  float weight_decay, int adamw_mode, int bias_correction, int step, int max_ctas,
+                                  cudaStream_t stream) {
+  return dsb200_p2p_rs_adam_range(peer_ptrs, nullptr, src_off, n, 0, n, p, m, v, lp, nullptr, nullptr, rank, world, scale, lr, beta1,
+                                  beta2, eps, weight_decay, adamw_mode, bias_correction, step, max_ctas, stream);
 }
 
 DSB_EXPORT int dsb200_p2p_allreduce_bf16(void* const* peer_ptrs, long long src_off, void* dst, long long n, int rank, int world,
@@ -582,6 +709,28 @@ DSB_EXPORT int dsb200_nvls_allgather(void* mc_base, long long dst_off, const voi
   DSB_REQUIRE(bytes % 16 == 0 && dst_off % 16 == 0, "nvls_allgather: sizes/offsets must be multiples of 16 bytes");
   nvls_allgather_kernel<<<comm_grid(static_cast<size_t>(bytes) / 16, max_ctas > 0 ? max_ctas : 64), 256, 0, stream>>>(
       static_cast<uint8_t*>(mc_base), static_cast<size_t>(dst_off), static_cast<const uint8_t*>(src), static_cast<size_t>(bytes), rank);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// qgZ consumer: q_off / s_off = byte offsets of the fp8 payload (W*n bytes) and the fp32 block scales (W*n/128 floats) in
+// every rank's symmetric buffer; n = elements per rank (multiple of 128); dst dtype 0 bf16 / 2 fp32.
+DSB_EXPORT int dsb200_p2p_fp8_reduce_scatter(void* const* peer_ptrs, long long q_off, long long s_off, void* dst, int dst_dtype,
+                                             long long n, int rank, int world, float scale, int accumulate, float* sumsq,
+                                             int max_ctas, cudaStream_t stream) {
+  DSB_REQUIRE(n % 128 == 0 && q_off % 16 == 0 && s_off % 4 == 0, "p2p_fp8_reduce_scatter: n must be a multiple of 128 (whole scale blocks)");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  const int grid = comm_grid(static_cast<size_t>(n) / 16, max_ctas);
+  if (dst_dtype == 0)
+    fp8_reduce_scatter_pull_kernel<true><<<grid, 256, 0, stream>>>(P, (size_t)q_off, (size_t)s_off, dst, (size_t)n, rank, world, scale, accumulate, sumsq);
+  else if (dst_dtype == 2)
+    fp8_reduce_scatter_pull_kernel<false><<<grid, 256, 0, stream>>>(P, (size_t)q_off, (size_t)s_off, dst, (size_t)n, rank, world, scale, accumulate, sumsq);
+  else {
+    set_last_error("p2p_fp8_reduce_scatter: unsupported destination dtype %d", dst_dtype);
+    return DSB_ERR_UNSUPPORTED;
+  }
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

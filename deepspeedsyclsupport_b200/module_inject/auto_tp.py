@@ -97,101 +97,106 @@ class AutoTP:
         self.linear_policies = None
         self.conv_linear_layer = False
 
+    # ------------------------------------------------------------------ parsing: which linears end in an all-reduce
+    # A transformer block is flattened into the ordered token list of its leaves: ".attn.o_proj" for a Linear (qualified by
+    # the names of the two innermost containers, as the policies expect), "ln" for a normalisation layer.  A linear needs
+    # an all-reduce when (a) it is the last linear before a norm, (b) its name is a known row-parallel output projection, or
+    # (c) it is the last linear of an MLP-like child that matched nothing else.
+    _NORM_NAMES = ("LayerNorm", "layer_norm", "ln_1", "ln_2")
+    _UNSUPPORTED = ("deberta", "flaubert", "fsmt", "gpt2", "led", "longformer", "xlm", "xlnet")
+
     @staticmethod
     def in_module_list(module, module_list):
-        for item in module_list:
-            if type(item).__name__ == type(module).__name__:
-                return True
-        return False
+        return any(type(m).__name__ == type(module).__name__ for m in module_list)
 
     @staticmethod
     def get_module_list(model):
-        mlist = []
+        """One representative of every distinct block class found inside the model's nn.ModuleLists (depth first)."""
+        found = []
         for child in model.children():
-            if isinstance(child, nn.ModuleList):
-                for module in child.children():
-                    if not mlist:
-                        mlist = [module]
-                    elif not AutoTP.in_module_list(module, mlist):
-                        mlist = mlist + [module]
-            else:
-                mlist = mlist + AutoTP.get_module_list(child)
-        return mlist
+            candidates = child.children() if isinstance(child, nn.ModuleList) else AutoTP.get_module_list(child)
+            for block in candidates:
+                if not AutoTP.in_module_list(block, found):
+                    found.append(block)
+        return found
 
     @staticmethod
     def supported(model):
-        unsupported = ["deberta", "flaubert", "fsmt", "gpt2", "led", "longformer", "xlm", "xlnet"]
-        model = str(model)
-        key = re.search(r": (.*?)Model", model)
-        if key is None:
-            key = re.search(r": (.*?)Stack", model)
-        if key is None:
-            key = re.match(r"(.*?)Model", model)
-        if key is None:
-            return True
-        return key.group(1).lower() not in unsupported
+        text = str(model)
+        for pattern, fn in ((r": (.*?)Model", re.search), (r": (.*?)Stack", re.search), (r"(.*?)Model", re.match)):
+            hit = fn(pattern, text)
+            if hit is not None:
+                return hit.group(1).lower() not in AutoTP._UNSUPPORTED
+        return True
+
+    @staticmethod
+    def _is_norm(key, module):
+        return isinstance(module, nn.LayerNorm) or key in AutoTP._NORM_NAMES[:2]
 
     @staticmethod
     def get_layers(parent, module):
-        layer_list = []
-        for key, submodule in module._modules.items():
-            if isinstance(submodule, nn.Linear):
-                layer_list = layer_list + [parent + "." + key]
-            elif isinstance(submodule, nn.LayerNorm) or key == "LayerNorm" or key == "layer_norm":
-                layer_list = layer_list + ["ln"]
+        tokens = []
+        for key, sub in module._modules.items():
+            if isinstance(sub, nn.Linear):
+                tokens.append(f"{parent}.{key}")
+            elif AutoTP._is_norm(key, sub):
+                tokens.append("ln")
             else:
-                layer_list = layer_list + AutoTP.get_layers(key, submodule)
-        return layer_list
+                tokens.extend(AutoTP.get_layers(key, sub))
+        return tokens
 
     @staticmethod
     def update_policy_list(policy_list, new_module, new_gems):
-        if len(policy_list):
-            for i, policy in enumerate(policy_list):
-                if policy[0] == type(new_module):
-                    new_gems = set(new_gems + policy[1])
-                    policy_list[i] = tuple([type(new_module), new_gems])
-                    return policy_list
-        policy_list.append(tuple([type(new_module), new_gems]))
+        for i, (cls, gems) in enumerate(policy_list):
+            if cls is type(new_module):
+                policy_list[i] = (cls, set(new_gems) | set(gems))
+                return policy_list
+        policy_list.append((type(new_module), new_gems))
         return policy_list
 
     @staticmethod
     def kernel_supported(module_list):
-        policy = []
         return False
 
     @staticmethod
+    def _is_output_projection(token, model_text, block_type_text):
+        if any(tag in token for tag in ("out_proj", "o_proj", "down_proj", "dense_4h_to_h")):
+            return True
+        if "attention.dense" in token and "GPTNeoX" in model_text:
+            return True
+        if "self_attention.dense" in token and "falcon" in block_type_text:
+            return True
+        return "w2" in token and "mixtral" in block_type_text
+
+    @staticmethod
     def tp_parser(model):
-        """[(block class, {names of linears that need an all-reduce})]"""
-        policy_list = []
-        module_list = AutoTP.get_module_list(model)
-        assert AutoTP.supported(model), "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
-        norm_layer_name_list = ["LayerNorm", "layer_norm", "ln_1", "ln_2"]
-        for module in module_list:
-            for key, submodule in module._modules.items():
-                if isinstance(submodule, nn.Linear):
-                    layer_list = ["." + key]
-                elif isinstance(submodule, nn.LayerNorm) or key in norm_layer_name_list:
-                    layer_list = ["ln"]
+        """[(block class, names of the linears whose output must be all-reduced)]"""
+        unsupported_msg = "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
+        assert AutoTP.supported(model), unsupported_msg
+        model_text = str(model)
+        policies = []
+        for block in AutoTP.get_module_list(model):
+            block_text = str(type(block)).lower()
+            for key, sub in block._modules.items():
+                if isinstance(sub, nn.Linear):
+                    tokens = ["." + key]
+                elif isinstance(sub, nn.LayerNorm) or key in AutoTP._NORM_NAMES:
+                    tokens = ["ln"]
                 else:
-                    layer_list = AutoTP.get_layers(key, submodule)
-                gem_list = []
-                for i, layer in enumerate(layer_list):
-                    if layer == "ln":
-                        if i > 0 and layer_list[i - 1] != "ln":
-                            gem_list = gem_list + [layer_list[i - 1]]
-                    elif "out_proj" in layer or "o_proj" in layer or "down_proj" in layer or "attention.dense" in layer and "GPTNeoX" in str(model) \
-                            or "self_attention.dense" in layer and "falcon" in str(type(module)).lower() or "dense_4h_to_h" in layer \
-                            or "w2" in layer and "mixtral" in str(type(module)).lower():
-                        gem_list = gem_list + [layer]
-                if len(layer_list) > 0 and layer_list[-1] != "ln" and len(gem_list) == 0 and key in ("mlp", "feed_forward", "ffn"):
-                    gem_list = gem_list + [layer_list[-1]]
-                layer_list = []
-                if gem_list != []:
-                    gem_list = list(set(gem_list))
-                    policy_list = AutoTP.update_policy_list(policy_list, module, gem_list)
-                    gem_list = []
-        assert len(policy_list), "AutoTP not supported for model. Please use kernel injection since container policy for model exists."
-        return policy_list
+                    tokens = AutoTP.get_layers(key, sub)
+                picked = set()
+                for before, tok in zip([None] + tokens[:-1], tokens):
+                    if tok == "ln":
+                        if before not in (None, "ln"):
+                            picked.add(before)
+                    elif AutoTP._is_output_projection(tok, model_text, block_text):
+                        picked.add(tok)
+                if not picked and tokens and tokens[-1] != "ln" and key in ("mlp", "feed_forward", "ffn"):
+                    picked.add(tokens[-1])
+                if picked:
+                    policies = AutoTP.update_policy_list(policies, block, list(picked))
+        assert policies, unsupported_msg
+        return policies
 
     def set_tensor_parallel_config(self, mp_size, mp_group):
         self.mp_size = mp_size
@@ -237,40 +242,40 @@ class AutoTP:
         new_embedding.replaced = True
         return new_embedding
 
+    _HEAD_COUNT_ATTRS = ("n_heads", "inner_dim", "num_heads", "num_kv", "num_attention_heads", "num_attn_heads", "all_head_size",
+                         "embed_dim", "hidden_size", "num_key_value_heads", "num_kv_heads", "kv_n_heads", "d_model")
+
     def update_mp_params(self, child):
+        """Attention modules cache head counts / widths: divide the ones that split evenly, once per module."""
         if getattr(child, "replaced", False):
             return
-        for param in ["n_heads", "inner_dim", "num_heads", "num_kv", "num_attention_heads", "num_attn_heads", "all_head_size",
-                      "embed_dim", "hidden_size", "num_key_value_heads", "num_kv_heads", "kv_n_heads", "d_model"]:
-            if hasattr(child, param):
-                param_val = getattr(child, param)
-                if isinstance(param_val, int) and param_val % self.mp_size == 0:
-                    setattr(child, param, param_val // self.mp_size)
-        setattr(child, "replaced", True)
+        for attr in self._HEAD_COUNT_ATTRS:
+            value = getattr(child, attr, None)
+            if isinstance(value, int) and value % self.mp_size == 0:
+                setattr(child, attr, value // self.mp_size)
+        child.replaced = True
 
     def update_linear_policies(self):
         self.conv_linear_layer = False
-        if self.linear_layer_setting is not None:
-            self.linear_policies = {self.linear_layer_setting[0]: self._replace}
-            if len(self.linear_layer_setting) == 2:
-                self.linear_policies.update({self.linear_layer_setting[1]: self._slice_embedding})
-        else:
+        setting = self.linear_layer_setting
+        if setting is None:
             self.linear_policies = {nn.Linear: self._replace}
+            return
+        self.linear_policies = {setting[0]: self._replace}
+        if len(setting) == 2:
+            self.linear_policies[setting[1]] = self._slice_embedding
 
     def _replace_module(self, r_module, prev_name="", prev_class_name=""):
+        """Depth-first walk: leaves with a policy are swapped for their sliced twins, every other module gets its head counts
+        adjusted.  A leaf is known to the policies by ".<parent>.<name>"."""
+        scope = ".".join(x for x in (prev_class_name, prev_name) if x)
         for name, child in r_module.named_children():
-            if prev_class_name == "":
-                class_name = prev_name
-            elif prev_name == "":
-                class_name = prev_class_name
-            else:
-                class_name = prev_class_name + "." + prev_name
-            checking_key = self.prefix + "." + class_name + "." + name + "." if class_name != "" else self.prefix + "." + name + "."
-            if child.__class__ in self.linear_policies:
-                setattr(r_module, name, self.linear_policies[child.__class__](child, prev_name + "." + name, self.conv_linear_layer))
+            swap = self.linear_policies.get(type(child))
+            if swap is not None:
+                setattr(r_module, name, swap(child, f"{prev_name}.{name}", self.conv_linear_layer))
             else:
                 self.update_mp_params(child)
-                self._replace_module(child, name, class_name)
+                self._replace_module(child, name, scope)
         return r_module
 
     def get_model_num_kv_heads(self, config):

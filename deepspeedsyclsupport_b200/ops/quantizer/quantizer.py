@@ -33,15 +33,25 @@ def dequantize_fp8_block_ref(q, scales, dtype=torch.bfloat16):
     return (q.view(torch.float8_e4m3fn).float().view(-1, FP8_BLOCK) * scales[:, None]).to(dtype).view(-1)
 
 
-def quantize_fp8_block(x):
-    """x: flat tensor with numel % 128 == 0 -> (uint8 payload [n], fp32 scales [n/128])."""
+def quantize_fp8_block(x, out=None):
+    """x: flat tensor with numel % 128 == 0 -> (uint8 payload [n], fp32 scales [n/128]).  `out=(payload, scales)` writes
+    into existing buffers (e.g. regions of a symmetric buffer that peers read)."""
     x = x.contiguous().view(-1)
     n = x.numel()
     assert n % FP8_BLOCK == 0, "pad to a multiple of 128 elements"
     if not x.is_cuda:
-        return quantize_fp8_block_ref(x)
-    q = torch.empty(n, dtype=torch.uint8, device=x.device)
-    s = torch.empty(n // FP8_BLOCK, dtype=torch.float32, device=x.device)
+        q, s = quantize_fp8_block_ref(x)
+        if out is not None:
+            out[0].copy_(q)
+            out[1].copy_(s)
+            return out
+        return q, s
+    if out is not None:
+        q, s = out
+        assert q.numel() == n and s.numel() == n // FP8_BLOCK and q.dtype == torch.uint8 and s.dtype == torch.float32
+    else:
+        q = torch.empty(n, dtype=torch.uint8, device=x.device)
+        s = torch.empty(n // FP8_BLOCK, dtype=torch.float32, device=x.device)
     rc = native.lib().dsb200_fp8_block_quantize(native.ptr(x), native.ptr(q), native.ptr(s), n, _DT[x.dtype], native.stream_ptr())
     native.check(rc)
     return q, s

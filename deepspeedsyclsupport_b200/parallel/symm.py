@@ -28,6 +28,8 @@ native.register_sigs({
     "dsb200_p2p_rs_adam": "p l pppp l ii f fffff iii i p",
     "dsb200_p2p_allreduce_bf16": "p l p l iii p",
     "dsb200_p2p_allgather_ce": "p l p l ii p",
+    "dsb200_p2p_fp8_reduce_scatter": "p ll p i l ii f i p i p",
+    "dsb200_p2p_rs_adam_range": "pp lll l pppppp ii f fffff iii i p",
     "dsb200_nvls_reduce_scatter": "p l i p i l ii f i p i p",
     "dsb200_nvls_allreduce_bf16": "p l l ii i p",
     "dsb200_nvls_allgather": "p l p l i i p",
@@ -144,6 +146,28 @@ class _PeerOps:
                                              native.ptr(v), native.ptr(lp), n_per_rank, r, self.world, float(scale), lr, beta1, beta2,
                                              eps, weight_decay, int(adamw_mode), int(bias_correction), int(step), max_ctas,
                                              native.stream_ptr())
+        native.check(rc)
+
+    def fp8_reduce_scatter(self, dst, q_offset, s_offset, n_per_rank, scale=1.0, accumulate=False, sumsq=None, max_ctas=0):
+        """qgZ consumer: every rank holds its W*n gradient buffer as block-scaled fp8 (payload at q_offset, fp32 scale per
+        128 elements at s_offset); this rank pulls slice `rank` from all peers, dequantises, sums, scales into `dst`."""
+        rc = native.lib().dsb200_p2p_fp8_reduce_scatter(ctypes.cast(self._table(), ctypes.c_void_p), q_offset, s_offset,
+                                                        native.ptr(dst), _DT[dst.dtype], n_per_rank, self.rank, self.world,
+                                                        float(scale), int(accumulate), native.ptr(sumsq), max_ctas,
+                                                        native.stream_ptr())
+        native.check(rc)
+        return dst
+
+    def rs_adam_range(self, src_offset, n_per_rank, elem_lo, p, m, v, lp, *, scale, lr, beta1, beta2, eps, weight_decay,
+                      adamw_mode=True, bias_correction=True, step=1, g_out=None, sumsq=None, nvls=False, max_ctas=0):
+        """Reduce-scatter fused with AdamW on elements [elem_lo, elem_lo + p.numel()) of this rank's slice of the bf16 gradient
+        buffer at `src_offset` (W * n_per_rank elements).  nvls=True takes the sum from the switch.  `g_out` (bf16) keeps the
+        reduced gradient, `sumsq` accumulates its squared norm."""
+        rc = native.lib().dsb200_p2p_rs_adam_range(ctypes.cast(self._table(), ctypes.c_void_p), self.mc_ptr if nvls else None,
+                                                   src_offset, n_per_rank, elem_lo, p.numel(), native.ptr(p), native.ptr(m),
+                                                   native.ptr(v), native.ptr(lp), native.ptr(g_out), native.ptr(sumsq), self.rank,
+                                                   self.world, float(scale), lr, beta1, beta2, eps, weight_decay, int(adamw_mode),
+                                                   int(bias_correction), int(step), max_ctas, native.stream_ptr())
         native.check(rc)
 
     def all_reduce_bf16(self, dst, src_offset, n, rank=None, max_ctas=0, scratch_offset=None, algo="auto"):

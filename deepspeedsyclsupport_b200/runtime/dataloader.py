@@ -1,4 +1,10 @@
-"""DeepSpeedDataLoader + RepeatingLoader (parity: deepspeed/runtime/dataloader.py:17-162)."""
+"""Data loading glue of the engine: `DeepSpeedDataLoader` (what `engine.deepspeed_io` returns) and `RepeatingLoader`.
+
+`DeepSpeedDataLoader` picks the sampler the job needs -- the curriculum batch sampler when data-efficiency sampling is on,
+the caller's sampler, a `DistributedSampler` over the data-parallel group for launcher-started ranks (local_rank >= 0), or
+a `RandomSampler` with the batch scaled by the visible device count for single-process use -- and builds the torch
+`DataLoader` lazily on `iter()`.  Constructor signature and attributes follow deepspeed/runtime/dataloader.py:17-162.
+"""
 from torch.utils.data import DataLoader, RandomSampler
 from torch.utils.data.distributed import DistributedSampler
 
@@ -6,22 +12,23 @@ from ..accelerator import get_accelerator
 
 
 class RepeatingLoader:
-    """Wraps an iterator to restart automatically when exhausted."""
+    """Endless iterator over a loader: starts it again each time it runs out."""
 
     def __init__(self, loader):
         self.loader = loader
-        self.data_iter = iter(self.loader)
+        self.data_iter = iter(loader)
 
     def __iter__(self):
         return self
 
     def __next__(self):
-        try:
-            batch = next(self.data_iter)
-        except StopIteration:
-            self.data_iter = iter(self.loader)
-            batch = next(self.data_iter)
-        return batch
+        for attempt in (0, 1):
+            try:
+                return next(self.data_iter)
+            except StopIteration:
+                if attempt:
+                    raise  # an empty loader stays empty
+                self.data_iter = iter(self.loader)
 
 
 class DeepSpeedDataLoader:
@@ -29,46 +36,38 @@ class DeepSpeedDataLoader:
     def __init__(self, dataset, batch_size, pin_memory, local_rank, tput_timer, collate_fn=None, num_local_io_workers=None,
                  data_sampler=None, data_parallel_world_size=None, data_parallel_rank=None, dataloader_drop_last=False,
                  deepspeed_dataloader_config={}):
-        self.deepspeed_dataloader_config = deepspeed_dataloader_config
-        self.tput_timer = tput_timer
+        cfg = self.deepspeed_dataloader_config = deepspeed_dataloader_config
+        self.dataset, self.collate_fn, self.tput_timer = dataset, collate_fn, tput_timer
         self.batch_size = batch_size
-        self.curriculum_learning_enabled = bool(deepspeed_dataloader_config.get("curriculum_learning_enabled", False))
-        if self.curriculum_learning_enabled:
-            # curriculum learning: a batch sampler that draws every global batch from the currently eligible data clusters
-            from .data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
-            c = deepspeed_dataloader_config
-            data_sampler = DeepSpeedDataSampler(c["data_efficiency_config"], len(dataset), batch_size, data_parallel_rank, data_parallel_world_size,
-                                                c.get("data_parallel_group"), c.get("gradient_accumulation_steps", 1), c.get("global_rank", 0),
-                                                drop_last=dataloader_drop_last)
-        if local_rank >= 0:
-            if data_sampler is None:
-                data_sampler = DistributedSampler(dataset=dataset, num_replicas=data_parallel_world_size, rank=data_parallel_rank)
-            device_count = 1
-        else:
-            if data_sampler is None:
-                data_sampler = RandomSampler(dataset)
-            device_count = get_accelerator().device_count()
-            batch_size *= device_count
-        if num_local_io_workers is None:
-            num_local_io_workers = 2 * device_count
-        self.num_local_io_workers = num_local_io_workers
-        self.data_sampler = data_sampler
-        self.dataset = dataset
-        self.collate_fn = collate_fn
-        self.device_count = device_count
-        self.pin_memory = pin_memory and get_accelerator().device_name() == "cuda"
-        self.data = None
         self.dataloader_drop_last = dataloader_drop_last
         self.post_process_func = None
-        self.len = len(self.data_sampler) // self.batch_size if self.dataloader_drop_last else \
-            -(-len(self.data_sampler) // self.batch_size)
+        self.data = None
+        self.curriculum_learning_enabled = bool(cfg.get("curriculum_learning_enabled", False))
+        launched = local_rank >= 0
+        self.device_count = 1 if launched else get_accelerator().device_count()
+        if self.curriculum_learning_enabled:
+            from .data_pipeline.data_sampling.data_sampler import DeepSpeedDataSampler
+            data_sampler = DeepSpeedDataSampler(cfg["data_efficiency_config"], len(dataset), batch_size, data_parallel_rank,
+                                                data_parallel_world_size, cfg.get("data_parallel_group"),
+                                                cfg.get("gradient_accumulation_steps", 1), cfg.get("global_rank", 0),
+                                                drop_last=dataloader_drop_last)
+        elif data_sampler is None and launched:
+            data_sampler = DistributedSampler(dataset=dataset, num_replicas=data_parallel_world_size, rank=data_parallel_rank)
+        elif data_sampler is None:
+            data_sampler = RandomSampler(dataset)
+        self.data_sampler = data_sampler
+        self._loader_batch = batch_size * self.device_count  # one process feeding several devices takes a batch for each
+        self.num_local_io_workers = 2 * self.device_count if num_local_io_workers is None else num_local_io_workers
+        self.pin_memory = bool(pin_memory) and get_accelerator().device_name() == "cuda"
+        samples = len(data_sampler)
+        self.len = samples // batch_size if dataloader_drop_last else (samples + batch_size - 1) // batch_size
+
+    def __len__(self):
+        return self.len
 
     def __iter__(self):
         self._create_dataloader()
         return self
-
-    def __len__(self):
-        return self.len
 
     def __next__(self):
         if self.tput_timer:
@@ -76,13 +75,13 @@ class DeepSpeedDataLoader:
         return next(self.data)
 
     def _create_dataloader(self):
+        options = {"pin_memory": self.pin_memory, "num_workers": self.num_local_io_workers}
         if self.curriculum_learning_enabled:
-            kw = dict(pin_memory=self.pin_memory, batch_sampler=self.data_sampler, num_workers=self.num_local_io_workers)
+            options["batch_sampler"] = self.data_sampler  # yields whole micro-batches of sample ids
         else:
-            kw = dict(batch_size=self.batch_size, pin_memory=self.pin_memory, sampler=self.data_sampler,
-                      num_workers=self.num_local_io_workers, drop_last=self.dataloader_drop_last)
+            options.update(batch_size=self._loader_batch, sampler=self.data_sampler, drop_last=self.dataloader_drop_last)
         if self.collate_fn is not None:
-            kw["collate_fn"] = self.collate_fn
-        self.dataloader = DataLoader(self.dataset, **kw)
-        self.data = (x for x in self.dataloader)
+            options["collate_fn"] = self.collate_fn
+        self.dataloader = DataLoader(self.dataset, **options)
+        self.data = iter(self.dataloader)
         return self.dataloader

@@ -29,128 +29,128 @@ def _has(key, patterns):
     return any(p in key for p in patterns)
 
 
+def _cpu(storage, loc):
+    return storage
+
+
 class SDLoaderFactory:
 
     @staticmethod
     def get_sd_loader_json(json_file, checkpoint_engine):
-        if isinstance(json_file, str):
-            with open(json_file) as f:
-                data = json.load(f)
+        """`json_file`: path or dict with "type", "checkpoints", "version" (+ optional "parallelization", "mp_size").  Descriptions
+        of bloom / ds_model checkpoints are returned as they are (the inference engine walks them itself)."""
+        if isinstance(json_file, dict):
+            spec = json_file
         else:
-            assert isinstance(json_file, dict)
-            data = json_file
-        sd_type = data["type"]
-        ckpt_list = data["checkpoints"]
-        version = data["version"]
-        ckpt_type = data.get("parallelization", "pp")
-        mp_size = data.get("mp_size", 0)
-        if sd_type.lower() in ["bloom", "ds_model"]:
-            return data
-        return SDLoaderFactory.get_sd_loader(ckpt_list, checkpoint_engine, sd_type, version)
+            with open(json_file) as fd:
+                spec = json.load(fd)
+        kind = spec["type"]
+        if kind.lower() in ("bloom", "ds_model"):
+            return spec
+        return SDLoaderFactory.get_sd_loader(spec["checkpoints"], checkpoint_engine, kind, spec["version"])
 
     @staticmethod
     def get_sd_loader(ckpt_list, checkpoint_engine, sd_type="Megatron", version=None):
-        if sd_type == "Megatron":
-            return MegatronSDLoader(ckpt_list, version, checkpoint_engine)
-        assert False, "{} checkpoint type is not supported".format(sd_type)
+        loaders = {"Megatron": MegatronSDLoader}
+        assert sd_type in loaders, "{} checkpoint type is not supported".format(sd_type)
+        return loaders[sd_type](ckpt_list, version, checkpoint_engine)
 
 
 class SDLoaderBase(ABC):
+    """Maps (files on disk, requested tensor-parallel degree, rank) to one of three plans:
+         same   as many files as ranks     -> read file `rank`
+         merge  k files per rank           -> read files [k*rank, k*(rank+1)) and join them   (subclass: merge_state_dict)
+         split  k ranks per file           -> read file rank // k, keep slice rank % k        (subclass: split_state_dict)"""
 
     def __init__(self, ckpt_list, version, checkpoint_engine):
-        self.module_key = None
-        self.ckpt_list = ckpt_list
-        self.version = version
         if checkpoint_engine is None:
             from .checkpoint_engine.torch_checkpoint_engine import TorchCheckpointEngine
             checkpoint_engine = TorchCheckpointEngine()
-        self.checkpoint_engine = checkpoint_engine
+        self.ckpt_list, self.version, self.checkpoint_engine = ckpt_list, version, checkpoint_engine
+        self.module_key = None
         self.check_ckpt_list()
+
+    def _read(self, path):
+        return self.checkpoint_engine.load(path, map_location=_cpu)
 
     def load(self, mp_world_size, mp_rank, module_key=AUTO_MODULE_KEY, is_pipe_parallel=False, quantize=False, quantize_bits=8, quantize_groups=64,
              mlp_extra_grouping=True):
-        """-> (checkpoint file used for naming, state dict for this mp_rank, (scales, merge_count) or None)."""
+        """-> (path of the file that names this shard, state dict for `mp_rank`, (quantisation scales or None, files merged))."""
         self.module_key = module_key
-        num_ckpt = len(self.ckpt_list)
-        idx = mp_rank * num_ckpt // mp_world_size
-        # pipeline-parallel checkpoints keep one mp_rank file per (tp) rank only: reshaping is done by the layer loader
-        if is_pipe_parallel and module_key is not None and mp_world_size != num_ckpt:
-            mp_world_size = num_ckpt
-            idx = 0
-        load_path = self.ckpt_list[idx]
-        merge_count = 1
-        if num_ckpt == mp_world_size:
-            assert os.path.exists(load_path)
-            sd = self.checkpoint_engine.load(load_path, map_location=lambda storage, loc: storage)
-            if quantize:
-                quantizer = WeightQuantization(mlp_extra_grouping=mlp_extra_grouping, mp_size=mp_world_size)
-                sd_module, all_scales = quantizer.sd_quantize_megatron(self.get_module(sd), quantize_bits, quantize_groups)
-                self.set_module(sd, sd_module)
-            else:
-                all_scales = None
-        elif num_ckpt > mp_world_size:
-            sd, all_scales, merge_count = self.merge_state_dict(mp_world_size, mp_rank, quantize, quantize_bits, quantize_groups, mlp_extra_grouping)
-        else:
-            sd, all_scales = self.split_state_dict(mp_world_size, mp_rank, quantize, quantize_bits, quantize_groups, mlp_extra_grouping)
-        return load_path, sd, (all_scales, merge_count)
+        files = len(self.ckpt_list)
+        first = mp_rank * files // mp_world_size
+        if is_pipe_parallel and module_key is not None and mp_world_size != files:
+            # pipeline checkpoints hold one mp_rank file per tp rank; the layer files are reshaped elsewhere
+            mp_world_size, first = files, 0
+        path = self.ckpt_list[first]
+        q_args = (quantize, quantize_bits, quantize_groups, mlp_extra_grouping)
+        if files > mp_world_size:
+            sd, scales, merged = self.merge_state_dict(mp_world_size, mp_rank, *q_args)
+            return path, sd, (scales, merged)
+        if files < mp_world_size:
+            sd, scales = self.split_state_dict(mp_world_size, mp_rank, *q_args)
+            return path, sd, (scales, 1)
+        assert os.path.exists(path), f"checkpoint shard {path} is missing"
+        sd, scales = self._read(path), None
+        if quantize:
+            quantizer = WeightQuantization(mlp_extra_grouping=mlp_extra_grouping, mp_size=mp_world_size)
+            module, scales = quantizer.sd_quantize_megatron(self.get_module(sd), quantize_bits, quantize_groups)
+            self.set_module(sd, module)
+        return path, sd, (scales, 1)
 
     def get_merge_state_dicts(self, mp_world_size, mp_rank):
-        num_ckpt = len(self.ckpt_list)
-        assert num_ckpt % mp_world_size == 0, "Invalid checkpoints and world size for sd merge"
-        num_to_merge = num_ckpt // mp_world_size
-        ckpt_list = [self.ckpt_list[i] for i in range(num_to_merge * mp_rank, num_to_merge * (mp_rank + 1))]
-        logger.info(f"mp_rank: {mp_rank}, ckpt_list: {ckpt_list}")
-        return [self.checkpoint_engine.load(ckpt, map_location=lambda storage, loc: storage) for ckpt in ckpt_list]
+        per_rank, rest = divmod(len(self.ckpt_list), mp_world_size)
+        assert rest == 0, "Invalid checkpoints and world size for sd merge"
+        mine = self.ckpt_list[per_rank * mp_rank:per_rank * (mp_rank + 1)]
+        logger.info(f"mp_rank: {mp_rank}, ckpt_list: {mine}")
+        return [self._read(path) for path in mine]
 
     def get_split_state_dict(self, mp_world_size, mp_rank):
-        num_ckpt = len(self.ckpt_list)
-        assert mp_world_size % num_ckpt == 0, "Invalid checkpoints and world size for sd split"
-        num_to_split = mp_world_size // num_ckpt
-        ckpt_index = mp_rank // num_to_split
-        ckpt_offset = mp_rank % num_to_split
-        logger.info(f"mp_rank: {mp_rank}, ckpt_list: {self.ckpt_list[ckpt_index]}, offset: {ckpt_offset}")
-        sd = self.checkpoint_engine.load(self.ckpt_list[ckpt_index], map_location=lambda storage, loc: storage)
-        return sd, num_to_split, ckpt_offset
+        ranks_per_file, rest = divmod(mp_world_size, len(self.ckpt_list))
+        assert rest == 0, "Invalid checkpoints and world size for sd split"
+        which, offset = divmod(mp_rank, ranks_per_file)
+        logger.info(f"mp_rank: {mp_rank}, ckpt_list: {self.ckpt_list[which]}, offset: {offset}")
+        return self._read(self.ckpt_list[which]), ranks_per_file, offset
 
+    # ---- where the module's tensors live inside a checkpoint dict: at the top (key None), under a given key, or under
+    # ---- whichever of "module" / "model" exists ("auto")
     def _choose_module_key(self, sd):
-        assert not ("module" in sd and "model" in sd), "checkpoint has both 'model' and 'module' keys, not sure how to proceed"
-        assert "module" in sd or "model" in sd, "checkpoint contains neither 'model' or 'module' keys, not sure how to proceed"
-        return "module" if "module" in sd else "model"
+        found = [k for k in ("module", "model") if k in sd]
+        assert len(found) < 2, "checkpoint has both 'model' and 'module' keys, not sure how to proceed"
+        assert found, "checkpoint contains neither 'model' or 'module' keys, not sure how to proceed"
+        return found[0]
+
+    def _resolved_key(self, sd):
+        return self._choose_module_key(sd) if self.module_key == AUTO_MODULE_KEY else self.module_key
 
     def get_module(self, sd):
-        if self.module_key is None:
-            return sd
-        if self.module_key == AUTO_MODULE_KEY:
-            return sd[self._choose_module_key(sd)]
-        return sd[self.module_key]
+        key = self._resolved_key(sd) if self.module_key is not None else None
+        return sd if key is None else sd[key]
 
     def set_module(self, sd, module):
         if self.module_key is None:
-            sd = module
-        elif self.module_key == AUTO_MODULE_KEY:
-            sd[self._choose_module_key(sd)] = module
-        else:
-            sd[self.module_key] = module
+            return module
+        sd[self._resolved_key(sd)] = module
         return sd
 
     def check_ckpt_list(self):
-        assert len(self.ckpt_list) > 0
-        sd = self.checkpoint_engine.load(self.ckpt_list[0], map_location=lambda storage, loc: storage)
-        # a DeepSpeed checkpoint records its mp world size; the number of files must agree with it
-        if "mp_world_size" in sd.keys():
-            assert len(self.ckpt_list) == sd["mp_world_size"], f"checkpoint count {len(self.ckpt_list)} is different from saved mp_world_size {sd['mp_world_size']}"
+        assert len(self.ckpt_list) > 0, "empty checkpoint list"
+        head = self._read(self.ckpt_list[0])
+        recorded = head.get("mp_world_size") if hasattr(head, "get") else None
+        if recorded is not None:  # a DeepSpeed checkpoint knows how many shards it was written with
+            assert len(self.ckpt_list) == recorded, f"checkpoint count {len(self.ckpt_list)} is different from saved mp_world_size {recorded}"
 
     @abstractmethod
     def merge_state_dict(self, mp_world_size, mp_rank, quantize, quantize_bits, groups, mlp_extra_grouping):
-        pass
+        ...
 
     @abstractmethod
     def split_state_dict(self, mp_world_size, mp_rank, quantize, quantize_bits, groups, mlp_extra_grouping):
-        pass
+        ...
 
     @abstractmethod
     def sanity_check(self, ckpt_file_name):
-        pass
+        ...
 
 
 class MegatronSDLoader(SDLoaderBase):
@@ -242,7 +242,7 @@ class MegatronSDLoader(SDLoaderBase):
 
     def sanity_check(self, ckpt_file_name):
         required = ["attention.dense.weight", "mlp.dense_4h_to_h.weight", "attention.query_key_value", "mlp.dense_h_to_4h.weight", "mlp.dense_h_to_4h.bias"]
-        module = self.get_module(self.checkpoint_engine.load(ckpt_file_name, map_location=lambda storage, loc: storage))
+        module = self.get_module(self._read(ckpt_file_name))
         for part in required:
             assert any(part in k for k in module.keys()), f"key: {part} is not found in the checkpoint {ckpt_file_name}"
 

@@ -20,7 +20,7 @@ from enum import Enum
 
 import torch
 
-ALIGN = 64  # elements; keeps every shard boundary 128-byte aligned for 16-bit dtypes (TMA / 16-byte vector access)
+ALIGN = 128  # elements: shard boundaries are 256-byte aligned for 16-bit dtypes (TMA, 16-byte vectors) and whole fp8 quantisation blocks (ZeRO++)
 
 
 class ZeroParamType(Enum):

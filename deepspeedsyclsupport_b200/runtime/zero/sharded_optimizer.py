@@ -394,7 +394,6 @@ class ZeroShardedOptimizer:
         fused with 1/world scaling, dtype cast, accumulation into the gradient shard and the grad-norm partial."""
         want = (self.cuda and self.stage == 3 and self.shard_world > 1 and self.replica_world == 1 and not self.offload_param and
                 bool(getattr(self.zero_config, "fused_collectives", True)) and self.dtype == torch.bfloat16 and
-                not self.zero_config.zero_quantized_weights and not self.zero_config.zero_quantized_gradients and
                 os.environ.get("DSB200_DISABLE_P2P", "0") != "1" and self.shard_world <= 16)
         if not want:
             return
@@ -406,7 +405,36 @@ class ZeroShardedOptimizer:
             lp_bytes = (self.total_shard * esz + 255) // 256 * 256
             self._p2p_slot_bytes = (max_unit * esz + 255) // 256 * 256
             self._p2p_grad_off = lp_bytes
-            self.p2p = SymmetricBuffer(self.shard_group, lp_bytes + self.P2P_GRAD_SLOTS * self._p2p_slot_bytes)
+            total = lp_bytes + self.P2P_GRAD_SLOTS * self._p2p_slot_bytes
+            # ZeRO++ regions (block-scaled fp8: 1 payload byte per element + one fp32 scale per 128 elements)
+            self._qwz = bool(self.zero_config.zero_quantized_weights)
+            self._qgz = bool(self.zero_config.zero_quantized_gradients)
+            r256 = lambda n: (n + 255) // 256 * 256
+            if self._qgz:  # per gradient slot: payload + scales of one whole unit
+                self._qgz_q_off, self._qgz_q_bytes = total, r256(max_unit)
+                total += self.P2P_GRAD_SLOTS * self._qgz_q_bytes
+                self._qgz_s_off, self._qgz_s_bytes = total, r256(max_unit // 128 * 4)
+                total += self.P2P_GRAD_SLOTS * self._qgz_s_bytes
+            if self._qwz:  # quantised twin of this rank's parameter shard, refreshed after every step
+                self._qwz_q_off = total
+                total += r256(self.total_shard)
+                self._qwz_s_off = total
+                total += r256(self.total_shard // 128 * 4)
+            self.p2p = SymmetricBuffer(self.shard_group, total)
+            if self._qgz:
+                self._qgz_q = [self.p2p.view(self._qgz_q_off + k * self._qgz_q_bytes, (max_unit, ), torch.uint8) for k in range(self.P2P_GRAD_SLOTS)]
+                self._qgz_s = [self.p2p.view(self._qgz_s_off + k * self._qgz_s_bytes, (max_unit // 128, ), torch.float32) for k in range(self.P2P_GRAD_SLOTS)]
+            if self._qwz:
+                self._qwz_q = self.p2p.view(self._qwz_q_off, (self.total_shard, ), torch.uint8)
+                self._qwz_s = self.p2p.view(self._qwz_s_off, (self.total_shard // 128, ), torch.float32)
+            hpz = int(getattr(self.zero_config, "zero_hpz_partition_size", 1) or 1)
+            if hpz > 1:
+                # hpZ keeps a secondary shard inside the node so the backward all-gather stays off the inter-node links; this
+                # shard group is one NVSwitch domain, where every peer is already "intra-node" at full bandwidth
+                assert self.shard_world % hpz == 0 or hpz % self.shard_world == 0, \
+                    f"zero_hpz_partition_size={hpz} must divide (or be a multiple of) the shard world {self.shard_world}"
+                logger.info(f"ZeRO++ hpZ: partition size {hpz} inside one NVSwitch domain of {self.shard_world} GPUs -- the primary "
+                            "shards already are the intra-node secondary shards; no second copy is kept")
             self._p2p_slot_views = [self.p2p.view(self._p2p_grad_off + k * self._p2p_slot_bytes, (max_unit, ), torch.bfloat16)
                                     for k in range(self.P2P_GRAD_SLOTS)]
             self._p2p_next_slot = 0
@@ -419,8 +447,10 @@ class ZeroShardedOptimizer:
             if self._p2p_rs_mode == "nvls" and not self.p2p.mc_ptr:
                 self._p2p_rs_mode = "pull"
             self._p2p_comm_ctas = int(os.environ.get("DSB200_COMM_CTAS", "0"))
-            logger.info(f"ZeRO-3 peer-memory collectives: backend={self.p2p.backend} all-gather={self._p2p_ag_mode} "
-                        f"reduce-scatter={self._p2p_rs_mode}")
+            if self._qgz:
+                self._p2p_rs_mode = "fp8-pull"
+            logger.info(f"ZeRO-3 peer-memory collectives: backend={self.p2p.backend} all-gather={self._p2p_ag_mode}"
+                        f"{' (qwZ fp8 payload)' if self._qwz else ''} reduce-scatter={self._p2p_rs_mode}")
             self.comm_dtype = torch.bfloat16
         except Exception as e:  # pragma: no cover - peer access unavailable: keep the NCCL path
             logger.warning(f"peer-memory collectives unavailable ({e}); using NCCL")
@@ -459,12 +489,79 @@ class ZeroShardedOptimizer:
             self._p2p_reduce_count += 1
             dst = self.grad_shard[u.shard_off:u.shard_off + u.shard_numel]
             fuse_norm = self.gas == 1
+            if self._rs_adam_enabled() and self._p2p_rs_adam_unit(u):
+                u.full_grad = None
+                u.reduced = True
+                return
+            if self._qgz and u.shard_numel % 128 == 0:
+                return self._p2p_reduce_unit_qgz(u, dst, fuse_norm)
             rs = self.p2p.nvls_reduce_scatter if self._p2p_rs_mode == "nvls" else self.p2p.reduce_scatter
             rs(dst, self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes, torch.bfloat16, u.shard_numel,
                scale=1.0 / self.grad_divisor, accumulate=self.gas > 1, sumsq=self._p2p_sumsq if fuse_norm else None,
                max_ctas=self._p2p_comm_ctas)
         u.full_grad = None
         u.reduced = True
+
+    def _p2p_reduce_unit_qgz(self, u, dst, fuse_norm):
+        """qgZ on one NVSwitch hop: quantise this rank's whole unit gradient to block-scaled fp8 inside its symmetric slot,
+        barrier, then every rank pulls ITS slice of payload + scales from all peers and dequant-reduces (fp32 sum) straight
+        into the gradient shard, with scale / sum-of-squares fused.  (Called on the reduce stream; the bf16 -> fp8 barrier
+        replaces the plain one.)"""
+        from ...ops import quantizer as Q
+        k = u.p2p_slot
+        Q.quantize_fp8_block(self._p2p_slot_views[k][:u.padded], out=(self._qgz_q[k][:u.padded], self._qgz_s[k][:u.padded // 128]))
+        self.p2p.barrier()  # every rank's payload is written
+        self.p2p.fp8_reduce_scatter(dst, self._qgz_q_off + k * self._qgz_q_bytes, self._qgz_s_off + k * self._qgz_s_bytes,
+                                    u.shard_numel, scale=1.0 / self.grad_divisor, accumulate=self.gas > 1,
+                                    sumsq=self._p2p_sumsq if fuse_norm else None, max_ctas=self._p2p_comm_ctas)
+        u.full_grad = None
+        u.reduced = True
+
+    # ---- reduce-scatter fused with the partitioned AdamW update (csrc/comm/symm.cu rs_adam_kernel)
+    def _rs_adam_enabled(self):
+        """The update may run inside backward, unit by unit, only when nothing global has to be known first: no gradient
+        clipping (the clip factor needs the norm of ALL gradients), no accumulation, no loss scaling / overflow skip (bf16),
+        a fused Adam flavour, optimizer state resident on the device.  With clipping the step stays two-phase: the fused
+        reduce-scatter produces shard + sum of squares during backward, then one Adam pass reads the clip factor on the device."""
+        ok = getattr(self, "_rs_adam_ok", None)
+        if ok is None:
+            ok = (self.p2p is not None and self.gas == 1 and self.clip_grad == 0.0 and self.dtype == torch.bfloat16 and
+                  self._opt_kind in _ADAM_TYPES and not self.custom_loss_scaler and len(self.regions) == 1 and
+                  self.regions[0].device.type == "cuda" and not getattr(self.regions[0], "is_nvme", False) and
+                  self.replica_world == 1 and os.environ.get("DSB200_FUSED_RS_ADAM", "1") != "0")
+            self._rs_adam_ok = ok
+            if ok:
+                logger.info("ZeRO-3: gradient reduce-scatter fused with the partitioned AdamW update (no clipping, gas == 1)")
+        return ok
+
+    def _unit_runs(self, u):
+        """[(group, lo, hi)] in rank-flat shard coordinates for one unit (trainable ranges only)."""
+        runs = getattr(u, "_flat_runs", None)
+        if runs is None:
+            runs = u._flat_runs = [(g, u.shard_off + a, u.shard_off + b) for g, a, b in u.shard_group_runs() if g >= 0 and b > a]
+        return runs
+
+    def _p2p_rs_adam_unit(self, u):
+        runs = self._unit_runs(u)
+        if any((lo - u.shard_off) % 8 or (hi - lo) % 8 for _, lo, hi in runs):
+            return False
+        region = self.regions[0]
+        self._ensure_state(region, self._opt_kind)
+        kind = self._opt_kind
+        adamw = False if kind == "Adam" else (True if kind == "AdamW" else bool(getattr(self.optimizer, "adam_w_mode", True)))
+        g_out = self.grad_shard if self.grad_shard.dtype == torch.bfloat16 else None
+        src_off = self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes
+        for gi, lo, hi in runs:
+            hp = self.param_groups[gi]
+            b1, b2 = hp.get("betas", (0.9, 0.999))
+            self.p2p.rs_adam_range(src_off, u.shard_numel, lo - u.shard_off, region.master[lo:hi], region.state["exp_avg"][lo:hi],
+                                   region.state["exp_avg_sq"][lo:hi], self.lp_shard[lo:hi], scale=1.0 / self.grad_divisor,
+                                   lr=hp["lr"], beta1=b1, beta2=b2, eps=hp.get("eps", 1e-8), weight_decay=hp.get("weight_decay", 0.0),
+                                   adamw_mode=adamw, bias_correction=hp.get("bias_correction", True), step=self._step_count + 1,
+                                   g_out=g_out[lo:hi] if g_out is not None else None, sumsq=self._p2p_sumsq,
+                                   nvls=self._p2p_rs_mode == "nvls", max_ctas=self._p2p_comm_ctas)
+        u.adam_done = True
+        return True
 
     def _build_runs(self):
         """(group_id, lo, hi) runs over the rank-flat shard space, merged across unit boundaries."""
@@ -717,10 +814,31 @@ class ZeroShardedOptimizer:
         persistent GEMMs keep all 148 SMs); small ones (norm weights) use one pull kernel, cheaper than W tiny DMAs."""
         nbytes = u.shard_numel * 2
         off = self._p2p_lp_off + u.shard_off * 2
+        if self._qwz and nbytes >= self.P2P_CE_MIN_BYTES:
+            return self._p2p_gather_unit_qwz(u)
         if nbytes >= self.P2P_CE_MIN_BYTES and self._p2p_ag_mode == "ce":
             self.p2p.all_gather_ce(u.full, off, nbytes)
         else:
             self.p2p.all_gather(u.full, off, nbytes, max_ctas=self._p2p_comm_ctas)
+
+    def _p2p_gather_unit_qwz(self, u):
+        """qwZ: peers' shards arrive as block-scaled fp8 (half the NVLink bytes of bf16) on the copy engines into a staging
+        buffer; one local kernel dequantises into u.full.  This rank's own slice is copied in bf16 (exact)."""
+        from ...ops import quantizer as Q
+        n, W, r = u.shard_numel, self.shard_world, self.shard_rank
+        stage_q = torch.empty(W * n, dtype=torch.uint8, device=self.device)
+        stage_s = torch.empty(W * n // 128, dtype=torch.float32, device=self.device)
+        self.p2p.all_gather_ce(stage_q, self._qwz_q_off + u.shard_off, n)
+        self.p2p.all_gather_ce(stage_s, self._qwz_s_off + u.shard_off // 128 * 4, n // 128 * 4)
+        Q.dequantize_fp8_block(stage_q, stage_s, out=u.full)
+        u.full[r * n:(r + 1) * n].copy_(u.shard)
+        stage_q.record_stream(torch.cuda.current_stream())
+        stage_s.record_stream(torch.cuda.current_stream())
+
+    def _p2p_refresh_qwz(self):
+        """Re-quantise this rank's parameter shard into its symmetric fp8 twin (after every update of the shard)."""
+        from ...ops import quantizer as Q
+        Q.quantize_fp8_block(self.lp_shard, out=(self._qwz_q, self._qwz_s))
 
     def _p2p_shards_written(self):
         """Call after writing this rank's 16-bit shard outside step() (write-back of gathered parameters, checkpoint load,
@@ -736,6 +854,8 @@ class ZeroShardedOptimizer:
             return
         if stream is not None and main is not None:
             stream.wait_stream(main)
+        if self._qwz:
+            self._p2p_refresh_qwz()
         self.p2p.barrier()
         self._p2p_shards_synced = True
 
@@ -1089,6 +1209,18 @@ class ZeroShardedOptimizer:
         kind = self._opt_kind
         if not self._is_fused_kind(kind):
             return self._generic_step()
+        if getattr(self, "_rs_adam_ok", False):
+            # units whose update already ran inside backward are done; the rest (no gradient this step) take the plain kernel
+            region = self.regions[0]
+            self._ensure_state(region, kind)
+            for u in self.units:
+                if getattr(u, "adam_done", False):
+                    u.adam_done = False
+                    continue
+                for gi, lo, hi in self._unit_runs(u):
+                    s_ = slice(lo, hi)
+                    self._apply_update(kind, region, s_, self.grad_shard[s_], self.lp_shard[s_], self.param_groups[gi], self._inv_scale, 1.0)
+            return
         for region in self.regions:
             self._ensure_state(region, kind)
             on_host = region.device.type == "cpu" and self.cuda
@@ -1207,6 +1339,8 @@ class ZeroShardedOptimizer:
             pass
         if self.p2p is not None:
             # peers may pull the updated shards only after every rank finished its step: device barrier, no host sync
+            if self._qwz:
+                self._p2p_refresh_qwz()
             self.p2p.barrier()
             self._p2p_shards_synced = True
             for u in self.units:

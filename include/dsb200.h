@@ -131,6 +131,14 @@ int dsb200_p2p_alltoall(void* const* peer_ptrs, long long src_off, void* dst, lo
 int dsb200_p2p_reduce_scatter(void* const* peer_ptrs, long long src_off, int src_dtype, void* dst, int dst_dtype,
                               long long n, int rank, int world, float scale, int accumulate, float* sumsq, int max_ctas,
                               dsb200_stream_t stream);
+/* Range form: Adam on elements [elem_lo, elem_lo + n) of this rank's slice (slice length n_per_rank) of the W*n_per_rank
+ * bf16 gradient buffer at src_off.  p/m/v/lp/g_out point at element elem_lo of the local shard.  mc_base != NULL: the sum
+ * comes from the NVSwitch (multimem.ld_reduce); NULL: pulled from the peers.  g_out / sumsq optional (may be NULL). */
+int dsb200_p2p_rs_adam_range(void* const* peer_ptrs, void* mc_base, long long src_off, long long n_per_rank,
+                             long long elem_lo, long long n, float* p, float* m, float* v, void* lp, void* g_out,
+                             float* sumsq, int rank, int world, float scale, float lr, float beta1, float beta2, float eps,
+                             float weight_decay, int adamw_mode, int bias_correction, int step, int max_ctas,
+                             dsb200_stream_t stream);
 int dsb200_p2p_rs_adam(void* const* peer_ptrs, long long src_off, float* p, float* m, float* v, void* lp, long long n,
                        int rank, int world, float scale, float lr, float beta1, float beta2, float eps, float weight_decay,
                        int adamw_mode, int bias_correction, int step, int max_ctas, dsb200_stream_t stream);
@@ -150,6 +158,11 @@ int dsb200_nvls_allreduce_bf16(void* mc_base, long long off, long long n, int ra
                                dsb200_stream_t stream);
 int dsb200_nvls_allgather(void* mc_base, long long dst_off, const void* src, long long bytes, int rank, int max_ctas,
                           dsb200_stream_t stream);
+/* qgZ consumer: q_off / s_off = byte offsets of the fp8 payload (W*n bytes) and the fp32 block scales (W*n/128 floats) in
+ * every rank's symmetric buffer; n = elements per rank (multiple of 128); dst dtype 0 bf16 / 2 fp32. */
+int dsb200_p2p_fp8_reduce_scatter(void* const* peer_ptrs, long long q_off, long long s_off, void* dst, int dst_dtype,
+                                  long long n, int rank, int world, float scale, int accumulate, float* sumsq,
+                                  int max_ctas, dsb200_stream_t stream);
 
 /* ---- csrc/elementwise/elementwise.cu */
 /* out[0] += sum(x[i]^2) over n elements (dtype 0 bf16 / 1 fp16 / 2 fp32).  x must be 16-byte aligned. */

@@ -369,8 +369,9 @@ def test_nvls_and_copy_engine_collectives_match_nccl():
                     backend="nccl")
 
 
-def _zero3_train(steps, disable_p2p):
+def _zero3_train(steps, disable_p2p, clip=1.0, fused_rs_adam=True, zeropp=False):
     import os
+    os.environ["DSB200_FUSED_RS_ADAM"] = "1" if fused_rs_adam else "0"
     import deepspeedsyclsupport_b200 as deepspeed
     from deepspeedsyclsupport_b200 import comm as dist
     from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
@@ -384,11 +385,14 @@ def _zero3_train(steps, disable_p2p):
     # turning the bf16 / atomic-order noise of near-zero gradients into +-lr steps, so parameter differences between the two
     # runs measure the communication path and not the optimizer's sign amplification
     engine, _, _, _ = deepspeed.initialize(model=model, config={
-        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": 1.0,
-        "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "eps": 1e-1, "weight_decay": 0.0}},
-        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0}})
+        "train_micro_batch_size_per_gpu": 2, "bf16": {"enabled": True}, "gradient_clipping": clip,
+        "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "eps": 1e-1, "weight_decay": 0.01}},
+        "zero_optimization": {"stage": 3, "stage3_param_persistence_threshold": 0, "zero_quantized_weights": zeropp,
+                              "zero_quantized_gradients": zeropp, "zero_hpz_partition_size": 2 if zeropp else 1}})
     opt = engine.optimizer
     assert (opt.p2p is None) == bool(disable_p2p)
+    if zeropp:
+        opt.P2P_CE_MIN_BYTES = 1024  # tiny test model: send its units through the quantised path too
     init = {n: opt.get_full_fp32_param(p).float().cpu() for n, p in model.named_parameters()}
     g = torch.Generator().manual_seed(5 + rank)
     ids = torch.randint(0, 1024, (2, 128), generator=g).cuda()
@@ -403,7 +407,7 @@ def _zero3_train(steps, disable_p2p):
         engine.step()
         losses.append(loss.item())
     delta = {n: opt.get_full_fp32_param(p).float().cpu() - init[n] for n, p in model.named_parameters()}
-    mode = getattr(opt, "_p2p_rs_mode", "nccl")
+    mode = getattr(opt, "_p2p_rs_mode", "nccl") + ("+rs_adam" if getattr(opt, "_rs_adam_ok", False) else "")
     return losses, delta, grads, mode
 
 
@@ -475,3 +479,49 @@ def _shard_write_race_body():
 
 def test_zero3_peer_path_shard_write_is_ordered_before_pulls():
     run_distributed(_shard_write_race_body, world_size=2, backend="nccl")
+
+
+def _zero3_rs_adam_body():
+    """Without clipping the partitioned AdamW update runs inside backward, fused into each unit's reduce-scatter
+    (rs_adam_kernel); parameters after 4 steps must equal the two-phase path (reduce-scatter, then one Adam pass in step())."""
+    from deepspeedsyclsupport_b200 import comm as dist
+    l_f, d_f, g_f, mode_f = _zero3_train(4, disable_p2p=False, clip=0.0, fused_rs_adam=True)
+    l_u, d_u, g_u, mode_u = _zero3_train(4, disable_p2p=False, clip=0.0, fused_rs_adam=False)
+    assert mode_f.endswith("+rs_adam") and not mode_u.endswith("+rs_adam"), (mode_f, mode_u)
+
+    def rel(a, b):
+        return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+    assert rel(g_f, g_u) < 2e-2, ("kept gradient shard", rel(g_f, g_u))
+    worst = max(rel(d_f[n], d_u[n]) for n in d_f)
+    assert worst < 5e-2, worst
+    assert all(abs(x - y) < 5e-2 for x, y in zip(l_f, l_u)), (l_f, l_u)
+    if dist.get_rank() == 0:
+        print(f"ZERO3 {mode_f} vs {mode_u}: worst parameter-update rel diff after 4 steps {worst:.2e}; losses {l_f} vs {l_u}", flush=True)
+
+
+def test_zero3_fused_reduce_scatter_adam_equals_two_phase():
+    run_distributed(_zero3_rs_adam_body, world_size=2, backend="nccl", timeout=400)
+
+
+def _zeropp_body():
+    """ZeRO++ on the peer path: qwZ (fp8 block-scaled weight all-gather on the copy engines + local dequant) and qgZ
+    (quantise -> pull -> dequant-reduce) must track plain bf16 ZeRO-3 within fp8 quantisation error."""
+    from deepspeedsyclsupport_b200 import comm as dist
+    l_q, d_q, g_q, mode = _zero3_train(5, disable_p2p=False, zeropp=True)
+    l_b, d_b, g_b, _ = _zero3_train(5, disable_p2p=False, zeropp=False)
+    assert mode.startswith("fp8-pull"), mode
+
+    def rel(a, b):
+        return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+    g_err = rel(g_q, g_b)
+    assert 1e-4 < g_err < 8e-2, ("first-step gradient shard (must differ by quantisation error only)", g_err)
+    assert all(abs(x - y) < 0.15 for x, y in zip(l_q, l_b)), (l_q, l_b)
+    assert l_q[-1] < l_q[0], l_q
+    if dist.get_rank() == 0:
+        print(f"ZEROPP qwZ+qgZ vs bf16 ZeRO-3: first-step gradient rel diff {g_err:.2e}; losses {l_q} vs {l_b}", flush=True)
+
+
+def test_zeropp_quantized_weights_and_gradients_track_bf16():
+    run_distributed(_zeropp_body, world_size=2, backend="nccl", timeout=400)
