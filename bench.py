@@ -91,7 +91,7 @@ class ClockSampler:
 
 def ds_config(args, world):
     cfg = _ds_config(args, world)
-    if args.zeropp:
+    if getattr(args, "zeropp", False):
         cfg["zero_optimization"].update({"zero_quantized_weights": True, "zero_quantized_gradients": True})
     return cfg
 
@@ -215,15 +215,17 @@ def run_own(args):
 
     ms, e2e, launches, clocks = timed_loops(args, step, step_e2e, world, dist, torch, lambda: native.launch_count)
     # exposed communication: separate pass with the optimizer's comm probe on (not inside the timed region)
-    exposed_ms, exposed_sites = 0.0, {}
+    exposed_ms, exposed_sites, nvlink_rx = 0.0, {}, 0
     opt = engine.optimizer
     if world > 1 and hasattr(opt, "comm_probe_start"):
         k = max(2, min(args.steps, 4))
         torch.cuda.synchronize()
         dist.barrier()
         opt.comm_probe_start()
+        rx0 = getattr(opt, "nvlink_rx_bytes", 0)
         for _ in range(k):
             step()
+        nvlink_rx = (getattr(opt, "nvlink_rx_bytes", 0) - rx0) // k
         total, sites = opt.comm_probe_stop(detail=True)
         t = torch.tensor([total / k], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -239,6 +241,9 @@ def run_own(args):
         act = False if (args.no_act_ckpt or resolved in (None, "none")) else resolved
         extra["exposed_comm_ms"] = exposed_ms
         extra["exposed_comm_sites_rank0"] = exposed_sites
+        extra["nvlink_rx_bytes_per_step_per_gpu"] = int(nvlink_rx)  # payload bytes of the ZeRO collectives, counted by the optimizer
+        if os.environ.get("DSB200_PROBE_TRACE") == "1":
+            extra["exposed_comm_trace_rank0"] = [ms for site, ms in getattr(opt, "comm_probe_trace", []) if site == "gather_wait"]
         extra["exposed_comm_how"] = ("CUDA-event pairs around every point where the compute stream waits for a gather / reduce stream or "
                                      "runs a collective itself (grad-norm all-reduce, post-step barrier + persistent gathers); "
                                      "per step, max over ranks, measured in a separate pass after the timed one")

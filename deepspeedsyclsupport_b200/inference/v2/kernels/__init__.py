@@ -1,5 +1,6 @@
 """Python wrappers of the ragged device ops (csrc/ragged/ragged_ops.cu) with PyTorch oracles for CPU / tests."""
 import math
+import os
 
 import torch
 
@@ -8,12 +9,14 @@ from ....ops import native
 native.register_sigs({
     "dsb200_kv_rotary_append": "pppppp iiiiiii p",
     "dsb200_paged_attention": "pppppp iiiiii f p",
+    "dsb200_paged_flash_attention": "pppppp iiiiiii f ii p p",
+    "dsb200_paged_flash_scratch_bytes": "iiiii",
     "dsb200_ragged_embed": "ppppp iii p",
     "dsb200_logits_gather": "ppp ii p",
     "dsb200_top_k_gating": "ppppp iiii p",
     "dsb200_moe_scatter": "ppppppp iiii p",
     "dsb200_moe_gather": "pppp iii p",
-})
+}, restype_long=("dsb200_paged_flash_scratch_bytes", ))
 
 
 def kv_rotary_append(qkv, kv_cache, tok_seq, tok_pos, block_table, inv_freq, hq, hkv, d, rot_dim=None):
@@ -59,10 +62,44 @@ def paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d
     return out
 
 
-def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None):
+def paged_flash_supported(qkv, kv_cache, hq, hkv, d):
+    """The tcgen05 kernel covers bf16, head_dim 64 / 128, q:kv head ratios and KV block sizes that divide 128."""
+    group = hq // max(hkv, 1)
+    return (qkv.is_cuda and qkv.dtype == torch.bfloat16 and kv_cache.dtype == torch.bfloat16 and d in (64, 128) and hq % hkv == 0 and
+            128 % group == 0 and kv_cache.shape[2] >= 8 and 128 % kv_cache.shape[2] == 0 and os.environ.get("DSB200_PAGED_FLASH", "1") != "0")
+
+
+def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, n_splits=None):
+    """Attention of every ragged token over its sequence's paged KV history on the tensor cores (csrc/attn/paged_flash.cu):
+    atoms of up to 128/group tokens x kv head, KV pages fetched by TMA through the block table, prefill chunks and decode steps
+    alike; small batches over long contexts are split along the KV axis (`n_splits`, chosen here unless given) and merged."""
+    scale = scale if scale is not None else 1.0 / math.sqrt(d)
+    T = qkv.shape[0]
+    bs, group = kv_cache.shape[2], hq // hkv
+    nt = 128 // group
+    max_atoms = max(1, min(T, (T + nt - 1) // nt + block_table.shape[0]))
+    if n_splits is None:
+        pages = -(-(max_context if max_context is not None else block_table.shape[1] * bs) // 128)
+        ctas = max_atoms * hkv
+        n_splits = 1 if ctas >= 96 else max(1, min(16, 148 // ctas, pages))
+    out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
+    nbytes = native.lib().dsb200_paged_flash_scratch_bytes(T, hq, d, max_atoms, n_splits)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=qkv.device)
+    rc = native.lib().dsb200_paged_flash_attention(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq),
+                                                   native.ptr(tok_pos), native.ptr(block_table), T, hq, hkv, d, bs,
+                                                   block_table.shape[1], kv_cache.shape[0], float(scale), max_atoms, n_splits,
+                                                   native.ptr(scratch), native.stream_ptr())
+    native.check(rc)
+    return out
+
+
+def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None):
     scale = scale if scale is not None else 1.0 / math.sqrt(d)
     if not qkv.is_cuda:
         return paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale)
+    if paged_flash_supported(qkv, kv_cache, hq, hkv, d):
+        return paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, max_context=max_context)
+    # head sizes the tensor-core kernel does not cover (96, 256): CUDA-core kernel, one CTA per (token, kv head)
     T = qkv.shape[0]
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
     rc = native.lib().dsb200_paged_attention(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq),

@@ -383,10 +383,41 @@ class RaggedTransformer:
         yield "non_transformer", self.non_transformer
 
     # ---- forward
+    def _tp_ops(self):
+        """Peer-memory TP collectives (fused GEMM + all-reduce, switch all-reduce, logits push), built on first use; None when
+        the group is not a single-node CUDA bf16 group (then NCCL is used)."""
+        ops = getattr(self, "_tp_coll", False)
+        if ops is False:
+            ops = None
+            import os
+            if (self.tp > 1 and self.dtype == torch.bfloat16 and torch.device(self.device).type == "cuda" and
+                    os.environ.get("DSB200_DISABLE_P2P", "0") != "1" and self.tp <= torch.cuda.device_count()):
+                try:
+                    from ..tp_collectives import RaggedTPCollectives
+                    sm = getattr(self.engine_config, "state_manager", None)
+                    ops = RaggedTPCollectives(self.tp_group, self.spec.hidden_size, getattr(sm, "max_ragged_batch_size", 768),
+                                              getattr(sm, "max_ragged_sequence_count", 512), self.vocab_padded // self.tp)
+                except Exception as e:  # no peer access: stay on NCCL
+                    from ....utils.logging import logger
+                    logger.warning(f"FastGen peer-memory TP collectives unavailable ({e}); using NCCL")
+                    ops = None
+            self._tp_coll = ops
+        return ops
+
     def _all_reduce(self, x):
         if self.tp > 1:
+            ops = self._tp_ops()
+            if ops is not None:
+                return ops.all_reduce(x if x.is_contiguous() else x.contiguous())
             dist.all_reduce(x, group=self.tp_group)
         return x
+
+    def _row_parallel(self, lin, x, w):
+        """all-reduce(lin(x, w)): one fused tcgen05 GEMM + peer all-reduce kernel when the weight is plain bf16."""
+        ops = self._tp_ops() if self.tp > 1 else None
+        if ops is not None and ops.usable_for(x, w):
+            return ops.row_parallel(x, w)
+        return self._all_reduce(lin(x, w))
 
     def _mlp(self, L, h):
         if self.moe_mod is not None:
@@ -403,7 +434,10 @@ class RaggedTransformer:
             residual, hn = self.norm_mod(x if residual is None else residual, None if residual is None else x, L["norm1_w"], L.get("norm1_b"))
             qkv = self.qkv_lin(hn, L["qkv_w"], L.get("qkv_b"))
             attn = self.attn_mod(qkv, state_manager.get_cache(li), batch)
-            attn_out = self.o_lin(attn, L["o_w"])
+            if not s.parallel_block:
+                attn_out = self._row_parallel(self.o_lin, attn, L["o_w"])
+            else:
+                attn_out = self.o_lin(attn, L["o_w"])
             if s.parallel_block:
                 # gpt-neox gives the MLP its own LayerNorm of the block input (= the residual stream after the fused add)
                 mlp_in = self.norm_mod(residual, None, L["norm2_w"], L.get("norm2_b"))[1] if s.parallel_norm2 else hn
@@ -413,17 +447,23 @@ class RaggedTransformer:
                 if "mlp2_b" in L:
                     x = x + L["mlp2_b"]
                 continue
-            attn_out = self._all_reduce(attn_out)
             if "o_b" in L:
                 attn_out = attn_out + L["o_b"]
             residual, hn = self.norm_mod(residual, attn_out, L["norm2_w"], L.get("norm2_b"))
-            x = self._all_reduce(self._mlp(L, hn))
+            if self.moe_mod is None:
+                x = self._row_parallel(self.mlp2_lin, self.mlp1_lin(hn, L["mlp1_w"], L.get("mlp1_b")), L["mlp2_w"])
+            else:
+                x = self._all_reduce(self._mlp(L, hn))
             if "mlp2_b" in L:
                 x = x + L["mlp2_b"]
         logits = self.unembed_mod(x, nt.lm_head, batch, bias=nt.get("lm_head_b"), gamma=nt.final_norm_w, beta=nt.get("final_norm_b"),
                                   residual=residual)
         if self.tp > 1:
-            full = torch.empty(self.tp, *logits.shape, dtype=logits.dtype, device=logits.device)
-            dist.all_gather_into_tensor(full, logits.contiguous(), group=self.tp_group)
-            logits = full.permute(1, 0, 2).reshape(logits.shape[0], -1)
+            ops = self._tp_ops()
+            if ops is not None:
+                logits = ops.gather_logits(logits)
+            else:
+                full = torch.empty(self.tp, *logits.shape, dtype=logits.dtype, device=logits.device)
+                dist.all_gather_into_tensor(full, logits.contiguous(), group=self.tp_group)
+                logits = full.permute(1, 0, 2).reshape(logits.shape[0], -1)
         return logits[:, :s.vocab_size]

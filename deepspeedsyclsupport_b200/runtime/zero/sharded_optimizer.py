@@ -30,6 +30,7 @@ from ..fp16.loss_scaler import CreateLossScaler
 from .param_store import ParamUnit, ZeroParamStatus, build_units
 
 _ADAM_TYPES = ("Adam", "AdamW", "FusedAdam", "DeepSpeedCPUAdam")
+_LAST_OPT = None
 
 
 def _in_backward():
@@ -212,6 +213,8 @@ class ZeroShardedOptimizer:
         self._inv_scale = torch.ones(1, dtype=torch.float32, device=self.device)
         self._skip_flag = torch.zeros(1, dtype=torch.int32, device=self.device)
 
+        global _LAST_OPT
+        _LAST_OPT = self  # debugging / test hook: the most recently built ZeRO optimizer of this process
         self._opt_kind = type(self.optimizer).__name__ if self.optimizer is not None else None
         self._fwd_keep = None
         self._local_grads_only = False
@@ -441,6 +444,7 @@ class ZeroShardedOptimizer:
             self._p2p_reduce_count = 0
             self._p2p_barrier_events = {}
             self._p2p_sumsq = torch.zeros(1, dtype=torch.float32, device=self.device)
+            self.nvlink_rx_bytes = 0  # running count of payload bytes this rank receives over NVLink (algorithmic, for reports)
             self._p2p_shards_synced = False
             self._p2p_ag_mode = os.environ.get("DSB200_AG_MODE", "ce")       # ce = copy engines, sm = pull kernel
             self._p2p_rs_mode = os.environ.get("DSB200_RS_MODE", "nvls" if self.p2p.mc_ptr else "pull")
@@ -494,7 +498,10 @@ class ZeroShardedOptimizer:
                 u.reduced = True
                 return
             if self._qgz and u.shard_numel % 128 == 0:
+                self.nvlink_rx_bytes += (self.shard_world - 1) * (u.shard_numel + u.shard_numel // 128 * 4)
                 return self._p2p_reduce_unit_qgz(u, dst, fuse_norm)
+            # NVLS: the switch delivers the finished sum (1x the slice); pull: one read of the slice per peer
+            self.nvlink_rx_bytes += u.shard_numel * 2 * (1 if self._p2p_rs_mode == "nvls" else self.shard_world - 1)
             rs = self.p2p.nvls_reduce_scatter if self._p2p_rs_mode == "nvls" else self.p2p.reduce_scatter
             rs(dst, self._p2p_grad_off + u.p2p_slot * self._p2p_slot_bytes, torch.bfloat16, u.shard_numel,
                scale=1.0 / self.grad_divisor, accumulate=self.gas > 1, sumsq=self._p2p_sumsq if fuse_norm else None,
@@ -815,7 +822,9 @@ class ZeroShardedOptimizer:
         nbytes = u.shard_numel * 2
         off = self._p2p_lp_off + u.shard_off * 2
         if self._qwz and nbytes >= self.P2P_CE_MIN_BYTES:
+            self.nvlink_rx_bytes += (self.shard_world - 1) * (u.shard_numel + u.shard_numel // 128 * 4)
             return self._p2p_gather_unit_qwz(u)
+        self.nvlink_rx_bytes += (self.shard_world - 1) * nbytes
         if nbytes >= self.P2P_CE_MIN_BYTES and self._p2p_ag_mode == "ce":
             self.p2p.all_gather_ce(u.full, off, nbytes)
         else:
@@ -896,8 +905,11 @@ class ZeroShardedOptimizer:
         if self.cuda:
             torch.cuda.synchronize()
         by_site = {}
+        self.comm_probe_trace = []  # [(site, ms)] in program order, for timelines
         for site, a, b in pairs:
-            by_site[site] = by_site.get(site, 0.0) + a.elapsed_time(b)
+            ms = a.elapsed_time(b)
+            by_site[site] = by_site.get(site, 0.0) + ms
+            self.comm_probe_trace.append((site, round(ms, 3)))
         total = float(sum(by_site.values()))
         return (total, by_site) if detail else total
 
@@ -992,10 +1004,19 @@ class ZeroShardedOptimizer:
         for u in self.units:
             for m in u.modules:
                 mod_units.setdefault(id(m), (m, []))[1].append(u)
-        # modules that *use* a tied parameter owned by another unit must fetch that unit as well
+        # modules that *use* a tied parameter owned by another unit must fetch that unit as well.  Only the parameters a hooked
+        # module holds itself (directly, or through children without a hook of their own) count: descending into hooked
+        # children would make the root module fetch -- and wait for -- every unit of the model before its first kernel
+        def held(m, top=True):
+            if not top and id(m) in mod_units:
+                return
+            yield from m.parameters(recurse=False)
+            for child in m.children():
+                yield from held(child, False)
+
         for m in self.module.modules():
             if id(m) in mod_units:
-                for p in m.parameters():
+                for p in held(m):
                     u = self.owner.get(id(p))
                     if u is not None and u not in mod_units[id(m)][1]:
                         mod_units[id(m)][1].append(u)

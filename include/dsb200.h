@@ -113,6 +113,17 @@ int dsb200_flash_fwd_trace(long long* buf);
 int dsb200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int hq, int hkv, int head_dim, int causal,
                           float scale, dsb200_stream_t stream);
 
+/* ---- csrc/attn/paged_flash.cu */
+/* Bytes of scratch dsb200_paged_flash_attention needs: atom list + count, plus the split-KV partials when n_splits > 1. */
+long long dsb200_paged_flash_scratch_bytes(int n_tokens, int hq, int head_dim, int max_atoms, int n_splits);
+/* out[t][hq*D] = attention of ragged token t over keys [0, tok_pos[t]] of its sequence, KV read from the blocked cache
+ * [num_blocks][2][block_size][hkv][D] (bf16) through the block table.  max_atoms >= number of atoms of the batch
+ * (<= n_tokens; ceil(n_tokens / (128/group)) + number of sequences is enough).  n_splits >= 1 splits the KV range of every atom. */
+int dsb200_paged_flash_attention(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
+                                 const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
+                                 int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
+                                 void* scratch, dsb200_stream_t stream);
+
 /* ---- csrc/comm/symm.cu */
 /* ---- allocation / mapping (host pointers unless noted) */
 int dsb200_symm_alloc(long long bytes, void** ptr, unsigned char* handle64);

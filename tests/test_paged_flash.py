@@ -1,0 +1,72 @@
+"""Paged flash attention (csrc/attn/paged_flash.cu, tcgen05): oracle = dense fp32 attention over the gathered KV history."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed=0):
+    """Ragged batch of len(seq_new) sequences: seq_seen[i] tokens already cached, seq_new[i] new ones.  Blocks are handed out in a
+    shuffled order so page gathering is really exercised."""
+    g = torch.Generator().manual_seed(seed)
+    n_seq = len(seq_new)
+    max_len = max(a + b for a, b in zip(seq_new, seq_seen))
+    max_blocks = -(-max_len // bs) + 1
+    num_blocks = n_seq * max_blocks + 3
+    perm = torch.randperm(num_blocks, generator=g)
+    block_table = perm[:n_seq * max_blocks].view(n_seq, max_blocks).int()
+    kv_cache = torch.randn(num_blocks, 2, bs, hkv, d, generator=g).bfloat16()
+    tok_seq, tok_pos = [], []
+    for s in range(n_seq):
+        for i in range(seq_new[s]):
+            tok_seq.append(s)
+            tok_pos.append(seq_seen[s] + i)
+    T = len(tok_seq)
+    qkv = torch.randn(T, (hq + 2 * hkv) * d, generator=g).bfloat16()
+    dev = "cuda"
+    return (qkv.to(dev), kv_cache.to(dev), torch.tensor(tok_seq, dtype=torch.int32, device=dev),
+            torch.tensor(tok_pos, dtype=torch.int32, device=dev), block_table.to(dev))
+
+
+def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0):
+    from deepspeedsyclsupport_b200.inference.v2 import kernels as K
+    qkv, kv, ts, tp, bt = _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed)
+    scale = d ** -0.5
+    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits).float()
+    want = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), hq, hkv, d, scale).float().cuda()
+    torch.cuda.synchronize()
+    err = (got - want).abs().max().item()
+    assert torch.isfinite(got).all() and err < 2e-2, (seq_new, seq_seen, hq, hkv, d, bs, n_splits, err)
+
+
+def test_mixed_prefill_and_decode_gqa():
+    # GQA 8:1 (16 tokens per atom): a long prefill chunk, a chunk continuing a cached prefix, and three decode steps
+    _check(seq_new=[300, 70, 1, 1, 1], seq_seen=[0, 517, 129, 5, 1000], hq=16, hkv=2, d=128, bs=128)
+
+
+def test_small_blocks_and_mha():
+    _check(seq_new=[130, 1, 33], seq_seen=[64, 255, 0], hq=4, hkv=4, d=64, bs=64, seed=1)   # group 1: 128 tokens per atom
+    _check(seq_new=[20, 1], seq_seen=[200, 300], hq=8, hkv=2, d=128, bs=32, seed=2)            # 4 cache blocks per 128-key page
+
+
+def test_split_kv_decode():
+    # decode over long contexts with the KV range of every atom cut into 4 and 7 slices (some slices empty for short sequences)
+    _check(seq_new=[1, 1, 1], seq_seen=[2000, 130, 3], hq=8, hkv=1, d=128, bs=128, n_splits=4, seed=3)
+    _check(seq_new=[1, 40], seq_seen=[900, 500], hq=8, hkv=1, d=128, bs=128, n_splits=7, seed=4)
+
+
+def test_dispatch_uses_flash_kernel_and_falls_back():
+    from deepspeedsyclsupport_b200.inference.v2 import kernels as K
+    from deepspeedsyclsupport_b200.ops import native
+    qkv, kv, ts, tp, bt = _make_batch([5, 1], [10, 140], 8, 2, 128, 128)
+    assert K.paged_flash_supported(qkv, kv, 8, 2, 128)
+    a = K.paged_attention(qkv, kv, ts, tp, bt, 8, 2, 128).float()
+    b = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), 8, 2, 128, 128 ** -0.5).float().cuda()
+    assert (a - b).abs().max().item() < 2e-2
+    # head size 96 is outside the tensor-core kernel: the CUDA-core kernel answers
+    qkv, kv, ts, tp, bt = _make_batch([3, 1], [4, 20], 4, 2, 96, 128)
+    assert not K.paged_flash_supported(qkv, kv, 4, 2, 96)
+    a = K.paged_attention(qkv, kv, ts, tp, bt, 4, 2, 96).float()
+    b = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), 4, 2, 96, 96 ** -0.5).float().cuda()
+    assert (a - b).abs().max().item() < 2e-2
+    assert native.launch_count > 0
