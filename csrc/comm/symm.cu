@@ -407,6 +407,137 @@ __global__ void allreduce_oneshot_kernel(Peers peers, size_t src_off, __nv_bfloa
   }
 }
 
+// ---------------------------------------------------------------- MoE expert parallelism: dispatch push / combine pull
+// Capacity layout of the reference's MoE (moe/sharded_moe.py:477-554): token s routed to expert e lands in slot c of that
+// expert's [C, M] buffer; expert e lives on rank e / n_local.  The receive buffer of a rank is [W src ranks][n_local][C][M]
+// inside its symmetric buffer.  Dispatch = every (token, k) row is STORED straight into the owner's receive buffer at
+// [my rank][e % n_local][slot] (replaces scatter + all-to-all); combine = every token PULLS its k expert-output rows from the
+// owners' buffers and sums them with the gate weights (replaces all-to-all + gather).  One warp per (token, k) / per token.
+__device__ __forceinline__ void st_peer_v4(void* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint8_t* moe_row_ptr(const Peers& peers, size_t buf_off, int rank, int e, int slot, int n_local,
+                                                int capacity, int M) {
+  const int owner = e / n_local, le = e - owner * n_local;
+  const size_t row = (static_cast<size_t>(rank) * n_local + le) * capacity + slot;
+  return static_cast<uint8_t*>(peers.ptr[owner]) + buf_off + row * static_cast<size_t>(M) * 2;
+}
+// x [S][M] bf16; token_expert / token_slot [S][K] (expert < 0 = dropped); row_scale optional [S][K] fp32 (backward of combine:
+// rows are scaled by the gate weight on the way out)
+__global__ void moe_dispatch_push_kernel(Peers peers, size_t buf_off, const __nv_bfloat16* __restrict__ x, const int* __restrict__ token_expert,
+                                         const int* __restrict__ token_slot, const float* __restrict__ row_scale, int S, int K, int M,
+                                         int rank, int n_local, int capacity) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (wid >= S * K) return;
+  const int s = wid / K;
+  const int e = token_expert[wid];
+  if (e < 0) return;
+  uint8_t* dst = moe_row_ptr(peers, buf_off, rank, e, token_slot[wid], n_local, capacity, M);
+  const uint4* src = reinterpret_cast<const uint4*>(x + static_cast<size_t>(s) * M);
+  const float sc = row_scale ? row_scale[wid] : 1.f;
+  for (int v = lane; v < M / 8; v += 32) {
+    uint4 val = src[v];
+    if (row_scale) {
+      __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&val);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float2 f = __bfloat1622float2(h[i]);
+        h[i] = __floats2bfloat162_rn(f.x * sc, f.y * sc);
+      }
+    }
+    st_peer_v4(dst + v * 16, val);
+  }
+}
+// out[s] = sum_k w[s][k] * row(e_k, slot_k) pulled from the owner; weights NULL = plain sum (backward of dispatch).
+// dot_out optional [S][K]: <pulled row, dot_with[s]> (gate-weight gradient in the backward of combine; out may be NULL then)
+__global__ void moe_combine_pull_kernel(Peers peers, size_t buf_off, __nv_bfloat16* __restrict__ out, const int* __restrict__ token_expert,
+                                        const int* __restrict__ token_slot, const float* __restrict__ weights,
+                                        const __nv_bfloat16* __restrict__ dot_with, float* __restrict__ dot_out, int S, int K, int M, int rank,
+                                        int n_local, int capacity) {
+  const int s = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (s >= S) return;
+  for (int v0 = lane; v0 < M / 8 || (dot_out && v0 < ((M / 8 + 31) / 32) * 32); v0 += 32) {
+    const bool in = v0 < M / 8;
+    float acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) acc[i] = 0.f;
+    uint4 dw = make_uint4(0, 0, 0, 0);
+    if (dot_out && in) dw = *reinterpret_cast<const uint4*>(dot_with + static_cast<size_t>(s) * M + v0 * 8);
+    for (int k = 0; k < K; ++k) {
+      const int e = token_expert[s * K + k];
+      float part = 0.f;
+      if (e >= 0 && in) {
+        const uint8_t* src = moe_row_ptr(peers, buf_off, rank, e, token_slot[s * K + k], n_local, capacity, M);
+        const uint4 raw = ld_peer_v4(src + v0 * 16);
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&raw);
+        const __nv_bfloat162* d = reinterpret_cast<const __nv_bfloat162*>(&dw);
+        const float w = weights ? weights[s * K + k] : 1.f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __bfloat1622float2(h[i]);
+          acc[2 * i] = fmaf(w, f.x, acc[2 * i]);
+          acc[2 * i + 1] = fmaf(w, f.y, acc[2 * i + 1]);
+          if (dot_out) {
+            const float2 g = __bfloat1622float2(d[i]);
+            part = fmaf(f.x, g.x, fmaf(f.y, g.y, part));
+          }
+        }
+      }
+      if (dot_out) {
+        part = warp_sum(part);
+        if (lane == 0 && e >= 0) dot_out[s * K + k] += part;  // one warp owns token s: plain accumulate over the v0 passes
+      }
+    }
+    if (out && in) {
+      uint4 o;
+      o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]); o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
+      *reinterpret_cast<uint4*>(out + static_cast<size_t>(s) * M + v0 * 8) = o;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- Ulysses: sequence <-> head exchange fused with its layout change
+// "Source layout"  (sequence-sharded): rows = B x S_local tokens of this rank, every row holds ALL heads of up to three
+//                   segments (q | k | v of a packed QKV projection, or the attention output alone).
+// "Dest layout"    (head-sharded): rows = B x S tokens of the WHOLE sequence (S = P * S_local, rank-major), every row holds
+//                   this rank's heads of each segment, packed.
+// push: local source rows are STORED straight into the owners' dest-layout buffers (the all-to-all before attention, with
+//       its reshapes and the q/k/v merge folded in); pull: local source rows are LOADED from the owners' dest-layout buffers
+//       (the all-to-all after attention).  Each is the other's backward.  One 16-byte vector per thread per step.
+struct HeadSeg {
+  int src_col, dst_col, heads, heads_per_rank;  // columns in elements; heads of the segment in total / per rank
+};
+struct HeadSegs {
+  HeadSeg s[3];
+  int n;
+  int vec_per_row;  // sum over segments of heads * D / 8
+};
+template <bool PUSH>
+__global__ void ulysses_heads_kernel(Peers peers, size_t buf_off, __nv_bfloat16* __restrict__ local, int B, int S_local, int P, int rank,
+                                     int D, int src_ld, int dst_ld, HeadSegs segs) {
+  const long long total = static_cast<long long>(B) * S_local * segs.vec_per_row;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  const int dv = D / 8;
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long t = i / segs.vec_per_row;
+    int v = static_cast<int>(i - t * segs.vec_per_row);
+    int si = 0;
+    while (si + 1 < segs.n && v >= segs.s[si].heads * dv) {
+      v -= segs.s[si].heads * dv;
+      ++si;
+    }
+    const HeadSeg sg = segs.s[si];
+    const int head = v / dv, d8 = v - head * dv;
+    const int owner = head / sg.heads_per_rank, lh = head - owner * sg.heads_per_rank;
+    const int b = static_cast<int>(t / S_local), sl = static_cast<int>(t - static_cast<long long>(b) * S_local);
+    const long long dst_row = static_cast<long long>(b) * S_local * P + static_cast<long long>(rank) * S_local + sl;
+    __nv_bfloat16* lp = local + t * src_ld + sg.src_col + head * D + d8 * 8;
+    uint8_t* rp = static_cast<uint8_t*>(peers.ptr[owner]) + buf_off + (dst_row * dst_ld + sg.dst_col + lh * D + d8 * 8) * 2;
+    if constexpr (PUSH) st_peer_v4(rp, *reinterpret_cast<const uint4*>(lp));
+    else *reinterpret_cast<uint4*>(lp) = ld_peer_v4(rp);
+  }
+}
+
 // ---------------------------------------------------------------- NVLS (NVSwitch multicast) collectives
 // `mc` is the multicast mapping of the SAME symmetric buffer: a multimem.ld_reduce at offset x returns the sum over every
 // rank's bytes at x, added inside the switch (each GPU receives 1x the slice instead of reading W-1 peers); a multimem.st
@@ -731,6 +862,72 @@ DSB_EXPORT int dsb200_p2p_fp8_reduce_scatter(void* const* peer_ptrs, long long q
     set_last_error("p2p_fp8_reduce_scatter: unsupported destination dtype %d", dst_dtype);
     return DSB_ERR_UNSUPPORTED;
   }
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// ---- MoE expert-parallel dispatch / combine over peer memory.  buf_off: byte offset of the [W][n_local][capacity][M] bf16
+// receive buffer inside every rank's symmetric buffer; token_expert / token_slot: [S][K] int32 (expert < 0 = dropped token).
+DSB_EXPORT int dsb200_moe_dispatch_push(void* const* peer_ptrs, long long buf_off, const void* x, const int* token_expert,
+                                        const int* token_slot, const float* row_scale, int S, int K, int M, int rank, int world,
+                                        int n_local, int capacity, cudaStream_t stream) {
+  DSB_REQUIRE(M % 8 == 0 && buf_off % 16 == 0 && S >= 0 && K >= 1, "moe_dispatch_push: model dim must be a multiple of 8");
+  if (S == 0) return DSB_OK;
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  const long long warps = static_cast<long long>(S) * K;
+  moe_dispatch_push_kernel<<<static_cast<unsigned>((warps * 32 + 255) / 256), 256, 0, stream>>>(
+      P, static_cast<size_t>(buf_off), static_cast<const __nv_bfloat16*>(x), token_expert, token_slot, row_scale, S, K, M, rank, n_local, capacity);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// out [S][M] bf16 (may be NULL when only dot_out is wanted); weights [S][K] fp32 or NULL; dot_with [S][M] bf16 + dot_out [S][K]
+// fp32 (zero-initialised by the caller) optional.
+DSB_EXPORT int dsb200_moe_combine_pull(void* const* peer_ptrs, long long buf_off, void* out, const int* token_expert,
+                                       const int* token_slot, const float* weights, const void* dot_with, float* dot_out, int S, int K,
+                                       int M, int rank, int world, int n_local, int capacity, cudaStream_t stream) {
+  DSB_REQUIRE(M % 8 == 0 && buf_off % 16 == 0 && S >= 0 && K >= 1, "moe_combine_pull: model dim must be a multiple of 8");
+  DSB_REQUIRE((dot_with == nullptr) == (dot_out == nullptr), "moe_combine_pull: dot_with and dot_out go together");
+  if (S == 0) return DSB_OK;
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  moe_combine_pull_kernel<<<static_cast<unsigned>((static_cast<long long>(S) * 32 + 255) / 256), 256, 0, stream>>>(
+      P, static_cast<size_t>(buf_off), static_cast<__nv_bfloat16*>(out), token_expert, token_slot, weights,
+      static_cast<const __nv_bfloat16*>(dot_with), dot_out, S, K, M, rank, n_local, capacity);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// Ulysses head <-> sequence exchange over peer memory.  `local`: [B * S_local][src_ld] bf16 (source layout); the dest-layout buffer
+// [B * S_local * world][dst_ld] lives at buf_off of every rank's symmetric buffer.  segs: n_seg x {src_col, dst_col, heads,
+// heads_per_rank} (ints, host).  push = 1: local -> owners' buffers; push = 0: owners' buffers -> local.
+DSB_EXPORT int dsb200_ulysses_heads_exchange(void* const* peer_ptrs, long long buf_off, void* local, int B, int S_local, int rank, int world,
+                                             int D, int src_ld, int dst_ld, const int* segs, int n_seg, int push, int max_ctas,
+                                             cudaStream_t stream) {
+  DSB_REQUIRE(D % 8 == 0 && src_ld % 8 == 0 && dst_ld % 8 == 0 && buf_off % 16 == 0 && n_seg >= 1 && n_seg <= 3,
+              "ulysses_heads_exchange: head size and row strides must be multiples of 8, 1..3 segments");
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  HeadSegs hs;
+  hs.n = n_seg;
+  hs.vec_per_row = 0;
+  for (int i = 0; i < n_seg; ++i) {
+    hs.s[i].src_col = segs[4 * i]; hs.s[i].dst_col = segs[4 * i + 1]; hs.s[i].heads = segs[4 * i + 2]; hs.s[i].heads_per_rank = segs[4 * i + 3];
+    DSB_REQUIRE(hs.s[i].heads == hs.s[i].heads_per_rank * world && hs.s[i].src_col % 8 == 0 && hs.s[i].dst_col % 8 == 0,
+                "ulysses_heads_exchange: segment %d: heads must split evenly over the ranks", i);
+    hs.vec_per_row += hs.s[i].heads * (D / 8);
+  }
+  const long long total = static_cast<long long>(B) * S_local * hs.vec_per_row;
+  if (total == 0) return DSB_OK;
+  const int grid = comm_grid(static_cast<size_t>(total), max_ctas);
+  if (push)
+    ulysses_heads_kernel<true><<<grid, 256, 0, stream>>>(P, static_cast<size_t>(buf_off), static_cast<__nv_bfloat16*>(local), B, S_local, world, rank, D, src_ld, dst_ld, hs);
+  else
+    ulysses_heads_kernel<false><<<grid, 256, 0, stream>>>(P, static_cast<size_t>(buf_off), static_cast<__nv_bfloat16*>(local), B, S_local, world, rank, D, src_ld, dst_ld, hs);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

@@ -177,15 +177,28 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tmA, const CUtenso
     // ------------------------------------------------------------- all-gather copy warps (AG only): peers -> b_local
     if constexpr (AG) {
       const int ct = threadIdx.x - 192;  // 0..63
+      // Copy work = tiles_n x gridDim.x chunks, handed out in consumption order through ONE global claim counter
+      // (flags[tiles_n]): whichever CTAs are resident copy everything, so the kernel makes progress even when other
+      // kernels hold some SMs and part of this grid has not started yet (no CTA waits for a specific other CTA).
+      __shared__ int s_claim;
       const long long row_elems = p.K;
-      for (int nb = 0; nb < p.tiles_n; ++nb) {
+      const int chunks_per_nb = static_cast<int>(gridDim.x);
+      const int total_chunks = p.tiles_n * chunks_per_nb;
+      int* claim = ag->flags + p.tiles_n;
+      while (true) {
+        if (ct == 0) s_claim = atomicAdd(claim, 1);
+        named_bar_sync(2, 64);
+        const int idx = s_claim;
+        named_bar_sync(2, 64);  // everyone has read s_claim before the next claim overwrites it
+        if (idx >= total_chunks) break;
+        const int nb = idx / chunks_per_nb, chunk = idx - nb * chunks_per_nb;
         const long long rows = min(BN2, p.N - nb * BN2);
         const long long chunk_elems = rows * row_elems;
-        const long long chunk_off = static_cast<long long>(nb) * BN2 * row_elems;
+        const long long chunk_off = static_cast<long long>(nb) * BN2 * row_elems;  // offset inside B
         const long long vecs = chunk_elems / 8;
-        const long long per_cta = (vecs + gridDim.x - 1) / gridDim.x;
-        const long long v_lo = per_cta * blockIdx.x;
-        const long long v_hi = min(vecs, v_lo + per_cta);
+        const long long per_chunk = (vecs + chunks_per_nb - 1) / chunks_per_nb;
+        const long long v_lo = per_chunk * chunk;
+        const long long v_hi = min(vecs, v_lo + per_chunk);
         constexpr int UNR = 8;
         for (long long v = v_lo + ct; v < v_hi; v += 64 * UNR) {
           uint4 buf[UNR];
@@ -193,7 +206,7 @@ __device__ __forceinline__ void gemm2_body(const CUtensorMap& tmA, const CUtenso
           for (int u = 0; u < UNR; ++u) {
             const long long vv = v + static_cast<long long>(u) * 64;
             if (vv < v_hi) {
-              const long long e = ag->w_off + chunk_off + vv * 8;
+              const long long e = ag->w_off + chunk_off + vv * 8;  // flat element index in the unit
               const int peer = static_cast<int>(e / ag->shard_numel);
               const long long le = e - static_cast<long long>(peer) * ag->shard_numel;
               const void* src = static_cast<const __nv_bfloat16*>(ag->peer_shard[peer]) + le;

@@ -40,7 +40,7 @@ static int launch_ag2(const void* A, void* b_local, void* C, int M, int N, int K
   ag.b_local = static_cast<__nv_bfloat16*>(b_local);
   ag.flags = flags;
   ag.world = world;
-  DSB_CHECK_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * p.tiles_n, stream));
+  DSB_CHECK_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * (p.tiles_n + 1), stream));  // per-block counters + the claim counter
   int clusters = p.tiles_m * p.tiles_n;
   if (clusters > num_sms() / 2) clusters = num_sms() / 2;
   kern<<<2 * clusters, NUM_THREADS_AG, S::TOTAL, stream>>>(tmA, tmB, tmC, p, ag);
@@ -77,7 +77,7 @@ static int launch_ag(const void* A, void* b_local, void* C, int M, int N, int K,
   ag.b_local = static_cast<__nv_bfloat16*>(b_local);
   ag.flags = flags;
   ag.world = world;
-  DSB_CHECK_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * p.tiles_n, stream));
+  DSB_CHECK_CUDA(cudaMemsetAsync(flags, 0, sizeof(int) * (p.tiles_n + 1), stream));  // per-block counters + the claim counter
   int grid = p.tiles_m * p.tiles_n;
   const int cap = num_sms();
   if (grid > cap) grid = cap;
@@ -93,7 +93,7 @@ static int launch_ag(const void* A, void* b_local, void* C, int M, int N, int K,
 //   b_local     : [N,K] bf16 destination of the gather (kept for backward); also the GEMM's B operand
 //   peer_shards : HOST array of `world` device pointers -- each rank's shard region of the unit (this process's mappings)
 //   w_off       : flat element offset of W[0][0] inside the unit; shard_numel: elements per rank shard
-//   flags       : device scratch, >= ceil(N/256) ints (zeroed by this call)
+//   flags       : device scratch, >= ceil(N/256) + 1 ints (zeroed by this call): per n-block arrival counters + one work-claim counter
 DSB_EXPORT int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int K, int lda, int ldc,
                                    void* const* peer_shards, long long w_off, long long shard_numel, int* flags, int world,
                                    cudaStream_t stream) {

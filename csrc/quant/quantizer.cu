@@ -91,6 +91,63 @@ __global__ void fp8_dequant_reduce_kernel(const uint8_t* __restrict__ q, const f
   for (int k = 0; k < 4; ++k) stf<T>(out, base + k, acc[k] * scale_out);
 }
 
+// ---------------------------------------------------------------- per-row (per-token) fp8 quantisation for the W8A8 linear
+// One warp per row: the row is read once into registers (up to 32 x 32 = 8192 elements... longer rows take a second read),
+// amax by warp shuffle, scale = amax / 448, payload e4m3.  Replaces an abs / amax / div / clamp / cast chain of five eager
+// passes over the activation in front of every fp8 GEMM.
+template <typename T>
+__global__ void fp8_rowwise_quant_kernel(const T* __restrict__ x, uint8_t* __restrict__ q, float* __restrict__ scales, int rows, int cols,
+                                         long long ldx) {
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const T* xr = x + static_cast<size_t>(row) * ldx;
+  uint8_t* qr = q + static_cast<size_t>(row) * cols;
+  constexpr int MAXV = 8;  // vectors of 8 elements cached per lane: rows up to 32 * 8 * 8 = 2048 elements stay in registers
+  const int nvec = cols / 8;
+  float cache[MAXV][8];
+  float amax = 0.f;
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int v = lane + j * 32;
+    if (v < nvec) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        cache[j][k] = ldf<T>(xr, static_cast<size_t>(v) * 8 + k);
+        amax = fmaxf(amax, fabsf(cache[j][k]));
+      }
+    }
+  }
+  for (int v = lane + MAXV * 32; v < nvec; v += 32)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) amax = fmaxf(amax, fabsf(ldf<T>(xr, static_cast<size_t>(v) * 8 + k)));
+  amax = warp_max(amax);
+  const float scale = fmaxf(amax, 1e-12f) / FP8_MAX;
+  const float inv = 1.f / scale;
+  auto pack8 = [&](const float* f) {
+    uint2 o;
+    uint32_t w[2] = {0, 0};
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      __nv_fp8_e4m3 e(fminf(fmaxf(f[k] * inv, -FP8_MAX), FP8_MAX));
+      w[k >> 2] |= static_cast<uint32_t>(e.__x) << (8 * (k & 3));
+    }
+    o.x = w[0]; o.y = w[1];
+    return o;
+  };
+#pragma unroll
+  for (int j = 0; j < MAXV; ++j) {
+    const int v = lane + j * 32;
+    if (v < nvec) *reinterpret_cast<uint2*>(qr + static_cast<size_t>(v) * 8) = pack8(cache[j]);
+  }
+  for (int v = lane + MAXV * 32; v < nvec; v += 32) {
+    float f[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = ldf<T>(xr, static_cast<size_t>(v) * 8 + k);
+    *reinterpret_cast<uint2*>(qr + static_cast<size_t>(v) * 8) = pack8(f);
+  }
+  if (lane == 0) scales[row] = scale;
+}
+
 // ---------------------------------------------------------------- int8 / int4 group quantization (one CTA per group)
 __device__ __forceinline__ float block_reduce(float v, float* red, bool is_max) {
   v = is_max ? warp_max(v) : -warp_max(-v);
@@ -294,6 +351,25 @@ DSB_EXPORT int dsb200_fake_quantize(void* x, long long groups, int group_size, i
   if (groups == 0) return DSB_OK;
   DSB_Q_DISPATCH(dtype, (fake_quant_kernel<T><<<static_cast<unsigned>(groups), 256, 0, stream>>>((T*)x, group_size, bits, symmetric,
                                                                                                  stochastic, (uint64_t)seed)));
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// q[rows][cols] (e4m3) and scales[rows] (fp32) with x ~= q * scale per row; x: [rows][cols] with row stride ldx (elements).
+// dtype: 0 bf16, 1 fp16, 2 fp32.  cols must be a multiple of 8.
+DSB_EXPORT int dsb200_fp8_rowwise_quantize(const void* x, void* q, float* scales, int rows, int cols, long long ldx, int dtype,
+                                           cudaStream_t stream) {
+  DSB_REQUIRE(cols % 8 == 0 && rows >= 0 && ldx >= cols, "fp8_rowwise_quantize: cols must be a multiple of 8");
+  if (rows == 0) return DSB_OK;
+  const unsigned grid = static_cast<unsigned>((static_cast<long long>(rows) * 32 + 255) / 256);
+  uint8_t* qq = static_cast<uint8_t*>(q);
+  if (dtype == 0) quant::fp8_rowwise_quant_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), qq, scales, rows, cols, ldx);
+  else if (dtype == 1) quant::fp8_rowwise_quant_kernel<__half><<<grid, 256, 0, stream>>>(static_cast<const __half*>(x), qq, scales, rows, cols, ldx);
+  else if (dtype == 2) quant::fp8_rowwise_quant_kernel<float><<<grid, 256, 0, stream>>>(static_cast<const float*>(x), qq, scales, rows, cols, ldx);
+  else {
+    set_last_error("fp8_rowwise_quantize: unsupported dtype %d", dtype);
+    return DSB_ERR_UNSUPPORTED;
+  }
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

@@ -10,7 +10,9 @@ class DeepSpeedTPConfig(DeepSpeedConfigModel):
 
 
 class QuantizationConfig(DeepSpeedConfigModel):
-    quantization_mode: str = ""  # "" (16-bit weights) | "wf8af8" (e4m3 weights per output feature x e4m3 activations per token)
+    # "" (16-bit weights) | "wf8af8" (e4m3 weights per output feature x e4m3 activations per token)
+    # | "wf8af8_block" (block-scaled: one fp32 scale per 128 input features on both operands, the ZeRO++ wire format)
+    quantization_mode: str = ""
 
 
 class RaggedInferenceEngineConfig(DeepSpeedConfigModel):

@@ -26,8 +26,11 @@ def instantiate_embed(embed_config: DSEmbeddingsConfig, engine_config: RaggedInf
 
 def instantiate_linear(linear_config: DSLinearConfig, engine_config: RaggedInferenceEngineConfig = None) -> DSLinearBase:
     name = "blas_fp_linear"
-    if _quant_mode(engine_config) == "wf8af8" and DSLinearRegistry.registry["fp8_linear"].supports_config(linear_config):
+    mode = _quant_mode(engine_config)
+    if mode == "wf8af8" and DSLinearRegistry.registry["fp8_linear"].supports_config(linear_config):
         name = "fp8_linear"
+    elif mode == "wf8af8_block" and DSLinearRegistry.registry["fp8_block_linear"].supports_config(linear_config):
+        name = "fp8_block_linear"
     return DSLinearRegistry.instantiate_config(ConfigBundle(name=name, config=linear_config))
 
 

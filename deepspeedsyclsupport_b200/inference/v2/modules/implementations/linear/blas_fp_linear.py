@@ -2,13 +2,15 @@
 
 `blas_fp_linear`: 16-bit weights on the tcgen05 GEMM, bias + activation (plain or gated) in one pass over the output.
 `fp8_linear`: e4m3 weights with one scale per output feature, activations quantised per token, product on the fp8 tensor-core
-GEMM (csrc/gemm/gemm_fp8.cu) -- chosen by the heuristics when the engine's quantization_mode is "wf8af8"."""
+GEMM (csrc/gemm/gemm_fp8.cu) -- chosen by the heuristics when the engine's quantization_mode is "wf8af8".
+`fp8_block_linear`: block-scaled e4m3 weights and activations (one fp32 scale per 128 input features of every row, the ZeRO++
+wire format) on csrc/gemm/gemm_fp8_block.cu -- quantization_mode "wf8af8_block"."""
 from typing import Any, Dict, Optional
 
 import torch
 
 from ......ops import fused_ops as FO
-from ......ops.gemm import gemm, linear_fp8, quantize_fp8_rowwise
+from ......ops.gemm import gemm, linear_fp8, linear_fp8_block, quantize_fp8_rowwise
 from ....inference_parameter import InferenceParameter
 from ....inference_utils import ActivationType, DtypeEnum, activation_name, is_gated
 from ...configs import DSLinearConfig
@@ -90,3 +92,26 @@ class FP8Linear(_LinearCommon):
 
     def forward(self, hidden_states: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
         return self._epilogue(linear_fp8(hidden_states, w, w.scales), b)
+
+
+@DSLinearRegistry.register_module
+class FP8BlockLinear(_LinearCommon):
+
+    @staticmethod
+    def name() -> str:
+        return "fp8_block_linear"
+
+    @staticmethod
+    def supports_config(config: DSLinearConfig) -> bool:
+        return _supported(config) and config.in_channels % 128 == 0
+
+    def transform_param(self, param: torch.Tensor) -> InferenceParameter:
+        if param.dim() != 2:
+            return InferenceParameter.initialize(param.to(DtypeEnum(self._config.input_dtype).value).contiguous())
+        from ......ops.quantizer import quantize_fp8_block
+        w = param.to(DtypeEnum(self._config.input_dtype).value).contiguous()
+        q, scale = quantize_fp8_block(w)
+        return InferenceParameter.initialize(q.view(w.shape), scales=scale.view(w.shape[0], w.shape[1] // 128))
+
+    def forward(self, hidden_states: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self._epilogue(linear_fp8_block(hidden_states, w, w.scales), b)

@@ -36,6 +36,10 @@ class LlamaConfig:
     checkpoint_policy: str = "auto"
     save_attention_in_checkpoint: bool = True  # legacy switch: False forces checkpoint_policy = "full"
     initializer_range: float = 0.02
+    # DeepSpeed-Ulysses: every rank of the group sees S / P consecutive tokens of each sequence (LlamaForCausalLM.set_sequence_parallel)
+    sequence_parallel_group: object = None
+    sequence_parallel_size: int = 1
+    sequence_parallel_rank: int = 0
 
     @property
     def head_dim(self):
@@ -93,7 +97,17 @@ class LlamaDecoderLayer(nn.Module):
         else:
             hn, residual = self.input_layernorm(x, residual)
         qkv = linear_rope(hn, self.qkv_proj, self.inv_freq, S, self.hq + self.hkv, self.d, positions, tag=RC.QKV)
-        attn = attention(qkv, B, S, self.hq, self.hkv, self.d, causal=True)
+        sp = self.cfg.sequence_parallel_group
+        if sp is not None and self.cfg.sequence_parallel_size > 1:
+            # DeepSpeed-Ulysses: S is this rank's slice of the sequence; re-shard to (whole sequence, this rank's heads) around
+            # the local attention (sequence/fused.py: one-sided peer kernels that also do the layout change)
+            from ..sequence.fused import attn_to_sequence, qkv_to_heads
+            P = self.cfg.sequence_parallel_size
+            qkv_h = qkv_to_heads(qkv.view(B * S, -1), B, S, self.hq, self.hkv, self.d, sp)
+            attn_h = attention(qkv_h, B, S * P, self.hq // P, self.hkv // P, self.d, causal=True)
+            attn = attn_to_sequence(attn_h.view(B * S * P, -1), B, S, self.hq, self.d, sp)
+        else:
+            attn = attention(qkv, B, S, self.hq, self.hkv, self.d, causal=True)
         attn_out = linear(attn.view(B, S, -1), self.o_proj, tag=RC.O_PROJ)
         hn, residual = self.post_attention_layernorm(attn_out, residual)
         act = FO.gated_act(linear(hn, self.gate_up_proj, tag=RC.GATE_UP), "silu")
@@ -131,6 +145,10 @@ class LlamaModel(nn.Module):
 
     def forward(self, input_ids, positions=None):
         x = self.embed_tokens(input_ids)
+        if positions is None and self.cfg.sequence_parallel_size > 1:
+            # this rank holds tokens [rank * S_local, (rank + 1) * S_local) of every sequence: RoPE needs their true positions
+            B, S_local = input_ids.shape
+            positions = (self.cfg.sequence_parallel_rank * S_local + torch.arange(S_local, device=input_ids.device)).repeat(B)
         residual = None
         for layer in self.layers:
             policy = self._checkpoint_policy(x) if (self.cfg.activation_checkpointing and self.training) else "none"
@@ -164,6 +182,18 @@ class LlamaForCausalLM(nn.Module):
         else:
             self.lm_head = nn.Parameter(torch.empty(cfg.vocab_size, cfg.hidden_size))
             nn.init.normal_(self.lm_head, mean=0.0, std=cfg.initializer_range)
+
+    def set_sequence_parallel(self, group):
+        """Turn on DeepSpeed-Ulysses over `group` (None = off): inputs are then the rank's S / P slice of every sequence, heads
+        must divide by the group size, and the loss is the mean over the local tokens (average it over the group)."""
+        from .. import comm as dist
+        cfg = self.cfg
+        cfg.sequence_parallel_group = group
+        cfg.sequence_parallel_size = dist.get_world_size(group) if group is not None else 1
+        cfg.sequence_parallel_rank = dist.get_rank(group) if group is not None else 0
+        P = cfg.sequence_parallel_size
+        assert cfg.num_attention_heads % P == 0 and cfg.num_key_value_heads % P == 0, "heads must split over the sequence-parallel group"
+        return self
 
     def head_weight(self):
         return self.model.embed_tokens.weight if self.lm_head is None else self.lm_head

@@ -91,7 +91,7 @@ def top1gating(logits, capacity_factor, min_capacity, used_token=None, noisy_gat
     mask1 = F.one_hot(indices1_s, num_classes=num_experts)
     if used_token is not None:
         mask1 = torch.einsum("s,se->se", used_token, mask1)
-    exp_counts = torch.sum(mask1, dim=0).detach().to("cpu")
+    exp_counts = torch.sum(mask1, dim=0).detach()  # stays on the device: no host synchronisation in the gate (call .cpu() to log it)
     if not drop_tokens:
         new_capacity = torch.max(exp_counts).to(logits.device)
         if dist.is_initialized():
@@ -136,7 +136,7 @@ def top2gating(logits, capacity_factor, min_capacity, drop_tokens=True):
     mask2 = F.one_hot(indices2_s, num_classes=num_experts)
     locations1 = _slot_positions(mask1)
     locations2 = _slot_positions(mask2) + torch.sum(mask1, dim=0, keepdim=True)
-    exp_counts = torch.sum(mask1, dim=0).detach().to("cpu")
+    exp_counts = torch.sum(mask1, dim=0).detach()
     me = torch.mean(gates, dim=0)
     ce = torch.mean(mask1.float(), dim=0)
     l_aux = torch.mean(me * ce) * num_experts * num_experts
@@ -144,7 +144,7 @@ def top2gating(logits, capacity_factor, min_capacity, drop_tokens=True):
         mask1 = mask1 * torch.lt(locations1, capacity)
         mask2 = mask2 * torch.lt(locations2, capacity)
     else:
-        new_capacity = torch.max(exp_counts + torch.sum(mask2, dim=0).detach().cpu()).to(logits.device)
+        new_capacity = torch.max(exp_counts + torch.sum(mask2, dim=0).detach()).to(logits.device)
         if dist.is_initialized():
             dist.all_reduce(new_capacity, op=dist.ReduceOp.MAX, group=dist.get_world_group())
         capacity = int(new_capacity.item())
@@ -218,31 +218,27 @@ class TopKGate(Module):
 
 
 def dispatch_tokens(x, token_expert, token_slot, num_experts, capacity):
-    """x [S, M] -> [E, C, M]; differentiable (index_put)."""
+    """x [S, M] -> [E, C, M]; differentiable.  Dropped tokens (expert < 0) go to a dummy row that is cut off again, so no
+    data-dependent shape (and no host synchronisation) is involved."""
     S, M = x.shape
     K = token_expert.shape[1]
-    out = x.new_zeros(num_experts * capacity, M)
-    for k in range(K):
-        valid = token_expert[:, k] >= 0
-        idx = torch.nonzero(valid).squeeze(1)
-        dst = token_expert[idx, k] * capacity + token_slot[idx, k]
-        out = out.index_add(0, dst, x.index_select(0, idx))
-    return out.view(num_experts, capacity, M)
+    rows = num_experts * capacity
+    dst = torch.where(token_expert >= 0, token_expert * capacity + token_slot, torch.full_like(token_expert, rows))
+    src = x if K == 1 else x.repeat_interleave(K, dim=0)
+    out = x.new_zeros(rows + 1, M).index_add(0, dst.reshape(-1), src)
+    return out[:rows].view(num_experts, capacity, M)
 
 
 def combine_tokens(expert_out, token_expert, token_slot, token_weight, num_tokens):
-    """expert_out [E, C, M] -> [S, M] = sum_k w_k * expert_out[e_k, slot_k]."""
+    """expert_out [E, C, M] -> [S, M] = sum_k w_k * expert_out[e_k, slot_k] (dropped tokens read a zero row)."""
     E, C, M = expert_out.shape
-    flat = expert_out.reshape(E * C, M)
-    out = flat.new_zeros(num_tokens, M)
     K = token_expert.shape[1]
-    for k in range(K):
-        valid = token_expert[:, k] >= 0
-        idx = torch.nonzero(valid).squeeze(1)
-        src = token_expert[idx, k] * C + token_slot[idx, k]
-        rows = flat.index_select(0, src) * token_weight[idx, k].to(flat.dtype)[:, None]
-        out = out.index_add(0, idx, rows)
-    return out
+    flat = torch.cat([expert_out.reshape(E * C, M), expert_out.new_zeros(1, M)])
+    valid = token_expert >= 0
+    src = torch.where(valid, token_expert * C + token_slot, torch.full_like(token_expert, E * C))
+    rows = flat.index_select(0, src.reshape(-1)).view(num_tokens, K, M)
+    w = (token_weight * valid.to(token_weight.dtype)).to(flat.dtype)
+    return (rows * w[:, :, None]).sum(dim=1)
 
 
 class MOELayer(Module):
@@ -266,6 +262,20 @@ class MOELayer(Module):
     def _set_ep_group(self, ep_group):
         self.ep_group = ep_group
 
+    def _forward_peer(self, original, tokens, token_expert, token_slot, token_weight, capacity):
+        """Expert parallelism inside one NVSwitch domain: dispatch = one push kernel into the owners' receive buffers,
+        combine = one weighted pull kernel (moe/peer_dispatch.py, csrc/comm/symm.cu); no all-to-all, no scatter tensor."""
+        from .peer_dispatch import PeerCombine, PeerDispatch, PeerMoEBuffers
+        d_model = tokens.shape[-1]
+        bufs = PeerMoEBuffers.get(self.ep_group, self.num_local_experts, int(capacity), d_model)
+        received = PeerDispatch.apply(tokens, token_expert, token_slot, bufs)             # [ep, n_local, C_buf, M]
+        expert_output = self.experts(received)
+        out = PeerCombine.apply(expert_output.contiguous(), token_expert, token_slot, token_weight, tokens.shape[0], bufs)
+        if self.wall_clock_breakdown:
+            self.timers(MOE_TIMER).stop()
+            self.time_moe = self.timers(MOE_TIMER).elapsed(reset=False)
+        return out.reshape(original.shape)
+
     def forward(self, *input, **kwargs):
         if self.wall_clock_breakdown:
             self.timers(MOE_TIMER).start()
@@ -274,6 +284,10 @@ class MOELayer(Module):
         self.l_aux, token_expert, token_slot, token_weight, capacity, self.exp_counts = self.gate(
             reshaped_input, input[1] if len(input) > 1 else None)
         E = self.ep_size * self.num_local_experts
+        from . import peer_dispatch
+        if peer_dispatch.usable(reshaped_input, self.ep_size, self.ep_group) and not (
+                groups._get_expert_model_parallel_world_size() == 1 and groups._get_model_parallel_world_size() > 1):
+            return self._forward_peer(input[0], reshaped_input, token_expert, token_slot, token_weight, capacity)
         dispatched_input = dispatch_tokens(reshaped_input, token_expert, token_slot, E, capacity)
         if self.wall_clock_breakdown:
             self.timers(FIRST_ALLTOALL_TIMER).start()

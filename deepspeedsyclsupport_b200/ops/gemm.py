@@ -56,10 +56,21 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
 
 
 FP8_MAX = 448.0  # largest finite e4m3 value
+_ROWQ_DT = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
+native.register_sigs({"dsb200_fp8_rowwise_quantize": "ppp ii l i p", "dsb200_gemm_fp8_block": "ppppp iii iii i p"})
 
 
 def quantize_fp8_rowwise(x):
-    """-> (e4m3 tensor of x's shape, fp32 scale per row): x ~= q * scale[:, None]."""
+    """-> (e4m3 tensor of x's shape, fp32 scale per row): x ~= q * scale[:, None].  On the GPU: one kernel, one pass
+    (csrc/quant/quantizer.cu fp8_rowwise_quant_kernel); the eager formula below is the CPU path and the oracle."""
+    if x.is_cuda and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] % 8 == 0 and x.dtype in _ROWQ_DT and x.data_ptr() % 16 == 0:
+        rows, cols = x.shape
+        q = torch.empty(rows, cols, dtype=torch.float8_e4m3fn, device=x.device)
+        scale = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rc = native.lib().dsb200_fp8_rowwise_quantize(native.ptr(x), native.ptr(q), native.ptr(scale), rows, cols, x.stride(0), _ROWQ_DT[x.dtype],
+                                                      native.stream_ptr())
+        native.check(rc)
+        return q, scale
     xf = x.float()
     amax = xf.abs().amax(dim=-1).clamp_min(1e-12)
     scale = amax / FP8_MAX
@@ -92,6 +103,44 @@ def gemm_fp8(a_q, b_q, a_scale=None, b_scale=None, out=None, max_ctas=0):
     if _prof._ACTIVE:
         _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_fp8")
     return out
+
+
+def gemm_fp8_block(a_q, b_q, a_scale, b_scale, out=None, max_ctas=0):
+    """Block-scaled fp8 GEMM (csrc/gemm/gemm_fp8_block.cu): C[M,N] (bf16) = sum over 128-wide K blocks of
+    a_scale[m, kb] * b_scale[n, kb] * (A_kb B_kb^T).  a_q [M,K], b_q [N,K]: float8_e4m3fn or uint8 payloads, K % 128 == 0;
+    scales fp32 [M, K/128] / [N, K/128] -- the layout `ops.quantizer.quantize_fp8_block` (the ZeRO++ wire format) produces
+    for row-major operands, so a quantised weight shard is consumed as it arrived."""
+    M, K = a_q.shape
+    N = b_q.shape[0]
+    assert b_q.shape[1] == K and K % 128 == 0 and a_q.stride(1) == 1 and b_q.stride(1) == 1
+    a_scale, b_scale = a_scale.reshape(M, K // 128), b_scale.reshape(N, K // 128)
+    if not a_q.is_cuda:
+        af = a_q.view(torch.float8_e4m3fn).float().view(M, K // 128, 128) * a_scale[:, :, None]
+        bf = b_q.view(torch.float8_e4m3fn).float().view(N, K // 128, 128) * b_scale[:, :, None]
+        return (af.view(M, K) @ bf.view(N, K).t()).to(torch.bfloat16)
+    if out is None:
+        ld = (N + 7) // 8 * 8
+        out = torch.empty(M, ld, dtype=torch.bfloat16, device=a_q.device)[:, :N]
+    rc = native.lib().dsb200_gemm_fp8_block(native.ptr(a_q), native.ptr(b_q), native.ptr(out), native.ptr(a_scale.contiguous()),
+                                            native.ptr(b_scale.contiguous()), M, N, K, a_q.stride(0), b_q.stride(0), out.stride(0), int(max_ctas),
+                                            native.stream_ptr())
+    native.check(rc)
+    if _prof._ACTIVE:
+        _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_fp8_block")
+    return out
+
+
+def linear_fp8_block(x, w_q, w_scale, bias=None):
+    """x @ W^T with W held as a block-scaled fp8 payload (one fp32 scale per 128 input features of every output row -- e.g. a
+    ZeRO++ qwZ shard, or a checkpoint quantised once at load): activations are quantised to the same format in one kernel and
+    the tensor cores multiply fp8 x fp8; the weight is never expanded to 16 bits."""
+    from .quantizer import quantize_fp8_block
+    x2 = x.reshape(-1, x.shape[-1]).contiguous()
+    xq, xs = quantize_fp8_block(x2)
+    y = gemm_fp8_block(xq.view(x2.shape), w_q, xs, w_scale).view(*x.shape[:-1], w_q.shape[0])
+    if y.dtype != x.dtype:
+        y = y.to(x.dtype)
+    return y if bias is None else y + bias
 
 
 def linear_fp8(x, w_q, w_scale, bias=None):

@@ -21,7 +21,7 @@ native.register_sigs({
 
 def ag_gemm(x, w_local, out, peer_shard_ptrs, w_off, shard_numel, flags, N, K):
     """x: [M,K] bf16; w_local: [N,K] bf16 buffer that receives the gathered weight; peer_shard_ptrs: list of device
-    pointers to every rank's shard region (own included); flags: int32 scratch with >= ceil(N/256) entries."""
+    pointers to every rank's shard region (own included); flags: int32 scratch with >= ceil(N/256) + 1 entries."""
     M = x.shape[0]
     world = len(peer_shard_ptrs)
     arr = (ctypes.c_void_p * world)(*peer_shard_ptrs)

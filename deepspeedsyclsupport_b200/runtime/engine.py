@@ -1111,8 +1111,12 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
                 with self.optimizer.gathered_unit(u):
                     for p in u.params:
                         name = self.param_names.get(p)
-                        if name in module_state_dict:
-                            p.data.copy_(module_state_dict[name].to(p.device, p.dtype))
+                        src = module_state_dict.get(name) if name is not None else None
+                        if src is None or src.numel() == 0:
+                            continue  # ZeRO-3 model-states files hold empty placeholders for partitioned parameters
+                        if src.numel() != p.data.numel():
+                            raise RuntimeError(f"checkpoint tensor '{name}' has {src.numel()} elements, the parameter has {p.data.numel()}")
+                        p.data.copy_(src.to(p.device, p.dtype).view_as(p.data))
                     self.optimizer._write_back_unit(u)
             # buffers
             for n, b in self.module.named_buffers():
@@ -1375,6 +1379,12 @@ class DeepSpeedEngine(EngineCompatMixin, Module):
             load_moe_state_dict(self, load_dir, tag, checkpoint)
         z3 = self.zero_optimization_partition_weights() and self.optimizer is not None and self.optimizer.shard_world > 1
         if z3 and "ds_lp_shard" in checkpoint:
+            saved_world = checkpoint.get("dp_world_size")
+            if checkpoint["ds_lp_shard"].numel() != self.optimizer.lp_shard.numel():
+                raise RuntimeError(
+                    f"ZeRO-3 checkpoint was written with data-parallel world size {saved_world} (shard of {checkpoint['ds_lp_shard'].numel()} "
+                    f"elements); this job has world size {self.optimizer.shard_world} (shard of {self.optimizer.lp_shard.numel()}).  Convert it with "
+                    "checkpoint/ds_to_universal.py (loads at any world size) or utils/zero_to_fp32.py.")
             self.optimizer.lp_shard.copy_(checkpoint["ds_lp_shard"].to(self.optimizer.lp_shard.device))
             self.optimizer._refresh_master(0, self.optimizer.total_shard)
             self.optimizer._post_load_sync()

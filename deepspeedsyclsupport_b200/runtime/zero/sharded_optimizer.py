@@ -185,6 +185,8 @@ class ZeroShardedOptimizer:
         self.comm_dtype = communication_data_type or dtype
         self.ag_stream = torch.cuda.Stream() if self.cuda else None
         self.rs_stream = torch.cuda.Stream() if self.cuda else None
+        self.offload_stream = torch.cuda.Stream() if self.cuda else None
+        self._d2h_done = []
 
         # ---- parameter groups -> units
         self.param_groups = self.optimizer.param_groups if self.optimizer is not None else []
@@ -508,6 +510,7 @@ class ZeroShardedOptimizer:
                max_ctas=self._p2p_comm_ctas)
         u.full_grad = None
         u.reduced = True
+        self._offload_grad_async(u, stream)
 
     def _p2p_reduce_unit_qgz(self, u, dst, fuse_norm):
         """qgZ on one NVSwitch hop: quantise this rank's whole unit gradient to block-scaled fp8 inside its symmetric slot,
@@ -691,6 +694,8 @@ class ZeroShardedOptimizer:
         u.ready = 0
         if self.shard_world == 1 and self.replica_world == 1:
             u.reduced = True
+            if self.cuda and self._grad_is_shard:
+                self._offload_grad_async(u, torch.cuda.current_stream())
         elif self.stage >= 2 and self.shard_world > 1:
             self._reduce_unit(u)
         # stage 0/1: reduction happens once at the accumulation boundary (reduce_gradients)
@@ -739,6 +744,8 @@ class ZeroShardedOptimizer:
         if self.grad_full_persistent is None and self.shard_world > 1:
             u.full_grad = None
         u.reduced = True
+        if self.cuda:
+            self._offload_grad_async(u, stream if stream is not None else torch.cuda.current_stream())
 
     def reduce_gradients(self, pipeline_parallel=False):
         """Called by the engine after backward at an accumulation boundary (stage 0/1) or every micro-step (stage >= 2)
@@ -1084,6 +1091,7 @@ class ZeroShardedOptimizer:
             self.loss_scaler.backward(loss.float(), retain_graph=retain_graph)
 
     def zero_grad(self, set_to_none=True):
+        self._d2h_done = []  # early gradient copies to the host belong to the step that just ended (or was skipped)
         for u in self.units:
             for p in u.params:
                 p.grad = None
@@ -1107,7 +1115,12 @@ class ZeroShardedOptimizer:
     def _check_overflow(self):
         if self.dtype != torch.float16:
             return False
-        bad = (~torch.isfinite(self.grad_shard.float().sum())).to(torch.float32).reshape(1)
+        if self.grad_shard.is_cuda:
+            from ...ops.fused_ops import sumsq
+            probe = sumsq(self.grad_shard)  # one fused pass; an inf / nan anywhere makes the sum of squares non-finite
+        else:
+            probe = self.grad_shard.float().sum().reshape(1)
+        bad = (~torch.isfinite(probe)).to(torch.float32).reshape(1)
         if dist.is_initialized():
             if self.shard_world > 1:
                 dist.all_reduce(bad, op=dist.ReduceOp.MAX, group=self.shard_group)
@@ -1246,11 +1259,13 @@ class ZeroShardedOptimizer:
             self._ensure_state(region, kind)
             on_host = region.device.type == "cpu" and self.cuda
             if on_host:
-                if region.host_grad is None:
-                    region.host_grad = torch.empty(region.hi - region.lo, dtype=self.grad_shard.dtype).pin_memory()
-                    region.host_lp = torch.empty(region.hi - region.lo, dtype=self.dtype).pin_memory()
-                region.host_grad.copy_(self.grad_shard[region.lo:region.hi], non_blocking=True)
-                inv_host = float(self._inv_scale.item())  # also synchronises the D2H copy above
+                self._ensure_host_staging(region)
+                # most of the gradient shard already left for the host during backward (side stream, _offload_grad_async);
+                # only what was not covered then -- units without gradients, accumulation boundaries -- is copied now
+                torch.cuda.current_stream().wait_stream(self.offload_stream)
+                for a, b in self._uncopied_ranges(region.lo, region.hi):
+                    region.host_grad[a - region.lo:b - region.lo].copy_(self.grad_shard[a:b], non_blocking=True)
+                inv_host = float(self._inv_scale.item())  # also synchronises the D2H copies
                 grads, lp_all, inv_dev, gs = region.host_grad, region.host_lp, None, inv_host
             else:
                 grads = self.grad_shard[region.lo:region.hi]
@@ -1277,6 +1292,48 @@ class ZeroShardedOptimizer:
                 self.lp_shard[region.lo:region.hi].copy_(region.host_lp, non_blocking=True)
             elif lp_all.data_ptr() != self.lp_shard[region.lo:region.hi].data_ptr() and self.dtype != torch.float32:
                 self.lp_shard[region.lo:region.hi].copy_(lp_all)
+
+    # ---- ZeRO-Offload: gradients of host-resident optimizer regions leave the device on a side stream during backward
+    def _ensure_host_staging(self, region):
+        if region.host_grad is None:
+            region.host_grad = torch.empty(region.hi - region.lo, dtype=self.grad_shard.dtype).pin_memory()
+            region.host_lp = torch.empty(region.hi - region.lo, dtype=self.dtype).pin_memory()
+
+    def _offload_grad_async(self, u, producer_stream):
+        """Called when unit `u`'s slice of the gradient shard is final for this step (after its reduction on
+        `producer_stream`): start the device -> pinned-host copy now, under the rest of backward, instead of at step()
+        (reference: stage_1_and_2.py:1149-1242 overlaps its gradient offload the same way)."""
+        if not self.cuda or not getattr(self, "offload_optimizer", False) or self.micro_step_id != self.gas - 1:
+            return
+        lo, hi = u.shard_off, u.shard_off + u.shard_numel
+        stream = self.offload_stream
+        started = False
+        for region in self.regions:
+            if region.device.type != "cpu":
+                continue
+            a, b = max(lo, region.lo), min(hi, region.hi)
+            if a >= b:
+                continue
+            self._ensure_host_staging(region)
+            if not started:
+                stream.wait_stream(producer_stream)
+                started = True
+            with torch.cuda.stream(stream):
+                region.host_grad[a - region.lo:b - region.lo].copy_(self.grad_shard[a:b], non_blocking=True)
+            self._d2h_done.append((a, b))
+
+    def _uncopied_ranges(self, lo, hi):
+        """[lo, hi) minus everything _offload_grad_async already copied this step; clears the record."""
+        done = sorted(r for r in self._d2h_done if r[1] > lo and r[0] < hi)
+        self._d2h_done = [r for r in self._d2h_done if not (r[1] > lo and r[0] < hi)]
+        out, cur = [], lo
+        for a, b in done:
+            if a > cur:
+                out.append((cur, a))
+            cur = max(cur, b)
+        if cur < hi:
+            out.append((cur, hi))
+        return out
 
     def _nvme_region_step(self, kind, region, grads, lp_all, inv_dev, gs):
         """Sub-group by sub-group update of a file-backed region with double-buffered reads / writes."""

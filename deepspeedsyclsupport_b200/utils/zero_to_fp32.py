@@ -63,6 +63,11 @@ def _get_fp32_state_dict_from_zero_checkpoint(ds_checkpoint_dir):
                          "Possibly due to an overwrite of an old checkpoint, or a checkpoint didn't get saved by one or more processes.")
     print(f"Detected checkpoint of type zero stage {zero_stage}, world_size: {world}")
     state_dict = OrderedDict()
+    if "ds_unit_layout" not in first:
+        # written by the reference implementation: per-param-group flat partitions described by `param_shapes`
+        state_dict = _from_reference_layout(ds_checkpoint_dir, per_rank, zero_stage, world)
+        print(f"Reconstructed fp32 state dict with {len(state_dict)} params {sum(v.numel() for v in state_dict.values())} elements")
+        return state_dict
     n_sub = len(_merge_optimizer_sd(per_rank[0]))
     for sub in range(n_sub):
         sds = [_merge_optimizer_sd(r)[sub] for r in per_rank]
@@ -88,6 +93,50 @@ def _get_fp32_state_dict_from_zero_checkpoint(ds_checkpoint_dir):
         pass
     print(f"Reconstructed fp32 state dict with {len(state_dict)} params {sum(v.numel() for v in state_dict.values())} elements")
     return state_dict
+
+
+def _from_reference_layout(ds_checkpoint_dir, per_rank, zero_stage, world):
+    """Checkpoints of the reference DeepSpeed (no `ds_unit_layout`): the model-states file lists, per optimizer param group, the
+    parameter names and shapes in flattening order (`param_shapes`).
+      stage 1/2  every rank holds one contiguous slice of each group's flat fp32 buffer (the buffer is padded at its end so it
+                 divides evenly): concatenate the slices, then cut the parameters off one after the other;
+      stage 3    every parameter is partitioned by itself: each rank's flat buffer holds, parameter after parameter,
+                 ceil(numel / world) elements of it (the last rank's piece is padded)."""
+    ms = _load(get_model_state_file(ds_checkpoint_dir, zero_stage))
+    param_shapes = ms["param_shapes"]
+    if isinstance(param_shapes, dict):
+        param_shapes = [param_shapes]
+    key = "fp32_flat_groups" if zero_stage == 3 else "single_partition_of_fp32_groups"
+    groups_per_rank = [[t.float().reshape(-1) for t in r[key]] for r in per_rank]
+    out = OrderedDict()
+    if zero_stage == 3:
+        # the reference concatenates all groups of a rank before walking the parameters
+        flat_per_rank = [torch.cat(g) for g in groups_per_rank]
+        offset = 0
+        for shapes in param_shapes:
+            for name, shape in shapes.items():
+                numel = int(math.prod(shape)) if len(shape) else 1
+                piece = math.ceil(numel / world)
+                full = torch.cat([flat_per_rank[r][offset:offset + piece] for r in range(world)])
+                out[name] = full[:numel].view(*shape).clone()
+                offset += piece
+    else:
+        for g, shapes in enumerate(param_shapes):
+            full = torch.cat([groups_per_rank[r][g] for r in range(world)])
+            offset = 0
+            for name, shape in shapes.items():
+                numel = int(math.prod(shape)) if len(shape) else 1
+                out[name] = full[offset:offset + numel].view(*shape).clone()
+                offset += numel
+    for name, value in (ms.get("frozen_param_fragments") or {}).items():
+        out.setdefault(name, value.float() if value.is_floating_point() else value)
+    for bn in ms.get("buffer_names", []) or []:
+        if bn in ms.get("module", {}):
+            out[bn] = ms["module"][bn]
+    for dst, src in (ms.get("shared_params") or {}).items():
+        if src in out:
+            out[dst] = out[src]
+    return out
 
 
 def get_fp32_state_dict_from_zero_checkpoint(checkpoint_dir, tag=None, exclude_frozen_parameters=False):

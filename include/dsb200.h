@@ -174,6 +174,22 @@ int dsb200_nvls_allgather(void* mc_base, long long dst_off, const void* src, lon
 int dsb200_p2p_fp8_reduce_scatter(void* const* peer_ptrs, long long q_off, long long s_off, void* dst, int dst_dtype,
                                   long long n, int rank, int world, float scale, int accumulate, float* sumsq,
                                   int max_ctas, dsb200_stream_t stream);
+/* ---- MoE expert-parallel dispatch / combine over peer memory.  buf_off: byte offset of the [W][n_local][capacity][M] bf16
+ * receive buffer inside every rank's symmetric buffer; token_expert / token_slot: [S][K] int32 (expert < 0 = dropped token). */
+int dsb200_moe_dispatch_push(void* const* peer_ptrs, long long buf_off, const void* x, const int* token_expert,
+                             const int* token_slot, const float* row_scale, int S, int K, int M, int rank, int world,
+                             int n_local, int capacity, dsb200_stream_t stream);
+/* out [S][M] bf16 (may be NULL when only dot_out is wanted); weights [S][K] fp32 or NULL; dot_with [S][M] bf16 + dot_out [S][K]
+ * fp32 (zero-initialised by the caller) optional. */
+int dsb200_moe_combine_pull(void* const* peer_ptrs, long long buf_off, void* out, const int* token_expert,
+                            const int* token_slot, const float* weights, const void* dot_with, float* dot_out, int S,
+                            int K, int M, int rank, int world, int n_local, int capacity, dsb200_stream_t stream);
+/* Ulysses head <-> sequence exchange over peer memory.  `local`: [B * S_local][src_ld] bf16 (source layout); the dest-layout buffer
+ * [B * S_local * world][dst_ld] lives at buf_off of every rank's symmetric buffer.  segs: n_seg x {src_col, dst_col, heads,
+ * heads_per_rank} (ints, host).  push = 1: local -> owners' buffers; push = 0: owners' buffers -> local. */
+int dsb200_ulysses_heads_exchange(void* const* peer_ptrs, long long buf_off, void* local, int B, int S_local, int rank,
+                                  int world, int D, int src_ld, int dst_ld, const int* segs, int n_seg, int push,
+                                  int max_ctas, dsb200_stream_t stream);
 
 /* ---- csrc/elementwise/elementwise.cu */
 /* out[0] += sum(x[i]^2) over n elements (dtype 0 bf16 / 1 fp16 / 2 fp32).  x must be 16-byte aligned. */
@@ -184,7 +200,7 @@ int dsb200_sumsq(const void* x, long long n, int dtype, float* out, dsb200_strea
  *   b_local     : [N,K] bf16 destination of the gather (kept for backward); also the GEMM's B operand
  *   peer_shards : HOST array of `world` device pointers -- each rank's shard region of the unit (this process's mappings)
  *   w_off       : flat element offset of W[0][0] inside the unit; shard_numel: elements per rank shard
- *   flags       : device scratch, >= ceil(N/256) ints (zeroed by this call) */
+ *   flags       : device scratch, >= ceil(N/256) + 1 ints (zeroed by this call): per n-block arrival counters + one work-claim counter */
 int dsb200_gemm_ag_bf16(const void* A, void* b_local, void* C, int M, int N, int K, int lda, int ldc,
                         void* const* peer_shards, long long w_off, long long shard_numel, int* flags, int world,
                         dsb200_stream_t stream);
@@ -206,6 +222,12 @@ int dsb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_ptrs, lo
  * sa [M] / sb [N] fp32 scales, either may be null (= 1).  lda / ldb in elements (= bytes), multiples of 16; ldc multiple of 8. */
 int dsb200_gemm_fp8(const void* A, const void* B, void* C, const float* sa, const float* sb, int M, int N, int K, int lda,
                     int ldb, int ldc, int max_ctas, dsb200_stream_t stream);
+
+/* ---- csrc/gemm/gemm_fp8_block.cu */
+/* C[M,N] (bf16) = sum over 128-wide K blocks of sa[m][kb] * sb[n][kb] * (A_kb * B_kb^T); A [M][K], B [N][K] e4m3 (K contiguous,
+ * K % 128 == 0), sa [M][K/128], sb [N][K/128] fp32 (the layout dsb200_fp8_block_quantize writes for row-major operands). */
+int dsb200_gemm_fp8_block(const void* A, const void* B, void* C, const float* sa, const float* sb, int M, int N, int K,
+                          int lda, int ldb, int ldc, int max_ctas, dsb200_stream_t stream);
 
 /* ---- csrc/gemm/gemm_grouped.cu */
 /* C[r, :] = A[r, :] * W[expert(r)]^T for rows sorted by expert; `cum` (device, int64[E]) holds inclusive cumulative row counts.
@@ -274,6 +296,10 @@ int dsb200_int_dequantize(const void* q, const float* params, void* out, long lo
                           int symmetric, int dtype, dsb200_stream_t stream);
 int dsb200_fake_quantize(void* x, long long groups, int group_size, int bits, int symmetric, int stochastic,
                          long long seed, int dtype, dsb200_stream_t stream);
+/* q[rows][cols] (e4m3) and scales[rows] (fp32) with x ~= q * scale per row; x: [rows][cols] with row stride ldx (elements).
+ * dtype: 0 bf16, 1 fp16, 2 fp32.  cols must be a multiple of 8. */
+int dsb200_fp8_rowwise_quantize(const void* x, void* q, float* scales, int rows, int cols, long long ldx, int dtype,
+                                dsb200_stream_t stream);
 
 /* ---- csrc/ragged/ragged_ops.cu */
 int dsb200_kv_rotary_append(void* qkv, void* kv_cache, const int* tok_seq, const int* tok_pos, const int* block_table,

@@ -130,3 +130,42 @@ def test_reshape_maps():
     assert len(maps) == 2 and maps[0].get_data(0, 0) == [0, 1, 4, 5] and maps[1].get_data(1, 0) == [10, 11, 14, 15]
     ok, err = model_3d_desc(1, 1, 1).can_reshape(model_3d_desc(2, 1, 1))
     assert not ok and "Expansion" in err[0]
+
+
+def test_zero_to_fp32_reads_reference_layout_checkpoints(tmp_path):
+    """Checkpoints written by the reference implementation carry no `ds_unit_layout`: stage 1/2 = one slice of every param
+    group's padded flat buffer per rank, stage 3 = every parameter partitioned by itself (ceil(numel / world) per rank), both
+    described by `param_shapes` in the model-states file (deepspeed/utils/zero_to_fp32.py:140-420)."""
+    import math
+    import os
+    from collections import OrderedDict
+    from deepspeedsyclsupport_b200.utils.zero_to_fp32 import get_fp32_state_dict_from_zero_checkpoint
+    torch.manual_seed(0)
+    params = OrderedDict(a=torch.randn(5, 3), b=torch.randn(7), c=torch.randn(2, 2, 2))
+    world = 2
+    for stage in (2, 3):
+        root = tmp_path / f"stage{stage}"
+        os.makedirs(root / "global_step1")
+        (root / "latest").write_text("global_step1")
+        shapes = [OrderedDict((k, v.shape) for k, v in params.items())]
+        if stage == 2:
+            flat = torch.cat([v.flatten() for v in params.values()])
+            flat = torch.cat([flat, flat.new_zeros((-flat.numel()) % (2 * world))])
+            per = [[part] for part in flat.chunk(world)]
+            model_file = "mp_rank_00_model_states.pt"
+        else:
+            pieces = [[] for _ in range(world)]
+            for v in params.values():
+                n = math.ceil(v.numel() / world)
+                f = torch.cat([v.flatten(), v.new_zeros(n * world - v.numel())])
+                for r in range(world):
+                    pieces[r].append(f[r * n:(r + 1) * n])
+            per = [[torch.cat(p)] for p in pieces]
+            model_file = "zero_pp_rank_0_mp_rank_00_model_states.pt"
+        torch.save({"param_shapes": shapes, "buffer_names": [], "shared_params": {}, "module": {}}, root / "global_step1" / model_file)
+        key = "fp32_flat_groups" if stage == 3 else "single_partition_of_fp32_groups"
+        for r in range(world):
+            torch.save({"optimizer_state_dict": {"zero_stage": stage, "partition_count": world, key: per[r]}},
+                       root / "global_step1" / f"zero_pp_rank_{r}_mp_rank_00_optim_states.pt")
+        sd = get_fp32_state_dict_from_zero_checkpoint(str(root))
+        assert all(torch.equal(sd[k], v) for k, v in params.items()), stage

@@ -791,6 +791,28 @@ def test_ragged_engine_w8a8_gpu():
     assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
 
 
+def test_ragged_engine_block_scaled_fp8_gpu():
+    """FastGen with quantization_mode = wf8af8_block: projections on the block-scaled fp8 GEMM (1 x 128 scales on weights and
+    activations); logits close to the bf16 engine."""
+    from test_inference_v2 import _hf_llama_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    cfg = dict(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+               rms_norm_eps=1e-5)
+    sd = _hf_llama_state(cfg)
+    mk = lambda mode: RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 256, "max_ragged_sequence_count": 8, "max_context": 256,
+                                                                 "memory_config": {"mode": "allocate", "size": 40}},
+                                                  quantization={"quantization_mode": mode})
+    torch.manual_seed(2)
+    a = torch.randint(0, 512, (130, ))
+    ref = build_engine_from_state_dict("llama", cfg, sd, mk(""), dtype=torch.bfloat16).put([1], [a])[0].float()
+    eng = build_engine_from_state_dict("llama", cfg, sd, mk("wf8af8_block"), dtype=torch.bfloat16)
+    w = eng._model.layers[0]["mlp1_w"]
+    assert type(eng._model.qkv_lin).__name__ == "FP8BlockLinear" and w.dtype == torch.uint8 and w.scales.shape == (w.shape[0], w.shape[1] // 128)
+    out = eng.put([1], [a])[0].float()
+    assert (out - ref).abs().max() < 0.35 * ref.abs().max()
+    assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
+
+
 @pytest.mark.parametrize("shape", [(300, 512, 256), (128, 4096, 1024), (1000, 1096, 328)])
 def test_fused_gemm_allreduce_single_rank(shape):
     """GEMM -> all-reduce kernel at world 1 (the reducers wait on this rank's own tile flags only): equals the plain product,
@@ -868,3 +890,46 @@ def test_fused_gemm_reduce_scatter_rows_single_rank():
         want = ref[lo:hi] + res.float()
         assert (out[:hi - lo].float() - want).abs().max() <= 1e-2 * want.abs().max(), (lo, hi)
         assert torch.all(out[hi - lo] == 7.0)
+
+
+@pytest.mark.parametrize("shape,dtype", [((37, 4096), torch.bfloat16), ((5, 11008), torch.bfloat16), ((64, 1024), torch.float16), ((3, 264), torch.float32)])
+def test_fp8_rowwise_quantize_kernel_matches_eager(shape, dtype):
+    """One-kernel per-token fp8 quantisation (rows longer than the 2048-element register cache take the second read) against the
+    eager abs / amax / div / clamp / cast chain it replaces."""
+    from deepspeedsyclsupport_b200.ops.gemm import FP8_MAX, quantize_fp8_rowwise
+    torch.manual_seed(1)
+    x = (torch.randn(*shape, device=_dev()) * torch.rand(shape[0], 1, device=_dev()) * 4).to(dtype)
+    x[0] = 0  # an all-zero row must not divide by zero
+    q, s = quantize_fp8_rowwise(x)
+    xf = x.float()
+    s_ref = xf.abs().amax(-1).clamp_min(1e-12) / FP8_MAX
+    q_ref = (xf / s_ref[:, None]).clamp(-FP8_MAX, FP8_MAX).to(torch.float8_e4m3fn)
+    assert torch.allclose(s, s_ref, rtol=1e-6, atol=0)
+    # identical up to the rounding of x * (1/scale) versus x / scale at e4m3 tie points
+    mism = (q.float() != q_ref.float()).float().mean().item()
+    assert mism < 2e-3, mism
+    assert ((q.float() * s[:, None] - xf).abs() <= 0.07 * xf.abs().amax(-1, keepdim=True) + 1e-9).all()
+
+
+@pytest.mark.parametrize("shape", [(256, 256, 256), (1000, 1096, 384), (4096, 4096, 4096), (77, 264, 128), (512, 11008, 4096)])
+def test_gemm_fp8_block_scaled(shape):
+    """Block-scaled fp8 tcgen05 GEMM (1 x 128 scale blocks on both operands, promotion in registers) against the fp32 product of
+    the dequantised operands, and against the unquantised product within fp8 tolerance; operands come from the ZeRO++ block
+    quantiser, i.e. a qwZ weight payload is consumed as it is."""
+    from deepspeedsyclsupport_b200.ops.gemm import gemm_fp8_block, linear_fp8_block
+    from deepspeedsyclsupport_b200.ops.quantizer import dequantize_fp8_block, quantize_fp8_block
+    M, N, K = shape
+    torch.manual_seed(0)
+    a = (torch.randn(M, K, device=_dev()) * (1 + 3 * torch.rand(M, K // 128, device=_dev()).repeat_interleave(128, 1))).bfloat16()
+    b = (torch.randn(N, K, device=_dev()) * 0.05 * (1 + 5 * torch.rand(N, K // 128, device=_dev()).repeat_interleave(128, 1))).bfloat16()
+    aq, sa = quantize_fp8_block(a)
+    bq, sb = quantize_fp8_block(b)
+    c = gemm_fp8_block(aq.view(M, K), bq.view(N, K), sa, sb).float()
+    a_dq = dequantize_fp8_block(aq, sa, dtype=torch.float32).view(M, K)
+    b_dq = dequantize_fp8_block(bq, sb, dtype=torch.float32).view(N, K)
+    ref_q = a_dq @ b_dq.t()
+    assert (c - ref_q).abs().max() <= 1e-2 * ref_q.abs().max(), (c - ref_q).abs().max() / ref_q.abs().max()
+    ref = a.float() @ b.float().t()
+    assert (c - ref).norm() <= 0.06 * ref.norm()
+    y = linear_fp8_block(a, bq.view(N, K), sb).float()
+    assert (y - ref).norm() <= 0.06 * ref.norm()

@@ -537,17 +537,17 @@ def test_zeropp_quantized_weights_and_gradients_track_bf16():
     run_distributed(_zeropp_body, world_size=2, backend="nccl", timeout=400)
 
 
-def _fastgen_tp_body():
+def _fastgen_tp_body(tp=2):
     """FastGen at TP=2 on the peer-memory collectives (fused GEMM + all-reduce for o_proj / down_proj, logits pushed through the
     switch): ragged prefill + decode logits must match the fp32 dense forward, and the fused kernels must actually be taken."""
     import os
     from deepspeedsyclsupport_b200 import comm as dist
     from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
     from test_inference_v2 import _dense_llama_logits, _hf_llama_state
-    cfg = dict(vocab_size=512, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
-               rms_norm_eps=1e-5)
+    cfg = dict(vocab_size=512, hidden_size=256 * (tp // 2), intermediate_size=512 * (tp // 2), num_hidden_layers=2, num_attention_heads=2 * tp,
+               num_key_value_heads=tp, rms_norm_eps=1e-5)
     sd = _hf_llama_state(cfg)
-    ecfg = RaggedInferenceEngineConfig(tensor_parallel={"tp_size": 2},
+    ecfg = RaggedInferenceEngineConfig(tensor_parallel={"tp_size": tp},
                                        state_manager={"max_ragged_batch_size": 512, "max_ragged_sequence_count": 8, "max_context": 1024,
                                                       "memory_config": {"mode": "allocate", "size": 64}})
     eng = build_engine_from_state_dict("llama", cfg, sd, ecfg, dtype=torch.bfloat16)
@@ -569,7 +569,125 @@ def _fastgen_tp_body():
         print(f"FASTGEN_TP collectives used: {ops.calls}, nvls={ops.nvls}", flush=True)
     assert ops is not None and ops.calls["fused_one_shot"] + ops.calls["fused_two_shot"] >= 8 and ops.calls["gather_logits"] == 2, \
         (None if ops is None else ops.calls)
+    if tp >= 4 and ops.nvls:
+        assert ops.calls["fused_two_shot"] >= 4, ops.calls  # the 256-token prefill chunk takes the reduce-scatter + multicast all-gather form
 
 
 def test_fastgen_tp2_uses_fused_collectives_and_matches_dense():
     run_distributed(_fastgen_tp_body, world_size=2, backend="nccl", timeout=400)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+def test_fastgen_tp4_two_shot_collectives_match_dense():
+    run_distributed(_fastgen_tp_body, world_size=4, backend="nccl", args=(4, ), timeout=400)
+
+
+def _moe_peer_body():
+    """Expert parallelism over peer memory (dispatch push / combine pull kernels, moe/peer_dispatch.py) against the NCCL
+    all-to-all path and the dense einsum formulation: outputs and every gradient (input, router, experts), top-1 and top-2."""
+    import os
+    import deepspeedsyclsupport_b200 as deepspeed  # noqa: F401
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.moe import sharded_moe as SM
+    from deepspeedsyclsupport_b200.moe.layer import MoE
+    from deepspeedsyclsupport_b200.utils import groups
+    rank = dist.get_rank()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    d, E, S = 256, 4, 192
+
+    class Expert(torch.nn.Module):
+
+        def __init__(self):
+            super().__init__()
+            self.fc = torch.nn.Linear(d, d)
+
+        def forward(self, x):
+            return torch.nn.functional.gelu(self.fc(x))
+
+    for k in (1, 2):
+        torch.manual_seed(11)
+        moe = MoE(hidden_size=d, expert=Expert(), num_experts=E, ep_size=2, k=k, use_rts=False, capacity_factor=1.5, min_capacity=0).to(dev).bfloat16()
+        moe.set_deepspeed_parallelism()
+        torch.manual_seed(100 + rank)
+        x0 = torch.randn(S, d, device=dev).bfloat16()
+        g0 = torch.randn(S, d, device=dev).bfloat16()
+        results = {}
+        for mode in ("0", "1"):
+            os.environ["DSB200_MOE_PEER"] = mode
+            for p in moe.parameters():
+                p.grad = None
+            x = x0.clone().requires_grad_(True)
+            if k == 2:
+                torch.manual_seed(5)  # top-2 draws gumbel noise for the second choice: same noise in both modes
+            y, l_aux, _ = moe(x)
+            (y.float() * g0.float()).sum().backward()
+            torch.cuda.synchronize()
+            results[mode] = (y.float().clone(), x.grad.float().clone(), {n: p.grad.float().clone() for n, p in moe.named_parameters()})
+        (y_n, gx_n, gp_n), (y_p, gx_p, gp_p) = results["0"], results["1"]
+
+        def rel(a, b):
+            return ((a - b).norm() / (b.norm() + 1e-20)).item()
+
+        assert rel(y_p, y_n) < 2e-2, ("output", k, rel(y_p, y_n))
+        assert rel(gx_p, gx_n) < 3e-2, ("input gradient", k, rel(gx_p, gx_n))
+        for n in gp_n:
+            assert rel(gp_p[n], gp_n[n]) < 5e-2, (n, k, rel(gp_p[n], gp_n[n]))
+        from deepspeedsyclsupport_b200.moe.peer_dispatch import PeerMoEBuffers
+        assert PeerMoEBuffers._by_group, "the peer path was not taken"
+        if rank == 0:
+            print(f"MOE_PEER top-{k}: output rel diff {rel(y_p, y_n):.2e}, input-grad {rel(gx_p, gx_n):.2e}, "
+                  f"worst param-grad {max(rel(gp_p[n], gp_n[n]) for n in gp_n):.2e}", flush=True)
+    os.environ["DSB200_MOE_PEER"] = "1"
+
+
+def test_moe_peer_dispatch_combine_matches_all_to_all():
+    run_distributed(_moe_peer_body, world_size=2, backend="nccl", timeout=400)
+
+
+def _ulysses_llama_body():
+    """Llama with DeepSpeed-Ulysses over 2 GPUs (packed QKV re-sharded by the peer push kernel, attention over the whole sequence
+    for half of the heads, output pulled back) against the same model on the whole sequence in one process: loss and gradients."""
+    import os
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.models import LlamaForCausalLM, llama_config
+    from deepspeedsyclsupport_b200.sequence import fused as UF
+    rank, P = dist.get_rank(), dist.get_world_size()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    B, S = 2, 512
+    cfg_kw = dict(hidden_size=512, intermediate_size=1024, num_attention_heads=4, num_key_value_heads=2, num_hidden_layers=2, vocab_size=1024,
+                  activation_checkpointing=False)
+    torch.manual_seed(0)
+    ref_model = LlamaForCausalLM(llama_config("tiny", **cfg_kw)).to(dev).bfloat16()
+    torch.manual_seed(0)
+    sp_model = LlamaForCausalLM(llama_config("tiny", **cfg_kw)).to(dev).bfloat16().set_sequence_parallel(dist.get_world_group())
+    g = torch.Generator().manual_seed(3)
+    ids = torch.randint(0, 1024, (B, S), generator=g).to(dev)
+    labels = torch.randint(0, 1024, (B, S), generator=g).to(dev)
+    full_loss = ref_model(ids, labels)
+    full_loss.backward()
+    S_local = S // P
+    sl = slice(rank * S_local, (rank + 1) * S_local)
+    for mode in ("1", "0"):  # peer kernels, then the NCCL all-to-all fall-back
+        os.environ["DSB200_ULYSSES_PEER"] = mode
+        for p_ in sp_model.parameters():
+            p_.grad = None
+        local_loss = sp_model(ids[:, sl].contiguous(), labels[:, sl].contiguous())
+        (local_loss / P).backward()
+        total = local_loss.detach().float().clone()
+        dist.all_reduce(total)
+        assert abs(total.item() / P - full_loss.item()) < 2e-2 * abs(full_loss.item()), (mode, total.item() / P, full_loss.item())
+        worst = 0.0
+        for (n, p_sp), (_, p_ref) in zip(sp_model.named_parameters(), ref_model.named_parameters()):
+            gsum = p_sp.grad.float().clone()
+            dist.all_reduce(gsum)
+            rel = ((gsum - p_ref.grad.float()).norm() / (p_ref.grad.float().norm() + 1e-20)).item()
+            worst = max(worst, rel)
+            assert rel < 0.12, (mode, n, rel)
+        if rank == 0:
+            print(f"ULYSSES peer={mode}: loss {total.item() / P:.5f} vs {full_loss.item():.5f}; worst gradient rel diff {worst:.2e}", flush=True)
+    assert UF._Exchange._by_group, "the peer exchange was not taken"
+    os.environ["DSB200_ULYSSES_PEER"] = "1"
+
+
+def test_llama_ulysses_peer_exchange_matches_full_sequence():
+    run_distributed(_ulysses_llama_body, world_size=2, backend="nccl", timeout=400)

@@ -1,13 +1,10 @@
 #!/bin/bash
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
-$TR --master-port 29611 tools/determinism_probe.py --reps 2 2>&1 | grep -E "instance|rep |Error" | cut -c1-400
-$TR --master-port 29612 tools/determinism_probe.py --reps 2 --no-p2p 2>&1 | grep -E "instance|rep |Error" | cut -c1-400
-timeout 1500 python -m pytest tests/test_multigpu.py -q -s -k "equals or shard_write or zeropp or fused_reduce or fastgen" > gpurun_out/mgpu_tests.log 2>&1
-echo "pytest rc=$?"; grep -E "SYMM|ZERO3|ZEROPP|FASTGEN|  unit |passed|failed|skipped|Error|error|assert" gpurun_out/mgpu_tests.log | cut -c1-400 | head -60
-DSB200_PROBE_TRACE=1 timeout 600 $TR --master-port 29620 bench.py --gpus 2 --steps 5 --warmup 3 > gpurun_out/bench_own_2gpu.json 2> gpurun_out/bench_own_2gpu.err
-tail -1 gpurun_out/bench_own_2gpu.json | cut -c1-3000
-timeout 600 $TR --master-port 29621 bench.py --gpus 2 --steps 5 --warmup 3 --zeropp > gpurun_out/bench_own_2gpu_zeropp.json 2> gpurun_out/bench_own_2gpu_zeropp.err
-tail -1 gpurun_out/bench_own_2gpu_zeropp.json | cut -c1-2200
-timeout 600 $TR --master-port 29604 tools/step_breakdown.py --out gpurun_out/step_breakdown_7b_2gpu.txt > gpurun_out/step_breakdown.log 2>&1
-head -14 gpurun_out/step_breakdown_7b_2gpu.txt | cut -c1-160
+timeout 900 python -m pytest tests/test_kernels_gpu.py -q -x -k "fp8_block_scaled or rowwise_quantize or block_scaled_fp8 or w8a8" > gpurun_out/kernel_tests.log 2>&1
+echo "kernel tests rc=$?"; tail -4 gpurun_out/kernel_tests.log | cut -c1-400
+timeout 900 python -m pytest tests/test_peer_one_gpu.py -q -x > gpurun_out/peer_one_gpu.log 2>&1
+echo "one-gpu peer rc=$?"; tail -4 gpurun_out/peer_one_gpu.log | cut -c1-600
+timeout 900 python -m pytest tests/test_multigpu.py -q -s -k "moe_peer or ulysses" > gpurun_out/mgpu_tests.log 2>&1
+echo "pytest rc=$?"; grep -E "MOE_PEER|ULYSSES|passed|failed|skipped|Error|error|assert" gpurun_out/mgpu_tests.log | cut -c1-400 | head -40
+timeout 600 python tools/paged_flash_bench.py --out gpurun_out/paged_flash_bench.json > gpurun_out/paged_flash_bench.log 2>&1
+echo "paged bench rc=$?"; grep -E "paged_flash_ms|tflops|kv_fraction|speedup|cuda_core|sm_mhz|\"(prefill|decode)" gpurun_out/paged_flash_bench.json | tr -d '\n' | cut -c1-2000
