@@ -12,6 +12,7 @@ class DeepSpeedTPConfig(DeepSpeedConfigModel):
 class QuantizationConfig(DeepSpeedConfigModel):
     # "" (16-bit weights) | "wf8af8" (e4m3 weights per output feature x e4m3 activations per token)
     # | "wf8af8_block" (block-scaled: one fp32 scale per 128 input features on both operands, the ZeRO++ wire format)
+    # | "wf8af8_mx" (MXFP8: one UE8M0 scale per 32 input features, applied by the tensor core: tcgen05 mxf8f6f4.block_scale)
     quantization_mode: str = ""
 
 

@@ -29,7 +29,8 @@ class InferenceEngineV2:
         self.device = torch.device(acc.current_device_name())
         self._model = model_builder(self._tp_group, self.device)
         spec = self._model.spec
-        kv_cfg = KVCacheConfig(block_size=128 if self.device.type == "cuda" else 16,
+        block = int(getattr(engine_config.state_manager, "kv_block_size", 0) or 0) or (128 if self.device.type == "cuda" else 16)
+        kv_cfg = KVCacheConfig(block_size=block,
                                cache_shape=(spec.num_layers, self._model.hkv, spec.head_dim), cache_dtype="bf16")
         self._state_manager = DSStateManager(engine_config.state_manager, kv_cfg, base_mp_group=self._tp_group)
         self._batch = RaggedBatchWrapper(engine_config.state_manager)

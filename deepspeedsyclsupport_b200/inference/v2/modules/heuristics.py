@@ -31,6 +31,8 @@ def instantiate_linear(linear_config: DSLinearConfig, engine_config: RaggedInfer
         name = "fp8_linear"
     elif mode == "wf8af8_block" and DSLinearRegistry.registry["fp8_block_linear"].supports_config(linear_config):
         name = "fp8_block_linear"
+    elif mode == "wf8af8_mx" and DSLinearRegistry.registry["mxfp8_linear"].supports_config(linear_config):
+        name = "mxfp8_linear"
     return DSLinearRegistry.instantiate_config(ConfigBundle(name=name, config=linear_config))
 
 

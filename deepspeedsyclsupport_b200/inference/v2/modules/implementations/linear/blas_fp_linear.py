@@ -4,13 +4,15 @@
 `fp8_linear`: e4m3 weights with one scale per output feature, activations quantised per token, product on the fp8 tensor-core
 GEMM (csrc/gemm/gemm_fp8.cu) -- chosen by the heuristics when the engine's quantization_mode is "wf8af8".
 `fp8_block_linear`: block-scaled e4m3 weights and activations (one fp32 scale per 128 input features of every row, the ZeRO++
-wire format) on csrc/gemm/gemm_fp8_block.cu -- quantization_mode "wf8af8_block"."""
+wire format) on csrc/gemm/gemm_fp8_block.cu -- quantization_mode "wf8af8_block".
+`mxfp8_linear`: MXFP8 (e4m3 + one UE8M0 scale per 32 input features) on the hardware block-scaled tensor-core path
+(tcgen05.mma.kind::mxf8f6f4.block_scale, csrc/gemm/gemm_mxfp8.cu) -- quantization_mode "wf8af8_mx"."""
 from typing import Any, Dict, Optional
 
 import torch
 
 from ......ops import fused_ops as FO
-from ......ops.gemm import gemm, linear_fp8, linear_fp8_block, quantize_fp8_rowwise
+from ......ops.gemm import gemm, linear_fp8, linear_fp8_block, linear_mxfp8, quantize_fp8_rowwise, quantize_mxfp8
 from ....inference_parameter import InferenceParameter
 from ....inference_utils import ActivationType, DtypeEnum, activation_name, is_gated
 from ...configs import DSLinearConfig
@@ -115,3 +117,24 @@ class FP8BlockLinear(_LinearCommon):
 
     def forward(self, hidden_states: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
         return self._epilogue(linear_fp8_block(hidden_states, w, w.scales), b)
+
+
+@DSLinearRegistry.register_module
+class MXFP8Linear(_LinearCommon):
+
+    @staticmethod
+    def name() -> str:
+        return "mxfp8_linear"
+
+    @staticmethod
+    def supports_config(config: DSLinearConfig) -> bool:
+        return _supported(config) and config.in_channels % 128 == 0
+
+    def transform_param(self, param: torch.Tensor) -> InferenceParameter:
+        if param.dim() != 2:
+            return InferenceParameter.initialize(param.to(DtypeEnum(self._config.input_dtype).value).contiguous())
+        q, sf = quantize_mxfp8(param.to(DtypeEnum(self._config.input_dtype).value).contiguous())
+        return InferenceParameter.initialize(q, scales=sf)
+
+    def forward(self, hidden_states: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor] = None) -> torch.Tensor:
+        return self._epilogue(linear_mxfp8(hidden_states, w, w.scales), b)

@@ -37,6 +37,9 @@ class DSStateManagerConfig(DeepSpeedConfigModel):
     max_context: int = Field(8192, gt=0)
     memory_config: MemoryConfig = MemoryConfig()
     offload: bool = False
+    # tokens per KV block; 0 = pick for the device (128 on CUDA: one block is one TMA page of the paged flash kernel; 16 on hosts).
+    # The tensor-core attention kernel wants a divisor of 128.
+    kv_block_size: int = Field(0, ge=0)
 
     @model_validator(mode="after")
     def max_ragged_sequence_count_validator(self):

@@ -57,7 +57,9 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
 
 FP8_MAX = 448.0  # largest finite e4m3 value
 _ROWQ_DT = {torch.bfloat16: 0, torch.float16: 1, torch.float32: 2}
-native.register_sigs({"dsb200_fp8_rowwise_quantize": "ppp ii l i p", "dsb200_gemm_fp8_block": "ppppp iii iii i p"})
+native.register_sigs({"dsb200_fp8_rowwise_quantize": "ppp ii l i p", "dsb200_gemm_fp8_block": "ppppp iii iii i p",
+                      "dsb200_gemm_mxfp8": "ppppp iii iii i p", "dsb200_mxfp8_quantize": "ppp ii l i p", "dsb200_mxfp8_sf_bytes": "ii"},
+                     restype_long=("dsb200_mxfp8_sf_bytes", ))
 
 
 def quantize_fp8_rowwise(x):
@@ -138,6 +140,76 @@ def linear_fp8_block(x, w_q, w_scale, bias=None):
     x2 = x.reshape(-1, x.shape[-1]).contiguous()
     xq, xs = quantize_fp8_block(x2)
     y = gemm_fp8_block(xq.view(x2.shape), w_q, xs, w_scale).view(*x.shape[:-1], w_q.shape[0])
+    if y.dtype != x.dtype:
+        y = y.to(x.dtype)
+    return y if bias is None else y + bias
+
+
+# ---- MXFP8: e4m3 payload + one UE8M0 (power-of-two) scale per 32 elements, multiplied by the hardware block-scaled MMA
+def mxfp8_unpack_scales(sf, rows, K):
+    """Packed scale tiles (csrc/gemm/gemm_mxfp8.cu layout) -> fp32 scales [rows, K // 32] (tests, CPU oracle)."""
+    KB = K // 128
+    r = torch.arange(rows, device=sf.device)[:, None]
+    k32 = torch.arange(K // 32, device=sf.device)[None, :]
+    idx = ((r // 128) * KB + k32 // 4) * 512 + (r % 32) * 16 + (r % 128 // 32) * 4 + k32 % 4
+    return torch.exp2(sf.view(-1)[idx].float() - 127.0)
+
+
+def _mxfp8_quantize_ref(x):
+    rows, K = x.shape
+    xf = x.float().view(rows, K // 32, 32)
+    amax = xf.abs().amax(-1)
+    e = torch.ceil(torch.log2((amax / FP8_MAX).clamp_min(2.0 ** -126))).clamp(-126, 126)
+    q = (xf * torch.exp2(-e)[:, :, None]).clamp(-FP8_MAX, FP8_MAX).to(torch.float8_e4m3fn).view(rows, K)
+    KB = K // 128
+    sf = torch.zeros((rows + 255) // 256 * 2 * KB * 512, dtype=torch.uint8)
+    r = torch.arange(rows)[:, None]
+    k32 = torch.arange(K // 32)[None, :]
+    idx = ((r // 128) * KB + k32 // 4) * 512 + (r % 32) * 16 + (r % 128 // 32) * 4 + k32 % 4
+    sf[idx.reshape(-1)] = (e + 127).to(torch.uint8).reshape(-1)
+    return q.view(torch.uint8), sf
+
+
+def quantize_mxfp8(x):
+    """x [rows, K] (K % 128 == 0) -> (uint8 e4m3 payload [rows, K], packed UE8M0 scale tiles) for `gemm_mxfp8`."""
+    assert x.dim() == 2 and x.shape[1] % 128 == 0 and x.stride(1) == 1
+    rows, K = x.shape
+    if not x.is_cuda:
+        return _mxfp8_quantize_ref(x)
+    q = torch.empty(rows, K, dtype=torch.uint8, device=x.device)
+    sf = torch.zeros(native.lib().dsb200_mxfp8_sf_bytes(rows, K), dtype=torch.uint8, device=x.device)
+    rc = native.lib().dsb200_mxfp8_quantize(native.ptr(x), native.ptr(q), native.ptr(sf), rows, K, x.stride(0), _ROWQ_DT[x.dtype], native.stream_ptr())
+    native.check(rc)
+    return q, sf
+
+
+def gemm_mxfp8(a_q, b_q, sfa, sfb, out=None, max_ctas=0):
+    """C[M,N] (bf16) = dequant(A) dequant(B)^T on tcgen05.mma.kind::mxf8f6f4.block_scale (csrc/gemm/gemm_mxfp8.cu): the UE8M0 scales
+    are applied by the tensor core itself, from tensor memory."""
+    M, K = a_q.shape
+    N = b_q.shape[0]
+    assert b_q.shape[1] == K and K % 128 == 0 and a_q.stride(1) == 1 and b_q.stride(1) == 1
+    if not a_q.is_cuda:
+        af = a_q.view(torch.float8_e4m3fn).float() * mxfp8_unpack_scales(sfa, M, K).repeat_interleave(32, 1)
+        bf = b_q.view(torch.float8_e4m3fn).float() * mxfp8_unpack_scales(sfb, N, K).repeat_interleave(32, 1)
+        return (af @ bf.t()).to(torch.bfloat16)
+    if out is None:
+        ld = (N + 7) // 8 * 8
+        out = torch.empty(M, ld, dtype=torch.bfloat16, device=a_q.device)[:, :N]
+    rc = native.lib().dsb200_gemm_mxfp8(native.ptr(a_q), native.ptr(b_q), native.ptr(out), native.ptr(sfa), native.ptr(sfb), M, N, K, a_q.stride(0),
+                                        b_q.stride(0), out.stride(0), int(max_ctas), native.stream_ptr())
+    native.check(rc)
+    if _prof._ACTIVE:
+        _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_mxfp8")
+    return out
+
+
+def linear_mxfp8(x, w_q, w_sf, bias=None):
+    """x @ W^T with W held as MXFP8 (payload + packed scales, quantised once at load); activations are quantised by one kernel."""
+    x2 = x.reshape(-1, x.shape[-1])
+    x2 = x2 if x2.stride(1) == 1 else x2.contiguous()
+    xq, xsf = quantize_mxfp8(x2)
+    y = gemm_mxfp8(xq, w_q, xsf, w_sf).view(*x.shape[:-1], w_q.shape[0])
     if y.dtype != x.dtype:
         y = y.to(x.dtype)
     return y if bias is None else y + bias

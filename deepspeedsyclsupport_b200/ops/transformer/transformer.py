@@ -150,7 +150,16 @@ class DeepSpeedTransformerLayer(nn.Module):
     def _attention(self, x, attention_mask):
         B, S, H = x.shape
         heads = self.config.heads
-        qkv = self._linear(x, self.attn_qkvw, self.attn_qkvb).view(B, S, 3, heads, H // heads)
+        d = H // heads
+        qkv2d = self._linear(x, self.attn_qkvw, self.attn_qkvb)
+        p_drop = self.config.attn_dropout_ratio if self.training and self.config.attn_dropout_ratio > 0 else 0.0
+        if (attention_mask is None and p_drop == 0.0 and qkv2d.is_cuda and qkv2d.dtype == torch.bfloat16 and S % 128 == 0 and d in (64, 128)):
+            # unmasked, no attention dropout: the packed projection [B*S, (q | k | v heads) * d] is exactly what the tcgen05 flash
+            # attention kernels read (csrc/attn/flash_fwd*.cu, flash_bwd.cu) -- no head transposes, no S x S matrix in HBM
+            from ..flash_attention import flash_attention_packed
+            ctx = flash_attention_packed(qkv2d.reshape(B * S, 3 * H), B, S, heads, heads, d, causal=False)
+            return self._linear(ctx.view(B, S, H), self.attn_ow, self.attn_ob)
+        qkv = qkv2d.view(B, S, 3, heads, d)
         q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))
         mask = None
         if attention_mask is not None:

@@ -235,6 +235,17 @@ int dsb200_gemm_fp8_block(const void* A, const void* B, void* C, const float* sa
 int dsb200_moe_gemm_bf16(const void* A, const void* W, void* C, const long long* cum, int R, int N, int K, int E, int lda,
                          int ldw, int ldc, dsb200_stream_t stream);
 
+/* ---- csrc/gemm/gemm_mxfp8.cu */
+/* Bytes of the packed scale tensor for a [rows][K] operand (rows padded to a multiple of 256 so either operand role works). */
+long long dsb200_mxfp8_sf_bytes(int rows, int K);
+/* x [rows][K] (row stride ldx elements; dtype 0 bf16, 1 fp16, 2 fp32; K % 128 == 0) -> q [rows][K] e4m3 + sf (dsb200_mxfp8_sf_bytes,
+ * ZERO-INITIALISED by the caller: rows beyond `rows` keep scale byte 0). */
+int dsb200_mxfp8_quantize(const void* x, void* q, void* sf, int rows, int K, long long ldx, int dtype,
+                          dsb200_stream_t stream);
+/* C[M,N] (bf16) = dequant(A) * dequant(B)^T with MXFP8 operands (payload + packed UE8M0 scales from dsb200_mxfp8_quantize). */
+int dsb200_gemm_mxfp8(const void* A, const void* B, void* C, const void* sfa, const void* sfb, int M, int N, int K,
+                      int lda, int ldb, int ldc, int max_ctas, dsb200_stream_t stream);
+
 /* ---- csrc/host/aio.cpp */
 void* dsbh_aio_create(int64_t block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);
 void dsbh_aio_destroy(void* hp);

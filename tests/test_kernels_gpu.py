@@ -791,9 +791,10 @@ def test_ragged_engine_w8a8_gpu():
     assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
 
 
-def test_ragged_engine_block_scaled_fp8_gpu():
-    """FastGen with quantization_mode = wf8af8_block: projections on the block-scaled fp8 GEMM (1 x 128 scales on weights and
-    activations); logits close to the bf16 engine."""
+@pytest.mark.parametrize("mode,cls", [("wf8af8_block", "FP8BlockLinear"), ("wf8af8_mx", "MXFP8Linear")])
+def test_ragged_engine_block_scaled_fp8_gpu(mode, cls):
+    """FastGen with the block-scaled fp8 modes: wf8af8_block (1 x 128 fp32 scales, promotion in registers) and wf8af8_mx (MXFP8 on
+    the hardware block-scaled MMA); logits close to the bf16 engine."""
     from test_inference_v2 import _hf_llama_state
     from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
     cfg = dict(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
@@ -805,9 +806,9 @@ def test_ragged_engine_block_scaled_fp8_gpu():
     torch.manual_seed(2)
     a = torch.randint(0, 512, (130, ))
     ref = build_engine_from_state_dict("llama", cfg, sd, mk(""), dtype=torch.bfloat16).put([1], [a])[0].float()
-    eng = build_engine_from_state_dict("llama", cfg, sd, mk("wf8af8_block"), dtype=torch.bfloat16)
+    eng = build_engine_from_state_dict("llama", cfg, sd, mk(mode), dtype=torch.bfloat16)
     w = eng._model.layers[0]["mlp1_w"]
-    assert type(eng._model.qkv_lin).__name__ == "FP8BlockLinear" and w.dtype == torch.uint8 and w.scales.shape == (w.shape[0], w.shape[1] // 128)
+    assert type(eng._model.qkv_lin).__name__ == cls and w.dtype == torch.uint8 and w.scales.is_cuda
     out = eng.put([1], [a])[0].float()
     assert (out - ref).abs().max() < 0.35 * ref.abs().max()
     assert (out - ref).abs().mean() < 0.08 * ref.abs().max()
@@ -932,4 +933,31 @@ def test_gemm_fp8_block_scaled(shape):
     ref = a.float() @ b.float().t()
     assert (c - ref).norm() <= 0.06 * ref.norm()
     y = linear_fp8_block(a, bq.view(N, K), sb).float()
+    assert (y - ref).norm() <= 0.06 * ref.norm()
+
+
+@pytest.mark.parametrize("shape", [(128, 256, 128), (256, 512, 512), (1000, 1096, 384), (4096, 4096, 4096), (77, 264, 128)])
+def test_gemm_mxfp8_hardware_block_scaled(shape):
+    """MXFP8 GEMM on tcgen05.mma.kind::mxf8f6f4.block_scale (UE8M0 scale per 32 elements, staged smem -> TMEM with tcgen05.cp):
+    quantiser against its restatement, GEMM against the fp32 product of the dequantised operands (exact up to accumulation
+    order + bf16 output) with scales that vary strongly per 32-element block, and against the unquantised product."""
+    from deepspeedsyclsupport_b200.ops.gemm import gemm_mxfp8, linear_mxfp8, mxfp8_unpack_scales, quantize_mxfp8, _mxfp8_quantize_ref
+    M, N, K = shape
+    torch.manual_seed(0)
+    blk = lambda r: torch.exp2(torch.randint(-6, 7, (r, K // 32), device=_dev()).float()).repeat_interleave(32, 1)
+    a = (torch.randn(M, K, device=_dev()) * blk(M)).bfloat16()
+    b = (torch.randn(N, K, device=_dev()) * 0.05 * blk(N)).bfloat16()
+    aq, sfa = quantize_mxfp8(a)
+    bq, sfb = quantize_mxfp8(b)
+    aq_ref, sfa_ref = _mxfp8_quantize_ref(a.cpu())
+    assert torch.equal(mxfp8_unpack_scales(sfa, M, K).cpu(), mxfp8_unpack_scales(sfa_ref, M, K))
+    assert (aq.cpu().view(torch.float8_e4m3fn).float() != aq_ref.view(torch.float8_e4m3fn).float()).float().mean() < 1e-3
+    a_dq = aq.view(torch.float8_e4m3fn).float() * mxfp8_unpack_scales(sfa, M, K).repeat_interleave(32, 1)
+    b_dq = bq.view(torch.float8_e4m3fn).float() * mxfp8_unpack_scales(sfb, N, K).repeat_interleave(32, 1)
+    ref_q = a_dq @ b_dq.t()
+    c = gemm_mxfp8(aq, bq, sfa, sfb).float()
+    assert (c - ref_q).abs().max() <= 1e-2 * ref_q.abs().max(), ((c - ref_q).abs().max() / ref_q.abs().max()).item()
+    ref = a.float() @ b.float().t()
+    assert (c - ref).norm() <= 0.06 * ref.norm()
+    y = linear_mxfp8(a, bq, sfb).float()
     assert (y - ref).norm() <= 0.06 * ref.norm()

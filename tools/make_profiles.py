@@ -57,22 +57,28 @@ def sass_summary(out_md):
         m = re.search(r"^\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
         if m:
             op = m.group(1)
-            for key in ("UTCHMMA", "UTCQMMA", "UTCBAR", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "LDTM", "STTM", "UTCATOMSWS", "HMMA", "SYNCS",
+            for key in ("UTCHMMA", "UTCQMMA", "UTCCP", "UTCBAR", "UTMALDG", "UTMASTG", "UTMAREDG", "UBLKCP", "LDTM", "STTM", "UTCATOMSWS", "HMMA", "SYNCS",
                         "LDG", "STG", "LDGSTS", "MUFU", "ATOM", "RED"):
                 if op.startswith(key):
                     per[cur][key] += 1
+            if "MC" in op.split(".")[0] or ".MC" in op or "LDGMC" in op:
+                per[cur]["MULTIMEM"] += 1
             if op.startswith("UTCHMMA") and ".2CTA" in op:
                 per[cur]["2CTA"] += 1
     lines = ["# SASS evidence (cuobjdump -sass libdsb200.so, sm_100a)", "",
              "Counts of Blackwell-specific mnemonics per kernel: `UTCHMMA` = tcgen05.mma (bf16; `.2CTA` = cta_group::2 pair MMA), `UTMALDG/UTMASTG/UTMAREDG` = TMA "
              "load/store/reduce, `LDTM/STTM` = tcgen05.ld/st, `SYNCS` = mbarrier ops, `HMMA` = legacy mma.sync (must be 0).", "",
-             "| kernel | UTCHMMA | of which .2CTA | UTMALDG | UTMASTG | UTMAREDG | LDTM | STTM | SYNCS | HMMA | LDG | STG |", "|---|---|---|---|---|---|---|---|---|---|---|---|"]
+             "`UTCQMMA` = tcgen05.mma block-scaled (mxf8f6f4.block_scale), `UTCCP` = tcgen05.cp (smem -> TMEM), `UBLKCP` = cp.async.bulk, "
+             "`MULTIMEM` = multimem.ld_reduce / multimem.st (NVLS: LDGMC / STG...MC forms).", "",
+             "| kernel | UTCHMMA | of which .2CTA | UTCQMMA | UTCCP | UTMALDG | UTMASTG | UTMAREDG | UBLKCP | LDTM | STTM | SYNCS | MULTIMEM | HMMA | LDG | STG |",
+             "|---|---|---|---|---|---|---|---|---|---|---|---|---|---|---|---|"]
     for k, c in sorted(per.items()):
         if sum(c.values()) == 0:
             continue
         dem = subprocess.run(["c++filt", k], capture_output=True, text=True).stdout.strip()
         dem = re.sub(r"\(.*", "", dem)[:90]
-        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['2CTA']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['LDTM']} | {c['STTM']} | {c['SYNCS']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
+        lines.append(f"| `{dem}` | {c['UTCHMMA']} | {c['2CTA']} | {c['UTCQMMA']} | {c['UTCCP']} | {c['UTMALDG']} | {c['UTMASTG']} | {c['UTMAREDG']} | {c['UBLKCP']} | "
+                     f"{c['LDTM']} | {c['STTM']} | {c['SYNCS']} | {c['MULTIMEM']} | {c['HMMA']} | {c['LDG']} | {c['STG']} |")
     open(out_md, "w").write("\n".join(lines) + "\n")
 
 
