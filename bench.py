@@ -362,6 +362,9 @@ def run_reference(args):
 
 def main():
     args = parse()
+    if os.environ.get("DSB200_HANG_DUMP"):  # diagnosis: dump every thread's stack if the process is still running after N seconds
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ["DSB200_HANG_DUMP"]), repeat=False, file=sys.stderr)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29511")
     # N == 1 is launched without torchrun: behave like a one-rank job (the reference would otherwise probe for MPI)

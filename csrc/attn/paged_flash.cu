@@ -41,6 +41,12 @@ struct Smem {
   static constexpr int TOTAL = BAR_OFF + 256 + 1024;
 };
 
+__device__ __forceinline__ float ex2_fast(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 struct Params {
   const int* tok_seq;      // [T] sequence slot of every token of the ragged batch
   const int* tok_pos;      // [T] position of the token inside its sequence
@@ -229,7 +235,8 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         tc_fence_after();
         const int key0 = (pg0 + j) * BN;
         const int visible = limit - key0;  // columns [0, visible) of this page count; may be <= 0 or >= 128
-        float m_blk = -INFINITY;
+        // four independent max / sum chains: a single running value would serialise 128 dependent operations per pass
+        float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint32_t sv[32];
@@ -239,14 +246,15 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           for (int i = 0; i < 32; ++i) {
             float v = __uint_as_float(sv[i]);
             if (c * 32 + i >= visible) v = -INFINITY;
-            m_blk = fmaxf(m_blk, v);
+            mx[i & 3] = fmaxf(mx[i & 3], v);
           }
         }
+        const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
         // a page with no visible key for this row leaves the running max alone (and -inf - -inf is never formed)
         const float m_new = fmaxf(m_run, m_blk * p.scale_log2);
         const float m_use = m_new == -INFINITY ? 0.f : m_new;
         const float alpha = m_run == -INFINITY ? 0.f : exp2f(m_run - m_use);
-        float l_blk = 0.f;
+        float ls[4] = {0.f, 0.f, 0.f, 0.f};
         uint8_t* pbuf = smem + SMEM::P_OFF + st * SMEM::P_BYTES;
         const int sw = row & 7;
 #pragma unroll
@@ -261,8 +269,8 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const float v = fmaf(__uint_as_float(sv[u * 8 + i]), p.scale_log2, -m_use);
-              e[i] = (c * 32 + u * 8 + i >= visible) ? 0.f : exp2f(v);
-              l_blk += e[i];
+              e[i] = (c * 32 + u * 8 + i >= visible) ? 0.f : ex2_fast(v);
+              ls[i & 3] += e[i];
             }
             uint4 val;
             val.x = pack_bf16x2(e[0], e[1]);
@@ -273,7 +281,7 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
             *reinterpret_cast<uint4*>(rowp + ((unit ^ sw) << 4)) = val;
           }
         }
-        l_run = l_run * alpha + l_blk;
+        l_run = l_run * alpha + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
         m_run = m_new;
         fence_proxy_async_smem();
         tc_fence_before();

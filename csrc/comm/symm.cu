@@ -52,7 +52,9 @@ __global__ void barrier_kernel(Peers peers, size_t flag_off, int rank, int world
   const int t = threadIdx.x;
   if (t < world) {
     uint32_t* remote = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(peers.ptr[t]) + flag_off) + rank;
-    st_release_sys(remote, epoch);
+    // max, not store: barriers issued on different streams may execute out of epoch order on a rank, and a late, lower epoch
+    // must never lower a flag a peer is already waiting on
+    asm volatile("red.release.sys.global.max.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
     const uint32_t* local = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(peers.ptr[rank]) + flag_off) + t;
     uint32_t spins = 0;
     while (static_cast<int32_t>(ld_acquire_sys(local) - epoch) < 0) {

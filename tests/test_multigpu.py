@@ -560,14 +560,16 @@ def _fastgen_tp_body(tp=2):
         x, ref = x.float().cpu(), ref.float()
         return (x - ref).abs().max().item() <= 0.05 * ref.abs().max().item() + 0.02
 
-    out = eng.put([1, 2], [a[:256], b[:39]])
-    assert close(out[0], ref_a[255]) and close(out[1], ref_b[38]), "prefill"
+    out = eng.put([1], [a[:256]])  # 256 rows: divisible by the TP degree -> two-shot form on >= 4 ranks
+    assert close(out[0], ref_a[255]), "prefill"
+    out = eng.put([2], [b[:39]])
+    assert close(out[0], ref_b[38]), "second prefill"
     out = eng.put([1, 2], [a[256:300], b[39:40]])
     assert close(out[0], ref_a[299]) and close(out[1], ref_b[39]), "chunk + decode"
     ops = eng._model._tp_ops() if hasattr(eng, "_model") else None
     if ops is not None and dist.get_rank() == 0:
         print(f"FASTGEN_TP collectives used: {ops.calls}, nvls={ops.nvls}", flush=True)
-    assert ops is not None and ops.calls["fused_one_shot"] + ops.calls["fused_two_shot"] >= 8 and ops.calls["gather_logits"] == 2, \
+    assert ops is not None and ops.calls["fused_one_shot"] + ops.calls["fused_two_shot"] >= 12 and ops.calls["gather_logits"] == 3, \
         (None if ops is None else ops.calls)
     if tp >= 4 and ops.nvls:
         assert ops.calls["fused_two_shot"] >= 4, ops.calls  # the 256-token prefill chunk takes the reduce-scatter + multicast all-gather form
