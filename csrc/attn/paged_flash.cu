@@ -8,10 +8,13 @@
 // the batch, the first token of its sequence in this batch, or its position is a multiple of 128/group.
 //
 //   warp 0   TMA producer : Q tile once (3-D map over [token][head][D], box [128/group tokens][group heads][64]), then K and V
-//                           pages (4-D map over [block*2+kv][slot][kv head][D]; block ids from the block table) through a 2-stage ring
-//   warp 1   MMA issuer   : S = Q K^T (128 x 128 x D, SS) into TMEM, PV = P V (P from smem, V MN-major) into TMEM
+//                           pages (4-D map over [block*2+kv][slot][kv head][D]; block ids from the block table) through a ring of
+//                           KV_STAGES K tiles and KV_STAGES V tiles; a K tile is released as soon as its QK^T has retired and a
+//                           V tile when its PV has, so two to three pages of loads are in flight per SM (decode is a pure
+//                           KV-bandwidth problem: with one page in flight the kernel sat at 35 % of HBM)
+//   warp 1   MMA issuer   : S = Q K^T (128 x 128 x D, SS) into TMEM, PV = P V (TS: P read from TMEM, V MN-major from smem) into TMEM
 //   warps 2-5 softmax     : thread == row: S row from TMEM, per-row causal limit (position + 1), online softmax in exp2 domain,
-//                           P (bf16) to swizzled smem, O kept in registers
+//                           P (bf16, two per column) stored back over the first 64 columns of its S buffer, O kept in registers
 // Long contexts at small batch do not fill 148 SMs with one CTA per (atom, kv head): with n_splits > 1 every CTA handles a
 // slice of the pages and writes an unnormalised partial (O, running max, running sum) to scratch; a second kernel merges.
 // Reference counterpart: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 (closed flash_attn_by_atoms)
@@ -24,21 +27,21 @@ namespace paged {
 
 constexpr int BM = 128;
 constexpr int BN = 128;
-constexpr int NUM_THREADS = 192;
-constexpr int SM_THREADS = 128;
+constexpr int NUM_THREADS = 320;  // TMA warp, MMA warp, 8 softmax warps
+constexpr int SM_THREADS = 256;
 constexpr int CHUNK_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled chunk
 
 template <int D>
 struct Smem {
   static constexpr int NCH = D / 64;
   static constexpr int TILE = NCH * CHUNK_BYTES;
-  static constexpr int P_BYTES = 2 * CHUNK_BYTES;
+  static constexpr int STAGES = D == 128 ? 3 : 6;  // K and V tiles each; Q + 2 * STAGES tiles = 224 KB (d = 128) / 208 KB (d = 64)
   static constexpr int Q_OFF = 0;
   static constexpr int K_OFF = Q_OFF + TILE;
-  static constexpr int V_OFF = K_OFF + 2 * TILE;
-  static constexpr int P_OFF = V_OFF + 2 * TILE;
-  static constexpr int BAR_OFF = P_OFF + 2 * P_BYTES;
-  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+  static constexpr int V_OFF = K_OFF + STAGES * TILE;
+  static constexpr int BAR_OFF = V_OFF + STAGES * TILE;
+  static constexpr int X_OFF = BAR_OFF + 384;  // 1 KB: page maxima exchanged between the two column halves of a row
+  static constexpr int TOTAL = X_OFF + 1024 + 1024;
 };
 
 __device__ __forceinline__ float ex2_fast(float x) {
@@ -81,15 +84,18 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM::BAR_OFF);
+  constexpr int NS = SMEM::STAGES;
   uint64_t* q_full = bars + 0;
-  uint64_t* kv_full = bars + 1;    // [2]
-  uint64_t* kv_empty = bars + 3;   // [2]
-  uint64_t* s_full = bars + 5;     // [2]
-  uint64_t* p_full = bars + 7;     // [2]
-  uint64_t* o_full = bars + 9;     // [2]
-  uint64_t* o_free = bars + 11;    // [2]
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 13);
-  int* s_nt = reinterpret_cast<int*>(bars + 14);  // tokens in this atom
+  uint64_t* k_full = bars + 1;             // [NS]
+  uint64_t* v_full = k_full + NS;          // [NS]
+  uint64_t* k_empty = v_full + NS;         // [NS]
+  uint64_t* v_empty = k_empty + NS;        // [NS]
+  uint64_t* s_full = v_empty + NS;         // [2]
+  uint64_t* p_full = s_full + 2;           // [2]
+  uint64_t* o_full = p_full + 2;           // [2]
+  uint64_t* o_free = o_full + 2;           // [2]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
+  int* s_nt = reinterpret_cast<int*>(o_free + 3);  // tokens in this atom
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t0 = p.atoms[blockIdx.x];
@@ -100,9 +106,13 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmKV);
     mbar_init(q_full, 1);
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&kv_full[i], 1);
-      mbar_init(&kv_empty[i], 1);
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], SM_THREADS);
       mbar_init(&o_full[i], 1);
@@ -142,21 +152,24 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const int* bt = p.block_table + static_cast<size_t>(seq) * p.max_blocks;
         const int sub = BN / p.block_size;  // cache blocks per 128-key page
         const int last_blk = (pos0 + nt - 1) / p.block_size;
+        int st = 0, ph = 0;
         for (int j = 0; j < n_blocks; ++j) {
-          const int st = j & 1;
-          mbar_wait(&kv_empty[st], ((j >> 1) & 1) ^ 1);
-          mbar_expect_tx(&kv_full[st], 2 * SMEM::TILE);
-          for (int s = 0; s < sub; ++s) {
-            // blocks past the sequence's extent are never unmasked, but their bytes must be finite: re-read a valid block
-            const int logical = min((pg0 + j) * sub + s, last_blk);
-            const int blk = bt[logical];
-            const int row_off = s * p.block_size * 128;
 #pragma unroll
-            for (int c = 0; c < NCH; ++c) {
-              tma_load_4d(&tmKV, &kv_full[st], smem + SMEM::K_OFF + st * SMEM::TILE + c * CHUNK_BYTES + row_off, c * 64, kvh, 0, blk * 2);
-              tma_load_4d(&tmKV, &kv_full[st], smem + SMEM::V_OFF + st * SMEM::TILE + c * CHUNK_BYTES + row_off, c * 64, kvh, 0, blk * 2 + 1);
+          for (int is_v = 0; is_v < 2; ++is_v) {
+            uint64_t* full = is_v ? &v_full[st] : &k_full[st];
+            mbar_wait(is_v ? &v_empty[st] : &k_empty[st], ph ^ 1);
+            mbar_expect_tx(full, SMEM::TILE);
+            uint8_t* tile = smem + (is_v ? SMEM::V_OFF : SMEM::K_OFF) + st * SMEM::TILE;
+            for (int s = 0; s < sub; ++s) {
+              // blocks past the sequence's extent are never unmasked, but their bytes must be finite: re-read a valid block
+              const int logical = min((pg0 + j) * sub + s, last_blk);
+              const int blk = bt[logical];
+              const int row_off = s * p.block_size * 128;
+#pragma unroll
+              for (int c = 0; c < NCH; ++c) tma_load_4d(&tmKV, full, tile + c * CHUNK_BYTES + row_off, c * 64, kvh, 0, blk * 2 + is_v);
             }
           }
+          if (++st == NS) { st = 0; ph ^= 1; }
         }
       }
     } else if (warp == 1) {
@@ -164,141 +177,175 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         constexpr uint32_t idesc_qk = umma_idesc(BM, BN, 1, 1, 0, 0);
         constexpr uint32_t idesc_pv = umma_idesc(BM, D, 1, 1, 0, 1);
         const uint32_t q_s = smem_u32(smem + SMEM::Q_OFF);
-        auto issue_qk = [&](int j) {
-          const int st = j & 1;
-          mbar_wait(&kv_full[st], (j >> 1) & 1);
+        // S / P / partial-O buffers alternate with the page parity; K and V tiles cycle through their NS-deep rings.
+        // The tensor pipe executes this thread's MMAs in issue order, so QK(j+1) cannot overwrite S buffer (j+1)&1 before
+        // PV(j-1), which reads P out of the same columns, has retired.
+        auto issue_qk = [&](int j, int st, int ph) {
+          const int b = j & 1;
+          mbar_wait(&k_full[st], ph);
           tc_fence_after();
           const uint32_t k_s = smem_u32(smem + SMEM::K_OFF + st * SMEM::TILE);
 #pragma unroll
           for (int kk = 0; kk < D / 16; ++kk) {
             const uint32_t off = (kk >> 2) * CHUNK_BYTES + (kk & 3) * 32;
-            umma_f16<1>(TM_S + st * 128, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_qk,
+            umma_f16<1>(TM_S + b * 128, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_qk,
                         kk != 0 ? 1u : 0u);
           }
-          umma_commit<1>(&s_full[st]);
+          umma_commit<1>(&s_full[b]);
+          umma_commit<1>(&k_empty[st]);
         };
-        auto issue_pv = [&](int j) {
-          const int st = j & 1;
-          mbar_wait(&p_full[st], (j >> 1) & 1);
-          if (j >= 2) mbar_wait(&o_free[st], ((j >> 1) - 1) & 1);
+        auto issue_pv = [&](int j, int st, int ph) {
+          const int b = j & 1;
+          mbar_wait(&v_full[st], ph);
+          mbar_wait(&p_full[b], (j >> 1) & 1);
+          if (j >= 2) mbar_wait(&o_free[b], ((j >> 1) - 1) & 1);
           tc_fence_after();
-          const uint32_t p_s = smem_u32(smem + SMEM::P_OFF + st * SMEM::P_BYTES);
           const uint32_t v_s = smem_u32(smem + SMEM::V_OFF + st * SMEM::TILE);
 #pragma unroll
-          for (int kk = 0; kk < BN / 16; ++kk) {
-            const uint32_t a_off = (kk >> 2) * CHUNK_BYTES + (kk & 3) * 32;
-            umma_f16<1>(TM_PV + st * 128, umma_smem_desc(p_s + a_off, 16, 1024),
+          for (int kk = 0; kk < BN / 16; ++kk)
+            // P of keys [16 kk, 16 kk + 16): the softmax half that owns them packed it into the first 32 columns of its 64
+            umma_f16_ts(TM_PV + b * 128, TM_S + b * 128 + (kk >> 2) * 64 + (kk & 3) * 8,
                         umma_smem_desc(v_s + kk * 2048, CHUNK_BYTES, 1024), idesc_pv, kk != 0 ? 1u : 0u);
-          }
-          umma_commit<1>(&o_full[st]);
-          umma_commit<1>(&kv_empty[st]);
+          umma_commit<1>(&o_full[b]);
+          umma_commit<1>(&v_empty[st]);
         };
         mbar_wait(q_full, 0);
-        issue_qk(0);
+        issue_qk(0, 0, 0);
+        int st = 0, ph = 0;  // ring position of page j
         for (int j = 0; j < n_blocks; ++j) {
-          if (j + 1 < n_blocks) issue_qk(j + 1);
-          issue_pv(j);
+          int st1 = st + 1, ph1 = ph;
+          if (st1 == NS) { st1 = 0; ph1 ^= 1; }
+          if (j + 1 < n_blocks) issue_qk(j + 1, st1, ph1);
+          issue_pv(j, st, ph);
+          st = st1; ph = ph1;
         }
       }
     } else {
-      const int q4 = warp & 3;
+      // 8 softmax warps: warp quarter q4 (the TMEM lanes a warp may touch) x column half.  Thread == (row, half): it owns keys
+      // [64 half, 64 half + 64) of the row's S and columns [D/2 half, D/2 half + D/2) of its O.  One warp per scheduler doing
+      // a whole row was latency-bound on its own instruction stream (~1500 dependent-ish instructions per page); two warps per
+      // scheduler with half the work each overlap each other's latencies.  The halves agree on the page maximum through shared
+      // memory (rounded up to bf16: any common reference >= the true maximum is exact for the result); sums merge at the end.
+      const int q4 = warp & 3, half = (warp - 2) >> 2;
       const int row = q4 * 32 + lane;
       const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
       const int ti = row / p.group, g = row - ti * p.group;
       const bool live = ti < nt;
-      const int limit = live ? pos0 + ti + 1 : 1;  // keys [0, limit) are visible; dead rows keep one key so nothing is NaN
-      float o_acc[D];
+      // keys [0, limit) are visible.  Dead rows (past the atom) see everything: their operands are finite (TMA zero fill /
+      // other tokens' rows, zero-initialised cache) and nothing of theirs is stored
+      const int limit = live ? pos0 + ti + 1 : 0x3fffffff;
+      constexpr int DH = D / 2;
+      float o_acc[DH];
 #pragma unroll
-      for (int i = 0; i < D; ++i) o_acc[i] = 0.f;
+      for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
       float m_run = -INFINITY, l_run = 0.f;
+      __nv_bfloat16* xmax = reinterpret_cast<__nv_bfloat16*>(smem + SMEM::X_OFF);  // [page parity][half][row]
+      const uint32_t pair_bar = 1 + q4;
 
+      // O (in the scale of the previous page's maximum) * alpha + partial PV of page j
       auto accumulate_pv = [&](int j, float alpha) {
-        const int st = j & 1;
-        mbar_wait(&o_full[st], (j >> 1) & 1);
+        const int b = j & 1;
+        mbar_wait(&o_full[b], (j >> 1) & 1);
         tc_fence_after();
 #pragma unroll
-        for (int c = 0; c < D / 32; ++c) {
+        for (int c = 0; c < DH / 32; ++c) {
           uint32_t v[32];
-          tmem_ld_32x32(TM_PV + st * 128 + c * 32 + lane_off, v);
+          tmem_ld_32x32(TM_PV + b * 128 + half * DH + c * 32 + lane_off, v);
           tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = (o_acc[c * 32 + i] + __uint_as_float(v[i])) * alpha;
+          for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = fmaf(o_acc[c * 32 + i], alpha, __uint_as_float(v[i]));
         }
         tc_fence_before();
-        mbar_arrive(&o_free[st]);
+        mbar_arrive(&o_free[b]);
       };
 
       float alpha_prev = 1.f;
       for (int j = 0; j < n_blocks; ++j) {
-        const int st = j & 1;
-        mbar_wait(&s_full[st], (j >> 1) & 1);
+        const int b = j & 1;
+        mbar_wait(&s_full[b], (j >> 1) & 1);
         tc_fence_after();
-        const int key0 = (pg0 + j) * BN;
-        const int visible = limit - key0;  // columns [0, visible) of this page count; may be <= 0 or >= 128
-        // four independent max / sum chains: a single running value would serialise 128 dependent operations per pass
+        const int visible = limit - ((pg0 + j) * BN + half * 64);  // of this thread's 64 keys, [0, visible) count
+        const bool all_visible = __all_sync(0xffffffffu, visible >= 64);  // every page but the diagonal one(s)
+        const uint32_t s_addr = TM_S + b * 128 + half * 64 + lane_off;
+        // pass 1: maximum of the thread's 64 scores (four independent chains)
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t sv[32];
-          tmem_ld_32x32(TM_S + st * 128 + c * 32 + lane_off, sv);
+          tmem_ld_32x32(s_addr + c * 32, sv);
           tmem_ld_wait();
+          if (all_visible) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            float v = __uint_as_float(sv[i]);
-            if (c * 32 + i >= visible) v = -INFINITY;
-            mx[i & 3] = fmaxf(mx[i & 3], v);
+            for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sv[i]));
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], c * 32 + i >= visible ? -INFINITY : __uint_as_float(sv[i]));
           }
         }
-        const float m_blk = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+        const __nv_bfloat16 mine = __float2bfloat16_ru(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])));
+        xmax[(b * 2 + half) * 128 + row] = mine;
+        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+        const float m_blk = fmaxf(__bfloat162float(mine), __bfloat162float(xmax[(b * 2 + (half ^ 1)) * 128 + row]));
         // a page with no visible key for this row leaves the running max alone (and -inf - -inf is never formed)
         const float m_new = fmaxf(m_run, m_blk * p.scale_log2);
         const float m_use = m_new == -INFINITY ? 0.f : m_new;
         const float alpha = m_run == -INFINITY ? 0.f : exp2f(m_run - m_use);
         float ls[4] = {0.f, 0.f, 0.f, 0.f};
-        uint8_t* pbuf = smem + SMEM::P_OFF + st * SMEM::P_BYTES;
-        const int sw = row & 7;
+        // pass 2: P chunk c (32 keys -> 16 packed columns) goes to columns [16 c, 16 c + 16) of the thread's own half of the
+        // S buffer: always columns it has already consumed (chunk 0) or holds in registers (chunk c)
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint32_t sv[32];
-          tmem_ld_32x32(TM_S + st * 128 + c * 32 + lane_off, sv);
+          tmem_ld_32x32(s_addr + c * 32, sv);
           tmem_ld_wait();
-          uint8_t* rowp = pbuf + (c >> 1) * CHUNK_BYTES + row * 128;
+          uint32_t pk[16];
+          if (all_visible) {
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            float e[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const float v = fmaf(__uint_as_float(sv[u * 8 + i]), p.scale_log2, -m_use);
-              e[i] = (c * 32 + u * 8 + i >= visible) ? 0.f : ex2_fast(v);
-              ls[i & 3] += e[i];
+            for (int i = 0; i < 16; ++i) {
+              const float e0 = ex2_fast(fmaf(__uint_as_float(sv[2 * i]), p.scale_log2, -m_use));
+              const float e1 = ex2_fast(fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2, -m_use));
+              ls[i & 1] += e0;
+              ls[2 + (i & 1)] += e1;
+              pk[i] = pack_bf16x2(e0, e1);
             }
-            uint4 val;
-            val.x = pack_bf16x2(e[0], e[1]);
-            val.y = pack_bf16x2(e[2], e[3]);
-            val.z = pack_bf16x2(e[4], e[5]);
-            val.w = pack_bf16x2(e[6], e[7]);
-            const int unit = (c & 1) * 4 + u;
-            *reinterpret_cast<uint4*>(rowp + ((unit ^ sw) << 4)) = val;
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+              const float v0 = fmaf(__uint_as_float(sv[2 * i]), p.scale_log2, -m_use);
+              const float v1 = fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2, -m_use);
+              const float e0 = (c * 32 + 2 * i >= visible) ? 0.f : ex2_fast(v0);
+              const float e1 = (c * 32 + 2 * i + 1 >= visible) ? 0.f : ex2_fast(v1);
+              ls[i & 1] += e0;
+              ls[2 + (i & 1)] += e1;
+              pk[i] = pack_bf16x2(e0, e1);
+            }
           }
+          tmem_st_32x16(s_addr + c * 16, pk);
         }
         l_run = l_run * alpha + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
         m_run = m_new;
-        fence_proxy_async_smem();
+        tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(&p_full[st]);
-        if (j > 0) accumulate_pv(j - 1, alpha);
+        mbar_arrive(&p_full[b]);
+        if (j > 0) accumulate_pv(j - 1, alpha_prev);
         alpha_prev = alpha;
       }
-      (void)alpha_prev;
-      accumulate_pv(n_blocks - 1, 1.f);
+      accumulate_pv(n_blocks - 1, alpha_prev);
+
+      // the row's sum = both halves' sums (same sequence of maxima): exchange through the (now idle) max buffer
+      float* xl = reinterpret_cast<float*>(smem + SMEM::X_OFF);  // [half][row]
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      xl[half * 128 + row] = l_run;
+      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
+      l_run += xl[(half ^ 1) * 128 + row];
 
       if (live) {
         const int t = t0 + ti, head = kvh * p.group + g;
         if (!partial) {
           const float inv_l = 1.f / l_run;
-          __nv_bfloat16* dst = p.out + (static_cast<size_t>(t) * p.hq + head) * D;
+          __nv_bfloat16* dst = p.out + (static_cast<size_t>(t) * p.hq + head) * D + half * DH;
 #pragma unroll
-          for (int u = 0; u < D / 8; ++u) {
+          for (int u = 0; u < DH / 8; ++u) {
             uint4 val;
             const float* o = &o_acc[u * 8];
             val.x = pack_bf16x2(o[0] * inv_l, o[1] * inv_l);
@@ -309,16 +356,18 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           }
         } else {
           const size_t slot = (static_cast<size_t>(t) * p.hq + head) * p.n_splits + split;
-          float* dst = p.part_o + slot * D;
+          float* dst = p.part_o + slot * D + half * DH;
 #pragma unroll
-          for (int u = 0; u < D / 4; ++u)
+          for (int u = 0; u < DH / 4; ++u)
             *reinterpret_cast<float4*>(dst + u * 4) = make_float4(o_acc[u * 4], o_acc[u * 4 + 1], o_acc[u * 4 + 2], o_acc[u * 4 + 3]);
-          p.part_ml[slot * 2] = m_run;
-          p.part_ml[slot * 2 + 1] = l_run;
+          if (half == 0) {
+            p.part_ml[slot * 2] = m_run;
+            p.part_ml[slot * 2 + 1] = l_run;
+          }
         }
       }
     }
-  } else if (partial && warp >= 2) {
+  } else if (partial && warp >= 2 && warp < 6) {
     // this split has no pages (short context): publish an empty partial for every live row
     const int row = (warp & 3) * 32 + lane;
     const int ti = row / p.group, g = row - ti * p.group;

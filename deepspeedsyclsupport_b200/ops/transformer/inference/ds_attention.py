@@ -3,7 +3,11 @@ DeepSpeedSelfAttention over csrc/transformer/inference `qkv_gemm` / `softmax_con
 
 Parameters keep the reference names (attn_qkvw / attn_qkvb / attn_ow / attn_ob) but are stored [out, in] -- the native layout of
 the tcgen05 GEMM (`transposed_mode` of the reference).  QKV is one fused projection; GQA through `config.num_kv`; rotary
-(`rotary_dim`, rotate_half or rotate_every_two) is applied to the new tokens before they are appended to the cache."""
+(`rotary_dim`, rotate_half or rotate_every_two) is applied to the new tokens before they are appended to the cache.
+
+Plain causal steps (bf16, head size 64 / 128, no padding mask, no ALiBi) run on the layer's KV arena (kv_arena.py): rotary+append
+kernel, then the tcgen05 paged flash kernel for prompt and decode alike.  Masked / biased steps keep a dense cache and the
+general masked-softmax formulation."""
 import math
 
 import torch
@@ -11,6 +15,8 @@ from torch import nn
 
 from ....accelerator import get_accelerator
 from ... import gemm as G
+from .kv_arena import KVArena
+from .kv_arena import eligible as arena_eligible
 
 
 def _linear(x, w, b):
@@ -61,21 +67,58 @@ class DeepSpeedSelfAttention(nn.Module):
         self.scale = 1.0 / math.sqrt(self.head_dim) if config.scale_attention else 1.0
         if config.scale_attn_by_inverse_layer_idx:
             self.scale /= float(self.layer_id + 1)
-        self.k_cache = self.v_cache = None  # [B, heads_kv, T, D]
+        self.k_cache = self.v_cache = None  # [B, heads_kv, T, D] -- masked / biased path only
+        self.arena = KVArena(min_tokens=max(int(getattr(config, "max_out_tokens", 1024) or 1024), 128))
+        self._inv_freq = None
 
     def reset_cache(self):
         self.k_cache = self.v_cache = None
+        self.arena.reset()
+
+    def _forward_arena(self, qkv, B, S, get_present):
+        """Plain causal attention on the tensor-core kernels: rotary + append into the layer's KV arena, paged flash attention."""
+        cfg = self.config
+        inv_freq, rot = None, 0
+        if cfg.rotary_dim > 0:
+            if cfg.rotate_half:
+                if self._inv_freq is None or self._inv_freq.device != qkv.device:
+                    d = cfg.rotary_dim
+                    self._inv_freq = 1.0 / (cfg.rope_theta**(torch.arange(0, d, 2, device=qkv.device, dtype=torch.float32) / d))
+                inv_freq, rot = self._inv_freq, cfg.rotary_dim
+            else:  # rotate_every_two pairing (GPT-J): rotated here, the kernel only appends
+                pos = torch.arange(self.arena.length, self.arena.length + S, device=qkv.device)
+                x = qkv.view(B, S, self.heads + 2 * self.kv_heads, self.head_dim)
+                n = self.heads + self.kv_heads
+                x[:, :, :n] = apply_rotary(x[:, :, :n], pos, cfg.rotary_dim, cfg.rope_theta, False)
+        ctx = self.arena.attend(qkv, self.heads, self.kv_heads, self.head_dim, self.scale, inv_freq, rot)
+        out = _linear(ctx, self.attn_ow, None)
+        if self.mp_group is not None and cfg.mp_size > 1:
+            from .... import comm as dist
+            dist.all_reduce(out, group=self.mp_group)
+        if self.attn_ob is not None:
+            out = out + self.attn_ob
+        if get_present:
+            k, v = self.arena.keys_values()
+        else:
+            x = qkv.view(B, S, self.heads + 2 * self.kv_heads, self.head_dim)
+            k, v = x[:, :, self.heads:self.heads + self.kv_heads].transpose(1, 2), x[:, :, self.heads + self.kv_heads:].transpose(1, 2)
+        return out, k, v
 
     def forward(self, input, input_mask=None, head_mask=None, layer_past=None, get_present=False, encoder_hidden_states=None,
                 encoder_attention_mask=None, output_attentions=False, norm_w=None, norm_b=None, alibi=None):
         """input: [B, S, hidden] already normalised by the caller (pre-LN) -- returns (attn_out [B,S,hidden], key, value)."""
         B, S, _ = input.shape
         qkv = _linear(input, self.attn_qkvw, self.attn_qkvb)
+        if layer_past is None and S > 1:
+            self.reset_cache()  # a new prompt
+        if self.k_cache is None and arena_eligible(qkv, self.head_dim, self.heads, self.kv_heads, self.config, input_mask, alibi, layer_past):
+            return self._forward_arena(qkv, B, S, get_present)
+        if self.k_cache is None and self.arena.length > 0:  # a decode step the arena kernels cannot take: continue densely
+            self.k_cache, self.v_cache = (t.contiguous() for t in self.arena.keys_values())
+            self.arena.reset()
         q, k, v = qkv.view(B, S, self.heads + 2 * self.kv_heads, self.head_dim).split([self.heads, self.kv_heads, self.kv_heads], 2)
         if layer_past is not None:
             self.k_cache, self.v_cache = layer_past
-        elif S > 1:
-            self.reset_cache()  # a new prompt
         past = 0 if self.k_cache is None else self.k_cache.shape[2]
         cfg = self.config
         if cfg.rotary_dim > 0:

@@ -961,3 +961,31 @@ def test_gemm_mxfp8_hardware_block_scaled(shape):
     assert (c - ref).norm() <= 0.06 * ref.norm()
     y = linear_mxfp8(a, bq, sfb).float()
     assert (y - ref).norm() <= 0.06 * ref.norm()
+
+
+@pytest.mark.parametrize("rotate_half,kv_heads,head_dim", [(True, 2, 64), (False, 8, 64), (True, 4, 128)])
+def test_v1_attention_kv_arena_matches_dense_path(monkeypatch, rotate_half, kv_heads, head_dim):
+    """Kernel-injection attention: prompt + decode steps on the KV arena (rotary/append kernel + tcgen05 paged flash) equal the
+    dense masked-softmax path of the same module, including growth of the arena past its initial size."""
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    from deepspeedsyclsupport_b200.ops.transformer.inference.ds_attention import DeepSpeedSelfAttention
+    torch.manual_seed(0)
+    heads = 8
+    H = heads * head_dim
+    cfg = DeepSpeedInferenceConfig(hidden_size=H, heads=heads, num_kv=kv_heads if kv_heads != heads else -1, dtype=torch.bfloat16,
+                                   rotary_dim=head_dim // 2, rotate_half=rotate_half, max_out_tokens=128, triangular_masking=True)
+    a, b = DeepSpeedSelfAttention(cfg), DeepSpeedSelfAttention(cfg)
+    for name in ("attn_qkvw", "attn_qkvb", "attn_ow", "attn_ob"):
+        w = torch.randn_like(getattr(a, name).float()) * (0.05 if name.endswith("w") else 0.1)
+        getattr(a, name).data.copy_(w)
+        getattr(b, name).data.copy_(w)
+    steps = [torch.randn(2, 250, H, device="cuda").bfloat16()] + [torch.randn(2, 1, H, device="cuda").bfloat16() for _ in range(8)]
+    outs = {}
+    for tag, mod, flag in (("arena", a, "1"), ("dense", b, "0")):
+        monkeypatch.setenv("DSB200_V1_ARENA", flag)
+        outs[tag] = [mod(x.clone(), get_present=True) for x in steps]
+    assert a.arena.length == 258 and a.arena.per_seq == 4 and a.k_cache is None and b.arena.length == 0  # grew from 2 blocks
+    for (oa, ka, va), (ob, kb, vb) in zip(outs["arena"], outs["dense"]):
+        assert oa.shape == ob.shape and ka.shape == kb.shape
+        assert (oa.float() - ob.float()).abs().max() < 0.03 * ob.float().abs().max() + 1e-3
+        assert (ka.float() - kb.float()).abs().max() < 0.07 and (va.float() - vb.float()).abs().max() < 1e-6  # rotated k: a bf16 ulp or two

@@ -1,6 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_kernels_gpu.py -q -x -k "mxfp8 or transformer_layer_bf16" > gpurun_out/mx_tests.log 2>&1
-echo "mx tests rc=$?"; grep -E "passed|failed|Error|error|assert|rel" gpurun_out/mx_tests.log | cut -c1-400 | head -20
-timeout 300 python tools/gemm_fp8_bench.py --out gpurun_out/gemm_fp8_bench_r2.json > gpurun_out/gemm_fp8_bench.log 2>&1
-echo "fp8 bench rc=$?"; cut -c1-700 gpurun_out/gemm_fp8_bench.log
+timeout 300 python -m pytest tests/test_kernels_gpu.py -q -x -k "v1_attention_kv_arena" > gpurun_out/arena_tests.log 2>&1
+echo "arena tests rc=$?"; tail -3 gpurun_out/arena_tests.log | cut -c1-300
+for w in decode prefill; do
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:paged_flash_kernel -c 1 -f -o gpurun_out/ncu_paged_${w}_v3 python tools/paged_flash_bench.py --profile $w > gpurun_out/ncu_paged_${w}_v3.log 2>&1
+echo "ncu $w rc=$?"
+done
