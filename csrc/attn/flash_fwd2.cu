@@ -38,54 +38,6 @@ __device__ __forceinline__ void reg_inc() {
 }
 
 
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// ---- packed fp32x2 arithmetic (sm_100: FFMA2 / FADD2 process two floats per lane per instruction)
-__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
-  uint64_t d;
-  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
-  uint64_t d;
-  asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-__device__ __forceinline__ uint64_t exp2_mufu2(uint64_t x2) {
-  float a, b;
-  unpack2(x2, a, b);
-  return pack2(ex2_approx(a), ex2_approx(b));
-}
-// exp2 on the FMA pipe: n = round(x) via the 1.5 * 2^23 trick, f = x - n in [-0.5, 0.5], 2^f by a degree-3 minimax
-// polynomial (max relative error 7.5e-5, far below the bf16 rounding of P), exponent added as an integer.
-__device__ __forceinline__ uint64_t exp2_poly2(uint64_t x2) {
-  float a, b;
-  unpack2(x2, a, b);
-  x2 = pack2(fmaxf(a, -125.f), fmaxf(b, -125.f));
-  const uint64_t magic = pack2(12582912.f, 12582912.f), neg_magic = pack2(-12582912.f, -12582912.f);
-  const uint64_t xf = add2(x2, magic);
-  const uint64_t n = add2(xf, neg_magic);
-  const uint64_t f = fma2(n, pack2(-1.f, -1.f), x2);
-  uint64_t pl = fma2(f, pack2(0.05517164617776871f, 0.05517164617776871f), pack2(0.2426111251115799f, 0.2426111251115799f));
-  pl = fma2(pl, f, pack2(0.6932609677314758f, 0.6932609677314758f));
-  pl = fma2(pl, f, pack2(0.9999280571937561f, 0.9999280571937561f));
-  float p0, p1, x0, x1;
-  unpack2(pl, p0, p1);
-  unpack2(xf, x0, x1);
-  p0 = __int_as_float(__float_as_int(p0) + (__float_as_int(x0) << 23));
-  p1 = __int_as_float(__float_as_int(p1) + (__float_as_int(x1) << 23));
-  return pack2(p0, p1);
-}
 constexpr int POLY_OF_8 = 3;  // pairs out of every 8 that use exp2_poly2
 
 template <int D>

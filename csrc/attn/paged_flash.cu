@@ -13,8 +13,9 @@
 //                           V tile when its PV has, so two to three pages of loads are in flight per SM (decode is a pure
 //                           KV-bandwidth problem: with one page in flight the kernel sat at 35 % of HBM)
 //   warp 1   MMA issuer   : S = Q K^T (128 x 128 x D, SS) into TMEM, PV = P V (TS: P read from TMEM, V MN-major from smem) into TMEM
-//   warps 2-5 softmax     : thread == row: S row from TMEM, per-row causal limit (position + 1), online softmax in exp2 domain,
-//                           P (bf16, two per column) stored back over the first 64 columns of its S buffer, O kept in registers
+//   warps 2-17 softmax    : thread == (row, quarter of the columns): S from TMEM, per-row causal limit (position + 1), online
+//                           softmax in exp2 domain, P (bf16, two per column) stored back over the thread's own S columns, its
+//                           quarter of O kept in registers
 // Long contexts at small batch do not fill 148 SMs with one CTA per (atom, kv head): with n_splits > 1 every CTA handles a
 // slice of the pages and writes an unnormalised partial (O, running max, running sum) to scratch; a second kernel merges.
 // Reference counterpart: inference/v2/kernels/ragged_ops/blocked_flash/blocked_flash.cpp:21-101 (closed flash_attn_by_atoms)
@@ -27,8 +28,8 @@ namespace paged {
 
 constexpr int BM = 128;
 constexpr int BN = 128;
-constexpr int NUM_THREADS = 320;  // TMA warp, MMA warp, 8 softmax warps
-constexpr int SM_THREADS = 256;
+constexpr int NUM_THREADS = 576;  // TMA warp, MMA warp, 16 softmax warps
+constexpr int SM_THREADS = 512;
 constexpr int CHUNK_BYTES = 128 * 128;  // one [128 rows x 64 bf16] swizzled chunk
 
 template <int D>
@@ -40,7 +41,7 @@ struct Smem {
   static constexpr int K_OFF = Q_OFF + TILE;
   static constexpr int V_OFF = K_OFF + STAGES * TILE;
   static constexpr int BAR_OFF = V_OFF + STAGES * TILE;
-  static constexpr int X_OFF = BAR_OFF + 384;  // 1 KB: page maxima exchanged between the two column halves of a row
+  static constexpr int X_OFF = BAR_OFF + 400;  // 1 KB: page maxima exchanged between the four column parts of a row
   static constexpr int TOTAL = X_OFF + 1024 + 1024;
 };
 
@@ -61,7 +62,11 @@ struct Params {
   float* part_ml;          // [T][hq][n_splits][2]
   int T, hq, hkv, group, nt_tile, block_size, max_blocks, n_splits;
   float scale_log2;
+  long long* trace;  // diagnostics only (DSB200_PF_TRACE=1): clock64 stamps of the first CTA with >= 8 pages, [page][8 events]
 };
+// events: 0 K landed (MMA thread)  1 P ready seen by the MMA thread  2 S ready seen by softmax  3 P published  4 partial O read
+#define DSB_PF_TRACE(ev, j) \
+  if (tracing && (j) < 64) p.trace[8 + (j) * 8 + (ev)] = clock64();
 
 // ---------------------------------------------------------------- atom discovery (one thread per token)
 __global__ void find_atoms_kernel(const int* __restrict__ tok_seq, const int* __restrict__ tok_pos, int T, int nt_tile,
@@ -92,8 +97,8 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* v_empty = k_empty + NS;        // [NS]
   uint64_t* s_full = v_empty + NS;         // [2]
   uint64_t* p_full = s_full + 2;           // [2]
-  uint64_t* o_full = p_full + 2;           // [2]
-  uint64_t* o_free = o_full + 2;           // [2]
+  uint64_t* o_full = p_full + 2;           // [0] only: phase j completes when PV(j) has retired
+  uint64_t* o_free = o_full + 2;           // [0]: "Q is in TMEM" (softmax warps -> MMA thread); [1] unused
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_free + 2);
   int* s_nt = reinterpret_cast<int*>(o_free + 3);  // tokens in this atom
 
@@ -116,13 +121,25 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       mbar_init(&s_full[i], 1);
       mbar_init(&p_full[i], SM_THREADS);
       mbar_init(&o_full[i], 1);
-      mbar_init(&o_free[i], 1 * SM_THREADS);
+      mbar_init(&o_free[i], 128 * (D / 32));
     }
     fence_barrier_init();
-    // length of the atom: consecutive tokens of the same sequence, up to the next multiple of nt_tile
-    int nt = 1;
-    while (nt < p.nt_tile && t0 + nt < p.T && p.tok_seq[t0 + nt] == seq && p.tok_pos[t0 + nt] == pos0 + nt && ((pos0 + nt) % p.nt_tile) != 0) ++nt;
-    *s_nt = nt;
+  }
+  if (warp == 2) {
+    // length of the atom: consecutive tokens of the same sequence, up to the next multiple of nt_tile.  Lane i tests token
+    // t0 + i (one round of loads for 32 candidates instead of a serial chain of dependent global loads)
+    int nt = p.nt_tile;
+    for (int base = 0; base < p.nt_tile; base += 32) {
+      const int i = base + lane;
+      const bool ok = i == 0 || (i < p.nt_tile && t0 + i < p.T && p.tok_seq[t0 + i] == seq && p.tok_pos[t0 + i] == pos0 + i &&
+                                 ((pos0 + i) % p.nt_tile) != 0);
+      const uint32_t bad = __ballot_sync(0xffffffffu, !ok);
+      if (bad) {
+        nt = base + __ffs(bad) - 1;
+        break;
+      }
+    }
+    if (lane == 0) *s_nt = nt;
   }
   if (warp == 1) {
     tmem_alloc<1>(tmem_ptr, 512);
@@ -133,7 +150,8 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
   const uint32_t TM_S = tmem_base;
-  const uint32_t TM_PV = tmem_base + 256;
+  const uint32_t TM_O = tmem_base + 256;  // O accumulates here across the pages of the CTA
+  const uint32_t TM_Q = tmem_base + 384;  // Q as the A operand of QK^T: two bf16 per column, D/2 columns
   const int nt = *s_nt;
   // pages visible to the last token of the atom, and this CTA's slice of them
   const int n_pages = (pos0 + nt + BN - 1) / BN;
@@ -142,6 +160,14 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   const int pg1 = min(n_pages, pg0 + per_split);
   const int n_blocks = max(0, pg1 - pg0);
   const bool partial = p.n_splits > 1;
+  bool tracing = false;
+  if (p.trace != nullptr) {  // one CTA with enough pages claims the trace buffer
+    int* claim = reinterpret_cast<int*>(bars + 48);
+    if (threadIdx.x == 0) *claim = (n_blocks >= 8 && atomicCAS(reinterpret_cast<int*>(p.trace), 0, 1) == 0) ? 1 : 0;
+    __syncthreads();
+    tracing = *claim != 0;
+    if (tracing && threadIdx.x == 0) p.trace[1] = clock64();
+  }
 
   if (n_blocks > 0) {
     if (warp == 0) {
@@ -173,60 +199,70 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         }
       }
     } else if (warp == 1) {
-      if (lane == 0) {
-        constexpr uint32_t idesc_qk = umma_idesc(BM, BN, 1, 1, 0, 0);
-        constexpr uint32_t idesc_pv = umma_idesc(BM, D, 1, 1, 0, 1);
-        const uint32_t q_s = smem_u32(smem + SMEM::Q_OFF);
-        // S / P / partial-O buffers alternate with the page parity; K and V tiles cycle through their NS-deep rings.
-        // The tensor pipe executes this thread's MMAs in issue order, so QK(j+1) cannot overwrite S buffer (j+1)&1 before
-        // PV(j-1), which reads P out of the same columns, has retired.
-        auto issue_qk = [&](int j, int st, int ph) {
-          const int b = j & 1;
-          mbar_wait(&k_full[st], ph);
-          tc_fence_after();
-          const uint32_t k_s = smem_u32(smem + SMEM::K_OFF + st * SMEM::TILE);
+      // The whole warp stays converged and one elected lane issues: inside an `if (lane == 0)` region every descriptor and
+      // TMEM address is a per-thread value that the compiler moves to the uniform registers with an elect / broadcast loop
+      // per instruction, ~81 cycles per tcgen05.mma against a 64-cycle floor for 128 x 128 x 16 (tools/microbench/mma_rate.cu).
+      // Descriptors are built once; a k-step or a ring stage is a 32-bit add to the low word.
+      const bool leader = elect_one();
+      constexpr uint32_t idesc_qk = umma_idesc(BM, BN, 1, 1, 0, 0);
+      constexpr uint32_t idesc_pv = umma_idesc(BM, D, 1, 1, 0, 1);
+      const uint32_t tm_s = __shfl_sync(0xffffffffu, TM_S, 0), tm_o = tm_s + 256, tm_q = tm_s + 384;
+      const uint64_t k_desc0 = umma_smem_desc(smem_u32(smem + SMEM::K_OFF), 16, 1024);
+      const uint64_t v_desc0 = umma_smem_desc(smem_u32(smem + SMEM::V_OFF), CHUNK_BYTES, 1024);
+      // S / P buffers alternate with the page parity; K and V tiles cycle through their NS-deep rings.  The tensor pipe
+      // executes this warp's MMAs in issue order, so QK(j+1) cannot overwrite S buffer (j+1)&1 before PV(j-1), which reads P
+      // out of the same columns, has retired.
+      auto issue_qk = [&](int j, int st, int ph) {
+        const int b = j & 1;
+        mbar_wait_lean(&k_full[st], ph);
+        if (leader) { DSB_PF_TRACE(0, j) }
+        tc_fence_after();
+        if (leader) {
+          const uint64_t kd = k_desc0 + static_cast<uint32_t>((st * SMEM::TILE) >> 4);
 #pragma unroll
-          for (int kk = 0; kk < D / 16; ++kk) {
-            const uint32_t off = (kk >> 2) * CHUNK_BYTES + (kk & 3) * 32;
-            umma_f16<1>(TM_S + b * 128, umma_smem_desc(q_s + off, 16, 1024), umma_smem_desc(k_s + off, 16, 1024), idesc_qk,
+          for (int kk = 0; kk < D / 16; ++kk)
+            // A = Q from TMEM (stationary for the CTA): only the K tile crosses the shared-memory port
+            umma_f16_ts(tm_s + b * 128, tm_q + kk * 8, kd + static_cast<uint32_t>(((kk >> 2) * CHUNK_BYTES + (kk & 3) * 32) >> 4), idesc_qk,
                         kk != 0 ? 1u : 0u);
-          }
           umma_commit<1>(&s_full[b]);
           umma_commit<1>(&k_empty[st]);
-        };
-        auto issue_pv = [&](int j, int st, int ph) {
-          const int b = j & 1;
-          mbar_wait(&v_full[st], ph);
-          mbar_wait(&p_full[b], (j >> 1) & 1);
-          if (j >= 2) mbar_wait(&o_free[b], ((j >> 1) - 1) & 1);
-          tc_fence_after();
-          const uint32_t v_s = smem_u32(smem + SMEM::V_OFF + st * SMEM::TILE);
+        }
+      };
+      auto issue_pv = [&](int j, int st, int ph) {
+        const int b = j & 1;
+        mbar_wait_lean(&v_full[st], ph);
+        mbar_wait_lean(&p_full[b], (j >> 1) & 1);
+        if (leader) { DSB_PF_TRACE(1, j) }
+        tc_fence_after();
+        if (leader) {
+          const uint64_t vd = v_desc0 + static_cast<uint32_t>((st * SMEM::TILE) >> 4);
 #pragma unroll
           for (int kk = 0; kk < BN / 16; ++kk)
-            // P of keys [16 kk, 16 kk + 16): the softmax half that owns them packed it into the first 32 columns of its 64
-            umma_f16_ts(TM_PV + b * 128, TM_S + b * 128 + (kk >> 2) * 64 + (kk & 3) * 8,
-                        umma_smem_desc(v_s + kk * 2048, CHUNK_BYTES, 1024), idesc_pv, kk != 0 ? 1u : 0u);
-          umma_commit<1>(&o_full[b]);
+            // P of keys [16 kk, 16 kk + 16): the softmax part that owns them packed it into the first 16 columns of its 32
+            umma_f16_ts(tm_o, tm_s + b * 128 + (kk >> 1) * 32 + (kk & 1) * 8, vd + static_cast<uint32_t>((kk * 2048) >> 4), idesc_pv,
+                        (j | kk) != 0 ? 1u : 0u);
+          umma_commit<1>(&o_full[0]);  // phase j completes when PV(j) has retired
           umma_commit<1>(&v_empty[st]);
-        };
-        mbar_wait(q_full, 0);
-        issue_qk(0, 0, 0);
-        int st = 0, ph = 0;  // ring position of page j
-        for (int j = 0; j < n_blocks; ++j) {
-          int st1 = st + 1, ph1 = ph;
-          if (st1 == NS) { st1 = 0; ph1 ^= 1; }
-          if (j + 1 < n_blocks) issue_qk(j + 1, st1, ph1);
-          issue_pv(j, st, ph);
-          st = st1; ph = ph1;
         }
+      };
+      mbar_wait_lean(&o_free[0], 0);  // Q copied into TMEM
+      tc_fence_after();
+      issue_qk(0, 0, 0);
+      int st = 0, ph = 0;  // ring position of page j
+      for (int j = 0; j < n_blocks; ++j) {
+        int st1 = st + 1, ph1 = ph;
+        if (st1 == NS) { st1 = 0; ph1 ^= 1; }
+        if (j + 1 < n_blocks) issue_qk(j + 1, st1, ph1);
+        issue_pv(j, st, ph);
+        st = st1; ph = ph1;
       }
     } else {
-      // 8 softmax warps: warp quarter q4 (the TMEM lanes a warp may touch) x column half.  Thread == (row, half): it owns keys
-      // [64 half, 64 half + 64) of the row's S and columns [D/2 half, D/2 half + D/2) of its O.  One warp per scheduler doing
-      // a whole row was latency-bound on its own instruction stream (~1500 dependent-ish instructions per page); two warps per
-      // scheduler with half the work each overlap each other's latencies.  The halves agree on the page maximum through shared
+      // 16 softmax warps: warp quarter q4 (the TMEM lanes a warp may touch) x column quarter `part`.  Thread == (row, part): it
+      // owns keys [32 part, 32 part + 32) of the row's S and columns [D/4 part, D/4 part + D/4) of its O.  Four warps per
+      // scheduler, each with a quarter of a row, hide one another's TMEM / MUFU / dependent-issue latencies (one warp per
+      // scheduler owning whole rows ran at 0.3 IPC and ~2 us a page).  The four parts agree on the page maximum through shared
       // memory (rounded up to bf16: any common reference >= the true maximum is exact for the result); sums merge at the end.
-      const int q4 = warp & 3, half = (warp - 2) >> 2;
+      const int q4 = warp & 3, part = (warp - 2) >> 2;
       const int row = q4 * 32 + lane;
       const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
       const int ti = row / p.group, g = row - ti * p.group;
@@ -234,118 +270,131 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       // keys [0, limit) are visible.  Dead rows (past the atom) see everything: their operands are finite (TMA zero fill /
       // other tokens' rows, zero-initialised cache) and nothing of theirs is stored
       const int limit = live ? pos0 + ti + 1 : 0x3fffffff;
-      constexpr int DH = D / 2;
-      float o_acc[DH];
-#pragma unroll
-      for (int i = 0; i < DH; ++i) o_acc[i] = 0.f;
+      constexpr int DQ = D / 4;
+      // m_run is the reference maximum P and O are expressed in.  It follows the true running maximum lazily: only when that
+      // has grown by more than 2^8 is O (in TMEM, accumulated by the tensor core) read, rescaled and written back.  Reading
+      // the partial O of every page back into registers cost as much TMEM bandwidth as reading S (64 B/clk/SM, the limiter).
       float m_run = -INFINITY, l_run = 0.f;
-      __nv_bfloat16* xmax = reinterpret_cast<__nv_bfloat16*>(smem + SMEM::X_OFF);  // [page parity][half][row]
-      const uint32_t pair_bar = 1 + q4;
+      __nv_bfloat16* xmax = reinterpret_cast<__nv_bfloat16*>(smem + SMEM::X_OFF);  // [part][row]
+      const uint32_t bar_a = 1 + q4, bar_b = 5 + q4;  // the 4 warps (128 threads) that share the rows of this quarter
+      const uint32_t o_addr = TM_O + part * DQ + lane_off;
+      const bool warp_live = q4 * 32 < nt * p.group;  // rows are packed from 0: a warp past them has nothing to compute
 
-      // O (in the scale of the previous page's maximum) * alpha + partial PV of page j
-      auto accumulate_pv = [&](int j, float alpha) {
-        const int b = j & 1;
-        mbar_wait(&o_full[b], (j >> 1) & 1);
-        tc_fence_after();
+      // Q: swizzled smem tile (TMA) -> TMEM.  Parts 0 .. D/32-1 of every row quarter move 32 elements (16 packed columns) each
+      if (part < D / 32) {
+        mbar_wait(q_full, 0);
+        const uint8_t* qrow = smem + SMEM::Q_OFF + (part >> 1) * CHUNK_BYTES + row * 128;
+        uint32_t qv[16];
 #pragma unroll
-        for (int c = 0; c < DH / 32; ++c) {
-          uint32_t v[32];
-          tmem_ld_32x32(TM_PV + b * 128 + half * DH + c * 32 + lane_off, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o_acc[c * 32 + i] = fmaf(o_acc[c * 32 + i], alpha, __uint_as_float(v[i]));
+        for (int u = 0; u < 4; ++u) {
+          const uint4 x = *reinterpret_cast<const uint4*>(qrow + ((((part & 1) * 4 + u) ^ (row & 7)) << 4));
+          qv[u * 4] = x.x; qv[u * 4 + 1] = x.y; qv[u * 4 + 2] = x.z; qv[u * 4 + 3] = x.w;
         }
+        tmem_st_32x16(TM_Q + part * 16 + lane_off, qv);
+        tmem_st_wait();
         tc_fence_before();
-        mbar_arrive(&o_free[b]);
-      };
-
-      float alpha_prev = 1.f;
+        mbar_arrive(&o_free[0]);
+      }
+      if (!warp_live) {
+        // keep the P barrier's arrival count: one arrival per page, paced by the completion of that page's phase
+        for (int j = 0; j < n_blocks; ++j) {
+          mbar_arrive(&p_full[j & 1]);
+          mbar_wait(&p_full[j & 1], (j >> 1) & 1);
+        }
+      } else {
       for (int j = 0; j < n_blocks; ++j) {
         const int b = j & 1;
         mbar_wait(&s_full[b], (j >> 1) & 1);
+        if (warp == 4 && lane == 0) { DSB_PF_TRACE(2, j) }
         tc_fence_after();
-        const int visible = limit - ((pg0 + j) * BN + half * 64);  // of this thread's 64 keys, [0, visible) count
-        const bool all_visible = __all_sync(0xffffffffu, visible >= 64);  // every page but the diagonal one(s)
-        const uint32_t s_addr = TM_S + b * 128 + half * 64 + lane_off;
-        // pass 1: maximum of the thread's 64 scores (four independent chains)
+        const int visible = limit - ((pg0 + j) * BN + part * 32);  // of this thread's 32 keys, [0, visible) count
+        const uint32_t s_addr = TM_S + b * 128 + part * 32 + lane_off;
+        uint32_t sv[32];  // the thread's scores stay in registers for both passes
+        tmem_ld_32x32(s_addr, sv);
+        tmem_ld_wait();
+        if (!__all_sync(0xffffffffu, visible >= 32)) {  // only the diagonal page(s)
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (i >= visible) sv[i] = 0xff800000u;  // -inf: exp2 gives exactly 0 below
+        }
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t sv[32];
-          tmem_ld_32x32(s_addr + c * 32, sv);
-          tmem_ld_wait();
-          if (all_visible) {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sv[i]));
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], c * 32 + i >= visible ? -INFINITY : __uint_as_float(sv[i]));
-          }
-        }
+        for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sv[i]));
         const __nv_bfloat16 mine = __float2bfloat16_ru(fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3])));
-        xmax[(b * 2 + half) * 128 + row] = mine;
-        asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-        const float m_blk = fmaxf(__bfloat162float(mine), __bfloat162float(xmax[(b * 2 + (half ^ 1)) * 128 + row]));
-        // a page with no visible key for this row leaves the running max alone (and -inf - -inf is never formed)
-        const float m_new = fmaxf(m_run, m_blk * p.scale_log2);
-        const float m_use = m_new == -INFINITY ? 0.f : m_new;
-        const float alpha = m_run == -INFINITY ? 0.f : exp2f(m_run - m_use);
-        float ls[4] = {0.f, 0.f, 0.f, 0.f};
-        // pass 2: P chunk c (32 keys -> 16 packed columns) goes to columns [16 c, 16 c + 16) of the thread's own half of the
-        // S buffer: always columns it has already consumed (chunk 0) or holds in registers (chunk c)
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t sv[32];
-          tmem_ld_32x32(s_addr + c * 32, sv);
+        if (j > 0) asm volatile("bar.sync %0, 128;" ::"r"(bar_b) : "memory");  // everyone has read the previous page's maxima
+        xmax[part * 128 + row] = mine;
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
+        const float m_blk = fmaxf(fmaxf(__bfloat162float(xmax[row]), __bfloat162float(xmax[128 + row])),
+                                  fmaxf(__bfloat162float(xmax[256 + row]), __bfloat162float(xmax[384 + row])));
+        // a page with no visible key for this row leaves the reference alone (and -inf - -inf is never formed)
+        const float m_cand = fmaxf(m_run, m_blk * p.scale_log2);
+        const bool fresh = m_run == -INFINITY;  // nothing accumulated for this row yet: O row and l are exactly 0
+        const float m_new = (fresh || m_cand - m_run > 8.f) ? m_cand : m_run;
+        const bool rescale = !fresh && m_new != m_run && j > 0;
+        if (__any_sync(0xffffffffu, rescale)) {  // identical decision in the 4 warps that share these rows
+          const float alpha = rescale ? exp2f(m_run - m_new) : 1.f;
+          mbar_wait(&o_full[0], (j - 1) & 1);  // PV(j-1) has retired; PV(j) cannot start before this thread publishes P(j)
+          tc_fence_after();
+          uint32_t v[DQ];
+          if constexpr (DQ == 32) tmem_ld_32x32(o_addr, v);
+          else tmem_ld_32x16(o_addr, v);
           tmem_ld_wait();
-          uint32_t pk[16];
-          if (all_visible) {
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float e0 = ex2_fast(fmaf(__uint_as_float(sv[2 * i]), p.scale_log2, -m_use));
-              const float e1 = ex2_fast(fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2, -m_use));
-              ls[i & 1] += e0;
-              ls[2 + (i & 1)] += e1;
-              pk[i] = pack_bf16x2(e0, e1);
-            }
-          } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              const float v0 = fmaf(__uint_as_float(sv[2 * i]), p.scale_log2, -m_use);
-              const float v1 = fmaf(__uint_as_float(sv[2 * i + 1]), p.scale_log2, -m_use);
-              const float e0 = (c * 32 + 2 * i >= visible) ? 0.f : ex2_fast(v0);
-              const float e1 = (c * 32 + 2 * i + 1 >= visible) ? 0.f : ex2_fast(v1);
-              ls[i & 1] += e0;
-              ls[2 + (i & 1)] += e1;
-              pk[i] = pack_bf16x2(e0, e1);
-            }
-          }
-          tmem_st_32x16(s_addr + c * 16, pk);
+          for (int i = 0; i < DQ; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+          if constexpr (DQ == 32) tmem_st_32x32(o_addr, v);
+          else tmem_st_32x16(o_addr, v);
+          l_run *= alpha;
         }
-        l_run = l_run * alpha + ((ls[0] + ls[1]) + (ls[2] + ls[3]));
         m_run = m_new;
+        const float m_use = m_new == -INFINITY ? 0.f : m_new;
+        float ls[2];
+        // P (32 keys -> 16 packed columns) goes to the first 16 columns of the thread's own quarter of the S buffer
+        // The MUFU unit (16 ex2 / clk / SM: 1024 cycles for a 128 x 128 page) is the limiter of this loop: 3 pairs of every 8
+        // take the polynomial exp2 on the FMA pipe, in packed fp32x2 arithmetic
+        uint32_t pk[16];
+        const uint64_t sc2 = pack2(p.scale_log2, p.scale_log2), negm2 = pack2(-m_use, -m_use);
+        uint64_t l2a = 0ull, l2b = 0ull;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const uint64_t x2 = fma2(pack2(__uint_as_float(sv[2 * i]), __uint_as_float(sv[2 * i + 1])), sc2, negm2);
+          const uint64_t e2 = ((i & 7) < 3) ? exp2_poly2(x2) : exp2_mufu2(x2);
+          if (i & 1) l2b = add2(l2b, e2); else l2a = add2(l2a, e2);
+          float e0, e1;
+          unpack2(e2, e0, e1);
+          pk[i] = pack_bf16x2(e0, e1);
+        }
+        tmem_st_32x16(s_addr, pk);
+        unpack2(add2(l2a, l2b), ls[0], ls[1]);
+        l_run += ls[0] + ls[1];
         tmem_st_wait();
         tc_fence_before();
         mbar_arrive(&p_full[b]);
-        if (j > 0) accumulate_pv(j - 1, alpha_prev);
-        alpha_prev = alpha;
+        if (warp == 4 && lane == 0) { DSB_PF_TRACE(3, j) }
       }
-      accumulate_pv(n_blocks - 1, alpha_prev);
+      mbar_wait(&o_full[0], (n_blocks - 1) & 1);
+      tc_fence_after();
+      uint32_t o_bits[DQ];
+      if constexpr (DQ == 32) tmem_ld_32x32(o_addr, o_bits);
+      else tmem_ld_32x16(o_addr, o_bits);
+      tmem_ld_wait();
+      float o_acc[DQ];
+#pragma unroll
+      for (int i = 0; i < DQ; ++i) o_acc[i] = __uint_as_float(o_bits[i]);
 
-      // the row's sum = both halves' sums (same sequence of maxima): exchange through the (now idle) max buffer
-      float* xl = reinterpret_cast<float*>(smem + SMEM::X_OFF);  // [half][row]
-      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-      xl[half * 128 + row] = l_run;
-      asm volatile("bar.sync %0, 64;" ::"r"(pair_bar) : "memory");
-      l_run += xl[(half ^ 1) * 128 + row];
+      // the row's sum = the four parts' sums (same sequence of maxima).  The last partial product has been read, so every MMA
+      // and every TMA load of this CTA has retired: the first K tile is free to carry the exchange
+      float* xl = reinterpret_cast<float*>(smem + SMEM::K_OFF);  // [part][row]
+      xl[part * 128 + row] = l_run;
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_a) : "memory");
+      l_run = (xl[row] + xl[128 + row]) + (xl[256 + row] + xl[384 + row]);
 
       if (live) {
         const int t = t0 + ti, head = kvh * p.group + g;
         if (!partial) {
           const float inv_l = 1.f / l_run;
-          __nv_bfloat16* dst = p.out + (static_cast<size_t>(t) * p.hq + head) * D + half * DH;
+          __nv_bfloat16* dst = p.out + (static_cast<size_t>(t) * p.hq + head) * D + part * DQ;
 #pragma unroll
-          for (int u = 0; u < DH / 8; ++u) {
+          for (int u = 0; u < DQ / 8; ++u) {
             uint4 val;
             const float* o = &o_acc[u * 8];
             val.x = pack_bf16x2(o[0] * inv_l, o[1] * inv_l);
@@ -356,16 +405,17 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           }
         } else {
           const size_t slot = (static_cast<size_t>(t) * p.hq + head) * p.n_splits + split;
-          float* dst = p.part_o + slot * D + half * DH;
+          float* dst = p.part_o + slot * D + part * DQ;
 #pragma unroll
-          for (int u = 0; u < DH / 4; ++u)
+          for (int u = 0; u < DQ / 4; ++u)
             *reinterpret_cast<float4*>(dst + u * 4) = make_float4(o_acc[u * 4], o_acc[u * 4 + 1], o_acc[u * 4 + 2], o_acc[u * 4 + 3]);
-          if (half == 0) {
+          if (part == 0) {
             p.part_ml[slot * 2] = m_run;
             p.part_ml[slot * 2 + 1] = l_run;
           }
         }
       }
+      }  // warp_live
     }
   } else if (partial && warp >= 2 && warp < 6) {
     // this split has no pages (short context): publish an empty partial for every live row
@@ -456,9 +506,27 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
   p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
   p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
   p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f;
+  static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
+  static long long* trace_buf = nullptr;
+  p.trace = nullptr;
+  if (want_trace) {
+    if (!trace_buf) DSB_CHECK_CUDA(cudaMalloc(&trace_buf, (8 + 64 * 8) * sizeof(long long)));
+    DSB_CHECK_CUDA(cudaMemsetAsync(trace_buf, 0, (8 + 64 * 8) * sizeof(long long), stream));
+    p.trace = trace_buf;
+  }
   dim3 grid(max_atoms, hkv, n_splits);
   kern<<<grid, NUM_THREADS, SMEM::TOTAL, stream>>>(tmQ, tmKV, p);
   DSB_CHECK_CUDA(cudaGetLastError());
+  if (want_trace) {  // diagnostics: synchronous dump of the claimed CTA's timeline (cycles relative to its start)
+    long long h[8 + 64 * 8];
+    DSB_CHECK_CUDA(cudaStreamSynchronize(stream));
+    DSB_CHECK_CUDA(cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    printf("paged_flash trace (T=%d splits=%d): page  K_landed  P_seen_by_mma  S_seen  P_published  O_read\n", T, n_splits);
+    for (int j = 0; j < 64 && h[8 + j * 8 + 2]; ++j)
+      printf("  %2d %8lld %8lld %8lld %8lld %8lld\n", j, h[8 + j * 8] - h[1], h[8 + j * 8 + 1] - h[1], h[8 + j * 8 + 2] - h[1],
+             h[8 + j * 8 + 3] - h[1], h[8 + j * 8 + 4] - h[1]);
+    fflush(stdout);
+  }
   if (n_splits > 1) {
     const int rows = T * hq;
     combine_splits_kernel<D><<<(rows * 32 + 255) / 256, 256, 0, stream>>>(part_o, part_ml, static_cast<__nv_bfloat16*>(out), rows, n_splits);

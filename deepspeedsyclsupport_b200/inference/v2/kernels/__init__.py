@@ -69,6 +69,21 @@ def paged_flash_supported(qkv, kv_cache, hq, hkv, d):
             128 % group == 0 and kv_cache.shape[2] >= 8 and 128 % kv_cache.shape[2] == 0 and os.environ.get("DSB200_PAGED_FLASH", "1") != "0")
 
 
+def _pick_splits(T, hq, d, ctas, pages):
+    """KV splits per (atom, kv head): more splits fill the 148 SMs when the batch is small, but every split writes an fp32
+    partial per (token, head) that the merge kernel reads back.  Cost model in microseconds: waves of CTAs x (5 us of set-up + pages per CTA at
+    ~0.7 us a page), plus the partial traffic at HBM speed and the merge launch."""
+    best, best_cost = 1, None
+    for n in range(1, min(16, pages) + 1):
+        waves = -(-ctas * n // 148)
+        cost = (5.0 + -(-pages // n) * 0.7) * waves
+        if n > 1:
+            cost += 2.0 * T * hq * (d + 2) * 4 * n / 6.0e6 + 3.0
+        if best_cost is None or cost < best_cost - 1e-9:
+            best, best_cost = n, cost
+    return best
+
+
 def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, n_splits=None):
     """Attention of every ragged token over its sequence's paged KV history on the tensor cores (csrc/attn/paged_flash.cu):
     atoms of up to 128/group tokens x kv head, KV pages fetched by TMA through the block table, prefill chunks and decode steps
@@ -80,8 +95,7 @@ def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv,
     max_atoms = max(1, min(T, (T + nt - 1) // nt + block_table.shape[0]))
     if n_splits is None:
         pages = -(-(max_context if max_context is not None else block_table.shape[1] * bs) // 128)
-        ctas = max_atoms * hkv
-        n_splits = 1 if ctas >= 96 else max(1, min(16, 148 // ctas, pages))
+        n_splits = _pick_splits(T, hq, d, max_atoms * hkv, pages)
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
     nbytes = native.lib().dsb200_paged_flash_scratch_bytes(T, hq, d, max_atoms, n_splits)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=qkv.device)
