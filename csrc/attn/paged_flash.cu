@@ -436,6 +436,349 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   }
 }
 
+// ================================================================================================ decode (small atoms)
+// Transposed formulation for atoms of at most 16 rows (decode steps: 1 token x `group` heads).  In the kernel above a decode
+// atom fills 8 of the 128 MMA rows, yet the softmax warps of that lane quarter still execute a full 32 x 128 tile per page --
+// all on one scheduler -- and the tensor core a full 128 x 128 x 128 product: 1.7 us a page, 54 % of HBM.  Here the keys take
+// the M dimension:
+//     S^T [128 keys x 16] = K_page (smem, K-major A)  x  Q^T (16 q rows of the atom, smem, K-major B)        8 MMAs of 128 x 16 x 16
+//     O^T [128 d    x 16] += V_page^T (smem, MN-major A)  x  P^T (smem, K-major B [16 rows][128 keys])       8 MMAs of 128 x 16 x 16
+// thread == (key, 4 of the 16 columns): every lane live, the work spread over all four schedulers.  Per-column
+// maxima are reduced across the 128 keys (shuffles + one shared-memory exchange); the sums stay per-thread partials until
+// the end.  O^T accumulates in TMEM and is rescaled lazily (reference maximum moves only by > 2^8).  head_dim 128 only.
+constexpr int NQ = 16;              // q rows (columns of S^T / O^T) per atom
+constexpr int DEC_THREADS = 576;    // TMA warp, MMA warp, 16 softmax warps
+struct DecSmem {
+  static constexpr int TILE = 2 * CHUNK_BYTES;       // one K or V page: [128 keys][128 d] as two 64-column chunks
+  static constexpr int STAGES = 3;
+  static constexpr int Q_BYTES = 2 * NQ * 128;       // [2 chunks][16 rows][128 B]
+  static constexpr int P_BYTES = 2 * NQ * 128;       // [2 key chunks][16 rows][128 B]
+  static constexpr int K_OFF = 0;
+  static constexpr int V_OFF = K_OFF + STAGES * TILE;
+  static constexpr int Q_OFF = V_OFF + STAGES * TILE;
+  static constexpr int P_OFF = Q_OFF + Q_BYTES;      // two buffers
+  static constexpr int BAR_OFF = P_OFF + 2 * P_BYTES;
+  static constexpr int X_OFF = BAR_OFF + 256;        // [2 parities][4 warps][16] page maxima, then the final sums
+  static constexpr int TOTAL = X_OFF + 1024 + 1024;
+};
+
+__global__ void __launch_bounds__(DEC_THREADS, 1)
+paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV, const Params p) {
+  using SMEM = DecSmem;
+  constexpr int D = 128, NS = SMEM::STAGES;
+  // One CTA per token: it runs only when its token opens an atom (first of the batch / of its sequence in the batch / of a
+  // 16/group-aligned run).  Decode batches are a few hundred tokens at most, and this drops the atom-list kernel and its
+  // counter memset from the launch chain (they cost more than a tenth of a 64-sequence decode step).
+  const int t0 = blockIdx.x;
+  const int seq = p.tok_seq[t0], pos0 = p.tok_pos[t0];
+  if (t0 > 0 && p.tok_seq[t0 - 1] == seq && p.tok_pos[t0 - 1] + 1 == pos0 && (pos0 % p.nt_tile) != 0) return;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + SMEM::BAR_OFF);
+  uint64_t* q_full = bars + 0;
+  uint64_t* k_full = bars + 1;       // [NS]
+  uint64_t* v_full = k_full + NS;    // [NS]
+  uint64_t* k_empty = v_full + NS;   // [NS]
+  uint64_t* v_empty = k_empty + NS;  // [NS]
+  uint64_t* s_full = v_empty + NS;   // [2]
+  uint64_t* p_full = s_full + 2;     // [2] softmax -> MMA: P^T(j) is in shared memory
+  uint64_t* p_free = p_full + 2;     // [2] MMA -> softmax: PV(j) has read P^T buffer j & 1
+  uint64_t* o_full = p_free + 2;     // phase j completes when PV(j) has retired
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(o_full + 1);
+  int* s_nt = reinterpret_cast<int*>(o_full + 2);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int kvh = blockIdx.y, split = blockIdx.z;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmKV);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < NS; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&s_full[i], 1);
+      mbar_init(&p_full[i], DEC_THREADS - 64);
+      mbar_init(&p_free[i], 1);
+    }
+    mbar_init(o_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {  // atom length, as in the kernel above (nt_tile = 16 / group here)
+    int nt = p.nt_tile;
+    const int i = lane;
+    const bool ok = i == 0 || (i < p.nt_tile && t0 + i < p.T && p.tok_seq[t0 + i] == seq && p.tok_pos[t0 + i] == pos0 + i &&
+                               ((pos0 + i) % p.nt_tile) != 0);
+    const uint32_t bad = __ballot_sync(0xffffffffu, !ok);
+    if (bad) nt = __ffs(bad) - 1;
+    if (lane == 0) *s_nt = nt;
+  }
+  if (warp == 1) {
+    tmem_alloc<1>(tmem_ptr, 64);
+    tmem_relinquish<1>();
+  }
+  // P^T buffers start zeroed: rows of q columns past the atom are never written
+  for (int i = threadIdx.x; i < 2 * SMEM::P_BYTES / 16; i += DEC_THREADS)
+    reinterpret_cast<uint4*>(smem + SMEM::P_OFF)[i] = make_uint4(0, 0, 0, 0);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr;
+  const int nt = *s_nt;
+  const int nq = nt * p.group;  // live columns
+  const int n_pages = (pos0 + nt + BN - 1) / BN;
+  const int per_split = (n_pages + p.n_splits - 1) / p.n_splits;
+  const int pg0 = split * per_split;
+  const int pg1 = min(n_pages, pg0 + per_split);
+  const int n_blocks = max(0, pg1 - pg0);
+  const bool partial = p.n_splits > 1;
+  bool tracing = false;
+  if (p.trace != nullptr) {
+    int* claim = reinterpret_cast<int*>(bars + 30);
+    if (threadIdx.x == 0) *claim = (n_blocks >= 8 && atomicCAS(reinterpret_cast<int*>(p.trace), 0, 1) == 0) ? 1 : 0;
+    __syncthreads();
+    tracing = *claim != 0;
+    if (tracing && threadIdx.x == 0) p.trace[1] = clock64();
+  }
+
+  if (n_blocks > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        mbar_expect_tx(q_full, SMEM::Q_BYTES);
+#pragma unroll
+        for (int c = 0; c < 2; ++c) tma_load_3d(&tmQ, q_full, smem + SMEM::Q_OFF + c * NQ * 128, c * 64, kvh * p.group, t0);
+        const int* bt = p.block_table + static_cast<size_t>(seq) * p.max_blocks;
+        const int sub = BN / p.block_size;
+        const int last_blk = (pos0 + nt - 1) / p.block_size;
+        int st = 0, ph = 0;
+        for (int j = 0; j < n_blocks; ++j) {
+#pragma unroll
+          for (int is_v = 0; is_v < 2; ++is_v) {
+            uint64_t* full = is_v ? &v_full[st] : &k_full[st];
+            mbar_wait(is_v ? &v_empty[st] : &k_empty[st], ph ^ 1);
+            mbar_expect_tx(full, SMEM::TILE);
+            uint8_t* tile = smem + (is_v ? SMEM::V_OFF : SMEM::K_OFF) + st * SMEM::TILE;
+            for (int s = 0; s < sub; ++s) {
+              const int logical = min((pg0 + j) * sub + s, last_blk);
+              const int blk = bt[logical];
+              const int row_off = s * p.block_size * 128;
+#pragma unroll
+              for (int c = 0; c < 2; ++c) tma_load_4d(&tmKV, full, tile + c * CHUNK_BYTES + row_off, c * 64, kvh, 0, blk * 2 + is_v);
+            }
+          }
+          if (++st == NS) { st = 0; ph ^= 1; }
+        }
+      }
+    } else if (warp == 1) {
+      const bool leader = elect_one();
+      constexpr uint32_t idesc_qk = umma_idesc(128, NQ, 1, 1, 0, 0);  // A = K page (K-major), B = Q rows (K-major)
+      constexpr uint32_t idesc_pv = umma_idesc(128, NQ, 1, 1, 1, 0);  // A = V page^T (MN-major), B = P^T (K-major)
+      const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+      const uint32_t tm_o = tm + 32;
+      const uint64_t k_desc0 = umma_smem_desc(smem_u32(smem + SMEM::K_OFF), 16, 1024);
+      const uint64_t v_desc0 = umma_smem_desc(smem_u32(smem + SMEM::V_OFF), CHUNK_BYTES, 1024);
+      const uint64_t q_desc0 = umma_smem_desc(smem_u32(smem + SMEM::Q_OFF), 16, 1024);
+      const uint64_t p_desc0 = umma_smem_desc(smem_u32(smem + SMEM::P_OFF), 16, 1024);
+      auto issue_qk = [&](int j, int st, int ph) {
+        const int b = j & 1;
+        mbar_wait_lean(&k_full[st], ph);
+        tc_fence_after();
+        if (leader) {
+          DSB_PF_TRACE(0, j)
+          const uint64_t kd = k_desc0 + static_cast<uint32_t>((st * SMEM::TILE) >> 4);
+#pragma unroll
+          for (int kk = 0; kk < D / 16; ++kk)
+            umma_f16<1>(tm + b * NQ, kd + static_cast<uint32_t>(((kk >> 2) * CHUNK_BYTES + (kk & 3) * 32) >> 4),
+                        q_desc0 + static_cast<uint32_t>(((kk >> 2) * NQ * 128 + (kk & 3) * 32) >> 4), idesc_qk, kk != 0 ? 1u : 0u);
+          umma_commit<1>(&s_full[b]);
+          umma_commit<1>(&k_empty[st]);
+        }
+      };
+      auto issue_pv = [&](int j, int st, int ph) {
+        const int b = j & 1;
+        mbar_wait_lean(&v_full[st], ph);
+        mbar_wait_lean(&p_full[b], (j >> 1) & 1);
+        tc_fence_after();
+        if (leader) {
+          DSB_PF_TRACE(1, j)
+          const uint64_t vd = v_desc0 + static_cast<uint32_t>((st * SMEM::TILE) >> 4);
+          const uint64_t pd = p_desc0 + static_cast<uint32_t>((b * SMEM::P_BYTES) >> 4);
+#pragma unroll
+          for (int kk = 0; kk < BN / 16; ++kk)
+            umma_f16<1>(tm_o, vd + static_cast<uint32_t>((kk * 2048) >> 4),
+                        pd + static_cast<uint32_t>(((kk >> 2) * NQ * 128 + (kk & 3) * 32) >> 4), idesc_pv, (j | kk) != 0 ? 1u : 0u);
+          umma_commit<1>(o_full);
+          umma_commit<1>(&v_empty[st]);
+          umma_commit<1>(&p_free[b]);
+        }
+      };
+      mbar_wait_lean(q_full, 0);
+      tc_fence_after();
+      issue_qk(0, 0, 0);
+      int st = 0, ph = 0;
+      for (int j = 0; j < n_blocks; ++j) {
+        int st1 = st + 1, ph1 = ph;
+        if (st1 == NS) { st1 = 0; ph1 ^= 1; }
+        if (j + 1 < n_blocks) issue_qk(j + 1, st1, ph1);
+        issue_pv(j, st, ph);
+        st = st1; ph = ph1;
+      }
+    } else {
+      // softmax: thread == (key of the page = TMEM lane, 4 of the 16 q columns).  16 warps: lane quarter w x column part; the
+      // parts past the atom's live columns only keep the barrier counts.  One warp per scheduler owning all 16 columns ran
+      // ~600 latency-bound instructions a page.
+      const int w = warp & 3, part = (warp - 2) >> 2;
+      constexpr int CPT = 4;
+      const int c0 = part * CPT;
+      const int row = w * 32 + lane;
+      const uint32_t lane_off = static_cast<uint32_t>(w * 32) << 16;
+      if (c0 >= nq) {
+        for (int j = 0; j < n_blocks; ++j) {
+          mbar_arrive(&p_full[j & 1]);
+          mbar_wait(&p_full[j & 1], (j >> 1) & 1);
+        }
+      } else {
+      float* xmax = reinterpret_cast<float*>(smem + SMEM::X_OFF);  // [parity][warp quarter][16]
+      const uint32_t bar_id = 1 + part;  // the 4 warps (128 key-lanes) that share these columns
+      float m_run[CPT], l_part[CPT];  // reference maximum per column (uniform over the part), this key-lane's share of the sums
+      int limit[CPT];                 // keys [0, limit) are visible to column c
+#pragma unroll
+      for (int i = 0; i < CPT; ++i) {
+        m_run[i] = -INFINITY;
+        l_part[i] = 0.f;
+        limit[i] = c0 + i < nq ? pos0 + (c0 + i) / p.group + 1 : 0x3fffffff;
+      }
+      const uint32_t s_addr0 = tmem_base + c0 + lane_off, o_addr = tmem_base + 32 + c0 + lane_off;
+      for (int j = 0; j < n_blocks; ++j) {
+        const int b = j & 1;
+        mbar_wait(&s_full[b], (j >> 1) & 1);
+        if (warp == 4 && lane == 0) { DSB_PF_TRACE(2, j) }
+        tc_fence_after();
+        uint32_t sv[CPT];
+        tmem_ld_32x4(s_addr0 + b * NQ, sv);
+        tmem_ld_wait();
+        const int key = (pg0 + j) * BN + row;
+        float s[CPT], wm[CPT];
+        // column maxima over the 128 keys: one REDUX per column inside the warp (floats mapped monotonically to unsigned),
+        // then the 4 lane-quarter warps meet in shared memory
+#pragma unroll
+        for (int i = 0; i < CPT; ++i) {
+          s[i] = key >= limit[i] ? -INFINITY : __uint_as_float(sv[i]);
+          const uint32_t bits = __float_as_uint(s[i]);
+          const uint32_t r = __reduce_max_sync(0xffffffffu, bits ^ ((bits >> 31) ? 0xffffffffu : 0x80000000u));
+          wm[i] = __uint_as_float(r ^ ((r >> 31) ? 0x80000000u : 0xffffffffu));
+        }
+        if (lane == 0) *reinterpret_cast<float4*>(xmax + (b * 4 + w) * NQ + c0) = make_float4(wm[0], wm[1], wm[2], wm[3]);
+        asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+        float comb[CPT];
+        {
+          const float4 a0 = *reinterpret_cast<const float4*>(xmax + (b * 4 + 0) * NQ + c0);
+          const float4 a1 = *reinterpret_cast<const float4*>(xmax + (b * 4 + 1) * NQ + c0);
+          const float4 a2 = *reinterpret_cast<const float4*>(xmax + (b * 4 + 2) * NQ + c0);
+          const float4 a3 = *reinterpret_cast<const float4*>(xmax + (b * 4 + 3) * NQ + c0);
+          comb[0] = fmaxf(fmaxf(a0.x, a1.x), fmaxf(a2.x, a3.x));
+          comb[1] = fmaxf(fmaxf(a0.y, a1.y), fmaxf(a2.y, a3.y));
+          comb[2] = fmaxf(fmaxf(a0.z, a1.z), fmaxf(a2.z, a3.z));
+          comb[3] = fmaxf(fmaxf(a0.w, a1.w), fmaxf(a2.w, a3.w));
+        }
+        bool any_rescale = false;
+        float alpha[CPT], m_use[CPT];
+#pragma unroll
+        for (int i = 0; i < CPT; ++i) {
+          const float m_cand = fmaxf(m_run[i], comb[i] * p.scale_log2);
+          const bool fresh = m_run[i] == -INFINITY;
+          const float m_new = (fresh || m_cand - m_run[i] > 8.f) ? m_cand : m_run[i];
+          const bool rescale = !fresh && m_new != m_run[i];
+          alpha[i] = rescale ? ex2_fast(m_run[i] - m_new) : 1.f;
+          any_rescale |= rescale;
+          m_run[i] = m_new;
+          m_use[i] = m_new == -INFINITY ? 0.f : m_new;
+        }
+        if (any_rescale && j > 0) {  // uniform over the part: every thread of it sees the same maxima
+          mbar_wait(o_full, (j - 1) & 1);  // PV(j-1) has retired; PV(j) cannot start before this thread publishes P(j)
+          tc_fence_after();
+          uint32_t ov[CPT];
+          tmem_ld_32x4(o_addr, ov);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < CPT; ++i) {
+            ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha[i]);
+            l_part[i] *= alpha[i];
+          }
+          tmem_st_32x4(o_addr, ov);
+          tmem_st_wait();
+          tc_fence_before();
+        }
+        if (j >= 2) mbar_wait(&p_free[b], ((j >> 1) - 1) & 1);  // PV(j-2) has read this P^T buffer
+        // P^T [16 rows][128 keys] bf16, K-major, 128-byte swizzle rows of 64 keys: this thread owns column `row` of its q rows
+        uint8_t* pbuf = smem + SMEM::P_OFF + b * SMEM::P_BYTES + (row >> 6) * (NQ * 128);
+        const int k64 = row & 63;
+#pragma unroll
+        for (int i = 0; i < CPT; ++i) {
+          const int c = c0 + i;
+          if (c < nq) {
+            const float e = ex2_fast(fmaf(s[i], p.scale_log2, -m_use[i]));
+            l_part[i] += e;
+            *reinterpret_cast<__nv_bfloat16*>(pbuf + c * 128 + ((((k64 >> 3) ^ (c & 7)) << 4) | ((k64 & 7) << 1))) = __float2bfloat16_rn(e);
+          }
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(&p_full[b]);
+        if (warp == 4 && lane == 0) { DSB_PF_TRACE(3, j) }
+      }
+      // epilogue: O^T [d = row][this part's columns]; column sums over the 128 key-lanes
+      mbar_wait(o_full, (n_blocks - 1) & 1);
+      tc_fence_after();
+      uint32_t ov[CPT];
+      tmem_ld_32x4(o_addr, ov);
+      tmem_ld_wait();
+      float* xl = reinterpret_cast<float*>(smem + SMEM::X_OFF) + 2 * 4 * NQ;  // [warp quarter][16], behind the maxima
+      float tsum[CPT];
+#pragma unroll
+      for (int i = 0; i < CPT; ++i) tsum[i] = warp_sum(l_part[i]);
+      if (lane == 0) *reinterpret_cast<float4*>(xl + w * NQ + c0) = make_float4(tsum[0], tsum[1], tsum[2], tsum[3]);
+      asm volatile("bar.sync %0, 128;" ::"r"(bar_id) : "memory");
+#pragma unroll
+      for (int i = 0; i < CPT; ++i) {
+        const int c = c0 + i;
+        const float l = (xl[c] + xl[NQ + c]) + (xl[2 * NQ + c] + xl[3 * NQ + c]);
+        if (c < nq) {
+          const int t = t0 + c / p.group, head = kvh * p.group + c % p.group;
+          if (!partial) {
+            p.out[(static_cast<size_t>(t) * p.hq + head) * D + row] = __float2bfloat16_rn(__uint_as_float(ov[i]) / l);
+          } else {
+            const size_t slot = (static_cast<size_t>(t) * p.hq + head) * p.n_splits + split;
+            p.part_o[slot * D + row] = __uint_as_float(ov[i]);
+            if (row == 0) {
+              p.part_ml[slot * 2] = m_run[i];
+              p.part_ml[slot * 2 + 1] = l;
+            }
+          }
+        }
+      }
+      }  // live part
+    }
+  } else if (partial && warp == 2) {
+    const int c = lane;  // this split has no pages: an empty partial per live column
+    if (c < nq) {
+      const size_t slot = (static_cast<size_t>(t0 + c / p.group) * p.hq + kvh * p.group + c % p.group) * p.n_splits + split;
+      p.part_ml[slot * 2] = -INFINITY;
+      p.part_ml[slot * 2 + 1] = 0.f;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, 64);
+  }
+}
+
 // out[t][h][:] = sum_s 2^(m_s - M) O_s / sum_s 2^(m_s - M) l_s ; one warp per (token, head)
 template <int D>
 __global__ void combine_splits_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml, __nv_bfloat16* __restrict__ out,
@@ -535,6 +878,72 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
   return DSB_OK;
 }
 
+// decode variant: atoms of at most 16 / group tokens, head_dim 128
+static int launch_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos, const int* block_table,
+                         int T, int hq, int hkv, int block_size, int max_blocks, int num_blocks, float scale, int max_atoms,
+                         int n_splits, void* scratch, cudaStream_t stream) {
+  constexpr int D = 128;
+  const int group = hq / hkv, nt_tile = NQ / group;
+  const int heads = hq + 2 * hkv;
+  CUtensorMap tmQ, tmKV;
+  {
+    const uint64_t dims[3] = {static_cast<uint64_t>(D), static_cast<uint64_t>(heads), static_cast<uint64_t>(T)};
+    const uint64_t strides[2] = {static_cast<uint64_t>(D) * 2, static_cast<uint64_t>(heads) * D * 2};
+    const uint32_t box[3] = {64, static_cast<uint32_t>(group), static_cast<uint32_t>(nt_tile)};
+    int rc = make_tensor_map(&tmQ, TMA_BF16, 3, qkv, dims, strides, box, TMA_SW_128);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[4] = {static_cast<uint64_t>(D), static_cast<uint64_t>(hkv), static_cast<uint64_t>(block_size),
+                              static_cast<uint64_t>(num_blocks) * 2};
+    const uint64_t strides[3] = {static_cast<uint64_t>(D) * 2, static_cast<uint64_t>(hkv) * D * 2,
+                                 static_cast<uint64_t>(block_size) * hkv * D * 2};
+    const uint32_t box[4] = {64, 1, static_cast<uint32_t>(block_size), 1};
+    int rc = make_tensor_map(&tmKV, TMA_BF16, 4, kv_cache, dims, strides, box, TMA_SW_128);
+    if (rc) return rc;
+  }
+  int* atoms = static_cast<int*>(scratch);  // (layout shared with the general kernel; the atom list itself is not used here)
+  const size_t head_ints = (static_cast<size_t>(max_atoms) + 1 + 3) / 4 * 4;
+  float* part_o = reinterpret_cast<float*>(atoms + head_ints);
+  float* part_ml = part_o + static_cast<size_t>(T) * hq * n_splits * D;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DSB_CHECK_CUDA(cudaFuncSetAttribute(paged_decode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DecSmem::TOTAL));
+    attr_set = true;
+  }
+  Params p;
+  p.tok_seq = tok_seq; p.tok_pos = tok_pos; p.block_table = block_table; p.atoms = nullptr; p.n_atoms = nullptr;
+  p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
+  p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
+  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.trace = nullptr;
+  static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
+  static long long* trace_buf = nullptr;
+  if (want_trace) {
+    if (!trace_buf) DSB_CHECK_CUDA(cudaMalloc(&trace_buf, (8 + 64 * 8) * sizeof(long long)));
+    DSB_CHECK_CUDA(cudaMemsetAsync(trace_buf, 0, (8 + 64 * 8) * sizeof(long long), stream));
+    p.trace = trace_buf;
+  }
+  dim3 grid(T, hkv, n_splits);
+  paged_decode_kernel<<<grid, DEC_THREADS, DecSmem::TOTAL, stream>>>(tmQ, tmKV, p);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  if (want_trace) {
+    long long h[8 + 64 * 8];
+    DSB_CHECK_CUDA(cudaStreamSynchronize(stream));
+    DSB_CHECK_CUDA(cudaMemcpy(h, trace_buf, sizeof(h), cudaMemcpyDeviceToHost));
+    printf("paged_decode trace (T=%d splits=%d): page  QK_issue  P_seen_by_mma  S_seen  max_exchanged  alpha_done  p_free_seen  stored  P_published\n", T, n_splits);
+    for (int j = 0; j < 64 && h[8 + j * 8 + 2]; ++j)
+      printf("  %2d %8lld %8lld %8lld %8lld %8lld %8lld %8lld %8lld\n", j, h[8 + j * 8] - h[1], h[8 + j * 8 + 1] - h[1], h[8 + j * 8 + 2] - h[1],
+             h[8 + j * 8 + 4] - h[1], h[8 + j * 8 + 5] - h[1], h[8 + j * 8 + 6] - h[1], h[8 + j * 8 + 7] - h[1], h[8 + j * 8 + 3] - h[1]);
+    fflush(stdout);
+  }
+  if (n_splits > 1) {
+    const int rows = T * hq;
+    combine_splits_kernel<D><<<(rows * 32 + 255) / 256, 256, 0, stream>>>(part_o, part_ml, static_cast<__nv_bfloat16*>(out), rows, n_splits);
+    DSB_CHECK_CUDA(cudaGetLastError());
+  }
+  return DSB_OK;
+}
+
 }  // namespace paged
 }  // namespace dsb
 
@@ -564,4 +973,21 @@ DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cach
                               num_blocks, scale, max_atoms, n_splits, scratch, stream);
   return paged::launch<64>(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
                            num_blocks, scale, max_atoms, n_splits, scratch, stream);
+}
+
+// Same contract as dsb200_paged_flash_attention for batches of small atoms (decode steps): atoms hold at most 16 / group tokens,
+// keys take the M dimension of the MMAs (see paged_decode_kernel).  head_dim 128, q:kv head ratio dividing 16.
+// max_atoms >= ceil(n_tokens / (16/group)) + number of sequences (<= n_tokens).
+DSB_EXPORT int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
+                                         const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
+                                         int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
+                                         void* scratch, cudaStream_t stream) {
+  using namespace dsb;
+  if (n_tokens == 0) return DSB_OK;
+  DSB_REQUIRE(head_dim == 128, "paged_flash_decode: head_dim %d unsupported (128)", head_dim);
+  DSB_REQUIRE(hq % hkv == 0 && 16 % (hq / hkv) == 0, "paged_flash_decode: q/kv head ratio %d must divide 16", hq / hkv);
+  DSB_REQUIRE(block_size >= 8 && block_size <= 128 && 128 % block_size == 0, "paged_flash_decode: KV block size %d must divide 128", block_size);
+  DSB_REQUIRE(max_atoms >= 1 && n_splits >= 1 && n_splits <= 64 && scratch != nullptr, "paged_flash_decode: bad max_atoms / n_splits / scratch");
+  return paged::launch_decode(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
+                              num_blocks, scale, max_atoms, n_splits, scratch, stream);
 }

@@ -10,6 +10,7 @@ native.register_sigs({
     "dsb200_kv_rotary_append": "pppppp iiiiiii p",
     "dsb200_paged_attention": "pppppp iiiiii f p",
     "dsb200_paged_flash_attention": "pppppp iiiiiii f ii p p",
+    "dsb200_paged_flash_decode": "pppppp iiiiiii f ii p p",
     "dsb200_paged_flash_scratch_bytes": "iiiii",
     "dsb200_ragged_embed": "ppppp iii p",
     "dsb200_logits_gather": "ppp ii p",
@@ -69,14 +70,14 @@ def paged_flash_supported(qkv, kv_cache, hq, hkv, d):
             128 % group == 0 and kv_cache.shape[2] >= 8 and 128 % kv_cache.shape[2] == 0 and os.environ.get("DSB200_PAGED_FLASH", "1") != "0")
 
 
-def _pick_splits(T, hq, d, ctas, pages):
+def _pick_splits(T, hq, d, ctas, pages, page_us=0.7):
     """KV splits per (atom, kv head): more splits fill the 148 SMs when the batch is small, but every split writes an fp32
     partial per (token, head) that the merge kernel reads back.  Cost model in microseconds: waves of CTAs x (5 us of set-up + pages per CTA at
     ~0.7 us a page), plus the partial traffic at HBM speed and the merge launch."""
     best, best_cost = 1, None
     for n in range(1, min(16, pages) + 1):
         waves = -(-ctas * n // 148)
-        cost = (5.0 + -(-pages // n) * 0.7) * waves
+        cost = (5.0 + -(-pages // n) * page_us) * waves
         if n > 1:
             cost += 2.0 * T * hq * (d + 2) * 4 * n / 6.0e6 + 3.0
         if best_cost is None or cost < best_cost - 1e-9:
@@ -84,25 +85,30 @@ def _pick_splits(T, hq, d, ctas, pages):
     return best
 
 
-def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, n_splits=None):
+def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, n_splits=None,
+                          decode=None):
     """Attention of every ragged token over its sequence's paged KV history on the tensor cores (csrc/attn/paged_flash.cu):
     atoms of up to 128/group tokens x kv head, KV pages fetched by TMA through the block table, prefill chunks and decode steps
-    alike; small batches over long contexts are split along the KV axis (`n_splits`, chosen here unless given) and merged."""
+    alike; small batches over long contexts are split along the KV axis (`n_splits`, chosen here unless given) and merged.
+    `decode`: the batch is (almost) one token per sequence -- use the transposed small-atom kernel (keys on the MMA M axis,
+    16 q rows per atom).  Default: when the batch has no more tokens than the block table has sequences and d == 128."""
     scale = scale if scale is not None else 1.0 / math.sqrt(d)
     T = qkv.shape[0]
     bs, group = kv_cache.shape[2], hq // hkv
-    nt = 128 // group
+    if decode is None:
+        decode = T <= block_table.shape[0]
+    decode = bool(decode) and d == 128 and 16 % group == 0 and os.environ.get("DSB200_PAGED_DECODE", "1") != "0"
+    nt = (16 if decode else 128) // group
     max_atoms = max(1, min(T, (T + nt - 1) // nt + block_table.shape[0]))
     if n_splits is None:
         pages = -(-(max_context if max_context is not None else block_table.shape[1] * bs) // 128)
-        n_splits = _pick_splits(T, hq, d, max_atoms * hkv, pages)
+        n_splits = _pick_splits(T, hq, d, max_atoms * hkv, pages, page_us=0.45 if decode else 0.7)
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
     nbytes = native.lib().dsb200_paged_flash_scratch_bytes(T, hq, d, max_atoms, n_splits)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=qkv.device)
-    rc = native.lib().dsb200_paged_flash_attention(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq),
-                                                   native.ptr(tok_pos), native.ptr(block_table), T, hq, hkv, d, bs,
-                                                   block_table.shape[1], kv_cache.shape[0], float(scale), max_atoms, n_splits,
-                                                   native.ptr(scratch), native.stream_ptr())
+    fn = native.lib().dsb200_paged_flash_decode if decode else native.lib().dsb200_paged_flash_attention
+    rc = fn(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq), native.ptr(tok_pos), native.ptr(block_table), T, hq,
+            hkv, d, bs, block_table.shape[1], kv_cache.shape[0], float(scale), max_atoms, n_splits, native.ptr(scratch), native.stream_ptr())
     native.check(rc)
     return out
 

@@ -123,6 +123,13 @@ int dsb200_paged_flash_attention(const void* qkv, const void* kv_cache, void* ou
                                  const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                  int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
                                  void* scratch, dsb200_stream_t stream);
+/* Same contract as dsb200_paged_flash_attention for batches of small atoms (decode steps): atoms hold at most 16 / group tokens,
+ * keys take the M dimension of the MMAs (see paged_decode_kernel).  head_dim 128, q:kv head ratio dividing 16.
+ * max_atoms >= ceil(n_tokens / (16/group)) + number of sequences (<= n_tokens). */
+int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
+                              const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
+                              int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
+                              void* scratch, dsb200_stream_t stream);
 
 /* ---- csrc/comm/symm.cu */
 /* ---- allocation / mapping (host pointers unless noted) */

@@ -28,15 +28,15 @@ def _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed=0):
             torch.tensor(tok_pos, dtype=torch.int32, device=dev), block_table.to(dev))
 
 
-def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0):
+def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0, decode=None):
     from deepspeedsyclsupport_b200.inference.v2 import kernels as K
     qkv, kv, ts, tp, bt = _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed)
     scale = d ** -0.5
-    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits).float()
+    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits, decode=decode).float()
     want = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), hq, hkv, d, scale).float().cuda()
     torch.cuda.synchronize()
     err = (got - want).abs().max().item()
-    assert torch.isfinite(got).all() and err < 2e-2, (seq_new, seq_seen, hq, hkv, d, bs, n_splits, err)
+    assert torch.isfinite(got).all() and err < 2e-2, (seq_new, seq_seen, hq, hkv, d, bs, n_splits, decode, err)
 
 
 def test_mixed_prefill_and_decode_gqa():
@@ -53,6 +53,16 @@ def test_split_kv_decode():
     # decode over long contexts with the KV range of every atom cut into 4 and 7 slices (some slices empty for short sequences)
     _check(seq_new=[1, 1, 1], seq_seen=[2000, 130, 3], hq=8, hkv=1, d=128, bs=128, n_splits=4, seed=3)
     _check(seq_new=[1, 40], seq_seen=[900, 500], hq=8, hkv=1, d=128, bs=128, n_splits=7, seed=4)
+
+
+def test_transposed_decode_kernel():
+    # keys on the MMA M axis, 16 q rows per atom: pure decode batches (GQA 8:1, 4:1, MHA), with and without KV splits ...
+    _check(seq_new=[1] * 6, seq_seen=[0, 1, 127, 128, 700, 2049], hq=8, hkv=1, d=128, bs=128, seed=5, decode=True, n_splits=1)
+    _check(seq_new=[1] * 5, seq_seen=[3000, 130, 3, 511, 512], hq=16, hkv=4, d=128, bs=64, seed=6, decode=True, n_splits=3)
+    _check(seq_new=[1, 1, 1], seq_seen=[300, 5, 1000], hq=4, hkv=4, d=128, bs=128, seed=7, decode=True)
+    # ... and forced onto a mixed batch: prefill chunks are cut into atoms of 16 / group tokens, still exact
+    _check(seq_new=[37, 1, 9], seq_seen=[100, 640, 0], hq=8, hkv=1, d=128, bs=128, seed=8, decode=True, n_splits=2)
+    _check(seq_new=[40, 1], seq_seen=[250, 17], hq=8, hkv=8, d=128, bs=32, seed=9, decode=True)
 
 
 def test_dispatch_uses_flash_kernel_and_falls_back():
