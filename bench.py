@@ -35,6 +35,14 @@ def parse():
     p.add_argument("--no-act-ckpt", action="store_true")
     p.add_argument("--zero-stage", type=int, default=3)
     p.add_argument("--zeropp", action="store_true", help="ZeRO++: zero_quantized_weights + zero_quantized_gradients (config #2, second half)")
+    p.add_argument("--workload", default="llama7b", choices=["llama7b", "fastgen70b", "mixtral", "ulysses13b"],
+                   help="llama7b = the headline (config #2); the others are the end-to-end runs of configs #5 / #4 / #3 (bench_workloads.py)")
+    p.add_argument("--quant", default="", help="fastgen70b: '' (bf16) | wf8af8_mx | wf8af8_block | wf8af8")
+    p.add_argument("--sequences", type=int, default=64, help="fastgen70b: concurrent sequences")
+    p.add_argument("--prompt-min", type=int, default=256)
+    p.add_argument("--prompt-max", type=int, default=1024)
+    p.add_argument("--token-budget", type=int, default=2048, help="fastgen70b: tokens per forward (ragged batch size)")
+    p.add_argument("--gen-tokens", type=int, default=16, help="fastgen70b: decode steps per timed step")
     p.add_argument("--local_rank", type=int, default=-1)
     p.add_argument("--ref-child", action="store_true", help="internal: run one reference configuration in this process")
     return p.parse_args()
@@ -372,6 +380,12 @@ def main():
     os.environ.setdefault("LOCAL_RANK", "0")
     os.environ.setdefault("WORLD_SIZE", "1")
     os.environ.setdefault("LOCAL_SIZE", os.environ["WORLD_SIZE"])
+    if args.workload != "llama7b":
+        if args.impl == "reference":
+            print(json.dumps({"impl": "reference", "unavailable": f"no reference arm for --workload {args.workload} (see the line's reference_arm note)"}))
+            return
+        import bench_workloads
+        return bench_workloads.WORKLOADS[args.workload](args)
     if args.impl == "reference":
         if int(os.environ["WORLD_SIZE"]) == 1 and not args.ref_child and not args.no_act_ckpt:
             run_reference_best_of(args)

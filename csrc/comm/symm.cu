@@ -70,6 +70,31 @@ __global__ void barrier_kernel(Peers peers, size_t flag_off, int rank, int world
   __threadfence_system();
 }
 
+// Graph-capturable form: the epoch is a counter in this rank's LOCAL memory, advanced by the kernel itself (one CTA: every thread
+// reads it before the block barrier, thread 0 writes it after), so a captured barrier replays correctly.  Every rank must issue
+// these barriers in the same order on one stream (or capture them in one graph); their flag pad is separate from the host-epoch one.
+__global__ void barrier_dev_kernel(Peers peers, size_t flag_off, int rank, int world, uint32_t* epoch_ctr) {
+  __threadfence_system();
+  const int t = threadIdx.x;
+  const uint32_t epoch = *epoch_ctr + 1;
+  if (t < world) {
+    uint32_t* remote = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(peers.ptr[t]) + flag_off) + rank;
+    asm volatile("red.release.sys.global.max.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+    const uint32_t* local = reinterpret_cast<const uint32_t*>(static_cast<uint8_t*>(peers.ptr[rank]) + flag_off) + t;
+    uint32_t spins = 0;
+    while (static_cast<int32_t>(ld_acquire_sys(local) - epoch) < 0) {
+      if (++spins > DSB_SPIN_LIMIT) {
+        printf("dsb200: cross-GPU barrier (device epoch) timed out on rank %d waiting for rank %d (epoch %u)\n", rank, t, epoch);
+        __trap();
+      }
+      __nanosleep(64);
+    }
+  }
+  __syncthreads();
+  if (t == 0) *epoch_ctr = epoch;
+  __threadfence_system();
+}
+
 // ---------------------------------------------------------------- all-gather (pull): out[p*n .. (p+1)*n) = peer p's shard
 // `src_off` = byte offset of the shard inside each rank's symmetric buffer; dst is local memory (any allocation).
 __global__ void allgather_pull_kernel(Peers peers, size_t src_off, uint8_t* __restrict__ dst, size_t bytes_per_rank, int rank,
@@ -676,6 +701,18 @@ DSB_EXPORT int dsb200_symm_barrier(void* const* peer_ptrs, long long flag_off, i
   int rc = make_peers(&P, peer_ptrs, world);
   if (rc) return rc;
   barrier_kernel<<<1, 32, 0, stream>>>(P, static_cast<size_t>(flag_off), rank, world, epoch, nullptr);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  return DSB_OK;
+}
+
+// flag_off: a pad of `world` uint32 used ONLY by device-epoch barriers (zero-initialised); epoch_ctr: local device uint32
+DSB_EXPORT int dsb200_symm_barrier_dev(void* const* peer_ptrs, long long flag_off, int rank, int world, unsigned int* epoch_ctr,
+                                       cudaStream_t stream) {
+  Peers P;
+  int rc = make_peers(&P, peer_ptrs, world);
+  if (rc) return rc;
+  DSB_REQUIRE(epoch_ctr != nullptr, "symm_barrier_dev: epoch counter missing");
+  barrier_dev_kernel<<<1, 32, 0, stream>>>(P, static_cast<size_t>(flag_off), rank, world, epoch_ctr);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }

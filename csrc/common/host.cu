@@ -66,10 +66,21 @@ int make_tensor_map(CUtensorMap* out, TmaDtype dt, int rank, const void* base, c
     estr[i] = 1;
     if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
   }
-  CUresult r = enc(out, cdt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims, gstr, gbox, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   sw == TMA_SW_128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  auto encode = [&] {
+    return enc(out, cdt, static_cast<cuuint32_t>(rank), const_cast<void*>(base), gdims, gstr, gbox, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+               sw == TMA_SW_128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  CUresult r = encode();
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // a thread that has made no runtime call yet (an autograd worker running its first backward) has no current context:
+    // bind the primary context of the device that owns `base`, then retry
+    cudaPointerAttributes attr;
+    if (cudaPointerGetAttributes(&attr, base) == cudaSuccess && attr.type == cudaMemoryTypeDevice) cudaSetDevice(attr.device);
+    cudaFree(nullptr);
+    (void)cudaGetLastError();
+    r = encode();
+  }
   if (r != CUDA_SUCCESS) {
     set_last_error("cuTensorMapEncodeTiled failed (%d): rank=%d base=%p dims=[%llu,%llu,..] stride1=%llu box=[%u,%u]",
                    (int)r, rank, base, (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0),

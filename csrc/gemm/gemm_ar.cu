@@ -39,6 +39,10 @@ struct Params {
   unsigned long long part_off;  // byte offset of the [M][N] bf16 partial buffer of this call's parity
   unsigned long long flag_off;  // byte offset of the uint32 flags[tiles]
   uint32_t epoch;
+  // graph-capturable form: the epoch is read from device memory (bumped by a one-thread kernel in front of this one) and picks
+  // the partial area by its parity: part_off (even) / part_off_alt (odd).  nullptr: `epoch` / `part_off` as given by the host.
+  const uint32_t* epoch_ptr;
+  unsigned long long part_off_alt;
   int rank, world;
   __nv_bfloat16* out;
   int ldo;
@@ -48,6 +52,11 @@ struct Params {
 };
 
 __device__ __forceinline__ void wait_lean(uint64_t* bar, uint32_t parity) { mbar_wait_lean(bar, parity); }
+__device__ __forceinline__ uint32_t cur_epoch(const Params& p) { return p.epoch_ptr ? *p.epoch_ptr : p.epoch; }
+__device__ __forceinline__ unsigned long long cur_part_off(const Params& p) {
+  return (p.epoch_ptr && (*p.epoch_ptr & 1u)) ? p.part_off_alt : p.part_off;
+}
+__global__ void bump_epoch_kernel(uint32_t* ctr) { *ctr += 1; }
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -77,6 +86,7 @@ __device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int
   constexpr int VEC_PER_ROW = BN / 8;
   constexpr int NW = W;
   constexpr int world = W;
+  const unsigned long long part_off = cur_part_off(p);
 #pragma unroll 1
   for (int v0 = rt; v0 < BM * VEC_PER_ROW; v0 += RED_THREADS * U) {
     uint4 part[U][NW];
@@ -94,7 +104,7 @@ __device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int
     for (int k = 0; k < NW; ++k) {
       if (k < world) {
         const int src = (k + p.rank) % world;
-        const uint8_t* base = static_cast<const uint8_t*>(p.peer[src]) + p.part_off;
+        const uint8_t* base = static_cast<const uint8_t*>(p.peer[src]) + part_off;
 #pragma unroll
         for (int u = 0; u < U; ++u)
           if (ok[u]) part[u][k] = ld_peer_v4(base + static_cast<size_t>(off[u]) * 16);
@@ -124,11 +134,12 @@ __device__ __forceinline__ void reduce_tile(const Params& p, int m0, int n0, int
 
 // Any world size: one vector at a time, peers summed in arrival order of the loads the compiler can keep in flight.
 __device__ __noinline__ void reduce_tile_any(const Params& p, int m0, int n0, int rt) {
+  const unsigned long long part_off = cur_part_off(p);
   for (int v = rt; v < BM * (BN / 8); v += RED_THREADS) {
     const int r = v / (BN / 8), cv = v - r * (BN / 8);
     const int gr = m0 + r, gc = n0 + cv * 8;
     if (gr >= p.row_hi || gr < p.row_lo || gc >= p.N) continue;
-    const size_t off = p.part_off + (static_cast<size_t>(gr) * p.N + gc) * 2;
+    const size_t off = part_off + (static_cast<size_t>(gr) * p.N + gc) * 2;
     const size_t lr = static_cast<size_t>(gr - p.row_lo);
     float a[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     for (int k = 0; k < p.world; ++k) acc_bf16x8(a, ld_peer_v4(static_cast<const uint8_t*>(p.peer[(k + p.rank) % p.world]) + off));
@@ -144,7 +155,7 @@ __device__ __noinline__ void reduce_tile_any(const Params& p, int m0, int n0, in
 
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmP, const __grid_constant__ Params p) {
+               const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmP1, const __grid_constant__ Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* epi_buf = smem + STAGES * STAGE_BYTES;
@@ -157,11 +168,14 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int num_kb = (p.K + BK - 1) / BK;
+  const uint32_t epoch = cur_epoch(p);
+  const CUtensorMap* tmPart = (p.epoch_ptr && (epoch & 1u)) ? &tmP1 : &tmP;  // partial area of this call's parity
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     tma_prefetch_desc(&tmP);
+    tma_prefetch_desc(&tmP1);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -284,7 +298,7 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         fence_proxy_async_smem();
         named_bar_sync(1, EPI_THREADS);
         if (epi_tid == 0) {
-          tma_store_2d(&tmP, buf, n0 + c * CW, m0);
+          tma_store_2d(tmPart, buf, n0 + c * CW, m0);
           tma_commit_group();
         }
         ++buf_idx;
@@ -292,7 +306,7 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (epi_tid == 0) {
         tma_wait_group<0>();      // every byte of this tile's partial has been written
         __threadfence_system();
-        st_release_sys(my_flags + tile, p.epoch);
+        st_release_sys(my_flags + tile, epoch);
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
@@ -308,9 +322,9 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (rt < p.world) {
         const uint32_t* f = reinterpret_cast<const uint32_t*>(static_cast<const uint8_t*>(p.peer[rt]) + p.flag_off) + tile;
         uint32_t spins = 0;
-        while (static_cast<int32_t>(ld_acquire_sys(f) - p.epoch) < 0) {
+        while (static_cast<int32_t>(ld_acquire_sys(f) - epoch) < 0) {
           if (++spins > DSB_SPIN_LIMIT) {
-            printf("dsb200: GEMM-allreduce rank %d timed out waiting for tile %d of rank %d (epoch %u)\n", p.rank, tile, rt, p.epoch);
+            printf("dsb200: GEMM-allreduce rank %d timed out waiting for tile %d of rank %d (epoch %u)\n", p.rank, tile, rt, epoch);
             __trap();
           }
           __nanosleep(32);
@@ -344,7 +358,7 @@ gemm_ar_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 //   * flags: ceil(M/128)*ceil(N/256) uint32, zero-initialised once (flag_off, 4-byte aligned)
 // and passes the same, strictly increasing `epoch` (>= 1) on every rank for each call.  N must be a multiple of 8.
 static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off, unsigned int epoch,
-                          void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo, int ldr, int rank, int world,
+                          unsigned int* epoch_ctr, long long part_off_alt, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo, int ldr, int rank, int world,
                           int row_lo, int row_hi, int max_ctas, cudaStream_t stream) {
   using namespace dsb;
   namespace G = gemm_ar;
@@ -352,9 +366,10 @@ static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, 
   DSB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_ar: empty problem M=%d N=%d K=%d", M, N, K);
   DSB_REQUIRE(world >= 1 && world <= G::MAX_RANKS && rank >= 0 && rank < world, "gemm_ar: rank %d / world %d", rank, world);
   DSB_REQUIRE(N % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && ldo % 8 == 0, "gemm_ar: N, lda, ldb, ldo must be multiples of 8");
-  DSB_REQUIRE(part_off % 16 == 0 && flag_off % 4 == 0 && epoch >= 1, "gemm_ar: part_off must be 16-byte aligned, flag_off 4-byte, epoch >= 1");
+  DSB_REQUIRE(part_off % 16 == 0 && part_off_alt % 16 == 0 && flag_off % 4 == 0 && (epoch >= 1 || epoch_ctr != nullptr),
+              "gemm_ar: part_off must be 16-byte aligned, flag_off 4-byte, epoch >= 1");
   DSB_REQUIRE(residual == nullptr || ldr % 8 == 0, "gemm_ar: ldr must be a multiple of 8");
-  CUtensorMap tmA, tmB, tmP;
+  CUtensorMap tmA, tmB, tmP, tmP1;
   int rc = make_tensor_map_2d(&tmA, TMA_BF16, A, M, K, lda, G::BM, G::BK, TMA_SW_128);
   if (rc) return rc;
   rc = make_tensor_map_2d(&tmB, TMA_BF16, B, N, K, ldb, G::BN, G::BK, TMA_SW_128);
@@ -362,6 +377,9 @@ static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, 
   // the partial tiles are stored into THIS rank's own buffer (the tensor map covers local memory only)
   void* my_part = static_cast<uint8_t*>(peer_ptrs[rank]) + part_off;
   rc = make_tensor_map_2d(&tmP, TMA_BF16, my_part, M, N, N, G::BM, 64, TMA_SW_128);
+  if (rc) return rc;
+  void* my_part1 = static_cast<uint8_t*>(peer_ptrs[rank]) + (epoch_ctr ? part_off_alt : part_off);
+  rc = make_tensor_map_2d(&tmP1, TMA_BF16, my_part1, M, N, N, G::BM, 64, TMA_SW_128);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
@@ -378,6 +396,8 @@ static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, 
   p.part_off = static_cast<unsigned long long>(part_off);
   p.flag_off = static_cast<unsigned long long>(flag_off);
   p.epoch = epoch;
+  p.epoch_ptr = epoch_ctr;
+  p.part_off_alt = static_cast<unsigned long long>(part_off_alt);
   p.rank = rank;
   p.world = world;
   p.out = static_cast<__nv_bfloat16*>(out);
@@ -390,7 +410,8 @@ static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, 
   int cap = num_sms();
   if (max_ctas > 0 && max_ctas < cap) cap = max_ctas;
   if (grid > cap) grid = cap;
-  G::gemm_ar_kernel<<<grid, G::NUM_THREADS, G::SMEM_TOTAL, stream>>>(tmA, tmB, tmP, p);
+  if (epoch_ctr) G::bump_epoch_kernel<<<1, 1, 0, stream>>>(epoch_ctr);
+  G::gemm_ar_kernel<<<grid, G::NUM_THREADS, G::SMEM_TOTAL, stream>>>(tmA, tmB, tmP, tmP1, p);
   DSB_CHECK_CUDA(cudaGetLastError());
   return DSB_OK;
 }
@@ -398,8 +419,8 @@ static int launch_gemm_ar(const void* A, const void* B, void* const* peer_ptrs, 
 DSB_EXPORT int dsb200_gemm_ar_bf16(const void* A, const void* B, void* const* peer_ptrs, long long part_off, long long flag_off,
                                    unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo,
                                    int ldr, int rank, int world, int max_ctas, cudaStream_t stream) {
-  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world, 0, M, max_ctas,
-                        stream);
+  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, nullptr, part_off, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world,
+                        0, M, max_ctas, stream);
 }
 
 // GEMM -> reduce-scatter over rows (sequence-parallel tensor parallelism): same kernel, but this rank reduces and writes only rows
@@ -409,6 +430,19 @@ DSB_EXPORT int dsb200_gemm_rs_bf16(const void* A, const void* B, void* const* pe
                                    unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb, int ldo,
                                    int ldr, int rank, int world, int row_lo, int row_hi, int max_ctas, cudaStream_t stream) {
   DSB_REQUIRE(row_hi > row_lo, "gemm_rs: rank %d owns no rows", rank);
-  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world, row_lo, row_hi,
-                        max_ctas, stream);
+  return launch_gemm_ar(A, B, peer_ptrs, part_off, flag_off, epoch, nullptr, part_off, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world,
+                        row_lo, row_hi, max_ctas, stream);
+}
+
+// Graph-capturable forms: the epoch lives in device memory (`epoch_ctr`, one uint32 of LOCAL memory per rank, all ranks start it at
+// the same value); every call bumps it with a one-thread kernel in front of the GEMM, and the GEMM picks the partial area
+// part_off0 / part_off1 by the bumped value's parity.  A captured call therefore replays correctly any number of times.
+// row_lo = 0, row_hi = M: all-reduce; a sub-range: reduce-scatter over rows.
+DSB_EXPORT int dsb200_gemm_ar_bf16_dev(const void* A, const void* B, void* const* peer_ptrs, long long part_off0, long long part_off1,
+                                       long long flag_off, unsigned int* epoch_ctr, void* out, const void* residual, int M, int N, int K,
+                                       int lda, int ldb, int ldo, int ldr, int rank, int world, int row_lo, int row_hi, int max_ctas,
+                                       cudaStream_t stream) {
+  DSB_REQUIRE(epoch_ctr != nullptr && row_hi > row_lo, "gemm_ar_dev: epoch counter missing or empty row range");
+  return launch_gemm_ar(A, B, peer_ptrs, part_off0, flag_off, 0, epoch_ctr, part_off1, out, residual, M, N, K, lda, ldb, ldo, ldr, rank, world,
+                        row_lo, row_hi, max_ctas, stream);
 }

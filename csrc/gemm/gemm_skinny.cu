@@ -1,0 +1,215 @@
+// Skinny GEMM for decode steps: out[M, N] = x[M, K] w[N, K]^T with few rows (M <= 128 tokens) and a large weight matrix.
+//
+// The op is a read of the weights; what matters is that all 148 SMs stream them.  The square-tile kernels put 128 tokens x
+// 256 features on a CTA: a 5120-feature projection of a 16-token batch is 20 CTAs, 1/7 of the machine.  Here the roles are
+// swapped and K is split:
+//     D^T [128 weight rows x NT tokens] += W_tile [128 x 64] (A, smem, K-major)  x  X_tile^T [NT x 64] (B, smem, K-major)
+// grid = (ceil(N / 128), splits): every CTA streams a [128 x K/splits] slab of W through a 6-8 stage TMA ring (16 KB of W per
+// stage -> ~100 KB in flight per SM) and issues 4 tcgen05.mma (M = 128, N = NT, K = 16) per stage; the accumulator is
+// [128 lanes x NT columns] of TMEM.  splits == 1: the epilogue writes bf16 out[token][feature] directly; otherwise fp32
+// partials go to a workspace [split][token][feature] and a second kernel sums them.  NT = 16 / 32 / 64 / 128 (rows past M are
+// TMA zero fill: they cost no HBM traffic).
+#include "../common/host.h"
+#include "../common/ptx.cuh"
+
+namespace dsb {
+namespace skinny {
+
+constexpr int BW = 128;  // weight rows per CTA (MMA M)
+constexpr int BK = 64;   // k elements per stage (one 128-byte swizzle row)
+constexpr int NUM_THREADS = 192;  // TMA warp, MMA warp, 4 epilogue warps
+
+template <int NT>
+struct Smem {
+  static constexpr int STAGES = NT == 128 ? 6 : 8;  // 6 x 32 KB / 8 x (16 KB + the token tile)
+  static constexpr int W_BYTES = BW * BK * 2;
+  static constexpr int X_BYTES = NT * BK * 2;
+  static constexpr int X_STRIDE = (X_BYTES + 1023) / 1024 * 1024;  // tiles stay 1024-byte aligned (128-byte swizzle atoms)
+  static constexpr int STAGE = W_BYTES + X_STRIDE;
+  static constexpr int BAR_OFF = STAGES * STAGE;
+  static constexpr int TOTAL = BAR_OFF + 256 + 1024;
+};
+
+struct Params {
+  int M, N, K;
+  int kb_per_split, kb_total;
+  __nv_bfloat16* out;  // [M][ldo] (splits == 1)
+  int ldo;
+  float* ws;           // [splits][M][N] (splits > 1)
+};
+
+template <int NT>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const Params p) {
+  using SM = Smem<NT>;
+  constexpr int STAGES = SM::STAGES;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + SM::BAR_OFF);
+  uint64_t* empty = full + STAGES;
+  uint64_t* done = empty + STAGES;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(done + 1);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BW;
+  const int split = blockIdx.y;
+  const int kb0 = split * p.kb_per_split;
+  const int kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+  const int nkb = max(0, kb1 - kb0);
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmX);
+    for (int i = 0; i < STAGES; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  constexpr int TM_COLS = NT < 32 ? 32 : NT;
+  if (warp == 1) {
+    tmem_alloc<1>(tmem_ptr, TM_COLS);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tm = *tmem_ptr;
+
+  if (nkb > 0) {
+    if (warp == 0) {
+      if (lane == 0) {
+        int st = 0, ph = 0;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty[st], ph ^ 1);
+          mbar_expect_tx(&full[st], SM::W_BYTES + SM::X_BYTES);
+          uint8_t* base = smem + st * SM::STAGE;
+          tma_load_2d(&tmW, &full[st], base, kb * BK, n0);
+          tma_load_2d(&tmX, &full[st], base + SM::W_BYTES, kb * BK, 0);
+          if (++st == STAGES) { st = 0; ph ^= 1; }
+        }
+      }
+    } else if (warp == 1) {
+      const bool leader = elect_one();
+      constexpr uint32_t idesc = umma_idesc(BW, NT, 1, 1, 0, 0);
+      const uint32_t tmu = __shfl_sync(0xffffffffu, tm, 0);
+      const uint64_t w_desc0 = umma_smem_desc(smem_u32(smem), 16, 1024);
+      const uint64_t x_desc0 = umma_smem_desc(smem_u32(smem + SM::W_BYTES), 16, 1024);
+      int st = 0, ph = 0;
+      for (int i = 0; i < nkb; ++i) {
+        mbar_wait_lean(&full[st], ph);
+        tc_fence_after();
+        if (leader) {
+          const uint32_t so = static_cast<uint32_t>((st * SM::STAGE) >> 4);
+#pragma unroll
+          for (int kk = 0; kk < BK / 16; ++kk)
+            umma_f16<1>(tmu, w_desc0 + so + static_cast<uint32_t>((kk * 32) >> 4), x_desc0 + so + static_cast<uint32_t>((kk * 32) >> 4), idesc,
+                        (i | kk) != 0 ? 1u : 0u);
+          umma_commit<1>(&empty[st]);
+          if (i == nkb - 1) umma_commit<1>(done);
+        }
+        if (++st == STAGES) { st = 0; ph ^= 1; }
+      }
+    } else {
+      // epilogue: thread == weight row (TMEM lane); a warp's 32 rows are 32 consecutive output features of one token
+      const int q4 = warp & 3;
+      const int n = n0 + q4 * 32 + lane;
+      mbar_wait(done, 0);
+      tc_fence_after();
+      const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
+#pragma unroll
+      for (int c = 0; c < NT / 16; ++c) {
+        uint32_t v[16];
+        tmem_ld_32x16(tm + c * 16 + lane_off, v);
+        tmem_ld_wait();
+        if (n < p.N) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int t = c * 16 + i;
+            if (t < p.M) {
+              if (p.ws != nullptr) p.ws[(static_cast<size_t>(split) * p.M + t) * p.N + n] = __uint_as_float(v[i]);
+              else p.out[static_cast<size_t>(t) * p.ldo + n] = __float2bfloat16_rn(__uint_as_float(v[i]));
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= 2 && p.ws != nullptr) {
+    // this split has no k-blocks (K shorter than the split grid): its partial is zero
+    const int n = n0 + (warp & 3) * 32 + lane;
+    if (n < p.N)
+      for (int t = 0; t < p.M; ++t) p.ws[(static_cast<size_t>(split) * p.M + t) * p.N + n] = 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tm, TM_COLS);
+  }
+}
+
+// out[t][n] = sum_s ws[s][t][n]; 4 features per thread
+__global__ void skinny_reduce_kernel(const float* __restrict__ ws, __nv_bfloat16* __restrict__ out, int M, int N, int ldo, int splits) {
+  const long long i4 = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= static_cast<long long>(M) * N) return;
+  const int t = static_cast<int>(i4 / N), n = static_cast<int>(i4 - static_cast<long long>(t) * N);
+  float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int s = 0; s < splits; ++s) {
+    const float4 v = *reinterpret_cast<const float4*>(ws + (static_cast<size_t>(s) * M + t) * N + n);
+    a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w;
+  }
+  __nv_bfloat16* o = out + static_cast<size_t>(t) * ldo + n;
+  *reinterpret_cast<uint2*>(o) = make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w));
+}
+
+template <int NT>
+static int launch(const void* x, const void* w, void* out, float* ws, int M, int N, int K, int ldx, int ldw, int ldo, int splits,
+                  cudaStream_t stream) {
+  using SM = Smem<NT>;
+  CUtensorMap tmW, tmX;
+  int rc = make_tensor_map_2d(&tmW, TMA_BF16, w, N, K, ldw, BW, BK, TMA_SW_128);
+  if (rc) return rc;
+  rc = make_tensor_map_2d(&tmX, TMA_BF16, x, M, K, ldx, NT, BK, TMA_SW_128);
+  if (rc) return rc;
+  auto kern = skinny_kernel<NT>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
+    attr_set = true;
+  }
+  Params p;
+  p.M = M; p.N = N; p.K = K;
+  p.kb_total = (K + BK - 1) / BK;
+  p.kb_per_split = (p.kb_total + splits - 1) / splits;
+  p.out = static_cast<__nv_bfloat16*>(out);
+  p.ldo = ldo;
+  p.ws = splits > 1 ? ws : nullptr;
+  dim3 grid((N + BW - 1) / BW, splits);
+  kern<<<grid, NUM_THREADS, SM::TOTAL, stream>>>(tmW, tmX, p);
+  DSB_CHECK_CUDA(cudaGetLastError());
+  if (splits > 1) {
+    const long long quads = static_cast<long long>(M) * N / 4;
+    skinny_reduce_kernel<<<static_cast<unsigned>((quads + 255) / 256), 256, 0, stream>>>(ws, static_cast<__nv_bfloat16*>(out), M, N, ldo, splits);
+    DSB_CHECK_CUDA(cudaGetLastError());
+  }
+  return DSB_OK;
+}
+
+}  // namespace skinny
+}  // namespace dsb
+
+// out[M][N] (bf16, row stride ldo) = x[M][K] w[N][K]^T, bf16 operands, M <= 128.  splits >= 1 cuts K; with splits > 1 the caller
+// passes a workspace of splits * M * N floats and N must be a multiple of 4.  K, ldx, ldw multiples of 8 (16-byte rows for TMA).
+DSB_EXPORT int dsb200_gemm_skinny_bf16(const void* x, const void* w, void* out, void* workspace, int M, int N, int K, int ldx, int ldw,
+                                       int ldo, int splits, cudaStream_t stream) {
+  using namespace dsb;
+  DSB_REQUIRE(M >= 1 && M <= 128 && N >= 1 && K >= 1, "gemm_skinny: M=%d (1..128) N=%d K=%d", M, N, K);
+  DSB_REQUIRE(K % 8 == 0 && ldx % 8 == 0 && ldw % 8 == 0, "gemm_skinny: K, ldx, ldw must be multiples of 8");
+  DSB_REQUIRE(splits >= 1 && (splits == 1 || (workspace != nullptr && N % 4 == 0 && ldo % 4 == 0)),
+              "gemm_skinny: splits=%d needs a workspace and N, ldo multiples of 4", splits);
+  float* ws = static_cast<float*>(workspace);
+  if (M <= 16) return skinny::launch<16>(x, w, out, ws, M, N, K, ldx, ldw, ldo, splits, stream);
+  if (M <= 32) return skinny::launch<32>(x, w, out, ws, M, N, K, ldx, ldw, ldo, splits, stream);
+  if (M <= 64) return skinny::launch<64>(x, w, out, ws, M, N, K, ldx, ldw, ldo, splits, stream);
+  return skinny::launch<128>(x, w, out, ws, M, N, K, ldx, ldw, ldo, splits, stream);
+}

@@ -78,7 +78,8 @@ class InferenceEngineV2:
             descs.append(seq)
         self._batch.finalize()
         with torch.no_grad():
-            logits = self._model.forward(self._batch, self._state_manager)
+            run = getattr(self._model, "forward_graphed", self._model.forward)  # decode steps replay a CUDA graph
+            logits = run(self._batch, self._state_manager)
         for seq in descs:
             seq.post_forward()
         return logits

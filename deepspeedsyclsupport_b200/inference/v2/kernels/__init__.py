@@ -113,12 +113,12 @@ def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv,
     return out
 
 
-def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None):
+def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, decode=None):
     scale = scale if scale is not None else 1.0 / math.sqrt(d)
     if not qkv.is_cuda:
         return paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale)
     if paged_flash_supported(qkv, kv_cache, hq, hkv, d):
-        return paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, max_context=max_context)
+        return paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, max_context=max_context, decode=decode)
     # head sizes the tensor-core kernel does not cover (96, 256): CUDA-core kernel, one CTA per (token, kv head)
     T = qkv.shape[0]
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)

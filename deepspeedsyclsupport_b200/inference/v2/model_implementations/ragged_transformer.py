@@ -15,6 +15,8 @@ import re
 from dataclasses import dataclass, field
 from typing import Optional
 
+import os
+
 import torch
 
 from .... import comm as dist
@@ -208,6 +210,8 @@ class RaggedTransformer:
         self.engine_config = engine_config
         self.tp_group = tp_group
         self.tp = dist.get_world_size(tp_group) if (tp_group is not None and dist.is_initialized()) else 1
+        self._graphs, self._graph_warm, self._graph_pool = {}, {}, None  # decode-step CUDA graphs by batch size (forward_graphed)
+        self._graphs_on = os.environ.get("DSB200_FASTGEN_GRAPHS", "1") != "0"
         self.rank = dist.get_rank(tp_group) if self.tp > 1 else 0
         self.dtype = dtype
         self.device = device or torch.device("cpu")
@@ -423,6 +427,41 @@ class RaggedTransformer:
         if self.moe_mod is not None:
             return self.moe_mod(h, L["router_w"], L["experts_gu"], L["experts_dn"])
         return self.mlp2_lin(self.mlp1_lin(h, L["mlp1_w"], L.get("mlp1_b")), L["mlp2_w"])
+
+    def forward_graphed(self, batch, state_manager):
+        """`forward`, with pure decode steps (one new token per sequence) replayed from a CUDA graph per batch size.
+
+        A decode step of a deep model is ~12 small launches per layer; issued one by one from Python they cost more host time than
+        the GPU needs to run them.  Everything a step reads sits at fixed device addresses (the ragged batch's metadata buffers,
+        the KV cache, the weights, the symmetric buffers; the epochs of the peer-memory collectives live in device memory), so
+        the launch sequence of a step with n sequences is captured once -- after two eager steps of that size -- and replayed.
+        Prefill / mixed batches run eagerly.  DSB200_FASTGEN_GRAPHS=0 turns this off."""
+        n = batch.current_sequences
+        if not (self._graphs_on and n == batch.current_tokens and n > 0 and batch.input_ids().is_cuda):
+            return self.forward(batch, state_manager)
+        entry = self._graphs.get(n)
+        if entry is None:
+            seen = self._graph_warm.get(n, 0)
+            if seen < 2:  # lazily built state (tensor maps, split heuristics, module buffers) settles in eager mode first
+                self._graph_warm[n] = seen + 1
+                return self.forward(batch, state_manager)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            try:
+                with torch.cuda.graph(g, pool=self._graph_pool):
+                    out = self.forward(batch, state_manager)
+            except Exception as e:  # something on this model's path is not capturable: stay eager from now on
+                from ....utils.logging import logger
+                logger.warning(f"FastGen decode step could not be captured into a CUDA graph ({type(e).__name__}: {e}); running eagerly")
+                self._graphs_on = False
+                torch.cuda.synchronize()
+                return self.forward(batch, state_manager)
+            if self._graph_pool is None:
+                self._graph_pool = g.pool()
+            entry = self._graphs[n] = (g, out)
+        g, out = entry
+        g.replay()
+        return out.clone()  # the graph's output buffer is rewritten by the next replay
 
     def forward(self, batch, state_manager):
         """batch: RaggedBatchWrapper (finalized).  Returns logits [n_seqs, vocab] for the last token of every sequence."""

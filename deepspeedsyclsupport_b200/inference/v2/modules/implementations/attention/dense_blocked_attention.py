@@ -71,4 +71,5 @@ class DSDenseBlockedAttention(DSSelfAttentionBase):
         freqs = self._freqs(q_k_v.device, inv_freqs) if self._rotary else None
         K.kv_rotary_append(q_k_v, kv_cache, tok_seq, tok_pos, bt, freqs, c.n_heads_q, c.n_heads_kv, c.head_size,
                            rot_dim=self._rot_dim if self._rotary else 0)
-        return K.paged_attention(q_k_v, kv_cache, tok_seq, tok_pos, bt, c.n_heads_q, c.n_heads_kv, c.head_size, self._scale)
+        return K.paged_attention(q_k_v, kv_cache, tok_seq, tok_pos, bt, c.n_heads_q, c.n_heads_kv, c.head_size, self._scale,
+                                 decode=batch.current_tokens <= 2 * batch.current_sequences)

@@ -9,6 +9,8 @@ projection of every layer, and all-gather the vocab-parallel logits (inference/v
   add the residual).  For many tokens on many ranks the one-shot pull moves (W-1) x the output per rank, so from
   `two_shot_min_rows` rows on (and W >= 4) the reduce-scatter form of the kernel is used -- every rank reduces 1/W of the rows --
   followed by a multicast-store all-gather of the row blocks through the switch (csrc/comm/symm.cu nvls_allgather_kernel).
+  Decode-sized calls (<= 128 rows) are a read of the weight shard: they take the weight-streaming GEMM (every SM, split K)
+  into the symmetric staging area + an in-place switch reduction instead.
 * `all_reduce(y)` for outputs produced by another kernel (fp8 / MoE GEMMs): in place through the switch
   (`multimem.ld_reduce` + `multimem.st`), or the one-shot pull kernel without a multicast mapping.
 * `gather_logits(local)`: every rank stores its vocabulary slice straight into all peers' logits buffers (multicast store, or
@@ -18,6 +20,7 @@ Every rank of the group must make the same sequence of calls (the engine's ranks
 import torch
 
 from ... import comm as dist
+from ...ops.gemm import gemm
 from ...parallel.fused import FusedGemmAllReduce
 from ...parallel.symm import SymmetricBuffer
 
@@ -38,11 +41,12 @@ class RaggedTPCollectives:
         act_bytes = _r256(max_tokens * hidden * 2)
         self._logit_off = self._act_off + act_bytes                    # [world][max_seqs][vocab_local] bf16
         self._logit_bytes = _r256(max_seqs * vocab_local * 2)
-        self.symm = SymmetricBuffer(group, self._logit_off + self.world * self._logit_bytes)
-        self.fused = FusedGemmAllReduce(self.symm, max_tokens, hidden, offset=0)
+        # epochs of the barriers and of the fused GEMMs live in device memory: a decode step captured into a CUDA graph replays
+        self.symm = SymmetricBuffer(group, self._logit_off + self.world * self._logit_bytes).use_device_epochs()
+        self.fused = FusedGemmAllReduce(self.symm, max_tokens, hidden, offset=0, device_epochs=True)
         self.symm.barrier()
         self.nvls = bool(self.symm.mc_ptr)
-        self.calls = {"fused_one_shot": 0, "fused_two_shot": 0, "all_reduce": 0, "gather_logits": 0}
+        self.calls = {"fused_one_shot": 0, "fused_two_shot": 0, "skinny_switch_reduce": 0, "all_reduce": 0, "gather_logits": 0}
 
     # ---- GEMM fused with its all-reduce
     def usable_for(self, x, w):
@@ -64,6 +68,15 @@ class RaggedTPCollectives:
             out = self.symm.view(self._act_off, (rows, self.hidden), torch.bfloat16).clone()
             self.symm.barrier()                               # staging may be overwritten by the next call
             return out
+        if rows <= 128 and self.nvls and (rows * self.hidden) % (8 * W) == 0 and w.shape[1] % 8 == 0:
+            # decode-sized: the op is a read of the weight shard.  The fused kernel's 128 x 256 output tiles put hidden/256 CTAs
+            # on it; the weight-streaming GEMM (csrc/gemm/gemm_skinny.cu) uses every SM and writes straight into the symmetric
+            # staging area, which the switch then reduces in place (multimem.ld_reduce + multicast store).
+            self.calls["skinny_switch_reduce"] += 1
+            stage = self.symm.view(self._act_off, (rows, self.hidden), torch.bfloat16)
+            gemm(x, w, out=stage)
+            self.symm.nvls_all_reduce_bf16(self._act_off, rows * self.hidden)  # barrier, reduce, barrier: nobody touches `stage` after it
+            return stage + residual if residual is not None else stage.clone()
         self.calls["fused_one_shot"] += 1
         return self.fused(x, w, residual=residual)
 

@@ -4,6 +4,7 @@ from dataclasses import dataclass
 
 import torch
 import torch.nn as nn
+import torch.utils.checkpoint
 
 from ..moe.layer import MoE
 from ..ops import fused_ops as FO
@@ -106,8 +107,12 @@ class MixtralForCausalLM(nn.Module):
     def forward(self, input_ids, labels=None):
         x = self.embed_tokens(input_ids)
         aux = 0.0
+        ckpt = self.cfg.activation_checkpointing and self.training and torch.is_grad_enabled()
         for layer in self.layers:
-            x, l_aux = layer(x)
+            if ckpt:  # per-layer recompute: the dispatched expert activations (capacity x 2 * intermediate per expert) are the bulk
+                x, l_aux = torch.utils.checkpoint.checkpoint(layer, x, use_reentrant=False)
+            else:
+                x, l_aux = layer(x)
             aux = aux + l_aux
         logits = linear(self.norm(x), self.lm_head)
         if labels is None:

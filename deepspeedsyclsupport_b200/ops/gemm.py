@@ -5,6 +5,8 @@ deepspeed/runtime/zero/linear.py:43-112 LinearFunctionForZeroStage3 -> cuBLAS). 
 dgrad and wgrad each map to one layout variant of the same kernel; wgrad can accumulate
 directly into an fp32 main-grad buffer with TMA reduce-add.
 """
+import os
+
 import torch
 
 from . import native
@@ -23,6 +25,10 @@ def _gemm_ref(a, b, a_mn, b_mn, out_dtype, out=None, accumulate=False):
     else:
         out.copy_(r.to(out.dtype))
     return out
+
+
+_SKINNY_ON = os.environ.get("DSB200_SKINNY_GEMM", "1") != "0"
+native.register_sigs({"dsb200_gemm_skinny_bf16": "pppp iii iii i p"})
 
 
 def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, accumulate=False, max_ctas=0):
@@ -45,6 +51,18 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
         out = torch.empty(M, ld, dtype=out_dtype, device=a.device)[:, :N]  # e.g. a vocabulary of 50257: padded rows, [M, N] view
     assert out.shape == (M, N) and out.stride(1) == 1
     f32 = out.dtype == torch.float32
+    if (M <= 128 and N >= 512 and not (a_mn or b_mn or accumulate or f32) and K % 8 == 0 and N % 4 == 0 and out.stride(0) % 4 == 0 and
+            a.stride(0) % 8 == 0 and b.stride(0) % 8 == 0 and _SKINNY_ON):
+        # decode-sized problem: weight-streaming kernel (swapped roles + split K) instead of 128 x 256 output tiles
+        tiles, kb = -(-N // 128), -(-K // 64)
+        splits = max(1, min(kb // 4, (148 if not max_ctas else max_ctas) // tiles)) if tiles < 148 else 1
+        ws = torch.empty(splits * M * N, dtype=torch.float32, device=a.device) if splits > 1 else None
+        rc = native.lib().dsb200_gemm_skinny_bf16(native.ptr(a), native.ptr(b), native.ptr(out), native.ptr(ws), M, N, K, a.stride(0), b.stride(0),
+                                                  out.stride(0), splits, native.stream_ptr())
+        native.check(rc)
+        if _prof._ACTIVE:
+            _prof.record_flops(2 * M * N * K, M * N * K, "dsb200_gemm_skinny_bf16")
+        return out
     mode = (2 if accumulate else 1) if f32 else (3 if accumulate else 0)
     rc = native.lib().dsb200_gemm_bf16(native.ptr(a), native.ptr(b), native.ptr(out), M, N, K, a.stride(0),
                                        b.stride(0), out.stride(0), int(a_mn), int(b_mn), mode, int(max_ctas),

@@ -15,6 +15,7 @@ from ..ops.gemm import gemm
 native.register_sigs({
     "dsb200_gemm_ag_bf16": "ppp iiiii p ll p i p",
     "dsb200_gemm_ar_bf16": "ppp ll i pp iii iiii ii i p",
+    "dsb200_gemm_ar_bf16_dev": "ppp lll p pp iii iiii ii ii i p",
     "dsb200_gemm_rs_bf16": "ppp ll i pp iii iiii ii ii i p",
 })
 
@@ -54,8 +55,11 @@ class FusedGemmAllReduce(object):
     `symm`: a SymmetricBuffer (or EmulatedPeers with world 1) holding, from `offset`: two partial areas of max_m * n * 2 bytes
     (double-buffered by call parity) followed by the per-tile flags.  Every rank must make the same sequence of calls."""
 
-    def __init__(self, symm, max_m, n, offset=0):
+    def __init__(self, symm, max_m, n, offset=0, device_epochs=False):
+        """device_epochs: keep the call counter in device memory (bumped by a one-thread kernel in front of every GEMM) so calls
+        captured into a CUDA graph replay correctly; the partial area is then picked on the device by the counter's parity."""
         self.symm, self.n, self.max_m = symm, n, max_m
+        self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=torch.device("cuda", torch.cuda.current_device())) if device_epochs else None
         self.part_bytes = (max_m * n * 2 + 255) // 256 * 256
         self.part_off = [offset, offset + self.part_bytes]
         self.flag_off = offset + 2 * self.part_bytes
@@ -81,9 +85,17 @@ class FusedGemmAllReduce(object):
         if out is None:
             out = torch.empty(hi - lo, N, dtype=torch.bfloat16, device=x.device)
         assert out.shape[0] == hi - lo and (residual is None or residual.shape[0] == hi - lo)
-        self.epoch += 1
         s = self.symm
         arr = (ctypes.c_void_p * s.world)(*s.ptrs)
+        if self._epoch_dev is not None:
+            rc = native.lib().dsb200_gemm_ar_bf16_dev(native.ptr(x), native.ptr(w_shard), ctypes.cast(arr, ctypes.c_void_p), self.part_off[0],
+                                                      self.part_off[1], self.flag_off, native.ptr(self._epoch_dev), native.ptr(out),
+                                                      native.ptr(residual), M, N, K, x.stride(0), w_shard.stride(0), out.stride(0),
+                                                      residual.stride(0) if residual is not None else 0, s.rank, s.world, int(lo), int(hi),
+                                                      int(max_ctas), native.stream_ptr())
+            native.check(rc)
+            return out
+        self.epoch += 1
         common = (native.ptr(x), native.ptr(w_shard), ctypes.cast(arr, ctypes.c_void_p), self.part_off[self.epoch & 1], self.flag_off, self.epoch,
                   native.ptr(out), native.ptr(residual), M, N, K, x.stride(0), w_shard.stride(0), out.stride(0),
                   residual.stride(0) if residual is not None else 0, s.rank, s.world)

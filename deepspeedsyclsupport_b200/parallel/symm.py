@@ -22,6 +22,7 @@ native.register_sigs({
     "dsb200_symm_close": "p",
     "dsb200_symm_free": "p",
     "dsb200_symm_barrier": "p l ii i p",
+    "dsb200_symm_barrier_dev": "p l ii p p",
     "dsb200_p2p_allgather": "p l p l iii p",
     "dsb200_p2p_alltoall": "p l p l iii p",
     "dsb200_p2p_reduce_scatter": "p l i p i l ii f i p i p",
@@ -281,8 +282,23 @@ class SymmetricBuffer(_PeerOps):
             self.ptrs.append(p.value)
             self._opened.append(p.value)
 
+    def use_device_epochs(self):
+        """Switch `barrier()` to the graph-capturable form: the epoch lives in a device counter that the barrier kernel advances
+        itself, so a barrier captured into a CUDA graph replays correctly.  For buffers whose barriers are all issued on ONE
+        stream in the same order on every rank (the FastGen tensor-parallel collectives); call it collectively before the
+        first use that must be capturable."""
+        if getattr(self, "_epoch_dev", None) is None:
+            self._epoch_dev = torch.zeros(1, dtype=torch.int32, device=self.device)
+        return self
+
     def barrier(self):
         """Device-side barrier across the group on the current stream (no host sync)."""
+        if getattr(self, "_epoch_dev", None) is not None:
+            # own flag pad (second half of the 4 KiB pad): device epochs and host epochs never mix on one set of flags
+            rc = native.lib().dsb200_symm_barrier_dev(ctypes.cast(self._table(), ctypes.c_void_p), self.nbytes + FLAG_PAD // 2, self.rank,
+                                                      self.world, native.ptr(self._epoch_dev), native.stream_ptr())
+            native.check(rc)
+            return
         self._epoch += 1
         rc = native.lib().dsb200_symm_barrier(ctypes.cast(self._table(), ctypes.c_void_p), self.nbytes, self.rank, self.world,
                                               self._epoch, native.stream_ptr())

@@ -140,6 +140,9 @@ int dsb200_symm_free(void* ptr);
 /* peer_ptrs: HOST array of `world` device pointers (this process's mappings of every rank's buffer, own included) */
 int dsb200_symm_barrier(void* const* peer_ptrs, long long flag_off, int rank, int world, unsigned int epoch,
                         dsb200_stream_t stream);
+/* flag_off: a pad of `world` uint32 used ONLY by device-epoch barriers (zero-initialised); epoch_ctr: local device uint32 */
+int dsb200_symm_barrier_dev(void* const* peer_ptrs, long long flag_off, int rank, int world, unsigned int* epoch_ctr,
+                            dsb200_stream_t stream);
 int dsb200_p2p_allgather(void* const* peer_ptrs, long long src_off, void* dst, long long bytes_per_rank, int rank,
                          int world, int max_ctas, dsb200_stream_t stream);
 /* dst[p * bytes_per_chunk ...] = chunk `rank` of peer p's buffer at src_off (equal-split all_to_all_single); dst is local memory. */
@@ -223,6 +226,14 @@ int dsb200_gemm_rs_bf16(const void* A, const void* B, void* const* peer_ptrs, lo
                         unsigned int epoch, void* out, const void* residual, int M, int N, int K, int lda, int ldb,
                         int ldo, int ldr, int rank, int world, int row_lo, int row_hi, int max_ctas,
                         dsb200_stream_t stream);
+/* Graph-capturable forms: the epoch lives in device memory (`epoch_ctr`, one uint32 of LOCAL memory per rank, all ranks start it at
+ * the same value); every call bumps it with a one-thread kernel in front of the GEMM, and the GEMM picks the partial area
+ * part_off0 / part_off1 by the bumped value's parity.  A captured call therefore replays correctly any number of times.
+ * row_lo = 0, row_hi = M: all-reduce; a sub-range: reduce-scatter over rows. */
+int dsb200_gemm_ar_bf16_dev(const void* A, const void* B, void* const* peer_ptrs, long long part_off0, long long part_off1,
+                            long long flag_off, unsigned int* epoch_ctr, void* out, const void* residual, int M, int N,
+                            int K, int lda, int ldb, int ldo, int ldr, int rank, int world, int row_lo, int row_hi,
+                            int max_ctas, dsb200_stream_t stream);
 
 /* ---- csrc/gemm/gemm_fp8.cu */
 /* C[M,N] (bf16) = diag(sa) * (A * B^T) * diag(sb) with A [M][K], B [N][K] in e4m3 (one byte per element, K contiguous).
@@ -252,6 +263,12 @@ int dsb200_mxfp8_quantize(const void* x, void* q, void* sf, int rows, int K, lon
 /* C[M,N] (bf16) = dequant(A) * dequant(B)^T with MXFP8 operands (payload + packed UE8M0 scales from dsb200_mxfp8_quantize). */
 int dsb200_gemm_mxfp8(const void* A, const void* B, void* C, const void* sfa, const void* sfb, int M, int N, int K,
                       int lda, int ldb, int ldc, int max_ctas, dsb200_stream_t stream);
+
+/* ---- csrc/gemm/gemm_skinny.cu */
+/* out[M][N] (bf16, row stride ldo) = x[M][K] w[N][K]^T, bf16 operands, M <= 128.  splits >= 1 cuts K; with splits > 1 the caller
+ * passes a workspace of splits * M * N floats and N must be a multiple of 4.  K, ldx, ldw multiples of 8 (16-byte rows for TMA). */
+int dsb200_gemm_skinny_bf16(const void* x, const void* w, void* out, void* workspace, int M, int N, int K, int ldx,
+                            int ldw, int ldo, int splits, dsb200_stream_t stream);
 
 /* ---- csrc/host/aio.cpp */
 void* dsbh_aio_create(int64_t block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);

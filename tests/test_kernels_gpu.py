@@ -445,6 +445,46 @@ def test_fastgen_engine_gpu_matches_dense():
     assert out.dtype == torch.bfloat16 and out.is_cuda
 
 
+def test_fastgen_decode_steps_replay_a_cuda_graph():
+    """Pure decode steps are captured into a CUDA graph per batch size after two eager steps (RaggedTransformer.forward_graphed);
+    every step -- eager, the capturing one, replays, and replays after the contexts grew into new KV blocks -- must match the
+    dense fp32 forward of the same token history."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_inference_v2 import _dense_llama_logits, _hf_llama_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    cfg = dict(vocab_size=512, hidden_size=512, intermediate_size=1024, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+               rms_norm_eps=1e-5)
+    sd = _hf_llama_state(cfg)
+    sd32 = {k: v.bfloat16().float() for k, v in sd.items()}
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 512, "max_ragged_sequence_count": 8, "max_context": 1024,
+                                                      "memory_config": {"mode": "allocate", "size": 64}})
+    eng = build_engine_from_state_dict("llama", cfg, sd, ecfg)
+    torch.manual_seed(2)
+    hist = {1: torch.randint(0, 512, (120, )), 2: torch.randint(0, 512, (250, )), 3: torch.randint(0, 512, (7, ))}
+    eng.put(list(hist), [hist[u] for u in hist])
+    for step in range(12):  # sequence 1 crosses the 128-token block boundary at step 8, sequence 2 at step 6
+        new = {u: torch.randint(0, 512, (1, )) for u in hist}
+        out = eng.put(list(hist), [new[u] for u in hist]).float().cpu()
+        for k, u in enumerate(hist):
+            hist[u] = torch.cat([hist[u], new[u]])
+            ref = _dense_llama_logits(sd32, cfg, hist[u])[-1]
+            assert (out[k] - ref).abs().max() < 0.06 * ref.abs().max() + 0.02, (step, u, (out[k] - ref).abs().max().item())
+    model = eng._model
+    assert 3 in model._graphs and model._graph_warm[3] == 2, "decode steps of 3 sequences were not captured"
+    # a different batch size gets its own warm-up and graph; the first one keeps working afterwards
+    eng.flush(3)
+    del hist[3]
+    for step in range(4):
+        new = {u: torch.randint(0, 512, (1, )) for u in hist}
+        out = eng.put(list(hist), [new[u] for u in hist]).float().cpu()
+        for k, u in enumerate(hist):
+            hist[u] = torch.cat([hist[u], new[u]])
+            ref = _dense_llama_logits(sd32, cfg, hist[u])[-1]
+            assert (out[k] - ref).abs().max() < 0.06 * ref.abs().max() + 0.02, ("two sequences", step, u)
+    assert 2 in model._graphs
+
+
 @pytest.mark.parametrize("n", [8 * 1024, 8 * 100_003])
 def test_onebit_compress_decompress(n):
     """fused sign-pack + error feedback and the unpack kernels vs. the torch formulas (runtime/comm/compressed.py CPU path)."""
@@ -989,3 +1029,24 @@ def test_v1_attention_kv_arena_matches_dense_path(monkeypatch, rotate_half, kv_h
         assert oa.shape == ob.shape and ka.shape == kb.shape
         assert (oa.float() - ob.float()).abs().max() < 0.03 * ob.float().abs().max() + 1e-3
         assert (ka.float() - kb.float()).abs().max() < 0.07 and (va.float() - vb.float()).abs().max() < 1e-6  # rotated k: a bf16 ulp or two
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 5120, 8192), (16, 8192, 3584), (33, 1024, 4096), (64, 28672, 1024), (128, 4096, 4096), (7, 1000, 520)])
+def test_gemm_skinny_weight_streaming(M, N, K):
+    """Decode-sized GEMM (csrc/gemm/gemm_skinny.cu: swapped roles, split K, fp32 partials + reduce) vs an fp32 matmul of the same
+    bf16 operands; `gemm()` must route these shapes to it."""
+    from deepspeedsyclsupport_b200.ops import gemm as G
+    from deepspeedsyclsupport_b200.ops import native
+    torch.manual_seed(M + N)
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    before = native.launch_count
+    y = G.gemm(x, w)
+    assert native.launch_count > before
+    ref = x.float() @ w.float().t()
+    err = (y.float() - ref).abs().max().item()
+    assert y.shape == (M, N) and err < 0.01 * ref.abs().max().item() + 1e-2, (M, N, K, err)
+    # strided output view (a column slice of a wider buffer), as the fused-QKV callers use
+    wide = torch.zeros(M, N + 64, device="cuda", dtype=torch.bfloat16)
+    G.gemm(x, w, out=wide[:, :N])
+    assert (wide[:, :N].float() - ref).abs().max().item() < 0.01 * ref.abs().max().item() + 1e-2 and float(wide[:, N:].abs().max()) == 0.0

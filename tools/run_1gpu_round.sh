@@ -1,8 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_paged_flash.py -q -x > gpurun_out/pf_tests.log 2>&1
-echo "pf tests rc=$?"; tail -8 gpurun_out/pf_tests.log | cut -c1-400
-timeout 300 python tools/paged_flash_bench.py --out gpurun_out/paged_flash_bench2.json > gpurun_out/pf_bench.log 2>&1
-echo "pf bench rc=$?"; grep -E "paged_flash_ms|kv_fraction|tflops|\"(prefill|decode)" gpurun_out/pf_bench.log | cut -c1-200
-DSB200_PF_TRACE=1 timeout 300 python tools/paged_flash_bench.py --profile decode > gpurun_out/pf_trace_decode.log 2>&1
-echo "trace decode rc=$?"; tail -8 gpurun_out/pf_trace_decode.log | cut -c1-60
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:paged_decode_kernel -c 1 -f -o gpurun_out/ncu_paged_decode_v4 python tools/paged_flash_bench.py --profile decode > gpurun_out/ncu_paged_decode_v4.log 2>&1
+echo "ncu decode rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:paged_flash_kernel -c 1 -f -o gpurun_out/ncu_paged_prefill_v4 python tools/paged_flash_bench.py --profile prefill > gpurun_out/ncu_paged_prefill_v4.log 2>&1
+echo "ncu prefill rc=$?"
+timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/gpu_tests.log 2>&1
+echo "pytest rc=$?"; tail -5 gpurun_out/gpu_tests.log | cut -c1-300
