@@ -51,11 +51,12 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
         out = torch.empty(M, ld, dtype=out_dtype, device=a.device)[:, :N]  # e.g. a vocabulary of 50257: padded rows, [M, N] view
     assert out.shape == (M, N) and out.stride(1) == 1
     f32 = out.dtype == torch.float32
-    if (M <= 128 and N >= 512 and not (a_mn or b_mn or accumulate or f32) and K % 8 == 0 and N % 4 == 0 and out.stride(0) % 4 == 0 and
+    if (M <= 128 and 512 <= N < 148 * 128 and not (a_mn or b_mn or accumulate or f32) and K % 8 == 0 and N % 4 == 0 and out.stride(0) % 4 == 0 and
             a.stride(0) % 8 == 0 and b.stride(0) % 8 == 0 and _SKINNY_ON):
-        # decode-sized problem: weight-streaming kernel (swapped roles + split K) instead of 128 x 256 output tiles
+        # decode-sized problem whose 128 x 256 output tiles would not fill the SMs: weight-streaming kernel (swapped roles, split K).
+        # (With >= 148 row tiles of the weight the tile kernel already streams at full rate: profiles/gemm_skinny_bench.json.)
         tiles, kb = -(-N // 128), -(-K // 64)
-        splits = max(1, min(kb // 4, (148 if not max_ctas else max_ctas) // tiles)) if tiles < 148 else 1
+        splits = max(1, min(kb // 4, (148 if not max_ctas else max_ctas) // tiles))
         ws = torch.empty(splits * M * N, dtype=torch.float32, device=a.device) if splits > 1 else None
         rc = native.lib().dsb200_gemm_skinny_bf16(native.ptr(a), native.ptr(b), native.ptr(out), native.ptr(ws), M, N, K, a.stride(0), b.stride(0),
                                                   out.stride(0), splits, native.stream_ptr())

@@ -269,6 +269,11 @@ int dsb200_gemm_mxfp8(const void* A, const void* B, void* C, const void* sfa, co
  * passes a workspace of splits * M * N floats and N must be a multiple of 4.  K, ldx, ldw multiples of 8 (16-byte rows for TMA). */
 int dsb200_gemm_skinny_bf16(const void* x, const void* w, void* out, void* workspace, int M, int N, int K, int ldx,
                             int ldw, int ldo, int splits, dsb200_stream_t stream);
+/* out[M][N] (bf16) = x[M][K] (bf16) * dequant(wq)[N][K]^T, M <= 128.  bits = 8: wq int8 [N][K]; bits = 4: wq uint8 [N][K/2] (low nibble
+ * first, value = nibble - 8).  scales fp32 [N][K / group], group a multiple of 64 dividing K; K a multiple of 64.
+ * splits > 1 needs a workspace of splits * M * N floats and N, ldo multiples of 4. */
+int dsb200_gemm_skinny_mixed(const void* x, const void* wq, const void* scales, void* out, void* workspace, int M, int N,
+                             int K, int ldx, int ldo, int bits, int group, int splits, dsb200_stream_t stream);
 
 /* ---- csrc/host/aio.cpp */
 void* dsbh_aio_create(int64_t block_size, int queue_depth, int single_submit, int overlap_events, int num_threads);

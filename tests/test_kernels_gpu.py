@@ -1050,3 +1050,26 @@ def test_gemm_skinny_weight_streaming(M, N, K):
     wide = torch.zeros(M, N + 64, device="cuda", dtype=torch.bfloat16)
     G.gemm(x, w, out=wide[:, :N])
     assert (wide[:, :N].float() - ref).abs().max().item() < 0.01 * ref.abs().max().item() + 1e-2 and float(wide[:, N:].abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("bits,M,N,K,group", [(8, 16, 4096, 4096, 128), (4, 16, 4096, 4096, 64), (8, 1, 1024, 8192, 8192), (4, 100, 2048, 1024, 256),
+                                             (8, 128, 11008, 512, 64)])
+def test_mixed_gemm_weight_only_quantised_skinny(bits, M, N, K, group):
+    """MixedGEMM at decode size runs the mixed-input weight-streaming kernel (int8 / packed int4 weights dequantised in shared
+    memory, tcgen05 MMA); oracle = fp32 matmul against the group-wise dequantised weight."""
+    from deepspeedsyclsupport_b200.inference.v2.inference_utils import ActivationType
+    from deepspeedsyclsupport_b200.inference.v2.kernels.cutlass_ops import MixedGEMM, _dequant, _mixed_skinny
+    torch.manual_seed(bits * 1000 + M)
+    x = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    sc = (torch.rand(N, K // group, device="cuda") * 0.01 + 0.002)
+    if bits == 8:
+        wq = torch.randint(-127, 128, (N, K), device="cuda", dtype=torch.int8)
+    else:
+        q4 = torch.randint(0, 16, (N, K), device="cuda")
+        wq = (q4[:, 0::2] | (q4[:, 1::2] << 4)).to(torch.uint8)
+    assert _mixed_skinny(x, wq, sc, bits) is not None, "the fused kernel did not take this shape"
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    MixedGEMM("bf16", ActivationType.IDENTITY, bits)(out, x, wq, sc)
+    ref = x.float() @ _dequant(wq, sc, bits, torch.float32).t()
+    err = (out.float() - ref).abs().max().item()
+    assert err < 0.01 * ref.abs().max().item() + 1e-2, (bits, M, N, K, group, err)
