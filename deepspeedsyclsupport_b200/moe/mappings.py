@@ -1,63 +1,77 @@
-"""Token drop/gather across the tensor-parallel group for MoE with non-TP experts (parity: deepspeed/moe/mappings.py)."""
+"""Token drop / gather across the tensor-parallel group for MoE with non-TP experts (parity: deepspeed/moe/mappings.py).
+
+With tensor-parallel attention but replicated (non-TP) experts every TP rank holds the same tokens; `drop_tokens` keeps this rank's
+1/tp slice along `dim` before the MoE layer and `gather_tokens` re-assembles the full tensor after it.  The two are each other's
+adjoint, so ONE autograd function parametrised by the direction serves both."""
 import torch
 
 from .. import comm as dist
 from ..utils import groups
 
 
+def _tp():
+    group = groups._get_model_parallel_group()
+    return group, dist.get_world_size(group)
+
+
 def _gather_tokens(input_, dim=0):
-    mpg = groups._get_model_parallel_group()
-    world = dist.get_world_size(mpg)
+    group, world = _tp()
     if world == 1:
         return input_
-    input_ = input_.contiguous()
-    tensor_list = [torch.empty_like(input_) for _ in range(world)]
-    dist.all_gather(tensor_list, input_, group=mpg)
-    return torch.cat(tensor_list, dim=dim).contiguous()
+    src = input_.contiguous()
+    pieces = [torch.empty_like(src) for _ in range(world)]
+    dist.all_gather(pieces, src, group=group)
+    return torch.cat(pieces, dim=dim).contiguous()
 
 
 def _drop_tokens(input_, dim=0):
-    mpg = groups._get_model_parallel_group()
-    world = dist.get_world_size(mpg)
+    group, world = _tp()
     if world == 1:
         return input_
-    rank = dist.get_rank(mpg)
-    assert input_.shape[dim] % world == 0, f"input dimension {dim} ({input_.shape[dim]}) is not divisible by tensor parallel world size ({world})"
-    chunk = input_.shape[dim] // world
-    return torch.narrow(input_, dim, rank * chunk, chunk)
+    size = input_.shape[dim]
+    assert size % world == 0, f"input dimension {dim} ({size}) is not divisible by tensor parallel world size ({world})"
+    return input_.narrow(dim, dist.get_rank(group) * (size // world), size // world)
 
 
-class _GatherTokens(torch.autograd.Function):
+class _Resplit(torch.autograd.Function):
+    """forward = gather (or drop), backward = the other one"""
+
+    @staticmethod
+    def forward(ctx, input_, dim, gather):
+        ctx.dim, ctx.gather = dim, gather
+        return (_gather_tokens if gather else _drop_tokens)(input_, dim)
+
+    @staticmethod
+    def backward(ctx, grad):
+        return (_drop_tokens if ctx.gather else _gather_tokens)(grad, ctx.dim), None, None
+
+
+# reference names of the two directions
+class _GatherTokens(_Resplit):
 
     @staticmethod
     def forward(ctx, input_, dim):
-        ctx.dim = dim
-        return _gather_tokens(input_, dim)
+        return _Resplit.forward(ctx, input_, dim, True)
 
     @staticmethod
-    def backward(ctx, grad_output):
-        return _drop_tokens(grad_output, ctx.dim), None
+    def backward(ctx, grad):
+        return _Resplit.backward(ctx, grad)[:2]
 
 
-class _DropTokens(torch.autograd.Function):
+class _DropTokens(_Resplit):
 
     @staticmethod
     def forward(ctx, input_, dim):
-        ctx.dim = dim
-        return _drop_tokens(input_, dim)
+        return _Resplit.forward(ctx, input_, dim, False)
 
     @staticmethod
-    def backward(ctx, input_):
-        return _gather_tokens(input_, ctx.dim), None
+    def backward(ctx, grad):
+        return _Resplit.backward(ctx, grad)[:2]
 
 
 def gather_tokens(input_, dim=0):
-    if groups._get_model_parallel_world_size() == 1:
-        return input_
-    return _GatherTokens.apply(input_, dim)
+    return input_ if groups._get_model_parallel_world_size() == 1 else _GatherTokens.apply(input_, dim)
 
 
 def drop_tokens(input_, dim=0):
-    if groups._get_model_parallel_world_size() == 1:
-        return input_
-    return _DropTokens.apply(input_, dim)
+    return input_ if groups._get_model_parallel_world_size() == 1 else _DropTokens.apply(input_, dim)

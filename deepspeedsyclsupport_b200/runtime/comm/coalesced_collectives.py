@@ -1,5 +1,4 @@
 """Batched collectives over lists of tensors (parity: deepspeed/runtime/comm/coalesced_collectives.py:29-139)."""
-import math
 from typing import List
 
 import torch
@@ -9,39 +8,34 @@ from ... import comm as dist
 
 
 def reduce_scatter_coalesced(tensors: List[Tensor], group=None) -> List[Tensor]:
-    """Simultaneously reduce-scatter a list of tensors - this can be done more efficiently than individual reduce scatter
-    calls: every tensor is padded to a multiple of world, the rank-r slices are packed into one flat send buffer per rank
-    and ONE reduce_scatter moves everything.  Returns this rank's (averaged) partition of each tensor."""
-    this_rank = dist.get_rank(group)
-    world_sz = dist.get_world_size(group)
-    partition_lst_for_each_tensor = [None] * len(tensors)
-    for tensor_idx, tensor in enumerate(tensors):
-        flattened_tensor = tensor.view(-1)
-        chunk_sz = math.ceil(tensor.numel() / world_sz)
-        partition_lst_for_each_tensor[tensor_idx] = [flattened_tensor[rank * chunk_sz:rank * chunk_sz + chunk_sz] for rank in range(0, world_sz)]
-    padded_partition_sz_for_each_tensor = tuple(math.ceil(t.numel() / world_sz) for t in tensors)
-    if len(tensors) == 1 and tensors[0].numel() % world_sz == 0:
-        tensor_partition_flat_buffer = tensors[0].view(-1)
+    """One reduce-scatter for a list of tensors; returns this rank's (averaged) partition of each.
+
+    Tensor i is cut into `world` chunks of c_i = ceil(n_i / world) elements (the last ranks' chunks may be short or empty).  The
+    send buffer is a [world, sum_i c_i] matrix: row r holds chunk r of every tensor, zero-padded to c_i, so ONE reduce_scatter
+    of its rows delivers every partition.  A single tensor that divides evenly is sent (and averaged) in place."""
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    chunk = [-(-t.numel() // world) for t in tensors]
+    if len(tensors) == 1 and tensors[0].numel() % world == 0:
+        send = tensors[0].view(-1)
     else:
-        tensor_partitions_lst_with_padding = []
-        for rank in range(world_sz):
-            for tensor_idx in range(len(tensors)):
-                tensor_chunk = partition_lst_for_each_tensor[tensor_idx][rank]
-                tensor_partitions_lst_with_padding.append(tensor_chunk)
-                padding_sz = padded_partition_sz_for_each_tensor[tensor_idx] - tensor_chunk.numel()
-                if padding_sz > 0:
-                    tensor_partitions_lst_with_padding.append(torch.empty(padding_sz, dtype=tensor_chunk.dtype, device=tensor_chunk.device))
-        tensor_partition_flat_buffer = torch.cat(tensor_partitions_lst_with_padding)
-    tensor_partition_flat_buffer.div_(world_sz)
-    per_rank = tensor_partition_flat_buffer.numel() // world_sz
-    out = torch.empty(per_rank, dtype=tensor_partition_flat_buffer.dtype, device=tensor_partition_flat_buffer.device)
-    dist.reduce_scatter_tensor(out, tensor_partition_flat_buffer, group=group)
-    output_lst = [None] * len(tensors)
-    offset = 0
-    for tensor_idx in range(len(tensors)):
-        output_lst[tensor_idx] = out.narrow(0, offset, partition_lst_for_each_tensor[tensor_idx][this_rank].numel())
-        offset += padded_partition_sz_for_each_tensor[tensor_idx]
-    return output_lst
+        send = tensors[0].new_zeros(world, sum(chunk))
+        col = 0
+        for t, c in zip(tensors, chunk):
+            flat = t.reshape(-1)
+            whole, rest = divmod(flat.numel(), c) if c else (0, 0)
+            send[:whole, col:col + c] = flat[:whole * c].view(whole, c)
+            if rest:
+                send[whole, col:col + rest] = flat[whole * c:]
+            col += c
+        send = send.view(-1)
+    send.div_(world)
+    mine = send.new_empty(send.numel() // world)
+    dist.reduce_scatter_tensor(mine, send, group=group)
+    parts, col = [], 0
+    for t, c in zip(tensors, chunk):
+        parts.append(mine.narrow(0, col, max(0, min(c, t.numel() - rank * c))))
+        col += c
+    return parts
 
 
 def all_to_all_quant_reduce(tensors: List[Tensor], groups: {}) -> List[Tensor]:

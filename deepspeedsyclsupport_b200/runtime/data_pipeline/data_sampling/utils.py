@@ -1,33 +1,32 @@
 """Small helpers of the data sampler / analyzer (parity: deepspeed/runtime/data_pipeline/data_sampling/utils.py)."""
-import math
-
 import numpy as np
 
 from ....utils.logging import logger
 from .indexed_dataset import MMapIndexedDatasetBuilder
 
+_UNSIGNED = (np.uint8, np.uint16, np.uint32, np.uint64)
+_SIGNED = (np.int8, np.int16, np.int32, np.int64)
+
 
 def find_fit_int_dtype(min_value, max_value):
-    if min_value >= 0:
-        for dt in (np.uint8, np.uint16, np.uint32):
-            if max_value <= np.iinfo(dt).max:
-                return dt
-        return np.uint64
-    for dt in (np.int8, np.int16, np.int32):
-        if max_value <= np.iinfo(dt).max and min_value >= np.iinfo(dt).min:
+    """Narrowest integer dtype that holds [min_value, max_value] (unsigned when nothing is negative)."""
+    for dt in (_UNSIGNED if min_value >= 0 else _SIGNED):
+        info = np.iinfo(dt)
+        if info.min <= min_value and max_value <= info.max:
             return dt
-    return np.int64
+    return _UNSIGNED[-1] if min_value >= 0 else _SIGNED[-1]
 
 
 def split_index(start_idx, end_idx, num_partitions):
-    partition_size = math.ceil((end_idx - start_idx) / num_partitions)
-    return [(x, min(end_idx, x + partition_size)) for x in range(start_idx, end_idx, partition_size)]
+    """[start, end) cut into consecutive ranges of ceil(len / num_partitions) items (the last may be shorter)."""
+    step = -(-(end_idx - start_idx) // num_partitions)
+    return [(lo, min(lo + step, end_idx)) for lo in range(start_idx, end_idx, step)]
 
 
 def split_dataset(dataset, num_workers, worker_id, num_threads):
-    worker_splits = split_index(0, len(dataset), num_workers)
-    thread_splits = split_index(worker_splits[worker_id][0], worker_splits[worker_id][1], num_threads)
-    return worker_splits, thread_splits
+    """(ranges of all workers, ranges of this worker's threads)"""
+    by_worker = split_index(0, len(dataset), num_workers)
+    return by_worker, split_index(*by_worker[worker_id], num_threads)
 
 
 def create_mmap_dataset_builder(fname, dtype):
