@@ -32,25 +32,28 @@ FIRST_ALLTOALL_TIMER = "1st_a2a"
 SECOND_ALLTOALL_TIMER = "2nd_a2a"
 
 
+def _sampler(cache, device, make):
+    """Per-device random sampler, built once (the three module-level maps keep the reference's names)."""
+    fn = cache.get(device)
+    if fn is None:
+        fn = cache[device] = make()
+    return fn
+
+
+def _uniform(lo, hi, device):
+    return torch.distributions.uniform.Uniform(low=torch.tensor(lo, device=device), high=torch.tensor(hi, device=device)).rsample
+
+
 def multiplicative_jitter(x, device, epsilon=1e-2):
+    """x * U(1 - eps, 1 + eps), element-wise (the 'Jitter' noisy-gate policy)."""
     if epsilon == 0:
         return x
-    uniform = uniform_map.get(device)
-    if uniform is None:
-        uniform = torch.distributions.uniform.Uniform(low=torch.tensor(1.0 - epsilon, device=device),
-                                                      high=torch.tensor(1.0 + epsilon, device=device)).rsample
-        uniform_map[device] = uniform
-    return x * uniform(x.shape)
+    return x * _sampler(uniform_map, device, lambda: _uniform(1.0 - epsilon, 1.0 + epsilon, device))(x.shape)
 
 
 def gumbel_rsample(shape, device):
-    gumbel = gumbel_map.get(device)
-    if gumbel is None:
-        one = torch.tensor(1.0, device=device)
-        zero = torch.tensor(0.0, device=device)
-        gumbel = torch.distributions.gumbel.Gumbel(zero, one).rsample
-        gumbel_map[device] = gumbel
-    return gumbel(shape)
+    make = lambda: torch.distributions.gumbel.Gumbel(torch.tensor(0.0, device=device), torch.tensor(1.0, device=device)).rsample
+    return _sampler(gumbel_map, device, make)(shape)
 
 
 class _AllToAll(torch.autograd.Function):
@@ -69,9 +72,8 @@ class _AllToAll(torch.autograd.Function):
 
 
 def _capacity(gates, capacity_factor, min_capacity):
-    num_tokens, num_experts = gates.shape[0], gates.shape[1]
-    capacity = math.ceil((num_tokens / num_experts) * capacity_factor)
-    return max(capacity, min_capacity)
+    tokens, experts = gates.shape
+    return max(math.ceil(tokens / experts * capacity_factor), min_capacity)
 
 
 def _slot_positions(mask):
@@ -79,90 +81,79 @@ def _slot_positions(mask):
     return torch.cumsum(mask, dim=0) - 1
 
 
+def _load_balance(gates, first_choice_mask):
+    """sum_e mean_s(gate[s, e]) * mean_s(first choice is e): the GShard auxiliary term before its normalisation constant."""
+    return gates.mean(dim=0) * first_choice_mask.float().mean(dim=0)
+
+
+def _no_drop_capacity(per_expert_load, device):
+    """Largest queue over all experts and all ranks (the only host synchronisation of the gate, no-drop mode only)."""
+    cap = per_expert_load.max().to(device)
+    if dist.is_initialized():
+        dist.all_reduce(cap, op=dist.ReduceOp.MAX, group=dist.get_world_group())
+    return int(cap.item())
+
+
+def _routes(mask, choice, slots):
+    """(expert or -1 when dropped, slot) per token from a 0/1 [S, E] mask of KEPT assignments."""
+    kept = mask.sum(dim=1) > 0
+    return torch.where(kept, choice, torch.full_like(choice, -1)), (slots * mask).sum(dim=1)
+
+
 def top1gating(logits, capacity_factor, min_capacity, used_token=None, noisy_gate_policy=None, drop_tokens=True,
                use_rts=True, use_tutel=False):
     """Returns (l_aux, token_expert [S,1], token_slot [S,1], token_weight [S,1], capacity, exp_counts)."""
-    if noisy_gate_policy == "RSample":
-        logits_w_noise = logits + gumbel_rsample(logits.shape, device=logits.device)
     gates = F.softmax(logits, dim=1)
+    experts = gates.shape[1]
     capacity = _capacity(gates, capacity_factor, min_capacity)
-    indices1_s = torch.argmax(logits_w_noise if noisy_gate_policy == "RSample" else gates, dim=1)
-    num_experts = int(gates.shape[1])
-    mask1 = F.one_hot(indices1_s, num_classes=num_experts)
+    ranked = logits + gumbel_rsample(logits.shape, device=logits.device) if noisy_gate_policy == "RSample" else gates
+    choice = ranked.argmax(dim=1)
+    mask = F.one_hot(choice, num_classes=experts)
     if used_token is not None:
-        mask1 = torch.einsum("s,se->se", used_token, mask1)
-    exp_counts = torch.sum(mask1, dim=0).detach()  # stays on the device: no host synchronisation in the gate (call .cpu() to log it)
+        mask = used_token[:, None] * mask
+    exp_counts = mask.sum(dim=0).detach()  # stays on the device: no host synchronisation in the gate (call .cpu() to log it)
     if not drop_tokens:
-        new_capacity = torch.max(exp_counts).to(logits.device)
-        if dist.is_initialized():
-            dist.all_reduce(new_capacity, op=dist.ReduceOp.MAX, group=dist.get_world_group())
-        capacity = int(new_capacity.item())
-    me = torch.mean(gates, dim=0)
-    ce = torch.mean(mask1.float(), dim=0)
-    l_aux = torch.sum(me * ce) * num_experts
-    if use_rts:
-        uniform = exp_selection_uniform_map.get(logits.device)
-        if uniform is None:
-            uniform = torch.distributions.uniform.Uniform(low=torch.tensor(0.0, device=logits.device),
-                                                          high=torch.tensor(1.0, device=logits.device)).rsample
-            exp_selection_uniform_map[logits.device] = uniform
-        mask1_rand = mask1 * uniform(mask1.shape)
-    else:
-        mask1_rand = mask1
+        capacity = _no_drop_capacity(exp_counts, logits.device)
+    l_aux = _load_balance(gates, mask).sum() * experts
     assert logits.shape[0] >= min_capacity, \
         "No. of tokens (batch-size) should be greater than min_capacity. Either set min_capacity to 0 or increase your batch size."
-    # keep the top-`capacity` tokens of every expert (by random priority under RTS, by arrival order otherwise)
-    k = min(capacity, mask1_rand.shape[0])
-    top_idx = torch.topk(mask1_rand, k=k, dim=0)[1]
-    new_mask1 = mask1 * torch.zeros_like(mask1).scatter_(0, top_idx, 1)
-    mask1 = new_mask1
-    locations1 = _slot_positions(mask1)
-    kept = mask1.sum(dim=1) > 0
-    token_slot = torch.sum(locations1 * mask1, dim=1)
-    gate_w = (gates * mask1.float()).sum(dim=1)
-    token_expert = torch.where(kept, indices1_s, torch.full_like(indices1_s, -1))
-    return l_aux, token_expert[:, None], token_slot[:, None], gate_w[:, None], capacity, exp_counts
+    # every expert keeps `capacity` of its tokens: the ones with the highest priority -- a uniform draw per assignment under
+    # random token selection (RTS), otherwise ties of 1s, i.e. whatever topk picks first
+    priority = mask
+    if use_rts:
+        priority = mask * _sampler(exp_selection_uniform_map, logits.device, lambda: _uniform(0.0, 1.0, logits.device))(mask.shape)
+    winners = torch.topk(priority, k=min(capacity, mask.shape[0]), dim=0).indices
+    mask = mask * torch.zeros_like(mask).scatter_(0, winners, 1)
+    token_expert, token_slot = _routes(mask, choice, _slot_positions(mask))
+    weight = (gates * mask.float()).sum(dim=1)
+    return l_aux, token_expert[:, None], token_slot[:, None], weight[:, None], capacity, exp_counts
 
 
 def top2gating(logits, capacity_factor, min_capacity, drop_tokens=True):
+    """Second expert = argmax of the gumbel-perturbed logits with the first one excluded; the two gate values are renormalised
+    to sum to 1; the second choices queue behind ALL first choices of their expert."""
     gates = F.softmax(logits, dim=1)
+    experts = gates.shape[1]
     capacity = _capacity(gates, capacity_factor * 2, min_capacity)
-    indices1_s = torch.argmax(gates, dim=1)
-    num_experts = int(gates.shape[1])
-    mask1 = F.one_hot(indices1_s, num_classes=num_experts)
-    logits_w_noise = logits + gumbel_rsample(logits.shape, device=logits.device)
-    logits_except1 = logits_w_noise.masked_fill(mask1.bool(), float("-inf"))
-    indices2_s = torch.argmax(logits_except1, dim=1)
-    mask2 = F.one_hot(indices2_s, num_classes=num_experts)
-    locations1 = _slot_positions(mask1)
-    locations2 = _slot_positions(mask2) + torch.sum(mask1, dim=0, keepdim=True)
-    exp_counts = torch.sum(mask1, dim=0).detach()
-    me = torch.mean(gates, dim=0)
-    ce = torch.mean(mask1.float(), dim=0)
-    l_aux = torch.mean(me * ce) * num_experts * num_experts
+    first = gates.argmax(dim=1)
+    m1 = F.one_hot(first, num_classes=experts)
+    noisy = logits + gumbel_rsample(logits.shape, device=logits.device)
+    second = noisy.masked_fill(m1.bool(), float("-inf")).argmax(dim=1)
+    m2 = F.one_hot(second, num_classes=experts)
+    pos1 = _slot_positions(m1)
+    pos2 = _slot_positions(m2) + m1.sum(dim=0, keepdim=True)
+    exp_counts = m1.sum(dim=0).detach()
+    l_aux = _load_balance(gates, m1).mean() * experts * experts
     if drop_tokens:
-        mask1 = mask1 * torch.lt(locations1, capacity)
-        mask2 = mask2 * torch.lt(locations2, capacity)
+        m1, m2 = m1 * (pos1 < capacity), m2 * (pos2 < capacity)
     else:
-        new_capacity = torch.max(exp_counts + torch.sum(mask2, dim=0).detach()).to(logits.device)
-        if dist.is_initialized():
-            dist.all_reduce(new_capacity, op=dist.ReduceOp.MAX, group=dist.get_world_group())
-        capacity = int(new_capacity.item())
-    slot1 = torch.sum(locations1 * mask1, dim=1)
-    slot2 = torch.sum(locations2 * mask2, dim=1)
-    mask1_float, mask2_float = mask1.float(), mask2.float()
-    gates1_s = torch.einsum("se,se->s", gates, mask1_float)
-    gates2_s = torch.einsum("se,se->s", gates, mask2_float)
-    denom_s = torch.clamp(gates1_s + gates2_s, min=torch.finfo(gates1_s.dtype).eps)
-    gates1_s = gates1_s / denom_s
-    gates2_s = gates2_s / denom_s
-    kept1, kept2 = mask1.sum(1) > 0, mask2.sum(1) > 0
-    e1 = torch.where(kept1, indices1_s, torch.full_like(indices1_s, -1))
-    e2 = torch.where(kept2, indices2_s, torch.full_like(indices2_s, -1))
-    token_expert = torch.stack([e1, e2], dim=1)
-    token_slot = torch.stack([slot1, slot2], dim=1)
-    token_weight = torch.stack([gates1_s, gates2_s], dim=1)
-    return l_aux, token_expert, token_slot, token_weight, capacity, exp_counts
+        capacity = _no_drop_capacity(exp_counts + m2.sum(dim=0).detach(), logits.device)
+    e1, slot1 = _routes(m1, first, pos1)
+    e2, slot2 = _routes(m2, second, pos2)
+    g1, g2 = (gates * m1.float()).sum(dim=1), (gates * m2.float()).sum(dim=1)
+    norm = (g1 + g2).clamp(min=torch.finfo(g1.dtype).eps)
+    return (l_aux, torch.stack([e1, e2], dim=1), torch.stack([slot1, slot2], dim=1), torch.stack([g1 / norm, g2 / norm], dim=1), capacity,
+            exp_counts)
 
 
 def dense_dispatch_masks(token_expert, token_slot, token_weight, num_experts, capacity):
