@@ -4,6 +4,8 @@
 // 256 features on a CTA: a 5120-feature projection of a 16-token batch is 20 CTAs, 1/7 of the machine.  Here the roles are
 // swapped and K is split:
 //     D^T [128 weight rows x NT tokens] += W_tile [128 x 64] (A, smem, K-major)  x  X_tile^T [NT x 64] (B, smem, K-major)
+// Up to 8 K slices are the CTAs of one thread-block cluster and reduce through distributed shared memory (one kernel); more
+// slices (or partials that do not fit the leader's stages) go through an fp32 workspace and a second kernel.
 // grid = (ceil(N / 128), splits): every CTA streams a [128 x K/splits] slab of W through a 6-8 stage TMA ring (16 KB of W per
 // stage -> ~100 KB in flight per SM) and issues 4 tcgen05.mma (M = 128, N = NT, K = 16) per stage; the accumulator is
 // [128 lanes x NT columns] of TMEM.  splits == 1: the epilogue writes bf16 out[token][feature] directly; otherwise fp32
@@ -38,7 +40,7 @@ struct Params {
   float* ws;           // [splits][M][N] (splits > 1)
 };
 
-template <int NT>
+template <int NT, bool CLUSTER>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmX, const Params p) {
   using SM = Smem<NT>;
@@ -89,6 +91,8 @@ skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
           if (++st == STAGES) { st = 0; ph ^= 1; }
         }
       }
+      __syncwarp();
+      if constexpr (CLUSTER) { cluster_sync_all(); cluster_sync_all(); }
     } else if (warp == 1) {
       const bool leader = elect_one();
       constexpr uint32_t idesc = umma_idesc(BW, NT, 1, 1, 0, 0);
@@ -110,30 +114,69 @@ skinny_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ C
         }
         if (++st == STAGES) { st = 0; ph ^= 1; }
       }
+      if constexpr (CLUSTER) { cluster_sync_all(); cluster_sync_all(); }
     } else {
       // epilogue: thread == weight row (TMEM lane); a warp's 32 rows are 32 consecutive output features of one token
       const int q4 = warp & 3;
-      const int n = n0 + q4 * 32 + lane;
+      const int r = q4 * 32 + lane;
+      const int n = n0 + r;
       mbar_wait(done, 0);
       tc_fence_after();
       const uint32_t lane_off = static_cast<uint32_t>(q4 * 32) << 16;
+      float acc[NT];
 #pragma unroll
       for (int c = 0; c < NT / 16; ++c) {
         uint32_t v[16];
         tmem_ld_32x16(tm + c * 16 + lane_off, v);
         tmem_ld_wait();
-        if (n < p.N) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int t = c * 16 + i;
-            if (t < p.M) {
-              if (p.ws != nullptr) p.ws[(static_cast<size_t>(split) * p.M + t) * p.N + n] = __uint_as_float(v[i]);
-              else p.out[static_cast<size_t>(t) * p.ldo + n] = __float2bfloat16_rn(__uint_as_float(v[i]));
-            }
+        for (int i = 0; i < 16; ++i) acc[c * 16 + i] = __uint_as_float(v[i]);
+      }
+      if constexpr (CLUSTER) {
+        // split-K inside a thread-block cluster: the K slices of one row tile are the CTAs of a cluster (cluster rank ==
+        // split); the non-leaders hand their fp32 accumulators to the leader through distributed shared memory -- its
+        // pipeline stages are idle by then -- laid out [rank - 1][token][weight row] (a warp stores 32 consecutive floats)
+        cluster_sync_all();  // every CTA's tensor core and TMA are done with their stages
+        float* red = reinterpret_cast<float*>(smem);
+        if (split != 0) {
+          uint32_t remote;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(red + (static_cast<size_t>(split - 1) * NT) * BW + r)), "r"(0));
+#pragma unroll
+          for (int t = 0; t < NT; ++t)
+            asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + static_cast<uint32_t>(t * BW * 4)), "f"(acc[t]) : "memory");
+        }
+        cluster_sync_all();  // partials have landed in the leader's shared memory
+        if (split == 0) {
+          const int S = static_cast<int>(gridDim.y);
+#pragma unroll
+          for (int t = 0; t < NT; ++t) {
+            float a = acc[t];
+            for (int q = 0; q < S - 1; ++q) a += red[(static_cast<size_t>(q) * NT + t) * BW + r];
+            if (n < p.N && t < p.M) p.out[static_cast<size_t>(t) * p.ldo + n] = __float2bfloat16_rn(a);
+          }
+        }
+      } else if (n < p.N) {
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+          if (t < p.M) {
+            if (p.ws != nullptr) p.ws[(static_cast<size_t>(split) * p.M + t) * p.N + n] = acc[t];
+            else p.out[static_cast<size_t>(t) * p.ldo + n] = __float2bfloat16_rn(acc[t]);
           }
         }
       }
     }
+  } else if (CLUSTER) {
+    // a split without k-blocks still joins the cluster protocol (its partial is zero)
+    cluster_sync_all();
+    if (warp >= 2 && split != 0) {
+      const int r = (warp & 3) * 32 + lane;
+      float* red = reinterpret_cast<float*>(smem);
+      uint32_t remote;
+      asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(red + (static_cast<size_t>(split - 1) * NT) * BW + r)), "r"(0));
+      for (int t = 0; t < NT; ++t)
+        asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote + static_cast<uint32_t>(t * BW * 4)), "f"(0.f) : "memory");
+    }
+    cluster_sync_all();
   } else if (warp >= 2 && p.ws != nullptr) {
     // this split has no k-blocks (K shorter than the split grid): its partial is zero
     const int n = n0 + (warp & 3) * 32 + lane;
@@ -171,20 +214,45 @@ static int launch(const void* x, const void* w, void* out, float* ws, int M, int
   if (rc) return rc;
   rc = make_tensor_map_2d(&tmX, TMA_BF16, x, M, K, ldx, NT, BK, TMA_SW_128);
   if (rc) return rc;
-  auto kern = skinny_kernel<NT>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
-    attr_set = true;
-  }
   Params p;
   p.M = M; p.N = N; p.K = K;
   p.kb_total = (K + BK - 1) / BK;
   p.kb_per_split = (p.kb_total + splits - 1) / splits;
   p.out = static_cast<__nv_bfloat16*>(out);
   p.ldo = ldo;
-  p.ws = splits > 1 ? ws : nullptr;
   dim3 grid((N + BW - 1) / BW, splits);
+  // up to 8 K slices whose fp32 partials fit the leader's pipeline stages: one kernel, reduction over distributed shared memory
+  const bool cluster = splits > 1 && splits <= 8 && static_cast<size_t>(splits - 1) * NT * BW * 4 <= static_cast<size_t>(SM::STAGES) * SM::STAGE;
+  if (cluster) {
+    auto kern = skinny_kernel<NT, true>;
+    static bool attr_set = false;
+    if (!attr_set) {
+      DSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
+      attr_set = true;
+    }
+    p.ws = nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = SM::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1;
+    attr[0].val.clusterDim.y = static_cast<unsigned>(splits);
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    DSB_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kern, tmW, tmX, p));
+    return DSB_OK;
+  }
+  auto kern = skinny_kernel<NT, false>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DSB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SM::TOTAL));
+    attr_set = true;
+  }
+  p.ws = splits > 1 ? ws : nullptr;
   kern<<<grid, NUM_THREADS, SM::TOTAL, stream>>>(tmW, tmX, p);
   DSB_CHECK_CUDA(cudaGetLastError());
   if (splits > 1) {

@@ -28,6 +28,7 @@ def _gemm_ref(a, b, a_mn, b_mn, out_dtype, out=None, accumulate=False):
 
 
 _SKINNY_ON = os.environ.get("DSB200_SKINNY_GEMM", "1") != "0"
+_SKINNY_CLUSTER = os.environ.get("DSB200_SKINNY_CLUSTER", "1") != "0"
 native.register_sigs({"dsb200_gemm_skinny_bf16": "pppp iii iii i p"})
 
 
@@ -51,12 +52,15 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
         out = torch.empty(M, ld, dtype=out_dtype, device=a.device)[:, :N]  # e.g. a vocabulary of 50257: padded rows, [M, N] view
     assert out.shape == (M, N) and out.stride(1) == 1
     f32 = out.dtype == torch.float32
-    if (M <= 128 and 512 <= N < 148 * 128 and not (a_mn or b_mn or accumulate or f32) and K % 8 == 0 and N % 4 == 0 and out.stride(0) % 4 == 0 and
+    if (M <= 128 and (M <= 32 or N <= 2048) and 512 <= N < 148 * 128 and not (a_mn or b_mn or accumulate or f32) and K % 8 == 0 and N % 4 == 0 and out.stride(0) % 4 == 0 and
             a.stride(0) % 8 == 0 and b.stride(0) % 8 == 0 and _SKINNY_ON):
         # decode-sized problem whose 128 x 256 output tiles would not fill the SMs: weight-streaming kernel (swapped roles, split K).
-        # (With >= 148 row tiles of the weight the tile kernel already streams at full rate: profiles/gemm_skinny_bench.json.)
+        # Measured window (profiles/gemm_skinny_bench.json): up to 32 rows, or narrow outputs; with 64+ rows and wide outputs, or
+        # >= 148 row tiles of the weight, the tile kernel is as fast or faster.
         tiles, kb = -(-N // 128), -(-K // 64)
         splits = max(1, min(kb // 4, (148 if not max_ctas else max_ctas) // tiles))
+        # (<= 8 slices reduce inside a thread-block cluster, one kernel; more go through the workspace + reduce kernel, which
+        # measured faster than capping a 10-tile problem at 8 slices: profiles/gemm_skinny_bench.json)
         ws = torch.empty(splits * M * N, dtype=torch.float32, device=a.device) if splits > 1 else None
         rc = native.lib().dsb200_gemm_skinny_bf16(native.ptr(a), native.ptr(b), native.ptr(out), native.ptr(ws), M, N, K, a.stride(0), b.stride(0),
                                                   out.stride(0), splits, native.stream_ptr())
