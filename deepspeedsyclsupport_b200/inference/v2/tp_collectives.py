@@ -9,7 +9,7 @@ projection of every layer, and all-gather the vocab-parallel logits (inference/v
   add the residual).  For many tokens on many ranks the one-shot pull moves (W-1) x the output per rank, so from
   `two_shot_min_rows` rows on (and W >= 4) the reduce-scatter form of the kernel is used -- every rank reduces 1/W of the rows --
   followed by a multicast-store all-gather of the row blocks through the switch (csrc/comm/symm.cu nvls_allgather_kernel).
-  Decode-sized calls (<= 128 rows) are a read of the weight shard: they take the weight-streaming GEMM (every SM, split K)
+  Decode-sized calls (<= 32 rows, the window where the weight-streaming GEMM wins) are a read of the weight shard: they take the weight-streaming GEMM (every SM, split K)
   into the symmetric staging area + an in-place switch reduction instead.
 * `all_reduce(y)` for outputs produced by another kernel (fp8 / MoE GEMMs): in place through the switch
   (`multimem.ld_reduce` + `multimem.st`), or the one-shot pull kernel without a multicast mapping.
@@ -68,7 +68,7 @@ class RaggedTPCollectives:
             out = self.symm.view(self._act_off, (rows, self.hidden), torch.bfloat16).clone()
             self.symm.barrier()                               # staging may be overwritten by the next call
             return out
-        if rows <= 128 and self.nvls and (rows * self.hidden) % (8 * W) == 0 and w.shape[1] % 8 == 0:
+        if rows <= 32 and self.nvls and (rows * self.hidden) % (8 * W) == 0 and w.shape[1] % 8 == 0:
             # decode-sized: the op is a read of the weight shard.  The fused kernel's 128 x 256 output tiles put hidden/256 CTAs
             # on it; the weight-streaming GEMM (csrc/gemm/gemm_skinny.cu) uses every SM and writes straight into the symmetric
             # staging area, which the switch then reduces in place (multimem.ld_reduce + multicast store).
