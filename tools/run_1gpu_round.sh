@@ -1,36 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_kernels_gpu.py -q -x -k "skinny or mixed_gemm or fastgen" > gpurun_out/k_tests.log 2>&1
-echo "subset rc=$?"; tail -4 gpurun_out/k_tests.log | cut -c1-300
-timeout 200 python - <<'PY' > gpurun_out/skinny_bench.log 2>&1
-import torch, json, sys, os
-sys.path.insert(0, '.')
-from bench import ClockSampler
-from deepspeedsyclsupport_b200.ops import gemm as G
-peaks = json.load(open('MEASURED_PEAKS.json')) if os.path.exists('MEASURED_PEAKS.json') else {}
-flush = torch.empty(256 << 20, dtype=torch.uint8, device='cuda')
-def timed(fn, iters=20):
-    for _ in range(3): fn()
-    torch.cuda.synchronize(); tot = 0.0
-    for _ in range(iters):
-        flush.zero_()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record(); torch.cuda.synchronize(); tot += a.elapsed_time(b)
-    return tot / iters
-s = ClockSampler(0); s.start()
-rows = []
-for name, M, N, K in [("qkv 70B/TP8", 16, 1280, 8192), ("gate_up 70B/TP8", 16, 7168, 8192), ("down 70B/TP8", 16, 8192, 3584), ("o 70B/TP8", 16, 8192, 1024),
-                      ("qkv 70B/TP8 x64", 64, 1280, 8192), ("gate_up 70B/TP8 x64", 64, 7168, 8192), ("down 70B/TP8 x64", 64, 8192, 3584),
-                      ("qkv 70B/TP2", 16, 5120, 8192), ("gate_up 70B/TP2", 64, 28672, 8192), ("lm_head", 64, 32000, 8192), ("gate_up 7B", 128, 22016, 4096)]:
-    x = torch.randn(M, K, device='cuda').bfloat16(); w = (torch.randn(N, K, device='cuda') * 0.02).bfloat16()
-    G._SKINNY_ON = True; G._SKINNY_CLUSTER = True; t1 = timed(lambda: G.gemm(x, w))
-    G._SKINNY_CLUSTER = False; t2 = timed(lambda: G.gemm(x, w))
-    G._SKINNY_ON = False; t0 = timed(lambda: G.gemm(x, w))
-    tl = timed(lambda: torch.matmul(x, w.t()))
-    best = min(t1, t2); gbs = N * K * 2 / best / 1e6
-    rows.append({"shape": name, "M": M, "N": N, "K": K, "skinny_cluster_ms": round(t1, 4), "skinny_workspace_ms": round(t2, 4), "tile_kernel_ms": round(t0, 4),
-                 "cublas_ms": round(tl, 4), "weight_gbytes_per_s": round(gbs, 1), "fraction_of_hbm_gbs": round(gbs / peaks.get("hbm_gbs", 6537.6), 3)})
-doc = {"what": "decode-sized bf16 GEMMs: weight-streaming kernel (csrc/gemm/gemm_skinny.cu; split K reduced inside a cluster over DSMEM, or through a workspace + reduce kernel) vs the 128x256-tile kernel vs cuBLAS (torch.matmul); CUDA events, L2 flushed between iterations; shapes >= 148 row tiles are routed to the tile kernel by ops.gemm", "rows": rows, "clocks": s.stop()}
-print(json.dumps(doc, indent=1)); open('gpurun_out/gemm_skinny_bench.json', 'w').write(json.dumps(doc, indent=1) + "\n")
-PY
-echo "skinny bench rc=$?"; grep -E "shape|_ms|fraction" gpurun_out/skinny_bench.log | tr -d '\n' | sed 's/"shape"/\n"shape"/g' | cut -c1-260
+timeout 1800 python -m pytest tests -m gpu -q -x > gpurun_out/gpu_tests.log 2>&1
+echo "pytest rc=$?"; tail -3 gpurun_out/gpu_tests.log | cut -c1-300
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1
+echo "smoke rc=$?"; tail -2 gpurun_out/smoke.log | cut -c1-200
+timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/bench_own_1gpu_final.json 2> gpurun_out/bench_own_1gpu_final.err
+echo "bench rc=$?"; tail -1 gpurun_out/bench_own_1gpu_final.json | cut -c1-700
