@@ -97,6 +97,19 @@ double dsbh_sumsq(const void* g, int grad_type, int64_t n);
 
 /* ==== generated by tools/gen_header.py from csrc/ -- do not edit below this line ==== */
 
+/* ---- csrc/attn/evoformer.cu */
+/* dtype: 0 bf16, 1 fp16.  q, k, v, o: [B][N][L][H][D] contiguous, D <= 64; bias1 [B][N][L] or NULL; bias2 [B][H][L][L] or NULL (same dtype);
+ * lse: [B][N][H][L] fp32 (written). */
+int dsb200_evoformer_attn_fwd(const void* q, const void* k, const void* v, const void* bias1, const void* bias2, void* o,
+                              float* lse, int B, int N, int L, int H, int D, float scale, int dtype,
+                              dsb200_stream_t stream);
+/* Gradients: dq, dk, dv as q; dbias1 [B][N][L] / dbias2 [B][H][L][L] fp32, ZERO-INITIALISED by the caller (NULL = not wanted);
+ * delta: [B][N][H][L] fp32 scratch. */
+int dsb200_evoformer_attn_bwd(const void* q, const void* k, const void* v, const void* bias1, const void* bias2,
+                              const void* o, const void* d_o, const float* lse, void* dq, void* dk, void* dv, float* delta,
+                              float* dbias1, float* dbias2, int B, int N, int L, int H, int D, float scale, int dtype,
+                              dsb200_stream_t stream);
+
 /* ---- csrc/attn/flash_bwd.cu */
 /* Gradient of dsb200_flash_attn_fwd.  dout/out: [B*S, hq*D] bf16; qkv, dqkv: packed [B*S, (hq+2*hkv)*D] bf16;
  * lse: [B, hq, S] from the forward.  Scratch supplied by the caller: dq_acc [B*S, hq*D] fp32 ZERO-INITIALISED,

@@ -1073,3 +1073,53 @@ def test_mixed_gemm_weight_only_quantised_skinny(bits, M, N, K, group):
     ref = x.float() @ _dequant(wq, sc, bits, torch.float32).t()
     err = (out.float() - ref).abs().max().item()
     assert err < 0.01 * ref.abs().max().item() + 1e-2, (bits, M, N, K, group, err)
+
+
+@pytest.mark.parametrize("B,N,L,H,D,dtype,use_b1,use_b2", [(1, 3, 70, 2, 32, torch.bfloat16, True, True), (2, 2, 33, 3, 64, torch.float16, True, False),
+                                                         (1, 2, 128, 4, 16, torch.bfloat16, False, True), (1, 1, 17, 1, 8, torch.bfloat16, False, False)])
+def test_evoformer_attention_kernels(B, N, L, H, D, dtype, use_b1, use_b2):
+    """csrc/attn/evoformer.cu (fused forward + LSE, row / column backward passes with bias gradients) against the explicit fp32
+    formula and its autograd gradients; bias1 carries -inf style mask entries."""
+    import math
+    from deepspeedsyclsupport_b200.ops.deepspeed4science.evoformer_attn import DS4Sci_EvoformerAttention, _native_ok
+    torch.manual_seed(L + D)
+    dev = "cuda"
+    q, k, v = (torch.randn(B, N, L, H, D, device=dev).to(dtype).requires_grad_(True) for _ in range(3))
+    biases = []
+    b1 = b2 = None
+    if use_b1:
+        mask = torch.rand(B, N, 1, 1, L, device=dev) < 0.2
+        mask[..., 0] = False  # never a fully masked row
+        b1 = (torch.randn(B, N, 1, 1, L, device=dev) * 0.5).masked_fill(mask, -1e4).to(dtype).requires_grad_(True)
+    if use_b2:
+        b2 = torch.randn(B, 1, H, L, L, device=dev).to(dtype).requires_grad_(True)
+    biases = [b for b in (b1, b2) if b is not None] if (use_b1 or not use_b2) else [None, b2]
+    assert _native_ok(q, k, v, b1, b2)
+    out = DS4Sci_EvoformerAttention(q, k, v, biases)
+    g = torch.randn_like(out)
+    out.backward(g)
+    # fp32 oracle on the same (rounded) inputs
+    qf, kf, vf = (t.detach().float().requires_grad_(True) for t in (q, k, v))
+    b1f = None if b1 is None else b1.detach().float().requires_grad_(True)
+    b2f = None if b2 is None else b2.detach().float().requires_grad_(True)
+    s = torch.einsum("bnihd,bnjhd->bnhij", qf, kf) / math.sqrt(D)
+    if b1f is not None:
+        s = s + b1f  # [B, N, 1, 1, L] broadcasts over heads and query rows
+    if b2f is not None:
+        s = s + b2f  # [B, 1, H, L, L] broadcasts over N
+    ref = torch.einsum("bnhij,bnjhd->bnihd", torch.softmax(s, -1), vf)
+    ref.backward(g.float())
+    tol = 2e-2 if dtype == torch.bfloat16 else 4e-3
+
+    def close(a, b_, name):
+        err = (a.float() - b_).abs().max().item()
+        assert err <= tol * max(1.0, b_.abs().max().item()), (name, err, b_.abs().max().item())
+
+    close(out, ref, "out")
+    close(q.grad, qf.grad, "dq")
+    close(k.grad, kf.grad, "dk")
+    close(v.grad, vf.grad, "dv")
+    if b1 is not None:
+        close(b1.grad, b1f.grad, "dbias1")
+    if b2 is not None:
+        close(b2.grad, b2f.grad, "dbias2")

@@ -17,7 +17,7 @@ def main():
             importlib.import_module("deepspeedsyclsupport_b200.ops." + m)
         except ImportError:
             pass
-    for m in ("parallel.symm", "parallel.fused", "inference.v2.kernels", "inference.v2.kernels.cutlass_ops", "runtime.comm.compressed", "ops.random_ltd.dropping_utils", "ops.spatial", "moe.peer_dispatch", "sequence.fused"):
+    for m in ("parallel.symm", "parallel.fused", "inference.v2.kernels", "inference.v2.kernels.cutlass_ops", "runtime.comm.compressed", "ops.random_ltd.dropping_utils", "ops.spatial", "ops.deepspeed4science.evoformer_attn", "moe.peer_dispatch", "sequence.fused"):
         try:
             importlib.import_module("deepspeedsyclsupport_b200." + m)
         except ImportError:
