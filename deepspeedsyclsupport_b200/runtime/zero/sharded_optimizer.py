@@ -526,6 +526,7 @@ class ZeroShardedOptimizer:
                                     sumsq=self._p2p_sumsq if fuse_norm else None, max_ctas=self._p2p_comm_ctas)
         u.full_grad = None
         u.reduced = True
+        self._zeropp_serialise(self.rs_stream)
 
     # ---- reduce-scatter fused with the partitioned AdamW update (csrc/comm/symm.cu rs_adam_kernel)
     def _rs_adam_enabled(self):
@@ -850,6 +851,16 @@ class ZeroShardedOptimizer:
         u.full[r * n:(r + 1) * n].copy_(u.shard)
         stage_q.record_stream(torch.cuda.current_stream())
         stage_s.record_stream(torch.cuda.current_stream())
+        self._zeropp_serialise(torch.cuda.current_stream())
+
+    def _zeropp_serialise(self, stream):
+        """UNVALIDATED mitigation for more than 4 ranks.  The ZeRO++ peer path runs at 2 and 4 GPUs; at 8 GPUs the asynchronous
+        run dead-locks in a device barrier while the same run with CUDA_LAUNCH_BLOCKING=1 completes (profiles/zeropp_8gpu/), i.e.
+        the hazard needs the host to run ahead of the device.  Until it is found, the host waits for every quantised gather /
+        reduce chain on such groups, which bounds the run-ahead to one unit (at some cost in overlap).  DSB200_ZEROPP_UNIT_SYNC=0
+        restores the fully asynchronous behaviour."""
+        if self.shard_world > 4 and os.environ.get("DSB200_ZEROPP_UNIT_SYNC", "1") != "0":
+            stream.synchronize()
 
     def _p2p_refresh_qwz(self):
         """Re-quantise this rank's parameter shard into its symmetric fp8 twin (after every update of the shard)."""
