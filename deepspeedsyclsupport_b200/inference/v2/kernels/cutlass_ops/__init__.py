@@ -71,7 +71,7 @@ def _mixed_skinny(x, weights, scales, num_bits):
     sc = scales if (scales.dtype == torch.float32 and scales.is_contiguous()) else scales.float().contiguous()
     wq = weights if weights.is_contiguous() else weights.contiguous()
     tiles, kb = -(-N // 128), K // 64
-    splits = max(1, min(kb // 4, 148 // tiles)) if tiles < 148 else 1
+    splits = max(1, min(148 // tiles, kb // (32 if tiles >= 32 else 8))) if tiles < 148 else 1  # as ops.gemm.gemm
     out = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
     ws = torch.empty(splits * M * N, dtype=torch.float32, device=x.device) if splits > 1 else None
     rc = native.lib().dsb200_gemm_skinny_mixed(native.ptr(x), native.ptr(wq), native.ptr(sc), native.ptr(out), native.ptr(ws), M, N, K,

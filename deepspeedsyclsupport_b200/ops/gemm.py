@@ -29,6 +29,7 @@ def _gemm_ref(a, b, a_mn, b_mn, out_dtype, out=None, accumulate=False):
 
 _SKINNY_ON = os.environ.get("DSB200_SKINNY_GEMM", "1") != "0"
 _SKINNY_CLUSTER = os.environ.get("DSB200_SKINNY_CLUSTER", "1") != "0"
+_FORCE_SPLITS = int(os.environ.get("DSB200_SKINNY_SPLITS", "0"))  # diagnostics: force the number of K slices
 native.register_sigs({"dsb200_gemm_skinny_bf16": "pppp iii iii i p"})
 
 
@@ -58,7 +59,10 @@ def gemm(a, b, *, a_mn=False, b_mn=False, out=None, out_dtype=torch.bfloat16, ac
         # Measured window (profiles/gemm_skinny_bench.json): up to 32 rows, or narrow outputs; with 64+ rows and wide outputs, or
         # >= 148 row tiles of the weight, the tile kernel is as fast or faster.
         tiles, kb = -(-N // 128), -(-K // 64)
-        splits = max(1, min(kb // 4, (148 if not max_ctas else max_ctas) // tiles))
+        # K slices: enough CTAs to fill the SMs, but every slice keeps >= 32 k-blocks once the row tiles alone cover a quarter of
+        # the machine (measured, tools/skinny_splits_probe.py: 64 tiles x K = 3584 / 1024 are fastest unsplit, 56 tiles x K = 8192
+        # with 2 slices, 10 tiles x K = 8192 with 8 - 14)
+        splits = _FORCE_SPLITS or max(1, min((148 if not max_ctas else max_ctas) // tiles, kb // (32 if tiles >= 32 else 8)))
         # (<= 8 slices reduce inside a thread-block cluster, one kernel; more go through the workspace + reduce kernel, which
         # measured faster than capping a 10-tile problem at 8 slices: profiles/gemm_skinny_bench.json)
         ws = torch.empty(splits * M * N, dtype=torch.float32, device=a.device) if splits > 1 else None
