@@ -62,6 +62,7 @@ struct Params {
   float* part_ml;          // [T][hq][n_splits][2]
   int T, hq, hkv, group, nt_tile, block_size, max_blocks, n_splits;
   float scale_log2;
+  const float* alibi;  // optional [hq] ALiBi slopes: score += slope[head] * key position (BLOOM / MPT / falcon-rw); nullptr = none
   long long* trace;  // diagnostics only (DSB200_PF_TRACE=1): clock64 stamps of the first CTA with >= 8 pages, [page][8 events]
 };
 // events: 0 K landed (MMA thread)  1 P ready seen by the MMA thread  2 S ready seen by softmax  3 P published  4 partial O read
@@ -275,6 +276,11 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       // has grown by more than 2^8 is O (in TMEM, accumulated by the tensor core) read, rescaled and written back.  Reading
       // the partial O of every page back into registers cost as much TMEM bandwidth as reading S (64 B/clk/SM, the limiter).
       float m_run = -INFINITY, l_run = 0.f;
+      // ALiBi: the biased score is formed in the exp2 domain right after the mask (s * scale_log2 + slope_log2 * key), after which
+      // the running maximum / exponent arithmetic below uses a scale of 1
+      const bool has_alibi = p.alibi != nullptr;
+      const float slope_l2 = (has_alibi && live) ? p.alibi[kvh * p.group + g] * 1.4426950408889634f : 0.f;
+      const float sl2 = has_alibi ? 1.f : p.scale_log2;
       __nv_bfloat16* xmax = reinterpret_cast<__nv_bfloat16*>(smem + SMEM::X_OFF);  // [part][row]
       const uint32_t bar_a = 1 + q4, bar_b = 5 + q4;  // the 4 warps (128 threads) that share the rows of this quarter
       const uint32_t o_addr = TM_O + part * DQ + lane_off;
@@ -317,6 +323,11 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           for (int i = 0; i < 32; ++i)
             if (i >= visible) sv[i] = 0xff800000u;  // -inf: exp2 gives exactly 0 below
         }
+        if (has_alibi) {
+          const float key0 = static_cast<float>((pg0 + j) * BN + part * 32);
+#pragma unroll
+          for (int i = 0; i < 32; ++i) sv[i] = __float_as_uint(fmaf(__uint_as_float(sv[i]), p.scale_log2, slope_l2 * (key0 + i)));
+        }
         float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
         for (int i = 0; i < 32; ++i) mx[i & 3] = fmaxf(mx[i & 3], __uint_as_float(sv[i]));
@@ -327,7 +338,7 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         const float m_blk = fmaxf(fmaxf(__bfloat162float(xmax[row]), __bfloat162float(xmax[128 + row])),
                                   fmaxf(__bfloat162float(xmax[256 + row]), __bfloat162float(xmax[384 + row])));
         // a page with no visible key for this row leaves the reference alone (and -inf - -inf is never formed)
-        const float m_cand = fmaxf(m_run, m_blk * p.scale_log2);
+        const float m_cand = fmaxf(m_run, m_blk * sl2);
         const bool fresh = m_run == -INFINITY;  // nothing accumulated for this row yet: O row and l are exactly 0
         const float m_new = (fresh || m_cand - m_run > 8.f) ? m_cand : m_run;
         const bool rescale = !fresh && m_new != m_run && j > 0;
@@ -352,7 +363,7 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         // The MUFU unit (16 ex2 / clk / SM: 1024 cycles for a 128 x 128 page) is the limiter of this loop: 3 pairs of every 8
         // take the polynomial exp2 on the FMA pipe, in packed fp32x2 arithmetic
         uint32_t pk[16];
-        const uint64_t sc2 = pack2(p.scale_log2, p.scale_log2), negm2 = pack2(-m_use, -m_use);
+        const uint64_t sc2 = pack2(sl2, sl2), negm2 = pack2(-m_use, -m_use);
         uint64_t l2a = 0ull, l2b = 0ull;
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -647,11 +658,15 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t bar_id = 1 + part;  // the 4 warps (128 key-lanes) that share these columns
       float m_run[CPT], l_part[CPT];  // reference maximum per column (uniform over the part), this key-lane's share of the sums
       int limit[CPT];                 // keys [0, limit) are visible to column c
+      float slope_l2[CPT];            // ALiBi slope of the column's head, exp2 domain (0 without ALiBi)
+      const bool has_alibi = p.alibi != nullptr;
+      const float sl2 = has_alibi ? 1.f : p.scale_log2;
 #pragma unroll
       for (int i = 0; i < CPT; ++i) {
         m_run[i] = -INFINITY;
         l_part[i] = 0.f;
         limit[i] = c0 + i < nq ? pos0 + (c0 + i) / p.group + 1 : 0x3fffffff;
+        slope_l2[i] = (has_alibi && c0 + i < nq) ? p.alibi[kvh * p.group + (c0 + i) % p.group] * 1.4426950408889634f : 0.f;
       }
       const uint32_t s_addr0 = tmem_base + c0 + lane_off, o_addr = tmem_base + 32 + c0 + lane_off;
       for (int j = 0; j < n_blocks; ++j) {
@@ -669,6 +684,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 #pragma unroll
         for (int i = 0; i < CPT; ++i) {
           s[i] = key >= limit[i] ? -INFINITY : __uint_as_float(sv[i]);
+          if (has_alibi) s[i] = fmaf(s[i], p.scale_log2, slope_l2[i] * static_cast<float>(key));
           const uint32_t bits = __float_as_uint(s[i]);
           const uint32_t r = __reduce_max_sync(0xffffffffu, bits ^ ((bits >> 31) ? 0xffffffffu : 0x80000000u));
           wm[i] = __uint_as_float(r ^ ((r >> 31) ? 0x80000000u : 0xffffffffu));
@@ -690,7 +706,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         float alpha[CPT], m_use[CPT];
 #pragma unroll
         for (int i = 0; i < CPT; ++i) {
-          const float m_cand = fmaxf(m_run[i], comb[i] * p.scale_log2);
+          const float m_cand = fmaxf(m_run[i], comb[i] * sl2);
           const bool fresh = m_run[i] == -INFINITY;
           const float m_new = (fresh || m_cand - m_run[i] > 8.f) ? m_cand : m_run[i];
           const bool rescale = !fresh && m_new != m_run[i];
@@ -722,7 +738,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         for (int i = 0; i < CPT; ++i) {
           const int c = c0 + i;
           if (c < nq) {
-            const float e = ex2_fast(fmaf(s[i], p.scale_log2, -m_use[i]));
+            const float e = ex2_fast(fmaf(s[i], sl2, -m_use[i]));
             l_part[i] += e;
             *reinterpret_cast<__nv_bfloat16*>(pbuf + c * 128 + ((((k64 >> 3) ^ (c & 7)) << 4) | ((k64 & 7) << 1))) = __float2bfloat16_rn(e);
           }
@@ -809,7 +825,7 @@ __global__ void combine_splits_kernel(const float* __restrict__ part_o, const fl
 template <int D>
 static int launch(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos, const int* block_table,
                   int T, int hq, int hkv, int block_size, int max_blocks, int num_blocks, float scale, int max_atoms, int n_splits,
-                  void* scratch, cudaStream_t stream) {
+                  void* scratch, const float* alibi, cudaStream_t stream) {
   using SMEM = Smem<D>;
   const int group = hq / hkv, nt_tile = BM / group;
   const int heads = hq + 2 * hkv;
@@ -848,7 +864,7 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
   p.tok_seq = tok_seq; p.tok_pos = tok_pos; p.block_table = block_table; p.atoms = atoms; p.n_atoms = n_atoms;
   p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
   p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
-  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f;
+  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.alibi = alibi;
   static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
   static long long* trace_buf = nullptr;
   p.trace = nullptr;
@@ -881,7 +897,7 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
 // decode variant: atoms of at most 16 / group tokens, head_dim 128
 static int launch_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos, const int* block_table,
                          int T, int hq, int hkv, int block_size, int max_blocks, int num_blocks, float scale, int max_atoms,
-                         int n_splits, void* scratch, cudaStream_t stream) {
+                         int n_splits, void* scratch, const float* alibi, cudaStream_t stream) {
   constexpr int D = 128;
   const int group = hq / hkv, nt_tile = NQ / group;
   const int heads = hq + 2 * hkv;
@@ -915,7 +931,7 @@ static int launch_decode(const void* qkv, const void* kv_cache, void* out, const
   p.tok_seq = tok_seq; p.tok_pos = tok_pos; p.block_table = block_table; p.atoms = nullptr; p.n_atoms = nullptr;
   p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
   p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
-  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.trace = nullptr;
+  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.trace = nullptr; p.alibi = alibi;
   static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
   static long long* trace_buf = nullptr;
   if (want_trace) {
@@ -958,10 +974,11 @@ DSB_EXPORT long long dsb200_paged_flash_scratch_bytes(int n_tokens, int hq, int 
 // out[t][hq*D] = attention of ragged token t over keys [0, tok_pos[t]] of its sequence, KV read from the blocked cache
 // [num_blocks][2][block_size][hkv][D] (bf16) through the block table.  max_atoms >= number of atoms of the batch
 // (<= n_tokens; ceil(n_tokens / (128/group)) + number of sequences is enough).  n_splits >= 1 splits the KV range of every atom.
+// alibi_slopes: optional [hq] fp32 (device): score += slope[head] * key position; NULL = none.
 DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                                             const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                             int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                                            void* scratch, cudaStream_t stream) {
+                                            void* scratch, const float* alibi_slopes, cudaStream_t stream) {
   using namespace dsb;
   if (n_tokens == 0) return DSB_OK;
   DSB_REQUIRE(head_dim == 64 || head_dim == 128, "paged_flash: head_dim %d unsupported (64 or 128)", head_dim);
@@ -970,9 +987,9 @@ DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cach
   DSB_REQUIRE(max_atoms >= 1 && n_splits >= 1 && n_splits <= 64 && scratch != nullptr, "paged_flash: bad max_atoms / n_splits / scratch");
   if (head_dim == 128)
     return paged::launch<128>(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                              num_blocks, scale, max_atoms, n_splits, scratch, stream);
+                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
   return paged::launch<64>(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                           num_blocks, scale, max_atoms, n_splits, scratch, stream);
+                           num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
 }
 
 // Same contract as dsb200_paged_flash_attention for batches of small atoms (decode steps): atoms hold at most 16 / group tokens,
@@ -981,7 +998,7 @@ DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cach
 DSB_EXPORT int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                                          const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                          int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                                         void* scratch, cudaStream_t stream) {
+                                         void* scratch, const float* alibi_slopes, cudaStream_t stream) {
   using namespace dsb;
   if (n_tokens == 0) return DSB_OK;
   DSB_REQUIRE(head_dim == 128, "paged_flash_decode: head_dim %d unsupported (128)", head_dim);
@@ -989,5 +1006,5 @@ DSB_EXPORT int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, 
   DSB_REQUIRE(block_size >= 8 && block_size <= 128 && 128 % block_size == 0, "paged_flash_decode: KV block size %d must divide 128", block_size);
   DSB_REQUIRE(max_atoms >= 1 && n_splits >= 1 && n_splits <= 64 && scratch != nullptr, "paged_flash_decode: bad max_atoms / n_splits / scratch");
   return paged::launch_decode(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                              num_blocks, scale, max_atoms, n_splits, scratch, stream);
+                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
 }

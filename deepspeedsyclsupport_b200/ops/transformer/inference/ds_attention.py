@@ -16,6 +16,7 @@ from torch import nn
 from ....accelerator import get_accelerator
 from ... import gemm as G
 from .kv_arena import KVArena
+from .kv_arena import alibi_slopes_of
 from .kv_arena import eligible as arena_eligible
 
 
@@ -70,12 +71,13 @@ class DeepSpeedSelfAttention(nn.Module):
         self.k_cache = self.v_cache = None  # [B, heads_kv, T, D] -- masked / biased path only
         self.arena = KVArena(min_tokens=max(int(getattr(config, "max_out_tokens", 1024) or 1024), 128))
         self._inv_freq = None
+        self._alibi_slopes = None  # per-head ALiBi slopes read off the first alibi tensor seen (BLOOM)
 
     def reset_cache(self):
         self.k_cache = self.v_cache = None
         self.arena.reset()
 
-    def _forward_arena(self, qkv, B, S, get_present):
+    def _forward_arena(self, qkv, B, S, get_present, alibi=None):
         """Plain causal attention on the tensor-core kernels: rotary + append into the layer's KV arena, paged flash attention."""
         cfg = self.config
         inv_freq, rot = None, 0
@@ -90,7 +92,12 @@ class DeepSpeedSelfAttention(nn.Module):
                 x = qkv.view(B, S, self.heads + 2 * self.kv_heads, self.head_dim)
                 n = self.heads + self.kv_heads
                 x[:, :, :n] = apply_rotary(x[:, :, :n], pos, cfg.rotary_dim, cfg.rope_theta, False)
-        ctx = self.arena.attend(qkv, self.heads, self.kv_heads, self.head_dim, self.scale, inv_freq, rot)
+        slopes = None
+        if alibi is not None:
+            if self._alibi_slopes is None:
+                self._alibi_slopes = alibi_slopes_of(alibi, B, self.heads)
+            slopes = self._alibi_slopes
+        ctx = self.arena.attend(qkv, self.heads, self.kv_heads, self.head_dim, self.scale, inv_freq, rot, alibi_slopes=slopes)
         out = _linear(ctx, self.attn_ow, None)
         if self.mp_group is not None and cfg.mp_size > 1:
             from .... import comm as dist
@@ -112,7 +119,7 @@ class DeepSpeedSelfAttention(nn.Module):
         if layer_past is None and S > 1:
             self.reset_cache()  # a new prompt
         if self.k_cache is None and arena_eligible(qkv, self.head_dim, self.heads, self.kv_heads, self.config, input_mask, alibi, layer_past):
-            return self._forward_arena(qkv, B, S, get_present)
+            return self._forward_arena(qkv, B, S, get_present, alibi)
         if self.k_cache is None and self.arena.length > 0:  # a decode step the arena kernels cannot take: continue densely
             self.k_cache, self.v_cache = (t.contiguous() for t in self.arena.keys_values())
             self.arena.reset()

@@ -32,15 +32,26 @@ def _token_index(B, S, past, device):
     return hit
 
 
+def alibi_slopes_of(alibi, batch, heads):
+    """Per-head slopes of a BLOOM-style ALiBi tensor ([batch * heads, 1, T] or [batch, heads, 1, T] = slope * key position for
+    unpadded sequences), or None when they cannot be read off it (fewer than two key positions)."""
+    al = alibi.reshape(batch, heads, -1)
+    if al.shape[-1] < 2:
+        return None
+    return (al[0, :, 1] - al[0, :, 0]).float().contiguous()
+
+
 def eligible(x, head_dim, heads, kv_heads, cfg, input_mask, alibi, layer_past):
-    """True when the step can run on the arena kernels: bf16 on the GPU, head size 64 / 128, plain causal masking, no additive
-    bias.  Padding masks and ALiBi (BLOOM) keep the general masked-softmax path."""
+    """True when the step can run on the arena kernels: bf16 on the GPU, head size 64 / 128, plain causal masking; ALiBi as
+    per-head slopes (BLOOM).  Padding masks keep the general masked-softmax path."""
     if not (x.is_cuda and x.dtype == torch.bfloat16 and head_dim in (64, 128)) or os.environ.get("DSB200_V1_ARENA", "1") == "0":
         return False
     if heads % kv_heads or 128 % (heads // kv_heads):
         return False
-    if alibi is not None or layer_past is not None or not cfg.triangular_masking or getattr(cfg, "local_attention", False):
+    if layer_past is not None or not cfg.triangular_masking or getattr(cfg, "local_attention", False):
         return False
+    if alibi is not None and (alibi.numel() < 2 * x.shape[0] * heads or x.shape[0] != 1 and input_mask is not None):
+        return False  # slopes are read off the tensor: needs two key positions and unpadded sequences
     return input_mask is None or input_mask.numel() <= 1 or x.shape[0] == 1  # one sequence has no padding to mask
 
 
@@ -72,7 +83,7 @@ class KVArena:
         self.cache, self.batch, self.per_seq = new, B, per_seq
         self.block_table = torch.arange(B * per_seq, device=device, dtype=torch.int32).view(B, per_seq)
 
-    def attend(self, qkv, heads, kv_heads, d, scale, inv_freq=None, rot_dim=0):
+    def attend(self, qkv, heads, kv_heads, d, scale, inv_freq=None, rot_dim=0, alibi_slopes=None):
         """qkv: [B, S, (heads + 2 kv_heads) * d], fresh projection output (rotated and consumed in place).
         Appends the S new rows of every sequence at positions [length, length + S) and returns the context [B, S, heads * d]."""
         from ....inference.v2 import kernels as K  # late: inference/ imports this package while it loads
@@ -85,7 +96,8 @@ class KVArena:
         if inv_freq is None:
             inv_freq, rot_dim = torch.empty(1, device=qkv.device, dtype=torch.float32), 0
         K.kv_rotary_append(flat, self.cache, seq, pos, self.block_table, inv_freq, heads, kv_heads, d, rot_dim)
-        ctx = K.paged_flash_attention(flat, self.cache, seq, pos, self.block_table, heads, kv_heads, d, scale, max_context=self.length + S)
+        ctx = K.paged_flash_attention(flat, self.cache, seq, pos, self.block_table, heads, kv_heads, d, scale, max_context=self.length + S,
+                                      alibi_slopes=alibi_slopes)
         self.length += S
         return ctx.view(B, S, heads * d)
 

@@ -1123,3 +1123,34 @@ def test_evoformer_attention_kernels(B, N, L, H, D, dtype, use_b1, use_b2):
         close(b1.grad, b1f.grad, "dbias1")
     if b2 is not None:
         close(b2.grad, b2f.grad, "dbias2")
+
+
+def test_v1_attention_kv_arena_with_alibi(monkeypatch):
+    """BLOOM-style ALiBi on the arena path: the per-head slopes are read off the alibi tensor and applied inside the paged flash
+    kernels; prompt + decode steps equal the dense masked-softmax path that adds the tensor itself."""
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    from deepspeedsyclsupport_b200.ops.transformer.inference.ds_attention import DeepSpeedSelfAttention
+    torch.manual_seed(3)
+    heads, head_dim = 8, 64
+    H = heads * head_dim
+    cfg = DeepSpeedInferenceConfig(hidden_size=H, heads=heads, dtype=torch.bfloat16, max_out_tokens=256, triangular_masking=True)
+    a, b = DeepSpeedSelfAttention(cfg), DeepSpeedSelfAttention(cfg)
+    for name in ("attn_qkvw", "attn_qkvb", "attn_ow", "attn_ob"):
+        w = torch.randn_like(getattr(a, name).float()) * (0.05 if name.endswith("w") else 0.1)
+        getattr(a, name).data.copy_(w)
+        getattr(b, name).data.copy_(w)
+    slopes = 2.0 ** (-8.0 * torch.arange(1, heads + 1, device="cuda") / heads)
+    B = 1
+    steps = [torch.randn(B, 90, H, device="cuda").bfloat16()] + [torch.randn(B, 1, H, device="cuda").bfloat16() for _ in range(4)]
+    outs = {}
+    for tag, mod, flag in (("arena", a, "1"), ("dense", b, "0")):
+        monkeypatch.setenv("DSB200_V1_ARENA", flag)
+        T, res = 0, []
+        for x in steps:
+            T += x.shape[1]
+            alibi = (slopes[:, None] * torch.arange(T, device="cuda")[None, :]).bfloat16().view(B * heads, 1, T)  # as HF builds it
+            res.append(mod(x.clone(), alibi=alibi)[0])
+        outs[tag] = res
+    assert a.arena.length == 94 and a._alibi_slopes is not None and b.arena.length == 0
+    for oa, ob in zip(outs["arena"], outs["dense"]):
+        assert (oa.float() - ob.float()).abs().max() < 0.04 * ob.float().abs().max() + 2e-3

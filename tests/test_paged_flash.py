@@ -28,12 +28,14 @@ def _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed=0):
             torch.tensor(tok_pos, dtype=torch.int32, device=dev), block_table.to(dev))
 
 
-def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0, decode=None):
+def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0, decode=None, alibi=False):
     from deepspeedsyclsupport_b200.inference.v2 import kernels as K
     qkv, kv, ts, tp, bt = _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed)
     scale = d ** -0.5
-    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits, decode=decode).float()
-    want = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), hq, hkv, d, scale).float().cuda()
+    slopes = (2.0 ** (-8.0 * torch.arange(1, hq + 1) / hq)).float().cuda() if alibi else None  # BLOOM's slopes for a power-of-two head count
+    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits, decode=decode, alibi_slopes=slopes).float()
+    want = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), hq, hkv, d, scale,
+                                 None if slopes is None else slopes.cpu()).float().cuda()
     torch.cuda.synchronize()
     err = (got - want).abs().max().item()
     assert torch.isfinite(got).all() and err < 2e-2, (seq_new, seq_seen, hq, hkv, d, bs, n_splits, decode, err)
@@ -63,6 +65,14 @@ def test_transposed_decode_kernel():
     # ... and forced onto a mixed batch: prefill chunks are cut into atoms of 16 / group tokens, still exact
     _check(seq_new=[37, 1, 9], seq_seen=[100, 640, 0], hq=8, hkv=1, d=128, bs=128, seed=8, decode=True, n_splits=2)
     _check(seq_new=[40, 1], seq_seen=[250, 17], hq=8, hkv=8, d=128, bs=32, seed=9, decode=True)
+
+
+def test_alibi_slopes_in_both_kernels():
+    # score += slope[head] * key position: prefill chunks + decode in the general kernel, pure decode in the transposed one
+    _check(seq_new=[150, 1, 20], seq_seen=[0, 300, 77], hq=8, hkv=8, d=64, bs=128, seed=11, alibi=True, decode=False)
+    _check(seq_new=[40, 1], seq_seen=[500, 129], hq=8, hkv=2, d=128, bs=64, seed=12, alibi=True, decode=False, n_splits=3)
+    _check(seq_new=[1, 1, 1, 1], seq_seen=[0, 130, 1000, 2047], hq=16, hkv=16, d=128, bs=128, seed=13, alibi=True, decode=True)
+    _check(seq_new=[1, 1], seq_seen=[700, 31], hq=8, hkv=1, d=128, bs=128, seed=14, alibi=True, decode=True, n_splits=2)
 
 
 def test_dispatch_uses_flash_kernel_and_falls_back():
