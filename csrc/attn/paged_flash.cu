@@ -62,6 +62,7 @@ struct Params {
   float* part_ml;          // [T][hq][n_splits][2]
   int T, hq, hkv, group, nt_tile, block_size, max_blocks, n_splits;
   float scale_log2;
+  int window;          // local attention: keys [pos - window + 1, pos] are visible; 0 = the whole history
   const float* alibi;  // optional [hq] ALiBi slopes: score += slope[head] * key position (BLOOM / MPT / falcon-rw); nullptr = none
   long long* trace;  // diagnostics only (DSB200_PF_TRACE=1): clock64 stamps of the first CTA with >= 8 pages, [page][8 events]
 };
@@ -271,6 +272,7 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       // keys [0, limit) are visible.  Dead rows (past the atom) see everything: their operands are finite (TMA zero fill /
       // other tokens' rows, zero-initialised cache) and nothing of theirs is stored
       const int limit = live ? pos0 + ti + 1 : 0x3fffffff;
+      const int first = (live && p.window > 0) ? max(0, pos0 + ti + 1 - p.window) : 0;  // first visible key (local attention)
       constexpr int DQ = D / 4;
       // m_run is the reference maximum P and O are expressed in.  It follows the true running maximum lazily: only when that
       // has grown by more than 2^8 is O (in TMEM, accumulated by the tensor core) read, rescaled and written back.  Reading
@@ -318,10 +320,11 @@ paged_flash_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         uint32_t sv[32];  // the thread's scores stay in registers for both passes
         tmem_ld_32x32(s_addr, sv);
         tmem_ld_wait();
-        if (!__all_sync(0xffffffffu, visible >= 32)) {  // only the diagonal page(s)
+        const int hidden = first - ((pg0 + j) * BN + part * 32);  // keys [0, hidden) of the thread's 32 precede the local window
+        if (!__all_sync(0xffffffffu, visible >= 32 && hidden <= 0)) {  // only the diagonal page(s) / the window's first page(s)
 #pragma unroll
           for (int i = 0; i < 32; ++i)
-            if (i >= visible) sv[i] = 0xff800000u;  // -inf: exp2 gives exactly 0 below
+            if (i >= visible || i < hidden) sv[i] = 0xff800000u;  // -inf: exp2 gives exactly 0 below
         }
         if (has_alibi) {
           const float key0 = static_cast<float>((pg0 + j) * BN + part * 32);
@@ -657,7 +660,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       float* xmax = reinterpret_cast<float*>(smem + SMEM::X_OFF);  // [parity][warp quarter][16]
       const uint32_t bar_id = 1 + part;  // the 4 warps (128 key-lanes) that share these columns
       float m_run[CPT], l_part[CPT];  // reference maximum per column (uniform over the part), this key-lane's share of the sums
-      int limit[CPT];                 // keys [0, limit) are visible to column c
+      int limit[CPT], first[CPT];     // keys [first, limit) are visible to column c
       float slope_l2[CPT];            // ALiBi slope of the column's head, exp2 domain (0 without ALiBi)
       const bool has_alibi = p.alibi != nullptr;
       const float sl2 = has_alibi ? 1.f : p.scale_log2;
@@ -666,6 +669,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         m_run[i] = -INFINITY;
         l_part[i] = 0.f;
         limit[i] = c0 + i < nq ? pos0 + (c0 + i) / p.group + 1 : 0x3fffffff;
+        first[i] = (c0 + i < nq && p.window > 0) ? max(0, limit[i] - p.window) : 0;
         slope_l2[i] = (has_alibi && c0 + i < nq) ? p.alibi[kvh * p.group + (c0 + i) % p.group] * 1.4426950408889634f : 0.f;
       }
       const uint32_t s_addr0 = tmem_base + c0 + lane_off, o_addr = tmem_base + 32 + c0 + lane_off;
@@ -683,7 +687,7 @@ paged_decode_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // then the 4 lane-quarter warps meet in shared memory
 #pragma unroll
         for (int i = 0; i < CPT; ++i) {
-          s[i] = key >= limit[i] ? -INFINITY : __uint_as_float(sv[i]);
+          s[i] = (key >= limit[i] || key < first[i]) ? -INFINITY : __uint_as_float(sv[i]);
           if (has_alibi) s[i] = fmaf(s[i], p.scale_log2, slope_l2[i] * static_cast<float>(key));
           const uint32_t bits = __float_as_uint(s[i]);
           const uint32_t r = __reduce_max_sync(0xffffffffu, bits ^ ((bits >> 31) ? 0xffffffffu : 0x80000000u));
@@ -825,7 +829,7 @@ __global__ void combine_splits_kernel(const float* __restrict__ part_o, const fl
 template <int D>
 static int launch(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos, const int* block_table,
                   int T, int hq, int hkv, int block_size, int max_blocks, int num_blocks, float scale, int max_atoms, int n_splits,
-                  void* scratch, const float* alibi, cudaStream_t stream) {
+                  void* scratch, const float* alibi, int window, cudaStream_t stream) {
   using SMEM = Smem<D>;
   const int group = hq / hkv, nt_tile = BM / group;
   const int heads = hq + 2 * hkv;
@@ -864,7 +868,7 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
   p.tok_seq = tok_seq; p.tok_pos = tok_pos; p.block_table = block_table; p.atoms = atoms; p.n_atoms = n_atoms;
   p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
   p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
-  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.alibi = alibi;
+  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.alibi = alibi; p.window = window;
   static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
   static long long* trace_buf = nullptr;
   p.trace = nullptr;
@@ -897,7 +901,7 @@ static int launch(const void* qkv, const void* kv_cache, void* out, const int* t
 // decode variant: atoms of at most 16 / group tokens, head_dim 128
 static int launch_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos, const int* block_table,
                          int T, int hq, int hkv, int block_size, int max_blocks, int num_blocks, float scale, int max_atoms,
-                         int n_splits, void* scratch, const float* alibi, cudaStream_t stream) {
+                         int n_splits, void* scratch, const float* alibi, int window, cudaStream_t stream) {
   constexpr int D = 128;
   const int group = hq / hkv, nt_tile = NQ / group;
   const int heads = hq + 2 * hkv;
@@ -931,7 +935,7 @@ static int launch_decode(const void* qkv, const void* kv_cache, void* out, const
   p.tok_seq = tok_seq; p.tok_pos = tok_pos; p.block_table = block_table; p.atoms = nullptr; p.n_atoms = nullptr;
   p.out = static_cast<__nv_bfloat16*>(out); p.part_o = part_o; p.part_ml = part_ml;
   p.T = T; p.hq = hq; p.hkv = hkv; p.group = group; p.nt_tile = nt_tile; p.block_size = block_size; p.max_blocks = max_blocks;
-  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.trace = nullptr; p.alibi = alibi;
+  p.n_splits = n_splits; p.scale_log2 = scale * 1.4426950408889634f; p.trace = nullptr; p.alibi = alibi; p.window = window;
   static const bool want_trace = [] { const char* e = getenv("DSB200_PF_TRACE"); return e && atoi(e) != 0; }();
   static long long* trace_buf = nullptr;
   if (want_trace) {
@@ -975,10 +979,11 @@ DSB_EXPORT long long dsb200_paged_flash_scratch_bytes(int n_tokens, int hq, int 
 // [num_blocks][2][block_size][hkv][D] (bf16) through the block table.  max_atoms >= number of atoms of the batch
 // (<= n_tokens; ceil(n_tokens / (128/group)) + number of sequences is enough).  n_splits >= 1 splits the KV range of every atom.
 // alibi_slopes: optional [hq] fp32 (device): score += slope[head] * key position; NULL = none.
+// window > 0: local attention, a token sees its last `window` keys (itself included); 0 = the whole history.
 DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                                             const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                             int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                                            void* scratch, const float* alibi_slopes, cudaStream_t stream) {
+                                            void* scratch, const float* alibi_slopes, int window, cudaStream_t stream) {
   using namespace dsb;
   if (n_tokens == 0) return DSB_OK;
   DSB_REQUIRE(head_dim == 64 || head_dim == 128, "paged_flash: head_dim %d unsupported (64 or 128)", head_dim);
@@ -987,9 +992,9 @@ DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cach
   DSB_REQUIRE(max_atoms >= 1 && n_splits >= 1 && n_splits <= 64 && scratch != nullptr, "paged_flash: bad max_atoms / n_splits / scratch");
   if (head_dim == 128)
     return paged::launch<128>(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
+                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, window, stream);
   return paged::launch<64>(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                           num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
+                           num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, window, stream);
 }
 
 // Same contract as dsb200_paged_flash_attention for batches of small atoms (decode steps): atoms hold at most 16 / group tokens,
@@ -998,7 +1003,7 @@ DSB_EXPORT int dsb200_paged_flash_attention(const void* qkv, const void* kv_cach
 DSB_EXPORT int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                                          const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                          int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                                         void* scratch, const float* alibi_slopes, cudaStream_t stream) {
+                                         void* scratch, const float* alibi_slopes, int window, cudaStream_t stream) {
   using namespace dsb;
   if (n_tokens == 0) return DSB_OK;
   DSB_REQUIRE(head_dim == 128, "paged_flash_decode: head_dim %d unsupported (128)", head_dim);
@@ -1006,5 +1011,5 @@ DSB_EXPORT int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, 
   DSB_REQUIRE(block_size >= 8 && block_size <= 128 && 128 % block_size == 0, "paged_flash_decode: KV block size %d must divide 128", block_size);
   DSB_REQUIRE(max_atoms >= 1 && n_splits >= 1 && n_splits <= 64 && scratch != nullptr, "paged_flash_decode: bad max_atoms / n_splits / scratch");
   return paged::launch_decode(qkv, kv_cache, out, tok_seq, tok_pos, block_table, n_tokens, hq, hkv, block_size, max_blocks_per_seq,
-                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, stream);
+                              num_blocks, scale, max_atoms, n_splits, scratch, alibi_slopes, window, stream);
 }

@@ -9,8 +9,8 @@ from ....ops import native
 native.register_sigs({
     "dsb200_kv_rotary_append": "pppppp iiiiiii p",
     "dsb200_paged_attention": "pppppp iiiiii f p",
-    "dsb200_paged_flash_attention": "pppppp iiiiiii f ii p p p",
-    "dsb200_paged_flash_decode": "pppppp iiiiiii f ii p p p",
+    "dsb200_paged_flash_attention": "pppppp iiiiiii f ii p p i p",
+    "dsb200_paged_flash_decode": "pppppp iiiiiii f ii p p i p",
     "dsb200_paged_flash_scratch_bytes": "iiiii",
     "dsb200_ragged_embed": "ppppp iii p",
     "dsb200_logits_gather": "ppp ii p",
@@ -47,7 +47,7 @@ def kv_rotary_append(qkv, kv_cache, tok_seq, tok_pos, block_table, inv_freq, hq,
     return qkv
 
 
-def paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, alibi_slopes=None):
+def paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, alibi_slopes=None, window=0):
     T = qkv.shape[0]
     bs = kv_cache.shape[2]
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)
@@ -61,6 +61,8 @@ def paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d
         s = torch.einsum("hd,nhd->hn", q[t], k) * scale
         if alibi_slopes is not None:
             s = s + alibi_slopes.float().to(s.device)[:, None] * torch.arange(n, device=s.device, dtype=torch.float32)[None, :]
+        if window and n > window:
+            s[:, :n - window] = float("-inf")
         out[t] = torch.einsum("hn,nhd->hd", torch.softmax(s, -1), v).reshape(-1).to(qkv.dtype)
     return out
 
@@ -88,13 +90,14 @@ def _pick_splits(T, hq, d, ctas, pages, page_us=0.7):
 
 
 def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, n_splits=None,
-                          decode=None, alibi_slopes=None):
+                          decode=None, alibi_slopes=None, window=0):
     """Attention of every ragged token over its sequence's paged KV history on the tensor cores (csrc/attn/paged_flash.cu):
     atoms of up to 128/group tokens x kv head, KV pages fetched by TMA through the block table, prefill chunks and decode steps
     alike; small batches over long contexts are split along the KV axis (`n_splits`, chosen here unless given) and merged.
     `decode`: the batch is (almost) one token per sequence -- use the transposed small-atom kernel (keys on the MMA M axis,
     16 q rows per atom).  Default: when the batch has no more tokens than the block table has sequences and d == 128.
-    `alibi_slopes`: optional [hq] fp32 device tensor; adds slope[head] * key position to the scores (BLOOM-style ALiBi)."""
+    `alibi_slopes`: optional [hq] fp32 device tensor; adds slope[head] * key position to the scores (BLOOM-style ALiBi).
+    `window` > 0: local attention over the last `window` keys (GPT-Neo's local layers)."""
     scale = scale if scale is not None else 1.0 / math.sqrt(d)
     T = qkv.shape[0]
     bs, group = kv_cache.shape[2], hq // hkv
@@ -112,19 +115,20 @@ def paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv,
     fn = native.lib().dsb200_paged_flash_decode if decode else native.lib().dsb200_paged_flash_attention
     rc = fn(native.ptr(qkv), native.ptr(kv_cache), native.ptr(out), native.ptr(tok_seq), native.ptr(tok_pos), native.ptr(block_table), T, hq,
             hkv, d, bs, block_table.shape[1], kv_cache.shape[0], float(scale), max_atoms, n_splits, native.ptr(scratch),
-            native.ptr(alibi_slopes), native.stream_ptr())
+            native.ptr(alibi_slopes), int(window), native.stream_ptr())
     native.check(rc)
     return out
 
 
-def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, decode=None, alibi_slopes=None):
+def paged_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale=None, max_context=None, decode=None, alibi_slopes=None,
+                    window=0):
     scale = scale if scale is not None else 1.0 / math.sqrt(d)
     if not qkv.is_cuda:
-        return paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, alibi_slopes)
+        return paged_attention_ref(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, alibi_slopes, window)
     if paged_flash_supported(qkv, kv_cache, hq, hkv, d):
         return paged_flash_attention(qkv, kv_cache, tok_seq, tok_pos, block_table, hq, hkv, d, scale, max_context=max_context, decode=decode,
-                                     alibi_slopes=alibi_slopes)
-    assert alibi_slopes is None, "ALiBi needs the tensor-core kernel (bf16, head size 64 / 128)"
+                                     alibi_slopes=alibi_slopes, window=window)
+    assert alibi_slopes is None and not window, "ALiBi / local attention need the tensor-core kernel (bf16, head size 64 / 128)"
     # head sizes the tensor-core kernel does not cover (96, 256): CUDA-core kernel, one CTA per (token, kv head)
     T = qkv.shape[0]
     out = torch.empty(T, hq * d, dtype=qkv.dtype, device=qkv.device)

@@ -97,7 +97,8 @@ class DeepSpeedSelfAttention(nn.Module):
             if self._alibi_slopes is None:
                 self._alibi_slopes = alibi_slopes_of(alibi, B, self.heads)
             slopes = self._alibi_slopes
-        ctx = self.arena.attend(qkv, self.heads, self.kv_heads, self.head_dim, self.scale, inv_freq, rot, alibi_slopes=slopes)
+        window = int(cfg.window_size) if getattr(cfg, "local_attention", False) else 0
+        ctx = self.arena.attend(qkv, self.heads, self.kv_heads, self.head_dim, self.scale, inv_freq, rot, alibi_slopes=slopes, window=window)
         out = _linear(ctx, self.attn_ow, None)
         if self.mp_group is not None and cfg.mp_size > 1:
             from .... import comm as dist

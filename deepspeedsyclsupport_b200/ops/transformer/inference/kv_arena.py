@@ -43,12 +43,12 @@ def alibi_slopes_of(alibi, batch, heads):
 
 def eligible(x, head_dim, heads, kv_heads, cfg, input_mask, alibi, layer_past):
     """True when the step can run on the arena kernels: bf16 on the GPU, head size 64 / 128, plain causal masking; ALiBi as
-    per-head slopes (BLOOM).  Padding masks keep the general masked-softmax path."""
+    per-head slopes (BLOOM), local windows (GPT-Neo).  Padding masks keep the general masked-softmax path."""
     if not (x.is_cuda and x.dtype == torch.bfloat16 and head_dim in (64, 128)) or os.environ.get("DSB200_V1_ARENA", "1") == "0":
         return False
     if heads % kv_heads or 128 % (heads // kv_heads):
         return False
-    if layer_past is not None or not cfg.triangular_masking or getattr(cfg, "local_attention", False):
+    if layer_past is not None or not cfg.triangular_masking:
         return False
     if alibi is not None and (alibi.numel() < 2 * x.shape[0] * heads or x.shape[0] != 1 and input_mask is not None):
         return False  # slopes are read off the tensor: needs two key positions and unpadded sequences
@@ -83,7 +83,7 @@ class KVArena:
         self.cache, self.batch, self.per_seq = new, B, per_seq
         self.block_table = torch.arange(B * per_seq, device=device, dtype=torch.int32).view(B, per_seq)
 
-    def attend(self, qkv, heads, kv_heads, d, scale, inv_freq=None, rot_dim=0, alibi_slopes=None):
+    def attend(self, qkv, heads, kv_heads, d, scale, inv_freq=None, rot_dim=0, alibi_slopes=None, window=0):
         """qkv: [B, S, (heads + 2 kv_heads) * d], fresh projection output (rotated and consumed in place).
         Appends the S new rows of every sequence at positions [length, length + S) and returns the context [B, S, heads * d]."""
         from ....inference.v2 import kernels as K  # late: inference/ imports this package while it loads
@@ -97,7 +97,7 @@ class KVArena:
             inv_freq, rot_dim = torch.empty(1, device=qkv.device, dtype=torch.float32), 0
         K.kv_rotary_append(flat, self.cache, seq, pos, self.block_table, inv_freq, heads, kv_heads, d, rot_dim)
         ctx = K.paged_flash_attention(flat, self.cache, seq, pos, self.block_table, heads, kv_heads, d, scale, max_context=self.length + S,
-                                      alibi_slopes=alibi_slopes)
+                                      alibi_slopes=alibi_slopes, window=window)
         self.length += S
         return ctx.view(B, S, heads * d)
 

@@ -32,7 +32,7 @@ class SoftmaxContextOp(BaseOp):
         d = query_key_value.shape[-1] // (heads + 2 * kv)
         masked = cfg.triangular_masking and not no_masking
         plain = (attn_mask is None or attn_mask.numel() <= 1 or B == 1) and (alibi is None or alibi.numel() <= 1)
-        if masked and plain and layer_id not in self._cache and arena_eligible(query_key_value, d, heads, kv, cfg, None, None, None):
+        if masked and plain and not cfg.local_attention and layer_id not in self._cache and arena_eligible(query_key_value, d, heads, kv, cfg, None, None, None):
             # tensor-core path: rotary + append into the layer's arena, paged flash attention (kv_arena.py)
             arena = self._arenas.get(layer_id)
             if arena is None:

@@ -132,18 +132,19 @@ long long dsb200_paged_flash_scratch_bytes(int n_tokens, int hq, int head_dim, i
 /* out[t][hq*D] = attention of ragged token t over keys [0, tok_pos[t]] of its sequence, KV read from the blocked cache
  * [num_blocks][2][block_size][hkv][D] (bf16) through the block table.  max_atoms >= number of atoms of the batch
  * (<= n_tokens; ceil(n_tokens / (128/group)) + number of sequences is enough).  n_splits >= 1 splits the KV range of every atom.
- * alibi_slopes: optional [hq] fp32 (device): score += slope[head] * key position; NULL = none. */
+ * alibi_slopes: optional [hq] fp32 (device): score += slope[head] * key position; NULL = none.
+ * window > 0: local attention, a token sees its last `window` keys (itself included); 0 = the whole history. */
 int dsb200_paged_flash_attention(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                                  const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                                  int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                                 void* scratch, const float* alibi_slopes, dsb200_stream_t stream);
+                                 void* scratch, const float* alibi_slopes, int window, dsb200_stream_t stream);
 /* Same contract as dsb200_paged_flash_attention for batches of small atoms (decode steps): atoms hold at most 16 / group tokens,
  * keys take the M dimension of the MMAs (see paged_decode_kernel).  head_dim 128, q:kv head ratio dividing 16.
  * max_atoms >= ceil(n_tokens / (16/group)) + number of sequences (<= n_tokens). */
 int dsb200_paged_flash_decode(const void* qkv, const void* kv_cache, void* out, const int* tok_seq, const int* tok_pos,
                               const int* block_table, int n_tokens, int hq, int hkv, int head_dim, int block_size,
                               int max_blocks_per_seq, int num_blocks, float scale, int max_atoms, int n_splits,
-                              void* scratch, const float* alibi_slopes, dsb200_stream_t stream);
+                              void* scratch, const float* alibi_slopes, int window, dsb200_stream_t stream);
 
 /* ---- csrc/comm/symm.cu */
 /* ---- allocation / mapping (host pointers unless noted) */

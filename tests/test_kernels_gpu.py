@@ -1154,3 +1154,28 @@ def test_v1_attention_kv_arena_with_alibi(monkeypatch):
     assert a.arena.length == 94 and a._alibi_slopes is not None and b.arena.length == 0
     for oa, ob in zip(outs["arena"], outs["dense"]):
         assert (oa.float() - ob.float()).abs().max() < 0.04 * ob.float().abs().max() + 2e-3
+
+
+def test_v1_attention_kv_arena_with_local_window(monkeypatch):
+    """GPT-Neo style local attention (window 64) on the arena path equals the dense masked-softmax path, prompt longer than the
+    window plus decode steps."""
+    from deepspeedsyclsupport_b200.ops.transformer.inference import DeepSpeedInferenceConfig
+    from deepspeedsyclsupport_b200.ops.transformer.inference.ds_attention import DeepSpeedSelfAttention
+    torch.manual_seed(4)
+    heads, head_dim = 4, 128
+    H = heads * head_dim
+    cfg = DeepSpeedInferenceConfig(hidden_size=H, heads=heads, dtype=torch.bfloat16, max_out_tokens=256, triangular_masking=True,
+                                   local_attention=True, window_size=64)
+    a, b = DeepSpeedSelfAttention(cfg), DeepSpeedSelfAttention(cfg)
+    for name in ("attn_qkvw", "attn_qkvb", "attn_ow", "attn_ob"):
+        w = torch.randn_like(getattr(a, name).float()) * (0.05 if name.endswith("w") else 0.1)
+        getattr(a, name).data.copy_(w)
+        getattr(b, name).data.copy_(w)
+    steps = [torch.randn(2, 150, H, device="cuda").bfloat16()] + [torch.randn(2, 1, H, device="cuda").bfloat16() for _ in range(3)]
+    outs = {}
+    for tag, mod, flag in (("arena", a, "1"), ("dense", b, "0")):
+        monkeypatch.setenv("DSB200_V1_ARENA", flag)
+        outs[tag] = [mod(x.clone())[0] for x in steps]
+    assert a.arena.length == 153 and b.arena.length == 0
+    for oa, ob in zip(outs["arena"], outs["dense"]):
+        assert (oa.float() - ob.float()).abs().max() < 0.04 * ob.float().abs().max() + 2e-3

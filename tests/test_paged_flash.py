@@ -28,14 +28,14 @@ def _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed=0):
             torch.tensor(tok_pos, dtype=torch.int32, device=dev), block_table.to(dev))
 
 
-def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0, decode=None, alibi=False):
+def _check(seq_new, seq_seen, hq, hkv, d, bs, n_splits=None, seed=0, decode=None, alibi=False, window=0):
     from deepspeedsyclsupport_b200.inference.v2 import kernels as K
     qkv, kv, ts, tp, bt = _make_batch(seq_new, seq_seen, hq, hkv, d, bs, seed)
     scale = d ** -0.5
     slopes = (2.0 ** (-8.0 * torch.arange(1, hq + 1) / hq)).float().cuda() if alibi else None  # BLOOM's slopes for a power-of-two head count
-    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits, decode=decode, alibi_slopes=slopes).float()
+    got = K.paged_flash_attention(qkv, kv, ts, tp, bt, hq, hkv, d, scale, n_splits=n_splits, decode=decode, alibi_slopes=slopes, window=window).float()
     want = K.paged_attention_ref(qkv.cpu(), kv.cpu(), ts.cpu(), tp.cpu(), bt.cpu(), hq, hkv, d, scale,
-                                 None if slopes is None else slopes.cpu()).float().cuda()
+                                 None if slopes is None else slopes.cpu(), window).float().cuda()
     torch.cuda.synchronize()
     err = (got - want).abs().max().item()
     assert torch.isfinite(got).all() and err < 2e-2, (seq_new, seq_seen, hq, hkv, d, bs, n_splits, decode, err)
@@ -73,6 +73,14 @@ def test_alibi_slopes_in_both_kernels():
     _check(seq_new=[40, 1], seq_seen=[500, 129], hq=8, hkv=2, d=128, bs=64, seed=12, alibi=True, decode=False, n_splits=3)
     _check(seq_new=[1, 1, 1, 1], seq_seen=[0, 130, 1000, 2047], hq=16, hkv=16, d=128, bs=128, seed=13, alibi=True, decode=True)
     _check(seq_new=[1, 1], seq_seen=[700, 31], hq=8, hkv=1, d=128, bs=128, seed=14, alibi=True, decode=True, n_splits=2)
+
+
+def test_local_window_in_both_kernels():
+    # a token sees its last `window` keys only; windows shorter and longer than a 128-key page, with and without KV splits
+    _check(seq_new=[200, 1, 30], seq_seen=[0, 400, 250], hq=8, hkv=8, d=64, bs=128, seed=21, window=256, decode=False)
+    _check(seq_new=[50, 1], seq_seen=[300, 700], hq=8, hkv=2, d=128, bs=64, seed=22, window=100, decode=False, n_splits=2)
+    _check(seq_new=[1, 1, 1], seq_seen=[10, 255, 1500], hq=16, hkv=16, d=128, bs=128, seed=23, window=256, decode=True)
+    _check(seq_new=[1, 1], seq_seen=[900, 129], hq=8, hkv=1, d=128, bs=128, seed=24, window=64, decode=True, n_splits=3, alibi=True)
 
 
 def test_dispatch_uses_flash_kernel_and_falls_back():
