@@ -87,6 +87,15 @@ def test_analyzer_then_curriculum_sampler(tmp_path):
         assert seen_max[-1] <= limit, (step, seen_max)
     sd = sampler.state_dict()
     assert sd[CURRICULUM_LEARNING_STEP] == 10 and len(sd[CURRICULUM_LEARNING_DATA_CLUSTER_PATHS]) == 3
+    # resume: a fresh sampler loaded from the state (and the cluster files on disk) continues with the same batches
+    import copy
+    resumed = DeepSpeedDataSampler(cfg, one_epoch_total_samples=200, micro_batch_size=4, data_parallel_rank=0, data_parallel_size=1,
+                                   data_parallel_group=None, gradient_accumulation_steps=2, global_rank=0)
+    resumed.load_state_dict(copy.deepcopy(sd))
+    it2 = iter(resumed)
+    for _ in range(6):
+        assert next(it) == next(it2)
+    assert resumed.state_dict()[CURRICULUM_LEARNING_DATA_CLUSTER_CURRENT_POSITION] == sampler.state_dict()[CURRICULUM_LEARNING_DATA_CLUSTER_CURRENT_POSITION]
 
 
 def test_random_ltd_layer_cpu():
