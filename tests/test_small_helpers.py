@@ -87,3 +87,49 @@ def test_gemm_cpu_reference_path():
     a, b = torch.randn(5, 16).bfloat16(), torch.randn(7, 16).bfloat16()
     out = gemm(a, b)
     assert out.shape == (5, 7) and torch.allclose(out.float(), a.float() @ b.float().t(), atol=0.1, rtol=0.05)
+
+
+def test_alibi_slopes_are_read_off_the_tensor_and_arena_eligibility():
+    from types import SimpleNamespace
+    from deepspeedsyclsupport_b200.ops.transformer.inference.kv_arena import alibi_slopes_of, eligible
+    heads, T = 4, 9
+    slopes = 2.0 ** (-8.0 * torch.arange(1, heads + 1) / heads)
+    alibi = (slopes[:, None] * torch.arange(T)[None, :]).view(heads, 1, T)  # [batch * heads, 1, T] as HF BLOOM builds it (batch 1)
+    assert torch.allclose(alibi_slopes_of(alibi, 1, heads), slopes)
+    assert alibi_slopes_of(alibi[..., :1], 1, heads) is None  # one key position: the slope cannot be recovered
+    cfg = SimpleNamespace(triangular_masking=True, local_attention=False)
+    x = torch.zeros(1, 3, 8, dtype=torch.bfloat16)
+    assert not eligible(x, 64, heads, heads, cfg, None, None, None)  # CPU tensors never take the arena kernels
+
+
+def test_lazy_llama_state_names_and_shapes():
+    import bench_workloads
+    cfg = dict(vocab_size=64, hidden_size=32, intermediate_size=48, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2)
+    items = dict(bench_workloads._LazyLlamaState(cfg, "cpu", torch.float32).items())
+    assert items["model.embed_tokens.weight"].shape == (64, 32) and items["lm_head.weight"].shape == (64, 32)
+    assert items["model.layers.1.self_attn.k_proj.weight"].shape == (16, 32) and items["model.layers.0.mlp.down_proj.weight"].shape == (32, 48)
+    assert len(items) == 3 + 2 * 9 and abs(float(items["model.norm.weight"].mean()) - 1.0) < 0.05
+
+
+def test_fastgen_decode_runs_eagerly_on_cpu():
+    """forward_graphed is the engine's entry point; without a CUDA device pure decode steps must simply run the eager forward."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_inference_v2 import _dense_llama_logits, _hf_llama_state
+    from deepspeedsyclsupport_b200.inference.v2 import RaggedInferenceEngineConfig, build_engine_from_state_dict
+    cfg = dict(vocab_size=128, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4, num_key_value_heads=2,
+               rms_norm_eps=1e-5)
+    sd = _hf_llama_state(cfg)
+    ecfg = RaggedInferenceEngineConfig(state_manager={"max_ragged_batch_size": 64, "max_ragged_sequence_count": 4, "max_context": 128,
+                                                      "memory_config": {"mode": "allocate", "size": 32}})
+    eng = build_engine_from_state_dict("llama", cfg, sd, ecfg, dtype=torch.float32)
+    hist = torch.randint(0, 128, (11, ))
+    eng.put([7], [hist])
+    for _ in range(4):
+        nxt = torch.randint(0, 128, (1, ))
+        out = eng.put([7], [nxt])
+        hist = torch.cat([hist, nxt])
+        ref = _dense_llama_logits(sd, cfg, hist)[-1]
+        assert (out[0].float() - ref).abs().max() < 5e-3 * max(1.0, ref.abs().max().item())
+    assert not eng._model._graphs
