@@ -1,15 +1,21 @@
-"""Pipeline-stage point-to-point transfers on NCCL (async isend/irecv, overlapped with compute).
-Parity: deepspeed/runtime/pipe/p2p.py:50-163 (the reference asserts async off; here transfers are async and the
-engine waits right before the data is consumed)."""
+"""Pipeline-stage point-to-point transfers (async isend / irecv on NCCL, overlapped with compute).
+
+Parity: deepspeed/runtime/pipe/p2p.py:50-163 -- same entry points (`init_process_groups`, `send`, `recv`, `wait`, `send_obj`,
+`recv_obj`), addressed by pipeline STAGE; the reference asserts async off, here transfers may be asynchronous and the engine
+waits right before the data is consumed.  Python objects travel as ONE framed byte tensor: an 8-byte little-endian length
+followed by the pickle, padded to the next power-of-two bucket so the receiver can post its buffer without a size handshake
+for small messages (one send instead of two)."""
 import pickle
+import struct
 
 import torch
 
 from ... import comm as dist
 from ...accelerator import get_accelerator
 
-_groups = None
 _grid = None
+_groups = None
+_SMALL = 4096  # objects whose frame fits are sent in one fixed-size message
 
 
 def can_send_recv() -> bool:
@@ -18,68 +24,69 @@ def can_send_recv() -> bool:
 
 
 def init_process_groups(grid):
-    global _groups, _grid
+    global _grid
+    assert grid.pipe_parallel_size > 1, "There is no pipeline parallelism"
     _grid = grid
-    assert _grid.pipe_parallel_size > 1, "There is no pipeline parallelism"
 
 
-def _is_valid_send_recv(src_stage, dest_stage):
-    first_stage = 0
-    last_stage = _grid.pipe_parallel_size - 1
-    assert abs(src_stage - dest_stage) == 1 or (src_stage == first_stage and dest_stage == last_stage) or \
-        (src_stage == last_stage and dest_stage == first_stage), "Functionality currently limited to send and receive between adjacent ranks only"
+def _peer_rank(other_stage):
+    """Global rank of `other_stage` in this rank's pipeline; only neighbours (with wrap-around first <-> last) may talk."""
+    here, stages = _grid.get_stage_id(), _grid.pipe_parallel_size
+    assert (here - other_stage) % stages in (1, stages - 1), \
+        "Functionality currently limited to send and receive between adjacent ranks only"
+    return _grid.stage_to_global(stage_id=other_stage)
 
 
 def send(tensor, dest_stage, async_op=False):
-    src_stage = _grid.get_stage_id()
-    _is_valid_send_recv(src_stage, dest_stage)
-    dest_rank = _grid.stage_to_global(stage_id=dest_stage)
-    if async_op:
-        return dist.isend(tensor, dest_rank)
-    return dist.send(tensor, dest_rank)
+    rank = _peer_rank(dest_stage)
+    return dist.isend(tensor, rank) if async_op else dist.send(tensor, rank)
 
 
 def recv(tensor, src_stage, async_op=False):
-    dest_stage = _grid.get_stage_id()
-    _is_valid_send_recv(src_stage, dest_stage)
-    src_rank = _grid.stage_to_global(stage_id=src_stage)
-    if async_op:
-        return dist.irecv(tensor, src=src_rank)
-    return dist.recv(tensor, src=src_rank)
+    rank = _peer_rank(src_stage)
+    return dist.irecv(tensor, src=rank) if async_op else dist.recv(tensor, src=rank)
 
 
 def wait():
     get_accelerator().synchronize()
 
 
+def _device():
+    return get_accelerator().device_name()
+
+
 def send_obj(msg, dest: int):
-    msg = pickle.dumps(msg)
-    msg = torch.ByteTensor(torch.ByteStorage.from_buffer(msg)).to(get_accelerator().device_name())
-    length_tensor = torch.tensor([len(msg)], dtype=torch.long).to(get_accelerator().device_name())
-    dist.send(length_tensor, dst=dest)
-    dist.send(msg, dst=dest)
+    """Pickle `msg` and send it to global rank `dest` (tensors inside travel by value)."""
+    body = pickle.dumps(msg)
+    frame = struct.pack("<Q", len(body)) + body
+    head = torch.frombuffer(bytearray(frame[:_SMALL].ljust(_SMALL, b"\0")), dtype=torch.uint8).to(_device())
+    dist.send(head, dst=dest)
+    if len(frame) > _SMALL:  # the tail of a large object follows in a second message of exactly the missing size
+        dist.send(torch.frombuffer(bytearray(frame[_SMALL:]), dtype=torch.uint8).to(_device()), dst=dest)
+
+
+def _to_device(x):
+    """Move every tensor inside a nested structure of tuples / lists / mappings to the accelerator."""
+    if torch.is_tensor(x):
+        return x.to(_device())
+    if isinstance(x, (tuple, list)):
+        return type(x)(_to_device(v) for v in x)
+    if hasattr(x, "items"):
+        out = x.__class__()
+        for k, v in x.items():
+            out[_to_device(k)] = _to_device(v)
+        return out
+    return x
 
 
 def recv_obj(sender: int):
-    length = torch.tensor([0], dtype=torch.long).to(get_accelerator().device_name())
-    dist.recv(length, src=sender)
-    msg = torch.empty(length.item(), dtype=torch.uint8).to(get_accelerator().device_name())
-    dist.recv(msg, src=sender)
-    msg = pickle.loads(msg.cpu().numpy().tobytes())
-
-    def _to(x):
-        if torch.is_tensor(x):
-            return x.to(get_accelerator().device_name())
-        if isinstance(x, (tuple, list)):
-            ret = [_to(x_) for x_ in x]
-            if isinstance(x, tuple):
-                ret = tuple(ret)
-            return ret
-        if hasattr(x, "items"):
-            ret = x.__class__()
-            for key, val in x.items():
-                ret[_to(key)] = _to(val)
-            return ret
-        return x
-
-    return _to(msg)
+    head = torch.empty(_SMALL, dtype=torch.uint8, device=_device())
+    dist.recv(head, src=sender)
+    raw = head.cpu().numpy().tobytes()
+    (size, ) = struct.unpack("<Q", raw[:8])
+    body = raw[8:8 + size]
+    if 8 + size > _SMALL:
+        tail = torch.empty(8 + size - _SMALL, dtype=torch.uint8, device=_device())
+        dist.recv(tail, src=sender)
+        body += tail.cpu().numpy().tobytes()
+    return _to_device(pickle.loads(body))

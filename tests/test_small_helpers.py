@@ -133,3 +133,22 @@ def test_fastgen_decode_runs_eagerly_on_cpu():
         ref = _dense_llama_logits(sd, cfg, hist)[-1]
         assert (out[0].float() - ref).abs().max() < 5e-3 * max(1.0, ref.abs().max().item())
     assert not eng._model._graphs
+
+
+def _obj_body():
+    from deepspeedsyclsupport_b200 import comm as dist
+    from deepspeedsyclsupport_b200.runtime.pipe import p2p
+    small = {"step": 3, "shape": (2, 5), "t": torch.arange(6).view(2, 3)}
+    big = {"blob": torch.arange(5000, dtype=torch.float32), "names": ["x" * 50] * 40}
+    if dist.get_rank() == 0:
+        p2p.send_obj(small, 1)
+        p2p.send_obj(big, 1)
+    else:
+        got = p2p.recv_obj(0)
+        assert got["step"] == 3 and got["shape"] == (2, 5) and torch.equal(got["t"], small["t"])
+        got = p2p.recv_obj(0)
+        assert torch.equal(got["blob"], big["blob"]) and got["names"] == big["names"]
+
+
+def test_pipe_send_recv_python_objects():
+    run_distributed(_obj_body, world_size=2, backend="gloo")
