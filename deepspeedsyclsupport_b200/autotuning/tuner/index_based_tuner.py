@@ -1,29 +1,36 @@
-"""Exhaustive and random search over the experiment list (parity: tuner/index_based_tuner.py)."""
+"""Exhaustive and random search over the experiment list (parity: tuner/index_based_tuner.py).  Both tuners hand out the remaining
+experiments in batches; they differ only in which ones leave the pool first."""
 import random
 
 from .base_tuner import BaseTuner
 
 
-class RandomTuner(BaseTuner):
+class _PoolTuner(BaseTuner):
+
+    def __init__(self, exps: list, resource_manager, metric):
+        super().__init__(exps, resource_manager, metric)
+
+    def _positions(self, count):
+        """Indices into self.all_exps of the next `count` experiments."""
+        raise NotImplementedError
+
+    def next_batch(self, sample_size=1):
+        take = sorted(self._positions(min(sample_size, len(self.all_exps))))
+        chosen = [self.all_exps[i] for i in take]
+        for i in reversed(take):
+            del self.all_exps[i]
+        return chosen
+
+
+class RandomTuner(_PoolTuner):
     """Explore the search space in random order"""
 
-    def __init__(self, exps: list, resource_manager, metric):
-        super().__init__(exps, resource_manager, metric)
-
-    def next_batch(self, sample_size=1):
-        sample_size = min(sample_size, len(self.all_exps))
-        picked = random.sample(self.all_exps, sample_size)
-        self.all_exps = [x for x in self.all_exps if x not in picked]
-        return picked
+    def _positions(self, count):
+        return random.sample(range(len(self.all_exps)), count)
 
 
-class GridSearchTuner(BaseTuner):
+class GridSearchTuner(_PoolTuner):
     """Explore the search space in sequential order"""
 
-    def __init__(self, exps: list, resource_manager, metric):
-        super().__init__(exps, resource_manager, metric)
-
-    def next_batch(self, sample_size=1):
-        sample_size = min(sample_size, len(self.all_exps))
-        picked, self.all_exps = self.all_exps[:sample_size], self.all_exps[sample_size:]
-        return picked
+    def _positions(self, count):
+        return list(range(count))

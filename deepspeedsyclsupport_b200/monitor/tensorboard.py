@@ -1,40 +1,47 @@
-"""TensorBoard backend (parity: deepspeed/monitor/tensorboard.py)."""
+"""TensorBoard backend (parity: deepspeed/monitor/tensorboard.py): scalars written by the global rank 0 only."""
 import os
 
 from .. import comm as dist
 from ..utils.logging import logger
 from .monitor import Monitor
 
+_DEFAULT_ROOT = os.path.join(os.path.expanduser("~"), "tensorboard")
+
 
 class TensorBoardMonitor(Monitor):
 
     def __init__(self, tensorboard_config):
         super().__init__(tensorboard_config)
-        self.enabled = tensorboard_config.enabled
-        self.output_path = tensorboard_config.output_path
-        self.job_name = tensorboard_config.job_name
+        cfg = tensorboard_config
+        self.enabled, self.output_path, self.job_name = cfg.enabled, cfg.output_path, cfg.job_name
         self.summary_writer = None
-        if self.enabled and dist.get_rank() == 0:
+        if self._active():
             self.get_summary_writer()
 
-    def get_summary_writer(self, base=os.path.join(os.path.expanduser("~"), "tensorboard")):
+    def _active(self):
+        return self.enabled and dist.get_rank() == 0
+
+    def get_summary_writer(self, base=_DEFAULT_ROOT):
+        """Create the writer under <output_path or ~/tensorboard>/<job_name>; a missing tensorboard package disables the backend."""
         try:
             from torch.utils.tensorboard import SummaryWriter
         except ImportError:
             logger.warning("tensorboard is not installed: TensorBoard monitor disabled")
             self.enabled = False
             return None
-        log_dir = os.path.join(self.output_path, self.job_name) if self.output_path else os.path.join(base, self.job_name)
-        os.makedirs(log_dir, exist_ok=True)
-        self.summary_writer = SummaryWriter(log_dir=log_dir)
+        where = os.path.join(self.output_path or base, self.job_name)
+        os.makedirs(where, exist_ok=True)
+        self.summary_writer = SummaryWriter(log_dir=where)
         return self.summary_writer
 
     def write_events(self, event_list, flush=True):
-        if self.enabled and self.summary_writer is not None and dist.get_rank() == 0:
-            for event in event_list:
-                self.summary_writer.add_scalar(*event)
-            if flush:
-                self.summary_writer.flush()
+        """event = (tag, value, step)"""
+        if not self._active() or self.summary_writer is None:
+            return
+        for tag, value, step, *_ in event_list:
+            self.summary_writer.add_scalar(tag, value, step)
+        if flush:
+            self.flush()
 
     def flush(self):
         if self.summary_writer is not None:

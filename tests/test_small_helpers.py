@@ -152,3 +152,35 @@ def _obj_body():
 
 def test_pipe_send_recv_python_objects():
     run_distributed(_obj_body, world_size=2, backend="gloo")
+
+
+def test_index_tuners_hand_out_every_experiment_once():
+    import random
+    from deepspeedsyclsupport_b200.autotuning.tuner.index_based_tuner import GridSearchTuner, RandomTuner
+    exps = [{"name": f"e{i}", "ds_config": {}} for i in range(7)]
+    grid = GridSearchTuner(list(exps), None, "throughput")
+    assert [e["name"] for e in grid.next_batch(3)] == ["e0", "e1", "e2"] and [e["name"] for e in grid.next_batch(10)] == ["e3", "e4", "e5", "e6"]
+    assert grid.next_batch(2) == []
+    random.seed(0)
+    rnd = RandomTuner(list(exps), None, "throughput")
+    seen = []
+    while True:
+        batch = rnd.next_batch(2)
+        if not batch:
+            break
+        seen += [e["name"] for e in batch]
+    assert sorted(seen) == [f"e{i}" for i in range(7)] and seen != [f"e{i}" for i in range(7)]
+
+
+def test_monitor_master_builds_only_enabled_backends(tmp_path):
+    from types import SimpleNamespace
+    from deepspeedsyclsupport_b200.monitor.monitor import MonitorMaster
+    off = SimpleNamespace(enabled=False)
+    cfg = SimpleNamespace(enabled=True, tensorboard=off, wandb=off,
+                          csv_monitor=SimpleNamespace(enabled=True, output_path=str(tmp_path), job_name="run"))
+    mm = MonitorMaster(cfg)
+    assert mm.tb_monitor is None and mm.wandb_monitor is None and mm.csv_monitor is not None
+    mm.write_events([("a/b", 1.0, 1)])
+    assert os.path.exists(os.path.join(tmp_path, "run", "a_b.csv"))
+    from deepspeedsyclsupport_b200.monitor import monitor as M
+    assert M.csvMonitor.__name__ == "csvMonitor" and M.TensorBoardMonitor.__name__ == "TensorBoardMonitor"
